@@ -1,0 +1,359 @@
+// elementwise.cu -- the small HBM/latency-bound kernels between the GEMMs and attention:
+// embedding gather, residual-add + RMSNorm, QK-norm + RoPE + KV page write, SwiGLU gate,
+// argmax helpers and the device-side decode bookkeeping.  Each kernel states the HF line it
+// reproduces and where it rounds to bf16 (the rounding points are the parity contract).
+#include "kernels.h"
+
+namespace b2 {
+
+// ---------------------------------------------------------------------------------------
+// a1: nn.Embedding lookup, HF:models/qwen3/modeling_qwen3.py:363,392
+// ---------------------------------------------------------------------------------------
+__global__ void embed_kernel(const int32_t* __restrict__ ids, const bf16* __restrict__ table, bf16* __restrict__ h,
+                             int H, int vocab) {
+  int t = blockIdx.x;
+  int id = ids[t];
+  if (id < 0 || id >= vocab) id = 0;
+  const uint4* src = reinterpret_cast<const uint4*>(table + (size_t)id * H);
+  uint4* dst = reinterpret_cast<uint4*>(h + (size_t)t * H);
+  for (int i = threadIdx.x; i < H / 8; i += blockDim.x) dst[i] = src[i];
+}
+
+int launch_embed(const int32_t* ids, const bf16* table, bf16* h, int T, int H, int vocab, cudaStream_t s) {
+  if (T <= 0) return 0;
+  embed_kernel<<<T, 128, 0, s>>>(ids, table, h, H, vocab);
+  B2_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+__global__ void gather_rows_kernel(const bf16* __restrict__ src, const int32_t* __restrict__ rows, bf16* __restrict__ dst,
+                                   int H) {
+  int r = rows[blockIdx.x];
+  const uint4* s = reinterpret_cast<const uint4*>(src + (size_t)r * H);
+  uint4* d = reinterpret_cast<uint4*>(dst + (size_t)blockIdx.x * H);
+  for (int i = threadIdx.x; i < H / 8; i += blockDim.x) d[i] = s[i];
+}
+int launch_gather_rows(const bf16* src, const int32_t* rows, bf16* dst, int n, int H, cudaStream_t s) {
+  if (n <= 0) return 0;
+  gather_rows_kernel<<<n, 128, 0, s>>>(src, rows, dst, H);
+  B2_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------
+// a2 + a9: residual add (HF:...:327,333) fused with Qwen3RMSNorm.forward (HF:...:59-64).
+//   o      = bf16(sum of split-K partials)            (nn.Linear rounds its output)
+//   h      = bf16(h + o)                              (bf16 tensor add)
+//   x      = bf16(w * bf16(float(h) * rsqrt(mean(h^2) + eps)))
+// One CTA per token, H/8 threads, one 16-byte vector per thread.
+// ---------------------------------------------------------------------------------------
+template <int MODE>  // 0: no delta, 1: bf16 delta, 2: fp32 partials
+__global__ void add_rmsnorm_kernel(bf16* __restrict__ h, const void* __restrict__ delta, int nsplit, size_t split_stride,
+                                   const bf16* __restrict__ w, bf16* __restrict__ x, int H, float eps) {
+  __shared__ float red[32];
+  const int t = blockIdx.x;
+  const int i = threadIdx.x;  // vector index, 8 elements
+  float v[8];
+  uint4 hv = reinterpret_cast<const uint4*>(h + (size_t)t * H)[i];
+  unpack8(hv, v);
+  if (MODE == 1) {
+    float d[8];
+    unpack8(reinterpret_cast<const uint4*>(reinterpret_cast<const bf16*>(delta) + (size_t)t * H)[i], d);
+#pragma unroll
+    for (int e = 0; e < 8; ++e) v[e] = bf16_round(v[e] + d[e]);
+  } else if (MODE == 2) {
+    float d[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) d[e] = 0.f;
+    const float* p = reinterpret_cast<const float*>(delta) + (size_t)t * H + (size_t)i * 8;
+    for (int s = 0; s < nsplit; ++s) {
+      float4 a = reinterpret_cast<const float4*>(p + s * split_stride)[0];
+      float4 b = reinterpret_cast<const float4*>(p + s * split_stride)[1];
+      d[0] += a.x; d[1] += a.y; d[2] += a.z; d[3] += a.w;
+      d[4] += b.x; d[5] += b.y; d[6] += b.z; d[7] += b.w;
+    }
+#pragma unroll
+    for (int e = 0; e < 8; ++e) v[e] = bf16_round(v[e] + bf16_round(d[e]));
+  }
+  if (MODE != 0) reinterpret_cast<uint4*>(h + (size_t)t * H)[i] = pack8(v);
+
+  float ss = 0.f;
+#pragma unroll
+  for (int e = 0; e < 8; ++e) ss += v[e] * v[e];
+  ss = warp_sum(ss);
+  const int nw = blockDim.x >> 5;
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
+  __syncthreads();
+  float tot = 0.f;
+  for (int k = 0; k < nw; ++k) tot += red[k];
+  const float var = tot / (float)H;
+  const float rstd = __fdiv_rn(1.0f, __fsqrt_rn(var + eps));
+  float wv[8];
+  unpack8(reinterpret_cast<const uint4*>(w)[i], wv);
+#pragma unroll
+  for (int e = 0; e < 8; ++e) v[e] = bf16_round(wv[e] * bf16_round(v[e] * rstd));
+  reinterpret_cast<uint4*>(x + (size_t)t * H)[i] = pack8(v);
+}
+
+int launch_add_rmsnorm(bf16* h, ActIn delta, const bf16* w, bf16* x, int T, int H, float eps, cudaStream_t s) {
+  if (T <= 0) return 0;
+  B2_REQUIRE(H % 256 == 0 && H <= 8192, "add_rmsnorm: hidden %d must be a multiple of 256 and <= 8192", H);
+  const int threads = H / 8;
+  if (delta.ptr == nullptr)
+    add_rmsnorm_kernel<0><<<T, threads, 0, s>>>(h, nullptr, 0, 0, w, x, H, eps);
+  else if (!delta.is_f32)
+    add_rmsnorm_kernel<1><<<T, threads, 0, s>>>(h, delta.ptr, 1, 0, w, x, H, eps);
+  else
+    add_rmsnorm_kernel<2><<<T, threads, 0, s>>>(h, delta.ptr, delta.nsplit, (size_t)T * H, w, x, H, eps);
+  B2_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------
+// a4 + a5 + a6: per-head RMSNorm of q and k (HF:...:248-249,263-264), RoPE with the half-split
+// rotate (HF:...:151-181; cos/sin were rounded to bf16, HF:...:148) and the KV page write
+// (HF:...:270-271).  One warp per (token, head); lane l owns elements 4l..4l+3, so the RoPE
+// partner element i +/- 64 lives in lane l ^ 16.
+//   n  = bf16(w * bf16(q * rsqrt(mean(q^2)+eps)))
+//   q' = bf16(bf16(n*cos) + bf16(rot(n)*sin))
+// ---------------------------------------------------------------------------------------
+template <bool F32IN>
+__global__ void qknorm_rope_kv_kernel(const void* __restrict__ qkv, int nsplit, size_t split_stride,
+                                      const bf16* __restrict__ qw, const bf16* __restrict__ kw,
+                                      const bf16* __restrict__ cos_sin, const int32_t* __restrict__ positions,
+                                      const int32_t* __restrict__ slots, bf16* __restrict__ q_out,
+                                      bf16* __restrict__ k_pages, bf16* __restrict__ v_pages, int T, int nq, int nkv,
+                                      int block_size, float eps) {
+  constexpr int HD = 128;
+  const int nheads = nq + 2 * nkv;
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (warp >= T * nheads) return;
+  const int t = warp / nheads;
+  const int head = warp % nheads;
+  const size_t row = (size_t)t * nheads * HD + (size_t)head * HD + lane * 4;
+
+  float v[4];
+  if (F32IN) {
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    const float* p = reinterpret_cast<const float*>(qkv) + row;
+    for (int s = 0; s < nsplit; ++s) {
+      float4 a = *reinterpret_cast<const float4*>(p + s * split_stride);
+      acc.x += a.x; acc.y += a.y; acc.z += a.z; acc.w += a.w;
+    }
+    v[0] = bf16_round(acc.x); v[1] = bf16_round(acc.y); v[2] = bf16_round(acc.z); v[3] = bf16_round(acc.w);
+  } else {
+    uint2 a = *reinterpret_cast<const uint2*>(reinterpret_cast<const bf16*>(qkv) + row);
+    v[0] = bf16lo(a.x); v[1] = bf16hi(a.x); v[2] = bf16lo(a.y); v[3] = bf16hi(a.y);
+  }
+
+  const bool is_q = head < nq;
+  const bool is_k = !is_q && head < nq + nkv;
+  if (is_q || is_k) {
+    float ss = v[0] * v[0] + v[1] * v[1] + v[2] * v[2] + v[3] * v[3];
+    ss = warp_sum(ss);
+    const float rstd = __fdiv_rn(1.0f, __fsqrt_rn(ss / (float)HD + eps));
+    uint2 wraw = *reinterpret_cast<const uint2*>((is_q ? qw : kw) + lane * 4);
+    const float wv[4] = {bf16lo(wraw.x), bf16hi(wraw.x), bf16lo(wraw.y), bf16hi(wraw.y)};
+    const int pos = max(positions[t], 0);
+    const bf16* cs = cos_sin + (size_t)pos * HD;
+    const int ci = (lane * 4) & 63;
+    uint2 craw = *reinterpret_cast<const uint2*>(cs + ci);
+    uint2 sraw = *reinterpret_cast<const uint2*>(cs + 64 + ci);
+    const float c[4] = {bf16lo(craw.x), bf16hi(craw.x), bf16lo(craw.y), bf16hi(craw.y)};
+    const float sn[4] = {bf16lo(sraw.x), bf16hi(sraw.x), bf16lo(sraw.y), bf16hi(sraw.y)};
+#pragma unroll
+    for (int e = 0; e < 4; ++e) v[e] = bf16_round(wv[e] * bf16_round(v[e] * rstd));
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      float partner = __shfl_xor_sync(0xffffffffu, v[e], 16);
+      float rot = (lane < 16) ? -partner : partner;
+      v[e] = bf16_round(bf16_round(v[e] * c[e]) + bf16_round(rot * sn[e]));
+    }
+  }
+  uint2 o;
+  o.x = pack_bf16x2(v[0], v[1]);
+  o.y = pack_bf16x2(v[2], v[3]);
+  if (is_q) {
+    *reinterpret_cast<uint2*>(q_out + ((size_t)t * nq + head) * HD + lane * 4) = o;
+  } else {
+    const int slot = slots[t];
+    if (slot < 0) return;
+    const int kvh = is_k ? head - nq : head - nq - nkv;
+    const int blk = slot / block_size, off = slot % block_size;
+    bf16* base = is_k ? k_pages : v_pages;
+    *reinterpret_cast<uint2*>(base + (((size_t)blk * nkv + kvh) * block_size + off) * HD + lane * 4) = o;
+  }
+}
+
+int launch_qknorm_rope_kv(ActIn qkv, const bf16* qw, const bf16* kw, const bf16* cos_sin, const int32_t* positions,
+                          const int32_t* slots, bf16* q_out, bf16* k_pages, bf16* v_pages, int T, int nq, int nkv,
+                          int hd, int block_size, float eps, cudaStream_t s) {
+  if (T <= 0) return 0;
+  B2_REQUIRE(hd == 128, "qknorm_rope_kv: head_dim %d not built (128 only)", hd);
+  const int nheads = nq + 2 * nkv;
+  const long long warps = (long long)T * nheads;
+  const int blocks = (int)((warps + 3) / 4);
+  if (qkv.is_f32)
+    qknorm_rope_kv_kernel<true><<<blocks, 128, 0, s>>>(qkv.ptr, qkv.nsplit, (size_t)T * nheads * hd, qw, kw, cos_sin,
+                                                       positions, slots, q_out, k_pages, v_pages, T, nq, nkv,
+                                                       block_size, eps);
+  else
+    qknorm_rope_kv_kernel<false><<<blocks, 128, 0, s>>>(qkv.ptr, 1, 0, qw, kw, cos_sin, positions, slots, q_out,
+                                                        k_pages, v_pages, T, nq, nkv, block_size, eps);
+  B2_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------
+// a8 (middle): act = bf16( bf16(silu(gate)) * up ), HF:...:81-83.  gate/up are the bf16-rounded
+// outputs of their Linear layers; silu is evaluated in fp32 as x / (1 + exp(-x)).
+// ---------------------------------------------------------------------------------------
+template <bool F32IN>
+__global__ void silu_mul_kernel(const void* __restrict__ gu, int nsplit, size_t split_stride, bf16* __restrict__ act,
+                                int T, int I) {
+  const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;  // vector of 8 over [T][I]
+  const size_t nvec = (size_t)T * I / 8;
+  if (idx >= nvec) return;
+  const int t = (int)(idx / (I / 8));
+  const int i = (int)(idx % (I / 8)) * 8;
+  float g[8], u[8];
+  if (F32IN) {
+#pragma unroll
+    for (int e = 0; e < 8; ++e) g[e] = u[e] = 0.f;
+    const float* pg = reinterpret_cast<const float*>(gu) + (size_t)t * 2 * I + i;
+    const float* pu = pg + I;
+    for (int s = 0; s < nsplit; ++s) {
+      float4 a = reinterpret_cast<const float4*>(pg + s * split_stride)[0];
+      float4 b = reinterpret_cast<const float4*>(pg + s * split_stride)[1];
+      float4 c = reinterpret_cast<const float4*>(pu + s * split_stride)[0];
+      float4 d = reinterpret_cast<const float4*>(pu + s * split_stride)[1];
+      g[0] += a.x; g[1] += a.y; g[2] += a.z; g[3] += a.w; g[4] += b.x; g[5] += b.y; g[6] += b.z; g[7] += b.w;
+      u[0] += c.x; u[1] += c.y; u[2] += c.z; u[3] += c.w; u[4] += d.x; u[5] += d.y; u[6] += d.z; u[7] += d.w;
+    }
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      g[e] = bf16_round(g[e]);
+      u[e] = bf16_round(u[e]);
+    }
+  } else {
+    const bf16* p = reinterpret_cast<const bf16*>(gu) + (size_t)t * 2 * I + i;
+    unpack8(*reinterpret_cast<const uint4*>(p), g);
+    unpack8(*reinterpret_cast<const uint4*>(p + I), u);
+  }
+  float o[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) {
+    float sl = bf16_round(__fdiv_rn(g[e], 1.0f + expf(-g[e])));
+    o[e] = bf16_round(sl * u[e]);
+  }
+  *reinterpret_cast<uint4*>(act + (size_t)t * I + i) = pack8(o);
+}
+
+int launch_silu_mul(ActIn gu, bf16* act, int T, int I, cudaStream_t s) {
+  if (T <= 0) return 0;
+  B2_REQUIRE(I % 8 == 0, "silu_mul: intermediate %d must be a multiple of 8", I);
+  const size_t nvec = (size_t)T * I / 8;
+  const int blocks = (int)((nvec + 255) / 256);
+  if (gu.is_f32)
+    silu_mul_kernel<true><<<blocks, 256, 0, s>>>(gu.ptr, gu.nsplit, (size_t)T * 2 * I, act, T, I);
+  else
+    silu_mul_kernel<false><<<blocks, 256, 0, s>>>(gu.ptr, 1, 0, act, T, I);
+  B2_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------
+// a11: greedy argmax over bf16 logits, lowest index on ties (torch.argmax on CPU).
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ unsigned long long argmax_pack(float v, int idx) {
+  uint32_t b = __float_as_uint(v);
+  uint32_t key = (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+  return ((unsigned long long)key << 32) | (unsigned long long)(0xffffffffu - (uint32_t)idx);
+}
+
+__global__ void argmax_rows_kernel(const bf16* __restrict__ logits, int32_t* __restrict__ out, int V) {
+  __shared__ unsigned long long red[32];
+  const bf16* row = logits + (size_t)blockIdx.x * V;
+  unsigned long long best = 0;
+  for (int i = threadIdx.x; i < V; i += blockDim.x) {
+    float v = __bfloat162float(row[i]);
+    if (v == v) {
+      unsigned long long p = argmax_pack(v, i);
+      best = p > best ? p : best;
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    unsigned long long other = __shfl_xor_sync(0xffffffffu, best, o);
+    best = other > best ? other : best;
+  }
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = best;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int k = 1; k < (int)(blockDim.x >> 5); ++k) best = red[k] > best ? red[k] : best;
+    out[blockIdx.x] = (int32_t)(0xffffffffu - (uint32_t)(best & 0xffffffffull));
+  }
+}
+int launch_argmax_rows(const bf16* logits, int32_t* out, int T, int V, cudaStream_t s) {
+  if (T <= 0) return 0;
+  argmax_rows_kernel<<<T, 1024, 0, s>>>(logits, out, V);
+  B2_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+__global__ void argmax_finalize_kernel(const unsigned long long* __restrict__ packed, int32_t* __restrict__ out, int T) {
+  int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t < T) out[t] = (int32_t)(0xffffffffu - (uint32_t)(packed[t] & 0xffffffffull));
+}
+int launch_argmax_finalize(const unsigned long long* packed, int32_t* out, int T, cudaStream_t s) {
+  if (T <= 0) return 0;
+  argmax_finalize_kernel<<<(T + 127) / 128, 128, 0, s>>>(packed, out, T);
+  B2_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------
+// decode bookkeeping: one thread per sequence of the running batch.
+// ---------------------------------------------------------------------------------------
+__global__ void decode_advance_kernel(int32_t* positions, int32_t* seq_lens, int32_t* slots,
+                                      const int32_t* __restrict__ block_table, int bt_stride, int block_size, int B) {
+  int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= B) return;
+  if (positions[b] < -1) {  // padding row of a graph bucket
+    seq_lens[b] = 0;
+    slots[b] = -1;
+    return;
+  }
+  int pos = positions[b] + 1;
+  positions[b] = pos;
+  seq_lens[b] = pos + 1;
+  int blk = block_table[(size_t)b * bt_stride + pos / block_size];
+  slots[b] = blk * block_size + pos % block_size;
+}
+int launch_decode_advance(int32_t* positions, int32_t* seq_lens, int32_t* slots, const int32_t* block_table,
+                          int bt_stride, int block_size, int B, cudaStream_t s) {
+  if (B <= 0) return 0;
+  decode_advance_kernel<<<(B + 127) / 128, 128, 0, s>>>(positions, seq_lens, slots, block_table, bt_stride, block_size, B);
+  B2_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+__global__ void logits_to_f32_kernel(const bf16* __restrict__ in, float* __restrict__ out, size_t n) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = __bfloat162float(in[i]);
+}
+int launch_logits_to_f32(const bf16* in, float* out, size_t n, cudaStream_t s) {
+  if (n == 0) return 0;
+  logits_to_f32_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(in, out, n);
+  B2_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+int device_num_sms() {
+  int dev = 0, n = 148;
+  if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+  return n;
+}
+
+}  // namespace b2

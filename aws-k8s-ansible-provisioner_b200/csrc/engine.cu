@@ -1,0 +1,1153 @@
+// engine.cu -- the model engine behind the C ABI (include/b2_engine.h): weights resident in
+// HBM, paged KV pool + block allocator, the Qwen3 layer loop (HF:models/qwen3/
+// modeling_qwen3.py:378-438, :305-334) as a stream of hand-written kernels, CUDA-graph replay
+// of the decode step, and the measurement hooks bench.py uses.
+#include <fcntl.h>
+#include <math.h>
+#include <stdarg.h>
+#include <string.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <unistd.h>
+
+#include <algorithm>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "../../include/b2_engine.h"
+#include "json.hpp"
+#include "kernels.h"
+
+// ---------------------------------------------------------------------------------------
+static thread_local char g_err[1024] = "";
+void b2_set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof g_err, fmt, ap);
+  va_end(ap);
+}
+extern "C" const char* b2_last_error(void) { return g_err; }
+extern "C" int b2_abi_version(void) { return B2_ABI_VERSION; }
+
+using namespace b2;
+
+namespace {
+
+struct LayerW {
+  bf16 *ln1 = nullptr, *ln2 = nullptr, *qnorm = nullptr, *knorm = nullptr;
+  bf16 *wqkv = nullptr, *wo = nullptr, *wgu = nullptr, *wd = nullptr;
+  CUtensorMap tm_qkv, tm_o, tm_gu, tm_d;
+};
+
+struct Seq {
+  bool active = false;
+  int len = 0;        // tokens whose K/V are in the cache
+  int reserved = 0;   // token capacity of the pages held
+  std::vector<int32_t> blocks;
+};
+
+enum XBuf { XB_X = 0, XB_ATTN = 1, XB_ACT = 2, XB_LAST = 3, XB_COUNT = 4 };
+static const int kBnList[5] = {16, 32, 64, 128, 256};
+static int bn_index(int bn) { return bn == 16 ? 0 : bn == 32 ? 1 : bn == 64 ? 2 : bn == 128 ? 3 : 4; }
+
+struct GraphKey {
+  int B, attn_split;
+  bool operator<(const GraphKey& o) const { return B != o.B ? B < o.B : attn_split < o.attn_split; }
+};
+
+}  // namespace
+
+struct b2_engine {
+  b2_config cfg;
+  int device = 0;
+  int num_sms = 148;
+  cudaStream_t stream = nullptr;
+  bool finalized = false;
+  int q_size = 0, kv_size = 0, qkv_size = 0;
+
+  // weights
+  bf16* embed = nullptr;
+  bf16* lm_head = nullptr;  // == embed when tied
+  bf16* final_norm = nullptr;
+  std::vector<LayerW> layers;
+  CUtensorMap tm_lm_head;
+  std::map<std::string, int> loaded;
+  int64_t weight_bytes = 0;
+  bf16* cos_sin = nullptr;  // [max_model_len][hd]: cos[hd/2] | sin[hd/2]
+
+  // KV pool
+  bf16* kv_pool = nullptr;
+  int64_t num_blocks = 0;
+  size_t layer_kv_elems = 0;  // elements of one layer's K (or V) pool
+  std::vector<int32_t> free_blocks;
+  std::vector<Seq> seqs;
+  int bt_stride = 0;
+
+  // activations (capacity rows = cap_tokens)
+  int cap_tokens = 0;
+  bf16 *h = nullptr, *x = nullptr, *qkv = nullptr, *qrot = nullptr, *attn = nullptr, *gu = nullptr, *act = nullptr,
+       *proj = nullptr, *xlast = nullptr;
+  float* partial = nullptr;
+  size_t partial_floats = 0;
+  float* attn_scratch = nullptr;
+  size_t attn_scratch_floats = 0;
+  CUtensorMap tm_x[XB_COUNT][5];
+
+  // batch state on the device
+  int32_t *d_tokens = nullptr, *d_positions = nullptr, *d_seq_lens = nullptr, *d_slots = nullptr, *d_block_table = nullptr,
+          *d_last_rows = nullptr, *d_out_tokens = nullptr, *d_token_log = nullptr, *d_step = nullptr;
+  unsigned long long* d_argmax = nullptr;
+  PrefillTile* d_tiles = nullptr;
+  int tiles_cap = 0;
+  int log_cap_steps = 0;
+  // pinned host staging
+  int32_t* h_stage = nullptr;
+  size_t h_stage_ints = 0;
+  PrefillTile* h_tiles = nullptr;
+  int32_t* h_out = nullptr;
+
+  std::vector<int32_t> cur_batch;  // sequence ids resident in d_* (decode fast path)
+  int cur_B = 0;                   // padded batch (graph bucket)
+  int last_n = 0;                  // sequences in the last forward
+  int last_tokens = 0;             // tokens in the last forward
+
+  // debug capture
+  int debug_flags = 0;
+  bf16* dbg_hidden = nullptr;
+  int dbg_cap_tokens = 0;
+  bf16* logits = nullptr;  // [max_seqs][vocab], allocated on demand
+
+  // graphs
+  std::map<GraphKey, cudaGraphExec_t> graphs;
+  std::map<GraphKey, int64_t> graph_nodes;
+  int64_t launches = 0;
+
+  // profiling
+  bool profiling = false;
+  std::vector<cudaEvent_t> ev_pool;
+  std::vector<std::pair<int, int>> ev_used;  // (class, index of start event)
+  int ev_next = 0;
+
+  // tunables (env)
+  int simt_max_tokens = 0;  // T <= this -> SIMT GEMV path
+  int attn_split_override = 0;
+  int force_gemm_impl = -1;
+};
+
+namespace {
+
+template <typename T>
+int dalloc(T** p, size_t n) {
+  void* q = nullptr;
+  cudaError_t e = cudaMalloc(&q, n * sizeof(T));
+  if (e != cudaSuccess) {
+    b2_set_error("cudaMalloc(%zu bytes) failed: %s", n * sizeof(T), cudaGetErrorString(e));
+    return -12;
+  }
+  *p = reinterpret_cast<T*>(q);
+  return 0;
+}
+#define B2_TRY(expr)      \
+  do {                    \
+    int _r = (expr);      \
+    if (_r != 0) return _r; \
+  } while (0)
+
+int env_int(const char* name, int dflt) {
+  const char* v = getenv(name);
+  return v && *v ? atoi(v) : dflt;
+}
+
+// kernel-launch bracket: counts launches and, in profile mode, times each one
+struct KL {
+  b2_engine* e;
+  int cls;
+  int ev = -1;
+  KL(b2_engine* e_, int cls_) : e(e_), cls(cls_) {
+    e->launches++;
+    if (e->profiling && e->ev_next + 2 <= (int)e->ev_pool.size()) {
+      ev = e->ev_next;
+      e->ev_next += 2;
+      cudaEventRecord(e->ev_pool[ev], e->stream);
+    }
+  }
+  ~KL() {
+    if (ev >= 0) {
+      cudaEventRecord(e->ev_pool[ev + 1], e->stream);
+      e->ev_used.emplace_back(cls, ev);
+    }
+  }
+};
+
+int bucket_batch(int B) {
+  static const int bk[] = {1, 2, 4, 8, 16, 24, 32, 48, 64, 96, 128, 192, 256, 384, 512};
+  for (int v : bk)
+    if (B <= v) return v;
+  return ((B + 127) / 128) * 128;
+}
+
+int pick_attn_split(b2_engine* e, int B, int max_len) {
+  if (e->attn_split_override > 0) return e->attn_split_override;
+  const int units = B * e->cfg.num_kv_heads;
+  const int blocks = (max_len + e->cfg.block_size - 1) / e->cfg.block_size;
+  int want = (4 * e->num_sms + units - 1) / units;  // >= 4 CTAs per SM in flight
+  int cap = std::max(1, blocks / 8);                // keep >= 8 pages (2 per warp) per CTA
+  int ns = std::max(1, std::min(want, cap));
+  // quantise so only a handful of graphs exist
+  int q = 1;
+  while (q * 2 <= ns && q < 16) q *= 2;
+  return q;
+}
+
+// ---- one Linear layer: picks SIMT GEMV or the tcgen05 kernel, bf16 or split-K partial output
+ActIn linear(b2_engine* e, int cls, XBuf xb, const bf16* xptr, const bf16* w, const CUtensorMap& tm_w, bf16* out_bf16, int T,
+             int N, int K, int* rc) {
+  *rc = 0;
+  int impl = e->force_gemm_impl >= 0 ? e->force_gemm_impl : (T <= e->simt_max_tokens ? 0 : 1);
+  if (impl == 0) {
+    KL k(e, cls);
+    *rc = launch_linear_simt(xptr, w, out_bf16, 0, T, N, K, e->stream);
+    return act_bf16(out_bf16);
+  }
+  TcGemmArgs a;
+  a.tmap_w = tm_w;
+  a.bn = tc_pick_bn(T);
+  a.tmap_x = e->tm_x[xb][bn_index(a.bn)];
+  a.T = T; a.N = N; a.K = K;
+  a.argmax_packed = nullptr;
+  int ns = tc_pick_nsplit(T, N, K, e->num_sms);
+  while (ns > 1 && (size_t)ns * T * N > e->partial_floats) --ns;
+  if (ns > 1) {  // re-validate (every split non-empty)
+    const int kb = K / 64, kps = (kb + ns - 1) / ns;
+    ns = (kb + kps - 1) / kps;
+  }
+  a.nsplit = ns;
+  KL k(e, cls);
+  if (ns == 1) {
+    a.epilogue = TC_EPI_BF16;
+    a.out = out_bf16;
+    *rc = launch_linear_tc(a, e->stream);
+    return act_bf16(out_bf16);
+  }
+  a.epilogue = TC_EPI_F32_PARTIAL;
+  a.out = e->partial;
+  *rc = launch_linear_tc(a, e->stream);
+  return act_f32(e->partial, ns);
+}
+
+void dbg_capture(b2_engine* e, int slot, const bf16* src, int T) {
+  if (!(e->debug_flags & 1) || e->dbg_hidden == nullptr || T > e->dbg_cap_tokens) return;
+  cudaMemcpyAsync(e->dbg_hidden + (size_t)slot * e->dbg_cap_tokens * e->cfg.hidden, src, (size_t)T * e->cfg.hidden * 2,
+                  cudaMemcpyDeviceToDevice, e->stream);
+}
+
+// The forward pass over T tokens already described by d_tokens/d_positions/d_slots (and, for
+// decode, d_seq_lens/d_block_table rows 0..T-1).  prefill_tiles > 0 selects the causal prefill
+// attention; nlast = number of rows that get logits (decode: T; prefill: one per sequence,
+// gathered through d_last_rows).
+int forward(b2_engine* e, int T, int ntiles, int nlast, int attn_split) {
+  const b2_config& c = e->cfg;
+  const int H = c.hidden, I = c.intermediate;
+  int rc = 0;
+  {
+    KL k(e, B2K_EMBED);
+    B2_TRY(launch_embed(e->d_tokens, e->embed, e->h, T, H, c.vocab, e->stream));
+  }
+  dbg_capture(e, 0, e->h, T);
+  ActIn delta = act_bf16(nullptr);
+  for (int l = 0; l < c.num_layers; ++l) {
+    LayerW& L = e->layers[l];
+    bf16* kp = e->kv_pool + (size_t)(2 * l) * e->layer_kv_elems;
+    bf16* vp = kp + e->layer_kv_elems;
+    {
+      KL k(e, B2K_NORM);
+      B2_TRY(launch_add_rmsnorm(e->h, delta, L.ln1, e->x, T, H, c.rms_eps, e->stream));
+    }
+    if (l > 0) dbg_capture(e, l, e->h, T);
+    ActIn qkv = linear(e, B2K_GEMM_QKV, XB_X, e->x, L.wqkv, L.tm_qkv, e->qkv, T, e->qkv_size, H, &rc);
+    B2_TRY(rc);
+    {
+      KL k(e, B2K_ROPE_KV);
+      B2_TRY(launch_qknorm_rope_kv(qkv, L.qnorm, L.knorm, e->cos_sin, e->d_positions, e->d_slots, e->qrot, kp, vp, T,
+                                   c.num_q_heads, c.num_kv_heads, c.head_dim, c.block_size, c.rms_eps, e->stream));
+    }
+    if (ntiles > 0) {
+      KL k(e, B2K_MISC);
+      B2_TRY(launch_attn_prefill(e->qrot, kp, vp, e->d_block_table, e->bt_stride, e->d_tiles, ntiles, e->attn,
+                                 c.num_q_heads, c.num_kv_heads, c.head_dim, c.block_size, e->stream));
+    } else {
+      {
+        KL k(e, B2K_ATTN_DECODE);
+        B2_TRY(launch_attn_decode(e->qrot, kp, vp, e->d_block_table, e->bt_stride, e->d_seq_lens, e->attn_scratch,
+                                  e->attn, T, c.num_q_heads, c.num_kv_heads, c.head_dim, c.block_size, attn_split,
+                                  e->stream));
+      }
+      if (attn_split > 1) {
+        KL k(e, B2K_ATTN_COMBINE);
+        B2_TRY(launch_attn_combine(e->attn_scratch, e->attn, T, c.num_q_heads, c.num_kv_heads, c.head_dim, attn_split,
+                                   e->stream));
+      }
+    }
+    ActIn o = linear(e, B2K_GEMM_O, XB_ATTN, e->attn, L.wo, L.tm_o, e->proj, T, H, e->q_size, &rc);
+    B2_TRY(rc);
+    {
+      KL k(e, B2K_NORM);
+      B2_TRY(launch_add_rmsnorm(e->h, o, L.ln2, e->x, T, H, c.rms_eps, e->stream));
+    }
+    ActIn gu = linear(e, B2K_GEMM_GATEUP, XB_X, e->x, L.wgu, L.tm_gu, e->gu, T, 2 * I, H, &rc);
+    B2_TRY(rc);
+    {
+      KL k(e, B2K_ACT);
+      B2_TRY(launch_silu_mul(gu, e->act, T, I, e->stream));
+    }
+    delta = linear(e, B2K_GEMM_DOWN, XB_ACT, e->act, L.wd, L.tm_d, e->proj, T, H, I, &rc);
+    B2_TRY(rc);
+  }
+  {
+    KL k(e, B2K_NORM);
+    B2_TRY(launch_add_rmsnorm(e->h, delta, e->final_norm, e->x, T, H, c.rms_eps, e->stream));
+  }
+  dbg_capture(e, c.num_layers, e->h, T);
+  dbg_capture(e, c.num_layers + 1, e->x, T);
+
+  // lm_head on the last position of every sequence + greedy argmax
+  const bf16* xl = e->x;
+  XBuf xb = XB_X;
+  if (ntiles > 0) {
+    KL k(e, B2K_MISC);
+    B2_TRY(launch_gather_rows(e->x, e->d_last_rows, e->xlast, nlast, H, e->stream));
+    xl = e->xlast;
+    xb = XB_LAST;
+  }
+  bf16* logits = (e->debug_flags & 2) ? e->logits : nullptr;
+  int impl = e->force_gemm_impl >= 0 ? e->force_gemm_impl : (nlast <= e->simt_max_tokens ? 0 : 1);
+  if (impl == 0) {
+    if (e->logits == nullptr) {
+      b2_set_error("SIMT lm_head path needs the logits buffer (b2_set_debug(e, 2))");
+      return -22;
+    }
+    {
+      KL k(e, B2K_LMHEAD);
+      B2_TRY(launch_linear_simt(xl, e->lm_head, e->logits, 0, nlast, c.vocab, H, e->stream));
+    }
+    KL k2(e, B2K_MISC);
+    B2_TRY(launch_argmax_rows(e->logits, e->d_out_tokens, nlast, c.vocab, e->stream));
+  } else {
+    B2_CUDA_OK(cudaMemsetAsync(e->d_argmax, 0, sizeof(unsigned long long) * nlast, e->stream));
+    TcGemmArgs a;
+    a.tmap_w = e->tm_lm_head;
+    a.bn = tc_pick_bn(nlast);
+    a.tmap_x = e->tm_x[xb][bn_index(a.bn)];
+    a.T = nlast; a.N = c.vocab; a.K = H;
+    a.nsplit = 1;
+    a.epilogue = TC_EPI_ARGMAX;
+    a.out = logits;
+    a.argmax_packed = e->d_argmax;
+    {
+      KL k(e, B2K_LMHEAD);
+      B2_TRY(launch_linear_tc(a, e->stream));
+    }
+    KL k2(e, B2K_MISC);
+    B2_TRY(launch_argmax_finalize(e->d_argmax, e->d_out_tokens, nlast, e->stream));
+  }
+  return 0;
+}
+
+__global__ void publish_tokens_kernel(const int32_t* __restrict__ out_tokens, int32_t* __restrict__ next_in,
+                                      int32_t* __restrict__ log, int32_t* step, int B, int log_cap_steps, int stride) {
+  const int st = *step;  // single CTA
+  for (int b = threadIdx.x; b < B; b += blockDim.x) {
+    next_in[b] = out_tokens[b];
+    if (st < log_cap_steps) log[(size_t)st * stride + b] = out_tokens[b];
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) *step = st + 1;
+}
+
+// decode step body recorded into a graph (or run eagerly): bookkeeping, forward, token feedback
+int decode_body(b2_engine* e, int B, int attn_split) {
+  {
+    KL k(e, B2K_MISC);
+    B2_TRY(launch_decode_advance(e->d_positions, e->d_seq_lens, e->d_slots, e->d_block_table, e->bt_stride,
+                                 e->cfg.block_size, B, e->stream));
+  }
+  B2_TRY(forward(e, B, 0, B, attn_split));
+  {
+    KL k(e, B2K_MISC);
+    publish_tokens_kernel<<<1, 256, 0, e->stream>>>(e->d_out_tokens, e->d_tokens, e->d_token_log, e->d_step, B,
+                                                                 e->log_cap_steps, e->cfg.max_seqs);
+    B2_CUDA_OK(cudaGetLastError());
+  }
+  return 0;
+}
+
+// Captures (once per (batch bucket, attention split)) the decode step as a CUDA graph.  Capture
+// does not advance any state: the eager warm-up that precedes it runs on saved bookkeeping.
+int ensure_graph(b2_engine* e, int B, int attn_split) {
+  GraphKey key{B, attn_split};
+  if (e->graphs.count(key)) return 0;
+  // Warm every kernel once outside capture (function attributes, module load), then restore the
+  // bookkeeping so the real state is not advanced twice.  (The warm-up writes K/V for position
+  // pos+1 with the same values the real step will write.)
+  std::vector<int32_t> save(3 * (size_t)B + 1);
+  B2_CUDA_OK(cudaStreamSynchronize(e->stream));
+  B2_CUDA_OK(cudaMemcpy(save.data(), e->d_positions, B * 4, cudaMemcpyDeviceToHost));
+  B2_CUDA_OK(cudaMemcpy(save.data() + B, e->d_seq_lens, B * 4, cudaMemcpyDeviceToHost));
+  B2_CUDA_OK(cudaMemcpy(save.data() + 2 * B, e->d_tokens, B * 4, cudaMemcpyDeviceToHost));
+  B2_CUDA_OK(cudaMemcpy(save.data() + 3 * B, e->d_step, 4, cudaMemcpyDeviceToHost));
+  const int64_t l0 = e->launches;
+  B2_TRY(decode_body(e, B, attn_split));
+  B2_CUDA_OK(cudaStreamSynchronize(e->stream));
+  const int64_t nodes = e->launches - l0;
+  e->launches = l0;
+  B2_CUDA_OK(cudaMemcpy(e->d_positions, save.data(), B * 4, cudaMemcpyHostToDevice));
+  B2_CUDA_OK(cudaMemcpy(e->d_seq_lens, save.data() + B, B * 4, cudaMemcpyHostToDevice));
+  B2_CUDA_OK(cudaMemcpy(e->d_tokens, save.data() + 2 * B, B * 4, cudaMemcpyHostToDevice));
+  B2_CUDA_OK(cudaMemcpy(e->d_step, save.data() + 3 * B, 4, cudaMemcpyHostToDevice));
+  cudaGraph_t g = nullptr;
+  B2_CUDA_OK(cudaStreamBeginCapture(e->stream, cudaStreamCaptureModeThreadLocal));
+  int rc = decode_body(e, B, attn_split);
+  cudaError_t ce = cudaStreamEndCapture(e->stream, &g);
+  e->launches = l0;
+  if (rc != 0) {
+    if (g) cudaGraphDestroy(g);
+    return rc;
+  }
+  B2_CUDA_OK(ce);
+  cudaGraphExec_t ge = nullptr;
+  B2_CUDA_OK(cudaGraphInstantiate(&ge, g, 0));
+  cudaGraphDestroy(g);
+  e->graphs[key] = ge;
+  e->graph_nodes[key] = nodes;
+  return 0;
+}
+
+bool graphs_enabled(b2_engine* e) { return e->cfg.use_cuda_graphs && !e->profiling && e->debug_flags == 0; }
+
+int run_decode_step(b2_engine* e, int B, int attn_split) {
+  if (!graphs_enabled(e)) return decode_body(e, B, attn_split);
+  B2_TRY(ensure_graph(e, B, attn_split));
+  GraphKey key{B, attn_split};
+  B2_CUDA_OK(cudaGraphLaunch(e->graphs[key], e->stream));
+  e->launches += e->graph_nodes[key];
+  return 0;
+}
+
+// Uploads the batch state of `seq_ids` (decode slow path).  Device positions hold len-1 so the
+// advance kernel at the head of the step brings them to the position of the appended token.
+int upload_decode_batch(b2_engine* e, int n, const int32_t* seq_ids, int B) {
+  const int bs = e->cfg.block_size;
+  size_t need = (size_t)3 * B + (size_t)B * e->bt_stride;
+  if (need > e->h_stage_ints) {
+    b2_set_error("decode batch of %d does not fit the staging buffer", B);
+    return -12;
+  }
+  int32_t* pos = e->h_stage;
+  int32_t* lens = pos + B;
+  int32_t* slots = lens + B;
+  int32_t* bt = slots + B;
+  memset(e->h_stage, 0, need * sizeof(int32_t));
+  for (int i = 0; i < B; ++i) {
+    if (i < n) {
+      Seq& s = e->seqs[seq_ids[i]];
+      pos[i] = s.len - 1;
+      lens[i] = s.len;
+      slots[i] = -1;
+      memcpy(bt + (size_t)i * e->bt_stride, s.blocks.data(), s.blocks.size() * sizeof(int32_t));
+    } else {  // padding rows of the graph bucket: no KV write, empty attention
+      pos[i] = -2;  // sentinel: decode_advance leaves padding rows inert
+      lens[i] = 0;
+      slots[i] = -1;
+    }
+  }
+  (void)bs;
+  B2_CUDA_OK(cudaMemcpyAsync(e->d_positions, pos, B * 4, cudaMemcpyHostToDevice, e->stream));
+  B2_CUDA_OK(cudaMemcpyAsync(e->d_seq_lens, lens, B * 4, cudaMemcpyHostToDevice, e->stream));
+  B2_CUDA_OK(cudaMemcpyAsync(e->d_slots, slots, B * 4, cudaMemcpyHostToDevice, e->stream));
+  B2_CUDA_OK(cudaMemcpyAsync(e->d_block_table, bt, (size_t)B * e->bt_stride * 4, cudaMemcpyHostToDevice, e->stream));
+  B2_CUDA_OK(cudaStreamSynchronize(e->stream));  // staging buffer is reused
+  e->cur_batch.assign(seq_ids, seq_ids + n);
+  e->cur_B = B;
+  return 0;
+}
+
+int check_seq(b2_engine* e, int id) {
+  if (id < 0 || id >= (int)e->seqs.size() || !e->seqs[id].active) {
+    b2_set_error("invalid sequence id %d", id);
+    return -22;
+  }
+  return 0;
+}
+
+int ensure_logits(b2_engine* e) {
+  if (e->logits) return 0;
+  return dalloc(&e->logits, (size_t)std::max(e->cfg.max_seqs, 1) * e->cfg.vocab);
+}
+
+int layer_tensor(b2_engine* e, const std::string& name, const void* host, size_t nbytes) {
+  const b2_config& c = e->cfg;
+  const int H = c.hidden, I = c.intermediate;
+  auto put = [&](bf16* dst, size_t elems) -> int {
+    if (nbytes != elems * 2) {
+      b2_set_error("tensor %s: expected %zu bytes, got %zu", name.c_str(), elems * 2, nbytes);
+      return -22;
+    }
+    B2_CUDA_OK(cudaMemcpy(dst, host, nbytes, cudaMemcpyHostToDevice));
+    e->loaded[name] = 1;
+    return 0;
+  };
+  if (name == "model.embed_tokens.weight") return put(e->embed, (size_t)c.vocab * H);
+  if (name == "model.norm.weight") return put(e->final_norm, H);
+  if (name == "lm_head.weight") {
+    if (c.tie_embeddings) {
+      e->loaded[name] = 1;  // tied: ignore the duplicate
+      return 0;
+    }
+    return put(e->lm_head, (size_t)c.vocab * H);
+  }
+  const std::string pre = "model.layers.";
+  if (name.compare(0, pre.size(), pre) != 0) {
+    b2_set_error("unknown tensor name %s", name.c_str());
+    return -22;
+  }
+  size_t dot = name.find('.', pre.size());
+  if (dot == std::string::npos) {
+    b2_set_error("bad tensor name %s", name.c_str());
+    return -22;
+  }
+  int l = atoi(name.substr(pre.size(), dot - pre.size()).c_str());
+  if (l < 0 || l >= c.num_layers) {
+    b2_set_error("tensor %s: layer out of range", name.c_str());
+    return -22;
+  }
+  LayerW& L = e->layers[l];
+  std::string rest = name.substr(dot + 1);
+  if (rest == "input_layernorm.weight") return put(L.ln1, H);
+  if (rest == "post_attention_layernorm.weight") return put(L.ln2, H);
+  if (rest == "self_attn.q_norm.weight") return put(L.qnorm, c.head_dim);
+  if (rest == "self_attn.k_norm.weight") return put(L.knorm, c.head_dim);
+  if (rest == "self_attn.q_proj.weight") return put(L.wqkv, (size_t)e->q_size * H);
+  if (rest == "self_attn.k_proj.weight") return put(L.wqkv + (size_t)e->q_size * H, (size_t)e->kv_size * H);
+  if (rest == "self_attn.v_proj.weight") return put(L.wqkv + (size_t)(e->q_size + e->kv_size) * H, (size_t)e->kv_size * H);
+  if (rest == "self_attn.o_proj.weight") return put(L.wo, (size_t)H * e->q_size);
+  if (rest == "mlp.gate_proj.weight") return put(L.wgu, (size_t)I * H);
+  if (rest == "mlp.up_proj.weight") return put(L.wgu + (size_t)I * H, (size_t)I * H);
+  if (rest == "mlp.down_proj.weight") return put(L.wd, (size_t)H * I);
+  b2_set_error("unknown tensor name %s", name.c_str());
+  return -22;
+}
+
+int load_safetensors(b2_engine* e, const char* path) {
+  int fd = open(path, O_RDONLY);
+  if (fd < 0) {
+    b2_set_error("cannot open %s: %s", path, strerror(errno));
+    return -2;
+  }
+  struct stat st;
+  fstat(fd, &st);
+  void* map = mmap(nullptr, st.st_size, PROT_READ, MAP_PRIVATE, fd, 0);
+  close(fd);
+  if (map == MAP_FAILED) {
+    b2_set_error("mmap %s failed", path);
+    return -5;
+  }
+  int rc = 0;
+  try {
+    const uint8_t* p = reinterpret_cast<const uint8_t*>(map);
+    uint64_t hlen = 0;
+    memcpy(&hlen, p, 8);
+    if (hlen + 8 > (uint64_t)st.st_size) throw std::runtime_error("header length exceeds file");
+    b2json::Value hdr = b2json::parse(reinterpret_cast<const char*>(p + 8), (size_t)hlen);
+    const uint8_t* data = p + 8 + hlen;
+    std::vector<uint16_t> conv;
+    for (auto& kv : *hdr.obj) {
+      if (kv.first == "__metadata__") continue;
+      const b2json::Value* dt = kv.second.find("dtype");
+      const b2json::Value* off = kv.second.find("data_offsets");
+      if (!dt || !off || off->size() != 2) throw std::runtime_error("malformed entry " + kv.first);
+      uint64_t a = (uint64_t)off->at(0).as_int(), b = (uint64_t)off->at(1).as_int();
+      if (b < a || 8 + hlen + b > (uint64_t)st.st_size) throw std::runtime_error("offsets out of range for " + kv.first);
+      const void* src = data + a;
+      size_t nbytes = b - a;
+      if (dt->as_string() == "F32") {  // convert to bf16 (round to nearest even)
+        size_t n = nbytes / 4;
+        conv.resize(n);
+        const uint32_t* f = reinterpret_cast<const uint32_t*>(src);
+        for (size_t i = 0; i < n; ++i) {
+          uint32_t u = f[i];
+          conv[i] = (uint16_t)((u + 0x7fffu + ((u >> 16) & 1u)) >> 16);
+        }
+        src = conv.data();
+        nbytes = n * 2;
+      } else if (dt->as_string() != "BF16") {
+        throw std::runtime_error("tensor " + kv.first + ": dtype " + dt->as_string() + " not supported (BF16/F32)");
+      }
+      if (kv.first.find("rotary_emb.inv_freq") != std::string::npos) continue;
+      rc = layer_tensor(e, kv.first, src, nbytes);
+      if (rc != 0) break;
+    }
+  } catch (const std::exception& ex) {
+    b2_set_error("safetensors %s: %s", path, ex.what());
+    rc = -22;
+  }
+  munmap(map, st.st_size);
+  return rc;
+}
+
+}  // namespace
+
+// =======================================================================================
+// C ABI
+// =======================================================================================
+extern "C" int b2_engine_create(const b2_config* cfg, const char* safetensors_path, int device, b2_engine** out) {
+  B2_REQUIRE(cfg != nullptr && out != nullptr, "b2_engine_create: null argument");
+  B2_REQUIRE(cfg->abi_version == B2_ABI_VERSION, "b2_engine_create: abi_version %d != %d", cfg->abi_version, B2_ABI_VERSION);
+  B2_REQUIRE(cfg->head_dim == 128, "head_dim %d not built this round (128 only)", cfg->head_dim);
+  B2_REQUIRE(cfg->num_q_heads == 2 * cfg->num_kv_heads, "GQA group must be 2 (nq=%d nkv=%d)", cfg->num_q_heads, cfg->num_kv_heads);
+  B2_REQUIRE(cfg->block_size == 16, "block_size %d not built (16 only)", cfg->block_size);
+  B2_REQUIRE(cfg->hidden % 256 == 0 && cfg->intermediate % 256 == 0, "hidden/intermediate must be multiples of 256");
+  B2_REQUIRE(cfg->max_seqs >= 1 && cfg->max_batch_tokens >= 1 && cfg->max_model_len >= 1, "bad sizing");
+  int ndev = 0;
+  cudaError_t ce = cudaGetDeviceCount(&ndev);
+  if (ce != cudaSuccess || ndev <= device) {
+    b2_set_error("no CUDA device %d available (%s); this engine has no CPU path", device,
+                 ce == cudaSuccess ? "device count too small" : cudaGetErrorString(ce));
+    return -19;
+  }
+  B2_CUDA_OK(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  B2_CUDA_OK(cudaGetDeviceProperties(&prop, device));
+  B2_REQUIRE(prop.major == 10, "device %d is sm_%d%d; this library is built for sm_100a only", device, prop.major, prop.minor);
+
+  b2_engine* e = new b2_engine();
+  e->cfg = *cfg;
+  e->cfg.rope_inv_freq = nullptr;
+  e->device = device;
+  e->num_sms = prop.multiProcessorCount;
+  const b2_config& c = e->cfg;
+  e->q_size = c.num_q_heads * c.head_dim;
+  e->kv_size = c.num_kv_heads * c.head_dim;
+  e->qkv_size = e->q_size + 2 * e->kv_size;
+  e->simt_max_tokens = env_int("B2_SIMT_MAX_TOKENS", 0);
+  e->attn_split_override = env_int("B2_ATTN_SPLITS", 0);
+  e->force_gemm_impl = env_int("B2_GEMM_IMPL", -1);
+  const int H = c.hidden, I = c.intermediate;
+  int rc = 0;
+#define E_TRY(expr)        \
+  do {                     \
+    rc = (expr);           \
+    if (rc != 0) goto fail; \
+  } while (0)
+#define E_CUDA(expr)                                                                           \
+  do {                                                                                         \
+    cudaError_t _e = (expr);                                                                   \
+    if (_e != cudaSuccess) {                                                                   \
+      b2_set_error("%s:%d: %s failed: %s", __FILE__, __LINE__, #expr, cudaGetErrorString(_e)); \
+      rc = -5;                                                                                 \
+      goto fail;                                                                               \
+    }                                                                                          \
+  } while (0)
+  {
+    E_CUDA(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
+    // ---- weights ----
+    E_TRY(dalloc(&e->embed, (size_t)c.vocab * H));
+    if (c.tie_embeddings) e->lm_head = e->embed;
+    else E_TRY(dalloc(&e->lm_head, (size_t)c.vocab * H));
+    E_TRY(dalloc(&e->final_norm, (size_t)H));
+    e->layers.resize(c.num_layers);
+    for (auto& L : e->layers) {
+      E_TRY(dalloc(&L.ln1, (size_t)H));
+      E_TRY(dalloc(&L.ln2, (size_t)H));
+      E_TRY(dalloc(&L.qnorm, (size_t)c.head_dim));
+      E_TRY(dalloc(&L.knorm, (size_t)c.head_dim));
+      E_TRY(dalloc(&L.wqkv, (size_t)e->qkv_size * H));
+      E_TRY(dalloc(&L.wo, (size_t)H * e->q_size));
+      E_TRY(dalloc(&L.wgu, (size_t)2 * I * H));
+      E_TRY(dalloc(&L.wd, (size_t)H * I));
+    }
+    e->weight_bytes = 2ll * ((int64_t)c.vocab * H * (c.tie_embeddings ? 1 : 2) + H +
+                             (int64_t)c.num_layers * (2 * H + 2 * c.head_dim + (int64_t)e->qkv_size * H +
+                                                      (int64_t)H * e->q_size + 3ll * I * H));
+    // ---- RoPE table: cos/sin in fp32 from fp32 inv_freq * position, rounded to bf16
+    //      (HF:models/qwen3/modeling_qwen3.py:132-148) ----
+    {
+      const int hd = c.head_dim, half = hd / 2;
+      std::vector<float> inv(half);
+      for (int i = 0; i < half; ++i) {
+        if (cfg->rope_inv_freq) inv[i] = cfg->rope_inv_freq[i];
+        else inv[i] = (float)(1.0 / pow((double)c.rope_theta, (double)(2 * i) / (double)hd));
+      }
+      std::vector<uint16_t> tab((size_t)c.max_model_len * hd);
+      auto to_bf16 = [](float f) -> uint16_t {
+        uint32_t u;
+        memcpy(&u, &f, 4);
+        return (uint16_t)((u + 0x7fffu + ((u >> 16) & 1u)) >> 16);
+      };
+      for (int p = 0; p < c.max_model_len; ++p)
+        for (int i = 0; i < half; ++i) {
+          float fr = (float)p * inv[i];  // fp32 product, as the fp32 matmul in HF
+          tab[(size_t)p * hd + i] = to_bf16((float)cos((double)fr));
+          tab[(size_t)p * hd + half + i] = to_bf16((float)sin((double)fr));
+        }
+      E_TRY(dalloc(&e->cos_sin, tab.size()));
+      E_CUDA(cudaMemcpy(e->cos_sin, tab.data(), tab.size() * 2, cudaMemcpyHostToDevice));
+    }
+    // ---- activations ----
+    e->cap_tokens = ((std::max(c.max_batch_tokens, c.max_seqs) + 255) / 256) * 256;
+    const size_t Tc = e->cap_tokens;
+    E_TRY(dalloc(&e->h, Tc * H));
+    E_TRY(dalloc(&e->x, Tc * H));
+    E_TRY(dalloc(&e->qkv, Tc * e->qkv_size));
+    E_TRY(dalloc(&e->qrot, Tc * e->q_size));
+    E_TRY(dalloc(&e->attn, Tc * e->q_size));
+    E_TRY(dalloc(&e->gu, Tc * 2 * I));
+    E_TRY(dalloc(&e->act, Tc * I));
+    E_TRY(dalloc(&e->proj, Tc * H));
+    const size_t last_rows = ((size_t)(c.max_seqs + 255) / 256) * 256;
+    E_TRY(dalloc(&e->xlast, last_rows * H));
+    E_CUDA(cudaMemset(e->x, 0, Tc * H * 2));
+    E_CUDA(cudaMemset(e->attn, 0, Tc * e->q_size * 2));
+    E_CUDA(cudaMemset(e->act, 0, Tc * I * 2));
+    E_CUDA(cudaMemset(e->xlast, 0, last_rows * H * 2));
+    e->partial_floats = (size_t)16 << 20;  // 64 MB of fp32 split-K partials
+    E_TRY(dalloc(&e->partial, e->partial_floats));
+    e->attn_scratch_floats = attn_decode_scratch_floats(bucket_batch(c.max_seqs), c.num_q_heads, c.num_kv_heads, c.head_dim, 16);
+    E_TRY(dalloc(&e->attn_scratch, e->attn_scratch_floats));
+    for (int bi = 0; bi < 5; ++bi) {
+      E_TRY(b2_make_tmap_bf16(&e->tm_x[XB_X][bi], e->x, Tc, H, H, kBnList[bi]));
+      E_TRY(b2_make_tmap_bf16(&e->tm_x[XB_ATTN][bi], e->attn, Tc, e->q_size, e->q_size, kBnList[bi]));
+      E_TRY(b2_make_tmap_bf16(&e->tm_x[XB_ACT][bi], e->act, Tc, I, I, kBnList[bi]));
+      E_TRY(b2_make_tmap_bf16(&e->tm_x[XB_LAST][bi], e->xlast, last_rows, H, H, kBnList[bi]));
+    }
+    for (auto& L : e->layers) {
+      E_TRY(b2_make_tmap_bf16(&L.tm_qkv, L.wqkv, e->qkv_size, H, H, 128));
+      E_TRY(b2_make_tmap_bf16(&L.tm_o, L.wo, H, e->q_size, e->q_size, 128));
+      E_TRY(b2_make_tmap_bf16(&L.tm_gu, L.wgu, 2 * I, H, H, 128));
+      E_TRY(b2_make_tmap_bf16(&L.tm_d, L.wd, H, I, I, 128));
+    }
+    E_TRY(b2_make_tmap_bf16(&e->tm_lm_head, e->lm_head, c.vocab, H, H, 128));
+    // ---- batch state ----
+    e->bt_stride = (c.max_model_len + c.block_size - 1) / c.block_size;
+    const size_t Bcap = bucket_batch(c.max_seqs);
+    E_TRY(dalloc(&e->d_tokens, Tc));
+    E_TRY(dalloc(&e->d_positions, Tc));
+    E_TRY(dalloc(&e->d_slots, Tc));
+    E_TRY(dalloc(&e->d_seq_lens, Bcap));
+    E_TRY(dalloc(&e->d_block_table, Bcap * e->bt_stride));
+    E_TRY(dalloc(&e->d_last_rows, Bcap));
+    E_TRY(dalloc(&e->d_out_tokens, Bcap));
+    E_TRY(dalloc(&e->d_argmax, Bcap));
+    E_TRY(dalloc(&e->d_step, (size_t)1));
+    e->log_cap_steps = 4096;
+    E_TRY(dalloc(&e->d_token_log, (size_t)e->log_cap_steps * c.max_seqs));
+    E_CUDA(cudaMemset(e->d_step, 0, 4));
+    E_CUDA(cudaMemset(e->d_block_table, 0, Bcap * e->bt_stride * 4));
+    e->tiles_cap = (int)(Tc / 64 + Bcap + 16);
+    E_TRY(dalloc(&e->d_tiles, (size_t)e->tiles_cap));
+    e->h_stage_ints = std::max((size_t)3 * Tc + Bcap * (size_t)e->bt_stride + 4 * Bcap, (size_t)1 << 16);
+    E_CUDA(cudaMallocHost(&e->h_stage, e->h_stage_ints * sizeof(int32_t)));
+    E_CUDA(cudaMallocHost(&e->h_tiles, (size_t)e->tiles_cap * sizeof(PrefillTile)));
+    E_CUDA(cudaMallocHost(&e->h_out, (size_t)e->log_cap_steps * c.max_seqs * sizeof(int32_t)));
+    e->seqs.resize(c.max_seqs);
+    // ---- KV pool ----
+    {
+      const size_t blk_elems = (size_t)c.num_kv_heads * c.block_size * c.head_dim;
+      int64_t nb = c.num_blocks;
+      if (nb <= 0) {
+        size_t free_b = 0, total_b = 0;
+        E_CUDA(cudaMemGetInfo(&free_b, &total_b));
+        const double frac = c.gpu_mem_fraction > 0 ? c.gpu_mem_fraction : 0.9;
+        const double usable = (double)free_b - (1.0 - frac) * (double)total_b - (512.0 * 1024 * 1024);
+        nb = (int64_t)(usable / ((double)blk_elems * 2 * 2 * c.num_layers));
+        if (nb < 16) {
+          b2_set_error("not enough free device memory for a KV pool (free %zu MiB)", free_b >> 20);
+          rc = -12;
+          goto fail;
+        }
+      }
+      e->num_blocks = nb;
+      e->layer_kv_elems = (size_t)nb * blk_elems;
+      E_TRY(dalloc(&e->kv_pool, (size_t)2 * c.num_layers * e->layer_kv_elems));
+      E_CUDA(cudaMemset(e->kv_pool, 0, (size_t)2 * c.num_layers * e->layer_kv_elems * 2));
+      e->free_blocks.reserve(nb);
+      for (int64_t b = nb - 1; b >= 1; --b) e->free_blocks.push_back((int32_t)b);  // page 0 = null page
+    }
+    e->ev_pool.resize(2 * 400);
+    for (auto& ev : e->ev_pool) E_CUDA(cudaEventCreate(&ev));
+    if (safetensors_path) {
+      E_TRY(load_safetensors(e, safetensors_path));
+      E_TRY(b2_engine_finalize(e));
+    }
+  }
+  *out = e;
+  return 0;
+fail:
+  b2_engine_free(e);
+  return rc;
+#undef E_TRY
+#undef E_CUDA
+}
+
+extern "C" int b2_engine_load_tensor(b2_engine* e, const char* hf_name, const void* host_bf16, size_t nbytes) {
+  B2_REQUIRE(e && hf_name && host_bf16, "b2_engine_load_tensor: null argument");
+  B2_CUDA_OK(cudaSetDevice(e->device));
+  return layer_tensor(e, hf_name, host_bf16, nbytes);
+}
+
+extern "C" int b2_engine_finalize(b2_engine* e) {
+  B2_REQUIRE(e, "b2_engine_finalize: null engine");
+  const int per_layer = 11;
+  const int want = 2 + e->cfg.num_layers * per_layer;
+  int have = 0;
+  for (auto& kv : e->loaded)
+    if (kv.first != "lm_head.weight") ++have;
+  if (!e->cfg.tie_embeddings) {
+    B2_REQUIRE(e->loaded.count("lm_head.weight"), "weights incomplete: lm_head.weight missing (untied head)");
+  }
+  B2_REQUIRE(have == want, "weights incomplete: %d of %d tensors loaded", have, want);
+  e->finalized = true;
+  return 0;
+}
+
+extern "C" void b2_engine_free(b2_engine* e) {
+  if (!e) return;
+  cudaSetDevice(e->device);
+  if (e->stream) cudaStreamSynchronize(e->stream);
+  for (auto& kv : e->graphs) cudaGraphExecDestroy(kv.second);
+  for (auto& ev : e->ev_pool)
+    if (ev) cudaEventDestroy(ev);
+  auto F = [](void* p) {
+    if (p) cudaFree(p);
+  };
+  if (e->lm_head != e->embed) F(e->lm_head);
+  F(e->embed); F(e->final_norm); F(e->cos_sin);
+  for (auto& L : e->layers) {
+    F(L.ln1); F(L.ln2); F(L.qnorm); F(L.knorm); F(L.wqkv); F(L.wo); F(L.wgu); F(L.wd);
+  }
+  F(e->kv_pool); F(e->h); F(e->x); F(e->qkv); F(e->qrot); F(e->attn); F(e->gu); F(e->act); F(e->proj); F(e->xlast);
+  F(e->partial); F(e->attn_scratch); F(e->d_tokens); F(e->d_positions); F(e->d_seq_lens); F(e->d_slots);
+  F(e->d_block_table); F(e->d_last_rows); F(e->d_out_tokens); F(e->d_token_log); F(e->d_step); F(e->d_argmax);
+  F(e->d_tiles); F(e->dbg_hidden); F(e->logits);
+  if (e->h_stage) cudaFreeHost(e->h_stage);
+  if (e->h_tiles) cudaFreeHost(e->h_tiles);
+  if (e->h_out) cudaFreeHost(e->h_out);
+  if (e->stream) cudaStreamDestroy(e->stream);
+  delete e;
+}
+
+extern "C" int b2_engine_info(b2_engine* e, int64_t* num_blocks, int64_t* free_blocks, int64_t* weight_bytes) {
+  B2_REQUIRE(e, "b2_engine_info: null engine");
+  if (num_blocks) *num_blocks = e->num_blocks;
+  if (free_blocks) *free_blocks = (int64_t)e->free_blocks.size();
+  if (weight_bytes) *weight_bytes = e->weight_bytes;
+  return 0;
+}
+
+extern "C" int b2_seq_create(b2_engine* e, int32_t reserve_tokens, int32_t* seq_id) {
+  B2_REQUIRE(e && seq_id, "b2_seq_create: null argument");
+  B2_REQUIRE(reserve_tokens >= 1 && reserve_tokens <= e->cfg.max_model_len, "reserve_tokens %d outside [1, max_model_len=%d]",
+             reserve_tokens, e->cfg.max_model_len);
+  const int bs = e->cfg.block_size;
+  const int need = (reserve_tokens + bs - 1) / bs;
+  if ((int)e->free_blocks.size() < need) {
+    b2_set_error("KV pool exhausted: need %d pages, %zu free", need, e->free_blocks.size());
+    return -12;
+  }
+  int id = -1;
+  for (int i = 0; i < (int)e->seqs.size(); ++i)
+    if (!e->seqs[i].active) {
+      id = i;
+      break;
+    }
+  if (id < 0) {
+    b2_set_error("all %d sequence slots in use", e->cfg.max_seqs);
+    return -11;
+  }
+  Seq& s = e->seqs[id];
+  s.active = true;
+  s.len = 0;
+  s.reserved = need * bs;
+  s.blocks.clear();
+  for (int i = 0; i < need; ++i) {
+    s.blocks.push_back(e->free_blocks.back());
+    e->free_blocks.pop_back();
+  }
+  *seq_id = id;
+  return 0;
+}
+
+extern "C" int b2_seq_free(b2_engine* e, int32_t seq_id) {
+  B2_REQUIRE(e, "b2_seq_free: null engine");
+  B2_TRY(check_seq(e, seq_id));
+  Seq& s = e->seqs[seq_id];
+  for (int32_t b : s.blocks) e->free_blocks.push_back(b);
+  s.blocks.clear();
+  s.active = false;
+  s.len = 0;
+  e->cur_batch.clear();
+  return 0;
+}
+
+extern "C" int b2_seq_len(b2_engine* e, int32_t seq_id) {
+  if (!e || check_seq(e, seq_id) != 0) return -22;
+  return e->seqs[seq_id].len;
+}
+
+extern "C" int b2_prefill(b2_engine* e, const int32_t* ids, const int32_t* seq_offsets, int32_t nseq, const int32_t* seq_ids,
+                          int32_t* out_tokens) {
+  B2_REQUIRE(e && ids && seq_offsets && seq_ids && nseq >= 1, "b2_prefill: bad arguments");
+  B2_REQUIRE(e->finalized, "b2_prefill: weights not finalized");
+  B2_REQUIRE(nseq <= e->cfg.max_seqs, "b2_prefill: %d sequences > max_seqs %d", nseq, e->cfg.max_seqs);
+  B2_CUDA_OK(cudaSetDevice(e->device));
+  const int T = seq_offsets[nseq] - seq_offsets[0];
+  B2_REQUIRE(T >= 1 && T <= e->cap_tokens && T <= e->cfg.max_batch_tokens, "b2_prefill: %d tokens exceed max_batch_tokens %d", T,
+             e->cfg.max_batch_tokens);
+  const int bs = e->cfg.block_size;
+  int32_t* tok = e->h_stage;
+  int32_t* pos = tok + T;
+  int32_t* slots = pos + T;
+  int32_t* last = slots + T;
+  int32_t* bt = last + nseq;
+  int ntiles = 0;
+  for (int i = 0; i < nseq; ++i) {
+    B2_TRY(check_seq(e, seq_ids[i]));
+    Seq& s = e->seqs[seq_ids[i]];
+    const int n = seq_offsets[i + 1] - seq_offsets[i];
+    B2_REQUIRE(n >= 1, "b2_prefill: sequence %d has no tokens", i);
+    B2_REQUIRE(s.len + n <= s.reserved, "b2_prefill: sequence %d would exceed its reservation (%d + %d > %d)", seq_ids[i], s.len, n,
+               s.reserved);
+    const int row0 = seq_offsets[i] - seq_offsets[0];
+    for (int j = 0; j < n; ++j) {
+      const int p = s.len + j;
+      tok[row0 + j] = ids[seq_offsets[i] + j];
+      pos[row0 + j] = p;
+      slots[row0 + j] = s.blocks[p / bs] * bs + p % bs;
+    }
+    last[i] = row0 + n - 1;
+    memset(bt + (size_t)i * e->bt_stride, 0, (size_t)e->bt_stride * 4);
+    memcpy(bt + (size_t)i * e->bt_stride, s.blocks.data(), s.blocks.size() * 4);
+    for (int j = 0; j < n; j += 64) {
+      B2_REQUIRE(ntiles < e->tiles_cap, "b2_prefill: too many attention tiles");
+      e->h_tiles[ntiles++] = PrefillTile{row0 + j, s.len + j, std::min(64, n - j), i};
+    }
+  }
+  B2_CUDA_OK(cudaMemcpyAsync(e->d_tokens, tok, T * 4, cudaMemcpyHostToDevice, e->stream));
+  B2_CUDA_OK(cudaMemcpyAsync(e->d_positions, pos, T * 4, cudaMemcpyHostToDevice, e->stream));
+  B2_CUDA_OK(cudaMemcpyAsync(e->d_slots, slots, T * 4, cudaMemcpyHostToDevice, e->stream));
+  B2_CUDA_OK(cudaMemcpyAsync(e->d_last_rows, last, nseq * 4, cudaMemcpyHostToDevice, e->stream));
+  B2_CUDA_OK(cudaMemcpyAsync(e->d_block_table, bt, (size_t)nseq * e->bt_stride * 4, cudaMemcpyHostToDevice, e->stream));
+  B2_CUDA_OK(cudaMemcpyAsync(e->d_tiles, e->h_tiles, ntiles * sizeof(PrefillTile), cudaMemcpyHostToDevice, e->stream));
+  if (e->debug_flags & 2) B2_TRY(ensure_logits(e));
+  e->cur_batch.clear();
+  B2_TRY(forward(e, T, ntiles, nseq, 1));
+  // the produced tokens become the device-resident "next input" of these sequences
+  B2_CUDA_OK(cudaMemcpyAsync(e->h_out, e->d_out_tokens, nseq * 4, cudaMemcpyDeviceToHost, e->stream));
+  B2_CUDA_OK(cudaStreamSynchronize(e->stream));
+  for (int i = 0; i < nseq; ++i) e->seqs[seq_ids[i]].len += seq_offsets[i + 1] - seq_offsets[i];
+  if (out_tokens) memcpy(out_tokens, e->h_out, nseq * 4);
+  // remember them host-side too so the first decode step can seed d_tokens
+  e->last_n = nseq;
+  e->last_tokens = T;
+  return 0;
+}
+
+namespace {
+// Prepares device state for a decode step over seq_ids; returns padded batch B.
+int prepare_decode(b2_engine* e, int n, const int32_t* seq_ids, const int32_t* in_tokens, int* B_out, int* split_out) {
+  B2_REQUIRE(e->finalized, "decode: weights not finalized");
+  B2_REQUIRE(n >= 1 && n <= e->cfg.max_seqs, "decode: batch %d outside [1, max_seqs=%d]", n, e->cfg.max_seqs);
+  int max_len = 0;
+  for (int i = 0; i < n; ++i) {
+    B2_TRY(check_seq(e, seq_ids[i]));
+    Seq& s = e->seqs[seq_ids[i]];
+    B2_REQUIRE(s.len >= 1, "decode: sequence %d has no prefilled tokens", seq_ids[i]);
+    B2_REQUIRE(s.len + 1 <= s.reserved, "decode: sequence %d would exceed its reservation (%d tokens)", seq_ids[i], s.reserved);
+    max_len = std::max(max_len, s.len + 1);
+  }
+  const int B = e->cfg.use_cuda_graphs ? bucket_batch(n) : n;
+  const bool same = (int)e->cur_batch.size() == n && e->cur_B == B && std::equal(seq_ids, seq_ids + n, e->cur_batch.begin());
+  if (!same) {
+    // Device tokens of the previous forward are in d_out_tokens order of THAT forward; the
+    // caller must pass in_tokens when the batch composition changes.
+    B2_REQUIRE(in_tokens != nullptr || e->last_n == n, "decode: batch changed, in_tokens required");
+    if (in_tokens == nullptr) {
+      // same count, first step after prefill: seed d_tokens from the prefill's outputs
+      B2_CUDA_OK(cudaMemcpyAsync(e->d_tokens, e->d_out_tokens, n * 4, cudaMemcpyDeviceToDevice, e->stream));
+    }
+    B2_TRY(upload_decode_batch(e, n, seq_ids, B));
+  }
+  if (in_tokens != nullptr) {
+    memcpy(e->h_stage, in_tokens, n * 4);
+    for (int i = n; i < B; ++i) e->h_stage[i] = 0;
+    B2_CUDA_OK(cudaMemcpyAsync(e->d_tokens, e->h_stage, B * 4, cudaMemcpyHostToDevice, e->stream));
+  }
+  *B_out = B;
+  *split_out = pick_attn_split(e, B, max_len);
+  return 0;
+}
+}  // namespace
+
+extern "C" int b2_decode_step(b2_engine* e, int32_t nseq, const int32_t* seq_ids, const int32_t* in_tokens, int32_t* out_tokens) {
+  B2_REQUIRE(e && seq_ids, "b2_decode_step: null argument");
+  B2_CUDA_OK(cudaSetDevice(e->device));
+  int B = 0, split = 1;
+  B2_TRY(prepare_decode(e, nseq, seq_ids, in_tokens, &B, &split));
+  if (e->debug_flags & 2) B2_TRY(ensure_logits(e));
+  B2_TRY(run_decode_step(e, B, split));
+  for (int i = 0; i < nseq; ++i) e->seqs[seq_ids[i]].len += 1;
+  e->last_n = nseq;
+  e->last_tokens = nseq;
+  if (out_tokens) {
+    B2_CUDA_OK(cudaMemcpyAsync(e->h_out, e->d_out_tokens, nseq * 4, cudaMemcpyDeviceToHost, e->stream));
+    B2_CUDA_OK(cudaStreamSynchronize(e->stream));
+    memcpy(out_tokens, e->h_out, nseq * 4);
+  }
+  return 0;
+}
+
+extern "C" int b2_decode_run(b2_engine* e, int32_t nseq, const int32_t* seq_ids, int32_t steps, int32_t* out_tokens,
+                             float* elapsed_ms) {
+  B2_REQUIRE(e && seq_ids && steps >= 1, "b2_decode_run: bad arguments");
+  B2_REQUIRE(steps <= e->log_cap_steps, "b2_decode_run: steps %d > %d", steps, e->log_cap_steps);
+  B2_CUDA_OK(cudaSetDevice(e->device));
+  for (int i = 0; i < nseq; ++i) {
+    B2_TRY(check_seq(e, seq_ids[i]));
+    Seq& s = e->seqs[seq_ids[i]];
+    B2_REQUIRE(s.len + steps <= s.reserved, "b2_decode_run: sequence %d reservation too small for %d steps", seq_ids[i], steps);
+  }
+  int B = 0, split = 1;
+  B2_TRY(prepare_decode(e, nseq, seq_ids, nullptr, &B, &split));
+  B2_CUDA_OK(cudaMemsetAsync(e->d_step, 0, 4, e->stream));
+  // the graph is captured before the timed region; the event pair brackets exactly `steps` steps
+  cudaEvent_t ev0 = e->ev_pool[e->ev_pool.size() - 2], ev1 = e->ev_pool[e->ev_pool.size() - 1];
+  int done = 0;
+  {
+    int max_len = 0;
+    for (int i = 0; i < nseq; ++i) max_len = std::max(max_len, e->seqs[seq_ids[i]].len + steps);
+    split = pick_attn_split(e, B, max_len);  // one graph for the whole run
+  }
+  if (graphs_enabled(e)) B2_TRY(ensure_graph(e, B, split));
+  B2_CUDA_OK(cudaEventRecord(ev0, e->stream));
+  for (; done < steps; ++done) B2_TRY(run_decode_step(e, B, split));
+  B2_CUDA_OK(cudaEventRecord(ev1, e->stream));
+  B2_CUDA_OK(cudaStreamSynchronize(e->stream));
+  if (elapsed_ms) B2_CUDA_OK(cudaEventElapsedTime(elapsed_ms, ev0, ev1));
+  for (int i = 0; i < nseq; ++i) e->seqs[seq_ids[i]].len += steps;
+  e->last_n = nseq;
+  e->last_tokens = nseq;
+  if (out_tokens) {
+    B2_CUDA_OK(cudaMemcpy(e->h_out, e->d_token_log, (size_t)steps * e->cfg.max_seqs * 4, cudaMemcpyDeviceToHost));
+    for (int st = 0; st < steps; ++st)
+      memcpy(out_tokens + (size_t)st * nseq, e->h_out + (size_t)st * e->cfg.max_seqs, nseq * 4);
+  }
+  return 0;
+}
+
+extern "C" int b2_decode_profile(b2_engine* e, int32_t nseq, const int32_t* seq_ids, int32_t steps, float* ms_by_class,
+                                 int64_t* launches_by_class) {
+  B2_REQUIRE(e && seq_ids && steps >= 1 && ms_by_class && launches_by_class, "b2_decode_profile: bad arguments");
+  B2_CUDA_OK(cudaSetDevice(e->device));
+  for (int k = 0; k < B2_NUM_KERNEL_CLASSES; ++k) {
+    ms_by_class[k] = 0.f;
+    launches_by_class[k] = 0;
+  }
+  for (int st = 0; st < steps; ++st) {
+    int B = 0, split = 1;
+    B2_TRY(prepare_decode(e, nseq, seq_ids, nullptr, &B, &split));
+    e->profiling = true;
+    e->ev_next = 0;
+    e->ev_used.clear();
+    int rc = run_decode_step(e, B, split);
+    e->profiling = false;
+    B2_TRY(rc);
+    B2_CUDA_OK(cudaStreamSynchronize(e->stream));
+    for (auto& u : e->ev_used) {
+      float ms = 0.f;
+      B2_CUDA_OK(cudaEventElapsedTime(&ms, e->ev_pool[u.second], e->ev_pool[u.second + 1]));
+      ms_by_class[u.first] += ms;
+      launches_by_class[u.first] += 1;
+    }
+    for (int i = 0; i < nseq; ++i) e->seqs[seq_ids[i]].len += 1;
+  }
+  e->last_n = nseq;
+  e->last_tokens = nseq;
+  return 0;
+}
+
+extern "C" int64_t b2_launch_count(b2_engine* e) { return e ? e->launches : 0; }
+
+extern "C" int b2_set_debug(b2_engine* e, int32_t flags) {
+  B2_REQUIRE(e, "b2_set_debug: null engine");
+  B2_CUDA_OK(cudaSetDevice(e->device));
+  e->debug_flags = flags;
+  if ((flags & 1) && e->dbg_hidden == nullptr) {
+    e->dbg_cap_tokens = std::min(e->cap_tokens, 1024);
+    B2_TRY(dalloc(&e->dbg_hidden, (size_t)(e->cfg.num_layers + 2) * e->dbg_cap_tokens * e->cfg.hidden));
+  }
+  if (flags & 2) B2_TRY(ensure_logits(e));
+  return 0;
+}
+
+extern "C" int b2_get_hidden(b2_engine* e, int32_t layer, int32_t ntokens, uint16_t* out_bf16) {
+  B2_REQUIRE(e && out_bf16, "b2_get_hidden: null argument");
+  B2_REQUIRE((e->debug_flags & 1) && e->dbg_hidden, "b2_get_hidden: hidden capture not enabled (b2_set_debug(e, 1))");
+  B2_REQUIRE(layer >= -1 && layer <= e->cfg.num_layers, "b2_get_hidden: layer %d out of range", layer);
+  B2_REQUIRE(ntokens >= 1 && ntokens <= e->dbg_cap_tokens && ntokens <= e->last_tokens, "b2_get_hidden: ntokens %d out of range", ntokens);
+  B2_CUDA_OK(cudaSetDevice(e->device));
+  B2_CUDA_OK(cudaStreamSynchronize(e->stream));
+  const int slot = layer + 1;  // -1 -> embeddings, l -> residual after layer l, L -> final norm output
+  B2_CUDA_OK(cudaMemcpy(out_bf16, e->dbg_hidden + (size_t)slot * e->dbg_cap_tokens * e->cfg.hidden,
+                        (size_t)ntokens * e->cfg.hidden * 2, cudaMemcpyDeviceToHost));
+  return 0;
+}
+
+extern "C" int b2_get_logits(b2_engine* e, int32_t nseq, float* out_logits) {
+  B2_REQUIRE(e && out_logits, "b2_get_logits: null argument");
+  B2_REQUIRE((e->debug_flags & 2) && e->logits, "b2_get_logits: logits capture not enabled (b2_set_debug(e, 2))");
+  B2_REQUIRE(nseq >= 1 && nseq <= e->last_n, "b2_get_logits: nseq %d > sequences of the last forward (%d)", nseq, e->last_n);
+  B2_CUDA_OK(cudaSetDevice(e->device));
+  const size_t n = (size_t)nseq * e->cfg.vocab;
+  float* tmp = nullptr;
+  B2_TRY(dalloc(&tmp, n));
+  int rc = launch_logits_to_f32(e->logits, tmp, n, e->stream);
+  if (rc == 0) {
+    cudaError_t ce = cudaMemcpyAsync(out_logits, tmp, n * 4, cudaMemcpyDeviceToHost, e->stream);
+    if (ce == cudaSuccess) ce = cudaStreamSynchronize(e->stream);
+    if (ce != cudaSuccess) {
+      b2_set_error("b2_get_logits: copy failed: %s", cudaGetErrorString(ce));
+      rc = -5;
+    }
+  }
+  cudaFree(tmp);
+  return rc;
+}
+
+extern "C" int b2_set_next_tokens(b2_engine* e, int32_t nseq, const int32_t* seq_ids, const int32_t* tokens) {
+  B2_REQUIRE(e && seq_ids && tokens, "b2_set_next_tokens: null argument");
+  B2_REQUIRE((int)e->cur_batch.size() == nseq && std::equal(seq_ids, seq_ids + nseq, e->cur_batch.begin()),
+             "b2_set_next_tokens: sequences must be the resident decode batch, in order");
+  B2_CUDA_OK(cudaSetDevice(e->device));
+  memcpy(e->h_stage, tokens, nseq * 4);
+  B2_CUDA_OK(cudaMemcpyAsync(e->d_tokens, e->h_stage, nseq * 4, cudaMemcpyHostToDevice, e->stream));
+  B2_CUDA_OK(cudaStreamSynchronize(e->stream));
+  return 0;
+}
+
+extern "C" int b2_sample(b2_engine* e, int32_t nseq, const b2_sampling* params, int32_t* out_tokens) {
+  B2_REQUIRE(e && params && out_tokens, "b2_sample: null argument");
+  B2_REQUIRE((e->debug_flags & 2) && e->logits, "b2_sample: logits capture not enabled (b2_set_debug(e, 2))");
+  B2_REQUIRE(nseq >= 1 && nseq <= e->last_n, "b2_sample: nseq %d > sequences of the last forward (%d)", nseq, e->last_n);
+  B2_CUDA_OK(cudaSetDevice(e->device));
+  if (params->temperature <= 0.f) {
+    B2_TRY(launch_argmax_rows(e->logits, e->d_out_tokens, nseq, e->cfg.vocab, e->stream));
+  } else {
+    B2_TRY(launch_sample(e->logits, e->d_out_tokens, nseq, e->cfg.vocab, params->temperature, params->top_k, params->top_p,
+                         params->seed, (uint64_t)e->launches, e->stream));
+  }
+  e->launches++;
+  B2_CUDA_OK(cudaMemcpyAsync(e->h_out, e->d_out_tokens, nseq * 4, cudaMemcpyDeviceToHost, e->stream));
+  B2_CUDA_OK(cudaStreamSynchronize(e->stream));
+  memcpy(out_tokens, e->h_out, nseq * 4);
+  return 0;
+}

@@ -1,0 +1,276 @@
+// gemm_tc.cu -- tcgen05 / TMEM GEMM for the projections (HF nn.Linear,
+// models/qwen3/modeling_qwen3.py:236-247,81-83,451): y[T][N] = x[T][K] . W[N][K]^T.
+//
+// Layout choice ("swap-AB"): the WEIGHT rows are the MMA M dimension (128 per CTA) and the
+// TOKENS are the MMA N dimension (16..256), so a decode batch of 1..64 tokens wastes no
+// tensor-core rows and the weight stream -- the only large operand -- is what TMA pipelines.
+//   warp 0   : TMA producer  (cp.async.bulk.tensor, 128B-swizzled 64-column k-blocks)
+//   warp 1   : TMEM allocator + single-thread tcgen05.mma issuer (accumulator in TMEM)
+//   warps 2-5: epilogue -- tcgen05.ld the 128 x BN fp32 accumulator, then
+//                TC_EPI_BF16        round to bf16, store y[T][N]
+//                TC_EPI_F32_PARTIAL store fp32 split-K partial [split][T][N] (summed in split
+//                                   order by the consumer kernel -> deterministic)
+//                TC_EPI_ARGMAX      lm_head: round to bf16, fused arg-max (lowest index on
+//                                   ties) via one 64-bit atomicMax per token per tile
+// Split-K (gridDim.z) exists because N/128 row tiles alone cannot fill 148 SMs for the
+// 1024-row projections; HBM bandwidth needs every SM streaming.
+#include "kernels.h"
+
+#include <mutex>
+
+namespace b2 {
+
+constexpr int TC_BM = 128;
+constexpr int TC_BK = 64;
+constexpr int TC_W_BYTES = TC_BM * TC_BK * 2;  // 16 KB per stage
+
+template <int BN>
+struct TcCfg {
+  static constexpr int X_BYTES = BN * TC_BK * 2;
+  static constexpr int STAGE_BYTES = TC_W_BYTES + X_BYTES;
+  static constexpr int STAGES = (BN <= 64) ? 8 : (BN == 128 ? 6 : 4);
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024;
+  static constexpr int TMEM_COLS = BN < 32 ? 32 : BN;
+};
+
+__device__ __forceinline__ unsigned long long tc_argmax_pack(float v, int idx) {
+  uint32_t b = __float_as_uint(v);
+  uint32_t key = (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+  return ((unsigned long long)key << 32) | (unsigned long long)(0xffffffffu - (uint32_t)idx);
+}
+
+template <int BN, int EPI>
+__global__ void __launch_bounds__(192, 1)
+linear_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_x,
+                 void* __restrict__ out, unsigned long long* __restrict__ argmax_packed, int T, int N, int K,
+                 int kb_per_split) {
+  using C = TcCfg<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t full_bar[C::STAGES];
+  __shared__ __align__(8) uint64_t empty_bar[C::STAGES];
+  __shared__ __align__(8) uint64_t tmem_full_bar;
+  __shared__ uint32_t tmem_slot;
+  __shared__ unsigned long long amax_red[EPI == TC_EPI_ARGMAX ? 4 * BN : 1];
+
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int m_tile = blockIdx.x, n_tile = blockIdx.y, split = blockIdx.z;
+  const int kb_total = K / TC_BK;
+  const int kb0 = split * kb_per_split;
+  const int kb1 = min(kb_total, kb0 + kb_per_split);
+  const int nkb = kb1 - kb0;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < C::STAGES; ++s) {
+      mbar_init(smem_u32(&full_bar[s]), 1);
+      mbar_init(smem_u32(&empty_bar[s]), 1);
+    }
+    mbar_init(smem_u32(&tmem_full_bar), 1);
+    mbar_fence_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(smem_u32(&tmem_slot), C::TMEM_COLS);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      tma_prefetch_desc(&tmap_w);
+      tma_prefetch_desc(&tmap_x);
+      for (int i = 0; i < nkb; ++i) {
+        const int s = i % C::STAGES;
+        const uint32_t ph = (i / C::STAGES) & 1;
+        mbar_wait(smem_u32(&empty_bar[s]), ph ^ 1);
+        const uint32_t fb = smem_u32(&full_bar[s]);
+        mbar_arrive_expect_tx(fb, C::STAGE_BYTES);
+        const uint32_t ws = smem_base + s * C::STAGE_BYTES;
+        tma_load_2d(ws, &tmap_w, (kb0 + i) * TC_BK, m_tile * TC_BM, fb);
+        tma_load_2d(ws + TC_W_BYTES, &tmap_x, (kb0 + i) * TC_BK, n_tile * BN, fb);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(TC_BM, BN);
+      for (int i = 0; i < nkb; ++i) {
+        const int s = i % C::STAGES;
+        const uint32_t ph = (i / C::STAGES) & 1;
+        mbar_wait(smem_u32(&full_bar[s]), ph);
+        tc_fence_after();
+        const uint32_t ws = smem_base + s * C::STAGE_BYTES;
+        const uint64_t da = umma_desc_sw128(ws);
+        const uint64_t db = umma_desc_sw128(ws + TC_W_BYTES);
+#pragma unroll
+        for (int k = 0; k < TC_BK / 16; ++k) {
+          // advance 16 bf16 = 32 bytes along K inside the 128-byte swizzle row: +2 in the
+          // (address >> 4) field of both descriptors
+          tc_mma_bf16(tmem_base, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (i > 0 || k > 0) ? 1u : 0u);
+        }
+        tc_commit(smem_u32(&empty_bar[s]));  // frees the smem stage once these MMAs retire
+      }
+      tc_commit(smem_u32(&tmem_full_bar));   // accumulator complete
+    }
+  } else {
+    const int q = warp & 3;  // TMEM lane quarter this warp may access
+    mbar_wait(smem_u32(&tmem_full_bar), 0);
+    tc_fence_after();
+    const int row = m_tile * TC_BM + q * 32 + lane;  // output feature
+    const bool row_ok = row < N;
+#pragma unroll 1
+    for (int c0 = 0; c0 < BN; c0 += 16) {
+      uint32_t r[16];
+      tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, r);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        const int tok = n_tile * BN + c0 + j;
+        const float acc = __uint_as_float(r[j]);
+        if (EPI == TC_EPI_BF16) {
+          if (tok < T && row_ok) reinterpret_cast<bf16*>(out)[(size_t)tok * N + row] = __float2bfloat16_rn(acc);
+        } else if (EPI == TC_EPI_F32_PARTIAL) {
+          if (tok < T && row_ok) reinterpret_cast<float*>(out)[((size_t)split * T + tok) * N + row] = acc;
+        } else {
+          const bf16 lb = __float2bfloat16_rn(acc);
+          const float lv = __bfloat162float(lb);
+          if (out != nullptr && tok < T && row_ok) reinterpret_cast<bf16*>(out)[(size_t)tok * N + row] = lb;
+          unsigned long long p = (row_ok && lv == lv) ? tc_argmax_pack(lv, row) : 0ull;
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) {
+            unsigned long long other = __shfl_xor_sync(0xffffffffu, p, o);
+            p = other > p ? other : p;
+          }
+          if (lane == 0) amax_red[q * BN + c0 + j] = p;
+        }
+      }
+    }
+    if (EPI == TC_EPI_ARGMAX) {
+      asm volatile("bar.sync 1, 128;" ::: "memory");  // the four epilogue warps only
+      for (int e = threadIdx.x - 64; e < BN; e += 128) {
+        const int tok = n_tile * BN + e;
+        if (tok < T) {
+          unsigned long long p = amax_red[e];
+#pragma unroll
+          for (int k = 1; k < 4; ++k) p = amax_red[k * BN + e] > p ? amax_red[k * BN + e] : p;
+          atomicMax(argmax_packed + tok, p);
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, C::TMEM_COLS);
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// host
+// ---------------------------------------------------------------------------------------
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static PFN_encodeTiled get_encode_fn() {
+  static PFN_encodeTiled fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<PFN_encodeTiled>(p);
+  });
+  return fn;
+}
+
+}  // namespace b2
+
+int b2_make_tmap_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows) {
+  auto fn = b2::get_encode_fn();
+  B2_REQUIRE(fn != nullptr, "cuTensorMapEncodeTiled driver entry point not available");
+  B2_REQUIRE(((uintptr_t)base & 15) == 0 && (ld * 2) % 16 == 0, "tensor map: base/stride must be 16-byte aligned");
+  cuuint64_t gdim[2] = {cols, rows};
+  cuuint64_t gstride[1] = {ld * 2};
+  cuuint32_t box[2] = {64, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstride, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  B2_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with CUresult %d (rows=%llu cols=%llu ld=%llu box=%u)",
+             (int)r, (unsigned long long)rows, (unsigned long long)cols, (unsigned long long)ld, box_rows);
+  return 0;
+}
+
+namespace b2 {
+
+int tc_pick_bn(int T) {
+  if (T <= 16) return 16;
+  if (T <= 32) return 32;
+  if (T <= 64) return 64;
+  if (T <= 128) return 128;
+  return 256;
+}
+
+int tc_pick_nsplit(int T, int N, int K, int num_sms) {
+  const int bn = tc_pick_bn(T);
+  const int tiles = ((N + TC_BM - 1) / TC_BM) * ((T + bn - 1) / bn);
+  const int kb_total = K / TC_BK;
+  int ns = num_sms / (tiles > 0 ? tiles : 1);
+  if (ns < 1) ns = 1;
+  if (ns > kb_total) ns = kb_total;
+  if (ns > 32) ns = 32;
+  const int kps = (kb_total + ns - 1) / ns;
+  return (kb_total + kps - 1) / kps;  // every split non-empty
+}
+
+template <int BN, int EPI>
+static int launch_one(const TcGemmArgs& a, int kb_per_split, cudaStream_t s) {
+  using C = TcCfg<BN>;
+  static bool attr_done = false;
+  if (!attr_done) {
+    B2_CUDA_OK(cudaFuncSetAttribute(linear_tc_kernel<BN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
+    attr_done = true;
+  }
+  dim3 grid((a.N + TC_BM - 1) / TC_BM, (a.T + BN - 1) / BN, a.nsplit);
+  linear_tc_kernel<BN, EPI><<<grid, 192, C::SMEM_BYTES, s>>>(a.tmap_w, a.tmap_x, a.out, a.argmax_packed, a.T, a.N, a.K,
+                                                              kb_per_split);
+  B2_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+template <int BN>
+static int launch_bn(const TcGemmArgs& a, int kps, cudaStream_t s) {
+  switch (a.epilogue) {
+    case TC_EPI_BF16: return launch_one<BN, TC_EPI_BF16>(a, kps, s);
+    case TC_EPI_F32_PARTIAL: return launch_one<BN, TC_EPI_F32_PARTIAL>(a, kps, s);
+    case TC_EPI_ARGMAX: return launch_one<BN, TC_EPI_ARGMAX>(a, kps, s);
+  }
+  b2_set_error("linear_tc: bad epilogue %d", a.epilogue);
+  return -22;
+}
+
+int launch_linear_tc(const TcGemmArgs& a, cudaStream_t s) {
+  if (a.T <= 0) return 0;
+  B2_REQUIRE(a.K % TC_BK == 0, "linear_tc: K=%d must be a multiple of %d", a.K, TC_BK);
+  const int kb_total = a.K / TC_BK;
+  B2_REQUIRE(a.nsplit >= 1 && a.nsplit <= kb_total, "linear_tc: nsplit=%d out of range (k-blocks=%d)", a.nsplit, kb_total);
+  const int kps = (kb_total + a.nsplit - 1) / a.nsplit;
+  B2_REQUIRE((kb_total + kps - 1) / kps == a.nsplit, "linear_tc: nsplit=%d leaves an empty split for %d k-blocks", a.nsplit,
+             kb_total);
+  B2_REQUIRE(a.nsplit == 1 || a.epilogue == TC_EPI_F32_PARTIAL, "linear_tc: split-K needs the fp32 partial epilogue");
+  switch (a.bn) {
+    case 16: return launch_bn<16>(a, kps, s);
+    case 32: return launch_bn<32>(a, kps, s);
+    case 64: return launch_bn<64>(a, kps, s);
+    case 128: return launch_bn<128>(a, kps, s);
+    case 256: return launch_bn<256>(a, kps, s);
+  }
+  b2_set_error("linear_tc: bad token tile %d", a.bn);
+  return -22;
+}
+
+}  // namespace b2

@@ -1,0 +1,78 @@
+// kernels.h -- internal C++ launch API of the sm_100a kernels (engine.cu and capi.cu call these).
+#pragma once
+#include "common.cuh"
+
+namespace b2 {
+
+// An activation operand that is either bf16 [T][N] or fp32 split-K partials [nsplit][T][N]
+// (summed in split order, then rounded to bf16 -- the rounding point of HF's nn.Linear).
+struct ActIn {
+  const void* ptr;
+  int is_f32;
+  int nsplit;
+};
+inline ActIn act_bf16(const void* p) { return ActIn{p, 0, 1}; }
+inline ActIn act_f32(const void* p, int nsplit) { return ActIn{p, 1, nsplit}; }
+
+// ---- elementwise.cu ----
+int launch_embed(const int32_t* ids, const bf16* table, bf16* h, int T, int H, int vocab, cudaStream_t s);
+int launch_add_rmsnorm(bf16* h, ActIn delta, const bf16* w, bf16* x, int T, int H, float eps, cudaStream_t s);
+int launch_qknorm_rope_kv(ActIn qkv, const bf16* qw, const bf16* kw, const bf16* cos_sin, const int32_t* positions,
+                          const int32_t* slots, bf16* q_out, bf16* k_pages, bf16* v_pages, int T, int nq, int nkv,
+                          int hd, int block_size, float eps, cudaStream_t s);
+int launch_silu_mul(ActIn gu, bf16* act, int T, int I, cudaStream_t s);
+int launch_gather_rows(const bf16* src, const int32_t* rows, bf16* dst, int n, int H, cudaStream_t s);
+int launch_argmax_rows(const bf16* logits, int32_t* out, int T, int V, cudaStream_t s);
+int launch_argmax_finalize(const unsigned long long* packed, int32_t* out, int T, cudaStream_t s);
+// decode bookkeeping on the device: positions/seq_lens += 1, slots from the block table, and
+// the tokens produced by the previous step become this step's input ids.
+int launch_decode_advance(int32_t* positions, int32_t* seq_lens, int32_t* slots, const int32_t* block_table,
+                          int bt_stride, int block_size, int B, cudaStream_t s);
+int launch_logits_to_f32(const bf16* in, float* out, size_t n, cudaStream_t s);
+
+// ---- gemm_simt.cu ----
+// out = x[T][K] . w[N][K]^T ; bf16 out [T][N] or fp32 [T][N] (single split).
+int launch_linear_simt(const bf16* x, const bf16* w, void* out, int out_is_f32, int T, int N, int K, cudaStream_t s);
+
+// ---- gemm_tc.cu ----
+enum TcEpilogue { TC_EPI_BF16 = 0, TC_EPI_F32_PARTIAL = 1, TC_EPI_ARGMAX = 2 };
+struct TcGemmArgs {
+  CUtensorMap tmap_w;  // W [N][K], box 64 x 128
+  CUtensorMap tmap_x;  // X [>=T rows][K], box 64 x bn
+  int bn;              // token tile: 16, 32, 64, 128 or 256
+  int T, N, K;
+  int nsplit;          // split-K factor (EPI_F32_PARTIAL when > 1)
+  int epilogue;
+  void* out;           // bf16 [T][N] | fp32 [nsplit][T][N] | bf16 logits (may be null) for ARGMAX
+  unsigned long long* argmax_packed;  // [T] for TC_EPI_ARGMAX (must be zeroed before launch)
+};
+int launch_linear_tc(const TcGemmArgs& a, cudaStream_t s);
+int tc_pick_bn(int T);
+// choose a split-K factor so that tiles * splits fills the SMs (each split gets >= 1 k-block)
+int tc_pick_nsplit(int T, int N, int K, int num_sms);
+
+// ---- attn_decode.cu ----
+size_t attn_decode_scratch_floats(int B, int nq, int nkv, int hd, int nsplit);
+int launch_attn_decode(const bf16* q, const bf16* k_pages, const bf16* v_pages, const int32_t* block_table,
+                       int bt_stride, const int32_t* seq_lens, float* scratch, bf16* out, int B, int nq, int nkv,
+                       int hd, int block_size, int nsplit, cudaStream_t s);
+int launch_attn_combine(const float* scratch, bf16* out, int B, int nq, int nkv, int hd, int nsplit, cudaStream_t s);
+
+// ---- attn_prefill.cu ----
+struct PrefillTile {  // one 64-query tile of one sequence
+  int32_t q_row0;     // first token row of the tile in the batch
+  int32_t q_pos0;     // position of that token in its sequence
+  int32_t nrows;      // valid rows (<= 64)
+  int32_t bt_row;     // row of the sequence in the block table
+};
+int launch_attn_prefill(const bf16* q, const bf16* k_pages, const bf16* v_pages, const int32_t* block_table,
+                        int bt_stride, const PrefillTile* tiles_dev, int ntiles, bf16* out, int nq, int nkv, int hd,
+                        int block_size, cudaStream_t s);
+
+// ---- sampling.cu ----
+int launch_sample(const bf16* logits, int32_t* out, int nseq, int V, float temperature, int top_k, float top_p, uint64_t seed,
+                  uint64_t step, cudaStream_t s);
+
+int device_num_sms();
+
+}  // namespace b2

@@ -1,0 +1,189 @@
+/*
+ * b2_engine.h -- C ABI of the B200-native model-server engine (libb2engine.so).
+ *
+ * The reference (redhat-et/aws-k8s-ansible-provisioner) has no FFI or plugin interface for
+ * its hot path: the path is the forward pass of the model-server container that
+ * llm-d-deploy.yaml:176-184 launches for the model named at llm-d-deploy.yaml:118, reached
+ * over HTTP by llm-d-test.yaml:32-43,61-73.  The arithmetic contract is HF transformers'
+ * Qwen3 forward (models/qwen3/modeling_qwen3.py, cited per entry point below as "HF:").
+ * This header is the in-process boundary the C++ server (b2serve) and the Python host mirror
+ * (aws-k8s-ansible-provisioner_b200/engine.py) both bind; INTEGRATION.md shows the ctypes stub.
+ *
+ * Conventions: plain pointers and sizes only.  Every function returns 0 on success or a
+ * negative errno-style code; b2_last_error() returns the message for the calling thread.
+ * "host" pointers are caller-owned CPU memory; "dev" pointers are CUDA device memory.
+ * One engine per device; an engine is NOT thread-safe (the server serialises onto one GPU
+ * thread).  There is no CPU fallback anywhere behind this ABI.
+ */
+#ifndef B2_ENGINE_H
+#define B2_ENGINE_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B2_ABI_VERSION 1
+
+typedef struct b2_engine b2_engine;
+
+/* Architecture + runtime sizing.  Field meanings follow HF Qwen3Config
+ * (HF:models/qwen3/configuration_qwen3.py) and `vllm serve` flags the llm-d chart passes
+ * (--max-model-len, --block-size, --max-num-seqs, --gpu-memory-utilization). */
+typedef struct b2_config {
+  int32_t abi_version;       /* must be B2_ABI_VERSION */
+  int32_t num_layers;        /* 28 */
+  int32_t hidden;            /* 1024 */
+  int32_t num_q_heads;       /* 16 */
+  int32_t num_kv_heads;      /* 8 */
+  int32_t head_dim;          /* 128 (only 128 is built this round) */
+  int32_t intermediate;      /* 3072 */
+  int32_t vocab;             /* 151936 */
+  int32_t tie_embeddings;    /* 1: lm_head shares embed_tokens (HF:...modeling_qwen3.py:443) */
+  float   rms_eps;           /* 1e-6 */
+  float   rope_theta;        /* 1e6 */
+  int32_t max_model_len;     /* longest prompt+output per sequence */
+  int32_t block_size;        /* KV page size in tokens; 16 */
+  int32_t num_blocks;        /* KV pool size in pages; 0 = derive from gpu_mem_fraction */
+  float   gpu_mem_fraction;  /* used when num_blocks == 0 */
+  int32_t max_seqs;          /* max concurrently resident sequences (decode batch ceiling) */
+  int32_t max_batch_tokens;  /* max tokens in one prefill forward */
+  int32_t use_cuda_graphs;   /* 1: decode steps replay a captured graph per batch bucket */
+  const float* rope_inv_freq;/* optional host [head_dim/2] fp32 table (HF:...:129-131); NULL =
+                                computed as theta^(-2i/d) in double, rounded to fp32 */
+} b2_config;
+
+const char* b2_last_error(void);
+int  b2_abi_version(void);
+
+/* ---- engine lifetime ------------------------------------------------------------------- */
+/* Creates the engine on CUDA device `device`.  If safetensors_path is non-NULL, every
+ * HF-named tensor is read from that file (bf16) and the weights are finalised; otherwise
+ * the caller uploads tensors with b2_engine_load_tensor and calls b2_engine_finalize.
+ * Replaces: the model-server container start at llm-d-deploy.yaml:176-193. */
+int  b2_engine_create(const b2_config* cfg, const char* safetensors_path, int device, b2_engine** out);
+int  b2_engine_load_tensor(b2_engine* e, const char* hf_name, const void* host_bf16, size_t nbytes);
+int  b2_engine_finalize(b2_engine* e);
+void b2_engine_free(b2_engine* e);
+/* Info: KV pages total / free, bytes of weights resident. */
+int  b2_engine_info(b2_engine* e, int64_t* num_blocks, int64_t* free_blocks, int64_t* weight_bytes);
+
+/* ---- sequences (paged KV allocator; HF:...modeling_qwen3.py:270-271 cache update) ------- */
+/* Reserves pages for up to reserve_tokens tokens (prompt + output) and returns a slot id. */
+int  b2_seq_create(b2_engine* e, int32_t reserve_tokens, int32_t* seq_id);
+int  b2_seq_free(b2_engine* e, int32_t seq_id);
+int  b2_seq_len(b2_engine* e, int32_t seq_id);
+
+/* ---- forward passes --------------------------------------------------------------------- */
+/* Prefill: appends ids[seq_offsets[i] .. seq_offsets[i+1]) to sequence seq_ids[i], runs the
+ * forward over all appended tokens (HF:...modeling_qwen3.py:378-438), and returns the greedy
+ * next token of every sequence (HF:...:504-505 lm_head on the last position + argmax, lowest
+ * index on ties) in out_tokens (host, may be NULL).  The next token is NOT appended. */
+int  b2_prefill(b2_engine* e, const int32_t* ids, const int32_t* seq_offsets, int32_t nseq,
+                const int32_t* seq_ids, int32_t* out_tokens);
+
+/* One decode step: appends in_tokens[i] to sequence seq_ids[i] (in_tokens == NULL: append the
+ * token the previous forward produced for that sequence, kept on the device), runs one
+ * forward, returns the greedy next tokens in out_tokens (host, may be NULL = no D2H copy). */
+int  b2_decode_step(b2_engine* e, int32_t nseq, const int32_t* seq_ids, const int32_t* in_tokens,
+                    int32_t* out_tokens);
+
+/* `steps` decode steps back to back, token feedback on the device, no host round trip
+ * between steps.  elapsed_ms (may be NULL) receives the CUDA-event time of the region on
+ * the engine stream.  out_tokens (host, [steps][nseq], may be NULL) is copied at the end. */
+int  b2_decode_run(b2_engine* e, int32_t nseq, const int32_t* seq_ids, int32_t steps,
+                   int32_t* out_tokens, float* elapsed_ms);
+
+/* Logits of the last forward's last positions, [nseq][vocab] fp32 on the host. */
+int  b2_get_logits(b2_engine* e, int32_t nseq, float* out_logits);
+/* Residual stream after layer `layer` (0-based; -1 = embeddings, num_layers = final norm
+ * output) for the tokens of the last forward, [ntokens][hidden] as bf16 bits on the host.
+ * Only filled when debug capture was enabled with b2_set_debug(e, 1). */
+int  b2_set_debug(b2_engine* e, int32_t capture_hidden);
+int  b2_get_hidden(b2_engine* e, int32_t layer, int32_t ntokens, uint16_t* out_bf16);
+
+/* Sampling for the API surface (temperature / top-k / top-p over the last logits). */
+typedef struct b2_sampling {
+  float    temperature;  /* 0 = greedy */
+  int32_t  top_k;        /* <=0 = off */
+  float    top_p;        /* >=1 = off */
+  uint64_t seed;
+} b2_sampling;
+int  b2_sample(b2_engine* e, int32_t nseq, const b2_sampling* params, int32_t* out_tokens);
+/* Overrides the device-resident "next token" of each listed sequence (after sampling on host
+ * or with b2_sample) so the following b2_decode_step(in_tokens=NULL) consumes it. */
+int  b2_set_next_tokens(b2_engine* e, int32_t nseq, const int32_t* seq_ids, const int32_t* tokens);
+
+/* ---- measurement ------------------------------------------------------------------------ */
+#define B2_NUM_KERNEL_CLASSES 12
+/* Runs `steps` decode steps eagerly (no graph) with a CUDA event pair around every kernel
+ * launch on the engine stream; ms_by_class / launches_by_class receive totals per class
+ * (index = enum below).  Used by bench.py for the live roofline figure. */
+enum b2_kernel_class {
+  B2K_EMBED = 0, B2K_NORM = 1, B2K_GEMM_QKV = 2, B2K_ROPE_KV = 3, B2K_ATTN_DECODE = 4,
+  B2K_ATTN_COMBINE = 5, B2K_GEMM_O = 6, B2K_GEMM_GATEUP = 7, B2K_ACT = 8, B2K_GEMM_DOWN = 9,
+  B2K_LMHEAD = 10, B2K_MISC = 11
+};
+int  b2_decode_profile(b2_engine* e, int32_t nseq, const int32_t* seq_ids, int32_t steps,
+                       float* ms_by_class, int64_t* launches_by_class);
+/* Number of kernel launches (graph nodes included) issued by this engine so far. */
+int64_t b2_launch_count(b2_engine* e);
+
+/* ---- kernel-level entry points (tests call each kernel on device buffers) --------------- */
+/* All take a cudaStream_t as void*; NULL = default stream.  Shapes are row-major. */
+
+/* HF:...modeling_qwen3.py:59-64 (+ residual add :327,333).  h [T][H] bf16 in/out; delta may be
+ * NULL, bf16 [T][H] (delta_is_f32 = 0) or fp32 split partials [nsplit][T][H] (= 1) that are
+ * summed in split order and rounded to bf16 before the add.  x = RMSNorm(h) * w. */
+int b2k_add_rmsnorm(void* h_bf16, const void* delta, int delta_is_f32, int nsplit,
+                    const void* w_bf16, void* x_bf16, int T, int H, float eps, void* stream);
+
+/* HF:...:248-249,263-264 (QK-norm), :151-181 (RoPE), :270-271 (cache write).
+ * qkv [T][(nq+2nkv)*hd] bf16 (or fp32 partials), positions/slots [T] int32,
+ * cos_sin [max_pos][hd] bf16 = cos[hd/2] | sin[hd/2].  Writes q_out [T][nq*hd] and the K/V
+ * pages ([block][nkv][block_size][hd]). */
+int b2k_qknorm_rope_kv(const void* qkv, int qkv_is_f32, int nsplit, const void* qnorm_w,
+                       const void* knorm_w, const void* cos_sin, const int32_t* positions,
+                       const int32_t* slots, void* q_out, void* k_pages, void* v_pages, int T,
+                       int nq, int nkv, int hd, int block_size, float eps, void* stream);
+
+/* HF:...:81-83: act = silu(gate) * up, gu [T][2*I] (gate | up) bf16 or fp32 partials. */
+int b2k_silu_mul(const void* gu, int gu_is_f32, int nsplit, void* act_bf16, int T, int I, void* stream);
+
+/* y[T][N] = x[T][K] . W[N][K]^T, bf16 in, fp32 accumulate (HF nn.Linear, :236-247).
+ * impl: 0 = SIMT GEMV path, 1 = tcgen05/TMEM path.  nsplit > 1: out is fp32 partials
+ * [nsplit][T][N]; nsplit == 1 && out_is_f32 == 0: bf16 [T][N]. */
+int b2k_linear(const void* x_bf16, const void* w_bf16, void* out, int out_is_f32, int nsplit,
+               int T, int N, int K, int impl, void* stream);
+
+/* lm_head + greedy argmax fused (HF:...:504-505 + generate(do_sample=False)).
+ * logits_bf16 may be NULL.  out_tokens [T] int32 (device). scratch: [T] uint64 (device). */
+int b2k_lmhead_argmax(const void* x_bf16, const void* w_bf16, void* logits_bf16,
+                      int32_t* out_tokens, void* scratch_u64, int T, int V, int K, int impl,
+                      void* stream);
+
+/* HF:integrations/sdpa_attention.py:40-104 at T == 1: paged GQA decode attention, split-K.
+ * q [B][nq*hd]; pages as above; block_table [B][bt_stride]; seq_lens [B] (including the
+ * current token).  scratch_f32: >= B*nkv*nsplit*(nq/nkv)*(hd+2) floats (ignored if
+ * nsplit == 1).  out [B][nq*hd] bf16. */
+int b2k_attn_decode(const void* q, const void* k_pages, const void* v_pages,
+                    const int32_t* block_table, int bt_stride, const int32_t* seq_lens,
+                    void* scratch_f32, void* out, int B, int nq, int nkv, int hd, int block_size,
+                    int nsplit, void* stream);
+size_t b2k_attn_decode_scratch_floats(int B, int nq, int nkv, int hd, int nsplit);
+
+/* Same contract at T > 1 (causal): ragged prefill over the paged cache.  q [T][nq*hd];
+ * q_seq[T] / q_pos[T] int32 give the sequence row in block_table and the position of each
+ * query token (tokens of one sequence contiguous and ascending).  Host arrays. */
+int b2k_attn_prefill(const void* q, const void* k_pages, const void* v_pages,
+                     const int32_t* block_table_dev, int bt_stride, const int32_t* host_seq_first_tok,
+                     const int32_t* host_seq_pos0, const int32_t* host_seq_ntok,
+                     const int32_t* host_seq_row, int nseq, void* out, int nq, int nkv, int hd,
+                     int block_size, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B2_ENGINE_H */
