@@ -43,6 +43,7 @@ SIGNATURES = {
     "b2_seq_create": (_I, [_P, C.c_int32, _I32P]),
     "b2_seq_free": (_I, [_P, C.c_int32]),
     "b2_seq_len": (_I, [_P, C.c_int32]),
+    "b2_seq_truncate": (_I, [_P, C.c_int32, C.c_int32]),
     "b2_prefill": (_I, [_P, _I32P, _I32P, C.c_int32, _I32P, _I32P]),
     "b2_decode_step": (_I, [_P, C.c_int32, _I32P, _I32P, _I32P]),
     "b2_decode_run": (_I, [_P, C.c_int32, _I32P, C.c_int32, _I32P, C.POINTER(C.c_float)]),

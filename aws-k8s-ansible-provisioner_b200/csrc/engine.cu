@@ -773,6 +773,7 @@ extern "C" int b2_engine_create(const b2_config* cfg, const char* safetensors_pa
       e->free_blocks.reserve(nb);
       for (int64_t b = nb - 1; b >= 1; --b) e->free_blocks.push_back((int32_t)b);  // page 0 = null page
     }
+    if (e->force_gemm_impl == 0 || e->simt_max_tokens > 0) E_TRY(ensure_logits(e));  // SIMT lm_head writes logits
     e->ev_pool.resize(2 * 400);
     for (auto& ev : e->ev_pool) E_CUDA(cudaEventCreate(&ev));
     if (safetensors_path) {
@@ -892,6 +893,16 @@ extern "C" int b2_seq_free(b2_engine* e, int32_t seq_id) {
 extern "C" int b2_seq_len(b2_engine* e, int32_t seq_id) {
   if (!e || check_seq(e, seq_id) != 0) return -22;
   return e->seqs[seq_id].len;
+}
+
+extern "C" int b2_seq_truncate(b2_engine* e, int32_t seq_id, int32_t new_len) {
+  B2_REQUIRE(e, "b2_seq_truncate: null engine");
+  B2_TRY(check_seq(e, seq_id));
+  Seq& s = e->seqs[seq_id];
+  B2_REQUIRE(new_len >= 0 && new_len <= s.len, "b2_seq_truncate: new_len %d outside [0, %d]", new_len, s.len);
+  s.len = new_len;
+  e->cur_batch.clear();
+  return 0;
 }
 
 extern "C" int b2_prefill(b2_engine* e, const int32_t* ids, const int32_t* seq_offsets, int32_t nseq, const int32_t* seq_ids,

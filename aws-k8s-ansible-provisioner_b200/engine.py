@@ -110,6 +110,9 @@ class Engine:
     def seq_len(self, seq_id: int) -> int:
         return self.lib.b2_seq_len(self.h, int(seq_id))
 
+    def seq_truncate(self, seq_id: int, new_len: int) -> None:
+        check(self.lib.b2_seq_truncate(self.h, int(seq_id), int(new_len)), self.lib)
+
     def info(self) -> dict:
         a, b, c = C.c_int64(), C.c_int64(), C.c_int64()
         check(self.lib.b2_engine_info(self.h, C.byref(a), C.byref(b), C.byref(c)), self.lib)

@@ -1,0 +1,355 @@
+#!/usr/bin/env python
+"""bench.py -- BASELINE.json's metric: Qwen3-0.6B bf16 greedy decode throughput (tok/s) on B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W]            our engine (CUDA, sm_100a)
+    python bench.py --impl reference [--gpus N] [--steps K] ...     HF transformers on the host cores
+
+Workload (config.workload = "C2"): BASELINE.json configs[1] -- batch 64, 512-token prompts,
+256 generated tokens, paged KV.  One "step" = one decode forward over the whole batch
+(64 tokens).  With the defaults (W=8, K=248) the timed region generates tokens 9..256 of every
+sequence, i.e. the context grows from 520 to 768 tokens inside it.
+
+Numbers on the JSON line:
+  value      device-resident decode: K steps replayed as CUDA graphs with token feedback on the GPU,
+             timed with CUDA events on the engine's stream, max over ranks
+  e2e        the same K steps through the public C-ABI call b2_decode_step with HOST token buffers
+             in and out every step (H2D + D2H inside the timed region, host clock)
+  roofline   the dominant kernel (paged decode attention): algorithmic K/V bytes per launch over
+             its CUDA-event duration, measured live in an eager profiled pass at mid context
+  cpu_baseline  HF Qwen3 on the host CPU, same batch/context, a bounded number of steps
+N > 1: one replica per GPU (request-level data parallelism, no collective on the data path);
+ranks only meet at a gloo barrier around the timed region ("scaling": "weak").
+"""
+from __future__ import annotations
+
+import argparse
+import importlib
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+PKG = "aws-k8s-ansible-provisioner_b200"
+
+BATCH = 64
+PROMPT = 512
+OUT_TOKENS = 256
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            d = json.load(open(p))
+            return float(d["hbm_gbs"]), "measured"
+        except Exception:
+            pass
+    return 6650.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device: int):
+        self.device = device
+        self.proc = None
+        self.lines: list[str] = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.device), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def dist_setup(n_gpus: int):
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    dist = None
+    if world > 1:
+        import torch.distributed as dist_mod
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        # the replicas never exchange data: gloo carries only the barrier and the max-over-ranks
+        dist_mod.init_process_group("gloo", rank=rank, world_size=world)
+        dist = dist_mod
+    return rank, world, local, dist
+
+
+def barrier(dist):
+    if dist is not None:
+        dist.barrier()
+
+
+def reduce_max(dist, x: float) -> float:
+    if dist is None:
+        return x
+    import torch
+    t = torch.tensor([x], dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t[0])
+
+
+def reduce_sum(dist, x: float) -> float:
+    if dist is None:
+        return x
+    import torch
+    t = torch.tensor([x], dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    return float(t[0])
+
+
+# -------------------------------------------------------------------------------------------------
+# CPU arm: HF transformers Qwen3 decode steps on the host cores (the reference's arithmetic)
+# -------------------------------------------------------------------------------------------------
+def hf_cpu_decode(batch: int, ctx: int, steps: int, warmup: int, budget_s: float):
+    """Times HF Qwen3ForCausalLM decode forwards (batch x 1 token against a `ctx`-token KV cache,
+    the C2 decode shape) on CPU.  The KV cache is filled with random bf16 (no CPU prefill: that alone
+    would take minutes and is not part of the metric).  If `steps` full-batch steps would overrun
+    `budget_s`, the per-step sample is cut to a sub-batch and said so."""
+    import torch
+    from transformers import DynamicCache
+    from oracle.qwen3_oracle import QWEN3_0_6B, hf_model  # the checker's model builder (CPU arm only)
+
+    arch = QWEN3_0_6B
+    threads = torch.get_num_threads()
+    model = hf_model(arch, seed=0)
+
+    def make_cache(b):
+        cache = DynamicCache()
+        g = torch.Generator().manual_seed(3)
+        for layer in range(arch.num_layers):
+            k = torch.randn(b, arch.num_kv_heads, ctx, arch.head_dim, generator=g).to(torch.bfloat16)
+            v = torch.randn(b, arch.num_kv_heads, ctx, arch.head_dim, generator=g).to(torch.bfloat16)
+            cache.update(k, v, layer)
+        return cache
+
+    def run(b, n):
+        cache = make_cache(b)
+        tok = torch.randint(0, arch.vocab, (b, 1), generator=torch.Generator().manual_seed(4))
+        times = []
+        with torch.no_grad():
+            for i in range(n):
+                pos = torch.full((b, 1), ctx + i, dtype=torch.long)
+                t0 = time.perf_counter()
+                out = model(input_ids=tok, past_key_values=cache, position_ids=pos, use_cache=True)
+                tok = out.logits[:, -1].argmax(-1, keepdim=True)
+                times.append(time.perf_counter() - t0)
+        return times
+
+    b = batch
+    probe = run(min(b, 8), 2)  # cheap probe to size the sample
+    est_full = probe[-1] * max(1.0, b / min(b, 8))
+    while b > 1 and est_full * (steps + warmup) > budget_s:
+        b //= 2
+        est_full /= 2
+    times = run(b, steps + warmup)[warmup:]
+    total = sum(times)
+    return {"tok_s": b * len(times) / total, "ms_per_step": 1e3 * total / len(times), "batch": b, "threads": threads,
+            "steps": len(times), "ctx": ctx}
+
+
+def run_reference(args, rank, world, dist):
+    if rank != 0:
+        return
+    steps = args.steps
+    warm = max(1, min(args.warmup, 2))
+    r = hf_cpu_decode(BATCH, PROMPT + args.warmup, steps=min(steps, 16), warmup=warm, budget_s=150.0)
+    sample = "HF transformers Qwen3 bf16 sdpa on host CPU: %d decode steps, batch %d of %d, context %d (random KV, no prefill)" % (
+        r["steps"], r["batch"], BATCH, r["ctx"])
+    line = {
+        "impl": "reference", "metric": "decode_tok_s", "value": r["tok_s"], "unit": "tok/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+        "config": {"workload": "C2", "model": "Qwen3-0.6B arch random-init", "batch": BATCH, "prompt_len": PROMPT,
+                   "new_tokens": OUT_TOKENS, "l2": "inputs_exceed_l2"},
+        "cpu_baseline": {"value": r["tok_s"], "unit": "tok/s", "cores": r["threads"], "kind": "reference", "sample": sample},
+        "e2e": {"value": r["tok_s"], "unit": "tok/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "host_cpus": os.cpu_count(),
+    }
+    print(json.dumps(line), flush=True)
+
+
+# -------------------------------------------------------------------------------------------------
+# GPU arm
+# -------------------------------------------------------------------------------------------------
+def run_b200(args, rank, world, local, dist):
+    import numpy as np
+    import torch
+
+    pkg = importlib.import_module(PKG)
+    weights = importlib.import_module(PKG + ".weights")
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; this engine has no CPU path (use --impl reference for the CPU arm)")
+    K, W = args.steps, args.warmup
+    assert W >= 3, "at least 3 warm-up steps"
+    assert W + K <= OUT_TOKENS + 1024
+    cfg = pkg.EngineConfig(max_model_len=PROMPT + W + K + 16, max_seqs=BATCH, max_batch_tokens=8192, use_cuda_graphs=True)
+    cfg.num_blocks = BATCH * ((cfg.max_model_len + 15) // 16) + 8
+    t0 = time.time()
+    sd = weights.random_state_dict(cfg, seed=0)
+    eng = pkg.Engine(cfg, device=local)
+    eng.load_state_dict(sd)
+    del sd
+    g = torch.Generator().manual_seed(1 + rank)
+    prompts = torch.randint(0, cfg.vocab, (BATCH, PROMPT), generator=g, dtype=torch.int32).numpy()
+    sids = [eng.seq_create(cfg.max_model_len) for _ in range(BATCH)]
+    per_chunk = max(1, cfg.max_batch_tokens // PROMPT)
+    torch.cuda.synchronize(local)
+    tp0 = time.perf_counter()
+    for i in range(0, BATCH, per_chunk):
+        eng.prefill(sids[i:i + per_chunk], [p.tolist() for p in prompts[i:i + per_chunk]])
+    prefill_s = time.perf_counter() - tp0
+    setup_s = time.time() - t0
+
+    # ---- device-resident decode: warm-up, then K timed steps -----------------------------------
+    eng.decode_run(sids, W, want_tokens=False)
+    sampler = ClockSampler(local)
+    torch.cuda.synchronize(local)
+    barrier(dist)
+    sampler.start()
+    l0 = eng.launch_count()
+    _, ms = eng.decode_run(sids, K, want_tokens=False)
+    torch.cuda.synchronize(local)
+    barrier(dist)
+    clocks = sampler.stop()
+    launches = eng.launch_count() - l0
+    ms_max = reduce_max(dist, ms)
+    tok_s = world * BATCH * K / (ms_max / 1e3)
+
+    # ---- end to end through the public call, host buffers in and out every step ----------------
+    for s in sids:
+        eng.seq_truncate(s, PROMPT + W)
+    tok = eng.decode_step(sids)  # re-seeds the device batch after the truncate (not timed)
+    for s in sids:
+        eng.seq_truncate(s, PROMPT + W)
+    torch.cuda.synchronize(local)
+    barrier(dist)
+    step_times = []
+    te0 = time.perf_counter()
+    for _ in range(K):
+        ts = time.perf_counter()
+        tok = eng.decode_step(sids, in_tokens=tok)  # H2D ids, graph launch, D2H ids, sync
+        step_times.append(time.perf_counter() - ts)
+    e2e_s = time.perf_counter() - te0
+    barrier(dist)
+    e2e_max = reduce_max(dist, e2e_s)
+    e2e_tok_s = world * BATCH * K / e2e_max
+
+    # ---- live roofline of the dominant kernel (eager profiled pass at mid context) --------------
+    mid = PROMPT + W + K // 2
+    for s in sids:
+        eng.seq_truncate(s, mid)
+    prof = eng.decode_profile(sids, 3)
+    attn = prof["attn_decode"]
+    attn_ms = attn["ms"] / max(1, attn["launches"])
+    ctx_mid = mid + 2  # mean context of the three profiled steps (the step's own token included)
+    kv_layer_token = 2 * cfg.num_kv_heads * cfg.head_dim * 2
+    attn_bytes = BATCH * ctx_mid * kv_layer_token + 2 * BATCH * cfg.num_q_heads * cfg.head_dim * 2
+    peak, peak_kind = measured_peaks()
+    achieved = attn_bytes / (attn_ms / 1e3) / 1e9
+    prof_total = sum(v["ms"] for v in prof.values()) / 3.0
+    kernel_ms = {k: round(v["ms"] / 3.0, 4) for k, v in prof.items() if v["launches"]}
+    # whole-step algorithmic bytes: W + B*S*kv + B*kv at the mean context of the timed region
+    s_mean = PROMPT + W + (K + 1) / 2.0
+    step_bytes = cfg.weight_bytes() + BATCH * s_mean * cfg.kv_bytes_per_token() + BATCH * cfg.kv_bytes_per_token()
+    step_frac = (step_bytes / (ms_max / K / 1e3) / 1e9) / peak
+
+    line = {
+        "metric": "decode_tok_s", "value": tok_s, "unit": "tok/s", "n_gpus": world, "steps": K, "warmup": W,
+        "ms_per_step": ms_max / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
+        "data": "synthetic",
+        "config": {"workload": "C2", "model": "Qwen3-0.6B arch random-init", "batch": BATCH, "prompt_len": PROMPT,
+                   "new_tokens": W + K, "kv_block": 16, "parallelism": "dp%d replicas, no collective" % world,
+                   "l2": "inputs_exceed_l2 (%.2f GB read per step)" % (step_bytes / 1e9)},
+        "e2e": {"value": e2e_tok_s, "unit": "tok/s", "h2d_bytes_per_step": BATCH * 4, "d2h_bytes_per_step": BATCH * 4},
+        "tpot_ms_p50": 1e3 * statistics.median(step_times),
+        "gpu_launches": int(launches),
+        "clocks": clocks,
+        "roofline": {"bound": "hbm", "kernel": "attn_decode_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                     "frac": achieved / peak, "traffic": None, "peak_kind": peak_kind, "bytes_per_launch": attn_bytes,
+                     "ms_per_launch": attn_ms, "context": ctx_mid},
+        "step_hbm_frac": step_frac,
+        "step_bytes": step_bytes,
+        "kernel_ms_per_step_eager": kernel_ms,
+        "eager_step_ms": prof_total,
+        "prefill_s": prefill_s,
+        "setup_s": setup_s,
+    }
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        try:
+            r = hf_cpu_decode(BATCH, PROMPT + W, steps=6, warmup=1, budget_s=40.0)
+            line["cpu_baseline"] = {
+                "value": r["tok_s"], "unit": "tok/s", "cores": r["threads"], "kind": "reference",
+                "sample": "HF transformers Qwen3 bf16 sdpa on host CPU: %d decode steps, batch %d of %d, context %d (random KV, "
+                          "no prefill); host has %d logical CPUs" % (r["steps"], r["batch"], BATCH, r["ctx"], os.cpu_count())}
+        except Exception as ex:  # the GPU numbers stand on their own
+            line["cpu_baseline"] = {"value": None, "unit": "tok/s", "cores": 0, "kind": "reference", "sample": "failed: %r" % (ex,)}
+    eng.close()
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=248)
+    ap.add_argument("--warmup", type=int, default=8)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank, world, local, dist = dist_setup(args.gpus)
+    try:
+        if args.impl == "reference":
+            run_reference(args, rank, world, dist)
+        else:
+            run_b200(args, rank, world, local, dist)
+    finally:
+        if dist is not None:
+            dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

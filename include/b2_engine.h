@@ -75,6 +75,9 @@ int  b2_engine_info(b2_engine* e, int64_t* num_blocks, int64_t* free_blocks, int
 int  b2_seq_create(b2_engine* e, int32_t reserve_tokens, int32_t* seq_id);
 int  b2_seq_free(b2_engine* e, int32_t seq_id);
 int  b2_seq_len(b2_engine* e, int32_t seq_id);
+/* Drops the tail of a sequence (new_len <= current length); its pages stay reserved.  Used to
+ * re-run a measurement over the same context and by stop-string handling in the server. */
+int  b2_seq_truncate(b2_engine* e, int32_t seq_id, int32_t new_len);
 
 /* ---- forward passes --------------------------------------------------------------------- */
 /* Prefill: appends ids[seq_offsets[i] .. seq_offsets[i+1]) to sequence seq_ids[i], runs the

@@ -1,0 +1,308 @@
+"""Kernel-level parity (GPU): every hand-written kernel is called through the C ABI
+(include/b2_engine.h, b2k_*) on seeded inputs and compared with the oracle's function for the
+same HF lines.  Bars: elementwise kernels reproduce the oracle's rounding points, so outputs must
+be within 1 bf16 ulp with only a small fraction differing at all (fp32 reduction order);
+GEMM/attention are fp32-accumulate with a different summation order, bar = 1-2 bf16 ulp."""
+import ctypes as C
+
+import pytest
+import torch
+
+from _util import assert_bf16_close, cuda_stream_ptr, pkg, ptr, rel_err
+from oracle.qwen3_oracle import (QWEN3_0_6B, apply_rope, attention_explicit, rms_norm, rope_cos_sin)
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def lib():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    return pkg().load_library()
+
+
+def chk(lib, rc):
+    assert rc == 0, (rc, lib.b2_last_error())
+    torch.cuda.synchronize()
+
+
+def bf(*shape, scale=1.0, seed=0):
+    g = torch.Generator().manual_seed(seed)
+    return (torch.randn(*shape, generator=g) * scale).to(torch.bfloat16)
+
+
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("mode", ["none", "bf16", "f32x3"])
+@pytest.mark.parametrize("H", [1024, 256])
+def test_add_rmsnorm(lib, mode, H):
+    T = 37
+    h = bf(T, H, seed=1)
+    w = (1 + 0.25 * torch.randn(H, generator=torch.Generator().manual_seed(2))).to(torch.bfloat16)
+    h_d, w_d = h.cuda(), w.cuda()
+    x_d = torch.empty_like(h_d)
+    if mode == "none":
+        chk(lib, lib.b2k_add_rmsnorm(ptr(h_d), None, 0, 0, ptr(w_d), ptr(x_d), T, H, 1e-6, cuda_stream_ptr()))
+        h_ref = h
+    elif mode == "bf16":
+        d = bf(T, H, scale=0.5, seed=3)
+        d_d = d.cuda()
+        chk(lib, lib.b2k_add_rmsnorm(ptr(h_d), ptr(d_d), 0, 1, ptr(w_d), ptr(x_d), T, H, 1e-6, cuda_stream_ptr()))
+        h_ref = h + d
+    else:
+        parts = torch.randn(3, T, H, generator=torch.Generator().manual_seed(4)) * 0.3
+        p_d = parts.cuda()
+        chk(lib, lib.b2k_add_rmsnorm(ptr(h_d), ptr(p_d), 1, 3, ptr(w_d), ptr(x_d), T, H, 1e-6, cuda_stream_ptr()))
+        o = ((parts[0] + parts[1]) + parts[2]).to(torch.bfloat16)  # split order, one rounding (nn.Linear output)
+        h_ref = h + o
+    assert torch.equal(h_d.cpu(), h_ref), "residual stream must be bit-exact"
+    x_ref = rms_norm(h_ref, w, 1e-6)
+    assert_bf16_close(x_d, x_ref, 1, 0.01, "rmsnorm " + mode)
+
+
+@pytest.mark.parametrize("f32in", [False, True])
+def test_qknorm_rope_kv(lib, f32in):
+    a = QWEN3_0_6B
+    T, nq, nkv, hd, bs = 19, a.num_q_heads, a.num_kv_heads, a.head_dim, 16
+    nblocks = 12
+    qkv = bf(T, (nq + 2 * nkv) * hd, seed=5)
+    g = torch.Generator().manual_seed(6)
+    qw = (1 + 0.25 * torch.randn(hd, generator=g)).to(torch.bfloat16)
+    kw = (1 + 0.25 * torch.randn(hd, generator=g)).to(torch.bfloat16)
+    positions = torch.randint(0, 4000, (T,), generator=g, dtype=torch.int32)
+    slots = torch.randperm(nblocks * bs, generator=g)[:T].to(torch.int32)
+    slots[3] = -1  # padding token: no cache write
+    maxpos = 4096
+    cos, sin = rope_cos_sin(a, torch.arange(maxpos)[None, :])
+    table = torch.cat([cos[0, :, :64], sin[0, :, :64]], dim=-1).contiguous()  # [pos][cos64 | sin64]
+    kp = torch.zeros(nblocks, nkv, bs, hd, dtype=torch.bfloat16, device="cuda")
+    vp = torch.zeros_like(kp)
+    q_out = torch.empty(T, nq * hd, dtype=torch.bfloat16, device="cuda")
+    if f32in:
+        parts = torch.randn(2, T, (nq + 2 * nkv) * hd, generator=g)
+        src = parts.cuda()
+        qkv = (parts[0] + parts[1]).to(torch.bfloat16)
+        rc = lib.b2k_qknorm_rope_kv(ptr(src), 1, 2, ptr(qw.cuda()), ptr(kw.cuda()), ptr(table.cuda()), ptr(positions.cuda()),
+                                    ptr(slots.cuda()), ptr(q_out), ptr(kp), ptr(vp), T, nq, nkv, hd, bs, 1e-6, cuda_stream_ptr())
+    else:
+        src = qkv.cuda()
+        rc = lib.b2k_qknorm_rope_kv(ptr(src), 0, 1, ptr(qw.cuda()), ptr(kw.cuda()), ptr(table.cuda()), ptr(positions.cuda()),
+                                    ptr(slots.cuda()), ptr(q_out), ptr(kp), ptr(vp), T, nq, nkv, hd, bs, 1e-6, cuda_stream_ptr())
+    chk(lib, rc)
+    q = qkv[:, : nq * hd].view(1, T, nq, hd)
+    k = qkv[:, nq * hd: (nq + nkv) * hd].view(1, T, nkv, hd)
+    v = qkv[:, (nq + nkv) * hd:].view(T, nkv, hd)
+    qn = rms_norm(q, qw, 1e-6).transpose(1, 2)
+    kn = rms_norm(k, kw, 1e-6).transpose(1, 2)
+    c, s = rope_cos_sin(a, positions[None, :].long())
+    qr, kr = apply_rope(qn, kn, c, s)
+    q_ref = qr.transpose(1, 2).reshape(T, nq * hd)
+    k_ref = kr.transpose(1, 2)[0]  # [T][nkv][hd]
+    assert_bf16_close(q_out, q_ref, 1, 0.01, "q rope")
+    kp_c, vp_c = kp.cpu(), vp.cpu()
+    for t in range(T):
+        sl = int(slots[t])
+        if sl < 0:
+            continue
+        assert_bf16_close(kp_c[sl // bs, :, sl % bs, :], k_ref[t], 1, 0.02, "k page t=%d" % t)
+        assert torch.equal(vp_c[sl // bs, :, sl % bs, :], v[t]), "v page must be a bit-exact copy"
+    written = {int(s_) for s_ in slots if s_ >= 0}
+    for sl in range(nblocks * bs):
+        if sl not in written:
+            assert not kp_c[sl // bs, :, sl % bs, :].any(), "stray K write at slot %d" % sl
+
+
+@pytest.mark.parametrize("f32in", [False, True])
+def test_silu_mul(lib, f32in):
+    T, I = 23, 3072
+    g = torch.Generator().manual_seed(7)
+    if f32in:
+        parts = torch.randn(3, T, 2 * I, generator=g)
+        gu = ((parts[0] + parts[1]) + parts[2]).to(torch.bfloat16)
+        src = parts.cuda()
+    else:
+        gu = (torch.randn(T, 2 * I, generator=g) * 2).to(torch.bfloat16)
+        src = gu.cuda()
+    act = torch.empty(T, I, dtype=torch.bfloat16, device="cuda")
+    chk(lib, lib.b2k_silu_mul(ptr(src), int(f32in), 3 if f32in else 1, ptr(act), T, I, cuda_stream_ptr()))
+    ref = torch.nn.functional.silu(gu[:, :I]) * gu[:, I:]
+    assert_bf16_close(act, ref, 1, 0.01, "silu_mul")
+
+
+# ---------------------------------------------------------------------------------------------
+LIN_SHAPES = [(1, 1024, 1024), (3, 4096, 1024), (16, 1024, 2048), (64, 6144, 1024), (64, 1024, 3072), (100, 256, 512),
+              (300, 1024, 1024), (513, 1024, 256)]
+
+
+@pytest.mark.parametrize("impl", [0, 1])
+@pytest.mark.parametrize("T,N,K", LIN_SHAPES)
+def test_linear_bf16(lib, impl, T, N, K):
+    if impl == 0 and T > 64:
+        pytest.skip("SIMT GEMV path is for tiny batches")
+    x = bf(T, K, seed=8)
+    w = bf(N, K, scale=0.05, seed=9)
+    out = torch.full((T, N), float("nan"), dtype=torch.bfloat16, device="cuda")
+    chk(lib, lib.b2k_linear(ptr(x.cuda()), ptr(w.cuda()), ptr(out), 0, 1, T, N, K, impl, cuda_stream_ptr()))
+    ref32 = x.float() @ w.float().t()
+    assert_bf16_close(out, ref32.to(torch.bfloat16), 1, 0.02, "linear impl=%d %s" % (impl, (T, N, K)), abs_floor=1e-3)
+    # and against the oracle's own op (HF nn.Linear on CPU)
+    ref_hf = torch.nn.functional.linear(x, w)
+    assert_bf16_close(out, ref_hf, 1, 0.03, "linear vs F.linear", abs_floor=1e-3)
+
+
+@pytest.mark.parametrize("T,N,K,ns", [(64, 1024, 2048, 16), (64, 4096, 1024, 4), (7, 1024, 3072, 16), (64, 6144, 1024, 3),
+                                     (200, 1024, 1024, 2)])
+def test_linear_splitk_partials(lib, T, N, K, ns):
+    x = bf(T, K, seed=10)
+    w = bf(N, K, scale=0.05, seed=11)
+    out = torch.full((ns, T, N), float("nan"), dtype=torch.float32, device="cuda")
+    chk(lib, lib.b2k_linear(ptr(x.cuda()), ptr(w.cuda()), ptr(out), 1, ns, T, N, K, 1, cuda_stream_ptr()))
+    assert torch.isfinite(out).all()
+    total = out.sum(0).cpu()
+    ref = x.float() @ w.float().t()
+    assert rel_err(total, ref) < 2e-5
+    # each split covers its own k-range: partial s == x[:, ks] @ w[:, ks]^T
+    kb = K // 64
+    kps = -(-kb // ns)
+    for s in (0, ns - 1):
+        k0, k1 = s * kps * 64, min(K, (s + 1) * kps * 64)
+        part = x[:, k0:k1].float() @ w[:, k0:k1].float().t()
+        assert rel_err(out[s].cpu(), part) < 2e-5, "split %d" % s
+
+
+def test_linear_is_deterministic(lib):
+    T, N, K = 64, 1024, 2048
+    x, w = bf(T, K, seed=12).cuda(), bf(N, K, scale=0.05, seed=13).cuda()
+    outs = []
+    for _ in range(3):
+        o = torch.empty(16, T, N, dtype=torch.float32, device="cuda")
+        chk(lib, lib.b2k_linear(ptr(x), ptr(w), ptr(o), 1, 16, T, N, K, 1, cuda_stream_ptr()))
+        outs.append(o.cpu())
+    assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])
+
+
+@pytest.mark.parametrize("impl", [0, 1])
+@pytest.mark.parametrize("T", [1, 5, 64])
+def test_lmhead_argmax_full_vocab(lib, impl, T):
+    a = QWEN3_0_6B
+    V, K = a.vocab, a.hidden
+    x = bf(T, K, seed=14)
+    w = bf(V, K, scale=0.02, seed=15)
+    # forced ties: rows 777 and 90000 equal the arg-max row -> the lowest index must win
+    ref_logits = torch.nn.functional.linear(x, w)
+    top = int(ref_logits[0].argmax())
+    w[90000] = w[top]
+    if top > 777:
+        w[777] = w[top]
+    x_d, w_d = x.cuda(), w.cuda()
+    logits = torch.empty(T, V, dtype=torch.bfloat16, device="cuda")
+    toks = torch.full((T,), -1, dtype=torch.int32, device="cuda")
+    scratch = torch.zeros(T, dtype=torch.int64, device="cuda")
+    chk(lib, lib.b2k_lmhead_argmax(ptr(x_d), ptr(w_d), ptr(logits), ptr(toks), ptr(scratch), T, V, K, impl, cuda_stream_ptr()))
+    ref_logits = torch.nn.functional.linear(x, w)
+    assert_bf16_close(logits, ref_logits, 1, 0.03, "lm_head logits", abs_floor=1e-3)
+    # the fused arg-max must equal torch.argmax over the kernel's own bf16 logits (first index on ties)
+    assert torch.equal(toks.cpu().long(), logits.cpu().float().argmax(-1))
+    assert int(toks[0]) == min(top, 777)
+    if impl == 1:  # without the logits buffer the fused path must give the same tokens
+        toks2 = torch.full((T,), -1, dtype=torch.int32, device="cuda")
+        chk(lib, lib.b2k_lmhead_argmax(ptr(x_d), ptr(w_d), None, ptr(toks2), ptr(scratch), T, V, K, 1, cuda_stream_ptr()))
+        assert torch.equal(toks, toks2)
+
+
+# ---------------------------------------------------------------------------------------------
+def build_pages(seq_lens, nkv, hd, bs, seed):
+    """Random K/V per sequence scattered into pages through a shuffled block table."""
+    g = torch.Generator().manual_seed(seed)
+    B = len(seq_lens)
+    nblk = [-(-s // bs) for s in seq_lens]
+    total = sum(nblk) + 1
+    perm = (torch.randperm(total - 1, generator=g) + 1).tolist()  # page 0 stays the null page
+    stride = max(nblk) + 2
+    bt = torch.zeros(B, stride, dtype=torch.int32)
+    kp = torch.zeros(total, nkv, bs, hd, dtype=torch.bfloat16)
+    vp = torch.zeros_like(kp)
+    ks, vs = [], []
+    it = iter(perm)
+    for b, s in enumerate(seq_lens):
+        k = torch.randn(nkv, s, hd, generator=g).to(torch.bfloat16)
+        v = torch.randn(nkv, s, hd, generator=g).to(torch.bfloat16)
+        ks.append(k)
+        vs.append(v)
+        for j in range(nblk[b]):
+            pg = next(it)
+            bt[b, j] = pg
+            n = min(bs, s - j * bs)
+            kp[pg, :, :n] = k[:, j * bs: j * bs + n]
+            vp[pg, :, :n] = v[:, j * bs: j * bs + n]
+            if n < bs:  # stale finite data beyond the sequence end must be ignored
+                kp[pg, :, n:] = 3.0
+                vp[pg, :, n:] = -7.0
+    return bt, kp, vp, ks, vs
+
+
+@pytest.mark.parametrize("nsplit", [1, 2, 4, 16])
+def test_attn_decode(lib, nsplit):
+    a = QWEN3_0_6B
+    nq, nkv, hd, bs = a.num_q_heads, a.num_kv_heads, a.head_dim, 16
+    seq_lens = [1, 16, 17, 37, 300, 1023, 640]
+    B = len(seq_lens)
+    bt, kp, vp, ks, vs = build_pages(seq_lens, nkv, hd, bs, seed=20)
+    q = bf(B, nq * hd, seed=21)
+    out = torch.full((B, nq * hd), float("nan"), dtype=torch.bfloat16, device="cuda")
+    nfl = lib.b2k_attn_decode_scratch_floats(B, nq, nkv, hd, nsplit)
+    scratch = torch.full((max(nfl, 1),), float("nan"), dtype=torch.float32, device="cuda")
+    chk(lib, lib.b2k_attn_decode(ptr(q.cuda()), ptr(kp.cuda()), ptr(vp.cuda()), ptr(bt.cuda()), bt.shape[1],
+                                ptr(torch.tensor(seq_lens, dtype=torch.int32).cuda()), ptr(scratch), ptr(out), B, nq, nkv, hd, bs,
+                                nsplit, cuda_stream_ptr()))
+    for b in range(B):
+        ref = attention_explicit(q[b].view(1, nq, 1, hd), ks[b][None], vs[b][None], hd ** -0.5, False).reshape(nq * hd)
+        assert_bf16_close(out[b], ref, 2, 0.25, "attn_decode b=%d S=%d nsplit=%d" % (b, seq_lens[b], nsplit), abs_floor=2e-3)
+        ref_sdpa = torch.nn.functional.scaled_dot_product_attention(q[b].view(1, nq, 1, hd), ks[b][None], vs[b][None],
+                                                                    enable_gqa=True).reshape(nq * hd)
+        assert rel_err(out[b], ref_sdpa) < 1e-2
+
+
+def test_attn_decode_empty_and_padding_rows(lib):
+    """A graph bucket pads the batch with rows of length 0: their output must be zeros, not NaN."""
+    a = QWEN3_0_6B
+    nq, nkv, hd, bs = a.num_q_heads, a.num_kv_heads, a.head_dim, 16
+    seq_lens = [0, 5, 0]
+    bt, kp, vp, ks, vs = build_pages([1, 5, 1], nkv, hd, bs, seed=22)
+    q = bf(3, nq * hd, seed=23)
+    for nsplit in (1, 2):
+        out = torch.full((3, nq * hd), float("nan"), dtype=torch.bfloat16, device="cuda")
+        scratch = torch.zeros(max(1, lib.b2k_attn_decode_scratch_floats(3, nq, nkv, hd, nsplit)), device="cuda")
+        chk(lib, lib.b2k_attn_decode(ptr(q.cuda()), ptr(kp.cuda()), ptr(vp.cuda()), ptr(bt.cuda()), bt.shape[1],
+                                    ptr(torch.tensor(seq_lens, dtype=torch.int32).cuda()), ptr(scratch), ptr(out), 3, nq, nkv, hd, bs,
+                                    nsplit, cuda_stream_ptr()))
+        o = out.cpu()
+        assert not o[0].any() and not o[2].any()
+        ref = attention_explicit(q[1].view(1, nq, 1, hd), ks[1][None], vs[1][None], hd ** -0.5, False).reshape(nq * hd)
+        assert_bf16_close(o[1], ref, 2, 0.25, "attn_decode mid row", abs_floor=2e-3)
+
+
+@pytest.mark.parametrize("case", ["fresh", "chunked"])
+def test_attn_prefill(lib, case):
+    a = QWEN3_0_6B
+    nq, nkv, hd, bs = a.num_q_heads, a.num_kv_heads, a.head_dim, 16
+    if case == "fresh":
+        pos0 = [0, 0, 0, 0]
+        ntok = [5, 64, 130, 1]
+    else:  # queries appended after an existing prefix (chunked prefill)
+        pos0 = [70, 3, 129]
+        ntok = [61, 200, 64]
+    total_len = [p + n for p, n in zip(pos0, ntok)]
+    bt, kp, vp, ks, vs = build_pages(total_len, nkv, hd, bs, seed=30)
+    T = sum(ntok)
+    q = bf(T, nq * hd, seed=31)
+    first = [sum(ntok[:i]) for i in range(len(ntok))]
+    out = torch.full((T, nq * hd), float("nan"), dtype=torch.bfloat16, device="cuda")
+    I32 = lambda v: (C.c_int32 * len(v))(*v)
+    chk(lib, lib.b2k_attn_prefill(ptr(q.cuda()), ptr(kp.cuda()), ptr(vp.cuda()), ptr(bt.cuda()), bt.shape[1], I32(first), I32(pos0),
+                                 I32(ntok), I32(list(range(len(ntok)))), len(ntok), ptr(out), nq, nkv, hd, bs, cuda_stream_ptr()))
+    o = out.cpu()
+    for i, n in enumerate(ntok):
+        qs = q[first[i]: first[i] + n].view(n, nq, hd).transpose(0, 1)[None]  # [1][nq][n][hd]
+        ref = attention_explicit(qs, ks[i][None], vs[i][None], hd ** -0.5, True)  # tril(diagonal=S-T): causal with prefix
+        ref = ref[0].transpose(0, 1).reshape(n, nq * hd)
+        assert_bf16_close(o[first[i]: first[i] + n], ref, 2, 0.3, "attn_prefill seq %d (%s)" % (i, case), abs_floor=2e-3)
