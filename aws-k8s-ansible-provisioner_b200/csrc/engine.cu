@@ -44,6 +44,8 @@ struct Seq {
   bool active = false;
   int len = 0;        // tokens whose K/V are in the cache
   int reserved = 0;   // token capacity of the pages held
+  int32_t next_token = 0;   // greedy token the last forward produced for this sequence (host copy)
+  bool next_valid = false;  // false when only the device holds it (no D2H was requested)
   std::vector<int32_t> blocks;
 };
 
@@ -106,6 +108,8 @@ struct b2_engine {
   size_t h_stage_ints = 0;
   PrefillTile* h_tiles = nullptr;
   int32_t* h_out = nullptr;
+  int32_t* h_tok = nullptr;
+  cudaEvent_t ev_tok = nullptr;
 
   std::vector<int32_t> cur_batch;  // sequence ids resident in d_* (decode fast path)
   int cur_B = 0;                   // padded batch (graph bucket)
@@ -749,6 +753,8 @@ extern "C" int b2_engine_create(const b2_config* cfg, const char* safetensors_pa
     E_CUDA(cudaMallocHost(&e->h_stage, e->h_stage_ints * sizeof(int32_t)));
     E_CUDA(cudaMallocHost(&e->h_tiles, (size_t)e->tiles_cap * sizeof(PrefillTile)));
     E_CUDA(cudaMallocHost(&e->h_out, (size_t)e->log_cap_steps * c.max_seqs * sizeof(int32_t)));
+    E_CUDA(cudaMallocHost(&e->h_tok, Bcap * sizeof(int32_t)));
+    E_CUDA(cudaEventCreateWithFlags(&e->ev_tok, cudaEventDisableTiming));
     e->seqs.resize(c.max_seqs);
     // ---- KV pool ----
     {
@@ -833,6 +839,8 @@ extern "C" void b2_engine_free(b2_engine* e) {
   if (e->h_stage) cudaFreeHost(e->h_stage);
   if (e->h_tiles) cudaFreeHost(e->h_tiles);
   if (e->h_out) cudaFreeHost(e->h_out);
+  if (e->h_tok) cudaFreeHost(e->h_tok);
+  if (e->ev_tok) cudaEventDestroy(e->ev_tok);
   if (e->stream) cudaStreamDestroy(e->stream);
   delete e;
 }
@@ -955,7 +963,12 @@ extern "C" int b2_prefill(b2_engine* e, const int32_t* ids, const int32_t* seq_o
   // the produced tokens become the device-resident "next input" of these sequences
   B2_CUDA_OK(cudaMemcpyAsync(e->h_out, e->d_out_tokens, nseq * 4, cudaMemcpyDeviceToHost, e->stream));
   B2_CUDA_OK(cudaStreamSynchronize(e->stream));
-  for (int i = 0; i < nseq; ++i) e->seqs[seq_ids[i]].len += seq_offsets[i + 1] - seq_offsets[i];
+  for (int i = 0; i < nseq; ++i) {
+    Seq& s = e->seqs[seq_ids[i]];
+    s.len += seq_offsets[i + 1] - seq_offsets[i];
+    s.next_token = e->h_out[i];
+    s.next_valid = true;
+  }
   if (out_tokens) memcpy(out_tokens, e->h_out, nseq * 4);
   // remember them host-side too so the first decode step can seed d_tokens
   e->last_n = nseq;
@@ -979,22 +992,45 @@ int prepare_decode(b2_engine* e, int n, const int32_t* seq_ids, const int32_t* i
   const int B = e->cfg.use_cuda_graphs ? bucket_batch(n) : n;
   const bool same = (int)e->cur_batch.size() == n && e->cur_B == B && std::equal(seq_ids, seq_ids + n, e->cur_batch.begin());
   if (!same) {
-    // Device tokens of the previous forward are in d_out_tokens order of THAT forward; the
-    // caller must pass in_tokens when the batch composition changes.
-    B2_REQUIRE(in_tokens != nullptr || e->last_n == n, "decode: batch changed, in_tokens required");
+    // The batch composition changed: the device-resident "next tokens" belong to another batch
+    // order, so seed this batch from the host copies kept per sequence (or from in_tokens).
     if (in_tokens == nullptr) {
-      // same count, first step after prefill: seed d_tokens from the prefill's outputs
-      B2_CUDA_OK(cudaMemcpyAsync(e->d_tokens, e->d_out_tokens, n * 4, cudaMemcpyDeviceToDevice, e->stream));
+      for (int i = 0; i < n; ++i) {
+        Seq& s = e->seqs[seq_ids[i]];
+        B2_REQUIRE(s.next_valid, "decode: batch changed and sequence %d has no host copy of its next token; pass in_tokens",
+                   seq_ids[i]);
+        e->h_stage[i] = s.next_token;
+      }
+      for (int i = n; i < B; ++i) e->h_stage[i] = 0;
+      B2_CUDA_OK(cudaMemcpyAsync(e->d_tokens, e->h_stage, B * 4, cudaMemcpyHostToDevice, e->stream));
+      B2_CUDA_OK(cudaStreamSynchronize(e->stream));
     }
     B2_TRY(upload_decode_batch(e, n, seq_ids, B));
   }
   if (in_tokens != nullptr) {
-    memcpy(e->h_stage, in_tokens, n * 4);
-    for (int i = n; i < B; ++i) e->h_stage[i] = 0;
-    B2_CUDA_OK(cudaMemcpyAsync(e->d_tokens, e->h_stage, B * 4, cudaMemcpyHostToDevice, e->stream));
+    // dedicated pinned slot for the per-step token upload; the event keeps a later call from
+    // overwriting it while the copy is still in flight (callers may skip the D2H sync)
+    B2_CUDA_OK(cudaEventSynchronize(e->ev_tok));
+    memcpy(e->h_tok, in_tokens, n * 4);
+    for (int i = n; i < B; ++i) e->h_tok[i] = 0;
+    B2_CUDA_OK(cudaMemcpyAsync(e->d_tokens, e->h_tok, B * 4, cudaMemcpyHostToDevice, e->stream));
+    B2_CUDA_OK(cudaEventRecord(e->ev_tok, e->stream));
   }
   *B_out = B;
   *split_out = pick_attn_split(e, B, max_len);
+  return 0;
+}
+}  // namespace
+
+namespace {
+int fetch_next_tokens(b2_engine* e, int nseq, const int32_t* seq_ids) {
+  int32_t* tmp = e->h_stage;
+  B2_CUDA_OK(cudaMemcpyAsync(tmp, e->d_out_tokens, nseq * 4, cudaMemcpyDeviceToHost, e->stream));
+  B2_CUDA_OK(cudaStreamSynchronize(e->stream));
+  for (int i = 0; i < nseq; ++i) {
+    e->seqs[seq_ids[i]].next_token = tmp[i];
+    e->seqs[seq_ids[i]].next_valid = true;
+  }
   return 0;
 }
 }  // namespace
@@ -1013,6 +1049,12 @@ extern "C" int b2_decode_step(b2_engine* e, int32_t nseq, const int32_t* seq_ids
     B2_CUDA_OK(cudaMemcpyAsync(e->h_out, e->d_out_tokens, nseq * 4, cudaMemcpyDeviceToHost, e->stream));
     B2_CUDA_OK(cudaStreamSynchronize(e->stream));
     memcpy(out_tokens, e->h_out, nseq * 4);
+    for (int i = 0; i < nseq; ++i) {
+      e->seqs[seq_ids[i]].next_token = e->h_out[i];
+      e->seqs[seq_ids[i]].next_valid = true;
+    }
+  } else {
+    for (int i = 0; i < nseq; ++i) e->seqs[seq_ids[i]].next_valid = false;
   }
   return 0;
 }
@@ -1047,6 +1089,7 @@ extern "C" int b2_decode_run(b2_engine* e, int32_t nseq, const int32_t* seq_ids,
   for (int i = 0; i < nseq; ++i) e->seqs[seq_ids[i]].len += steps;
   e->last_n = nseq;
   e->last_tokens = nseq;
+  B2_TRY(fetch_next_tokens(e, nseq, seq_ids));
   if (out_tokens) {
     B2_CUDA_OK(cudaMemcpy(e->h_out, e->d_token_log, (size_t)steps * e->cfg.max_seqs * 4, cudaMemcpyDeviceToHost));
     for (int st = 0; st < steps; ++st)
@@ -1083,6 +1126,7 @@ extern "C" int b2_decode_profile(b2_engine* e, int32_t nseq, const int32_t* seq_
   }
   e->last_n = nseq;
   e->last_tokens = nseq;
+  B2_TRY(fetch_next_tokens(e, nseq, seq_ids));
   return 0;
 }
 

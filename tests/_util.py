@@ -52,6 +52,12 @@ def rel_err(got: torch.Tensor, ref: torch.Tensor) -> float:
     return ((g - r).abs().max() / r.abs().max().clamp_min(1e-30)).item()
 
 
+def rel_fro(got: torch.Tensor, ref: torch.Tensor) -> float:
+    """||got-ref||_F / ||ref||_F."""
+    g, r = got.float().cpu(), ref.float().cpu()
+    return ((g - r).norm() / r.norm().clamp_min(1e-30)).item()
+
+
 def ptr(t: torch.Tensor):
     return C.c_void_p(t.data_ptr())
 

@@ -10,7 +10,7 @@ import numpy as np
 import pytest
 import torch
 
-from _util import ROOT, engine_config_from_arch, pkg, rel_err
+from _util import ROOT, engine_config_from_arch, pkg, rel_err, rel_fro
 from oracle.qwen3_oracle import (QWEN3_0_6B, QWEN3_TINY, KVState, Restated, attention_explicit, hf_model, hf_state_dict,
                                  make_prompts, perturb_norm_weights, random_weights, rope_inv_freq, top2_gap)
 
@@ -234,15 +234,29 @@ def test_full_c1_greedy_and_logits(P, full):
     T = len(full_ids)
     with torch.no_grad():
         out = model(torch.tensor([full_ids]), output_hidden_states=True)
+        # HF's own second attention implementation on the same weights: the bf16 noise floor of the
+        # oracle itself (SURVEY.md 7.2-1 measured sdpa vs eager at 1.5e-2 on the last layers)
+        model.set_attn_implementation("eager")
+        out_e = model(torch.tensor([full_ids]), output_hidden_states=True)
+        model.set_attn_implementation("sdpa")
     worst = 0.0
     for layer in range(-1, arch.num_layers - 1):
         got = bits_to_bf16(e.get_hidden(layer, T))
         ref = out.hidden_states[layer + 1][0]
-        err = rel_err(got, ref)
+        err, fro = rel_err(got, ref), rel_fro(got, ref)
+        floor, floor_fro = rel_err(out_e.hidden_states[layer + 1][0], ref), rel_fro(out_e.hidden_states[layer + 1][0], ref)
+        print("layer %2d: engine vs HF max-rel %.4g fro-rel %.4g | HF eager vs HF sdpa max-rel %.4g fro-rel %.4g" % (
+            layer, err, fro, floor, floor_fro))
         worst = max(worst, err)
-        assert err < REL_TOL, "hidden after layer %d: rel err %.4g" % (layer, err)
+        # bar: 1e-2 relative, or -- where HF's own two attention paths already disagree by more than
+        # that -- no worse than 1.5x the oracle's own disagreement at this layer
+        assert err < max(REL_TOL, 1.5 * floor), "hidden after layer %d: rel err %.4g (oracle floor %.4g)" % (layer, err, floor)
+        assert fro < max(REL_TOL, 1.5 * floor_fro), "hidden after layer %d: fro err %.4g (oracle floor %.4g)" % (layer, fro, floor_fro)
     lg = torch.from_numpy(e.get_logits(1))[0]
-    assert rel_err(lg, out.logits[0, -1].float()) < REL_TOL
+    lerr = rel_err(lg, out.logits[0, -1].float())
+    lfloor = rel_err(out_e.logits[0, -1].float(), out.logits[0, -1].float())
+    print("last-position logits: engine vs HF max-rel %.4g | HF eager vs sdpa %.4g" % (lerr, lfloor))
+    assert lerr < max(REL_TOL, 1.5 * lfloor)
     e.seq_free(sid)
 
     # greedy decode from the prompt

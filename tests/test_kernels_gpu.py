@@ -21,6 +21,24 @@ def lib():
     return pkg().load_library()
 
 
+_KEEP = []
+
+
+def dv(t: torch.Tensor) -> torch.Tensor:
+    """Device copy that stays alive until the test ends (a temporary passed as a raw pointer would
+    be returned to the caching allocator before the kernel runs)."""
+    d = t.cuda()
+    _KEEP.append(d)
+    return d
+
+
+@pytest.fixture(autouse=True)
+def _release_device_copies():
+    yield
+    torch.cuda.synchronize()
+    _KEEP.clear()
+
+
 def chk(lib, rc):
     assert rc == 0, (rc, lib.b2_last_error())
     torch.cuda.synchronize()
@@ -81,12 +99,12 @@ def test_qknorm_rope_kv(lib, f32in):
         parts = torch.randn(2, T, (nq + 2 * nkv) * hd, generator=g)
         src = parts.cuda()
         qkv = (parts[0] + parts[1]).to(torch.bfloat16)
-        rc = lib.b2k_qknorm_rope_kv(ptr(src), 1, 2, ptr(qw.cuda()), ptr(kw.cuda()), ptr(table.cuda()), ptr(positions.cuda()),
-                                    ptr(slots.cuda()), ptr(q_out), ptr(kp), ptr(vp), T, nq, nkv, hd, bs, 1e-6, cuda_stream_ptr())
+        rc = lib.b2k_qknorm_rope_kv(ptr(src), 1, 2, ptr(dv(qw)), ptr(dv(kw)), ptr(dv(table)), ptr(dv(positions)),
+                                    ptr(dv(slots)), ptr(q_out), ptr(kp), ptr(vp), T, nq, nkv, hd, bs, 1e-6, cuda_stream_ptr())
     else:
         src = qkv.cuda()
-        rc = lib.b2k_qknorm_rope_kv(ptr(src), 0, 1, ptr(qw.cuda()), ptr(kw.cuda()), ptr(table.cuda()), ptr(positions.cuda()),
-                                    ptr(slots.cuda()), ptr(q_out), ptr(kp), ptr(vp), T, nq, nkv, hd, bs, 1e-6, cuda_stream_ptr())
+        rc = lib.b2k_qknorm_rope_kv(ptr(src), 0, 1, ptr(dv(qw)), ptr(dv(kw)), ptr(dv(table)), ptr(dv(positions)),
+                                    ptr(dv(slots)), ptr(q_out), ptr(kp), ptr(vp), T, nq, nkv, hd, bs, 1e-6, cuda_stream_ptr())
     chk(lib, rc)
     q = qkv[:, : nq * hd].view(1, T, nq, hd)
     k = qkv[:, nq * hd: (nq + nkv) * hd].view(1, T, nkv, hd)
@@ -141,7 +159,7 @@ def test_linear_bf16(lib, impl, T, N, K):
     x = bf(T, K, seed=8)
     w = bf(N, K, scale=0.05, seed=9)
     out = torch.full((T, N), float("nan"), dtype=torch.bfloat16, device="cuda")
-    chk(lib, lib.b2k_linear(ptr(x.cuda()), ptr(w.cuda()), ptr(out), 0, 1, T, N, K, impl, cuda_stream_ptr()))
+    chk(lib, lib.b2k_linear(ptr(dv(x)), ptr(dv(w)), ptr(out), 0, 1, T, N, K, impl, cuda_stream_ptr()))
     ref32 = x.float() @ w.float().t()
     assert_bf16_close(out, ref32.to(torch.bfloat16), 1, 0.02, "linear impl=%d %s" % (impl, (T, N, K)), abs_floor=1e-3)
     # and against the oracle's own op (HF nn.Linear on CPU)
@@ -155,7 +173,7 @@ def test_linear_splitk_partials(lib, T, N, K, ns):
     x = bf(T, K, seed=10)
     w = bf(N, K, scale=0.05, seed=11)
     out = torch.full((ns, T, N), float("nan"), dtype=torch.float32, device="cuda")
-    chk(lib, lib.b2k_linear(ptr(x.cuda()), ptr(w.cuda()), ptr(out), 1, ns, T, N, K, 1, cuda_stream_ptr()))
+    chk(lib, lib.b2k_linear(ptr(dv(x)), ptr(dv(w)), ptr(out), 1, ns, T, N, K, 1, cuda_stream_ptr()))
     assert torch.isfinite(out).all()
     total = out.sum(0).cpu()
     ref = x.float() @ w.float().t()
@@ -251,8 +269,8 @@ def test_attn_decode(lib, nsplit):
     out = torch.full((B, nq * hd), float("nan"), dtype=torch.bfloat16, device="cuda")
     nfl = lib.b2k_attn_decode_scratch_floats(B, nq, nkv, hd, nsplit)
     scratch = torch.full((max(nfl, 1),), float("nan"), dtype=torch.float32, device="cuda")
-    chk(lib, lib.b2k_attn_decode(ptr(q.cuda()), ptr(kp.cuda()), ptr(vp.cuda()), ptr(bt.cuda()), bt.shape[1],
-                                ptr(torch.tensor(seq_lens, dtype=torch.int32).cuda()), ptr(scratch), ptr(out), B, nq, nkv, hd, bs,
+    chk(lib, lib.b2k_attn_decode(ptr(dv(q)), ptr(dv(kp)), ptr(dv(vp)), ptr(dv(bt)), bt.shape[1],
+                                ptr(dv(torch.tensor(seq_lens, dtype=torch.int32))), ptr(scratch), ptr(out), B, nq, nkv, hd, bs,
                                 nsplit, cuda_stream_ptr()))
     for b in range(B):
         ref = attention_explicit(q[b].view(1, nq, 1, hd), ks[b][None], vs[b][None], hd ** -0.5, False).reshape(nq * hd)
@@ -272,8 +290,8 @@ def test_attn_decode_empty_and_padding_rows(lib):
     for nsplit in (1, 2):
         out = torch.full((3, nq * hd), float("nan"), dtype=torch.bfloat16, device="cuda")
         scratch = torch.zeros(max(1, lib.b2k_attn_decode_scratch_floats(3, nq, nkv, hd, nsplit)), device="cuda")
-        chk(lib, lib.b2k_attn_decode(ptr(q.cuda()), ptr(kp.cuda()), ptr(vp.cuda()), ptr(bt.cuda()), bt.shape[1],
-                                    ptr(torch.tensor(seq_lens, dtype=torch.int32).cuda()), ptr(scratch), ptr(out), 3, nq, nkv, hd, bs,
+        chk(lib, lib.b2k_attn_decode(ptr(dv(q)), ptr(dv(kp)), ptr(dv(vp)), ptr(dv(bt)), bt.shape[1],
+                                    ptr(dv(torch.tensor(seq_lens, dtype=torch.int32))), ptr(scratch), ptr(out), 3, nq, nkv, hd, bs,
                                     nsplit, cuda_stream_ptr()))
         o = out.cpu()
         assert not o[0].any() and not o[2].any()
@@ -298,7 +316,7 @@ def test_attn_prefill(lib, case):
     first = [sum(ntok[:i]) for i in range(len(ntok))]
     out = torch.full((T, nq * hd), float("nan"), dtype=torch.bfloat16, device="cuda")
     I32 = lambda v: (C.c_int32 * len(v))(*v)
-    chk(lib, lib.b2k_attn_prefill(ptr(q.cuda()), ptr(kp.cuda()), ptr(vp.cuda()), ptr(bt.cuda()), bt.shape[1], I32(first), I32(pos0),
+    chk(lib, lib.b2k_attn_prefill(ptr(dv(q)), ptr(dv(kp)), ptr(dv(vp)), ptr(dv(bt)), bt.shape[1], I32(first), I32(pos0),
                                  I32(ntok), I32(list(range(len(ntok)))), len(ntok), ptr(out), nq, nkv, hd, bs, cuda_stream_ptr()))
     o = out.cpu()
     for i, n in enumerate(ntok):
