@@ -8,7 +8,7 @@ import ctypes as C
 import pytest
 import torch
 
-from _util import assert_bf16_close, cuda_stream_ptr, pkg, ptr, rel_err
+from _util import assert_bf16_close, cuda_stream_ptr, pkg, ptr, rel_err, rel_fro
 from oracle.qwen3_oracle import (QWEN3_0_6B, apply_rope, attention_explicit, rms_norm, rope_cos_sin)
 
 pytestmark = pytest.mark.gpu
@@ -228,6 +228,38 @@ def test_lmhead_argmax_full_vocab(lib, impl, T):
 
 
 # ---------------------------------------------------------------------------------------------
+def attention_exact(q, k, v, scaling, causal):
+    """fp64 softmax attention over the bf16 inputs: the value both the oracle and the kernel approximate."""
+    B, Hq, T, d = q.shape
+    g = Hq // k.shape[1]
+    kf, vf = k.double().repeat_interleave(g, 1), v.double().repeat_interleave(g, 1)
+    s = q.double() @ kf.transpose(-1, -2) * scaling
+    if causal:
+        S = k.shape[2]
+        s = s.masked_fill(~torch.ones(T, S, dtype=torch.bool).tril(diagonal=S - T), float("-inf"))
+    return torch.softmax(s, -1) @ vf
+
+
+def check_attention(got, q4, k4, v4, causal, what):
+    """Bar for attention outputs.  P is rounded to bf16 before P.V (as in torch's CPU flash kernel), which
+    by itself perturbs the result by about one output ulp, so two correct implementations that round P
+    against different running maxima differ in many elements by one ulp.  Hence: (1) every element within
+    2 bf16 ulp of the oracle's written-out rounding points, (2) within 1e-2 relative of HF's sdpa, and
+    (3) no further from the exact fp64 result than 1.25x the oracle's own CPU kernel is."""
+    hd = q4.shape[-1]
+    ref = attention_explicit(q4, k4, v4, hd ** -0.5, causal)
+    assert_bf16_close(got, ref.reshape(got.shape) if ref.shape != got.shape else ref, 2, 0.6, what, abs_floor=2e-3)
+    sdpa = torch.nn.functional.scaled_dot_product_attention(q4, k4, v4, is_causal=causal and q4.shape[2] > 1, enable_gqa=True) \
+        if (q4.shape[2] == 1 or q4.shape[2] == k4.shape[2]) else None
+    exact = attention_exact(q4, k4, v4, hd ** -0.5, causal)
+    mine = rel_fro(got.reshape(exact.shape).double(), exact)
+    floor = rel_fro(ref.double(), exact)
+    if sdpa is not None:
+        assert rel_err(got.reshape(sdpa.shape), sdpa) < 1e-2, what
+        floor = max(floor, rel_fro(sdpa.double(), exact))
+    assert mine <= 1.25 * floor + 1e-4, "%s: error vs exact %.3g, oracle's own %.3g" % (what, mine, floor)
+
+
 def build_pages(seq_lens, nkv, hd, bs, seed):
     """Random K/V per sequence scattered into pages through a shuffled block table."""
     g = torch.Generator().manual_seed(seed)
@@ -272,12 +304,10 @@ def test_attn_decode(lib, nsplit):
     chk(lib, lib.b2k_attn_decode(ptr(dv(q)), ptr(dv(kp)), ptr(dv(vp)), ptr(dv(bt)), bt.shape[1],
                                 ptr(dv(torch.tensor(seq_lens, dtype=torch.int32))), ptr(scratch), ptr(out), B, nq, nkv, hd, bs,
                                 nsplit, cuda_stream_ptr()))
+    o = out.cpu()
     for b in range(B):
-        ref = attention_explicit(q[b].view(1, nq, 1, hd), ks[b][None], vs[b][None], hd ** -0.5, False).reshape(nq * hd)
-        assert_bf16_close(out[b], ref, 2, 0.25, "attn_decode b=%d S=%d nsplit=%d" % (b, seq_lens[b], nsplit), abs_floor=2e-3)
-        ref_sdpa = torch.nn.functional.scaled_dot_product_attention(q[b].view(1, nq, 1, hd), ks[b][None], vs[b][None],
-                                                                    enable_gqa=True).reshape(nq * hd)
-        assert rel_err(out[b], ref_sdpa) < 1e-2
+        check_attention(o[b].view(1, nq, 1, hd), q[b].view(1, nq, 1, hd), ks[b][None], vs[b][None], False,
+                        "attn_decode b=%d S=%d nsplit=%d" % (b, seq_lens[b], nsplit))
 
 
 def test_attn_decode_empty_and_padding_rows(lib):
@@ -295,8 +325,7 @@ def test_attn_decode_empty_and_padding_rows(lib):
                                     nsplit, cuda_stream_ptr()))
         o = out.cpu()
         assert not o[0].any() and not o[2].any()
-        ref = attention_explicit(q[1].view(1, nq, 1, hd), ks[1][None], vs[1][None], hd ** -0.5, False).reshape(nq * hd)
-        assert_bf16_close(o[1], ref, 2, 0.25, "attn_decode mid row", abs_floor=2e-3)
+        check_attention(o[1].view(1, nq, 1, hd), q[1].view(1, nq, 1, hd), ks[1][None], vs[1][None], False, "attn_decode mid row")
 
 
 @pytest.mark.parametrize("case", ["fresh", "chunked"])
@@ -321,6 +350,5 @@ def test_attn_prefill(lib, case):
     o = out.cpu()
     for i, n in enumerate(ntok):
         qs = q[first[i]: first[i] + n].view(n, nq, hd).transpose(0, 1)[None]  # [1][nq][n][hd]
-        ref = attention_explicit(qs, ks[i][None], vs[i][None], hd ** -0.5, True)  # tril(diagonal=S-T): causal with prefix
-        ref = ref[0].transpose(0, 1).reshape(n, nq * hd)
-        assert_bf16_close(o[first[i]: first[i] + n], ref, 2, 0.3, "attn_prefill seq %d (%s)" % (i, case), abs_floor=2e-3)
+        got = o[first[i]: first[i] + n].view(n, nq, hd).transpose(0, 1)[None]  # causal with prefix: tril(diagonal=S-T)
+        check_attention(got, qs, ks[i][None], vs[i][None], True, "attn_prefill seq %d (%s)" % (i, case))
