@@ -35,6 +35,8 @@ attn_decode_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k_pages,
   __shared__ float sm_m[AD_WARPS][2], sm_l[AD_WARPS][2];
   __shared__ float sm_o[AD_WARPS][2][AD_HD];
 
+  pdl_launch_dependents();
+  pdl_wait();
   const int split = blockIdx.x, kvh = blockIdx.y, b = blockIdx.z;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int S = seq_lens[b];
@@ -221,6 +223,8 @@ attn_decode_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k_pages,
 // Reduces the split partials of one (sequence, query head) in split order.
 __global__ void __launch_bounds__(AD_HD)
 attn_combine_kernel(const float* __restrict__ scratch, bf16* __restrict__ out, int B, int nq, int nkv, int nsplit) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int b = blockIdx.x / nq, qh = blockIdx.x % nq;
   const int kvh = qh / 2, h = qh % 2;
   const int d = threadIdx.x;
@@ -260,17 +264,15 @@ int launch_attn_decode(const bf16* q, const bf16* k_pages, const bf16* v_pages, 
   }
   dim3 grid(nsplit, nkv, B);
   const float scale = (float)(1.0 / sqrt((double)hd));  // HF passes head_dim**-0.5 as a double
-  attn_decode_kernel<<<grid, AD_WARPS * 32, AD_SMEM, s>>>(q, k_pages, v_pages, block_table, bt_stride, seq_lens, scratch,
-                                                          out, B, nq, nkv, nsplit, scale);
-  B2_CUDA_OK(cudaGetLastError());
+  B2_CUDA_OK(b2_launch(attn_decode_kernel, grid, dim3(AD_WARPS * 32), (size_t)AD_SMEM, s, q, k_pages, v_pages, block_table,
+                       bt_stride, seq_lens, scratch, out, B, nq, nkv, nsplit, scale));
   return 0;
 }
 
 int launch_attn_combine(const float* scratch, bf16* out, int B, int nq, int nkv, int hd, int nsplit, cudaStream_t s) {
   if (B <= 0 || nsplit <= 1) return 0;
   B2_REQUIRE(hd == AD_HD, "attn_combine: head_dim %d not built", hd);
-  attn_combine_kernel<<<B * nq, AD_HD, 0, s>>>(scratch, out, B, nq, nkv, nsplit);
-  B2_CUDA_OK(cudaGetLastError());
+  B2_CUDA_OK(b2_launch(attn_combine_kernel, dim3(B * nq), dim3(AD_HD), 0, s, scratch, out, B, nq, nkv, nsplit));
   return 0;
 }
 

@@ -48,6 +48,8 @@ attn_prefill_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k_pages
                     const int32_t* __restrict__ block_table, int bt_stride, const PrefillTile* __restrict__ tiles,
                     bf16* __restrict__ out, int nq, int nkv, int block_size, float scale_log2) {
   extern __shared__ __align__(128) uint8_t smem[];
+  pdl_launch_dependents();
+  pdl_wait();
   const PrefillTile tile = tiles[blockIdx.x];
   const int h = blockIdx.y, kvh = h / (nq / nkv);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -225,9 +227,8 @@ int launch_attn_prefill(const bf16* q, const bf16* k_pages, const bf16* v_pages,
   }
   const float scale_log2 = (float)((1.0 / sqrt((double)hd)) * 1.4426950408889634);
   dim3 grid(ntiles, nq);
-  attn_prefill_kernel<<<grid, 128, AP_SMEM, s>>>(q, k_pages, v_pages, block_table, bt_stride, tiles_dev, out, nq, nkv,
-                                                 block_size, scale_log2);
-  B2_CUDA_OK(cudaGetLastError());
+  B2_CUDA_OK(b2_launch(attn_prefill_kernel, grid, dim3(128), (size_t)AP_SMEM, s, q, k_pages, v_pages, block_table, bt_stride,
+                       tiles_dev, out, nq, nkv, block_size, scale_log2));
   return 0;
 }
 

@@ -10,8 +10,13 @@ namespace b2 {
 // a1: nn.Embedding lookup, HF:models/qwen3/modeling_qwen3.py:363,392
 // ---------------------------------------------------------------------------------------
 __global__ void embed_kernel(const int32_t* __restrict__ ids, const bf16* __restrict__ table, bf16* __restrict__ h,
-                             int H, int vocab) {
+                             int H, int vocab, unsigned long long* __restrict__ zero_buf, int nzero) {
+  pdl_launch_dependents();
+  pdl_wait();
   int t = blockIdx.x;
+  // first kernel of every forward: also clears the fused arg-max slots the lm_head will atomicMax into
+  if (t == 0 && zero_buf != nullptr)
+    for (int i = threadIdx.x; i < nzero; i += blockDim.x) zero_buf[i] = 0ull;
   int id = ids[t];
   if (id < 0 || id >= vocab) id = 0;
   const uint4* src = reinterpret_cast<const uint4*>(table + (size_t)id * H);
@@ -19,15 +24,17 @@ __global__ void embed_kernel(const int32_t* __restrict__ ids, const bf16* __rest
   for (int i = threadIdx.x; i < H / 8; i += blockDim.x) dst[i] = src[i];
 }
 
-int launch_embed(const int32_t* ids, const bf16* table, bf16* h, int T, int H, int vocab, cudaStream_t s) {
+int launch_embed(const int32_t* ids, const bf16* table, bf16* h, int T, int H, int vocab, unsigned long long* zero_buf, int nzero,
+                 cudaStream_t s) {
   if (T <= 0) return 0;
-  embed_kernel<<<T, 128, 0, s>>>(ids, table, h, H, vocab);
-  B2_CUDA_OK(cudaGetLastError());
+  B2_CUDA_OK(b2_launch(embed_kernel, dim3(T), dim3(128), 0, s, ids, table, h, H, vocab, zero_buf, nzero));
   return 0;
 }
 
 __global__ void gather_rows_kernel(const bf16* __restrict__ src, const int32_t* __restrict__ rows, bf16* __restrict__ dst,
                                    int H) {
+  pdl_launch_dependents();
+  pdl_wait();
   int r = rows[blockIdx.x];
   const uint4* s = reinterpret_cast<const uint4*>(src + (size_t)r * H);
   uint4* d = reinterpret_cast<uint4*>(dst + (size_t)blockIdx.x * H);
@@ -35,8 +42,7 @@ __global__ void gather_rows_kernel(const bf16* __restrict__ src, const int32_t* 
 }
 int launch_gather_rows(const bf16* src, const int32_t* rows, bf16* dst, int n, int H, cudaStream_t s) {
   if (n <= 0) return 0;
-  gather_rows_kernel<<<n, 128, 0, s>>>(src, rows, dst, H);
-  B2_CUDA_OK(cudaGetLastError());
+  B2_CUDA_OK(b2_launch(gather_rows_kernel, dim3(n), dim3(128), 0, s, src, rows, dst, H));
   return 0;
 }
 
@@ -51,8 +57,12 @@ template <int MODE>  // 0: no delta, 1: bf16 delta, 2: fp32 partials
 __global__ void add_rmsnorm_kernel(bf16* __restrict__ h, const void* __restrict__ delta, int nsplit, size_t split_stride,
                                    const bf16* __restrict__ w, bf16* __restrict__ x, int H, float eps) {
   __shared__ float red[32];
+  pdl_launch_dependents();
   const int t = blockIdx.x;
   const int i = threadIdx.x;  // vector index, 8 elements
+  float wv[8];
+  unpack8(reinterpret_cast<const uint4*>(w)[i], wv);  // norm gains are constant: read before the dependency wait
+  pdl_wait();
   float v[8];
   uint4 hv = reinterpret_cast<const uint4*>(h + (size_t)t * H)[i];
   unpack8(hv, v);
@@ -66,11 +76,23 @@ __global__ void add_rmsnorm_kernel(bf16* __restrict__ h, const void* __restrict_
 #pragma unroll
     for (int e = 0; e < 8; ++e) d[e] = 0.f;
     const float* p = reinterpret_cast<const float*>(delta) + (size_t)t * H + (size_t)i * 8;
-    for (int s = 0; s < nsplit; ++s) {
-      float4 a = reinterpret_cast<const float4*>(p + s * split_stride)[0];
-      float4 b = reinterpret_cast<const float4*>(p + s * split_stride)[1];
-      d[0] += a.x; d[1] += a.y; d[2] += a.z; d[3] += a.w;
-      d[4] += b.x; d[5] += b.y; d[6] += b.z; d[7] += b.w;
+    // all loads of a group of 4 splits are issued before any add (the adds stay in split order)
+    for (int s0 = 0; s0 < nsplit; s0 += 4) {
+      float4 a[4], b[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        if (s0 + j < nsplit) {
+          a[j] = reinterpret_cast<const float4*>(p + (size_t)(s0 + j) * split_stride)[0];
+          b[j] = reinterpret_cast<const float4*>(p + (size_t)(s0 + j) * split_stride)[1];
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        if (s0 + j < nsplit) {
+          d[0] += a[j].x; d[1] += a[j].y; d[2] += a[j].z; d[3] += a[j].w;
+          d[4] += b[j].x; d[5] += b[j].y; d[6] += b[j].z; d[7] += b[j].w;
+        }
+      }
     }
 #pragma unroll
     for (int e = 0; e < 8; ++e) v[e] = bf16_round(v[e] + bf16_round(d[e]));
@@ -88,8 +110,6 @@ __global__ void add_rmsnorm_kernel(bf16* __restrict__ h, const void* __restrict_
   for (int k = 0; k < nw; ++k) tot += red[k];
   const float var = tot / (float)H;
   const float rstd = __fdiv_rn(1.0f, __fsqrt_rn(var + eps));
-  float wv[8];
-  unpack8(reinterpret_cast<const uint4*>(w)[i], wv);
 #pragma unroll
   for (int e = 0; e < 8; ++e) v[e] = bf16_round(wv[e] * bf16_round(v[e] * rstd));
   reinterpret_cast<uint4*>(x + (size_t)t * H)[i] = pack8(v);
@@ -100,12 +120,12 @@ int launch_add_rmsnorm(bf16* h, ActIn delta, const bf16* w, bf16* x, int T, int 
   B2_REQUIRE(H % 256 == 0 && H <= 8192, "add_rmsnorm: hidden %d must be a multiple of 256 and <= 8192", H);
   const int threads = H / 8;
   if (delta.ptr == nullptr)
-    add_rmsnorm_kernel<0><<<T, threads, 0, s>>>(h, nullptr, 0, 0, w, x, H, eps);
+    B2_CUDA_OK(b2_launch(add_rmsnorm_kernel<0>, dim3(T), dim3(threads), 0, s, h, (const void*)nullptr, 0, (size_t)0, w, x, H, eps));
   else if (!delta.is_f32)
-    add_rmsnorm_kernel<1><<<T, threads, 0, s>>>(h, delta.ptr, 1, 0, w, x, H, eps);
+    B2_CUDA_OK(b2_launch(add_rmsnorm_kernel<1>, dim3(T), dim3(threads), 0, s, h, delta.ptr, 1, (size_t)0, w, x, H, eps));
   else
-    add_rmsnorm_kernel<2><<<T, threads, 0, s>>>(h, delta.ptr, delta.nsplit, (size_t)T * H, w, x, H, eps);
-  B2_CUDA_OK(cudaGetLastError());
+    B2_CUDA_OK(b2_launch(add_rmsnorm_kernel<2>, dim3(T), dim3(threads), 0, s, h, delta.ptr, delta.nsplit, (size_t)T * H, w, x, H,
+                         eps));
   return 0;
 }
 
@@ -125,6 +145,8 @@ __global__ void qknorm_rope_kv_kernel(const void* __restrict__ qkv, int nsplit, 
                                       bf16* __restrict__ k_pages, bf16* __restrict__ v_pages, int T, int nq, int nkv,
                                       int block_size, float eps) {
   constexpr int HD = 128;
+  pdl_launch_dependents();
+  pdl_wait();
   const int nheads = nq + 2 * nkv;
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
@@ -195,13 +217,12 @@ int launch_qknorm_rope_kv(ActIn qkv, const bf16* qw, const bf16* kw, const bf16*
   const long long warps = (long long)T * nheads;
   const int blocks = (int)((warps + 3) / 4);
   if (qkv.is_f32)
-    qknorm_rope_kv_kernel<true><<<blocks, 128, 0, s>>>(qkv.ptr, qkv.nsplit, (size_t)T * nheads * hd, qw, kw, cos_sin,
-                                                       positions, slots, q_out, k_pages, v_pages, T, nq, nkv,
-                                                       block_size, eps);
+    B2_CUDA_OK(b2_launch(qknorm_rope_kv_kernel<true>, dim3(blocks), dim3(128), 0, s, qkv.ptr, qkv.nsplit,
+                         (size_t)T * nheads * hd, qw, kw, cos_sin, positions, slots, q_out, k_pages, v_pages, T, nq, nkv,
+                         block_size, eps));
   else
-    qknorm_rope_kv_kernel<false><<<blocks, 128, 0, s>>>(qkv.ptr, 1, 0, qw, kw, cos_sin, positions, slots, q_out,
-                                                        k_pages, v_pages, T, nq, nkv, block_size, eps);
-  B2_CUDA_OK(cudaGetLastError());
+    B2_CUDA_OK(b2_launch(qknorm_rope_kv_kernel<false>, dim3(blocks), dim3(128), 0, s, qkv.ptr, 1, (size_t)0, qw, kw, cos_sin,
+                         positions, slots, q_out, k_pages, v_pages, T, nq, nkv, block_size, eps));
   return 0;
 }
 
@@ -212,6 +233,8 @@ int launch_qknorm_rope_kv(ActIn qkv, const bf16* qw, const bf16* kw, const bf16*
 template <bool F32IN>
 __global__ void silu_mul_kernel(const void* __restrict__ gu, int nsplit, size_t split_stride, bf16* __restrict__ act,
                                 int T, int I) {
+  pdl_launch_dependents();
+  pdl_wait();
   const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;  // vector of 8 over [T][I]
   const size_t nvec = (size_t)T * I / 8;
   if (idx >= nvec) return;
@@ -256,10 +279,9 @@ int launch_silu_mul(ActIn gu, bf16* act, int T, int I, cudaStream_t s) {
   const size_t nvec = (size_t)T * I / 8;
   const int blocks = (int)((nvec + 255) / 256);
   if (gu.is_f32)
-    silu_mul_kernel<true><<<blocks, 256, 0, s>>>(gu.ptr, gu.nsplit, (size_t)T * 2 * I, act, T, I);
+    B2_CUDA_OK(b2_launch(silu_mul_kernel<true>, dim3(blocks), dim3(256), 0, s, gu.ptr, gu.nsplit, (size_t)T * 2 * I, act, T, I));
   else
-    silu_mul_kernel<false><<<blocks, 256, 0, s>>>(gu.ptr, 1, 0, act, T, I);
-  B2_CUDA_OK(cudaGetLastError());
+    B2_CUDA_OK(b2_launch(silu_mul_kernel<false>, dim3(blocks), dim3(256), 0, s, gu.ptr, 1, (size_t)0, act, T, I));
   return 0;
 }
 
@@ -274,6 +296,8 @@ __device__ __forceinline__ unsigned long long argmax_pack(float v, int idx) {
 
 __global__ void argmax_rows_kernel(const bf16* __restrict__ logits, int32_t* __restrict__ out, int V) {
   __shared__ unsigned long long red[32];
+  pdl_launch_dependents();
+  pdl_wait();
   const bf16* row = logits + (size_t)blockIdx.x * V;
   unsigned long long best = 0;
   for (int i = threadIdx.x; i < V; i += blockDim.x) {
@@ -297,19 +321,19 @@ __global__ void argmax_rows_kernel(const bf16* __restrict__ logits, int32_t* __r
 }
 int launch_argmax_rows(const bf16* logits, int32_t* out, int T, int V, cudaStream_t s) {
   if (T <= 0) return 0;
-  argmax_rows_kernel<<<T, 1024, 0, s>>>(logits, out, V);
-  B2_CUDA_OK(cudaGetLastError());
+  B2_CUDA_OK(b2_launch(argmax_rows_kernel, dim3(T), dim3(1024), 0, s, logits, out, V));
   return 0;
 }
 
 __global__ void argmax_finalize_kernel(const unsigned long long* __restrict__ packed, int32_t* __restrict__ out, int T) {
+  pdl_launch_dependents();
+  pdl_wait();
   int t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t < T) out[t] = (int32_t)(0xffffffffu - (uint32_t)(packed[t] & 0xffffffffull));
 }
 int launch_argmax_finalize(const unsigned long long* packed, int32_t* out, int T, cudaStream_t s) {
   if (T <= 0) return 0;
-  argmax_finalize_kernel<<<(T + 127) / 128, 128, 0, s>>>(packed, out, T);
-  B2_CUDA_OK(cudaGetLastError());
+  B2_CUDA_OK(b2_launch(argmax_finalize_kernel, dim3((T + 127) / 128), dim3(128), 0, s, packed, out, T));
   return 0;
 }
 
@@ -318,6 +342,8 @@ int launch_argmax_finalize(const unsigned long long* packed, int32_t* out, int T
 // ---------------------------------------------------------------------------------------
 __global__ void decode_advance_kernel(int32_t* positions, int32_t* seq_lens, int32_t* slots,
                                       const int32_t* __restrict__ block_table, int bt_stride, int block_size, int B) {
+  pdl_launch_dependents();
+  pdl_wait();
   int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= B) return;
   if (positions[b] < -1) {  // padding row of a graph bucket
@@ -334,8 +360,8 @@ __global__ void decode_advance_kernel(int32_t* positions, int32_t* seq_lens, int
 int launch_decode_advance(int32_t* positions, int32_t* seq_lens, int32_t* slots, const int32_t* block_table,
                           int bt_stride, int block_size, int B, cudaStream_t s) {
   if (B <= 0) return 0;
-  decode_advance_kernel<<<(B + 127) / 128, 128, 0, s>>>(positions, seq_lens, slots, block_table, bt_stride, block_size, B);
-  B2_CUDA_OK(cudaGetLastError());
+  B2_CUDA_OK(b2_launch(decode_advance_kernel, dim3((B + 127) / 128), dim3(128), 0, s, positions, seq_lens, slots, block_table,
+                       bt_stride, block_size, B));
   return 0;
 }
 

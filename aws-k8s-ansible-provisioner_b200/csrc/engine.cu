@@ -28,6 +28,14 @@ void b2_set_error(const char* fmt, ...) {
   va_end(ap);
 }
 extern "C" const char* b2_last_error(void) { return g_err; }
+bool b2_pdl_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("B2_PDL");
+    v = (e && *e == '0') ? 0 : 1;
+  }
+  return v != 0;
+}
 extern "C" int b2_abi_version(void) { return B2_ABI_VERSION; }
 
 using namespace b2;
@@ -256,7 +264,7 @@ int forward(b2_engine* e, int T, int ntiles, int nlast, int attn_split) {
   int rc = 0;
   {
     KL k(e, B2K_EMBED);
-    B2_TRY(launch_embed(e->d_tokens, e->embed, e->h, T, H, c.vocab, e->stream));
+    B2_TRY(launch_embed(e->d_tokens, e->embed, e->h, T, H, c.vocab, e->d_argmax, nlast, e->stream));
   }
   dbg_capture(e, 0, e->h, T);
   ActIn delta = act_bf16(nullptr);
@@ -338,7 +346,6 @@ int forward(b2_engine* e, int T, int ntiles, int nlast, int attn_split) {
     KL k2(e, B2K_MISC);
     B2_TRY(launch_argmax_rows(e->logits, e->d_out_tokens, nlast, c.vocab, e->stream));
   } else {
-    B2_CUDA_OK(cudaMemsetAsync(e->d_argmax, 0, sizeof(unsigned long long) * nlast, e->stream));
     TcGemmArgs a;
     a.tmap_w = e->tm_lm_head;
     a.bn = tc_pick_bn(nlast);
@@ -360,6 +367,8 @@ int forward(b2_engine* e, int T, int ntiles, int nlast, int attn_split) {
 
 __global__ void publish_tokens_kernel(const int32_t* __restrict__ out_tokens, int32_t* __restrict__ next_in,
                                       int32_t* __restrict__ log, int32_t* step, int B, int log_cap_steps, int stride) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int st = *step;  // single CTA
   for (int b = threadIdx.x; b < B; b += blockDim.x) {
     next_in[b] = out_tokens[b];
@@ -379,9 +388,8 @@ int decode_body(b2_engine* e, int B, int attn_split) {
   B2_TRY(forward(e, B, 0, B, attn_split));
   {
     KL k(e, B2K_MISC);
-    publish_tokens_kernel<<<1, 256, 0, e->stream>>>(e->d_out_tokens, e->d_tokens, e->d_token_log, e->d_step, B,
-                                                                 e->log_cap_steps, e->cfg.max_seqs);
-    B2_CUDA_OK(cudaGetLastError());
+    B2_CUDA_OK(b2_launch(publish_tokens_kernel, dim3(1), dim3(256), 0, e->stream, (const int32_t*)e->d_out_tokens, e->d_tokens,
+                         e->d_token_log, e->d_step, B, e->log_cap_steps, e->cfg.max_seqs));
   }
   return 0;
 }

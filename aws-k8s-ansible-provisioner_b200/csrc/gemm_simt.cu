@@ -11,6 +11,8 @@ namespace b2 {
 template <int TB, bool OUT_F32>
 __global__ void __launch_bounds__(128) linear_simt_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w,
                                                           void* __restrict__ out, int T, int N, int K) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n = blockIdx.x * 4 + warp;
   if (n >= N) return;
@@ -55,9 +57,9 @@ int launch_linear_simt(const bf16* x, const bf16* w, void* out, int out_is_f32, 
 #define B2_LAUNCH(TB)                                                                       \
   do {                                                                                      \
     if (out_is_f32)                                                                         \
-      linear_simt_kernel<TB, true><<<blocks, 128, 0, s>>>(x, w, out, T, N, K);              \
+      B2_CUDA_OK(b2_launch(linear_simt_kernel<TB, true>, dim3(blocks), dim3(128), 0, s, x, w, out, T, N, K));  \
     else                                                                                    \
-      linear_simt_kernel<TB, false><<<blocks, 128, 0, s>>>(x, w, out, T, N, K);             \
+      B2_CUDA_OK(b2_launch(linear_simt_kernel<TB, false>, dim3(blocks), dim3(128), 0, s, x, w, out, T, N, K)); \
   } while (0)
   if (T == 1)
     B2_LAUNCH(1);
@@ -68,7 +70,6 @@ int launch_linear_simt(const bf16* x, const bf16* w, void* out, int out_is_f32, 
   else
     B2_LAUNCH(8);
 #undef B2_LAUNCH
-  B2_CUDA_OK(cudaGetLastError());
   return 0;
 }
 

@@ -30,7 +30,7 @@ struct TcCfg {
   static constexpr int STAGE_BYTES = TC_W_BYTES + X_BYTES;
   static constexpr int STAGES = (BN <= 64) ? 8 : (BN == 128 ? 6 : 4);
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024;
-  static constexpr int TMEM_COLS = BN < 32 ? 32 : BN;
+  static constexpr int TMEM_COLS = 2 * BN < 32 ? 32 : 2 * BN;  // two accumulator stages
 };
 
 __device__ __forceinline__ unsigned long long tc_argmax_pack(float v, int idx) {
@@ -39,33 +39,38 @@ __device__ __forceinline__ unsigned long long tc_argmax_pack(float v, int idx) {
   return ((unsigned long long)key << 32) | (unsigned long long)(0xffffffffu - (uint32_t)idx);
 }
 
+// Persistent: gridDim.x CTAs walk the (m tile, token tile, k split) work list with stride
+// gridDim.x.  The smem stage ring runs on across tiles, and the accumulator is double buffered
+// in TMEM so the epilogue of tile i overlaps the TMA/MMA main loop of tile i+1.
 template <int BN, int EPI>
 __global__ void __launch_bounds__(192, 1)
 linear_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_x,
                  void* __restrict__ out, unsigned long long* __restrict__ argmax_packed, int T, int N, int K,
-                 int kb_per_split) {
+                 int kb_per_split, int m_tiles, int n_tiles, int nsplit) {
   using C = TcCfg<BN>;
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t full_bar[C::STAGES];
   __shared__ __align__(8) uint64_t empty_bar[C::STAGES];
-  __shared__ __align__(8) uint64_t tmem_full_bar;
+  __shared__ __align__(8) uint64_t tmem_full_bar[2];
+  __shared__ __align__(8) uint64_t tmem_empty_bar[2];
   __shared__ uint32_t tmem_slot;
   __shared__ unsigned long long amax_red[EPI == TC_EPI_ARGMAX ? 4 * BN : 1];
 
+  pdl_launch_dependents();
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int m_tile = blockIdx.x, n_tile = blockIdx.y, split = blockIdx.z;
   const int kb_total = K / TC_BK;
-  const int kb0 = split * kb_per_split;
-  const int kb1 = min(kb_total, kb0 + kb_per_split);
-  const int nkb = kb1 - kb0;
+  const int total_tiles = m_tiles * n_tiles * nsplit;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < C::STAGES; ++s) {
       mbar_init(smem_u32(&full_bar[s]), 1);
       mbar_init(smem_u32(&empty_bar[s]), 1);
     }
-    mbar_init(smem_u32(&tmem_full_bar), 1);
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(smem_u32(&tmem_full_bar[a]), 1);
+      mbar_init(smem_u32(&tmem_empty_bar[a]), 128);
+    }
     mbar_fence_init();
   }
   if (warp == 1) {
@@ -81,81 +86,137 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
     if (lane == 0) {
       tma_prefetch_desc(&tmap_w);
       tma_prefetch_desc(&tmap_x);
-      for (int i = 0; i < nkb; ++i) {
-        const int s = i % C::STAGES;
-        const uint32_t ph = (i / C::STAGES) & 1;
-        mbar_wait(smem_u32(&empty_bar[s]), ph ^ 1);
-        const uint32_t fb = smem_u32(&full_bar[s]);
-        mbar_arrive_expect_tx(fb, C::STAGE_BYTES);
-        const uint32_t ws = smem_base + s * C::STAGE_BYTES;
-        tma_load_2d(ws, &tmap_w, (kb0 + i) * TC_BK, m_tile * TC_BM, fb);
-        tma_load_2d(ws + TC_W_BYTES, &tmap_x, (kb0 + i) * TC_BK, n_tile * BN, fb);
+      int it = 0;
+      bool waited = false;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const int m_tile = tile % m_tiles;
+        const int n_tile = (tile / m_tiles) % n_tiles;
+        const int split = tile / (m_tiles * n_tiles);
+        const int kb0 = split * kb_per_split;
+        const int kb1 = min(kb_total, kb0 + kb_per_split);
+        if (!waited) {
+          // The weight stream does not depend on the previous kernel: start it for the first
+          // stages of the first tile, THEN wait for the producer of X (programmatic dependent launch).
+          const int npre = min(kb1 - kb0, C::STAGES);
+          for (int i = 0; i < npre; ++i) {
+            const uint32_t fb = smem_u32(&full_bar[i]);
+            mbar_arrive_expect_tx(fb, C::STAGE_BYTES);
+            tma_load_2d(smem_base + i * C::STAGE_BYTES, &tmap_w, (kb0 + i) * TC_BK, m_tile * TC_BM, fb);
+          }
+          pdl_wait();
+          waited = true;
+          for (int i = 0; i < npre; ++i)
+            tma_load_2d(smem_base + i * C::STAGE_BYTES + TC_W_BYTES, &tmap_x, (kb0 + i) * TC_BK, n_tile * BN,
+                        smem_u32(&full_bar[i]));
+          it = npre;
+          for (int kb = kb0 + npre; kb < kb1; ++kb, ++it) {
+            const int s = it % C::STAGES;
+            mbar_wait(smem_u32(&empty_bar[s]), ((it / C::STAGES) & 1) ^ 1);
+            const uint32_t fb = smem_u32(&full_bar[s]);
+            mbar_arrive_expect_tx(fb, C::STAGE_BYTES);
+            const uint32_t ws = smem_base + s * C::STAGE_BYTES;
+            tma_load_2d(ws, &tmap_w, kb * TC_BK, m_tile * TC_BM, fb);
+            tma_load_2d(ws + TC_W_BYTES, &tmap_x, kb * TC_BK, n_tile * BN, fb);
+          }
+          continue;
+        }
+        for (int kb = kb0; kb < kb1; ++kb, ++it) {
+          const int s = it % C::STAGES;
+          mbar_wait(smem_u32(&empty_bar[s]), ((it / C::STAGES) & 1) ^ 1);
+          const uint32_t fb = smem_u32(&full_bar[s]);
+          mbar_arrive_expect_tx(fb, C::STAGE_BYTES);
+          const uint32_t ws = smem_base + s * C::STAGE_BYTES;
+          tma_load_2d(ws, &tmap_w, kb * TC_BK, m_tile * TC_BM, fb);
+          tma_load_2d(ws + TC_W_BYTES, &tmap_x, kb * TC_BK, n_tile * BN, fb);
+        }
       }
+      if (!waited) pdl_wait();
     }
   } else if (warp == 1) {
     if (lane == 0) {
       constexpr uint32_t idesc = umma_idesc_bf16(TC_BM, BN);
-      for (int i = 0; i < nkb; ++i) {
-        const int s = i % C::STAGES;
-        const uint32_t ph = (i / C::STAGES) & 1;
-        mbar_wait(smem_u32(&full_bar[s]), ph);
+      int it = 0, lt = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
+        const int split = tile / (m_tiles * n_tiles);
+        const int kb0 = split * kb_per_split;
+        const int kb1 = min(kb_total, kb0 + kb_per_split);
+        const int as = lt & 1;
+        mbar_wait(smem_u32(&tmem_empty_bar[as]), ((lt >> 1) & 1) ^ 1);  // epilogue drained this accumulator
         tc_fence_after();
-        const uint32_t ws = smem_base + s * C::STAGE_BYTES;
-        const uint64_t da = umma_desc_sw128(ws);
-        const uint64_t db = umma_desc_sw128(ws + TC_W_BYTES);
+        const uint32_t tmem_d = tmem_base + (uint32_t)(as * BN);
+        for (int kb = kb0; kb < kb1; ++kb, ++it) {
+          const int s = it % C::STAGES;
+          mbar_wait(smem_u32(&full_bar[s]), (it / C::STAGES) & 1);
+          tc_fence_after();
+          const uint32_t ws = smem_base + s * C::STAGE_BYTES;
+          const uint64_t da = umma_desc_sw128(ws);
+          const uint64_t db = umma_desc_sw128(ws + TC_W_BYTES);
 #pragma unroll
-        for (int k = 0; k < TC_BK / 16; ++k) {
-          // advance 16 bf16 = 32 bytes along K inside the 128-byte swizzle row: +2 in the
-          // (address >> 4) field of both descriptors
-          tc_mma_bf16(tmem_base, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (i > 0 || k > 0) ? 1u : 0u);
+          for (int k = 0; k < TC_BK / 16; ++k) {
+            // advance 16 bf16 = 32 bytes along K inside the 128-byte swizzle row: +2 in the
+            // (address >> 4) field of both descriptors
+            tc_mma_bf16(tmem_d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+          }
+          tc_commit(smem_u32(&empty_bar[s]));  // frees the smem stage once these MMAs retire
         }
-        tc_commit(smem_u32(&empty_bar[s]));  // frees the smem stage once these MMAs retire
+        tc_commit(smem_u32(&tmem_full_bar[as]));  // accumulator complete
       }
-      tc_commit(smem_u32(&tmem_full_bar));   // accumulator complete
     }
   } else {
     const int q = warp & 3;  // TMEM lane quarter this warp may access
-    mbar_wait(smem_u32(&tmem_full_bar), 0);
-    tc_fence_after();
-    const int row = m_tile * TC_BM + q * 32 + lane;  // output feature
-    const bool row_ok = row < N;
+    pdl_wait();              // (returns at once: the accumulator cannot be ready before X arrived)
+    int lt = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
+      const int m_tile = tile % m_tiles;
+      const int n_tile = (tile / m_tiles) % n_tiles;
+      const int split = tile / (m_tiles * n_tiles);
+      const int as = lt & 1;
+      mbar_wait(smem_u32(&tmem_full_bar[as]), (lt >> 1) & 1);
+      tc_fence_after();
+      const int row = m_tile * TC_BM + q * 32 + lane;  // output feature
+      const bool row_ok = row < N;
 #pragma unroll 1
-    for (int c0 = 0; c0 < BN; c0 += 16) {
-      uint32_t r[16];
-      tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, r);
-      tmem_ld_wait();
+      for (int c0 = 0; c0 < BN; c0 += 16) {
+        uint32_t r[16];
+        tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN + c0), r);
+        tmem_ld_wait();
 #pragma unroll
-      for (int j = 0; j < 16; ++j) {
-        const int tok = n_tile * BN + c0 + j;
-        const float acc = __uint_as_float(r[j]);
-        if (EPI == TC_EPI_BF16) {
-          if (tok < T && row_ok) reinterpret_cast<bf16*>(out)[(size_t)tok * N + row] = __float2bfloat16_rn(acc);
-        } else if (EPI == TC_EPI_F32_PARTIAL) {
-          if (tok < T && row_ok) reinterpret_cast<float*>(out)[((size_t)split * T + tok) * N + row] = acc;
-        } else {
-          const bf16 lb = __float2bfloat16_rn(acc);
-          const float lv = __bfloat162float(lb);
-          if (out != nullptr && tok < T && row_ok) reinterpret_cast<bf16*>(out)[(size_t)tok * N + row] = lb;
-          unsigned long long p = (row_ok && lv == lv) ? tc_argmax_pack(lv, row) : 0ull;
+        for (int j = 0; j < 16; ++j) {
+          const int tok = n_tile * BN + c0 + j;
+          const float acc = __uint_as_float(r[j]);
+          if (EPI == TC_EPI_BF16) {
+            if (tok < T && row_ok) reinterpret_cast<bf16*>(out)[(size_t)tok * N + row] = __float2bfloat16_rn(acc);
+          } else if (EPI == TC_EPI_F32_PARTIAL) {
+            if (tok < T && row_ok) reinterpret_cast<float*>(out)[((size_t)split * T + tok) * N + row] = acc;
+          } else {
+            const bf16 lb = __float2bfloat16_rn(acc);
+            const float lv = __bfloat162float(lb);
+            if (out != nullptr && tok < T && row_ok) reinterpret_cast<bf16*>(out)[(size_t)tok * N + row] = lb;
+            unsigned long long p = (row_ok && lv == lv) ? tc_argmax_pack(lv, row) : 0ull;
 #pragma unroll
-          for (int o = 16; o > 0; o >>= 1) {
-            unsigned long long other = __shfl_xor_sync(0xffffffffu, p, o);
-            p = other > p ? other : p;
+            for (int o = 16; o > 0; o >>= 1) {
+              unsigned long long other = __shfl_xor_sync(0xffffffffu, p, o);
+              p = other > p ? other : p;
+            }
+            if (lane == 0) amax_red[q * BN + c0 + j] = p;
           }
-          if (lane == 0) amax_red[q * BN + c0 + j] = p;
         }
       }
-    }
-    if (EPI == TC_EPI_ARGMAX) {
-      asm volatile("bar.sync 1, 128;" ::: "memory");  // the four epilogue warps only
-      for (int e = threadIdx.x - 64; e < BN; e += 128) {
-        const int tok = n_tile * BN + e;
-        if (tok < T) {
-          unsigned long long p = amax_red[e];
+      // this thread's TMEM reads of the accumulator stage are complete: hand it back to the MMA warp
+      tc_fence_before();
+      mbar_arrive(smem_u32(&tmem_empty_bar[as]));
+      if (EPI == TC_EPI_ARGMAX) {
+        asm volatile("bar.sync 1, 128;" ::: "memory");  // the four epilogue warps only
+        for (int e = threadIdx.x - 64; e < BN; e += 128) {
+          const int tok = n_tile * BN + e;
+          if (tok < T) {
+            unsigned long long p = amax_red[e];
 #pragma unroll
-          for (int k = 1; k < 4; ++k) p = amax_red[k * BN + e] > p ? amax_red[k * BN + e] : p;
-          atomicMax(argmax_packed + tok, p);
+            for (int k = 1; k < 4; ++k) p = amax_red[k * BN + e] > p ? amax_red[k * BN + e] : p;
+            atomicMax(argmax_packed + tok, p);
+          }
         }
+        asm volatile("bar.sync 1, 128;" ::: "memory");  // amax_red is rewritten by the next tile
       }
     }
   }
@@ -235,10 +296,12 @@ static int launch_one(const TcGemmArgs& a, int kb_per_split, cudaStream_t s) {
     B2_CUDA_OK(cudaFuncSetAttribute(linear_tc_kernel<BN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
     attr_done = true;
   }
-  dim3 grid((a.N + TC_BM - 1) / TC_BM, (a.T + BN - 1) / BN, a.nsplit);
-  linear_tc_kernel<BN, EPI><<<grid, 192, C::SMEM_BYTES, s>>>(a.tmap_w, a.tmap_x, a.out, a.argmax_packed, a.T, a.N, a.K,
-                                                              kb_per_split);
-  B2_CUDA_OK(cudaGetLastError());
+  const int m_tiles = (a.N + TC_BM - 1) / TC_BM, n_tiles = (a.T + BN - 1) / BN;
+  const int total = m_tiles * n_tiles * a.nsplit;
+  static int sms = device_num_sms();
+  const int grid = total < sms ? total : sms;
+  B2_CUDA_OK(b2_launch(linear_tc_kernel<BN, EPI>, dim3(grid), dim3(192), (size_t)C::SMEM_BYTES, s, a.tmap_w, a.tmap_x, a.out,
+                       a.argmax_packed, a.T, a.N, a.K, kb_per_split, m_tiles, n_tiles, a.nsplit));
   return 0;
 }
 

@@ -15,7 +15,8 @@ inline ActIn act_bf16(const void* p) { return ActIn{p, 0, 1}; }
 inline ActIn act_f32(const void* p, int nsplit) { return ActIn{p, 1, nsplit}; }
 
 // ---- elementwise.cu ----
-int launch_embed(const int32_t* ids, const bf16* table, bf16* h, int T, int H, int vocab, cudaStream_t s);
+int launch_embed(const int32_t* ids, const bf16* table, bf16* h, int T, int H, int vocab, unsigned long long* zero_buf, int nzero,
+                 cudaStream_t s);
 int launch_add_rmsnorm(bf16* h, ActIn delta, const bf16* w, bf16* x, int T, int H, float eps, cudaStream_t s);
 int launch_qknorm_rope_kv(ActIn qkv, const bf16* qw, const bf16* kw, const bf16* cos_sin, const int32_t* positions,
                           const int32_t* slots, bf16* q_out, bf16* k_pages, bf16* v_pages, int T, int nq, int nkv,
