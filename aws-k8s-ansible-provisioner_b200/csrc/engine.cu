@@ -145,6 +145,7 @@ struct b2_engine {
   int simt_max_tokens = 0;  // T <= this -> SIMT GEMV path
   int attn_split_override = 0;
   int force_gemm_impl = -1;
+  unsigned skip_mask = 0;  // B2_SKIP_MASK: kernel classes left out (timing ablations only; results are garbage)
 };
 
 namespace {
@@ -176,7 +177,9 @@ struct KL {
   b2_engine* e;
   int cls;
   int ev = -1;
+  bool skip() const { return (e->skip_mask >> cls) & 1u; }
   KL(b2_engine* e_, int cls_) : e(e_), cls(cls_) {
+    if (skip()) return;
     e->launches++;
     if (e->profiling && e->ev_next + 2 <= (int)e->ev_pool.size()) {
       ev = e->ev_next;
@@ -203,7 +206,10 @@ int pick_attn_split(b2_engine* e, int B, int max_len) {
   if (e->attn_split_override > 0) return e->attn_split_override;
   const int units = B * e->cfg.num_kv_heads;
   const int blocks = (max_len + e->cfg.block_size - 1) / e->cfg.block_size;
-  int want = (4 * e->num_sms + units - 1) / units;  // >= 4 CTAs per SM in flight
+  // Measured on B200 (batch 64, context ~580, attention alone): 1 split 0.92 ms/step, 2 splits 0.99,
+  // 4 splits 1.10, 8 splits 1.46 -- per-CTA start-up and the merge dominate short chunks, so split
+  // only as far as needed to give every SM two CTAs.
+  int want = (2 * e->num_sms + units - 1) / units;
   int cap = std::max(1, blocks / 8);                // keep >= 8 pages (2 per warp) per CTA
   int ns = std::max(1, std::min(want, cap));
   // quantise so only a handful of graphs exist
@@ -219,7 +225,7 @@ ActIn linear(b2_engine* e, int cls, XBuf xb, const bf16* xptr, const bf16* w, co
   int impl = e->force_gemm_impl >= 0 ? e->force_gemm_impl : (T <= e->simt_max_tokens ? 0 : 1);
   if (impl == 0) {
     KL k(e, cls);
-    *rc = launch_linear_simt(xptr, w, out_bf16, 0, T, N, K, e->stream);
+    if (!k.skip()) *rc = launch_linear_simt(xptr, w, out_bf16, 0, T, N, K, e->stream);
     return act_bf16(out_bf16);
   }
   TcGemmArgs a;
@@ -239,12 +245,12 @@ ActIn linear(b2_engine* e, int cls, XBuf xb, const bf16* xptr, const bf16* w, co
   if (ns == 1) {
     a.epilogue = TC_EPI_BF16;
     a.out = out_bf16;
-    *rc = launch_linear_tc(a, e->stream);
+    if (!k.skip()) *rc = launch_linear_tc(a, e->stream);
     return act_bf16(out_bf16);
   }
   a.epilogue = TC_EPI_F32_PARTIAL;
   a.out = e->partial;
-  *rc = launch_linear_tc(a, e->stream);
+  if (!k.skip()) *rc = launch_linear_tc(a, e->stream);
   return act_f32(e->partial, ns);
 }
 
@@ -264,7 +270,7 @@ int forward(b2_engine* e, int T, int ntiles, int nlast, int attn_split) {
   int rc = 0;
   {
     KL k(e, B2K_EMBED);
-    B2_TRY(launch_embed(e->d_tokens, e->embed, e->h, T, H, c.vocab, e->d_argmax, nlast, e->stream));
+    if (!k.skip()) B2_TRY(launch_embed(e->d_tokens, e->embed, e->h, T, H, c.vocab, e->d_argmax, nlast, e->stream));
   }
   dbg_capture(e, 0, e->h, T);
   ActIn delta = act_bf16(nullptr);
@@ -274,30 +280,30 @@ int forward(b2_engine* e, int T, int ntiles, int nlast, int attn_split) {
     bf16* vp = kp + e->layer_kv_elems;
     {
       KL k(e, B2K_NORM);
-      B2_TRY(launch_add_rmsnorm(e->h, delta, L.ln1, e->x, T, H, c.rms_eps, e->stream));
+      if (!k.skip()) B2_TRY(launch_add_rmsnorm(e->h, delta, L.ln1, e->x, T, H, c.rms_eps, e->stream));
     }
     if (l > 0) dbg_capture(e, l, e->h, T);
     ActIn qkv = linear(e, B2K_GEMM_QKV, XB_X, e->x, L.wqkv, L.tm_qkv, e->qkv, T, e->qkv_size, H, &rc);
     B2_TRY(rc);
     {
       KL k(e, B2K_ROPE_KV);
-      B2_TRY(launch_qknorm_rope_kv(qkv, L.qnorm, L.knorm, e->cos_sin, e->d_positions, e->d_slots, e->qrot, kp, vp, T,
+      if (!k.skip()) B2_TRY(launch_qknorm_rope_kv(qkv, L.qnorm, L.knorm, e->cos_sin, e->d_positions, e->d_slots, e->qrot, kp, vp, T,
                                    c.num_q_heads, c.num_kv_heads, c.head_dim, c.block_size, c.rms_eps, e->stream));
     }
     if (ntiles > 0) {
       KL k(e, B2K_MISC);
-      B2_TRY(launch_attn_prefill(e->qrot, kp, vp, e->d_block_table, e->bt_stride, e->d_tiles, ntiles, e->attn,
+      if (!k.skip()) B2_TRY(launch_attn_prefill(e->qrot, kp, vp, e->d_block_table, e->bt_stride, e->d_tiles, ntiles, e->attn,
                                  c.num_q_heads, c.num_kv_heads, c.head_dim, c.block_size, e->stream));
     } else {
       {
         KL k(e, B2K_ATTN_DECODE);
-        B2_TRY(launch_attn_decode(e->qrot, kp, vp, e->d_block_table, e->bt_stride, e->d_seq_lens, e->attn_scratch,
+        if (!k.skip()) B2_TRY(launch_attn_decode(e->qrot, kp, vp, e->d_block_table, e->bt_stride, e->d_seq_lens, e->attn_scratch,
                                   e->attn, T, c.num_q_heads, c.num_kv_heads, c.head_dim, c.block_size, attn_split,
                                   e->stream));
       }
       if (attn_split > 1) {
         KL k(e, B2K_ATTN_COMBINE);
-        B2_TRY(launch_attn_combine(e->attn_scratch, e->attn, T, c.num_q_heads, c.num_kv_heads, c.head_dim, attn_split,
+        if (!k.skip()) B2_TRY(launch_attn_combine(e->attn_scratch, e->attn, T, c.num_q_heads, c.num_kv_heads, c.head_dim, attn_split,
                                    e->stream));
       }
     }
@@ -305,20 +311,20 @@ int forward(b2_engine* e, int T, int ntiles, int nlast, int attn_split) {
     B2_TRY(rc);
     {
       KL k(e, B2K_NORM);
-      B2_TRY(launch_add_rmsnorm(e->h, o, L.ln2, e->x, T, H, c.rms_eps, e->stream));
+      if (!k.skip()) B2_TRY(launch_add_rmsnorm(e->h, o, L.ln2, e->x, T, H, c.rms_eps, e->stream));
     }
     ActIn gu = linear(e, B2K_GEMM_GATEUP, XB_X, e->x, L.wgu, L.tm_gu, e->gu, T, 2 * I, H, &rc);
     B2_TRY(rc);
     {
       KL k(e, B2K_ACT);
-      B2_TRY(launch_silu_mul(gu, e->act, T, I, e->stream));
+      if (!k.skip()) B2_TRY(launch_silu_mul(gu, e->act, T, I, e->stream));
     }
     delta = linear(e, B2K_GEMM_DOWN, XB_ACT, e->act, L.wd, L.tm_d, e->proj, T, H, I, &rc);
     B2_TRY(rc);
   }
   {
     KL k(e, B2K_NORM);
-    B2_TRY(launch_add_rmsnorm(e->h, delta, e->final_norm, e->x, T, H, c.rms_eps, e->stream));
+    if (!k.skip()) B2_TRY(launch_add_rmsnorm(e->h, delta, e->final_norm, e->x, T, H, c.rms_eps, e->stream));
   }
   dbg_capture(e, c.num_layers, e->h, T);
   dbg_capture(e, c.num_layers + 1, e->x, T);
@@ -328,7 +334,7 @@ int forward(b2_engine* e, int T, int ntiles, int nlast, int attn_split) {
   XBuf xb = XB_X;
   if (ntiles > 0) {
     KL k(e, B2K_MISC);
-    B2_TRY(launch_gather_rows(e->x, e->d_last_rows, e->xlast, nlast, H, e->stream));
+    if (!k.skip()) B2_TRY(launch_gather_rows(e->x, e->d_last_rows, e->xlast, nlast, H, e->stream));
     xl = e->xlast;
     xb = XB_LAST;
   }
@@ -341,10 +347,10 @@ int forward(b2_engine* e, int T, int ntiles, int nlast, int attn_split) {
     }
     {
       KL k(e, B2K_LMHEAD);
-      B2_TRY(launch_linear_simt(xl, e->lm_head, e->logits, 0, nlast, c.vocab, H, e->stream));
+      if (!k.skip()) B2_TRY(launch_linear_simt(xl, e->lm_head, e->logits, 0, nlast, c.vocab, H, e->stream));
     }
     KL k2(e, B2K_MISC);
-    B2_TRY(launch_argmax_rows(e->logits, e->d_out_tokens, nlast, c.vocab, e->stream));
+    if (!k2.skip()) B2_TRY(launch_argmax_rows(e->logits, e->d_out_tokens, nlast, c.vocab, e->stream));
   } else {
     TcGemmArgs a;
     a.tmap_w = e->tm_lm_head;
@@ -357,10 +363,10 @@ int forward(b2_engine* e, int T, int ntiles, int nlast, int attn_split) {
     a.argmax_packed = e->d_argmax;
     {
       KL k(e, B2K_LMHEAD);
-      B2_TRY(launch_linear_tc(a, e->stream));
+      if (!k.skip()) B2_TRY(launch_linear_tc(a, e->stream));
     }
     KL k2(e, B2K_MISC);
-    B2_TRY(launch_argmax_finalize(e->d_argmax, e->d_out_tokens, nlast, e->stream));
+    if (!k2.skip()) B2_TRY(launch_argmax_finalize(e->d_argmax, e->d_out_tokens, nlast, e->stream));
   }
   return 0;
 }
@@ -382,13 +388,13 @@ __global__ void publish_tokens_kernel(const int32_t* __restrict__ out_tokens, in
 int decode_body(b2_engine* e, int B, int attn_split) {
   {
     KL k(e, B2K_MISC);
-    B2_TRY(launch_decode_advance(e->d_positions, e->d_seq_lens, e->d_slots, e->d_block_table, e->bt_stride,
+    if (!k.skip()) B2_TRY(launch_decode_advance(e->d_positions, e->d_seq_lens, e->d_slots, e->d_block_table, e->bt_stride,
                                  e->cfg.block_size, B, e->stream));
   }
   B2_TRY(forward(e, B, 0, B, attn_split));
   {
     KL k(e, B2K_MISC);
-    B2_CUDA_OK(b2_launch(publish_tokens_kernel, dim3(1), dim3(256), 0, e->stream, (const int32_t*)e->d_out_tokens, e->d_tokens,
+    if (!k.skip()) B2_CUDA_OK(b2_launch(publish_tokens_kernel, dim3(1), dim3(256), 0, e->stream, (const int32_t*)e->d_out_tokens, e->d_tokens,
                          e->d_token_log, e->d_step, B, e->log_cap_steps, e->cfg.max_seqs));
   }
   return 0;
@@ -644,6 +650,7 @@ extern "C" int b2_engine_create(const b2_config* cfg, const char* safetensors_pa
   e->simt_max_tokens = env_int("B2_SIMT_MAX_TOKENS", 0);
   e->attn_split_override = env_int("B2_ATTN_SPLITS", 0);
   e->force_gemm_impl = env_int("B2_GEMM_IMPL", -1);
+  e->skip_mask = (unsigned)env_int("B2_SKIP_MASK", 0);
   const int H = c.hidden, I = c.intermediate;
   int rc = 0;
 #define E_TRY(expr)        \

@@ -258,6 +258,12 @@ def run_b200(args, rank, world, local, dist):
     launches = eng.launch_count() - l0
     ms_max = reduce_max(dist, ms)
     tok_s = world * BATCH * K / (ms_max / 1e3)
+    if args.value_only:
+        if rank == 0:
+            print(json.dumps({"ms_per_step": ms_max / K, "value": tok_s, "skip_mask": os.environ.get("B2_SKIP_MASK", "0"),
+                              "env": {k: v for k, v in os.environ.items() if k.startswith("B2_")}}), flush=True)
+        eng.close()
+        return
 
     # ---- end to end through the public call, host buffers in and out every step ----------------
     for s in sids:
@@ -339,6 +345,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=8)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--value-only", action="store_true", help="device-resident timing only (ablation runs)")
     args = ap.parse_args()
     rank, world, local, dist = dist_setup(args.gpus)
     try:
