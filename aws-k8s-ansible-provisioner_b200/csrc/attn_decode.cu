@@ -257,11 +257,8 @@ int launch_attn_decode(const bf16* q, const bf16* k_pages, const bf16* v_pages, 
   B2_REQUIRE(hd == AD_HD && block_size == AD_BS, "attn_decode: built for head_dim 128 / page 16 (got %d / %d)", hd, block_size);
   B2_REQUIRE(nq == 2 * nkv, "attn_decode: built for a GQA group of 2 (nq=%d nkv=%d)", nq, nkv);
   B2_REQUIRE(nsplit >= 1 && (nsplit == 1 || scratch != nullptr), "attn_decode: nsplit=%d needs scratch", nsplit);
-  static bool attr_done = false;
-  if (!attr_done) {
-    B2_CUDA_OK(cudaFuncSetAttribute(attn_decode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AD_SMEM));
-    attr_done = true;
-  }
+  static B2PerDeviceOnce attr_once;
+  if (attr_once.need()) B2_CUDA_OK(cudaFuncSetAttribute(attn_decode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AD_SMEM));
   dim3 grid(nsplit, nkv, B);
   const float scale = (float)(1.0 / sqrt((double)hd));  // HF passes head_dim**-0.5 as a double
   B2_CUDA_OK(b2_launch(attn_decode_kernel, grid, dim3(AD_WARPS * 32), (size_t)AD_SMEM, s, q, k_pages, v_pages, block_table,

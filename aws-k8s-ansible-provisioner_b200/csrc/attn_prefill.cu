@@ -220,11 +220,8 @@ int launch_attn_prefill(const bf16* q, const bf16* k_pages, const bf16* v_pages,
   if (ntiles <= 0) return 0;
   B2_REQUIRE(hd == AP_HD, "attn_prefill: head_dim %d not built (128 only)", hd);
   B2_REQUIRE(nq % nkv == 0, "attn_prefill: nq=%d not a multiple of nkv=%d", nq, nkv);
-  static bool attr_done = false;
-  if (!attr_done) {
-    B2_CUDA_OK(cudaFuncSetAttribute(attn_prefill_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AP_SMEM));
-    attr_done = true;
-  }
+  static B2PerDeviceOnce attr_once;
+  if (attr_once.need()) B2_CUDA_OK(cudaFuncSetAttribute(attn_prefill_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AP_SMEM));
   const float scale_log2 = (float)((1.0 / sqrt((double)hd)) * 1.4426950408889634);
   dim3 grid(ntiles, nq);
   B2_CUDA_OK(b2_launch(attn_prefill_kernel, grid, dim3(128), (size_t)AP_SMEM, s, q, k_pages, v_pages, block_table, bt_stride,

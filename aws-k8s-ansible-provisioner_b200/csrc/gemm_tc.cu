@@ -291,11 +291,8 @@ int tc_pick_nsplit(int T, int N, int K, int num_sms) {
 template <int BN, int EPI>
 static int launch_one(const TcGemmArgs& a, int kb_per_split, cudaStream_t s) {
   using C = TcCfg<BN>;
-  static bool attr_done = false;
-  if (!attr_done) {
-    B2_CUDA_OK(cudaFuncSetAttribute(linear_tc_kernel<BN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
-    attr_done = true;
-  }
+  static B2PerDeviceOnce attr_once;
+  if (attr_once.need()) B2_CUDA_OK(cudaFuncSetAttribute(linear_tc_kernel<BN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
   const int m_tiles = (a.N + TC_BM - 1) / TC_BM, n_tiles = (a.T + BN - 1) / BN;
   const int total = m_tiles * n_tiles * a.nsplit;
   static int sms = device_num_sms();
