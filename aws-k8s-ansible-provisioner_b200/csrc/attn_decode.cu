@@ -14,6 +14,9 @@
 //   O += p_j * v_j  in fp32; final O * (1 / l) rounded once to bf16.
 // Warp partials merge through shared memory, CTA partials (nsplit > 1) through a global fp32
 // scratch that attn_combine_kernel reduces in split order (deterministic, no atomics).
+#include <mutex>
+
+#include "../../include/b2_engine.h"
 #include "kernels.h"
 
 namespace b2 {
@@ -273,4 +276,70 @@ int launch_attn_combine(const float* scratch, bf16* out, int B, int nq, int nkv,
   return 0;
 }
 
+
+// ---------------------------------------------------------------------------------------
+// Allocation-free variant of b2k_attn_decode.
+//
+// Some users of this library are not in a position to hand the kernel a scratch buffer:
+//   * a serving process that gave all remaining HBM to its KV pool at start-up (b2serve does, via
+//     gpu_mem_fraction) -- a cudaMalloc on the request path can simply fail there;
+//   * request-path code that must not stall: cudaMalloc/cudaFree synchronise the device, so one
+//     call delays every stream of the process, not just the caller's;
+//   * a plugin that only receives raw input/output pointers from a host framework and has no
+//     allocator of its own to ask.
+// For them the split partials live in the file-scope device array below.  It is part of the
+// library image: every GPU that loads libb2engine.so holds B2K_ATTN_NOALLOC_MAX_FLOATS * 4 bytes
+// (8 MiB) for it until the process exits, whether or not this entry point is ever called.
+// ---------------------------------------------------------------------------------------
+static __device__ __align__(256) float g_attn_noalloc_scratch[B2K_ATTN_NOALLOC_MAX_FLOATS];
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_noalloc_mu;
+float* g_noalloc_ptr[kMaxDevices] = {nullptr};
+
+// In host code `g_attn_noalloc_scratch` is only a handle for the symbol, not a device address: a
+// kernel given `&g_attn_noalloc_scratch[0]` from here would fault (or, where the GPU can reach host
+// memory, quietly use the wrong bytes).  The device address is looked up once per device, with that
+// device current, and cached.
+int noalloc_scratch_for_current_device(float** out) {
+  int dev = -1;
+  B2_CUDA_OK(cudaGetDevice(&dev));
+  B2_REQUIRE(dev >= 0 && dev < kMaxDevices, "b2k_attn_decode_noalloc: device index %d not supported", dev);
+  std::lock_guard<std::mutex> lock(g_noalloc_mu);
+  if (g_noalloc_ptr[dev] == nullptr) {
+    float* p = nullptr;
+    B2_CUDA_OK(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_attn_noalloc_scratch));
+    B2_REQUIRE(p != nullptr, "b2k_attn_decode_noalloc: no device address for the static scratch on device %d", dev);
+    g_noalloc_ptr[dev] = p;
+  }
+  *out = g_noalloc_ptr[dev];
+  return 0;
+}
+}  // namespace
+
 }  // namespace b2
+
+extern "C" int b2k_attn_decode_noalloc(const void* q, const void* k_pages, const void* v_pages, const int32_t* block_table,
+                                       int bt_stride, const int32_t* seq_lens, void* out, int B, int nq, int nkv, int hd,
+                                       int block_size, int nsplit, void* stream) {
+  using namespace b2;
+  B2_REQUIRE(q && k_pages && v_pages && block_table && seq_lens && out, "b2k_attn_decode_noalloc: null pointer");
+  B2_REQUIRE(B >= 1 && nsplit >= 1 && nq >= 1 && nkv >= 1, "b2k_attn_decode_noalloc: bad sizes");
+  const size_t need = attn_decode_scratch_floats(B, nq, nkv, hd, nsplit);
+  B2_REQUIRE(need <= (size_t)B2K_ATTN_NOALLOC_MAX_FLOATS,
+             "b2k_attn_decode_noalloc: batch %d x %d kv heads x %d splits needs %zu floats of scratch, the built-in array holds %d; "
+             "use fewer splits or b2k_attn_decode with your own buffer",
+             B, nkv, nsplit, need, (int)B2K_ATTN_NOALLOC_MAX_FLOATS);
+  float* scratch = nullptr;
+  int rc = noalloc_scratch_for_current_device(&scratch);
+  if (rc != 0) return rc;
+  cudaStream_t s = (cudaStream_t)stream;
+  // Nothing in the array has to start at zero: every slot the combine pass reads is written by the
+  // attention pass of the same call first, so what an earlier call left behind is never observed.
+  rc = launch_attn_decode((const bf16*)q, (const bf16*)k_pages, (const bf16*)v_pages, block_table, bt_stride, seq_lens, scratch,
+                          (bf16*)out, B, nq, nkv, hd, block_size, nsplit, s);
+  if (rc != 0) return rc;
+  if (nsplit > 1) rc = launch_attn_combine(scratch, (bf16*)out, B, nq, nkv, hd, nsplit, s);
+  return rc;
+}

@@ -177,6 +177,25 @@ int b2k_attn_decode(const void* q, const void* k_pages, const void* v_pages,
                     int nsplit, void* stream);
 size_t b2k_attn_decode_scratch_floats(int B, int nq, int nkv, int hd, int nsplit);
 
+/* No counterpart in the reference (it has no kernels at all).  Same computation and arguments as
+ * b2k_attn_decode, minus scratch_f32: for callers that cannot allocate device memory -- a server
+ * whose KV pool already owns the free HBM, request-path code that cannot afford the device-wide
+ * synchronisation of cudaMalloc/cudaFree, a plugin that is only handed input/output pointers.  The
+ * split partials go to an array compiled into the library (B2K_ATTN_NOALLOC_MAX_FLOATS floats =
+ * 8 MiB, resident on every GPU that loads the library until the process exits).  The call allocates
+ * and frees nothing.  It fails with a message if b2k_attn_decode_scratch_floats(B, nq, nkv, hd,
+ * nsplit) exceeds that size (nsplit == 1 needs none and always fits).
+ * The first call on each device looks up the array's device address (that device must be current)
+ * and caches it; make that first call before starting any stream capture.
+ * All calls share the one array and it keeps whatever the last call wrote; nothing in it needs to be
+ * cleared between calls, but two calls whose kernels overlap on the GPU (different streams, or
+ * different host threads) race on it -- serialise them. */
+#define B2K_ATTN_NOALLOC_MAX_FLOATS (2 * 1024 * 1024)
+int b2k_attn_decode_noalloc(const void* q, const void* k_pages, const void* v_pages,
+                            const int32_t* block_table, int bt_stride, const int32_t* seq_lens,
+                            void* out, int B, int nq, int nkv, int hd, int block_size, int nsplit,
+                            void* stream);
+
 /* Same contract at T > 1 (causal): ragged prefill over the paged cache.  q [T][nq*hd];
  * q_seq[T] / q_pos[T] int32 give the sequence row in block_table and the position of each
  * query token (tokens of one sequence contiguous and ascending).  Host arrays. */
