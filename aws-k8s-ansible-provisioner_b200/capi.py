@@ -59,9 +59,9 @@ SIGNATURES = {
     "b2k_silu_mul": (_I, [_P, _I, _I, _P, _I, _I, _P]),
     "b2k_linear": (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _I, _P]),
     "b2k_lmhead_argmax": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _I, _P]),
-    "b2k_attn_decode": (_I, [_P, _P, _P, _P, _I, _P, _P, _P, _I, _I, _I, _I, _I, _I, _P]),
-    "b2k_attn_decode_scratch_floats": (C.c_size_t, [_I, _I, _I, _I, _I]),
-    "b2k_attn_decode_noalloc": (_I, [_P, _P, _P, _P, _I, _P, _P, _I, _I, _I, _I, _I, _I, _P]),
+    "b2k_attn_decode": (_I, [_P, _P, _P, _P, _I, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
+    "b2k_attn_decode_scratch_floats": (C.c_size_t, [_I, _I, _I, _I]),
+    "b2k_attn_decode_noalloc": (_I, [_P, _P, _P, _P, _I, _P, _P, _I, _I, _I, _I, _I, _P]),
     "b2k_attn_prefill": (_I, [_P, _P, _P, _P, _I, _I32P, _I32P, _I32P, _I32P, _I, _P, _I, _I, _I, _I, _P]),
 }
 

@@ -1,19 +1,24 @@
-// attn_decode.cu -- paged GQA decode attention, flash-decoding split-K
+// attn_decode.cu -- paged GQA decode attention
 // (HF:integrations/sdpa_attention.py:40-104 at T == 1; eager form HF:models/qwen3/
-// modeling_qwen3.py:196-218).  This is the HBM-dominant kernel of batch-64 decode: per step it
-// reads every resident K and V page once (B * S * 114688 B per step).
+// modeling_qwen3.py:196-218).  This is the HBM-dominant kernel of batch-64 decode: per step and
+// layer it reads every resident K and V page exactly once.
 //
-// Work split: one CTA per (kv-split, kv head, sequence); both query heads of the GQA group
-// share every K/V page, so each page is fetched once per group.  Inside a CTA each of the 4
-// warps runs its own TMA pipeline: lane 0 issues two 4 KB bulk copies (cp.async.bulk, one K
-// page-slice and one V page-slice of [16 tokens][128 dims]) per stage onto an mbarrier, three
-// stages deep, while the warp computes on the previous stage:
-//   scores  s_j = (q . k_j) * scale      fp32 accumulate over bf16 inputs
-//   online softmax in fp32; p_j = exp(s_j - m) is ROUNDED TO bf16 before P.V (what torch's CPU
-//   flash kernel does for reduced-precision inputs), the row sum uses the unrounded fp32 p_j
-//   O += p_j * v_j  in fp32; final O * (1 / l) rounded once to bf16.
-// Warp partials merge through shared memory, CTA partials (nsplit > 1) through a global fp32
-// scratch that attn_combine_kernel reduces in split order (deterministic, no atomics).
+// Work distribution ("stream-K" over pages): the pages of all (sequence, kv head) units are laid
+// end to end, and each of the grid's persistent warps (8 per SM) takes one contiguous run of that
+// line, so every warp moves the same number of bytes whatever the mix of sequence lengths, and a
+// warp's TMA pipeline runs without interruption across unit boundaries.  Where a run ends inside a
+// unit the warp leaves a partial (m, l, O) record; attn_combine_kernel merges the 1..few records of
+// each unit in run order (deterministic, no atomics).
+//
+// Per warp: lane 0 issues two 4 KB bulk copies (cp.async.bulk, one K and one V page-slice of
+// [16 tokens][128 dims]) per stage onto an mbarrier, three stages deep.  Pages are stored with the
+// 16-byte chunks of every token row XOR-swizzled by (row & 7) (kv_swizzled_chunk in kernels.h), so
+// the dense copy lands in shared memory already bank-conflict-free for ldmatrix.  Math per page:
+//   S = K.Q^T     mma.sync m16n8k16: 16 tokens x (2 query heads of the GQA group, padded to 8)
+//   online softmax in fp32; p = exp(s*scale - m) ROUNDED TO bf16 for P.V (what torch's CPU flash
+//   kernel does for bf16 inputs), the row sum uses the unrounded fp32 p
+//   O^T += V^T.P^T  mma.sync with V read through ldmatrix.trans; fp32 accumulate
+// Final O * (1/l) is rounded once to bf16 in the combine pass.
 #include <mutex>
 
 #include "../../include/b2_engine.h"
@@ -21,261 +26,342 @@
 
 namespace b2 {
 
-constexpr int AD_WARPS = 4;
+constexpr int AD_WARPS = 8;
 constexpr int AD_STAGES = 3;
 constexpr int AD_BS = 16;    // tokens per KV page
 constexpr int AD_HD = 128;   // head dim
 constexpr int AD_TILE = AD_BS * AD_HD * 2;       // 4096 B: one page-slice of K (or V) for one kv head
 constexpr int AD_STAGE = 2 * AD_TILE;            // K + V
-constexpr int AD_SMEM = AD_WARPS * AD_STAGES * AD_STAGE;  // 96 KB
+constexpr int AD_SMEM = AD_WARPS * AD_STAGES * AD_STAGE;  // 192 KB
+constexpr int AD_MAX_B = 512;
+constexpr int AD_MAX_CTAS = 160;
+constexpr int AD_META = 1024;                    // ints at the head of the scratch: [0]=pages per warp, [1..B+1]=page prefix
+constexpr int AD_REC = 2 * AD_HD + 4;            // floats per partial record: O[2][128], m[2], l[2]
 
-__global__ void __launch_bounds__(AD_WARPS * 32)
+__device__ __forceinline__ void ad_ldsm_x4(uint32_t addr, uint32_t* r) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+               : "r"(addr));
+}
+__device__ __forceinline__ void ad_ldsm_x4_t(uint32_t addr, uint32_t* r) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+               : "r"(addr));
+}
+__device__ __forceinline__ void ad_mma(float* d, const uint32_t* a, uint32_t b0, uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+struct AdPos {  // a position on the page line
+  int b, kvh, j, nb;
+};
+
+__global__ void __launch_bounds__(AD_WARPS * 32, 1)
 attn_decode_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k_pages, const bf16* __restrict__ v_pages,
                    const int32_t* __restrict__ block_table, int bt_stride, const int32_t* __restrict__ seq_lens,
-                   float* __restrict__ scratch, bf16* __restrict__ out, int B, int nq, int nkv, int nsplit, float scale) {
+                   float* __restrict__ scratch, int B, int nq, int nkv, float scale) {
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ __align__(8) uint64_t bars[AD_WARPS][AD_STAGES];
-  __shared__ float sm_m[AD_WARPS][2], sm_l[AD_WARPS][2];
-  __shared__ float sm_o[AD_WARPS][2][AD_HD];
+  __shared__ int s_prefix[AD_MAX_B + 1];  // pages of sequences before b (exclusive prefix)
 
   pdl_launch_dependents();
-  pdl_wait();
-  const int split = blockIdx.x, kvh = blockIdx.y, b = blockIdx.z;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int S = seq_lens[b];
-  const int nblk = (S + AD_BS - 1) / AD_BS;
-  const int bps = (nblk + nsplit - 1) / nsplit;
-  const int blk0 = split * bps;
-  const int blk1 = min(nblk, blk0 + bps);
-  const int nb_w = (blk1 - blk0 > warp) ? (blk1 - blk0 - warp + AD_WARPS - 1) / AD_WARPS : 0;
-
   if (threadIdx.x == 0) {
     for (int w = 0; w < AD_WARPS; ++w)
       for (int s = 0; s < AD_STAGES; ++s) mbar_init(smem_u32(&bars[w][s]), 1);
     mbar_fence_init();
   }
-  __syncthreads();
-
-  // thread mapping of the QK phase: 4 lanes per token (part = 32-dim slice), 8 tokens per pass
-  const int part = lane & 3, tok8 = lane >> 2;
-  const int rot = 2 * (part >> 1) + (tok8 & 1);  // per-thread chunk rotation -> conflict-free LDS.128
-  float qreg[2][32];
-  {
-    const bf16* qb = q + ((size_t)b * nq + (size_t)kvh * 2) * AD_HD;
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int c = 4 * part + ((i + rot) & 3);
-#pragma unroll
-      for (int h = 0; h < 2; ++h) unpack8(*reinterpret_cast<const uint4*>(qb + h * AD_HD + c * 8), &qreg[h][i * 8]);
+  pdl_wait();
+  // ---- page prefix over sequences (warp 0: a slab of entries per lane, then a warp scan) ----
+  if (warp == 0) {
+    const int per = (B + 31) / 32;
+    int local = 0;
+    for (int i = 0; i < per; ++i) {
+      const int b = lane * per + i;
+      if (b < B) local += (seq_lens[b] + AD_BS - 1) / AD_BS;
     }
+    int incl = local;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int v = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += v;
+    }
+    int run = incl - local;
+    for (int i = 0; i < per; ++i) {
+      const int b = lane * per + i;
+      if (b < B) {
+        s_prefix[b] = run;
+        run += (seq_lens[b] + AD_BS - 1) / AD_BS;
+      }
+    }
+    if (lane == 31) s_prefix[B] = incl;
   }
+  __syncthreads();
+  const int total_pages = s_prefix[B] * nkv;  // length of the page line
+  const int wtot = gridDim.x * AD_WARPS;
+  const int ppw = max(1, (total_pages + wtot - 1) / wtot);
+  if (blockIdx.x == 0) {  // publish the geometry for the combine pass
+    int* meta = reinterpret_cast<int*>(scratch);
+    if (threadIdx.x == 0) meta[0] = ppw;
+    for (int i = threadIdx.x; i <= B; i += blockDim.x) meta[1 + i] = s_prefix[i];
+  }
+  const int gw = blockIdx.x * AD_WARPS + warp;
+  const int p0 = min(total_pages, gw * ppw), p1 = min(total_pages, p0 + ppw);
+  const int ntiles = p1 - p0;
+  if (ntiles <= 0) return;
 
-  const int32_t* bt = block_table + (size_t)b * bt_stride;
+  auto locate = [&](int p) -> AdPos {  // page-line position -> (sequence, kv head, page in sequence)
+    int lo = 0, hi = B - 1;
+    while (lo < hi) {  // largest b with nkv * prefix[b] <= p
+      const int mid = (lo + hi + 1) >> 1;
+      if (s_prefix[mid] * nkv <= p) lo = mid; else hi = mid - 1;
+    }
+    AdPos r;
+    r.b = lo;
+    r.nb = s_prefix[lo + 1] - s_prefix[lo];
+    const int rem = p - s_prefix[lo] * nkv;
+    r.kvh = rem / r.nb;
+    r.j = rem - r.kvh * r.nb;
+    return r;
+  };
+
   uint8_t* wsm = smem + (size_t)warp * AD_STAGES * AD_STAGE;
-  int cached_group = -1, cached_blk = 0;
-  auto get_blk = [&](int i) -> int {  // physical page of this warp's i-th tile (all lanes call)
-    const int g = i >> 5;
+  int cached_group = -1, cached_slice = 0;
+  auto slice_of = [&](int n) -> int {  // (physical page * nkv + kv head) of this warp's n-th tile; all lanes call
+    const int g = n >> 5;
     if (g != cached_group) {
-      const int ii = (g << 5) + lane;
-      cached_blk = (ii < nb_w) ? bt[blk0 + warp + AD_WARPS * ii] : 0;
+      const int nn = (g << 5) + lane;
+      cached_slice = 0;
+      if (nn < ntiles) {
+        const AdPos r = locate(p0 + nn);
+        cached_slice = block_table[(size_t)r.b * bt_stride + r.j] * nkv + r.kvh;
+      }
       cached_group = g;
     }
-    return __shfl_sync(0xffffffffu, cached_blk, i & 31);
+    return __shfl_sync(0xffffffffu, cached_slice, n & 31);
   };
-  auto issue = [&](int stage, int phys) {  // lane 0 only
+  auto issue = [&](int n, int slice) {  // lane 0 only
+    const int stage = n % AD_STAGES;
     const uint32_t bar = smem_u32(&bars[warp][stage]);
     const uint32_t dst = smem_u32(wsm + stage * AD_STAGE);
-    const size_t off = ((size_t)phys * nkv + kvh) * (AD_BS * AD_HD);
+    const size_t off = (size_t)slice * (AD_BS * AD_HD);
     mbar_arrive_expect_tx(bar, AD_STAGE);
     bulk_g2s(dst, k_pages + off, AD_TILE, bar);
     bulk_g2s(dst + AD_TILE, v_pages + off, AD_TILE, bar);
   };
-
-  for (int i = 0; i < AD_STAGES; ++i) {
-    const int phys = get_blk(i);
-    if (i < nb_w && lane == 0) issue(i, phys);
+  for (int n = 0; n < AD_STAGES; ++n) {
+    const int sl = slice_of(n);
+    if (n < ntiles && lane == 0) issue(n, sl);
   }
 
-  float m_run[2] = {-INFINITY, -INFINITY}, l_run[2] = {0.f, 0.f};
-  float acc[2][8];
-#pragma unroll
-  for (int e = 0; e < 8; ++e) acc[0][e] = acc[1][e] = 0.f;
-  const int half = lane >> 4, chunk = lane & 15;
+  const int g = lane >> 2, t4 = lane & 3;
+  AdPos cur = locate(p0);
+  int S = seq_lens[cur.b];
+  uint32_t qb0[8], qb1[8];
+  float oacc[8][4];
+  float m_run[2], l_run[2];
+  bool fresh = true;  // (re)load q and reset the running state at the next tile
 
-  for (int i = 0; i < nb_w; ++i) {
-    const int stage = i % AD_STAGES;
-    mbar_wait(smem_u32(&bars[warp][stage]), (uint32_t)((i / AD_STAGES) & 1));
-    const uint8_t* kbase = wsm + stage * AD_STAGE;
-    const uint8_t* vbase = kbase + AD_TILE;
-    const int tok_base = (blk0 + warp + AD_WARPS * i) * AD_BS;
-
-    // ---- scores for 16 tokens x 2 query heads ----
-    float sc[2][2];
+  for (int n = 0; n < ntiles; ++n) {
+    if (fresh) {
+      const bf16* qp = q + ((size_t)cur.b * nq + (size_t)cur.kvh * 2 + (g & 1)) * AD_HD;
 #pragma unroll
-    for (int pass = 0; pass < 2; ++pass) {
-      const int tk = pass * 8 + tok8;
-      float d0 = 0.f, d1 = 0.f;
-#pragma unroll
-      for (int ii = 0; ii < 4; ++ii) {
-        const int c = 4 * part + ((ii + rot) & 3);
-        float kf[8];
-        unpack8(*reinterpret_cast<const uint4*>(kbase + tk * (AD_HD * 2) + c * 16), kf);
-#pragma unroll
-        for (int e = 0; e < 8; ++e) {
-          d0 = fmaf(qreg[0][ii * 8 + e], kf[e], d0);
-          d1 = fmaf(qreg[1][ii * 8 + e], kf[e], d1);
-        }
+      for (int ks = 0; ks < 8; ++ks) {
+        qb0[ks] = g < 2 ? *reinterpret_cast<const uint32_t*>(qp + ks * 16 + 2 * t4) : 0u;
+        qb1[ks] = g < 2 ? *reinterpret_cast<const uint32_t*>(qp + ks * 16 + 8 + 2 * t4) : 0u;
       }
-      d0 += __shfl_xor_sync(0xffffffffu, d0, 1);
-      d1 += __shfl_xor_sync(0xffffffffu, d1, 1);
-      d0 += __shfl_xor_sync(0xffffffffu, d0, 2);
-      d1 += __shfl_xor_sync(0xffffffffu, d1, 2);
-      const bool valid = tok_base + tk < S;
-      sc[pass][0] = valid ? d0 * scale : -INFINITY;
-      sc[pass][1] = valid ? d1 * scale : -INFINITY;
+#pragma unroll
+      for (int dt = 0; dt < 8; ++dt) oacc[dt][0] = oacc[dt][1] = oacc[dt][2] = oacc[dt][3] = 0.f;
+      m_run[0] = m_run[1] = -INFINITY;
+      l_run[0] = l_run[1] = 0.f;
+      fresh = false;
     }
-    // ---- online softmax (running max / sum per head, warp-uniform max) ----
-    float pb[2][2];
+    const int stage = n % AD_STAGES;
+    mbar_wait(smem_u32(&bars[warp][stage]), (uint32_t)((n / AD_STAGES) & 1));
+    const uint32_t kb = smem_u32(wsm + stage * AD_STAGE);
+    const uint32_t vb = kb + AD_TILE;
+
+    // ---- S = K.Q^T : 16 tokens x 8 (2 real) heads ----
+    float sacc[4] = {0.f, 0.f, 0.f, 0.f};
+    {
+      const int row = (lane & 7) + ((lane >> 3) & 1) * 8;
+#pragma unroll
+      for (int ks = 0; ks < 8; ++ks) {
+        uint32_t a[4];
+        ad_ldsm_x4(kb + row * (AD_HD * 2) + (((2 * ks + (lane >> 4)) ^ (row & 7)) << 4), a);
+        ad_mma(sacc, a, qb0[ks], qb1[ks]);
+      }
+    }
+    // lanes with t4 == 0 hold (token g | g+8) x (head 0 | 1); give every lane of the quad a copy
+    float s[2][2];  // [token half][head]
+    s[0][0] = __shfl_sync(0xffffffffu, sacc[0], lane & ~3);
+    s[0][1] = __shfl_sync(0xffffffffu, sacc[1], lane & ~3);
+    s[1][0] = __shfl_sync(0xffffffffu, sacc[2], lane & ~3);
+    s[1][1] = __shfl_sync(0xffffffffu, sacc[3], lane & ~3);
+    const int tok = cur.j * AD_BS + g;
+    const bool ok_a = tok < S, ok_b = tok + 8 < S;
+    float p[2][2], corr[2];
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
-      float mx = fmaxf(sc[0][h], sc[1][h]);
+      const float sa = ok_a ? s[0][h] * scale : -INFINITY;
+      const float sb = ok_b ? s[1][h] * scale : -INFINITY;
+      float mx = fmaxf(sa, sb);
       mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 4));
       mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 8));
       mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 16));
-      const float m_new = fmaxf(m_run[h], mx);  // finite: every tile holds >= 1 valid token
-      const float corr = expf(m_run[h] - m_new);
-      const float p0 = expf(sc[0][h] - m_new), p1 = expf(sc[1][h] - m_new);
-      l_run[h] = l_run[h] * corr + (p0 + p1);
+      const float m_new = fmaxf(m_run[h], mx);  // finite: every page holds >= 1 valid token
+      corr[h] = expf(m_run[h] - m_new);
+      const float pa = expf(sa - m_new), pb = expf(sb - m_new);
+      float ls = pa + pb;
+      ls += __shfl_xor_sync(0xffffffffu, ls, 4);
+      ls += __shfl_xor_sync(0xffffffffu, ls, 8);
+      ls += __shfl_xor_sync(0xffffffffu, ls, 16);
+      l_run[h] = l_run[h] * corr[h] + ls;
       m_run[h] = m_new;
-#pragma unroll
-      for (int e = 0; e < 8; ++e) acc[h][e] *= corr;
-      pb[0][h] = bf16_round(p0);
-      pb[1][h] = bf16_round(p1);
+      p[0][h] = pa;
+      p[1][h] = pb;
     }
-    // ---- O += P . V : half-warp per token, 16 lanes x 8 dims ----
+    // ---- P^T as the B operand: lane (g = head, t4) needs tokens 2t4, 2t4+1 (+8) of head g ----
+    uint32_t pb0, pb1;
+    {
+      const int src = 8 * t4;  // quad that owns token 2*t4; the next quad (+4 lanes) owns token 2*t4+1
+      const float a00 = __shfl_sync(0xffffffffu, p[0][0], src), a01 = __shfl_sync(0xffffffffu, p[0][0], src + 4);
+      const float a10 = __shfl_sync(0xffffffffu, p[0][1], src), a11 = __shfl_sync(0xffffffffu, p[0][1], src + 4);
+      const float b00 = __shfl_sync(0xffffffffu, p[1][0], src), b01 = __shfl_sync(0xffffffffu, p[1][0], src + 4);
+      const float b10 = __shfl_sync(0xffffffffu, p[1][1], src), b11 = __shfl_sync(0xffffffffu, p[1][1], src + 4);
+      pb0 = g == 0 ? pack_bf16x2(a00, a01) : g == 1 ? pack_bf16x2(a10, a11) : 0u;
+      pb1 = g == 0 ? pack_bf16x2(b00, b01) : g == 1 ? pack_bf16x2(b10, b11) : 0u;
+    }
+    // ---- O^T = O^T * corr + V^T.P^T ----
+    {
+      const float c0 = corr[0], c1 = corr[1];  // accumulator columns are heads (2*t4, 2*t4+1): real for t4 == 0
+      const int row = (lane & 7) + ((lane >> 4) & 1) * 8;
 #pragma unroll
-    for (int i2 = 0; i2 < 8; ++i2) {
-      const int tk = 2 * i2 + half;
-      const int src = 4 * (tk & 7);
-      const float p0 = __shfl_sync(0xffffffffu, pb[i2 >> 2][0], src);
-      const float p1 = __shfl_sync(0xffffffffu, pb[i2 >> 2][1], src);
-      float vf[8];
-      unpack8(*reinterpret_cast<const uint4*>(vbase + tk * (AD_HD * 2) + chunk * 16), vf);
-#pragma unroll
-      for (int e = 0; e < 8; ++e) {
-        acc[0][e] = fmaf(p0, vf[e], acc[0][e]);
-        acc[1][e] = fmaf(p1, vf[e], acc[1][e]);
+      for (int dt = 0; dt < 8; ++dt) {
+        oacc[dt][0] *= c0; oacc[dt][1] *= c1; oacc[dt][2] *= c0; oacc[dt][3] *= c1;
+        uint32_t a[4];
+        ad_ldsm_x4_t(vb + row * (AD_HD * 2) + (((2 * dt + ((lane >> 3) & 1)) ^ (row & 7)) << 4), a);
+        ad_mma(oacc[dt], a, pb0, pb1);
       }
     }
     __syncwarp();
-    const int nxt = i + AD_STAGES;
-    const int phys = get_blk(nxt);
-    if (nxt < nb_w && lane == 0) issue(stage, phys);
-  }
-
-  // ---- merge: lanes -> warp -> CTA ----
-#pragma unroll
-  for (int h = 0; h < 2; ++h) {
-    l_run[h] += __shfl_xor_sync(0xffffffffu, l_run[h], 4);
-    l_run[h] += __shfl_xor_sync(0xffffffffu, l_run[h], 8);
-    l_run[h] += __shfl_xor_sync(0xffffffffu, l_run[h], 16);
-#pragma unroll
-    for (int e = 0; e < 8; ++e) acc[h][e] += __shfl_xor_sync(0xffffffffu, acc[h][e], 16);
-  }
-  if (lane == 0) {
-    sm_m[warp][0] = m_run[0]; sm_m[warp][1] = m_run[1];
-    sm_l[warp][0] = l_run[0]; sm_l[warp][1] = l_run[1];
-  }
-  if (lane < 16) {
-#pragma unroll
-    for (int h = 0; h < 2; ++h)
-#pragma unroll
-      for (int e = 0; e < 8; ++e) sm_o[warp][h][chunk * 8 + e] = acc[h][e];
-  }
-  __syncthreads();
-  const int d = threadIdx.x;  // 128 threads <-> 128 dims
-#pragma unroll
-  for (int h = 0; h < 2; ++h) {
-    float M = sm_m[0][h];
-#pragma unroll
-    for (int w = 1; w < AD_WARPS; ++w) M = fmaxf(M, sm_m[w][h]);
-    float O = 0.f, L = 0.f;
-    if (M > -INFINITY) {
-#pragma unroll
-      for (int w = 0; w < AD_WARPS; ++w) {
-        const float f = expf(sm_m[w][h] - M);
-        O = fmaf(f, sm_o[w][h][d], O);
-        L = fmaf(f, sm_l[w][h], L);
+    {
+      const int nxt = n + AD_STAGES;
+      const int sl = slice_of(nxt);
+      if (nxt < ntiles && lane == 0) issue(nxt, sl);
+    }
+    // ---- advance along the page line; leave a record when the unit (or the run) ends ----
+    const int unit = cur.b * nkv + cur.kvh;
+    bool unit_ends = (n + 1 == ntiles);
+    if (++cur.j == cur.nb) {
+      unit_ends = true;
+      cur.j = 0;
+      if (++cur.kvh == nkv) {
+        cur.kvh = 0;
+        do { ++cur.b; } while (cur.b < B && s_prefix[cur.b + 1] == s_prefix[cur.b]);
+        if (cur.b < B) {
+          cur.nb = s_prefix[cur.b + 1] - s_prefix[cur.b];
+          S = seq_lens[cur.b];
+        }
       }
     }
-    if (nsplit == 1) {
-      const float inv = L > 0.f ? __fdiv_rn(1.0f, L) : 0.f;
-      out[((size_t)b * nq + kvh * 2 + h) * AD_HD + d] = __float2bfloat16_rn(O * inv);
-    } else {
-      const size_t unit = (((size_t)b * nkv + kvh) * nsplit + split) * 2 + h;
-      scratch[unit * AD_HD + d] = O;
-      if (d == 0) {
-        float* ml = scratch + (size_t)B * nkv * nsplit * 2 * AD_HD;
-        ml[unit * 2 + 0] = M;
-        ml[unit * 2 + 1] = L;
+    if (unit_ends) {
+      float* rec = scratch + AD_META + (size_t)(unit + gw) * AD_REC;
+      if (t4 == 0) {
+#pragma unroll
+        for (int dt = 0; dt < 8; ++dt) {
+          rec[dt * 16 + g] = oacc[dt][0];
+          rec[AD_HD + dt * 16 + g] = oacc[dt][1];
+          rec[dt * 16 + 8 + g] = oacc[dt][2];
+          rec[AD_HD + dt * 16 + 8 + g] = oacc[dt][3];
+        }
       }
+      if (lane == 0) {
+        rec[2 * AD_HD + 0] = m_run[0];
+        rec[2 * AD_HD + 1] = m_run[1];
+        rec[2 * AD_HD + 2] = l_run[0];
+        rec[2 * AD_HD + 3] = l_run[1];
+      }
+      fresh = true;
     }
   }
 }
 
-// Reduces the split partials of one (sequence, query head) in split order.
-__global__ void __launch_bounds__(AD_HD)
-attn_combine_kernel(const float* __restrict__ scratch, bf16* __restrict__ out, int B, int nq, int nkv, int nsplit) {
+// One CTA per (sequence, kv head) unit, thread = (head, dim): merges the unit's records in run order.
+__global__ void __launch_bounds__(2 * AD_HD)
+attn_combine_kernel(const float* __restrict__ scratch, bf16* __restrict__ out, int B, int nq, int nkv) {
   pdl_launch_dependents();
   pdl_wait();
-  const int b = blockIdx.x / nq, qh = blockIdx.x % nq;
-  const int kvh = qh / 2, h = qh % 2;
-  const int d = threadIdx.x;
-  const float* ml = scratch + (size_t)B * nkv * nsplit * 2 * AD_HD;
-  const size_t unit0 = (((size_t)b * nkv + kvh) * nsplit) * 2 + h;
+  const int unit = blockIdx.x;
+  const int b = unit / nkv, kvh = unit % nkv;
+  const int h = threadIdx.x >> 7, d = threadIdx.x & (AD_HD - 1);
+  const int* meta = reinterpret_cast<const int*>(scratch);
+  const int ppw = meta[0];
+  const int pre = meta[1 + b], nb = meta[2 + b] - pre;
+  bf16* o = out + ((size_t)b * nq + kvh * 2 + h) * AD_HD + d;
+  if (nb <= 0) {  // empty sequence (padding row of a graph bucket)
+    *o = __float2bfloat16_rn(0.f);
+    return;
+  }
+  const int u0 = pre * nkv + kvh * nb;
+  const int w0 = u0 / ppw, w1 = (u0 + nb - 1) / ppw;
+  const float* recs = scratch + AD_META;
   float M = -INFINITY;
-  for (int s = 0; s < nsplit; ++s) M = fmaxf(M, ml[(unit0 + (size_t)s * 2) * 2]);
+  for (int w = w0; w <= w1; ++w) M = fmaxf(M, recs[(size_t)(unit + w) * AD_REC + 2 * AD_HD + h]);
   float O = 0.f, L = 0.f;
-  if (M > -INFINITY) {
-    for (int s = 0; s < nsplit; ++s) {
-      const size_t u = unit0 + (size_t)s * 2;
-      const float f = expf(ml[u * 2] - M);
-      O = fmaf(f, scratch[u * AD_HD + d], O);
-      L = fmaf(f, ml[u * 2 + 1], L);
-    }
+  for (int w = w0; w <= w1; ++w) {
+    const float* rec = recs + (size_t)(unit + w) * AD_REC;
+    const float f = expf(rec[2 * AD_HD + h] - M);
+    O = fmaf(f, rec[h * AD_HD + d], O);
+    L = fmaf(f, rec[2 * AD_HD + 2 + h], L);
   }
   const float inv = L > 0.f ? __fdiv_rn(1.0f, L) : 0.f;
-  out[((size_t)b * nq + qh) * AD_HD + d] = __float2bfloat16_rn(O * inv);
+  *o = __float2bfloat16_rn(O * inv);
 }
 
-size_t attn_decode_scratch_floats(int B, int nq, int nkv, int hd, int nsplit) {
-  if (nsplit <= 1) return 0;
-  return (size_t)B * nkv * nsplit * (nq / nkv) * (hd + 2);
+static int ad_grid() {
+  static int sms = device_num_sms();
+  return sms < AD_MAX_CTAS ? sms : AD_MAX_CTAS;
+}
+
+size_t attn_decode_scratch_floats(int B, int nq, int nkv, int hd) {
+  (void)nq;
+  (void)hd;
+  return (size_t)AD_META + ((size_t)B * nkv + (size_t)AD_MAX_CTAS * AD_WARPS) * AD_REC;
+}
+
+int launch_attn_decode_pass(const bf16* q, const bf16* k_pages, const bf16* v_pages, const int32_t* block_table,
+                            int bt_stride, const int32_t* seq_lens, float* scratch, int B, int nq, int nkv, int hd,
+                            int block_size, cudaStream_t s) {
+  if (B <= 0) return 0;
+  B2_REQUIRE(hd == AD_HD && block_size == AD_BS, "attn_decode: built for head_dim 128 / page 16 (got %d / %d)", hd, block_size);
+  B2_REQUIRE(nq == 2 * nkv, "attn_decode: built for a GQA group of 2 (nq=%d nkv=%d)", nq, nkv);
+  B2_REQUIRE(B <= AD_MAX_B, "attn_decode: batch %d > %d", B, AD_MAX_B);
+  B2_REQUIRE(scratch != nullptr, "attn_decode: scratch required");
+  static B2PerDeviceOnce attr_once;
+  if (attr_once.need()) B2_CUDA_OK(cudaFuncSetAttribute(attn_decode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AD_SMEM));
+  const float scale = (float)(1.0 / sqrt((double)hd));  // HF passes head_dim**-0.5 as a double
+  B2_CUDA_OK(b2_launch(attn_decode_kernel, dim3(ad_grid()), dim3(AD_WARPS * 32), (size_t)AD_SMEM, s, q, k_pages, v_pages,
+                       block_table, bt_stride, seq_lens, scratch, B, nq, nkv, scale));
+  return 0;
+}
+
+int launch_attn_combine(const float* scratch, bf16* out, int B, int nq, int nkv, cudaStream_t s) {
+  if (B <= 0) return 0;
+  B2_CUDA_OK(b2_launch(attn_combine_kernel, dim3(B * nkv), dim3(2 * AD_HD), 0, s, scratch, out, B, nq, nkv));
+  return 0;
 }
 
 int launch_attn_decode(const bf16* q, const bf16* k_pages, const bf16* v_pages, const int32_t* block_table,
                        int bt_stride, const int32_t* seq_lens, float* scratch, bf16* out, int B, int nq, int nkv,
-                       int hd, int block_size, int nsplit, cudaStream_t s) {
-  if (B <= 0) return 0;
-  B2_REQUIRE(hd == AD_HD && block_size == AD_BS, "attn_decode: built for head_dim 128 / page 16 (got %d / %d)", hd, block_size);
-  B2_REQUIRE(nq == 2 * nkv, "attn_decode: built for a GQA group of 2 (nq=%d nkv=%d)", nq, nkv);
-  B2_REQUIRE(nsplit >= 1 && (nsplit == 1 || scratch != nullptr), "attn_decode: nsplit=%d needs scratch", nsplit);
-  static B2PerDeviceOnce attr_once;
-  if (attr_once.need()) B2_CUDA_OK(cudaFuncSetAttribute(attn_decode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AD_SMEM));
-  dim3 grid(nsplit, nkv, B);
-  const float scale = (float)(1.0 / sqrt((double)hd));  // HF passes head_dim**-0.5 as a double
-  B2_CUDA_OK(b2_launch(attn_decode_kernel, grid, dim3(AD_WARPS * 32), (size_t)AD_SMEM, s, q, k_pages, v_pages, block_table,
-                       bt_stride, seq_lens, scratch, out, B, nq, nkv, nsplit, scale));
-  return 0;
+                       int hd, int block_size, cudaStream_t s) {
+  int rc = launch_attn_decode_pass(q, k_pages, v_pages, block_table, bt_stride, seq_lens, scratch, B, nq, nkv, hd, block_size, s);
+  if (rc != 0) return rc;
+  return launch_attn_combine(scratch, out, B, nq, nkv, s);
 }
-
-int launch_attn_combine(const float* scratch, bf16* out, int B, int nq, int nkv, int hd, int nsplit, cudaStream_t s) {
-  if (B <= 0 || nsplit <= 1) return 0;
-  B2_REQUIRE(hd == AD_HD, "attn_combine: head_dim %d not built", hd);
-  B2_CUDA_OK(b2_launch(attn_combine_kernel, dim3(B * nq), dim3(AD_HD), 0, s, scratch, out, B, nq, nkv, nsplit));
-  return 0;
-}
-
 
 // ---------------------------------------------------------------------------------------
 // Allocation-free variant of b2k_attn_decode.
@@ -287,7 +373,7 @@ int launch_attn_combine(const float* scratch, bf16* out, int B, int nq, int nkv,
 //     call delays every stream of the process, not just the caller's;
 //   * a plugin that only receives raw input/output pointers from a host framework and has no
 //     allocator of its own to ask.
-// For them the split partials live in the file-scope device array below.  It is part of the
+// For them the partial records live in the file-scope device array below.  It is part of the
 // library image: every GPU that loads libb2engine.so holds B2K_ATTN_NOALLOC_MAX_FLOATS * 4 bytes
 // (8 MiB) for it until the process exits, whether or not this entry point is ever called.
 // ---------------------------------------------------------------------------------------
@@ -322,24 +408,21 @@ int noalloc_scratch_for_current_device(float** out) {
 
 extern "C" int b2k_attn_decode_noalloc(const void* q, const void* k_pages, const void* v_pages, const int32_t* block_table,
                                        int bt_stride, const int32_t* seq_lens, void* out, int B, int nq, int nkv, int hd,
-                                       int block_size, int nsplit, void* stream) {
+                                       int block_size, void* stream) {
   using namespace b2;
   B2_REQUIRE(q && k_pages && v_pages && block_table && seq_lens && out, "b2k_attn_decode_noalloc: null pointer");
-  B2_REQUIRE(B >= 1 && nsplit >= 1 && nq >= 1 && nkv >= 1, "b2k_attn_decode_noalloc: bad sizes");
-  const size_t need = attn_decode_scratch_floats(B, nq, nkv, hd, nsplit);
+  B2_REQUIRE(B >= 1 && nq >= 1 && nkv >= 1, "b2k_attn_decode_noalloc: bad sizes");
+  const size_t need = attn_decode_scratch_floats(B, nq, nkv, hd);
   B2_REQUIRE(need <= (size_t)B2K_ATTN_NOALLOC_MAX_FLOATS,
-             "b2k_attn_decode_noalloc: batch %d x %d kv heads x %d splits needs %zu floats of scratch, the built-in array holds %d; "
-             "use fewer splits or b2k_attn_decode with your own buffer",
-             B, nkv, nsplit, need, (int)B2K_ATTN_NOALLOC_MAX_FLOATS);
+             "b2k_attn_decode_noalloc: batch %d x %d kv heads needs %zu floats of scratch, the built-in array holds %d; "
+             "use a smaller batch or b2k_attn_decode with your own buffer",
+             B, nkv, need, (int)B2K_ATTN_NOALLOC_MAX_FLOATS);
   float* scratch = nullptr;
   int rc = noalloc_scratch_for_current_device(&scratch);
   if (rc != 0) return rc;
-  cudaStream_t s = (cudaStream_t)stream;
-  // Nothing in the array has to start at zero: every slot the combine pass reads is written by the
-  // attention pass of the same call first, so what an earlier call left behind is never observed.
-  rc = launch_attn_decode((const bf16*)q, (const bf16*)k_pages, (const bf16*)v_pages, block_table, bt_stride, seq_lens, scratch,
-                          (bf16*)out, B, nq, nkv, hd, block_size, nsplit, s);
-  if (rc != 0) return rc;
-  if (nsplit > 1) rc = launch_attn_combine(scratch, (bf16*)out, B, nq, nkv, hd, nsplit, s);
-  return rc;
+  // Nothing in the array has to start at zero: every record and every geometry word the combine pass
+  // reads is written by the attention pass of the same call first, so what an earlier call left
+  // behind is never observed.
+  return launch_attn_decode((const bf16*)q, (const bf16*)k_pages, (const bf16*)v_pages, block_table, bt_stride, seq_lens, scratch,
+                            (bf16*)out, B, nq, nkv, hd, block_size, (cudaStream_t)stream);
 }

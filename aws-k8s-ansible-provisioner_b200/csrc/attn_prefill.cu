@@ -63,9 +63,12 @@ attn_prefill_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k_pages
     const uint32_t kdst = smem0 + buf * 2 * AP_TILE_BYTES;
     const uint32_t vdst = kdst + AP_TILE_BYTES;
     for (int idx = threadIdx.x; idx < AP_BN * 16; idx += 128) {
+      // c = PHYSICAL chunk position.  Pages are stored chunk-swizzled by (row & 7) (kv_swizzled_chunk),
+      // and tiles start at multiples of 16 tokens, so (key & 7) == (row in page & 7): the page's own
+      // swizzle is exactly the one the ldmatrix reads below expect -- a straight 16-byte copy.
       const int key = idx >> 4, c = idx & 15;
       const int kpos = j * AP_BN + key;
-      const uint32_t o = key * (AP_HD * 2) + ((c ^ (key & 7)) << 4);
+      const uint32_t o = key * (AP_HD * 2) + (c << 4);
       if (kpos < kv_len) {
         const int blk = bt[kpos / block_size];
         const size_t src = (((size_t)blk * nkv + kvh) * block_size + (kpos % block_size)) * AP_HD + c * 8;

@@ -86,19 +86,16 @@ extern "C" int b2k_lmhead_argmax(const void* x, const void* w, void* logits, int
   return launch_argmax_finalize((const unsigned long long*)scratch_u64, out_tokens, T, s);
 }
 
-extern "C" size_t b2k_attn_decode_scratch_floats(int B, int nq, int nkv, int hd, int nsplit) {
-  return attn_decode_scratch_floats(B, nq, nkv, hd, nsplit);
+extern "C" size_t b2k_attn_decode_scratch_floats(int B, int nq, int nkv, int hd) {
+  return attn_decode_scratch_floats(B, nq, nkv, hd);
 }
 
 extern "C" int b2k_attn_decode(const void* q, const void* k_pages, const void* v_pages, const int32_t* block_table, int bt_stride,
                                const int32_t* seq_lens, void* scratch_f32, void* out, int B, int nq, int nkv, int hd,
-                               int block_size, int nsplit, void* stream) {
-  B2_REQUIRE(q && k_pages && v_pages && block_table && seq_lens && out, "b2k_attn_decode: null pointer");
-  cudaStream_t s = (cudaStream_t)stream;
-  CAPI_TRY(launch_attn_decode((const bf16*)q, (const bf16*)k_pages, (const bf16*)v_pages, block_table, bt_stride, seq_lens,
-                              (float*)scratch_f32, (bf16*)out, B, nq, nkv, hd, block_size, nsplit, s));
-  if (nsplit > 1) CAPI_TRY(launch_attn_combine((const float*)scratch_f32, (bf16*)out, B, nq, nkv, hd, nsplit, s));
-  return 0;
+                               int block_size, void* stream) {
+  B2_REQUIRE(q && k_pages && v_pages && block_table && seq_lens && out && scratch_f32, "b2k_attn_decode: null pointer");
+  return launch_attn_decode((const bf16*)q, (const bf16*)k_pages, (const bf16*)v_pages, block_table, bt_stride, seq_lens,
+                            (float*)scratch_f32, (bf16*)out, B, nq, nkv, hd, block_size, (cudaStream_t)stream);
 }
 
 extern "C" int b2k_attn_prefill(const void* q, const void* k_pages, const void* v_pages, const int32_t* block_table_dev,

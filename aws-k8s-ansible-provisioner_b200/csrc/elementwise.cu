@@ -204,7 +204,9 @@ __global__ void qknorm_rope_kv_kernel(const void* __restrict__ qkv, int nsplit, 
     const int kvh = is_k ? head - nq : head - nq - nkv;
     const int blk = slot / block_size, off = slot % block_size;
     bf16* base = is_k ? k_pages : v_pages;
-    *reinterpret_cast<uint2*>(base + (((size_t)blk * nkv + kvh) * block_size + off) * HD + lane * 4) = o;
+    // lane l holds dims 4l..4l+3 = half of 16-byte chunk l/2; pages are stored chunk-swizzled
+    const int chunk = kv_swizzled_chunk(off, lane >> 1);
+    *reinterpret_cast<uint2*>(base + (((size_t)blk * nkv + kvh) * block_size + off) * HD + chunk * 8 + (lane & 1) * 4) = o;
   }
 }
 

@@ -203,19 +203,10 @@ int bucket_batch(int B) {
 }
 
 int pick_attn_split(b2_engine* e, int B, int max_len) {
-  if (e->attn_split_override > 0) return e->attn_split_override;
-  const int units = B * e->cfg.num_kv_heads;
-  const int blocks = (max_len + e->cfg.block_size - 1) / e->cfg.block_size;
-  // Measured on B200 (batch 64, context ~580, attention alone): 1 split 0.92 ms/step, 2 splits 0.99,
-  // 4 splits 1.10, 8 splits 1.46 -- per-CTA start-up and the merge dominate short chunks, so split
-  // only as far as needed to give every SM two CTAs.
-  int want = (2 * e->num_sms + units - 1) / units;
-  int cap = std::max(1, blocks / 8);                // keep >= 8 pages (2 per warp) per CTA
-  int ns = std::max(1, std::min(want, cap));
-  // quantise so only a handful of graphs exist
-  int q = 1;
-  while (q * 2 <= ns && q < 16) q *= 2;
-  return q;
+  // The decode-attention kernel balances pages over its persistent warps by itself; there is no
+  // host-side split factor any more (kept as a constant component of the graph key).
+  (void)e; (void)B; (void)max_len;
+  return 1;
 }
 
 // ---- one Linear layer: picks SIMT GEMV or the tcgen05 kernel, bf16 or split-K partial output
@@ -297,14 +288,13 @@ int forward(b2_engine* e, int T, int ntiles, int nlast, int attn_split) {
     } else {
       {
         KL k(e, B2K_ATTN_DECODE);
-        if (!k.skip()) B2_TRY(launch_attn_decode(e->qrot, kp, vp, e->d_block_table, e->bt_stride, e->d_seq_lens, e->attn_scratch,
-                                  e->attn, T, c.num_q_heads, c.num_kv_heads, c.head_dim, c.block_size, attn_split,
-                                  e->stream));
+        if (!k.skip())
+          B2_TRY(launch_attn_decode_pass(e->qrot, kp, vp, e->d_block_table, e->bt_stride, e->d_seq_lens, e->attn_scratch, T,
+                                         c.num_q_heads, c.num_kv_heads, c.head_dim, c.block_size, e->stream));
       }
-      if (attn_split > 1) {
+      {
         KL k(e, B2K_ATTN_COMBINE);
-        if (!k.skip()) B2_TRY(launch_attn_combine(e->attn_scratch, e->attn, T, c.num_q_heads, c.num_kv_heads, c.head_dim, attn_split,
-                                   e->stream));
+        if (!k.skip()) B2_TRY(launch_attn_combine(e->attn_scratch, e->attn, T, c.num_q_heads, c.num_kv_heads, e->stream));
       }
     }
     ActIn o = linear(e, B2K_GEMM_O, XB_ATTN, e->attn, L.wo, L.tm_o, e->proj, T, H, e->q_size, &rc);
@@ -731,7 +721,7 @@ extern "C" int b2_engine_create(const b2_config* cfg, const char* safetensors_pa
     E_CUDA(cudaMemset(e->xlast, 0, last_rows * H * 2));
     e->partial_floats = (size_t)16 << 20;  // 64 MB of fp32 split-K partials
     E_TRY(dalloc(&e->partial, e->partial_floats));
-    e->attn_scratch_floats = attn_decode_scratch_floats(bucket_batch(c.max_seqs), c.num_q_heads, c.num_kv_heads, c.head_dim, 16);
+    e->attn_scratch_floats = attn_decode_scratch_floats(bucket_batch(c.max_seqs), c.num_q_heads, c.num_kv_heads, c.head_dim);
     E_TRY(dalloc(&e->attn_scratch, e->attn_scratch_floats));
     for (int bi = 0; bi < 5; ++bi) {
       E_TRY(b2_make_tmap_bf16(&e->tm_x[XB_X][bi], e->x, Tc, H, H, kBnList[bi]));

@@ -53,11 +53,19 @@ int tc_pick_bn(int T);
 int tc_pick_nsplit(int T, int N, int K, int num_sms);
 
 // ---- attn_decode.cu ----
-size_t attn_decode_scratch_floats(int B, int nq, int nkv, int hd, int nsplit);
+// KV page-slice layout ([16 tokens][128 dims] bf16 = 4 KB per (page, kv head)): the 16-byte chunk c
+// (8 dims) of token row r is stored at chunk position c ^ (r & 7).  Every kernel that touches the
+// pages goes through this one function.
+__host__ __device__ inline int kv_swizzled_chunk(int row_in_page, int chunk) { return chunk ^ (row_in_page & 7); }
+size_t attn_decode_scratch_floats(int B, int nq, int nkv, int hd);
+int launch_attn_decode_pass(const bf16* q, const bf16* k_pages, const bf16* v_pages, const int32_t* block_table,
+                            int bt_stride, const int32_t* seq_lens, float* scratch, int B, int nq, int nkv, int hd,
+                            int block_size, cudaStream_t s);
+int launch_attn_combine(const float* scratch, bf16* out, int B, int nq, int nkv, cudaStream_t s);
+// attention pass + combine pass (two launches)
 int launch_attn_decode(const bf16* q, const bf16* k_pages, const bf16* v_pages, const int32_t* block_table,
                        int bt_stride, const int32_t* seq_lens, float* scratch, bf16* out, int B, int nq, int nkv,
-                       int hd, int block_size, int nsplit, cudaStream_t s);
-int launch_attn_combine(const float* scratch, bf16* out, int B, int nq, int nkv, int hd, int nsplit, cudaStream_t s);
+                       int hd, int block_size, cudaStream_t s);
 
 // ---- attn_prefill.cu ----
 struct PrefillTile {  // one 64-query tile of one sequence

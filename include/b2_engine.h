@@ -146,7 +146,7 @@ int b2k_add_rmsnorm(void* h_bf16, const void* delta, int delta_is_f32, int nspli
 /* HF:...:248-249,263-264 (QK-norm), :151-181 (RoPE), :270-271 (cache write).
  * qkv [T][(nq+2nkv)*hd] bf16 (or fp32 partials), positions/slots [T] int32,
  * cos_sin [max_pos][hd] bf16 = cos[hd/2] | sin[hd/2].  Writes q_out [T][nq*hd] and the K/V
- * pages ([block][nkv][block_size][hd]). */
+ * pages (layout: see "KV page layout" below). */
 int b2k_qknorm_rope_kv(const void* qkv, int qkv_is_f32, int nsplit, const void* qnorm_w,
                        const void* knorm_w, const void* cos_sin, const int32_t* positions,
                        const int32_t* slots, void* q_out, void* k_pages, void* v_pages, int T,
@@ -167,24 +167,29 @@ int b2k_lmhead_argmax(const void* x_bf16, const void* w_bf16, void* logits_bf16,
                       int32_t* out_tokens, void* scratch_u64, int T, int V, int K, int impl,
                       void* stream);
 
-/* HF:integrations/sdpa_attention.py:40-104 at T == 1: paged GQA decode attention, split-K.
- * q [B][nq*hd]; pages as above; block_table [B][bt_stride]; seq_lens [B] (including the
- * current token).  scratch_f32: >= B*nkv*nsplit*(nq/nkv)*(hd+2) floats (ignored if
- * nsplit == 1).  out [B][nq*hd] bf16. */
+/* KV page layout shared by every kernel below: one allocation per layer and per K/V,
+ * [page][kv_head][block_size = 16 tokens][head_dim = 128] bf16, i.e. a 4 KB slice per (page, kv head),
+ * in which the 16-byte chunk c (8 dims) of token row r sits at chunk position c ^ (r & 7).
+ * b2k_qknorm_rope_kv writes that layout; the two attention entry points read it. */
+
+/* HF:integrations/sdpa_attention.py:40-104 at T == 1: paged GQA decode attention.
+ * q [B][nq*hd]; pages as above; block_table [B][bt_stride]; seq_lens [B] (including the current
+ * token; 0 = empty row, output zeros).  scratch_f32: b2k_attn_decode_scratch_floats(...) floats of
+ * device memory for the partial records of the page-balanced attention pass.  out [B][nq*hd] bf16. */
 int b2k_attn_decode(const void* q, const void* k_pages, const void* v_pages,
                     const int32_t* block_table, int bt_stride, const int32_t* seq_lens,
                     void* scratch_f32, void* out, int B, int nq, int nkv, int hd, int block_size,
-                    int nsplit, void* stream);
-size_t b2k_attn_decode_scratch_floats(int B, int nq, int nkv, int hd, int nsplit);
+                    void* stream);
+size_t b2k_attn_decode_scratch_floats(int B, int nq, int nkv, int hd);
 
 /* No counterpart in the reference (it has no kernels at all).  Same computation and arguments as
  * b2k_attn_decode, minus scratch_f32: for callers that cannot allocate device memory -- a server
  * whose KV pool already owns the free HBM, request-path code that cannot afford the device-wide
  * synchronisation of cudaMalloc/cudaFree, a plugin that is only handed input/output pointers.  The
- * split partials go to an array compiled into the library (B2K_ATTN_NOALLOC_MAX_FLOATS floats =
+ * partial records go to an array compiled into the library (B2K_ATTN_NOALLOC_MAX_FLOATS floats =
  * 8 MiB, resident on every GPU that loads the library until the process exits).  The call allocates
- * and frees nothing.  It fails with a message if b2k_attn_decode_scratch_floats(B, nq, nkv, hd,
- * nsplit) exceeds that size (nsplit == 1 needs none and always fits).
+ * and frees nothing.  It fails with a message if b2k_attn_decode_scratch_floats(B, nq, nkv, hd)
+ * exceeds that size (B * nkv up to about 6 700 units fits).
  * The first call on each device looks up the array's device address (that device must be current)
  * and caches it; make that first call before starting any stream capture.
  * All calls share the one array and it keeps whatever the last call wrote; nothing in it needs to be
@@ -193,8 +198,7 @@ size_t b2k_attn_decode_scratch_floats(int B, int nq, int nkv, int hd, int nsplit
 #define B2K_ATTN_NOALLOC_MAX_FLOATS (2 * 1024 * 1024)
 int b2k_attn_decode_noalloc(const void* q, const void* k_pages, const void* v_pages,
                             const int32_t* block_table, int bt_stride, const int32_t* seq_lens,
-                            void* out, int B, int nq, int nkv, int hd, int block_size, int nsplit,
-                            void* stream);
+                            void* out, int B, int nq, int nkv, int hd, int block_size, void* stream);
 
 /* Same contract at T > 1 (causal): ragged prefill over the paged cache.  q [T][nq*hd];
  * q_seq[T] / q_pos[T] int32 give the sequence row in block_table and the position of each

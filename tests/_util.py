@@ -74,3 +74,15 @@ def engine_config_from_arch(p, arch, **kw):
     for k, v in kw.items():
         setattr(cfg, k, v)
     return cfg
+
+
+def kv_swizzle(pages: torch.Tensor) -> torch.Tensor:
+    """Logical [..., 16 tokens, 128 dims] -> the stored page layout of include/b2_engine.h: the 16-byte
+    chunk c of token row r sits at chunk position c ^ (r & 7).  The permutation is its own inverse."""
+    shp = pages.shape
+    x = pages.reshape(-1, 16, 16, 8)  # [slice][row][chunk][8 dims]
+    r = torch.arange(16)[:, None]
+    c = torch.arange(16)[None, :]
+    src = c ^ (r & 7)                  # stored[r][c] = logical[r][c ^ (r & 7)]
+    out = torch.gather(x, 2, src[None, :, :, None].expand(x.shape[0], 16, 16, 8))
+    return out.reshape(shp)
