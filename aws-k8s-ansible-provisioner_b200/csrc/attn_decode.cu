@@ -35,7 +35,7 @@ constexpr int AD_STAGE = 2 * AD_TILE;            // K + V
 constexpr int AD_SMEM = AD_WARPS * AD_STAGES * AD_STAGE;  // 192 KB
 constexpr int AD_MAX_B = 512;
 constexpr int AD_MAX_CTAS = 160;
-constexpr int AD_META = 1024;                    // ints at the head of the scratch: [0]=pages per warp, [1..B+1]=page prefix
+constexpr int AD_META = 1024;                    // ints at the head of the scratch: [0]=pages per warp (base), [599]=warps with one extra, [1..B+1]=page prefix
 constexpr int AD_REC = 2 * AD_HD + 4;            // floats per partial record: O[2][128], m[2], l[2]
 
 __device__ __forceinline__ void ad_ldsm_x4(uint32_t addr, uint32_t* r) {
@@ -101,17 +101,24 @@ attn_decode_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k_pages,
   }
   __syncthreads();
   const int total_pages = s_prefix[B] * nkv;  // length of the page line
+  // balanced partition of the page line: the first `rem` warps take base+1 pages, the rest base
   const int wtot = gridDim.x * AD_WARPS;
-  const int ppw = max(1, (total_pages + wtot - 1) / wtot);
+  const int base = total_pages / wtot, rem = total_pages - base * wtot;
+  unsigned long long t_start = 0;
+  if (threadIdx.x == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_start));
   if (blockIdx.x == 0) {  // publish the geometry for the combine pass
     int* meta = reinterpret_cast<int*>(scratch);
-    if (threadIdx.x == 0) meta[0] = ppw;
+    if (threadIdx.x == 0) {
+      meta[0] = base;
+      meta[599] = rem;
+    }
     for (int i = threadIdx.x; i <= B; i += blockDim.x) meta[1 + i] = s_prefix[i];
   }
   const int gw = blockIdx.x * AD_WARPS + warp;
-  const int p0 = min(total_pages, gw * ppw), p1 = min(total_pages, p0 + ppw);
-  const int ntiles = p1 - p0;
+  const int p0 = gw * base + min(gw, rem);
+  const int ntiles = base + (gw < rem ? 1 : 0);
   if (ntiles <= 0) return;
+  const bool dbg_time = (warp == 0 && lane == 0);
 
   auto locate = [&](int p) -> AdPos {  // page-line position -> (sequence, kv head, page in sequence)
     int lo = 0, hi = B - 1;
@@ -288,6 +295,13 @@ attn_decode_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k_pages,
       fresh = true;
     }
   }
+  if (dbg_time) {  // timing breadcrumbs for tools/attn_timeline.py (unused words of the geometry header)
+    unsigned long long t_end;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_end));
+    int* meta = reinterpret_cast<int*>(scratch);
+    meta[600 + 2 * blockIdx.x] = (int)(t_start & 0x7fffffff);
+    meta[601 + 2 * blockIdx.x] = (int)(t_end & 0x7fffffff);
+  }
 }
 
 // One CTA per (sequence, kv head) unit, thread = (head, dim): merges the unit's records in run order.
@@ -299,7 +313,7 @@ attn_combine_kernel(const float* __restrict__ scratch, bf16* __restrict__ out, i
   const int b = unit / nkv, kvh = unit % nkv;
   const int h = threadIdx.x >> 7, d = threadIdx.x & (AD_HD - 1);
   const int* meta = reinterpret_cast<const int*>(scratch);
-  const int ppw = meta[0];
+  const int base = meta[0], rem = meta[599];
   const int pre = meta[1 + b], nb = meta[2 + b] - pre;
   bf16* o = out + ((size_t)b * nq + kvh * 2 + h) * AD_HD + d;
   if (nb <= 0) {  // empty sequence (padding row of a graph bucket)
@@ -307,7 +321,12 @@ attn_combine_kernel(const float* __restrict__ scratch, bf16* __restrict__ out, i
     return;
   }
   const int u0 = pre * nkv + kvh * nb;
-  const int w0 = u0 / ppw, w1 = (u0 + nb - 1) / ppw;
+  // inverse of the attention pass's partition: which warp's run holds page-line position p
+  auto warp_of = [&](int p) -> int {
+    const int cut = rem * (base + 1);
+    return p < cut ? p / (base + 1) : rem + (p - cut) / base;  // base > 0 whenever p >= cut exists
+  };
+  const int w0 = warp_of(u0), w1 = warp_of(u0 + nb - 1);
   const float* recs = scratch + AD_META;
   float M = -INFINITY;
   for (int w = w0; w <= w1; ++w) M = fmaxf(M, recs[(size_t)(unit + w) * AD_REC + 2 * AD_HD + h]);

@@ -343,27 +343,42 @@ int launch_argmax_finalize(const unsigned long long* packed, int32_t* out, int T
 // decode bookkeeping: one thread per sequence of the running batch.
 // ---------------------------------------------------------------------------------------
 __global__ void decode_advance_kernel(int32_t* positions, int32_t* seq_lens, int32_t* slots,
-                                      const int32_t* __restrict__ block_table, int bt_stride, int block_size, int B) {
+                                      const int32_t* __restrict__ block_table, int bt_stride, int block_size, int B,
+                                      int32_t* frac_q16, long long l2_budget_bytes, long long bytes_per_page_all_heads) {
+  __shared__ int total_pages;
   pdl_launch_dependents();
   pdl_wait();
-  int b = blockIdx.x * blockDim.x + threadIdx.x;
-  if (b >= B) return;
-  if (positions[b] < -1) {  // padding row of a graph bucket
-    seq_lens[b] = 0;
-    slots[b] = -1;
-    return;
+  if (threadIdx.x == 0) total_pages = 0;
+  __syncthreads();
+  int my_pages = 0;
+  for (int b = threadIdx.x; b < B; b += blockDim.x) {  // single CTA
+    if (positions[b] < -1) {  // padding row of a graph bucket
+      seq_lens[b] = 0;
+      slots[b] = -1;
+      continue;
+    }
+    int pos = positions[b] + 1;
+    positions[b] = pos;
+    seq_lens[b] = pos + 1;
+    int blk = block_table[(size_t)b * bt_stride + pos / block_size];
+    slots[b] = blk * block_size + pos % block_size;
+    my_pages += (pos + block_size) / block_size;
   }
-  int pos = positions[b] + 1;
-  positions[b] = pos;
-  seq_lens[b] = pos + 1;
-  int blk = block_table[(size_t)b * bt_stride + pos / block_size];
-  slots[b] = blk * block_size + pos % block_size;
+  if (my_pages) atomicAdd(&total_pages, my_pages);
+  __syncthreads();
+  if (threadIdx.x == 0 && frac_q16 != nullptr) {
+    // share of one layer's K/V pages that fits the L2 budget, for the ride-along prefetch
+    const long long bytes = (long long)total_pages * bytes_per_page_all_heads;
+    long long f = bytes > 0 ? (l2_budget_bytes << 16) / bytes : 65536;
+    *frac_q16 = (int32_t)(f > 65536 ? 65536 : f);
+  }
 }
 int launch_decode_advance(int32_t* positions, int32_t* seq_lens, int32_t* slots, const int32_t* block_table,
-                          int bt_stride, int block_size, int B, cudaStream_t s) {
+                          int bt_stride, int block_size, int B, int32_t* frac_q16, long long l2_budget_bytes,
+                          long long bytes_per_page_all_heads, cudaStream_t s) {
   if (B <= 0) return 0;
-  B2_CUDA_OK(b2_launch(decode_advance_kernel, dim3((B + 127) / 128), dim3(128), 0, s, positions, seq_lens, slots, block_table,
-                       bt_stride, block_size, B));
+  B2_CUDA_OK(b2_launch(decode_advance_kernel, dim3(1), dim3(256), 0, s, positions, seq_lens, slots, block_table, bt_stride,
+                       block_size, B, frac_q16, l2_budget_bytes, bytes_per_page_all_heads));
   return 0;
 }
 

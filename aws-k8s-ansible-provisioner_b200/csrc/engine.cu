@@ -145,7 +145,9 @@ struct b2_engine {
   int simt_max_tokens = 0;  // T <= this -> SIMT GEMV path
   int attn_split_override = 0;
   int force_gemm_impl = -1;
-  unsigned skip_mask = 0;  // B2_SKIP_MASK: kernel classes left out (timing ablations only; results are garbage)
+  unsigned skip_mask = 0;
+  long long kv_l2_budget = 0;      // B2_KV_L2_MB: bytes of next-layer K/V the projections prefetch into L2 (0 = off)
+  int32_t* d_pf_frac = nullptr;  // B2_SKIP_MASK: kernel classes left out (timing ablations only; results are garbage)
 };
 
 namespace {
@@ -211,7 +213,7 @@ int pick_attn_split(b2_engine* e, int B, int max_len) {
 
 // ---- one Linear layer: picks SIMT GEMV or the tcgen05 kernel, bf16 or split-K partial output
 ActIn linear(b2_engine* e, int cls, XBuf xb, const bf16* xptr, const bf16* w, const CUtensorMap& tm_w, bf16* out_bf16, int T,
-             int N, int K, int* rc) {
+             int N, int K, int* rc, const KvPrefetch& pf = KvPrefetch()) {
   *rc = 0;
   int impl = e->force_gemm_impl >= 0 ? e->force_gemm_impl : (T <= e->simt_max_tokens ? 0 : 1);
   if (impl == 0) {
@@ -225,6 +227,7 @@ ActIn linear(b2_engine* e, int cls, XBuf xb, const bf16* xptr, const bf16* w, co
   a.tmap_x = e->tm_x[xb][bn_index(a.bn)];
   a.T = T; a.N = N; a.K = K;
   a.argmax_packed = nullptr;
+  a.prefetch = pf;
   int ns = tc_pick_nsplit(T, N, K, e->num_sms);
   while (ns > 1 && (size_t)ns * T * N > e->partial_floats) --ns;
   if (ns > 1) {  // re-validate (every split non-empty)
@@ -265,6 +268,23 @@ int forward(b2_engine* e, int T, int ntiles, int nlast, int attn_split) {
   }
   dbg_capture(e, 0, e->h, T);
   ActIn delta = act_bf16(nullptr);
+  // decode only: the projections of layer l prefetch shares of the K/V pages the next attention pass
+  // will read (QKV: this layer's own; O, gate-up, down: layer l+1's)
+  auto prefetch_for = [&](int layer, int part) -> KvPrefetch {
+    KvPrefetch pf;
+    if (ntiles > 0 || e->kv_l2_budget <= 0 || layer >= c.num_layers) return pf;
+    pf.k_pages = e->kv_pool + (size_t)(2 * layer) * e->layer_kv_elems;
+    pf.v_pages = pf.k_pages + e->layer_kv_elems;
+    pf.block_table = e->d_block_table;
+    pf.seq_lens = e->d_seq_lens;
+    pf.frac_q16 = e->d_pf_frac;
+    pf.bt_stride = e->bt_stride;
+    pf.B = T;
+    pf.nkv = c.num_kv_heads;
+    pf.part = part;
+    pf.nparts = 4;
+    return pf;
+  };
   for (int l = 0; l < c.num_layers; ++l) {
     LayerW& L = e->layers[l];
     bf16* kp = e->kv_pool + (size_t)(2 * l) * e->layer_kv_elems;
@@ -274,7 +294,7 @@ int forward(b2_engine* e, int T, int ntiles, int nlast, int attn_split) {
       if (!k.skip()) B2_TRY(launch_add_rmsnorm(e->h, delta, L.ln1, e->x, T, H, c.rms_eps, e->stream));
     }
     if (l > 0) dbg_capture(e, l, e->h, T);
-    ActIn qkv = linear(e, B2K_GEMM_QKV, XB_X, e->x, L.wqkv, L.tm_qkv, e->qkv, T, e->qkv_size, H, &rc);
+    ActIn qkv = linear(e, B2K_GEMM_QKV, XB_X, e->x, L.wqkv, L.tm_qkv, e->qkv, T, e->qkv_size, H, &rc, prefetch_for(l, 3));
     B2_TRY(rc);
     {
       KL k(e, B2K_ROPE_KV);
@@ -297,19 +317,19 @@ int forward(b2_engine* e, int T, int ntiles, int nlast, int attn_split) {
         if (!k.skip()) B2_TRY(launch_attn_combine(e->attn_scratch, e->attn, T, c.num_q_heads, c.num_kv_heads, e->stream));
       }
     }
-    ActIn o = linear(e, B2K_GEMM_O, XB_ATTN, e->attn, L.wo, L.tm_o, e->proj, T, H, e->q_size, &rc);
+    ActIn o = linear(e, B2K_GEMM_O, XB_ATTN, e->attn, L.wo, L.tm_o, e->proj, T, H, e->q_size, &rc, prefetch_for(l + 1, 0));
     B2_TRY(rc);
     {
       KL k(e, B2K_NORM);
       if (!k.skip()) B2_TRY(launch_add_rmsnorm(e->h, o, L.ln2, e->x, T, H, c.rms_eps, e->stream));
     }
-    ActIn gu = linear(e, B2K_GEMM_GATEUP, XB_X, e->x, L.wgu, L.tm_gu, e->gu, T, 2 * I, H, &rc);
+    ActIn gu = linear(e, B2K_GEMM_GATEUP, XB_X, e->x, L.wgu, L.tm_gu, e->gu, T, 2 * I, H, &rc, prefetch_for(l + 1, 1));
     B2_TRY(rc);
     {
       KL k(e, B2K_ACT);
       if (!k.skip()) B2_TRY(launch_silu_mul(gu, e->act, T, I, e->stream));
     }
-    delta = linear(e, B2K_GEMM_DOWN, XB_ACT, e->act, L.wd, L.tm_d, e->proj, T, H, I, &rc);
+    delta = linear(e, B2K_GEMM_DOWN, XB_ACT, e->act, L.wd, L.tm_d, e->proj, T, H, I, &rc, prefetch_for(l + 1, 2));
     B2_TRY(rc);
   }
   {
@@ -379,7 +399,8 @@ int decode_body(b2_engine* e, int B, int attn_split) {
   {
     KL k(e, B2K_MISC);
     if (!k.skip()) B2_TRY(launch_decode_advance(e->d_positions, e->d_seq_lens, e->d_slots, e->d_block_table, e->bt_stride,
-                                 e->cfg.block_size, B, e->stream));
+                                 e->cfg.block_size, B, e->d_pf_frac, e->kv_l2_budget,
+                                 (long long)e->cfg.num_kv_heads * e->cfg.block_size * e->cfg.head_dim * 2 * 2, e->stream));
   }
   B2_TRY(forward(e, B, 0, B, attn_split));
   {
@@ -641,6 +662,7 @@ extern "C" int b2_engine_create(const b2_config* cfg, const char* safetensors_pa
   e->attn_split_override = env_int("B2_ATTN_SPLITS", 0);
   e->force_gemm_impl = env_int("B2_GEMM_IMPL", -1);
   e->skip_mask = (unsigned)env_int("B2_SKIP_MASK", 0);
+  e->kv_l2_budget = (long long)env_int("B2_KV_L2_MB", 72) << 20;
   const int H = c.hidden, I = c.intermediate;
   int rc = 0;
 #define E_TRY(expr)        \
@@ -748,6 +770,8 @@ extern "C" int b2_engine_create(const b2_config* cfg, const char* safetensors_pa
     E_TRY(dalloc(&e->d_out_tokens, Bcap));
     E_TRY(dalloc(&e->d_argmax, Bcap));
     E_TRY(dalloc(&e->d_step, (size_t)1));
+    E_TRY(dalloc(&e->d_pf_frac, (size_t)1));
+    E_CUDA(cudaMemset(e->d_pf_frac, 0, 4));
     e->log_cap_steps = 4096;
     E_TRY(dalloc(&e->d_token_log, (size_t)e->log_cap_steps * c.max_seqs));
     E_CUDA(cudaMemset(e->d_step, 0, 4));
@@ -839,7 +863,7 @@ extern "C" void b2_engine_free(b2_engine* e) {
   }
   F(e->kv_pool); F(e->h); F(e->x); F(e->qkv); F(e->qrot); F(e->attn); F(e->gu); F(e->act); F(e->proj); F(e->xlast);
   F(e->partial); F(e->attn_scratch); F(e->d_tokens); F(e->d_positions); F(e->d_seq_lens); F(e->d_slots);
-  F(e->d_block_table); F(e->d_last_rows); F(e->d_out_tokens); F(e->d_token_log); F(e->d_step); F(e->d_argmax);
+  F(e->d_block_table); F(e->d_last_rows); F(e->d_out_tokens); F(e->d_token_log); F(e->d_step); F(e->d_argmax); F(e->d_pf_frac);
   F(e->d_tiles); F(e->dbg_hidden); F(e->logits);
   if (e->h_stage) cudaFreeHost(e->h_stage);
   if (e->h_tiles) cudaFreeHost(e->h_tiles);

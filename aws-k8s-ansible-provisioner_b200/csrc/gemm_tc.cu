@@ -46,7 +46,7 @@ template <int BN, int EPI>
 __global__ void __launch_bounds__(192, 1)
 linear_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_x,
                  void* __restrict__ out, unsigned long long* __restrict__ argmax_packed, int T, int N, int K,
-                 int kb_per_split, int m_tiles, int n_tiles, int nsplit) {
+                 int kb_per_split, int m_tiles, int n_tiles, int nsplit, const KvPrefetch pf) {
   using C = TcCfg<BN>;
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t full_bar[C::STAGES];
@@ -164,7 +164,25 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
     }
   } else {
     const int q = warp & 3;  // TMEM lane quarter this warp may access
-    pdl_wait();              // (returns at once: the accumulator cannot be ready before X arrived)
+    pdl_wait();
+    if (pf.k_pages != nullptr) {
+      // These four warps idle until the first accumulator is ready: spend the time asking the TMA
+      // engine to pull this launch's share of the next attention pass's K/V pages into L2.
+      const int frac = *pf.frac_q16;
+      const long long items = (long long)pf.B * pf.bt_stride * pf.nkv;
+      const long long step = (long long)gridDim.x * 128 * pf.nparts;
+      for (long long it = ((long long)blockIdx.x * 128 + (threadIdx.x - 64)) * pf.nparts + pf.part; it < items; it += step) {
+        const int kvh = (int)(it % pf.nkv);
+        const int j = (int)((it / pf.nkv) % pf.bt_stride);
+        const int b = (int)(it / ((long long)pf.nkv * pf.bt_stride));
+        const int nb = (pf.seq_lens[b] + 15) >> 4;
+        if (j < (int)(((long long)nb * frac + 65535) >> 16)) {
+          const size_t off = ((size_t)pf.block_table[(size_t)b * pf.bt_stride + j] * pf.nkv + kvh) * (16 * 128);
+          asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(pf.k_pages + off), "r"(4096) : "memory");
+          asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(pf.v_pages + off), "r"(4096) : "memory");
+        }
+      }
+    }
     int lt = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
       const int m_tile = tile % m_tiles;
@@ -298,7 +316,7 @@ static int launch_one(const TcGemmArgs& a, int kb_per_split, cudaStream_t s) {
   static int sms = device_num_sms();
   const int grid = total < sms ? total : sms;
   B2_CUDA_OK(b2_launch(linear_tc_kernel<BN, EPI>, dim3(grid), dim3(192), (size_t)C::SMEM_BYTES, s, a.tmap_w, a.tmap_x, a.out,
-                       a.argmax_packed, a.T, a.N, a.K, kb_per_split, m_tiles, n_tiles, a.nsplit));
+                       a.argmax_packed, a.T, a.N, a.K, kb_per_split, m_tiles, n_tiles, a.nsplit, a.prefetch));
   return 0;
 }
 

@@ -28,12 +28,27 @@ int launch_argmax_finalize(const unsigned long long* packed, int32_t* out, int T
 // decode bookkeeping on the device: positions/seq_lens += 1, slots from the block table, and
 // the tokens produced by the previous step become this step's input ids.
 int launch_decode_advance(int32_t* positions, int32_t* seq_lens, int32_t* slots, const int32_t* block_table,
-                          int bt_stride, int block_size, int B, cudaStream_t s);
+                          int bt_stride, int block_size, int B, int32_t* frac_q16, long long l2_budget_bytes,
+                          long long bytes_per_page_all_heads, cudaStream_t s);
 int launch_logits_to_f32(const bf16* in, float* out, size_t n, cudaStream_t s);
 
 // ---- gemm_simt.cu ----
 // out = x[T][K] . w[N][K]^T ; bf16 out [T][N] or fp32 [T][N] (single split).
 int launch_linear_simt(const bf16* x, const bf16* w, void* out, int out_is_f32, int T, int N, int K, cudaStream_t s);
+
+// Ride-along L2 prefetch of the next attention pass's K/V pages.  The projection kernels are
+// latency-bound and leave HBM idle, and B200's L2 (126 MB) holds a good part of one layer's pages,
+// so each projection asks the TMA engine to pull a share of them into L2 while it waits for its own
+// operands (cp.async.bulk.prefetch.L2; no SM resources, no completion to wait for).
+struct KvPrefetch {
+  const bf16* k_pages = nullptr;   // target layer's pools (null = no prefetch)
+  const bf16* v_pages = nullptr;
+  const int32_t* block_table = nullptr;
+  const int32_t* seq_lens = nullptr;
+  const int32_t* frac_q16 = nullptr;  // device: share of every sequence's pages to pull, in 1/65536
+  int bt_stride = 0, B = 0, nkv = 0;
+  int part = 0, nparts = 1;           // this launch takes items with (index % nparts == part)
+};
 
 // ---- gemm_tc.cu ----
 enum TcEpilogue { TC_EPI_BF16 = 0, TC_EPI_F32_PARTIAL = 1, TC_EPI_ARGMAX = 2 };
@@ -46,6 +61,7 @@ struct TcGemmArgs {
   int epilogue;
   void* out;           // bf16 [T][N] | fp32 [nsplit][T][N] | bf16 logits (may be null) for ARGMAX
   unsigned long long* argmax_packed;  // [T] for TC_EPI_ARGMAX (must be zeroed before launch)
+  KvPrefetch prefetch;                // optional ride-along K/V prefetch
 };
 int launch_linear_tc(const TcGemmArgs& a, cudaStream_t s);
 int tc_pick_bn(int T);
