@@ -51,6 +51,7 @@ SIGNATURES = {
     "b2_set_debug": (_I, [_P, C.c_int32]),
     "b2_get_hidden": (_I, [_P, C.c_int32, C.c_int32, C.POINTER(C.c_uint16)]),
     "b2_sample": (_I, [_P, C.c_int32, C.POINTER(b2_sampling), _I32P]),
+    "b2_sample_rows": (_I, [_P, C.c_int32, _I32P, C.POINTER(b2_sampling), _I32P]),
     "b2_set_next_tokens": (_I, [_P, C.c_int32, _I32P, _I32P]),
     "b2_decode_profile": (_I, [_P, C.c_int32, _I32P, C.c_int32, C.POINTER(C.c_float), C.POINTER(C.c_int64)]),
     "b2_launch_count": (C.c_int64, [_P]),

@@ -147,7 +147,8 @@ struct b2_engine {
   int force_gemm_impl = -1;
   unsigned skip_mask = 0;
   long long kv_l2_budget = 0;      // B2_KV_L2_MB: bytes of next-layer K/V the projections prefetch into L2 (0 = off)
-  int32_t* d_pf_frac = nullptr;  // B2_SKIP_MASK: kernel classes left out (timing ablations only; results are garbage)
+  int32_t* d_pf_frac = nullptr;
+  int32_t* d_sample_out = nullptr;  // B2_SKIP_MASK: kernel classes left out (timing ablations only; results are garbage)
 };
 
 namespace {
@@ -206,9 +207,9 @@ int bucket_batch(int B) {
 
 int pick_attn_split(b2_engine* e, int B, int max_len) {
   // The decode-attention kernel balances pages over its persistent warps by itself; there is no
-  // host-side split factor any more (kept as a constant component of the graph key).
-  (void)e; (void)B; (void)max_len;
-  return 1;
+  // host-side split factor any more.  The slot of the graph key now tells the two step variants apart.
+  (void)B; (void)max_len;
+  return (e->debug_flags & 2) ? 2 : 1;
 }
 
 // ---- one Linear layer: picks SIMT GEMV or the tcgen05 kernel, bf16 or split-K partial output
@@ -452,7 +453,9 @@ int ensure_graph(b2_engine* e, int B, int attn_split) {
   return 0;
 }
 
-bool graphs_enabled(b2_engine* e) { return e->cfg.use_cuda_graphs && !e->profiling && e->debug_flags == 0; }
+// hidden-state capture needs eager launches; the logits buffer is just another kernel argument, so it
+// only selects a different graph (attn_split slot of the key: 1 = argmax only, 2 = logits written too)
+bool graphs_enabled(b2_engine* e) { return e->cfg.use_cuda_graphs && !e->profiling && !(e->debug_flags & 1); }
 
 int run_decode_step(b2_engine* e, int B, int attn_split) {
   if (!graphs_enabled(e)) return decode_body(e, B, attn_split);
@@ -773,6 +776,7 @@ extern "C" int b2_engine_create(const b2_config* cfg, const char* safetensors_pa
     E_TRY(dalloc(&e->d_argmax, Bcap));
     E_TRY(dalloc(&e->d_step, (size_t)1));
     E_TRY(dalloc(&e->d_pf_frac, (size_t)1));
+    E_TRY(dalloc(&e->d_sample_out, Bcap));
     E_CUDA(cudaMemset(e->d_pf_frac, 0, 4));
     e->log_cap_steps = 4096;
     E_TRY(dalloc(&e->d_token_log, (size_t)e->log_cap_steps * c.max_seqs));
@@ -865,7 +869,7 @@ extern "C" void b2_engine_free(b2_engine* e) {
   }
   F(e->kv_pool); F(e->h); F(e->x); F(e->qkv); F(e->qrot); F(e->attn); F(e->gu); F(e->act); F(e->proj); F(e->xlast);
   F(e->partial); F(e->attn_scratch); F(e->d_tokens); F(e->d_positions); F(e->d_seq_lens); F(e->d_slots);
-  F(e->d_block_table); F(e->d_last_rows); F(e->d_out_tokens); F(e->d_token_log); F(e->d_step); F(e->d_argmax); F(e->d_pf_frac);
+  F(e->d_block_table); F(e->d_last_rows); F(e->d_out_tokens); F(e->d_token_log); F(e->d_step); F(e->d_argmax); F(e->d_pf_frac); F(e->d_sample_out);
   F(e->d_tiles); F(e->dbg_hidden); F(e->logits);
   if (e->h_stage) cudaFreeHost(e->h_stage);
   if (e->h_tiles) cudaFreeHost(e->h_tiles);
@@ -1235,5 +1239,26 @@ extern "C" int b2_sample(b2_engine* e, int32_t nseq, const b2_sampling* params, 
   B2_CUDA_OK(cudaMemcpyAsync(e->h_out, e->d_out_tokens, nseq * 4, cudaMemcpyDeviceToHost, e->stream));
   B2_CUDA_OK(cudaStreamSynchronize(e->stream));
   memcpy(out_tokens, e->h_out, nseq * 4);
+  return 0;
+}
+
+extern "C" int b2_sample_rows(b2_engine* e, int32_t nrows, const int32_t* rows, const b2_sampling* params, int32_t* out_tokens) {
+  B2_REQUIRE(e && rows && params && out_tokens && nrows >= 1, "b2_sample_rows: bad arguments");
+  B2_REQUIRE((e->debug_flags & 2) && e->logits, "b2_sample_rows: logits capture not enabled (b2_set_debug(e, 2))");
+  B2_REQUIRE(nrows <= e->cfg.max_seqs, "b2_sample_rows: too many rows");
+  B2_CUDA_OK(cudaSetDevice(e->device));
+  for (int i = 0; i < nrows; ++i) {
+    B2_REQUIRE(rows[i] >= 0 && rows[i] < e->last_n, "b2_sample_rows: row %d outside the last forward (%d rows)", rows[i], e->last_n);
+    const bf16* lg = e->logits + (size_t)rows[i] * e->cfg.vocab;
+    if (params[i].temperature <= 0.f)
+      B2_TRY(launch_argmax_rows(lg, e->d_sample_out + i, 1, e->cfg.vocab, e->stream));
+    else
+      B2_TRY(launch_sample(lg, e->d_sample_out + i, 1, e->cfg.vocab, params[i].temperature, params[i].top_k, params[i].top_p,
+                           params[i].seed, (uint64_t)e->launches, e->stream));
+    e->launches++;
+  }
+  B2_CUDA_OK(cudaMemcpyAsync(e->h_out, e->d_sample_out, nrows * 4, cudaMemcpyDeviceToHost, e->stream));
+  B2_CUDA_OK(cudaStreamSynchronize(e->stream));
+  memcpy(out_tokens, e->h_out, nrows * 4);
   return 0;
 }

@@ -115,6 +115,10 @@ typedef struct b2_sampling {
   uint64_t seed;
 } b2_sampling;
 int  b2_sample(b2_engine* e, int32_t nseq, const b2_sampling* params, int32_t* out_tokens);
+/* Per-row variant for a batch whose requests carry different sampling parameters: rows[i] indexes
+ * the last forward's batch, params[i] applies to it (temperature 0 = greedy). */
+int  b2_sample_rows(b2_engine* e, int32_t nrows, const int32_t* rows, const b2_sampling* params,
+                    int32_t* out_tokens);
 /* Overrides the device-resident "next token" of each listed sequence (after sampling on host
  * or with b2_sample) so the following b2_decode_step(in_tokens=NULL) consumes it. */
 int  b2_set_next_tokens(b2_engine* e, int32_t nseq, const int32_t* seq_ids, const int32_t* tokens);
