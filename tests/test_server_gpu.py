@@ -18,7 +18,7 @@ from oracle.qwen3_oracle import QWEN3_TINY, Restated, attention_explicit, pertur
 pytestmark = pytest.mark.gpu
 MODEL_ID = "Qwen/Qwen3-0.6B"  # served name, as in llm-d-test.yaml:7
 
-TEMPLATE = ("{%- for m in messages -%}[{{ m['role'] }}] {{ m['content'] }}\\n{%- endfor -%}"
+TEMPLATE = ("{%- for m in messages -%}[{{ m['role'] }}] {{ m['content'] + '\\n' }}{%- endfor -%}"
             "{%- if add_generation_prompt -%}[assistant] {%- endif -%}")
 
 
@@ -102,10 +102,12 @@ def test_greedy_token_prompt_matches_oracle(server):
                  {"model": MODEL_ID, "prompt": prompt[0].tolist(), "max_tokens": 12, "temperature": 0, "ignore_eos": True})
     assert st == 200, j
     ref, _ = Restated(arch, sd, attention=attention_explicit).greedy(prompt, 12)
-    want = "".join(("<|%d|>" % t) if t >= 256 else None or "" for t in ref[0].tolist())
-    got_ids = [int(x[:-2]) for x in j["choices"][0]["text"].split("<|")[1:]] if "<|" in j["choices"][0]["text"] else []
+    # the byte tokenizer renders ids >= 256 as <|id|>: recover those from the text and compare in order
+    import re
+    got_big = [int(x) for x in re.findall(r"<\|(\d+)\|>", j["choices"][0]["text"])]
     ref_big = [t for t in ref[0].tolist() if t >= 256]
-    assert got_ids[:6] == ref_big[:6], (j["choices"][0]["text"], ref[0].tolist())
+    assert len(ref_big) >= 4, "test prompt should produce ids outside the byte range"
+    assert got_big[:6] == ref_big[:6], (j["choices"][0]["text"], ref[0].tolist())
     assert j["usage"]["completion_tokens"] == 12
 
 
@@ -127,7 +129,7 @@ def test_chat_completion_and_template(server):
     assert j["object"] == "chat.completion" and j["id"].startswith("chatcmpl-")
     m = j["choices"][0]["message"]
     assert m["role"] == "assistant" and isinstance(m["content"], str)
-    rendered = "[system] Be brief.\n[user] Who are you?\n[assistant] "
+    rendered = "[system] Be brief.\n[user] Who are you?\n[assistant]"  # the {%- endif strips the space before it
     assert j["usage"]["prompt_tokens"] == len(rendered.encode())
     assert j["usage"]["completion_tokens"] == 5 and j["choices"][0]["finish_reason"] == "length"
 
