@@ -20,6 +20,17 @@
 
 namespace b2 {
 
+// Optional phase trace (tools/gemm_timeline.py): when a buffer is registered, every CTA stamps
+// %globaltimer at its phase boundaries into trace[blockIdx.x * 8 + slot].
+__device__ unsigned long long* g_tc_trace = nullptr;
+__device__ __forceinline__ void tc_stamp(int slot) {
+  if (g_tc_trace != nullptr) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    g_tc_trace[blockIdx.x * 8 + slot] = t;
+  }
+}
+
 constexpr int TC_BM = 128;
 constexpr int TC_BK = 64;
 constexpr int TC_W_BYTES = TC_BM * TC_BK * 2;  // 16 KB per stage
@@ -57,6 +68,7 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
   __shared__ unsigned long long amax_red[EPI == TC_EPI_ARGMAX ? 4 * BN : 1];
 
   pdl_launch_dependents();
+  if (threadIdx.x == 0) tc_stamp(0);  // CTA started
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int kb_total = K / TC_BK;
@@ -81,6 +93,7 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_slot;
+  if (threadIdx.x == 0) tc_stamp(1);  // barriers + TMEM ready
 
   if (warp == 0) {
     if (lane == 0) {
@@ -104,6 +117,7 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
             tma_load_2d(smem_base + i * C::STAGE_BYTES, &tmap_w, (kb0 + i) * TC_BK, m_tile * TC_BM, fb);
           }
           pdl_wait();
+          tc_stamp(2);  // dependency satisfied, X loads go out
           waited = true;
           for (int i = 0; i < npre; ++i)
             tma_load_2d(smem_base + i * C::STAGE_BYTES + TC_W_BYTES, &tmap_x, (kb0 + i) * TC_BK, n_tile * BN,
@@ -147,6 +161,7 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
         for (int kb = kb0; kb < kb1; ++kb, ++it) {
           const int s = it % C::STAGES;
           mbar_wait(smem_u32(&full_bar[s]), (it / C::STAGES) & 1);
+          if (it == 0) tc_stamp(3);  // first operands landed
           tc_fence_after();
           const uint32_t ws = smem_base + s * C::STAGE_BYTES;
           const uint64_t da = umma_desc_sw128(ws);
@@ -160,6 +175,7 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
           tc_commit(smem_u32(&empty_bar[s]));  // frees the smem stage once these MMAs retire
         }
         tc_commit(smem_u32(&tmem_full_bar[as]));  // accumulator complete
+        if (lt == 0) tc_stamp(4);  // all MMAs of the first tile issued
       }
     }
   } else {
@@ -190,24 +206,75 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
       const int split = tile / (m_tiles * n_tiles);
       const int as = lt & 1;
       mbar_wait(smem_u32(&tmem_full_bar[as]), (lt >> 1) & 1);
+      if (lt == 0 && threadIdx.x == 64) tc_stamp(5);  // accumulator visible to the epilogue
       tc_fence_after();
       const int row = m_tile * TC_BM + q * 32 + lane;  // output feature
       const bool row_ok = row < N;
-#pragma unroll 1
-      for (int c0 = 0; c0 < BN; c0 += 16) {
-        uint32_t r[16];
-        tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN + c0), r);
-        tmem_ld_wait();
+      const int tok0 = n_tile * BN;
+      const bool full = row_ok && tok0 + BN <= T;  // whole tile in range: no per-element predicates
+      const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN);
+      if (EPI == TC_EPI_F32_PARTIAL) {
+        float* dst = reinterpret_cast<float*>(out) + ((size_t)split * T + tok0) * N + row;  // + j * N per token
+        if (BN == 16) {
+          uint32_t r[16];
+          tmem_ld16(tbase, r);
+          tmem_ld_wait();
 #pragma unroll
-        for (int j = 0; j < 16; ++j) {
-          const int tok = n_tile * BN + c0 + j;
-          const float acc = __uint_as_float(r[j]);
-          if (EPI == TC_EPI_BF16) {
-            if (tok < T && row_ok) reinterpret_cast<bf16*>(out)[(size_t)tok * N + row] = __float2bfloat16_rn(acc);
-          } else if (EPI == TC_EPI_F32_PARTIAL) {
-            if (tok < T && row_ok) reinterpret_cast<float*>(out)[((size_t)split * T + tok) * N + row] = acc;
-          } else {
-            const bf16 lb = __float2bfloat16_rn(acc);
+          for (int j = 0; j < 16; ++j)
+            if (full || (row_ok && tok0 + j < T)) dst[(size_t)j * N] = __uint_as_float(r[j]);
+        } else {
+#pragma unroll 1
+          for (int c0 = 0; c0 < BN; c0 += 32) {
+            uint32_t r[32];
+            tmem_ld32(tbase + (uint32_t)c0, r);
+            tmem_ld_wait();
+            float* d = dst + (size_t)c0 * N;
+            if (full) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) d[(size_t)j * N] = __uint_as_float(r[j]);
+            } else {
+#pragma unroll
+              for (int j = 0; j < 32; ++j)
+                if (row_ok && tok0 + c0 + j < T) d[(size_t)j * N] = __uint_as_float(r[j]);
+            }
+          }
+        }
+      } else if (EPI == TC_EPI_BF16) {
+        bf16* dst = reinterpret_cast<bf16*>(out) + (size_t)tok0 * N + row;
+        if (BN == 16) {
+          uint32_t r[16];
+          tmem_ld16(tbase, r);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 16; ++j)
+            if (full || (row_ok && tok0 + j < T)) dst[(size_t)j * N] = __float2bfloat16_rn(__uint_as_float(r[j]));
+        } else {
+#pragma unroll 1
+          for (int c0 = 0; c0 < BN; c0 += 32) {
+            uint32_t r[32];
+            tmem_ld32(tbase + (uint32_t)c0, r);
+            tmem_ld_wait();
+            bf16* d = dst + (size_t)c0 * N;
+            if (full) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) d[(size_t)j * N] = __float2bfloat16_rn(__uint_as_float(r[j]));
+            } else {
+#pragma unroll
+              for (int j = 0; j < 32; ++j)
+                if (row_ok && tok0 + c0 + j < T) d[(size_t)j * N] = __float2bfloat16_rn(__uint_as_float(r[j]));
+            }
+          }
+        }
+      } else {
+#pragma unroll 1
+        for (int c0 = 0; c0 < BN; c0 += 16) {
+          uint32_t r[16];
+          tmem_ld16(tbase + (uint32_t)c0, r);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            const int tok = tok0 + c0 + j;
+            const bf16 lb = __float2bfloat16_rn(__uint_as_float(r[j]));
             const float lv = __bfloat162float(lb);
             if (out != nullptr && tok < T && row_ok) reinterpret_cast<bf16*>(out)[(size_t)tok * N + row] = lb;
             unsigned long long p = (row_ok && lv == lv) ? tc_argmax_pack(lv, row) : 0ull;
@@ -240,6 +307,7 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
   }
   tc_fence_before();
   __syncthreads();
+  if (threadIdx.x == 0) tc_stamp(6);  // epilogue done
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc(tmem_base, C::TMEM_COLS);
@@ -285,6 +353,11 @@ int b2_make_tmap_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_
 }
 
 namespace b2 {
+
+int tc_set_trace(unsigned long long* dev_buf) {
+  B2_CUDA_OK(cudaMemcpyToSymbol(g_tc_trace, &dev_buf, sizeof(dev_buf)));
+  return 0;
+}
 
 int tc_pick_bn(int T) {
   if (T <= 16) return 16;

@@ -65,6 +65,7 @@ struct TcGemmArgs {
 };
 int launch_linear_tc(const TcGemmArgs& a, cudaStream_t s);
 int tc_pick_bn(int T);
+int tc_set_trace(unsigned long long* dev_buf);  // diagnostics: per-CTA phase timestamps (null = off)
 // choose a split-K factor so that tiles * splits fills the SMs (each split gets >= 1 k-block)
 int tc_pick_nsplit(int T, int N, int K, int num_sms);
 

@@ -165,6 +165,10 @@ int b2k_silu_mul(const void* gu, int gu_is_f32, int nsplit, void* act_bf16, int 
 int b2k_linear(const void* x_bf16, const void* w_bf16, void* out, int out_is_f32, int nsplit,
                int T, int N, int K, int impl, void* stream);
 
+/* Diagnostics: register a device buffer of (148 * 8) uint64 in which every CTA of the tcgen05
+ * projection kernel stamps %globaltimer at its phase boundaries (NULL switches the trace off). */
+int b2k_debug_gemm_trace(void* dev_u64_buf);
+
 /* lm_head + greedy argmax fused (HF:...:504-505 + generate(do_sample=False)).
  * logits_bf16 may be NULL.  out_tokens [T] int32 (device). scratch: [T] uint64 (device). */
 int b2k_lmhead_argmax(const void* x_bf16, const void* w_bf16, void* logits_bf16,
