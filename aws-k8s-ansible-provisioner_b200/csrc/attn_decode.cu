@@ -36,6 +36,7 @@ constexpr int AD_SMEM = AD_WARPS * AD_STAGES * AD_STAGE;  // 192 KB
 constexpr int AD_MAX_B = 512;
 constexpr int AD_MAX_CTAS = 160;
 constexpr int AD_META = 1024;                    // ints at the head of the scratch: [0]=pages per warp (base), [599]=warps with one extra, [1..B+1]=page prefix
+constexpr int AD_LAST_PAGE = 1 << 30;            // flag on a slice id: last page of its sequence
 constexpr int AD_REC = 2 * AD_HD + 4;            // floats per partial record: O[2][128], m[2], l[2]
 
 __device__ __forceinline__ void ad_ldsm_x4(uint32_t addr, uint32_t* r) {
@@ -67,14 +68,15 @@ attn_decode_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k_pages,
   __shared__ __align__(8) uint64_t bars[AD_WARPS][AD_STAGES];
   __shared__ int s_prefix[AD_MAX_B + 1];  // pages of sequences before b (exclusive prefix)
 
-  pdl_launch_dependents();
+  // Everything up to pdl_wait() below runs while the previous kernel (QK-norm/RoPE, which writes q and
+  // the NEW token's K/V slot) is still executing: sequence lengths and block tables were written at the
+  // top of the step, and every page except the last one of each sequence is at least a step old.
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (threadIdx.x == 0) {
     for (int w = 0; w < AD_WARPS; ++w)
       for (int s = 0; s < AD_STAGES; ++s) mbar_init(smem_u32(&bars[w][s]), 1);
     mbar_fence_init();
   }
-  pdl_wait();
   // ---- page prefix over sequences (warp 0: a slab of entries per lane, then a warp scan) ----
   if (warp == 0) {
     const int per = (B + 31) / 32;
@@ -106,18 +108,10 @@ attn_decode_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k_pages,
   const int base = total_pages / wtot, rem = total_pages - base * wtot;
   unsigned long long t_start = 0;
   if (threadIdx.x == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_start));
-  if (blockIdx.x == 0) {  // publish the geometry for the combine pass
-    int* meta = reinterpret_cast<int*>(scratch);
-    if (threadIdx.x == 0) {
-      meta[0] = base;
-      meta[599] = rem;
-    }
-    for (int i = threadIdx.x; i <= B; i += blockDim.x) meta[1 + i] = s_prefix[i];
-  }
   const int gw = blockIdx.x * AD_WARPS + warp;
   const int p0 = gw * base + min(gw, rem);
   const int ntiles = base + (gw < rem ? 1 : 0);
-  if (ntiles <= 0) return;
+  if (ntiles <= 0 && blockIdx.x != 0) return;
   const bool dbg_time = (warp == 0 && lane == 0);
 
   auto locate = [&](int p) -> AdPos {  // page-line position -> (sequence, kv head, page in sequence)
@@ -145,6 +139,7 @@ attn_decode_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k_pages,
       if (nn < ntiles) {
         const AdPos r = locate(p0 + nn);
         cached_slice = block_table[(size_t)r.b * bt_stride + r.j] * nkv + r.kvh;
+        if (r.j == r.nb - 1) cached_slice |= AD_LAST_PAGE;  // holds the slot the previous kernel is writing
       }
       cached_group = g;
     }
@@ -154,12 +149,32 @@ attn_decode_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k_pages,
     const int stage = n % AD_STAGES;
     const uint32_t bar = smem_u32(&bars[warp][stage]);
     const uint32_t dst = smem_u32(wsm + stage * AD_STAGE);
-    const size_t off = (size_t)slice * (AD_BS * AD_HD);
+    const size_t off = (size_t)(slice & ~AD_LAST_PAGE) * (AD_BS * AD_HD);
     mbar_arrive_expect_tx(bar, AD_STAGE);
     bulk_g2s(dst, k_pages + off, AD_TILE, bar);
     bulk_g2s(dst + AD_TILE, v_pages + off, AD_TILE, bar);
   };
+  // start streaming: pages that do not hold a freshly written slot go out before the dependency wait
+  int issued = 0;
   for (int n = 0; n < AD_STAGES; ++n) {
+    const int sl = slice_of(n);
+    if (n < ntiles && issued == n && !(sl & AD_LAST_PAGE)) {
+      if (lane == 0) issue(n, sl);
+      issued = n + 1;
+    }
+  }
+  pdl_wait();
+  pdl_launch_dependents();
+  if (blockIdx.x == 0) {  // publish the geometry for the combine pass
+    int* meta = reinterpret_cast<int*>(scratch);
+    if (threadIdx.x == 0) {
+      meta[0] = base;
+      meta[599] = rem;
+    }
+    for (int i = threadIdx.x; i <= B; i += blockDim.x) meta[1 + i] = s_prefix[i];
+  }
+  if (ntiles <= 0) return;
+  for (int n = issued; n < AD_STAGES; ++n) {
     const int sl = slice_of(n);
     if (n < ntiles && lane == 0) issue(n, sl);
   }
@@ -307,8 +322,8 @@ attn_decode_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k_pages,
 // One CTA per (sequence, kv head) unit, thread = (head, dim): merges the unit's records in run order.
 __global__ void __launch_bounds__(2 * AD_HD)
 attn_combine_kernel(const float* __restrict__ scratch, bf16* __restrict__ out, int B, int nq, int nkv) {
-  pdl_launch_dependents();
   pdl_wait();
+  pdl_launch_dependents();
   const int unit = blockIdx.x;
   const int b = unit / nkv, kvh = unit % nkv;
   const int h = threadIdx.x >> 7, d = threadIdx.x & (AD_HD - 1);

@@ -48,8 +48,8 @@ attn_prefill_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k_pages
                     const int32_t* __restrict__ block_table, int bt_stride, const PrefillTile* __restrict__ tiles,
                     bf16* __restrict__ out, int nq, int nkv, int block_size, float scale_log2) {
   extern __shared__ __align__(128) uint8_t smem[];
-  pdl_launch_dependents();
   pdl_wait();
+  pdl_launch_dependents();
   const PrefillTile tile = tiles[blockIdx.x];
   const int h = blockIdx.y, kvh = h / (nq / nkv);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;

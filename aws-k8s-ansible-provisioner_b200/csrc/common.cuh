@@ -78,9 +78,12 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) {
 
 // ---------------------------------------------------------------------------------------
 // Programmatic dependent launch (PDL): every kernel is launched with the programmatic stream
-// serialization attribute, lets its successor start early (launch_dependents at the top) and
-// blocks at pdl_wait() before it touches anything its predecessors produce.  Code before
-// pdl_wait() may only read data that is constant for the whole step (weights, norm gains).
+// serialization attribute.  Discipline used throughout: a kernel calls pdl_wait() before it touches
+// anything its IMMEDIATE predecessor wrote, and only then pdl_launch_dependents().  So when a kernel
+// starts, its predecessor has already passed its own wait, i.e. everything older than the immediate
+// predecessor is complete and visible: code before pdl_wait() may read constants (weights, tables)
+// AND anything produced two or more kernels earlier (block tables, sequence lengths, the residual
+// stream, all K/V pages except the slots the previous kernel is writing).
 // ---------------------------------------------------------------------------------------
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }

@@ -11,8 +11,8 @@ namespace b2 {
 // ---------------------------------------------------------------------------------------
 __global__ void embed_kernel(const int32_t* __restrict__ ids, const bf16* __restrict__ table, bf16* __restrict__ h,
                              int H, int vocab, unsigned long long* __restrict__ zero_buf, int nzero) {
-  pdl_launch_dependents();
   pdl_wait();
+  pdl_launch_dependents();
   int t = blockIdx.x;
   // first kernel of every forward: also clears the fused arg-max slots the lm_head will atomicMax into
   if (t == 0 && zero_buf != nullptr)
@@ -33,8 +33,8 @@ int launch_embed(const int32_t* ids, const bf16* table, bf16* h, int T, int H, i
 
 __global__ void gather_rows_kernel(const bf16* __restrict__ src, const int32_t* __restrict__ rows, bf16* __restrict__ dst,
                                    int H) {
-  pdl_launch_dependents();
   pdl_wait();
+  pdl_launch_dependents();
   int r = rows[blockIdx.x];
   const uint4* s = reinterpret_cast<const uint4*>(src + (size_t)r * H);
   uint4* d = reinterpret_cast<uint4*>(dst + (size_t)blockIdx.x * H);
@@ -57,14 +57,19 @@ template <int MODE>  // 0: no delta, 1: bf16 delta, 2: fp32 partials
 __global__ void add_rmsnorm_kernel(bf16* __restrict__ h, const void* __restrict__ delta, int nsplit, size_t split_stride,
                                    const bf16* __restrict__ w, bf16* __restrict__ x, int H, float eps) {
   __shared__ float red[32];
-  pdl_launch_dependents();
   const int t = blockIdx.x;
   const int i = threadIdx.x;  // vector index, 8 elements
+  // Before the dependency wait: the norm gains (constant) and, when a delta is added, the residual
+  // stream h (last written several kernels ago).  With no delta, h comes from the embedding kernel
+  // that runs immediately before, so it is read after the wait.
   float wv[8];
-  unpack8(reinterpret_cast<const uint4*>(w)[i], wv);  // norm gains are constant: read before the dependency wait
+  unpack8(reinterpret_cast<const uint4*>(w)[i], wv);
+  uint4 hv = make_uint4(0, 0, 0, 0);
+  if (MODE != 0) hv = reinterpret_cast<const uint4*>(h + (size_t)t * H)[i];
   pdl_wait();
+  pdl_launch_dependents();
+  if (MODE == 0) hv = reinterpret_cast<const uint4*>(h + (size_t)t * H)[i];
   float v[8];
-  uint4 hv = reinterpret_cast<const uint4*>(h + (size_t)t * H)[i];
   unpack8(hv, v);
   if (MODE == 1) {
     float d[8];
@@ -145,15 +150,36 @@ __global__ void qknorm_rope_kv_kernel(const void* __restrict__ qkv, int nsplit, 
                                       bf16* __restrict__ k_pages, bf16* __restrict__ v_pages, int T, int nq, int nkv,
                                       int block_size, float eps) {
   constexpr int HD = 128;
-  pdl_launch_dependents();
-  pdl_wait();
   const int nheads = nq + 2 * nkv;
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
-  if (warp >= T * nheads) return;
+  if (warp >= T * nheads) {
+    pdl_wait();
+    pdl_launch_dependents();
+    return;
+  }
   const int t = warp / nheads;
   const int head = warp % nheads;
   const size_t row = (size_t)t * nheads * HD + (size_t)head * HD + lane * 4;
+  const bool is_q = head < nq;
+  const bool is_k = !is_q && head < nq + nkv;
+  // Before the dependency wait: everything that is not the QKV projection's output -- position and
+  // slot of the token (written at the top of the step), the RoPE table and the norm gains.
+  const int pos = max(positions[t], 0);
+  const int slot = slots[t];
+  float wv[4] = {1.f, 1.f, 1.f, 1.f}, c[4] = {1.f, 1.f, 1.f, 1.f}, sn[4] = {0.f, 0.f, 0.f, 0.f};
+  if (is_q || is_k) {
+    uint2 wraw = *reinterpret_cast<const uint2*>((is_q ? qw : kw) + lane * 4);
+    wv[0] = bf16lo(wraw.x); wv[1] = bf16hi(wraw.x); wv[2] = bf16lo(wraw.y); wv[3] = bf16hi(wraw.y);
+    const bf16* cs = cos_sin + (size_t)pos * HD;
+    const int ci = (lane * 4) & 63;
+    uint2 craw = *reinterpret_cast<const uint2*>(cs + ci);
+    uint2 sraw = *reinterpret_cast<const uint2*>(cs + 64 + ci);
+    c[0] = bf16lo(craw.x); c[1] = bf16hi(craw.x); c[2] = bf16lo(craw.y); c[3] = bf16hi(craw.y);
+    sn[0] = bf16lo(sraw.x); sn[1] = bf16hi(sraw.x); sn[2] = bf16lo(sraw.y); sn[3] = bf16hi(sraw.y);
+  }
+  pdl_wait();
+  pdl_launch_dependents();
 
   float v[4];
   if (F32IN) {
@@ -169,21 +195,10 @@ __global__ void qknorm_rope_kv_kernel(const void* __restrict__ qkv, int nsplit, 
     v[0] = bf16lo(a.x); v[1] = bf16hi(a.x); v[2] = bf16lo(a.y); v[3] = bf16hi(a.y);
   }
 
-  const bool is_q = head < nq;
-  const bool is_k = !is_q && head < nq + nkv;
   if (is_q || is_k) {
     float ss = v[0] * v[0] + v[1] * v[1] + v[2] * v[2] + v[3] * v[3];
     ss = warp_sum(ss);
     const float rstd = __fdiv_rn(1.0f, __fsqrt_rn(ss / (float)HD + eps));
-    uint2 wraw = *reinterpret_cast<const uint2*>((is_q ? qw : kw) + lane * 4);
-    const float wv[4] = {bf16lo(wraw.x), bf16hi(wraw.x), bf16lo(wraw.y), bf16hi(wraw.y)};
-    const int pos = max(positions[t], 0);
-    const bf16* cs = cos_sin + (size_t)pos * HD;
-    const int ci = (lane * 4) & 63;
-    uint2 craw = *reinterpret_cast<const uint2*>(cs + ci);
-    uint2 sraw = *reinterpret_cast<const uint2*>(cs + 64 + ci);
-    const float c[4] = {bf16lo(craw.x), bf16hi(craw.x), bf16lo(craw.y), bf16hi(craw.y)};
-    const float sn[4] = {bf16lo(sraw.x), bf16hi(sraw.x), bf16lo(sraw.y), bf16hi(sraw.y)};
 #pragma unroll
     for (int e = 0; e < 4; ++e) v[e] = bf16_round(wv[e] * bf16_round(v[e] * rstd));
 #pragma unroll
@@ -199,7 +214,6 @@ __global__ void qknorm_rope_kv_kernel(const void* __restrict__ qkv, int nsplit, 
   if (is_q) {
     *reinterpret_cast<uint2*>(q_out + ((size_t)t * nq + head) * HD + lane * 4) = o;
   } else {
-    const int slot = slots[t];
     if (slot < 0) return;
     const int kvh = is_k ? head - nq : head - nq - nkv;
     const int blk = slot / block_size, off = slot % block_size;
@@ -235,8 +249,8 @@ int launch_qknorm_rope_kv(ActIn qkv, const bf16* qw, const bf16* kw, const bf16*
 template <bool F32IN>
 __global__ void silu_mul_kernel(const void* __restrict__ gu, int nsplit, size_t split_stride, bf16* __restrict__ act,
                                 int T, int I) {
-  pdl_launch_dependents();
   pdl_wait();
+  pdl_launch_dependents();
   const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;  // vector of 8 over [T][I]
   const size_t nvec = (size_t)T * I / 8;
   if (idx >= nvec) return;
@@ -298,8 +312,8 @@ __device__ __forceinline__ unsigned long long argmax_pack(float v, int idx) {
 
 __global__ void argmax_rows_kernel(const bf16* __restrict__ logits, int32_t* __restrict__ out, int V) {
   __shared__ unsigned long long red[32];
-  pdl_launch_dependents();
   pdl_wait();
+  pdl_launch_dependents();
   const bf16* row = logits + (size_t)blockIdx.x * V;
   unsigned long long best = 0;
   for (int i = threadIdx.x; i < V; i += blockDim.x) {
@@ -328,8 +342,8 @@ int launch_argmax_rows(const bf16* logits, int32_t* out, int T, int V, cudaStrea
 }
 
 __global__ void argmax_finalize_kernel(const unsigned long long* __restrict__ packed, int32_t* __restrict__ out, int T) {
-  pdl_launch_dependents();
   pdl_wait();
+  pdl_launch_dependents();
   int t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t < T) out[t] = (int32_t)(0xffffffffu - (uint32_t)(packed[t] & 0xffffffffull));
 }
@@ -346,8 +360,8 @@ __global__ void decode_advance_kernel(int32_t* positions, int32_t* seq_lens, int
                                       const int32_t* __restrict__ block_table, int bt_stride, int block_size, int B,
                                       int32_t* frac_q16, long long l2_budget_bytes, long long bytes_per_page_all_heads) {
   __shared__ int total_pages;
-  pdl_launch_dependents();
   pdl_wait();
+  pdl_launch_dependents();
   if (threadIdx.x == 0) total_pages = 0;
   __syncthreads();
   int my_pages = 0;

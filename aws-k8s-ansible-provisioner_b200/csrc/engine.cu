@@ -384,8 +384,8 @@ int forward(b2_engine* e, int T, int ntiles, int nlast, int attn_split) {
 
 __global__ void publish_tokens_kernel(const int32_t* __restrict__ out_tokens, int32_t* __restrict__ next_in,
                                       int32_t* __restrict__ log, int32_t* step, int B, int log_cap_steps, int stride) {
-  pdl_launch_dependents();
   pdl_wait();
+  pdl_launch_dependents();
   const int st = *step;  // single CTA
   for (int b = threadIdx.x; b < B; b += blockDim.x) {
     next_in[b] = out_tokens[b];

@@ -11,8 +11,8 @@ namespace b2 {
 template <int TB, bool OUT_F32>
 __global__ void __launch_bounds__(128) linear_simt_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w,
                                                           void* __restrict__ out, int T, int N, int K) {
-  pdl_launch_dependents();
   pdl_wait();
+  pdl_launch_dependents();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n = blockIdx.x * 4 + warp;
   if (n >= N) return;

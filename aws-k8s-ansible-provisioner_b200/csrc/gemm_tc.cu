@@ -67,7 +67,6 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
   __shared__ uint32_t tmem_slot;
   __shared__ unsigned long long amax_red[EPI == TC_EPI_ARGMAX ? 4 * BN : 1];
 
-  pdl_launch_dependents();
   if (threadIdx.x == 0) tc_stamp(0);  // CTA started
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -117,6 +116,7 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
             tma_load_2d(smem_base + i * C::STAGE_BYTES, &tmap_w, (kb0 + i) * TC_BK, m_tile * TC_BM, fb);
           }
           pdl_wait();
+          pdl_launch_dependents();
           tc_stamp(2);  // dependency satisfied, X loads go out
           waited = true;
           for (int i = 0; i < npre; ++i)
@@ -144,7 +144,10 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
           tma_load_2d(ws + TC_W_BYTES, &tmap_x, kb * TC_BK, n_tile * BN, fb);
         }
       }
-      if (!waited) pdl_wait();
+      if (!waited) {
+        pdl_wait();
+        pdl_launch_dependents();
+      }
     }
   } else if (warp == 1) {
     if (lane == 0) {
