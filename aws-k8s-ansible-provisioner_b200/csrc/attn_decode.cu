@@ -7,8 +7,9 @@
 // end to end, and each of the grid's persistent warps (8 per SM) takes one contiguous run of that
 // line, so every warp moves the same number of bytes whatever the mix of sequence lengths, and a
 // warp's TMA pipeline runs without interruption across unit boundaries.  Where a run ends inside a
-// unit the warp leaves a partial (m, l, O) record; attn_combine_kernel merges the 1..few records of
-// each unit in run order (deterministic, no atomics).
+// unit the warp leaves a partial (m, l, O) record and bumps the unit's arrival counter; the warp that
+// arrives last merges the unit's 1..few records IN RUN ORDER (so the result does not depend on who
+// was last) and writes the bf16 output.  No second kernel, no floating-point atomics.
 //
 // Per warp: lane 0 issues two 4 KB bulk copies (cp.async.bulk, one K and one V page-slice of
 // [16 tokens][128 dims]) per stage onto an mbarrier, three stages deep.  Pages are stored with the
@@ -35,7 +36,8 @@ constexpr int AD_STAGE = 2 * AD_TILE;            // K + V
 constexpr int AD_SMEM = AD_WARPS * AD_STAGES * AD_STAGE;  // 192 KB
 constexpr int AD_MAX_B = 512;
 constexpr int AD_MAX_CTAS = 160;
-constexpr int AD_META = 1024;                    // ints at the head of the scratch: [0]=pages per warp (base), [599]=warps with one extra, [1..B+1]=page prefix
+constexpr int AD_CNT = 4096;                     // per-unit arrival counters (ints) after the geometry header; zero between launches
+constexpr int AD_META = 1024 + AD_CNT;           // ints at the head of the scratch: [0]=pages per warp (base), [599]=warps with one extra, [1..B+1]=page prefix
 constexpr int AD_LAST_PAGE = 1 << 30;            // flag on a slice id: last page of its sequence
 constexpr int AD_REC = 2 * AD_HD + 4;            // floats per partial record: O[2][128], m[2], l[2]
 
@@ -63,7 +65,7 @@ struct AdPos {  // a position on the page line
 __global__ void __launch_bounds__(AD_WARPS * 32, 1)
 attn_decode_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k_pages, const bf16* __restrict__ v_pages,
                    const int32_t* __restrict__ block_table, int bt_stride, const int32_t* __restrict__ seq_lens,
-                   float* __restrict__ scratch, int B, int nq, int nkv, float scale) {
+                   float* __restrict__ scratch, bf16* __restrict__ out, int B, int nq, int nkv, float scale) {
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ __align__(8) uint64_t bars[AD_WARPS][AD_STAGES];
   __shared__ int s_prefix[AD_MAX_B + 1];  // pages of sequences before b (exclusive prefix)
@@ -165,13 +167,12 @@ attn_decode_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k_pages,
   }
   pdl_wait();
   pdl_launch_dependents();
-  if (blockIdx.x == 0) {  // publish the geometry for the combine pass
-    int* meta = reinterpret_cast<int*>(scratch);
-    if (threadIdx.x == 0) {
-      meta[0] = base;
-      meta[599] = rem;
-    }
-    for (int i = threadIdx.x; i <= B; i += blockDim.x) meta[1 + i] = s_prefix[i];
+  if (blockIdx.x == 0) {
+    // empty sequences (padding rows of a graph bucket) own no pages: their output rows are zeros
+    for (int b = 0; b < B; ++b)
+      if (s_prefix[b + 1] == s_prefix[b])
+        for (int i = threadIdx.x; i < nq * AD_HD / 8; i += blockDim.x)
+          reinterpret_cast<uint4*>(out + (size_t)b * nq * AD_HD)[i] = make_uint4(0, 0, 0, 0);
   }
   if (ntiles <= 0) return;
   for (int n = issued; n < AD_STAGES; ++n) {
@@ -291,7 +292,8 @@ attn_decode_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k_pages,
       }
     }
     if (unit_ends) {
-      float* rec = scratch + AD_META + (size_t)(unit + gw) * AD_REC;
+      float* recs = scratch + AD_META;
+      float* rec = recs + (size_t)(unit + gw) * AD_REC;
       if (t4 == 0) {
 #pragma unroll
         for (int dt = 0; dt < 8; ++dt) {
@@ -307,6 +309,47 @@ attn_decode_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k_pages,
         rec[2 * AD_HD + 2] = l_run[0];
         rec[2 * AD_HD + 3] = l_run[1];
       }
+      // which warps' runs touch this unit (inverse of the partition above)
+      const int ub = unit / nkv, ukvh = unit - ub * nkv;
+      const int unb = s_prefix[ub + 1] - s_prefix[ub];
+      const int u0 = s_prefix[ub] * nkv + ukvh * unb;
+      const int cut = rem * (base + 1);
+      const int w0 = u0 < cut ? u0 / (base + 1) : rem + (u0 - cut) / base;
+      const int ulast = u0 + unb - 1;
+      const int w1 = ulast < cut ? ulast / (base + 1) : rem + (ulast - cut) / base;
+      int* cnt = reinterpret_cast<int*>(scratch) + 1024 + unit;
+      __threadfence();  // this warp's record is visible before its arrival is
+      __syncwarp();
+      int prev = 0;
+      if (lane == 0) prev = atomicAdd(cnt, 1);
+      prev = __shfl_sync(0xffffffffu, prev, 0);
+      if (prev == w1 - w0) {  // last to arrive: merge in run order and write the output
+        __threadfence();
+        if (lane == 0) *cnt = 0;  // ready for the next launch
+        float M[2] = {-INFINITY, -INFINITY};
+        for (int w = w0; w <= w1; ++w) {
+          const float* r2 = recs + (size_t)(unit + w) * AD_REC + 2 * AD_HD;
+          M[0] = fmaxf(M[0], __ldcg(r2 + 0));
+          M[1] = fmaxf(M[1], __ldcg(r2 + 1));
+        }
+        float O[8], L[2] = {0.f, 0.f};  // lane covers 8 of the 256 (head, dim) outputs: head = lane / 16
+#pragma unroll
+        for (int e = 0; e < 8; ++e) O[e] = 0.f;
+        const int hh = lane >> 4, d0 = (lane & 15) * 8;
+        for (int w = w0; w <= w1; ++w) {
+          const float* r2 = recs + (size_t)(unit + w) * AD_REC;
+          const float f = expf(__ldcg(r2 + 2 * AD_HD + hh) - M[hh]);
+          const float4 a = __ldcg(reinterpret_cast<const float4*>(r2 + hh * AD_HD + d0));
+          const float4 b = __ldcg(reinterpret_cast<const float4*>(r2 + hh * AD_HD + d0 + 4));
+          O[0] = fmaf(f, a.x, O[0]); O[1] = fmaf(f, a.y, O[1]); O[2] = fmaf(f, a.z, O[2]); O[3] = fmaf(f, a.w, O[3]);
+          O[4] = fmaf(f, b.x, O[4]); O[5] = fmaf(f, b.y, O[5]); O[6] = fmaf(f, b.z, O[6]); O[7] = fmaf(f, b.w, O[7]);
+          L[hh] = fmaf(f, __ldcg(r2 + 2 * AD_HD + 2 + hh), L[hh]);
+        }
+        const float inv = L[hh] > 0.f ? __fdiv_rn(1.0f, L[hh]) : 0.f;
+#pragma unroll
+        for (int e = 0; e < 8; ++e) O[e] *= inv;
+        *reinterpret_cast<uint4*>(out + ((size_t)ub * nq + ukvh * 2 + hh) * AD_HD + d0) = pack8(O);
+      }
       fresh = true;
     }
   }
@@ -317,43 +360,6 @@ attn_decode_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k_pages,
     meta[600 + 2 * blockIdx.x] = (int)(t_start & 0x7fffffff);
     meta[601 + 2 * blockIdx.x] = (int)(t_end & 0x7fffffff);
   }
-}
-
-// One CTA per (sequence, kv head) unit, thread = (head, dim): merges the unit's records in run order.
-__global__ void __launch_bounds__(2 * AD_HD)
-attn_combine_kernel(const float* __restrict__ scratch, bf16* __restrict__ out, int B, int nq, int nkv) {
-  pdl_wait();
-  pdl_launch_dependents();
-  const int unit = blockIdx.x;
-  const int b = unit / nkv, kvh = unit % nkv;
-  const int h = threadIdx.x >> 7, d = threadIdx.x & (AD_HD - 1);
-  const int* meta = reinterpret_cast<const int*>(scratch);
-  const int base = meta[0], rem = meta[599];
-  const int pre = meta[1 + b], nb = meta[2 + b] - pre;
-  bf16* o = out + ((size_t)b * nq + kvh * 2 + h) * AD_HD + d;
-  if (nb <= 0) {  // empty sequence (padding row of a graph bucket)
-    *o = __float2bfloat16_rn(0.f);
-    return;
-  }
-  const int u0 = pre * nkv + kvh * nb;
-  // inverse of the attention pass's partition: which warp's run holds page-line position p
-  auto warp_of = [&](int p) -> int {
-    const int cut = rem * (base + 1);
-    return p < cut ? p / (base + 1) : rem + (p - cut) / base;  // base > 0 whenever p >= cut exists
-  };
-  const int w0 = warp_of(u0), w1 = warp_of(u0 + nb - 1);
-  const float* recs = scratch + AD_META;
-  float M = -INFINITY;
-  for (int w = w0; w <= w1; ++w) M = fmaxf(M, recs[(size_t)(unit + w) * AD_REC + 2 * AD_HD + h]);
-  float O = 0.f, L = 0.f;
-  for (int w = w0; w <= w1; ++w) {
-    const float* rec = recs + (size_t)(unit + w) * AD_REC;
-    const float f = expf(rec[2 * AD_HD + h] - M);
-    O = fmaf(f, rec[h * AD_HD + d], O);
-    L = fmaf(f, rec[2 * AD_HD + 2 + h], L);
-  }
-  const float inv = L > 0.f ? __fdiv_rn(1.0f, L) : 0.f;
-  *o = __float2bfloat16_rn(O * inv);
 }
 
 static int ad_grid() {
@@ -367,34 +373,27 @@ size_t attn_decode_scratch_floats(int B, int nq, int nkv, int hd) {
   return (size_t)AD_META + ((size_t)B * nkv + (size_t)AD_MAX_CTAS * AD_WARPS) * AD_REC;
 }
 
-int launch_attn_decode_pass(const bf16* q, const bf16* k_pages, const bf16* v_pages, const int32_t* block_table,
-                            int bt_stride, const int32_t* seq_lens, float* scratch, int B, int nq, int nkv, int hd,
-                            int block_size, cudaStream_t s) {
+// scratch: attn_decode_scratch_floats() floats; its counter words (AD_CNT ints after the first 1024)
+// must be zero when the kernel starts -- the kernel leaves them zero again when it is done.
+int launch_attn_decode(const bf16* q, const bf16* k_pages, const bf16* v_pages, const int32_t* block_table,
+                       int bt_stride, const int32_t* seq_lens, float* scratch, bf16* out, int B, int nq, int nkv,
+                       int hd, int block_size, cudaStream_t s) {
   if (B <= 0) return 0;
   B2_REQUIRE(hd == AD_HD && block_size == AD_BS, "attn_decode: built for head_dim 128 / page 16 (got %d / %d)", hd, block_size);
   B2_REQUIRE(nq == 2 * nkv, "attn_decode: built for a GQA group of 2 (nq=%d nkv=%d)", nq, nkv);
-  B2_REQUIRE(B <= AD_MAX_B, "attn_decode: batch %d > %d", B, AD_MAX_B);
+  B2_REQUIRE(B <= AD_MAX_B && B * nkv <= AD_CNT, "attn_decode: batch %d x %d kv heads exceeds %d units", B, nkv, AD_CNT);
   B2_REQUIRE(scratch != nullptr, "attn_decode: scratch required");
   static B2PerDeviceOnce attr_once;
   if (attr_once.need()) B2_CUDA_OK(cudaFuncSetAttribute(attn_decode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AD_SMEM));
   const float scale = (float)(1.0 / sqrt((double)hd));  // HF passes head_dim**-0.5 as a double
   B2_CUDA_OK(b2_launch(attn_decode_kernel, dim3(ad_grid()), dim3(AD_WARPS * 32), (size_t)AD_SMEM, s, q, k_pages, v_pages,
-                       block_table, bt_stride, seq_lens, scratch, B, nq, nkv, scale));
+                       block_table, bt_stride, seq_lens, scratch, out, B, nq, nkv, scale));
   return 0;
 }
 
-int launch_attn_combine(const float* scratch, bf16* out, int B, int nq, int nkv, cudaStream_t s) {
-  if (B <= 0) return 0;
-  B2_CUDA_OK(b2_launch(attn_combine_kernel, dim3(B * nkv), dim3(2 * AD_HD), 0, s, scratch, out, B, nq, nkv));
+int attn_decode_zero_counters(float* scratch, cudaStream_t s) {
+  B2_CUDA_OK(cudaMemsetAsync(reinterpret_cast<int*>(scratch) + 1024, 0, AD_CNT * sizeof(int), s));
   return 0;
-}
-
-int launch_attn_decode(const bf16* q, const bf16* k_pages, const bf16* v_pages, const int32_t* block_table,
-                       int bt_stride, const int32_t* seq_lens, float* scratch, bf16* out, int B, int nq, int nkv,
-                       int hd, int block_size, cudaStream_t s) {
-  int rc = launch_attn_decode_pass(q, k_pages, v_pages, block_table, bt_stride, seq_lens, scratch, B, nq, nkv, hd, block_size, s);
-  if (rc != 0) return rc;
-  return launch_attn_combine(scratch, out, B, nq, nkv, s);
 }
 
 // ---------------------------------------------------------------------------------------
@@ -454,9 +453,12 @@ extern "C" int b2k_attn_decode_noalloc(const void* q, const void* k_pages, const
   float* scratch = nullptr;
   int rc = noalloc_scratch_for_current_device(&scratch);
   if (rc != 0) return rc;
-  // Nothing in the array has to start at zero: every record and every geometry word the combine pass
-  // reads is written by the attention pass of the same call first, so what an earlier call left
-  // behind is never observed.
+  // The only words that must start at zero are the per-unit arrival counters (16 KB); the kernel
+  // leaves them at zero itself, but they are cleared here as well so that a call cut short (a fault
+  // in an earlier launch) cannot poison the next one.  Records and geometry words are always written
+  // before they are read within one call, so their old contents are never observed.
+  rc = attn_decode_zero_counters(scratch, (cudaStream_t)stream);
+  if (rc != 0) return rc;
   return launch_attn_decode((const bf16*)q, (const bf16*)k_pages, (const bf16*)v_pages, block_table, bt_stride, seq_lens, scratch,
                             (bf16*)out, B, nq, nkv, hd, block_size, (cudaStream_t)stream);
 }

@@ -76,12 +76,12 @@ extern "C" int b2k_lmhead_argmax(const void* x, const void* w, void* logits, int
   B2_REQUIRE(scratch_u64 != nullptr, "b2k_lmhead_argmax: the tcgen05 path needs T uint64 of scratch");
   B2_CUDA_OK(cudaMemsetAsync(scratch_u64, 0, sizeof(unsigned long long) * (size_t)T, s));
   TcGemmArgs a;
-  a.bn = tc_pick_bn(T);
-  CAPI_TRY(b2_make_tmap_bf16(&a.tmap_w, w, (uint64_t)V, (uint64_t)K, (uint64_t)K, 128));
-  CAPI_TRY(b2_make_tmap_bf16(&a.tmap_x, x, (uint64_t)T, (uint64_t)K, (uint64_t)K, (uint32_t)a.bn));
+  a.bn = 128;  // tokens on MMA-M, 128 vocabulary rows per tile on MMA-N (see TC_EPI_ARGMAX_ROWS)
+  CAPI_TRY(b2_make_tmap_bf16(&a.tmap_w, x, (uint64_t)T, (uint64_t)K, (uint64_t)K, 128));
+  CAPI_TRY(b2_make_tmap_bf16(&a.tmap_x, w, (uint64_t)V, (uint64_t)K, (uint64_t)K, 128));
   a.T = T; a.N = V; a.K = K;
   a.nsplit = 1;
-  a.epilogue = TC_EPI_ARGMAX;
+  a.epilogue = TC_EPI_ARGMAX_ROWS;
   a.out = logits;
   a.argmax_packed = (unsigned long long*)scratch_u64;
   CAPI_TRY(launch_linear_tc(a, s));
@@ -96,6 +96,7 @@ extern "C" int b2k_attn_decode(const void* q, const void* k_pages, const void* v
                                const int32_t* seq_lens, void* scratch_f32, void* out, int B, int nq, int nkv, int hd,
                                int block_size, void* stream) {
   B2_REQUIRE(q && k_pages && v_pages && block_table && seq_lens && out && scratch_f32, "b2k_attn_decode: null pointer");
+  CAPI_TRY(attn_decode_zero_counters((float*)scratch_f32, (cudaStream_t)stream));  // callers hand in arbitrary memory
   return launch_attn_decode((const bf16*)q, (const bf16*)k_pages, (const bf16*)v_pages, block_table, bt_stride, seq_lens,
                             (float*)scratch_f32, (bf16*)out, B, nq, nkv, hd, block_size, (cudaStream_t)stream);
 }

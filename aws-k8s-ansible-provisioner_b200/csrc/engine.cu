@@ -307,16 +307,10 @@ int forward(b2_engine* e, int T, int ntiles, int nlast, int attn_split) {
       if (!k.skip()) B2_TRY(launch_attn_prefill(e->qrot, kp, vp, e->d_block_table, e->bt_stride, e->d_tiles, ntiles, e->attn,
                                  c.num_q_heads, c.num_kv_heads, c.head_dim, c.block_size, e->stream));
     } else {
-      {
-        KL k(e, B2K_ATTN_DECODE);
-        if (!k.skip())
-          B2_TRY(launch_attn_decode_pass(e->qrot, kp, vp, e->d_block_table, e->bt_stride, e->d_seq_lens, e->attn_scratch, T,
-                                         c.num_q_heads, c.num_kv_heads, c.head_dim, c.block_size, e->stream));
-      }
-      {
-        KL k(e, B2K_ATTN_COMBINE);
-        if (!k.skip()) B2_TRY(launch_attn_combine(e->attn_scratch, e->attn, T, c.num_q_heads, c.num_kv_heads, e->stream));
-      }
+      KL k(e, B2K_ATTN_DECODE);
+      if (!k.skip())
+        B2_TRY(launch_attn_decode(e->qrot, kp, vp, e->d_block_table, e->bt_stride, e->d_seq_lens, e->attn_scratch, e->attn, T,
+                                  c.num_q_heads, c.num_kv_heads, c.head_dim, c.block_size, e->stream));
     }
     ActIn o = linear(e, B2K_GEMM_O, XB_ATTN, e->attn, L.wo, L.tm_o, e->proj, T, H, e->q_size, &rc, prefetch_for(l + 1, 0));
     B2_TRY(rc);
@@ -364,12 +358,14 @@ int forward(b2_engine* e, int T, int ntiles, int nlast, int attn_split) {
     if (!k2.skip()) B2_TRY(launch_argmax_rows(e->logits, e->d_out_tokens, nlast, c.vocab, e->stream));
   } else {
     TcGemmArgs a;
-    a.tmap_w = e->tm_lm_head;
-    a.bn = tc_pick_bn(nlast);
-    a.tmap_x = e->tm_x[xb][bn_index(a.bn)];
+    // operands trade places for the fused arg-max: tokens on MMA-M (128-row box of X), 128 vocabulary
+    // rows per tile on MMA-N
+    a.bn = 128;
+    a.tmap_w = e->tm_x[xb][bn_index(128)];
+    a.tmap_x = e->tm_lm_head;
     a.T = nlast; a.N = c.vocab; a.K = H;
     a.nsplit = 1;
-    a.epilogue = TC_EPI_ARGMAX;
+    a.epilogue = TC_EPI_ARGMAX_ROWS;
     a.out = logits;
     a.argmax_packed = e->d_argmax;
     {
@@ -750,6 +746,7 @@ extern "C" int b2_engine_create(const b2_config* cfg, const char* safetensors_pa
     E_TRY(dalloc(&e->partial, e->partial_floats));
     e->attn_scratch_floats = attn_decode_scratch_floats(bucket_batch(c.max_seqs), c.num_q_heads, c.num_kv_heads, c.head_dim);
     E_TRY(dalloc(&e->attn_scratch, e->attn_scratch_floats));
+    E_CUDA(cudaMemset(e->attn_scratch, 0, e->attn_scratch_floats * sizeof(float)));  // arrival counters start at zero
     for (int bi = 0; bi < 5; ++bi) {
       E_TRY(b2_make_tmap_bf16(&e->tm_x[XB_X][bi], e->x, Tc, H, H, kBnList[bi]));
       E_TRY(b2_make_tmap_bf16(&e->tm_x[XB_ATTN][bi], e->attn, Tc, e->q_size, e->q_size, kBnList[bi]));

@@ -10,8 +10,12 @@
 //                TC_EPI_BF16        round to bf16, store y[T][N]
 //                TC_EPI_F32_PARTIAL store fp32 split-K partial [split][T][N] (summed in split
 //                                   order by the consumer kernel -> deterministic)
-//                TC_EPI_ARGMAX      lm_head: round to bf16, fused arg-max (lowest index on
+//                TC_EPI_ARGMAX      round to bf16, fused arg-max over the weight rows (lowest index on
 //                                   ties) via one 64-bit atomicMax per token per tile
+//                TC_EPI_ARGMAX_ROWS lm_head: operands trade places (tokens are MMA-M, vocabulary rows
+//                                   are MMA-N), so one epilogue thread owns one token and scans its
+//                                   logits with a running (value, -index) maximum in registers across
+//                                   all of the CTA's tiles: no shuffles, one atomicMax per token per CTA
 // Split-K (gridDim.z) exists because N/128 row tiles alone cannot fill 148 SMs for the
 // 1024-row projections; HBM bandwidth needs every SM streaming.
 #include "kernels.h"
@@ -66,6 +70,7 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
   __shared__ __align__(8) uint64_t tmem_empty_bar[2];
   __shared__ uint32_t tmem_slot;
   __shared__ unsigned long long amax_red[EPI == TC_EPI_ARGMAX ? 4 * BN : 1];
+  (void)amax_red;
 
   if (threadIdx.x == 0) tc_stamp(0);  // CTA started
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -183,6 +188,8 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
     }
   } else {
     const int q = warp & 3;  // TMEM lane quarter this warp may access
+    unsigned long long row_best = 0ull;  // TC_EPI_ARGMAX_ROWS: running arg-max of this thread's token
+    int row_best_tok = -1;
     pdl_wait();
     if (pf.k_pages != nullptr) {
       // These four warps idle until the first accumulator is ready: spend the time asking the TMA
@@ -216,7 +223,42 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
       const int tok0 = n_tile * BN;
       const bool full = row_ok && tok0 + BN <= T;  // whole tile in range: no per-element predicates
       const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN);
-      if (EPI == TC_EPI_F32_PARTIAL) {
+      if (EPI == TC_EPI_ARGMAX_ROWS) {
+        // here the accumulator row is a TOKEN and the columns are vocabulary entries col0 .. col0+BN
+        const int tok = row, col0 = n_tile * BN;
+        if (tok != row_best_tok) {
+          if (row_best_tok >= 0 && row_best_tok < T && row_best != 0ull) atomicMax(argmax_packed + row_best_tok, row_best);
+          row_best = 0ull;
+          row_best_tok = tok;
+        }
+#pragma unroll 1
+        for (int c0 = 0; c0 < BN; c0 += 32) {
+          uint32_t r[32];
+          tmem_ld32(tbase + (uint32_t)c0, r);
+          tmem_ld_wait();
+          uint32_t packed[16];
+#pragma unroll
+          for (int j = 0; j < 32; j += 2) {
+            const float a = __uint_as_float(r[j]), b = __uint_as_float(r[j + 1]);
+            packed[j >> 1] = pack_bf16x2(a, b);
+            const float la = bf16lo(packed[j >> 1]), lb = bf16hi(packed[j >> 1]);
+            const int ca = col0 + c0 + j;
+            if (ca < N && la == la) { const unsigned long long p = tc_argmax_pack(la, ca); row_best = p > row_best ? p : row_best; }
+            if (ca + 1 < N && lb == lb) { const unsigned long long p = tc_argmax_pack(lb, ca + 1); row_best = p > row_best ? p : row_best; }
+          }
+          if (out != nullptr && tok < T) {
+            bf16* d = reinterpret_cast<bf16*>(out) + (size_t)tok * N + col0 + c0;
+            if (col0 + c0 + 32 <= N) {
+#pragma unroll
+              for (int v4 = 0; v4 < 4; ++v4)
+                reinterpret_cast<uint4*>(d)[v4] = make_uint4(packed[4 * v4], packed[4 * v4 + 1], packed[4 * v4 + 2], packed[4 * v4 + 3]);
+            } else {
+              for (int j = 0; j < 32 && col0 + c0 + j < N; ++j)
+                d[j] = __ushort_as_bfloat16((unsigned short)((j & 1) ? (packed[j >> 1] >> 16) : (packed[j >> 1] & 0xffffu)));
+            }
+          }
+        }
+      } else if (EPI == TC_EPI_F32_PARTIAL) {
         float* dst = reinterpret_cast<float*>(out) + ((size_t)split * T + tok0) * N + row;  // + j * N per token
         if (BN == 16) {
           uint32_t r[16];
@@ -307,6 +349,8 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
         asm volatile("bar.sync 1, 128;" ::: "memory");  // amax_red is rewritten by the next tile
       }
     }
+    if (EPI == TC_EPI_ARGMAX_ROWS && row_best_tok >= 0 && row_best_tok < T && row_best != 0ull)
+      atomicMax(argmax_packed + row_best_tok, row_best);
   }
   tc_fence_before();
   __syncthreads();
@@ -387,7 +431,10 @@ static int launch_one(const TcGemmArgs& a, int kb_per_split, cudaStream_t s) {
   using C = TcCfg<BN>;
   static B2PerDeviceOnce attr_once;
   if (attr_once.need()) B2_CUDA_OK(cudaFuncSetAttribute(linear_tc_kernel<BN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
-  const int m_tiles = (a.N + TC_BM - 1) / TC_BM, n_tiles = (a.T + BN - 1) / BN;
+  // TC_EPI_ARGMAX_ROWS: tokens are the 128-row M tiles and weight rows the BN-wide N tiles
+  const bool rows_mode = (EPI == TC_EPI_ARGMAX_ROWS);
+  const int m_tiles = rows_mode ? (a.T + TC_BM - 1) / TC_BM : (a.N + TC_BM - 1) / TC_BM;
+  const int n_tiles = rows_mode ? (a.N + BN - 1) / BN : (a.T + BN - 1) / BN;
   const int total = m_tiles * n_tiles * a.nsplit;
   static int sms = device_num_sms();
   const int grid = total < sms ? total : sms;
@@ -402,6 +449,7 @@ static int launch_bn(const TcGemmArgs& a, int kps, cudaStream_t s) {
     case TC_EPI_BF16: return launch_one<BN, TC_EPI_BF16>(a, kps, s);
     case TC_EPI_F32_PARTIAL: return launch_one<BN, TC_EPI_F32_PARTIAL>(a, kps, s);
     case TC_EPI_ARGMAX: return launch_one<BN, TC_EPI_ARGMAX>(a, kps, s);
+    case TC_EPI_ARGMAX_ROWS: return launch_one<BN, TC_EPI_ARGMAX_ROWS>(a, kps, s);
   }
   b2_set_error("linear_tc: bad epilogue %d", a.epilogue);
   return -22;

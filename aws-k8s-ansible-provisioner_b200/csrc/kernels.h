@@ -51,10 +51,10 @@ struct KvPrefetch {
 };
 
 // ---- gemm_tc.cu ----
-enum TcEpilogue { TC_EPI_BF16 = 0, TC_EPI_F32_PARTIAL = 1, TC_EPI_ARGMAX = 2 };
+enum TcEpilogue { TC_EPI_BF16 = 0, TC_EPI_F32_PARTIAL = 1, TC_EPI_ARGMAX = 2, TC_EPI_ARGMAX_ROWS = 3 };
 struct TcGemmArgs {
-  CUtensorMap tmap_w;  // W [N][K], box 64 x 128
-  CUtensorMap tmap_x;  // X [>=T rows][K], box 64 x bn
+  CUtensorMap tmap_w;  // W [N][K], box 64 x 128   (TC_EPI_ARGMAX_ROWS: the operands trade places -- this is X, box 64 x 128)
+  CUtensorMap tmap_x;  // X [>=T rows][K], box 64 x bn  (TC_EPI_ARGMAX_ROWS: W [N][K], box 64 x bn)
   int bn;              // token tile: 16, 32, 64, 128 or 256
   int T, N, K;
   int nsplit;          // split-K factor (EPI_F32_PARTIAL when > 1)
@@ -75,11 +75,8 @@ int tc_pick_nsplit(int T, int N, int K, int num_sms);
 // pages goes through this one function.
 __host__ __device__ inline int kv_swizzled_chunk(int row_in_page, int chunk) { return chunk ^ (row_in_page & 7); }
 size_t attn_decode_scratch_floats(int B, int nq, int nkv, int hd);
-int launch_attn_decode_pass(const bf16* q, const bf16* k_pages, const bf16* v_pages, const int32_t* block_table,
-                            int bt_stride, const int32_t* seq_lens, float* scratch, int B, int nq, int nkv, int hd,
-                            int block_size, cudaStream_t s);
-int launch_attn_combine(const float* scratch, bf16* out, int B, int nq, int nkv, cudaStream_t s);
-// attention pass + combine pass (two launches)
+// scratch counters must be zero at launch (attn_decode_zero_counters once; the kernel re-zeroes them)
+int attn_decode_zero_counters(float* scratch, cudaStream_t s);
 int launch_attn_decode(const bf16* q, const bf16* k_pages, const bf16* v_pages, const int32_t* block_table,
                        int bt_stride, const int32_t* seq_lens, float* scratch, bf16* out, int B, int nq, int nkv,
                        int hd, int block_size, cudaStream_t s);
