@@ -27,13 +27,11 @@
 
 namespace b2 {
 
-constexpr int AD_WARPS = 8;
-constexpr int AD_STAGES = 3;
+constexpr int AD_WARPS_MAX = 16;
 constexpr int AD_BS = 16;    // tokens per KV page
 constexpr int AD_HD = 128;   // head dim
 constexpr int AD_TILE = AD_BS * AD_HD * 2;       // 4096 B: one page-slice of K (or V) for one kv head
 constexpr int AD_STAGE = 2 * AD_TILE;            // K + V
-constexpr int AD_SMEM = AD_WARPS * AD_STAGES * AD_STAGE;  // 192 KB
 constexpr int AD_MAX_B = 512;
 constexpr int AD_MAX_CTAS = 160;
 constexpr int AD_CNT = 4096;                     // per-unit arrival counters (ints) after the geometry header; zero between launches
@@ -62,6 +60,7 @@ struct AdPos {  // a position on the page line
   int b, kvh, j, nb;
 };
 
+template <int AD_WARPS, int AD_STAGES>
 __global__ void __launch_bounds__(AD_WARPS * 32, 1)
 attn_decode_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k_pages, const bf16* __restrict__ v_pages,
                    const int32_t* __restrict__ block_table, int bt_stride, const int32_t* __restrict__ seq_lens,
@@ -188,6 +187,55 @@ attn_decode_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k_pages,
   float m_run[2], l_run[2];
   bool fresh = true;  // (re)load q and reset the running state at the next tile
 
+  // Arrival + merge of one unit, deferred to the end of the warp's run so that the fence and the
+  // atomic round trip never stall the TMA pipeline mid-stream.
+  auto arrive_and_maybe_merge = [&](int unit) {
+    float* recs = scratch + AD_META;
+    // which warps' runs touch this unit (inverse of the partition above)
+    const int ub = unit / nkv, ukvh = unit - ub * nkv;
+    const int unb = s_prefix[ub + 1] - s_prefix[ub];
+    const int u0 = s_prefix[ub] * nkv + ukvh * unb;
+    const int cut = rem * (base + 1);
+    const int w0 = u0 < cut ? u0 / (base + 1) : rem + (u0 - cut) / base;
+    const int ulast = u0 + unb - 1;
+    const int w1 = ulast < cut ? ulast / (base + 1) : rem + (ulast - cut) / base;
+    int* cnt = reinterpret_cast<int*>(scratch) + 1024 + unit;
+    __threadfence();  // this warp's record is visible before its arrival is
+    __syncwarp();
+    int prev = 0;
+    if (lane == 0) prev = atomicAdd(cnt, 1);
+    prev = __shfl_sync(0xffffffffu, prev, 0);
+    if (prev == w1 - w0) {  // last to arrive: merge in run order and write the output
+      __threadfence();
+      if (lane == 0) *cnt = 0;  // ready for the next launch
+      float M[2] = {-INFINITY, -INFINITY};
+      for (int w = w0; w <= w1; ++w) {
+        const float* r2 = recs + (size_t)(unit + w) * AD_REC + 2 * AD_HD;
+        M[0] = fmaxf(M[0], __ldcg(r2 + 0));
+        M[1] = fmaxf(M[1], __ldcg(r2 + 1));
+      }
+      float O[8], L[2] = {0.f, 0.f};  // lane covers 8 of the 256 (head, dim) outputs: head = lane / 16
+#pragma unroll
+      for (int e = 0; e < 8; ++e) O[e] = 0.f;
+      const int hh = lane >> 4, d0 = (lane & 15) * 8;
+      for (int w = w0; w <= w1; ++w) {
+        const float* r2 = recs + (size_t)(unit + w) * AD_REC;
+        const float f = expf(__ldcg(r2 + 2 * AD_HD + hh) - M[hh]);
+        const float4 a = __ldcg(reinterpret_cast<const float4*>(r2 + hh * AD_HD + d0));
+        const float4 b = __ldcg(reinterpret_cast<const float4*>(r2 + hh * AD_HD + d0 + 4));
+        O[0] = fmaf(f, a.x, O[0]); O[1] = fmaf(f, a.y, O[1]); O[2] = fmaf(f, a.z, O[2]); O[3] = fmaf(f, a.w, O[3]);
+        O[4] = fmaf(f, b.x, O[4]); O[5] = fmaf(f, b.y, O[5]); O[6] = fmaf(f, b.z, O[6]); O[7] = fmaf(f, b.w, O[7]);
+        L[hh] = fmaf(f, __ldcg(r2 + 2 * AD_HD + 2 + hh), L[hh]);
+      }
+      const float inv = L[hh] > 0.f ? __fdiv_rn(1.0f, L[hh]) : 0.f;
+#pragma unroll
+      for (int e = 0; e < 8; ++e) O[e] *= inv;
+      *reinterpret_cast<uint4*>(out + ((size_t)ub * nq + ukvh * 2 + hh) * AD_HD + d0) = pack8(O);
+    }
+  };
+  int pending[8];
+  int npending = 0;
+
   for (int n = 0; n < ntiles; ++n) {
     if (fresh) {
       const bf16* qp = q + ((size_t)cur.b * nq + (size_t)cur.kvh * 2 + (g & 1)) * AD_HD;
@@ -309,50 +357,12 @@ attn_decode_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k_pages,
         rec[2 * AD_HD + 2] = l_run[0];
         rec[2 * AD_HD + 3] = l_run[1];
       }
-      // which warps' runs touch this unit (inverse of the partition above)
-      const int ub = unit / nkv, ukvh = unit - ub * nkv;
-      const int unb = s_prefix[ub + 1] - s_prefix[ub];
-      const int u0 = s_prefix[ub] * nkv + ukvh * unb;
-      const int cut = rem * (base + 1);
-      const int w0 = u0 < cut ? u0 / (base + 1) : rem + (u0 - cut) / base;
-      const int ulast = u0 + unb - 1;
-      const int w1 = ulast < cut ? ulast / (base + 1) : rem + (ulast - cut) / base;
-      int* cnt = reinterpret_cast<int*>(scratch) + 1024 + unit;
-      __threadfence();  // this warp's record is visible before its arrival is
-      __syncwarp();
-      int prev = 0;
-      if (lane == 0) prev = atomicAdd(cnt, 1);
-      prev = __shfl_sync(0xffffffffu, prev, 0);
-      if (prev == w1 - w0) {  // last to arrive: merge in run order and write the output
-        __threadfence();
-        if (lane == 0) *cnt = 0;  // ready for the next launch
-        float M[2] = {-INFINITY, -INFINITY};
-        for (int w = w0; w <= w1; ++w) {
-          const float* r2 = recs + (size_t)(unit + w) * AD_REC + 2 * AD_HD;
-          M[0] = fmaxf(M[0], __ldcg(r2 + 0));
-          M[1] = fmaxf(M[1], __ldcg(r2 + 1));
-        }
-        float O[8], L[2] = {0.f, 0.f};  // lane covers 8 of the 256 (head, dim) outputs: head = lane / 16
-#pragma unroll
-        for (int e = 0; e < 8; ++e) O[e] = 0.f;
-        const int hh = lane >> 4, d0 = (lane & 15) * 8;
-        for (int w = w0; w <= w1; ++w) {
-          const float* r2 = recs + (size_t)(unit + w) * AD_REC;
-          const float f = expf(__ldcg(r2 + 2 * AD_HD + hh) - M[hh]);
-          const float4 a = __ldcg(reinterpret_cast<const float4*>(r2 + hh * AD_HD + d0));
-          const float4 b = __ldcg(reinterpret_cast<const float4*>(r2 + hh * AD_HD + d0 + 4));
-          O[0] = fmaf(f, a.x, O[0]); O[1] = fmaf(f, a.y, O[1]); O[2] = fmaf(f, a.z, O[2]); O[3] = fmaf(f, a.w, O[3]);
-          O[4] = fmaf(f, b.x, O[4]); O[5] = fmaf(f, b.y, O[5]); O[6] = fmaf(f, b.z, O[6]); O[7] = fmaf(f, b.w, O[7]);
-          L[hh] = fmaf(f, __ldcg(r2 + 2 * AD_HD + 2 + hh), L[hh]);
-        }
-        const float inv = L[hh] > 0.f ? __fdiv_rn(1.0f, L[hh]) : 0.f;
-#pragma unroll
-        for (int e = 0; e < 8; ++e) O[e] *= inv;
-        *reinterpret_cast<uint4*>(out + ((size_t)ub * nq + ukvh * 2 + hh) * AD_HD + d0) = pack8(O);
-      }
+      if (npending < 8) pending[npending++] = unit;
+      else arrive_and_maybe_merge(unit);  // (never in practice: > 8 unit ends in one run)
       fresh = true;
     }
   }
+  for (int i = 0; i < npending; ++i) arrive_and_maybe_merge(pending[i]);
   if (dbg_time) {  // timing breadcrumbs for tools/attn_timeline.py (unused words of the geometry header)
     unsigned long long t_end;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_end));
@@ -362,15 +372,28 @@ attn_decode_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k_pages,
   }
 }
 
+size_t attn_decode_scratch_floats(int B, int nq, int nkv, int hd) {
+  (void)nq;
+  (void)hd;
+  return (size_t)AD_META + ((size_t)B * nkv + (size_t)AD_MAX_CTAS * AD_WARPS_MAX) * AD_REC;
+}
+
+// (warps per CTA, pipeline stages per warp): 8 x 3 x 8 KB = 192 KB of K/V in flight per SM.
+// B2_ATTN_CFG=<warps>x<stages> selects another built shape for experiments.
 static int ad_grid() {
   static int sms = device_num_sms();
   return sms < AD_MAX_CTAS ? sms : AD_MAX_CTAS;
 }
 
-size_t attn_decode_scratch_floats(int B, int nq, int nkv, int hd) {
-  (void)nq;
-  (void)hd;
-  return (size_t)AD_META + ((size_t)B * nkv + (size_t)AD_MAX_CTAS * AD_WARPS) * AD_REC;
+template <int W, int S>
+static int launch_cfg(const bf16* q, const bf16* k_pages, const bf16* v_pages, const int32_t* block_table, int bt_stride,
+                      const int32_t* seq_lens, float* scratch, bf16* out, int B, int nq, int nkv, float scale, cudaStream_t s) {
+  constexpr int SMEM = W * S * AD_STAGE;
+  static B2PerDeviceOnce attr_once;
+  if (attr_once.need()) B2_CUDA_OK(cudaFuncSetAttribute(attn_decode_kernel<W, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
+  B2_CUDA_OK(b2_launch(attn_decode_kernel<W, S>, dim3(ad_grid()), dim3(W * 32), (size_t)SMEM, s, q, k_pages, v_pages, block_table,
+                       bt_stride, seq_lens, scratch, out, B, nq, nkv, scale));
+  return 0;
 }
 
 // scratch: attn_decode_scratch_floats() floats; its counter words (AD_CNT ints after the first 1024)
@@ -383,12 +406,27 @@ int launch_attn_decode(const bf16* q, const bf16* k_pages, const bf16* v_pages, 
   B2_REQUIRE(nq == 2 * nkv, "attn_decode: built for a GQA group of 2 (nq=%d nkv=%d)", nq, nkv);
   B2_REQUIRE(B <= AD_MAX_B && B * nkv <= AD_CNT, "attn_decode: batch %d x %d kv heads exceeds %d units", B, nkv, AD_CNT);
   B2_REQUIRE(scratch != nullptr, "attn_decode: scratch required");
-  static B2PerDeviceOnce attr_once;
-  if (attr_once.need()) B2_CUDA_OK(cudaFuncSetAttribute(attn_decode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AD_SMEM));
   const float scale = (float)(1.0 / sqrt((double)hd));  // HF passes head_dim**-0.5 as a double
-  B2_CUDA_OK(b2_launch(attn_decode_kernel, dim3(ad_grid()), dim3(AD_WARPS * 32), (size_t)AD_SMEM, s, q, k_pages, v_pages,
-                       block_table, bt_stride, seq_lens, scratch, out, B, nq, nkv, scale));
-  return 0;
+  static int cfg = -1;
+  if (cfg < 0) {
+    const char* e = getenv("B2_ATTN_CFG");
+    cfg = 83;
+    if (e) { int w = 0, st = 0; if (sscanf(e, "%dx%d", &w, &st) == 2) cfg = w * 10 + st; }
+  }
+#define AD_CASE(W, S) case (W) * 10 + (S): return launch_cfg<W, S>(q, k_pages, v_pages, block_table, bt_stride, seq_lens, scratch, out, B, nq, nkv, scale, s)
+  switch (cfg) {
+    AD_CASE(8, 3);
+    AD_CASE(6, 4);
+    AD_CASE(12, 2);
+    AD_CASE(9, 3);
+    AD_CASE(13, 2);
+    AD_CASE(4, 6);
+    AD_CASE(8, 2);
+    AD_CASE(16, 1);
+  }
+#undef AD_CASE
+  b2_set_error("attn_decode: B2_ATTN_CFG shape %d not built", cfg);
+  return -22;
 }
 
 int attn_decode_zero_counters(float* scratch, cudaStream_t s) {

@@ -22,10 +22,13 @@ sl = torch.full((B,), S, dtype=torch.int32).cuda()
 q = torch.randn(B, nq * hd, generator=g).to(torch.bfloat16).cuda()
 out = torch.empty(B, nq * hd, dtype=torch.bfloat16, device="cuda")
 scratch = torch.zeros(lib.b2k_attn_decode_scratch_floats(B, nq, nkv, hd), dtype=torch.float32, device="cuda")
-flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
-for it in range(6):
-    if not NOFLUSH:
-        flush.zero_()
+# several independent K/V sets, visited round-robin, so nothing read is L2-resident and no dirty
+# lines have to be written back during the measurement (a memset flush would add write traffic)
+NSETS = 1 if NOFLUSH else 4
+sets = [(kp, vp)] + [(torch.randn_like(kp), torch.randn_like(vp)) for _ in range(NSETS - 1)]
+times = []
+for it in range(8):
+    kp, vp = sets[it % NSETS]
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
@@ -33,11 +36,19 @@ for it in range(6):
     e1.record()
     torch.cuda.synchronize()
     assert rc == 0
+    times.append(e0.elapsed_time(e1) * 1e3)
 meta = scratch.view(torch.int32)[:1024].cpu().numpy()
 st, en = meta[600:600 + 2 * 148:2].astype(np.int64), meta[601:601 + 2 * 148:2].astype(np.int64)
+live = st > 0
+st, en = st[live], en[live]
 t0 = st.min()
 dur = en - st
-print("mode", mode, "S", S, "event ms", e0.elapsed_time(e1), "bytes MB", B * S * 4096 / 1e6)
+print("cfg", os.environ.get("B2_ATTN_CFG", "8x3"), "mode", mode, "B", B, "S", S, "event us (last 5): %s" % ["%.1f" % t for t in times[-5:]], "MB %.1f" % (B * S * 4096 / 1e6))
 print("start skew us: max %.2f" % ((st.max() - t0) / 1e3), " end: min %.2f median %.2f max %.2f us" % ((en.min() - t0) / 1e3, np.median(en - t0) / 1e3, (en.max() - t0) / 1e3))
 print("per-CTA duration us: min %.2f p10 %.2f median %.2f p90 %.2f max %.2f" % tuple(np.percentile(dur, [0, 10, 50, 90, 100]) / 1e3))
 print("ideal at 6539.5 GB/s: %.2f us" % (B * S * 4096 / 6539.5e9 * 1e6))
+if os.environ.get("DUMP"):
+    allst = meta[600:600 + 2 * 148:2].astype(np.int64); allen = meta[601:601 + 2 * 148:2].astype(np.int64)
+    d = (allen - allst) / 1e3
+    print("per-CTA us by blockIdx:", " ".join("%.1f" % x for x in d))
+    print("start offsets us:", " ".join("%.1f" % ((x - allst[allst > 0].min()) / 1e3) for x in allst))
