@@ -148,7 +148,9 @@ struct b2_engine {
   unsigned skip_mask = 0;
   long long kv_l2_budget = 0;      // B2_KV_L2_MB: bytes of next-layer K/V the projections prefetch into L2 (0 = off)
   int32_t* d_pf_frac = nullptr;
-  int32_t* d_sample_out = nullptr;  // B2_SKIP_MASK: kernel classes left out (timing ablations only; results are garbage)
+  int32_t* d_sample_out = nullptr;
+  unsigned* d_gbar = nullptr;     // grid-barrier words of the decode chain kernel
+  int use_chain = 1;              // B2_CHAIN=0: decode through the separate per-step kernels (A/B runs, hidden-state capture)  // B2_SKIP_MASK: kernel classes left out (timing ablations only; results are garbage)
 };
 
 namespace {
@@ -259,10 +261,84 @@ void dbg_capture(b2_engine* e, int slot, const bf16* src, int T) {
 // decode, d_seq_lens/d_block_table rows 0..T-1).  prefill_tiles > 0 selects the causal prefill
 // attention; nlast = number of rows that get logits (decode: T; prefill: one per sequence,
 // gathered through d_last_rows).
+int lm_head_and_argmax(b2_engine* e, int nlast, const bf16* xl, XBuf xb);
+
+// Decode forward (one token per sequence): embedding, then per layer ONE attention launch and ONE
+// chain launch (chain.cu) instead of ten separate kernels.
+int forward_decode_chain(b2_engine* e, int T) {
+  const b2_config& c = e->cfg;
+  const int H = c.hidden, I = c.intermediate, L = c.num_layers;
+  {
+    KL k(e, B2K_EMBED);
+    if (!k.skip()) B2_TRY(launch_embed(e->d_tokens, e->embed, e->h, T, H, c.vocab, e->d_argmax, T, e->stream));
+  }
+  const int bn = tc_pick_bn(T), bi = bn_index(bn);
+  auto gemm_cfg = [&](int N, int K) {
+    ChainGemm g;
+    g.N = N; g.K = K;
+    int ns = tc_pick_nsplit(T, N, K, e->num_sms);
+    while (ns > 1 && (size_t)ns * T * N > e->partial_floats) --ns;
+    const int kb = K / 64;
+    g.kps = (kb + ns - 1) / ns;
+    g.nsplit = (kb + g.kps - 1) / g.kps;
+    return g;
+  };
+  ChainParams p;
+  memset(&p, 0, sizeof p);
+  p.T = T; p.bn = bn;
+  p.g[0] = gemm_cfg(H, e->q_size);
+  p.g[1] = gemm_cfg(2 * I, H);
+  p.g[2] = gemm_cfg(H, I);
+  p.g[3] = gemm_cfg(e->qkv_size, H);
+  p.partial = e->partial;
+  p.h = e->h; p.x = e->x; p.act = e->act; p.qrot = e->qrot;
+  p.cos_sin = e->cos_sin; p.positions = e->d_positions; p.slots = e->d_slots;
+  p.H = H; p.I = I; p.nq = c.num_q_heads; p.nkv = c.num_kv_heads; p.block_size = c.block_size; p.eps = c.rms_eps;
+  p.gbar = e->d_gbar;
+  CUtensorMap xm[4] = {e->tm_x[XB_ATTN][bi], e->tm_x[XB_X][bi], e->tm_x[XB_ACT][bi], e->tm_x[XB_X][bi]};
+  auto kv_of = [&](int l, bf16** kp, bf16** vp) {
+    *kp = e->kv_pool + (size_t)(2 * l) * e->layer_kv_elems;
+    *vp = *kp + e->layer_kv_elems;
+  };
+  {  // head of the forward: ln1 of layer 0 on the embeddings, QKV(0), QK-norm/RoPE/KV(0)
+    LayerW& L0 = e->layers[0];
+    CUtensorMap wm[4] = {L0.tm_o, L0.tm_gu, L0.tm_d, L0.tm_qkv};
+    p.phase_begin = 5; p.phase_end = 8;
+    p.norm_w_a = L0.ln2; p.norm_w_b = L0.ln1; p.norm_b_has_delta = 0;
+    p.qw = L0.qnorm; p.kw = L0.knorm;
+    kv_of(0, &p.k_pages, &p.v_pages);
+    KL k(e, B2K_CHAIN);
+    if (!k.skip()) B2_TRY(launch_decode_chain(wm, xm, p, e->stream));
+  }
+  for (int l = 0; l < L; ++l) {
+    LayerW& Lw = e->layers[l];
+    bf16 *kp, *vp;
+    kv_of(l, &kp, &vp);
+    {
+      KL k(e, B2K_ATTN_DECODE);
+      if (!k.skip())
+        B2_TRY(launch_attn_decode(e->qrot, kp, vp, e->d_block_table, e->bt_stride, e->d_seq_lens, e->attn_scratch, e->attn, T,
+                                  c.num_q_heads, c.num_kv_heads, c.head_dim, c.block_size, e->stream));
+    }
+    const bool last = (l + 1 == L);
+    LayerW& Ln = e->layers[last ? l : l + 1];
+    CUtensorMap wm[4] = {Lw.tm_o, Lw.tm_gu, Lw.tm_d, Ln.tm_qkv};
+    p.phase_begin = 0; p.phase_end = last ? 6 : 8;
+    p.norm_w_a = Lw.ln2; p.norm_w_b = last ? e->final_norm : Ln.ln1; p.norm_b_has_delta = 1;
+    p.qw = Ln.qnorm; p.kw = Ln.knorm;
+    kv_of(last ? l : l + 1, &p.k_pages, &p.v_pages);
+    KL k(e, B2K_CHAIN);
+    if (!k.skip()) B2_TRY(launch_decode_chain(wm, xm, p, e->stream));
+  }
+  return lm_head_and_argmax(e, T, e->x, XB_X);
+}
+
 int forward(b2_engine* e, int T, int ntiles, int nlast, int attn_split) {
   const b2_config& c = e->cfg;
   const int H = c.hidden, I = c.intermediate;
   int rc = 0;
+  if (ntiles == 0 && e->use_chain && !(e->debug_flags & 1) && e->force_gemm_impl != 0 && T > e->simt_max_tokens)
+    return forward_decode_chain(e, T);
   {
     KL k(e, B2K_EMBED);
     if (!k.skip()) B2_TRY(launch_embed(e->d_tokens, e->embed, e->h, T, H, c.vocab, e->d_argmax, nlast, e->stream));
@@ -343,6 +419,12 @@ int forward(b2_engine* e, int T, int ntiles, int nlast, int attn_split) {
     xl = e->xlast;
     xb = XB_LAST;
   }
+  return lm_head_and_argmax(e, nlast, xl, xb);
+}
+
+int lm_head_and_argmax(b2_engine* e, int nlast, const bf16* xl, XBuf xb) {
+  const b2_config& c = e->cfg;
+  const int H = c.hidden;
   bf16* logits = (e->debug_flags & 2) ? e->logits : nullptr;
   int impl = e->force_gemm_impl >= 0 ? e->force_gemm_impl : (nlast <= e->simt_max_tokens ? 0 : 1);
   if (impl == 0) {
@@ -661,6 +743,7 @@ extern "C" int b2_engine_create(const b2_config* cfg, const char* safetensors_pa
   e->attn_split_override = env_int("B2_ATTN_SPLITS", 0);
   e->force_gemm_impl = env_int("B2_GEMM_IMPL", -1);
   e->skip_mask = (unsigned)env_int("B2_SKIP_MASK", 0);
+  e->use_chain = env_int("B2_CHAIN", 1);
   // Off by default: measured on B200 at C2 (ms/step) 0 MB 2.22, 40 MB 2.24, 72 MB 2.33, 100 MB 2.38 --
   // un-paced prefetch bursts queue ahead of the projections' own latency-critical weight loads.
   e->kv_l2_budget = (long long)env_int("B2_KV_L2_MB", 0) << 20;
@@ -774,6 +857,8 @@ extern "C" int b2_engine_create(const b2_config* cfg, const char* safetensors_pa
     E_TRY(dalloc(&e->d_step, (size_t)1));
     E_TRY(dalloc(&e->d_pf_frac, (size_t)1));
     E_TRY(dalloc(&e->d_sample_out, Bcap));
+    E_TRY(dalloc(&e->d_gbar, (size_t)2));
+    E_CUDA(cudaMemset(e->d_gbar, 0, 8));
     E_CUDA(cudaMemset(e->d_pf_frac, 0, 4));
     e->log_cap_steps = 4096;
     E_TRY(dalloc(&e->d_token_log, (size_t)e->log_cap_steps * c.max_seqs));
@@ -866,7 +951,7 @@ extern "C" void b2_engine_free(b2_engine* e) {
   }
   F(e->kv_pool); F(e->h); F(e->x); F(e->qkv); F(e->qrot); F(e->attn); F(e->gu); F(e->act); F(e->proj); F(e->xlast);
   F(e->partial); F(e->attn_scratch); F(e->d_tokens); F(e->d_positions); F(e->d_seq_lens); F(e->d_slots);
-  F(e->d_block_table); F(e->d_last_rows); F(e->d_out_tokens); F(e->d_token_log); F(e->d_step); F(e->d_argmax); F(e->d_pf_frac); F(e->d_sample_out);
+  F(e->d_block_table); F(e->d_last_rows); F(e->d_out_tokens); F(e->d_token_log); F(e->d_step); F(e->d_argmax); F(e->d_pf_frac); F(e->d_sample_out); F(e->d_gbar);
   F(e->d_tiles); F(e->dbg_hidden); F(e->logits);
   if (e->h_stage) cudaFreeHost(e->h_stage);
   if (e->h_tiles) cudaFreeHost(e->h_tiles);

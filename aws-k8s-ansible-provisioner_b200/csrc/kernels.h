@@ -69,6 +69,28 @@ int tc_set_trace(unsigned long long* dev_buf);  // diagnostics: per-CTA phase ti
 // choose a split-K factor so that tiles * splits fills the SMs (each split gets >= 1 k-block)
 int tc_pick_nsplit(int T, int N, int K, int num_sms);
 
+// ---- chain.cu ----
+// The eight dependent steps between two decode-attention passes as one persistent kernel
+// (step numbers: 0 O-proj, 1 add+norm, 2 gate-up, 3 SwiGLU, 4 down, 5 add+norm, 6 QKV, 7 QK-norm/RoPE/KV).
+struct ChainGemm {
+  int N, K, nsplit, kps;  // kps = k-blocks (64 wide) per split
+};
+struct ChainParams {
+  int T, bn, phase_begin, phase_end;  // runs steps [phase_begin, phase_end)
+  ChainGemm g[4];                     // O, gate-up, down, QKV(next layer)
+  float* partial;                     // split-K partials, reused by every GEMM step
+  bf16 *h, *x, *act, *qrot;
+  const bf16 *norm_w_a, *norm_w_b;    // gains of step 1 / step 5
+  int norm_b_has_delta;               // 0: step 5 only normalises h (first call of a forward, after the embedding)
+  const bf16 *qw, *kw, *cos_sin;
+  const int32_t *positions, *slots;
+  bf16 *k_pages, *v_pages;            // pools of the layer whose QKV step 6 computes
+  int H, I, nq, nkv, block_size;
+  float eps;
+  unsigned* gbar;                     // [2] grid barrier words, zero before the first launch
+};
+int launch_decode_chain(const CUtensorMap* w_maps4, const CUtensorMap* x_maps4, const ChainParams& p, cudaStream_t s);
+
 // ---- attn_decode.cu ----
 // KV page-slice layout ([16 tokens][128 dims] bf16 = 4 KB per (page, kv head)): the 16-byte chunk c
 // (8 dims) of token row r is stored at chunk position c ^ (r & 7).  Every kernel that touches the

@@ -14,7 +14,7 @@ import numpy as np
 from . import capi
 from .capi import B2Error, b2_config, b2_sampling, check, load_library
 
-KERNEL_CLASSES = ["embed", "norm", "gemm_qkv", "rope_kv", "attn_decode", "attn_combine", "gemm_o", "gemm_gateup", "act",
+KERNEL_CLASSES = ["embed", "norm", "gemm_qkv", "rope_kv", "attn_decode", "chain", "gemm_o", "gemm_gateup", "act",
                   "gemm_down", "lmhead", "misc"]
 
 

@@ -130,7 +130,7 @@ int  b2_set_next_tokens(b2_engine* e, int32_t nseq, const int32_t* seq_ids, cons
  * (index = enum below).  Used by bench.py for the live roofline figure. */
 enum b2_kernel_class {
   B2K_EMBED = 0, B2K_NORM = 1, B2K_GEMM_QKV = 2, B2K_ROPE_KV = 3, B2K_ATTN_DECODE = 4,
-  B2K_ATTN_COMBINE = 5, B2K_GEMM_O = 6, B2K_GEMM_GATEUP = 7, B2K_ACT = 8, B2K_GEMM_DOWN = 9,
+  B2K_CHAIN = 5, B2K_GEMM_O = 6, B2K_GEMM_GATEUP = 7, B2K_ACT = 8, B2K_GEMM_DOWN = 9,
   B2K_LMHEAD = 10, B2K_MISC = 11
 };
 int  b2_decode_profile(b2_engine* e, int32_t nseq, const int32_t* seq_ids, int32_t steps,
