@@ -64,7 +64,7 @@ template <int AD_WARPS, int AD_STAGES>
 __global__ void __launch_bounds__(AD_WARPS * 32, 1)
 attn_decode_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k_pages, const bf16* __restrict__ v_pages,
                    const int32_t* __restrict__ block_table, int bt_stride, const int32_t* __restrict__ seq_lens,
-                   float* __restrict__ scratch, bf16* __restrict__ out, int B, int nq, int nkv, float scale) {
+                   float* __restrict__ scratch, bf16* __restrict__ out, int B, int nq, int nkv, float scale, int early) {
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ __align__(8) uint64_t bars[AD_WARPS][AD_STAGES];
   __shared__ int s_prefix[AD_MAX_B + 1];  // pages of sequences before b (exclusive prefix)
@@ -73,6 +73,7 @@ attn_decode_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k_pages,
   // the NEW token's K/V slot) is still executing: sequence lengths and block tables were written at the
   // top of the step, and every page except the last one of each sequence is at least a step old.
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (!early) pdl_wait();
   if (threadIdx.x == 0) {
     for (int w = 0; w < AD_WARPS; ++w)
       for (int s = 0; s < AD_STAGES; ++s) mbar_init(smem_u32(&bars[w][s]), 1);
@@ -394,7 +395,7 @@ static int launch_cfg(const bf16* q, const bf16* k_pages, const bf16* v_pages, c
   static B2PerDeviceOnce attr_once;
   if (attr_once.need()) B2_CUDA_OK(cudaFuncSetAttribute(attn_decode_kernel<W, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
   B2_CUDA_OK(b2_launch(attn_decode_kernel<W, S>, dim3(ad_grid()), dim3(W * 32), (size_t)SMEM, s, q, k_pages, v_pages, block_table,
-                       bt_stride, seq_lens, scratch, out, B, nq, nkv, scale));
+                       bt_stride, seq_lens, scratch, out, B, nq, nkv, scale, b2_pdl_early_mask() & 1));
   return 0;
 }
 

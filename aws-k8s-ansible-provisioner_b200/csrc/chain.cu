@@ -41,6 +41,22 @@ struct ChainMaps {
   CUtensorMap x[4];  // attn, x, act, x                 box 64 x BN
 };
 
+// Optional trace (tools/chain_timeline.py): thread 0 of every CTA stamps %globaltimer when it enters
+// each step (slot = step), when its CTA has finished the step's work (16 + step) and when it leaves the
+// kernel: trace[blockIdx.x * 32 + slot].
+__device__ unsigned long long* g_chain_trace = nullptr;
+__device__ __forceinline__ void chain_stamp(int slot) {
+  if (g_chain_trace != nullptr && threadIdx.x == 0) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    g_chain_trace[blockIdx.x * 32 + slot] = t;
+  }
+}
+int chain_set_trace(unsigned long long* dev_buf) {
+  B2_CUDA_OK(cudaMemcpyToSymbol(g_chain_trace, &dev_buf, sizeof(dev_buf)));
+  return 0;
+}
+
 __device__ __forceinline__ unsigned ld_acquire_u32(const unsigned* p) {
   unsigned v;
   asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
@@ -50,12 +66,15 @@ __device__ __forceinline__ void fence_proxy_async_global() { asm volatile("fence
 
 // Grid-wide barrier over the resident CTAs (gridDim.x <= number of SMs, one CTA per SM).
 // bar[0] = arrival count, bar[1] = generation; both zero before the first launch, left consistent after.
-__device__ __forceinline__ void chain_grid_sync(unsigned* bar) {
+// Pattern of cooperative-groups grid.sync(): the CTA barrier orders every thread's writes before thread
+// 0's cumulative gpu-scope fence, the arrival is a relaxed atomic after that fence, and the waiters
+// poll the generation word with acquire loads.
+__device__ __forceinline__ void chain_grid_sync(unsigned* bar, int step) {
   __syncthreads();
+  chain_stamp(16 + step);
   if (threadIdx.x == 0) {
     const unsigned my = ld_acquire_u32(bar + 1);
-    __threadfence();            // this CTA's global writes are visible before it arrives
-    fence_proxy_async_global(); // ... also to TMA reads of other CTAs
+    __threadfence();
     if (atomicAdd(bar, 1u) == gridDim.x - 1) {
       atomicExch(bar, 0u);
       __threadfence();
@@ -64,8 +83,7 @@ __device__ __forceinline__ void chain_grid_sync(unsigned* bar) {
       while (ld_acquire_u32(bar + 1) == my) {
       }
     }
-    __threadfence();
-    fence_proxy_async_global();
+    fence_proxy_async_global();  // thread 0 is also the TMA producer: order its coming async-proxy reads
   }
   __syncthreads();
 }
@@ -158,10 +176,13 @@ decode_chain_kernel(const __grid_constant__ ChainMaps maps, const ChainParams p)
         break;
       }
   }
+  chain_stamp(8);
   pdl_wait();
   if (threadIdx.x == 0) pdl_launch_dependents();
+  chain_stamp(9);
 
   for (int ph = p.phase_begin; ph < p.phase_end; ++ph) {
+    chain_stamp(ph);
     if ((ph & 1) == 0) {
       // =============================== GEMM step ===============================
       const int gi = ph >> 1;
@@ -284,16 +305,16 @@ decode_chain_kernel(const __grid_constant__ ChainMaps maps, const ChainParams p)
 #pragma unroll
                 for (int e = 0; e < 8; ++e) d[e] = 0.f;
                 const float* pp = p.partial + (size_t)r * H + (size_t)i * 8;
-                for (int s0 = 0; s0 < ns; s0 += 4) {
-                  float4 a[4], b[4];
+                for (int s0 = 0; s0 < ns; s0 += 8) {
+                  float4 a[8], b[8];
 #pragma unroll
-                  for (int j = 0; j < 4; ++j)
+                  for (int j = 0; j < 8; ++j)
                     if (s0 + j < ns) {
                       a[j] = __ldcg(reinterpret_cast<const float4*>(pp + (size_t)(s0 + j) * T * H));
                       b[j] = __ldcg(reinterpret_cast<const float4*>(pp + (size_t)(s0 + j) * T * H) + 1);
                     }
 #pragma unroll
-                  for (int j = 0; j < 4; ++j)
+                  for (int j = 0; j < 8; ++j)
                     if (s0 + j < ns) {
                       d[0] += a[j].x; d[1] += a[j].y; d[2] += a[j].z; d[3] += a[j].w;
                       d[4] += b[j].x; d[5] += b[j].y; d[6] += b[j].z; d[7] += b[j].w;
@@ -325,6 +346,7 @@ decode_chain_kernel(const __grid_constant__ ChainMaps maps, const ChainParams p)
           }
           epi_bar();  // red[] is reused by the next row
         }
+        fence_proxy_async_global();  // x is read through TMA by the next GEMM step
       } else if (ph == 3) {
         // SwiGLU gate (HF:...:81-83); rounding points as silu_mul_kernel
         const int I = p.I, ns = p.g[1].nsplit;
@@ -354,6 +376,7 @@ decode_chain_kernel(const __grid_constant__ ChainMaps maps, const ChainParams p)
           }
           *reinterpret_cast<uint4*>(p.act + (size_t)t * I + i) = pack8(o);
         }
+        fence_proxy_async_global();  // act is read through TMA by the down-projection step
       } else if (ph == 7) {
         // QK-norm + RoPE + KV page write (HF:...:248-249,263-264,151-181,270-271); as qknorm_rope_kv_kernel
         constexpr int HD = 128;
@@ -409,11 +432,12 @@ decode_chain_kernel(const __grid_constant__ ChainMaps maps, const ChainParams p)
         }
       }
     }
-    if (ph + 1 < p.phase_end) chain_grid_sync(p.gbar);
+    if (ph + 1 < p.phase_end) chain_grid_sync(p.gbar, ph);
   }
 
   tc_fence_before();
   __syncthreads();
+  chain_stamp(10);
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc(tmem_base, C::TMEM_COLS);

@@ -89,6 +89,7 @@ __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;"
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
 bool b2_pdl_enabled();
+int b2_pdl_early_mask();  // B2_PDL_EARLY bitmask (diagnostics): 1 attention streams before its wait, 2 norm, 4 rope
 // Function attributes (opt-in shared memory size) are per device: remember which devices were set.
 struct B2PerDeviceOnce {
   bool done[64] = {false};

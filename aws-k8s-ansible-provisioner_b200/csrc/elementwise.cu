@@ -55,8 +55,9 @@ int launch_gather_rows(const bf16* src, const int32_t* rows, bf16* dst, int n, i
 // ---------------------------------------------------------------------------------------
 template <int MODE>  // 0: no delta, 1: bf16 delta, 2: fp32 partials
 __global__ void add_rmsnorm_kernel(bf16* __restrict__ h, const void* __restrict__ delta, int nsplit, size_t split_stride,
-                                   const bf16* __restrict__ w, bf16* __restrict__ x, int H, float eps) {
+                                   const bf16* __restrict__ w, bf16* __restrict__ x, int H, float eps, int early) {
   __shared__ float red[32];
+  if (!early) pdl_wait();
   const int t = blockIdx.x;
   const int i = threadIdx.x;  // vector index, 8 elements
   // Before the dependency wait: the norm gains (constant) and, when a delta is added, the residual
@@ -125,12 +126,12 @@ int launch_add_rmsnorm(bf16* h, ActIn delta, const bf16* w, bf16* x, int T, int 
   B2_REQUIRE(H % 256 == 0 && H <= 8192, "add_rmsnorm: hidden %d must be a multiple of 256 and <= 8192", H);
   const int threads = H / 8;
   if (delta.ptr == nullptr)
-    B2_CUDA_OK(b2_launch(add_rmsnorm_kernel<0>, dim3(T), dim3(threads), 0, s, h, (const void*)nullptr, 0, (size_t)0, w, x, H, eps));
+    B2_CUDA_OK(b2_launch(add_rmsnorm_kernel<0>, dim3(T), dim3(threads), 0, s, h, (const void*)nullptr, 0, (size_t)0, w, x, H, eps, b2_pdl_early_mask() & 2));
   else if (!delta.is_f32)
-    B2_CUDA_OK(b2_launch(add_rmsnorm_kernel<1>, dim3(T), dim3(threads), 0, s, h, delta.ptr, 1, (size_t)0, w, x, H, eps));
+    B2_CUDA_OK(b2_launch(add_rmsnorm_kernel<1>, dim3(T), dim3(threads), 0, s, h, delta.ptr, 1, (size_t)0, w, x, H, eps, b2_pdl_early_mask() & 2));
   else
     B2_CUDA_OK(b2_launch(add_rmsnorm_kernel<2>, dim3(T), dim3(threads), 0, s, h, delta.ptr, delta.nsplit, (size_t)T * H, w, x, H,
-                         eps));
+                         eps, b2_pdl_early_mask() & 2));
   return 0;
 }
 
@@ -148,8 +149,9 @@ __global__ void qknorm_rope_kv_kernel(const void* __restrict__ qkv, int nsplit, 
                                       const bf16* __restrict__ cos_sin, const int32_t* __restrict__ positions,
                                       const int32_t* __restrict__ slots, bf16* __restrict__ q_out,
                                       bf16* __restrict__ k_pages, bf16* __restrict__ v_pages, int T, int nq, int nkv,
-                                      int block_size, float eps) {
+                                      int block_size, float eps, int early) {
   constexpr int HD = 128;
+  if (!early) pdl_wait();
   const int nheads = nq + 2 * nkv;
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
@@ -235,10 +237,10 @@ int launch_qknorm_rope_kv(ActIn qkv, const bf16* qw, const bf16* kw, const bf16*
   if (qkv.is_f32)
     B2_CUDA_OK(b2_launch(qknorm_rope_kv_kernel<true>, dim3(blocks), dim3(128), 0, s, qkv.ptr, qkv.nsplit,
                          (size_t)T * nheads * hd, qw, kw, cos_sin, positions, slots, q_out, k_pages, v_pages, T, nq, nkv,
-                         block_size, eps));
+                         block_size, eps, b2_pdl_early_mask() & 4));
   else
     B2_CUDA_OK(b2_launch(qknorm_rope_kv_kernel<false>, dim3(blocks), dim3(128), 0, s, qkv.ptr, 1, (size_t)0, qw, kw, cos_sin,
-                         positions, slots, q_out, k_pages, v_pages, T, nq, nkv, block_size, eps));
+                         positions, slots, q_out, k_pages, v_pages, T, nq, nkv, block_size, eps, b2_pdl_early_mask() & 4));
   return 0;
 }
 

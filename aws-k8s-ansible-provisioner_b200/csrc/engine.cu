@@ -28,6 +28,14 @@ void b2_set_error(const char* fmt, ...) {
   va_end(ap);
 }
 extern "C" const char* b2_last_error(void) { return g_err; }
+int b2_pdl_early_mask() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("B2_PDL_EARLY");
+    v = e ? atoi(e) : 7;
+  }
+  return v;
+}
 bool b2_pdl_enabled() {
   static int v = -1;
   if (v < 0) {

@@ -114,19 +114,24 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
         if (!waited) {
           // The weight stream does not depend on the previous kernel: start it for the first
           // stages of the first tile, THEN wait for the producer of X (programmatic dependent launch).
+          // (TC_EPI_ARGMAX_ROWS trades the operands: there the SECOND map holds the weights.)
+          constexpr bool kWeightsFirst = (EPI != TC_EPI_ARGMAX_ROWS);
           const int npre = min(kb1 - kb0, C::STAGES);
           for (int i = 0; i < npre; ++i) {
             const uint32_t fb = smem_u32(&full_bar[i]);
             mbar_arrive_expect_tx(fb, C::STAGE_BYTES);
-            tma_load_2d(smem_base + i * C::STAGE_BYTES, &tmap_w, (kb0 + i) * TC_BK, m_tile * TC_BM, fb);
+            if (kWeightsFirst) tma_load_2d(smem_base + i * C::STAGE_BYTES, &tmap_w, (kb0 + i) * TC_BK, m_tile * TC_BM, fb);
+            else tma_load_2d(smem_base + i * C::STAGE_BYTES + TC_W_BYTES, &tmap_x, (kb0 + i) * TC_BK, n_tile * BN, fb);
           }
           pdl_wait();
           pdl_launch_dependents();
-          tc_stamp(2);  // dependency satisfied, X loads go out
+          tc_stamp(2);  // dependency satisfied, the activation tiles go out
           waited = true;
-          for (int i = 0; i < npre; ++i)
-            tma_load_2d(smem_base + i * C::STAGE_BYTES + TC_W_BYTES, &tmap_x, (kb0 + i) * TC_BK, n_tile * BN,
-                        smem_u32(&full_bar[i]));
+          for (int i = 0; i < npre; ++i) {
+            const uint32_t fb = smem_u32(&full_bar[i]);
+            if (kWeightsFirst) tma_load_2d(smem_base + i * C::STAGE_BYTES + TC_W_BYTES, &tmap_x, (kb0 + i) * TC_BK, n_tile * BN, fb);
+            else tma_load_2d(smem_base + i * C::STAGE_BYTES, &tmap_w, (kb0 + i) * TC_BK, m_tile * TC_BM, fb);
+          }
           it = npre;
           for (int kb = kb0 + npre; kb < kb1; ++kb, ++it) {
             const int s = it % C::STAGES;

@@ -89,6 +89,7 @@ struct ChainParams {
   float eps;
   unsigned* gbar;                     // [2] grid barrier words, zero before the first launch
 };
+int chain_set_trace(unsigned long long* dev_buf);  // diagnostics (null = off)
 int launch_decode_chain(const CUtensorMap* w_maps4, const CUtensorMap* x_maps4, const ChainParams& p, cudaStream_t s);
 
 // ---- attn_decode.cu ----

@@ -168,6 +168,10 @@ int b2k_linear(const void* x_bf16, const void* w_bf16, void* out, int out_is_f32
 /* Diagnostics: register a device buffer of (148 * 8) uint64 in which every CTA of the tcgen05
  * projection kernel stamps %globaltimer at its phase boundaries (NULL switches the trace off). */
 int b2k_debug_gemm_trace(void* dev_u64_buf);
+/* Same for the decode chain kernel: (148 * 32) uint64; slots 0..7 = entry into step i, 16..23 = the
+ * CTA finished step i's work (before the grid barrier), 8 = CTA start, 9 = dependency satisfied,
+ * 10 = CTA done. */
+int b2k_debug_chain_trace(void* dev_u64_buf);
 
 /* lm_head + greedy argmax fused (HF:...:504-505 + generate(do_sample=False)).
  * logits_bf16 may be NULL.  out_tokens [T] int32 (device). scratch: [T] uint64 (device). */
