@@ -14,8 +14,8 @@
 //   * the producer warp pulls the NEXT GEMM step's first weight tiles into shared memory before it
 //     joins the barrier -- weights never depend on the barrier -- so the weight stream of step i+2
 //     hides behind step i+1.
-// The kernel keeps its shared memory to 96 KB so that the next attention pass's CTAs (128 KB) can
-// become resident beside it and start streaming K/V pages before this kernel has finished.
+// All of shared memory goes to the stage ring (8 stages at 64 tokens): a whole weight tile of the next
+// GEMM step fits ahead of the barrier.
 #include "kernels.h"
 
 namespace b2 {
@@ -23,7 +23,7 @@ namespace b2 {
 constexpr int CH_BM = 128;
 constexpr int CH_BK = 64;
 constexpr int CH_W_BYTES = CH_BM * CH_BK * 2;
-constexpr int CH_SMEM_BUDGET = 96 * 1024;
+constexpr int CH_SMEM_BUDGET = 192 * 1024;
 constexpr int CH_THREADS = 192;
 constexpr int CH_MAXV = 4;  // 16-byte vectors of a hidden row per epilogue thread (hidden <= 4096)
 
@@ -52,6 +52,14 @@ __device__ __forceinline__ void chain_stamp(int slot) {
     g_chain_trace[blockIdx.x * 32 + slot] = t;
   }
 }
+// same, by whichever thread calls it (sub-step stamps of the MMA and epilogue warps)
+__device__ __forceinline__ void chain_stamp_any(int slot) {
+  if (g_chain_trace != nullptr) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    g_chain_trace[blockIdx.x * 32 + slot] = t;
+  }
+}
 int chain_set_trace(unsigned long long* dev_buf) {
   B2_CUDA_OK(cudaMemcpyToSymbol(g_chain_trace, &dev_buf, sizeof(dev_buf)));
   return 0;
@@ -65,23 +73,26 @@ __device__ __forceinline__ unsigned ld_acquire_u32(const unsigned* p) {
 __device__ __forceinline__ void fence_proxy_async_global() { asm volatile("fence.proxy.async;" ::: "memory"); }
 
 // Grid-wide barrier over the resident CTAs (gridDim.x <= number of SMs, one CTA per SM).
-// bar[0] = arrival count, bar[1] = generation; both zero before the first launch, left consistent after.
-// Pattern of cooperative-groups grid.sync(): the CTA barrier orders every thread's writes before thread
-// 0's cumulative gpu-scope fence, the arrival is a relaxed atomic after that fence, and the waiters
-// poll the generation word with acquire loads.
-__device__ __forceinline__ void chain_grid_sync(unsigned* bar, int step) {
+// One 64-bit arrival counter that only ever grows: every launch uses the same grid size G and passes
+// whole barriers, so the counter is a multiple of G whenever no barrier is in flight.  A CTA finds the
+// base of its launch by rounding what it reads at its start down to a multiple of G -- exact even if
+// faster CTAs have already arrived at the first barrier, because none of them can get past it (and so
+// the counter cannot reach base + G) before this CTA arrives too.  The k-th barrier completes at
+// base + k*G.  Arrival is a fire-and-forget release reduction after a cumulative fence (the CTA barrier
+// orders every thread's writes before thread 0's fence); waiting is an acquire-load spin: about one L2
+// round trip after the last arrival.
+__device__ __forceinline__ unsigned long long ld_acquire_u64(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void chain_grid_sync(unsigned long long* bar, unsigned long long target, int step) {
   __syncthreads();
   chain_stamp(16 + step);
   if (threadIdx.x == 0) {
-    const unsigned my = ld_acquire_u32(bar + 1);
     __threadfence();
-    if (atomicAdd(bar, 1u) == gridDim.x - 1) {
-      atomicExch(bar, 0u);
-      __threadfence();
-      atomicAdd(bar + 1, 1u);
-    } else {
-      while (ld_acquire_u32(bar + 1) == my) {
-      }
+    asm volatile("red.release.gpu.global.add.u64 [%0], 1;" ::"l"(bar) : "memory");
+    while (ld_acquire_u64(bar) < target) {
     }
     fence_proxy_async_global();  // thread 0 is also the TMA producer: order its coming async-proxy reads
   }
@@ -180,6 +191,8 @@ decode_chain_kernel(const __grid_constant__ ChainMaps maps, const ChainParams p)
   pdl_wait();
   if (threadIdx.x == 0) pdl_launch_dependents();
   chain_stamp(9);
+  unsigned long long bar_target = 0;
+  if (threadIdx.x == 0) bar_target = (ld_acquire_u64(p.gbar) / gridDim.x) * gridDim.x;
 
   for (int ph = p.phase_begin; ph < p.phase_end; ++ph) {
     chain_stamp(ph);
@@ -229,6 +242,7 @@ decode_chain_kernel(const __grid_constant__ ChainMaps maps, const ChainParams p)
             const int s = it % C::STAGES;
             mbar_wait(smem_u32(&full_bar[s]), (it / C::STAGES) & 1);
             tc_fence_after();
+            if (ph == 0 && kb == kb0) chain_stamp_any(24);
             const uint32_t ws = smem_base + s * C::STAGE_BYTES;
             const uint64_t da = umma_desc_sw128(ws);
             const uint64_t db = umma_desc_sw128(ws + CH_W_BYTES);
@@ -238,6 +252,7 @@ decode_chain_kernel(const __grid_constant__ ChainMaps maps, const ChainParams p)
             tc_commit(smem_u32(&empty_bar[s]));
           }
           tc_commit(smem_u32(&tmem_full_bar[as]));
+          if (ph == 0) chain_stamp_any(25);
         }
       } else if (is_epi) {
         const int q = warp & 3;
@@ -249,6 +264,7 @@ decode_chain_kernel(const __grid_constant__ ChainMaps maps, const ChainParams p)
           const int as = lt & 1;
           mbar_wait(smem_u32(&tmem_full_bar[as]), (lt >> 1) & 1);
           tc_fence_after();
+          if (ph == 0 && et == 0) chain_stamp_any(26);
           const int row = m_tile * CH_BM + q * 32 + lane;
           const bool row_ok = row < Nn;
           const int tok0 = n_tile * BN;
@@ -281,6 +297,7 @@ decode_chain_kernel(const __grid_constant__ ChainMaps maps, const ChainParams p)
           }
           tc_fence_before();
           mbar_arrive(smem_u32(&tmem_empty_bar[as]));
+          if (ph == 0 && et == 0) chain_stamp_any(27);
         }
       }
     } else if (is_epi) {
@@ -305,16 +322,16 @@ decode_chain_kernel(const __grid_constant__ ChainMaps maps, const ChainParams p)
 #pragma unroll
                 for (int e = 0; e < 8; ++e) d[e] = 0.f;
                 const float* pp = p.partial + (size_t)r * H + (size_t)i * 8;
-                for (int s0 = 0; s0 < ns; s0 += 8) {
-                  float4 a[8], b[8];
+                for (int s0 = 0; s0 < ns; s0 += 16) {
+                  float4 a[16], b[16];
 #pragma unroll
-                  for (int j = 0; j < 8; ++j)
+                  for (int j = 0; j < 16; ++j)
                     if (s0 + j < ns) {
                       a[j] = __ldcg(reinterpret_cast<const float4*>(pp + (size_t)(s0 + j) * T * H));
                       b[j] = __ldcg(reinterpret_cast<const float4*>(pp + (size_t)(s0 + j) * T * H) + 1);
                     }
 #pragma unroll
-                  for (int j = 0; j < 8; ++j)
+                  for (int j = 0; j < 16; ++j)
                     if (s0 + j < ns) {
                       d[0] += a[j].x; d[1] += a[j].y; d[2] += a[j].z; d[3] += a[j].w;
                       d[4] += b[j].x; d[5] += b[j].y; d[6] += b[j].z; d[7] += b[j].w;
@@ -329,8 +346,10 @@ decode_chain_kernel(const __grid_constant__ ChainMaps maps, const ChainParams p)
             }
           }
           ss = warp_sum(ss);
+          if (ph == 1 && et == 0) chain_stamp_any(28);
           if (lane == 0) red[warp - 2] = ss;
           epi_bar();
+          if (ph == 1 && et == 0) chain_stamp_any(29);
           const float tot = ((red[0] + red[1]) + red[2]) + red[3];
           const float rstd = __fdiv_rn(1.0f, __fsqrt_rn(tot / (float)H + p.eps));
 #pragma unroll
@@ -344,9 +363,11 @@ decode_chain_kernel(const __grid_constant__ ChainMaps maps, const ChainParams p)
               reinterpret_cast<uint4*>(p.x + (size_t)r * H)[i] = pack8(o);
             }
           }
+          if (ph == 1 && et == 0) chain_stamp_any(30);
           epi_bar();  // red[] is reused by the next row
         }
         fence_proxy_async_global();  // x is read through TMA by the next GEMM step
+        if (ph == 1 && et == 0) chain_stamp_any(31);
       } else if (ph == 3) {
         // SwiGLU gate (HF:...:81-83); rounding points as silu_mul_kernel
         const int I = p.I, ns = p.g[1].nsplit;
@@ -359,13 +380,22 @@ decode_chain_kernel(const __grid_constant__ ChainMaps maps, const ChainParams p)
           for (int e = 0; e < 8; ++e) g[e] = u[e] = 0.f;
           const float* pg = p.partial + (size_t)t * 2 * I + i;
           const float* pu = pg + I;
-          for (int s = 0; s < ns; ++s) {
-            const float4 a = __ldcg(reinterpret_cast<const float4*>(pg + s * sstride));
-            const float4 b = __ldcg(reinterpret_cast<const float4*>(pg + s * sstride) + 1);
-            const float4 c = __ldcg(reinterpret_cast<const float4*>(pu + s * sstride));
-            const float4 d = __ldcg(reinterpret_cast<const float4*>(pu + s * sstride) + 1);
-            g[0] += a.x; g[1] += a.y; g[2] += a.z; g[3] += a.w; g[4] += b.x; g[5] += b.y; g[6] += b.z; g[7] += b.w;
-            u[0] += c.x; u[1] += c.y; u[2] += c.z; u[3] += c.w; u[4] += d.x; u[5] += d.y; u[6] += d.z; u[7] += d.w;
+          for (int s0 = 0; s0 < ns; s0 += 4) {
+            float4 a[4], b[4], c[4], d[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+              if (s0 + j < ns) {
+                a[j] = __ldcg(reinterpret_cast<const float4*>(pg + (s0 + j) * sstride));
+                b[j] = __ldcg(reinterpret_cast<const float4*>(pg + (s0 + j) * sstride) + 1);
+                c[j] = __ldcg(reinterpret_cast<const float4*>(pu + (s0 + j) * sstride));
+                d[j] = __ldcg(reinterpret_cast<const float4*>(pu + (s0 + j) * sstride) + 1);
+              }
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+              if (s0 + j < ns) {
+                g[0] += a[j].x; g[1] += a[j].y; g[2] += a[j].z; g[3] += a[j].w; g[4] += b[j].x; g[5] += b[j].y; g[6] += b[j].z; g[7] += b[j].w;
+                u[0] += c[j].x; u[1] += c[j].y; u[2] += c[j].z; u[3] += c[j].w; u[4] += d[j].x; u[5] += d[j].y; u[6] += d[j].z; u[7] += d[j].w;
+              }
           }
           float o[8];
 #pragma unroll
@@ -386,9 +416,14 @@ decode_chain_kernel(const __grid_constant__ ChainMaps maps, const ChainParams p)
           const int t = item / nheads, head = item % nheads;
           const size_t row = (size_t)t * nheads * HD + (size_t)head * HD + lane * 4;
           float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-          for (int s = 0; s < ns; ++s) {
-            const float4 a = __ldcg(reinterpret_cast<const float4*>(p.partial + row + s * sstride));
-            acc.x += a.x; acc.y += a.y; acc.z += a.z; acc.w += a.w;
+          for (int s0 = 0; s0 < ns; s0 += 8) {
+            float4 a[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+              if (s0 + j < ns) a[j] = __ldcg(reinterpret_cast<const float4*>(p.partial + row + (s0 + j) * sstride));
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+              if (s0 + j < ns) { acc.x += a[j].x; acc.y += a[j].y; acc.z += a[j].z; acc.w += a[j].w; }
           }
           float v[4] = {bf16_round(acc.x), bf16_round(acc.y), bf16_round(acc.z), bf16_round(acc.w)};
           const bool is_q = head < p.nq, is_k = !is_q && head < p.nq + p.nkv;
@@ -432,7 +467,10 @@ decode_chain_kernel(const __grid_constant__ ChainMaps maps, const ChainParams p)
         }
       }
     }
-    if (ph + 1 < p.phase_end) chain_grid_sync(p.gbar, ph);
+    if (ph + 1 < p.phase_end) {
+      bar_target += gridDim.x;
+      chain_grid_sync(p.gbar, bar_target, ph);
+    }
   }
 
   tc_fence_before();

@@ -157,8 +157,8 @@ struct b2_engine {
   long long kv_l2_budget = 0;      // B2_KV_L2_MB: bytes of next-layer K/V the projections prefetch into L2 (0 = off)
   int32_t* d_pf_frac = nullptr;
   int32_t* d_sample_out = nullptr;
-  unsigned* d_gbar = nullptr;     // grid-barrier words of the decode chain kernel
-  int use_chain = 1;              // B2_CHAIN=0: decode through the separate per-step kernels (A/B runs, hidden-state capture)  // B2_SKIP_MASK: kernel classes left out (timing ablations only; results are garbage)
+  unsigned long long* d_gbar = nullptr;  // grid-barrier arrival counter of the decode chain kernel
+  int use_chain = 0;              // B2_CHAIN=1: decode through the persistent chain kernel (chain.cu; measured slower, kept for A/B runs)  // B2_SKIP_MASK: kernel classes left out (timing ablations only; results are garbage)
 };
 
 namespace {
@@ -284,9 +284,12 @@ int forward_decode_chain(b2_engine* e, int T) {
   auto gemm_cfg = [&](int N, int K) {
     ChainGemm g;
     g.N = N; g.K = K;
+    // enough splits to give most SMs a tile, but at least 4 k-blocks per split: the weight tile of a
+    // split is prefetched a whole step ahead, so fatter splits cost nothing and halve the partials
     int ns = tc_pick_nsplit(T, N, K, e->num_sms);
-    while (ns > 1 && (size_t)ns * T * N > e->partial_floats) --ns;
     const int kb = K / 64;
+    if (kb / ns < 4) ns = std::max(1, kb / 4);
+    while (ns > 1 && (size_t)ns * T * N > e->partial_floats) --ns;
     g.kps = (kb + ns - 1) / ns;
     g.nsplit = (kb + g.kps - 1) / g.kps;
     return g;
@@ -751,7 +754,7 @@ extern "C" int b2_engine_create(const b2_config* cfg, const char* safetensors_pa
   e->attn_split_override = env_int("B2_ATTN_SPLITS", 0);
   e->force_gemm_impl = env_int("B2_GEMM_IMPL", -1);
   e->skip_mask = (unsigned)env_int("B2_SKIP_MASK", 0);
-  e->use_chain = env_int("B2_CHAIN", 1);
+  e->use_chain = env_int("B2_CHAIN", 0);
   // Off by default: measured on B200 at C2 (ms/step) 0 MB 2.22, 40 MB 2.24, 72 MB 2.33, 100 MB 2.38 --
   // un-paced prefetch bursts queue ahead of the projections' own latency-critical weight loads.
   e->kv_l2_budget = (long long)env_int("B2_KV_L2_MB", 0) << 20;
@@ -865,7 +868,7 @@ extern "C" int b2_engine_create(const b2_config* cfg, const char* safetensors_pa
     E_TRY(dalloc(&e->d_step, (size_t)1));
     E_TRY(dalloc(&e->d_pf_frac, (size_t)1));
     E_TRY(dalloc(&e->d_sample_out, Bcap));
-    E_TRY(dalloc(&e->d_gbar, (size_t)2));
+    E_TRY(dalloc(&e->d_gbar, (size_t)1));
     E_CUDA(cudaMemset(e->d_gbar, 0, 8));
     E_CUDA(cudaMemset(e->d_pf_frac, 0, 4));
     e->log_cap_steps = 4096;

@@ -87,7 +87,8 @@ struct ChainParams {
   bf16 *k_pages, *v_pages;            // pools of the layer whose QKV step 6 computes
   int H, I, nq, nkv, block_size;
   float eps;
-  unsigned* gbar;                     // [2] grid barrier words, zero before the first launch
+  unsigned long long* gbar;           // grid barrier arrival counter, zero before the first launch; every launch
+                                      // that shares it must use the same grid size
 };
 int chain_set_trace(unsigned long long* dev_buf);  // diagnostics (null = off)
 int launch_decode_chain(const CUtensorMap* w_maps4, const CUtensorMap* x_maps4, const ChainParams& p, cudaStream_t s);

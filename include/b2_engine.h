@@ -201,12 +201,16 @@ size_t b2k_attn_decode_scratch_floats(int B, int nq, int nkv, int hd);
  * partial records go to an array compiled into the library (B2K_ATTN_NOALLOC_MAX_FLOATS floats =
  * 8 MiB, resident on every GPU that loads the library until the process exits).  The call allocates
  * and frees nothing.  It fails with a message if b2k_attn_decode_scratch_floats(B, nq, nkv, hd)
- * exceeds that size (B * nkv up to about 6 700 units fits).
+ * exceeds that size: 5120 + (B * nkv + 2560) * 260 floats must fit, i.e. B * nkv <= 5486 (sequence, kv
+ * head) units; the kernel itself handles at most 4096 units per launch, so that is the limit reached
+ * first, and it is reported the same way.
  * The first call on each device looks up the array's device address (that device must be current)
  * and caches it; make that first call before starting any stream capture.
- * All calls share the one array and it keeps whatever the last call wrote; nothing in it needs to be
- * cleared between calls, but two calls whose kernels overlap on the GPU (different streams, or
- * different host threads) race on it -- serialise them. */
+ * All calls share the one array and it keeps whatever the last call wrote.  The only words that must
+ * start at zero are 16 KB of arrival counters, and every call clears them itself (a memset on the
+ * caller's stream ahead of the kernel); everything else is written before it is read.  Two calls
+ * whose kernels overlap on the GPU (different streams, or different host threads) race on the array
+ * -- serialise them. */
 #define B2K_ATTN_NOALLOC_MAX_FLOATS (2 * 1024 * 1024)
 int b2k_attn_decode_noalloc(const void* q, const void* k_pages, const void* v_pages,
                             const int32_t* block_table, int bt_stride, const int32_t* seq_lens,

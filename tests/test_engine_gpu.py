@@ -91,6 +91,26 @@ def test_tiny_prefill_decode_matches_oracle(P, tiny, graphs):
     e.close()
 
 
+def test_tiny_chain_path_matches_oracle(P, tiny, monkeypatch):
+    """The persistent chain kernel (chain.cu, B2_CHAIN=1) is an alternative schedule of the same
+    arithmetic: it must reproduce HF's greedy ids like the default path does."""
+    monkeypatch.setenv("B2_CHAIN", "1")
+    model, sd = tiny
+    g = np.load(os.path.join(GOLD, "qwen3_tiny.npz"))
+    prompts, gold = g["prompt_ids"], g["greedy_ids"]
+    e = make_engine(P, QWEN3_TINY, sd, max_model_len=256, num_blocks=64, max_seqs=8, max_batch_tokens=512, use_cuda_graphs=True)
+    sids = [e.seq_create(128) for _ in range(3)]
+    first = e.prefill(sids, [p.tolist() for p in prompts])
+    toks, _ = e.decode_run(sids, 31)
+    got = np.concatenate([first[None, :], toks], axis=0).T   # [3][32]
+    for i in range(3):
+        n = 0
+        while n < 32 and got[i, n] == gold[i, n]:
+            n += 1
+        assert n >= 16, "sequence %d: chain path agrees with HF on only %d leading tokens" % (i, n)
+    e.close()
+
+
 def test_tiny_batch_invariance_and_ragged(P, tiny):
     """Ragged prompts in one prefill + batched decode must equal each sequence run alone."""
     model, sd = tiny

@@ -32,3 +32,14 @@ for k in (8, 9, 0, 1, 2, 3, 4, 5, 10):
         w = (t[:, 16 + k] - t0) / 1e3
         line += "   | work done: min %7.2f median %7.2f max %7.2f" % (w.min(), np.median(w), w.max())
     print(line)
+
+sub = {24: "O: first stage full (MMA warp)", 25: "O: MMAs issued", 26: "O: accumulator ready (epilogue)", 27: "O: partial stores issued",
+       28: "norm: loads summed", 29: "norm: row reduced", 30: "norm: x stored", 31: "norm: proxy fence done"}
+busy = t[:, 24] > 0
+print("  busy CTAs (have an O tile): %d" % busy.sum())
+for k in sorted(sub):
+    m = t[:, k] > 0
+    if not m.any():
+        continue
+    col = (t[m, k] - t0) / 1e3
+    print("  %-34s min %7.2f median %7.2f max %7.2f us" % (sub[k], col.min(), np.median(col), col.max()))
