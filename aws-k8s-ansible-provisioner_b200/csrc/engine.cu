@@ -1258,6 +1258,46 @@ extern "C" int b2_decode_profile(b2_engine* e, int32_t nseq, const int32_t* seq_
   return 0;
 }
 
+extern "C" int b2_attn_profile(b2_engine* e, int32_t nseq, const int32_t* seq_ids, int32_t reps, float* ms_per_launch,
+                               int64_t* kv_bytes_per_launch) {
+  B2_REQUIRE(e && seq_ids && reps >= 1 && ms_per_launch && kv_bytes_per_launch, "b2_attn_profile: bad arguments");
+  B2_CUDA_OK(cudaSetDevice(e->device));
+  B2_REQUIRE((int)e->cur_batch.size() == nseq && std::equal(seq_ids, seq_ids + nseq, e->cur_batch.begin()),
+             "b2_attn_profile: run a decode step on exactly this batch first (the pass reuses its device-side page tables)");
+  const b2_config& c = e->cfg;
+  int64_t bytes = 0;
+  for (int i = 0; i < nseq; ++i) bytes += (int64_t)(e->seqs[seq_ids[i]].len + 1) * c.num_kv_heads * c.head_dim * 2 * 2;
+  const int B = e->cur_B;
+  auto pass = [&]() -> int {
+    for (int l = 0; l < c.num_layers; ++l) {
+      bf16* kp = e->kv_pool + (size_t)(2 * l) * e->layer_kv_elems;
+      bf16* vp = kp + e->layer_kv_elems;
+      B2_TRY(launch_attn_decode(e->qrot, kp, vp, e->d_block_table, e->bt_stride, e->d_seq_lens, e->attn_scratch, e->attn, B,
+                                c.num_q_heads, c.num_kv_heads, c.head_dim, c.block_size, e->stream));
+    }
+    return 0;
+  };
+  cudaEvent_t a, b;
+  B2_CUDA_OK(cudaEventCreate(&a));
+  B2_CUDA_OK(cudaEventCreate(&b));
+  int rc = pass();  // warm-up; each layer's K/V (B x S x 4 KB) is a different region, so no pass finds its pages in L2
+  if (rc == 0) rc = cudaEventRecord(a, e->stream) == cudaSuccess ? 0 : -5;
+  for (int r = 0; r < reps && rc == 0; ++r) rc = pass();
+  if (rc == 0) rc = cudaEventRecord(b, e->stream) == cudaSuccess ? 0 : -5;
+  if (rc == 0) rc = cudaEventSynchronize(b) == cudaSuccess ? 0 : -5;
+  float ms = 0.f;
+  if (rc == 0) rc = cudaEventElapsedTime(&ms, a, b) == cudaSuccess ? 0 : -5;
+  cudaEventDestroy(a);
+  cudaEventDestroy(b);
+  if (rc != 0) {
+    if (rc == -5) b2_set_error("b2_attn_profile: CUDA error: %s", cudaGetErrorString(cudaGetLastError()));
+    return rc;
+  }
+  *ms_per_launch = ms / (float)(reps * c.num_layers);
+  *kv_bytes_per_launch = bytes;
+  return 0;
+}
+
 extern "C" int64_t b2_launch_count(b2_engine* e) { return e ? e->launches : 0; }
 
 extern "C" int b2_set_debug(b2_engine* e, int32_t flags) {

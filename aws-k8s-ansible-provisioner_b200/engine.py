@@ -154,6 +154,15 @@ class Engine:
         check(self.lib.b2_decode_profile(self.h, len(sids), _p32(sids), int(steps), ms, cnt), self.lib)
         return {KERNEL_CLASSES[i]: {"ms": float(ms[i]), "launches": int(cnt[i])} for i in range(capi.NUM_KERNEL_CLASSES)}
 
+    def attn_profile(self, seq_ids, reps: int = 8):
+        """Decode-attention pass of every layer back to back, `reps` times, between one event pair.
+        Returns (ms per launch, K/V bytes one launch must read)."""
+        sids = _i32(seq_ids)
+        ms = C.c_float(0)
+        nbytes = C.c_int64(0)
+        check(self.lib.b2_attn_profile(self.h, len(sids), _p32(sids), int(reps), C.byref(ms), C.byref(nbytes)), self.lib)
+        return ms.value, int(nbytes.value)
+
     def launch_count(self) -> int:
         return int(self.lib.b2_launch_count(self.h))
 

@@ -15,7 +15,11 @@ Numbers on the JSON line:
   e2e        the same K steps through the public C-ABI call b2_decode_step with HOST token buffers
              in and out every step (H2D + D2H inside the timed region, host clock)
   roofline   the dominant kernel (paged decode attention): algorithmic K/V bytes per launch over
-             its CUDA-event duration, measured live in an eager profiled pass at mid context
+             its average launch duration at mid context, measured live after the timed region:
+             every layer's pass launched back to back over the real pages, 8 rounds (224 launches),
+             between one CUDA-event pair on the engine's stream (b2_attn_profile).  The per-class
+             table (kernel_ms_per_step_eager) and ms_per_launch_isolated come from an eager step
+             with an event pair around every launch, which adds launch latency to each figure
   cpu_baseline  HF Qwen3 on the host CPU, same batch/context, a bounded number of steps
 N > 1: one replica per GPU (request-level data parallelism, no collective on the data path);
 ranks only meet at a gloo barrier around the timed region ("scaling": "weak").
@@ -290,10 +294,12 @@ def run_b200(args, rank, world, local, dist):
         eng.seq_truncate(s, mid)
     prof = eng.decode_profile(sids, 3)
     attn = prof["attn_decode"]
-    attn_ms = attn["ms"] / max(1, attn["launches"])
-    ctx_mid = mid + 2  # mean context of the three profiled steps (the step's own token included)
-    kv_layer_token = 2 * cfg.num_kv_heads * cfg.head_dim * 2
-    attn_bytes = BATCH * ctx_mid * kv_layer_token + 2 * BATCH * cfg.num_q_heads * cfg.head_dim * 2
+    attn_ms_isolated = attn["ms"] / max(1, attn["launches"])  # event pair around every single launch: + launch latency
+    # the figure used: all layers' passes back to back over the real pages between ONE event pair, 8 rounds
+    # (28 x 8 launches; every layer's K/V is its own 170 MB region, so no launch finds its input in L2)
+    attn_ms, kv_bytes = eng.attn_profile(sids, reps=8)
+    ctx_mid = kv_bytes // (BATCH * 2 * cfg.num_kv_heads * cfg.head_dim * 2)
+    attn_bytes = kv_bytes + 2 * BATCH * cfg.num_q_heads * cfg.head_dim * 2  # + q in, o out
     peak, peak_kind = measured_peaks()
     achieved = attn_bytes / (attn_ms / 1e3) / 1e9
     prof_total = sum(v["ms"] for v in prof.values()) / 3.0
@@ -316,7 +322,8 @@ def run_b200(args, rank, world, local, dist):
         "clocks": clocks,
         "roofline": {"bound": "hbm", "kernel": "attn_decode_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": None, "peak_kind": peak_kind, "bytes_per_launch": attn_bytes,
-                     "ms_per_launch": attn_ms, "context": ctx_mid},
+                     "ms_per_launch": attn_ms, "context": ctx_mid,
+                     "launches_timed": 8 * cfg.num_layers, "ms_per_launch_isolated": attn_ms_isolated},
         "step_hbm_frac": step_frac,
         "step_bytes": step_bytes,
         "kernel_ms_per_step_eager": kernel_ms,

@@ -135,6 +135,15 @@ enum b2_kernel_class {
 };
 int  b2_decode_profile(b2_engine* e, int32_t nseq, const int32_t* seq_ids, int32_t steps,
                        float* ms_by_class, int64_t* launches_by_class);
+/* Times the dominant kernel on its own: the decode-attention pass of every layer, launched back to
+ * back on the engine stream over the batch's real K/V pages (the batch of the last decode call),
+ * `reps` times, between ONE pair of CUDA events.  ms_per_launch = elapsed / (reps * layers);
+ * kv_bytes_per_launch = the K and V bytes one launch has to read (sum over sequences of
+ * (len + 1) * kv_heads * head_dim * 2 tensors * 2 bytes).  Results of the pass are discarded.
+ * bench.py's roofline figure comes from here: an event pair around every single launch (as
+ * b2_decode_profile does) adds several microseconds of launch latency to a ~30 us kernel. */
+int  b2_attn_profile(b2_engine* e, int32_t nseq, const int32_t* seq_ids, int32_t reps,
+                     float* ms_per_launch, int64_t* kv_bytes_per_launch);
 /* Number of kernel launches (graph nodes included) issued by this engine so far. */
 int64_t b2_launch_count(b2_engine* e);
 
