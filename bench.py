@@ -302,6 +302,15 @@ def run_b200(args, rank, world, local, dist):
     attn_bytes = kv_bytes + 2 * BATCH * cfg.num_q_heads * cfg.head_dim * 2  # + q in, o out
     peak, peak_kind = measured_peaks()
     achieved = attn_bytes / (attn_ms / 1e3) / 1e9
+    # DRAM traffic of one launch, from the committed ncu --set full capture (taken at another context:
+    # scaled by its own traffic/algorithmic ratio, which is what the figure is for)
+    traffic = None
+    try:
+        with open(os.path.join(ROOT, "profiles", "r01_b_attn_traffic.json")) as f:
+            tj = json.load(f)
+        traffic = attn_bytes * (tj["dram_bytes_read"] + tj["dram_bytes_write"]) / tj["algorithmic_bytes"]
+    except (OSError, KeyError, ValueError):
+        pass
     prof_total = sum(v["ms"] for v in prof.values()) / 3.0
     kernel_ms = {k: round(v["ms"] / 3.0, 4) for k, v in prof.items() if v["launches"]}
     # whole-step algorithmic bytes: W + B*S*kv + B*kv at the mean context of the timed region
@@ -321,7 +330,8 @@ def run_b200(args, rank, world, local, dist):
         "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": {"bound": "hbm", "kernel": "attn_decode_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak, "traffic": None, "peak_kind": peak_kind, "bytes_per_launch": attn_bytes,
+                     "frac": achieved / peak, "traffic": traffic, "traffic_source": "ncu capture at context 520, ratio 1.05 applied",
+                     "peak_kind": peak_kind, "bytes_per_launch": attn_bytes,
                      "ms_per_launch": attn_ms, "context": ctx_mid,
                      "launches_timed": 8 * cfg.num_layers, "ms_per_launch_isolated": attn_ms_isolated},
         "step_hbm_frac": step_frac,
