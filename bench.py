@@ -158,6 +158,11 @@ def hf_cpu_decode(batch: int, ctx: int, steps: int, warmup: int, budget_s: float
     from oracle.qwen3_oracle import QWEN3_0_6B, hf_model  # the checker's model builder (CPU arm only)
 
     arch = QWEN3_0_6B
+    # all the host threads the CPU arm can use: torchrun exports OMP_NUM_THREADS=1 to every rank, which
+    # would silently turn this into a single-core measurement
+    avail = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    if torch.get_num_threads() < avail:
+        torch.set_num_threads(avail)
     threads = torch.get_num_threads()
     model = hf_model(arch, seed=0)
 
