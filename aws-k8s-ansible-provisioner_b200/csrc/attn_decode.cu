@@ -403,13 +403,14 @@ static int launch_cfg(const bf16* q, const bf16* k_pages, const bf16* v_pages, c
 // must be zero when the kernel starts -- the kernel leaves them zero again when it is done.
 int launch_attn_decode(const bf16* q, const bf16* k_pages, const bf16* v_pages, const int32_t* block_table,
                        int bt_stride, const int32_t* seq_lens, float* scratch, bf16* out, int B, int nq, int nkv,
-                       int hd, int block_size, cudaStream_t s) {
+                       int hd, int block_size, cudaStream_t s, float softmax_scale) {
   if (B <= 0) return 0;
   B2_REQUIRE(hd == AD_HD && block_size == AD_BS, "attn_decode: built for head_dim 128 / page 16 (got %d / %d)", hd, block_size);
   B2_REQUIRE(nq == 2 * nkv, "attn_decode: built for a GQA group of 2 (nq=%d nkv=%d)", nq, nkv);
   B2_REQUIRE(B <= AD_MAX_B && B * nkv <= AD_CNT, "attn_decode: batch %d x %d kv heads exceeds %d units", B, nkv, AD_CNT);
   B2_REQUIRE(scratch != nullptr, "attn_decode: scratch required");
-  const float scale = (float)(1.0 / sqrt((double)hd));  // HF passes head_dim**-0.5 as a double
+  // HF passes head_dim**-0.5 as a double
+  const float scale = softmax_scale > 0.f ? softmax_scale : (float)(1.0 / sqrt((double)hd));
   static int cfg = -1;
   if (cfg < 0) {
     const char* e = getenv("B2_ATTN_CFG");

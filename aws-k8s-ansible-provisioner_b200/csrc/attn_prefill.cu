@@ -219,13 +219,14 @@ attn_prefill_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k_pages
 
 int launch_attn_prefill(const bf16* q, const bf16* k_pages, const bf16* v_pages, const int32_t* block_table,
                         int bt_stride, const PrefillTile* tiles_dev, int ntiles, bf16* out, int nq, int nkv, int hd,
-                        int block_size, cudaStream_t s) {
+                        int block_size, cudaStream_t s, float softmax_scale) {
   if (ntiles <= 0) return 0;
   B2_REQUIRE(hd == AP_HD, "attn_prefill: head_dim %d not built (128 only)", hd);
   B2_REQUIRE(nq % nkv == 0, "attn_prefill: nq=%d not a multiple of nkv=%d", nq, nkv);
   static B2PerDeviceOnce attr_once;
   if (attr_once.need()) B2_CUDA_OK(cudaFuncSetAttribute(attn_prefill_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AP_SMEM));
-  const float scale_log2 = (float)((1.0 / sqrt((double)hd)) * 1.4426950408889634);
+  const double scale = softmax_scale > 0.f ? (double)softmax_scale : 1.0 / sqrt((double)hd);
+  const float scale_log2 = (float)(scale * 1.4426950408889634);
   dim3 grid(ntiles, nq);
   B2_CUDA_OK(b2_launch(attn_prefill_kernel, grid, dim3(128), (size_t)AP_SMEM, s, q, k_pages, v_pages, block_table, bt_stride,
                        tiles_dev, out, nq, nkv, block_size, scale_log2));

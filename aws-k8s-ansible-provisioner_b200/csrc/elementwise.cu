@@ -142,6 +142,10 @@ int launch_add_rmsnorm(bf16* h, ActIn delta, const bf16* w, bf16* x, int T, int 
 // partner element i +/- 64 lives in lane l ^ 16.
 //   n  = bf16(w * bf16(q * rsqrt(mean(q^2)+eps)))
 //   q' = bf16(bf16(n*cos) + bf16(rot(n)*sin))
+// Variants of the same step (Phi-3, HF:models/phi3/modeling_phi3.py:178-205,237-248): no QK-norm
+// (qw == kw == nullptr) and a rotary width other than 128 -- rot_quads = rotary_dim / 8 lanes hold
+// the first half, the next rot_quads lanes the second half, later lanes pass through (q_pass);
+// heads narrower than 128 are stored zero-padded, and zeros stay zeros through every step here.
 // ---------------------------------------------------------------------------------------
 template <bool F32IN>
 __global__ void qknorm_rope_kv_kernel(const void* __restrict__ qkv, int nsplit, size_t split_stride,
@@ -149,7 +153,7 @@ __global__ void qknorm_rope_kv_kernel(const void* __restrict__ qkv, int nsplit, 
                                       const bf16* __restrict__ cos_sin, const int32_t* __restrict__ positions,
                                       const int32_t* __restrict__ slots, bf16* __restrict__ q_out,
                                       bf16* __restrict__ k_pages, bf16* __restrict__ v_pages, int T, int nq, int nkv,
-                                      int block_size, float eps, int early) {
+                                      int block_size, float eps, int early, int rot_quads) {
   constexpr int HD = 128;
   if (!early) pdl_wait();
   const int nheads = nq + 2 * nkv;
@@ -170,15 +174,23 @@ __global__ void qknorm_rope_kv_kernel(const void* __restrict__ qkv, int nsplit, 
   const int pos = max(positions[t], 0);
   const int slot = slots[t];
   float wv[4] = {1.f, 1.f, 1.f, 1.f}, c[4] = {1.f, 1.f, 1.f, 1.f}, sn[4] = {0.f, 0.f, 0.f, 0.f};
+  const bool use_norm = qw != nullptr;
+  const bool first_half = lane < rot_quads;
+  const bool rotates = lane < 2 * rot_quads;
+  const int partner_lane = first_half ? lane + rot_quads : lane - rot_quads;  // == lane ^ 16 for a 128-wide rotary
   if (is_q || is_k) {
-    uint2 wraw = *reinterpret_cast<const uint2*>((is_q ? qw : kw) + lane * 4);
-    wv[0] = bf16lo(wraw.x); wv[1] = bf16hi(wraw.x); wv[2] = bf16lo(wraw.y); wv[3] = bf16hi(wraw.y);
-    const bf16* cs = cos_sin + (size_t)pos * HD;
-    const int ci = (lane * 4) & 63;
-    uint2 craw = *reinterpret_cast<const uint2*>(cs + ci);
-    uint2 sraw = *reinterpret_cast<const uint2*>(cs + 64 + ci);
-    c[0] = bf16lo(craw.x); c[1] = bf16hi(craw.x); c[2] = bf16lo(craw.y); c[3] = bf16hi(craw.y);
-    sn[0] = bf16lo(sraw.x); sn[1] = bf16hi(sraw.x); sn[2] = bf16lo(sraw.y); sn[3] = bf16hi(sraw.y);
+    if (use_norm) {
+      uint2 wraw = *reinterpret_cast<const uint2*>((is_q ? qw : kw) + lane * 4);
+      wv[0] = bf16lo(wraw.x); wv[1] = bf16hi(wraw.x); wv[2] = bf16lo(wraw.y); wv[3] = bf16hi(wraw.y);
+    }
+    if (rotates) {
+      const bf16* cs = cos_sin + (size_t)pos * HD;
+      const int ci = (first_half ? lane : lane - rot_quads) * 4;
+      uint2 craw = *reinterpret_cast<const uint2*>(cs + ci);
+      uint2 sraw = *reinterpret_cast<const uint2*>(cs + 64 + ci);
+      c[0] = bf16lo(craw.x); c[1] = bf16hi(craw.x); c[2] = bf16lo(craw.y); c[3] = bf16hi(craw.y);
+      sn[0] = bf16lo(sraw.x); sn[1] = bf16hi(sraw.x); sn[2] = bf16lo(sraw.y); sn[3] = bf16hi(sraw.y);
+    }
   }
   pdl_wait();
   pdl_launch_dependents();
@@ -198,16 +210,18 @@ __global__ void qknorm_rope_kv_kernel(const void* __restrict__ qkv, int nsplit, 
   }
 
   if (is_q || is_k) {
-    float ss = v[0] * v[0] + v[1] * v[1] + v[2] * v[2] + v[3] * v[3];
-    ss = warp_sum(ss);
-    const float rstd = __fdiv_rn(1.0f, __fsqrt_rn(ss / (float)HD + eps));
+    if (use_norm) {
+      float ss = v[0] * v[0] + v[1] * v[1] + v[2] * v[2] + v[3] * v[3];
+      ss = warp_sum(ss);
+      const float rstd = __fdiv_rn(1.0f, __fsqrt_rn(ss / (float)HD + eps));
 #pragma unroll
-    for (int e = 0; e < 4; ++e) v[e] = bf16_round(wv[e] * bf16_round(v[e] * rstd));
+      for (int e = 0; e < 4; ++e) v[e] = bf16_round(wv[e] * bf16_round(v[e] * rstd));
+    }
 #pragma unroll
     for (int e = 0; e < 4; ++e) {
-      float partner = __shfl_xor_sync(0xffffffffu, v[e], 16);
-      float rot = (lane < 16) ? -partner : partner;
-      v[e] = bf16_round(bf16_round(v[e] * c[e]) + bf16_round(rot * sn[e]));
+      float partner = __shfl_sync(0xffffffffu, v[e], partner_lane & 31);
+      float rot = first_half ? -partner : partner;
+      if (rotates) v[e] = bf16_round(bf16_round(v[e] * c[e]) + bf16_round(rot * sn[e]));
     }
   }
   uint2 o;
@@ -228,19 +242,22 @@ __global__ void qknorm_rope_kv_kernel(const void* __restrict__ qkv, int nsplit, 
 
 int launch_qknorm_rope_kv(ActIn qkv, const bf16* qw, const bf16* kw, const bf16* cos_sin, const int32_t* positions,
                           const int32_t* slots, bf16* q_out, bf16* k_pages, bf16* v_pages, int T, int nq, int nkv,
-                          int hd, int block_size, float eps, cudaStream_t s) {
+                          int hd, int block_size, float eps, cudaStream_t s, int rotary_dim) {
   if (T <= 0) return 0;
-  B2_REQUIRE(hd == 128, "qknorm_rope_kv: head_dim %d not built (128 only)", hd);
+  B2_REQUIRE(hd == 128, "qknorm_rope_kv: head_dim %d not built (128 only; narrower heads are stored padded)", hd);
+  B2_REQUIRE((qw == nullptr) == (kw == nullptr), "qknorm_rope_kv: q and k norm gains must both be given or both be null");
+  B2_REQUIRE(rotary_dim >= 8 && rotary_dim <= 128 && rotary_dim % 8 == 0, "qknorm_rope_kv: rotary width %d not supported", rotary_dim);
+  const int rot_quads = rotary_dim / 8;
   const int nheads = nq + 2 * nkv;
   const long long warps = (long long)T * nheads;
   const int blocks = (int)((warps + 3) / 4);
   if (qkv.is_f32)
     B2_CUDA_OK(b2_launch(qknorm_rope_kv_kernel<true>, dim3(blocks), dim3(128), 0, s, qkv.ptr, qkv.nsplit,
                          (size_t)T * nheads * hd, qw, kw, cos_sin, positions, slots, q_out, k_pages, v_pages, T, nq, nkv,
-                         block_size, eps, b2_pdl_early_mask() & 4));
+                         block_size, eps, b2_pdl_early_mask() & 4, rot_quads));
   else
     B2_CUDA_OK(b2_launch(qknorm_rope_kv_kernel<false>, dim3(blocks), dim3(128), 0, s, qkv.ptr, 1, (size_t)0, qw, kw, cos_sin,
-                         positions, slots, q_out, k_pages, v_pages, T, nq, nkv, block_size, eps, b2_pdl_early_mask() & 4));
+                         positions, slots, q_out, k_pages, v_pages, T, nq, nkv, block_size, eps, b2_pdl_early_mask() & 4, rot_quads));
   return 0;
 }
 

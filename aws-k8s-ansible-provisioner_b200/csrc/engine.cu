@@ -83,6 +83,18 @@ struct b2_engine {
   cudaStream_t stream = nullptr;
   bool finalized = false;
   int q_size = 0, kv_size = 0, qkv_size = 0;
+  // Internal geometry.  The attention kernels are built for 128-wide heads in GQA groups of two; a
+  // model with narrower heads (Phi-3: 96) or one query head per kv head (MHA) is laid out to fit:
+  // every head is zero-padded to 128 dims and, for MHA, every real query head is followed by an
+  // all-zero partner head.  The padding lives in the WEIGHTS (zero rows of Wqkv, zero columns of Wo,
+  // scattered once at load time), so activations, KV pages and kernels need no special cases and the
+  // arithmetic on the real elements is untouched; the cost is wasted bytes, which only matters for the
+  // parity configurations that use it.
+  int nq = 0, nkv = 0, hd = 128;  // internal (padded) head counts / width handed to the kernels
+  int qhead_step = 1;             // real query head h lives at internal head h * qhead_step
+  bool native_geom = true;        // cfg geometry == internal geometry (Qwen3): weights copy straight in
+  float attn_scale = 0.f;         // real head_dim^-0.5
+  int rotary_dim = 128;
 
   // weights
   bf16* embed = nullptr;
@@ -304,7 +316,7 @@ int forward_decode_chain(b2_engine* e, int T) {
   p.partial = e->partial;
   p.h = e->h; p.x = e->x; p.act = e->act; p.qrot = e->qrot;
   p.cos_sin = e->cos_sin; p.positions = e->d_positions; p.slots = e->d_slots;
-  p.H = H; p.I = I; p.nq = c.num_q_heads; p.nkv = c.num_kv_heads; p.block_size = c.block_size; p.eps = c.rms_eps;
+  p.H = H; p.I = I; p.nq = e->nq; p.nkv = e->nkv; p.block_size = c.block_size; p.eps = c.rms_eps;
   p.gbar = e->d_gbar;
   CUtensorMap xm[4] = {e->tm_x[XB_ATTN][bi], e->tm_x[XB_X][bi], e->tm_x[XB_ACT][bi], e->tm_x[XB_X][bi]};
   auto kv_of = [&](int l, bf16** kp, bf16** vp) {
@@ -329,7 +341,7 @@ int forward_decode_chain(b2_engine* e, int T) {
       KL k(e, B2K_ATTN_DECODE);
       if (!k.skip())
         B2_TRY(launch_attn_decode(e->qrot, kp, vp, e->d_block_table, e->bt_stride, e->d_seq_lens, e->attn_scratch, e->attn, T,
-                                  c.num_q_heads, c.num_kv_heads, c.head_dim, c.block_size, e->stream));
+                                  e->nq, e->nkv, e->hd, c.block_size, e->stream, e->attn_scale));
     }
     const bool last = (l + 1 == L);
     LayerW& Ln = e->layers[last ? l : l + 1];
@@ -368,7 +380,7 @@ int forward(b2_engine* e, int T, int ntiles, int nlast, int attn_split) {
     pf.frac_q16 = e->d_pf_frac;
     pf.bt_stride = e->bt_stride;
     pf.B = T;
-    pf.nkv = c.num_kv_heads;
+    pf.nkv = e->nkv;
     pf.part = part;
     pf.nparts = 4;
     return pf;
@@ -387,17 +399,17 @@ int forward(b2_engine* e, int T, int ntiles, int nlast, int attn_split) {
     {
       KL k(e, B2K_ROPE_KV);
       if (!k.skip()) B2_TRY(launch_qknorm_rope_kv(qkv, L.qnorm, L.knorm, e->cos_sin, e->d_positions, e->d_slots, e->qrot, kp, vp, T,
-                                   c.num_q_heads, c.num_kv_heads, c.head_dim, c.block_size, c.rms_eps, e->stream));
+                                   e->nq, e->nkv, e->hd, c.block_size, c.rms_eps, e->stream, e->rotary_dim));
     }
     if (ntiles > 0) {
       KL k(e, B2K_MISC);
       if (!k.skip()) B2_TRY(launch_attn_prefill(e->qrot, kp, vp, e->d_block_table, e->bt_stride, e->d_tiles, ntiles, e->attn,
-                                 c.num_q_heads, c.num_kv_heads, c.head_dim, c.block_size, e->stream));
+                                 e->nq, e->nkv, e->hd, c.block_size, e->stream, e->attn_scale));
     } else {
       KL k(e, B2K_ATTN_DECODE);
       if (!k.skip())
         B2_TRY(launch_attn_decode(e->qrot, kp, vp, e->d_block_table, e->bt_stride, e->d_seq_lens, e->attn_scratch, e->attn, T,
-                                  c.num_q_heads, c.num_kv_heads, c.head_dim, c.block_size, e->stream));
+                                  e->nq, e->nkv, e->hd, c.block_size, e->stream, e->attn_scale));
     }
     ActIn o = linear(e, B2K_GEMM_O, XB_ATTN, e->attn, L.wo, L.tm_o, e->proj, T, H, e->q_size, &rc, prefetch_for(l + 1, 0));
     B2_TRY(rc);
@@ -490,7 +502,7 @@ int decode_body(b2_engine* e, int B, int attn_split) {
     KL k(e, B2K_MISC);
     if (!k.skip()) B2_TRY(launch_decode_advance(e->d_positions, e->d_seq_lens, e->d_slots, e->d_block_table, e->bt_stride,
                                  e->cfg.block_size, B, e->d_pf_frac, e->kv_l2_budget,
-                                 (long long)e->cfg.num_kv_heads * e->cfg.block_size * e->cfg.head_dim * 2 * 2, e->stream));
+                                 (long long)e->nkv * e->cfg.block_size * e->hd * 2 * 2, e->stream));
   }
   B2_TRY(forward(e, B, 0, B, attn_split));
   {
@@ -618,6 +630,35 @@ int layer_tensor(b2_engine* e, const std::string& name, const void* host, size_t
     e->loaded[name] = 1;
     return 0;
   };
+  // Per-head blocks of the attention projections go through the internal geometry (see b2_engine):
+  // head h of the checkpoint lands at internal head h * step, its head_dim rows (or columns, for the
+  // output projection) at the start of a 128-wide slot; everything else in the slot stays zero.
+  const int hd_r = c.head_dim;
+  auto put_head_rows = [&](bf16* dst, const uint16_t* src, int heads, int step, int slots) -> int {
+    std::vector<uint16_t> stage((size_t)slots * 128 * H, 0);
+    for (int h = 0; h < heads; ++h)
+      memcpy(&stage[(size_t)h * step * 128 * H], src + (size_t)h * hd_r * H, (size_t)hd_r * H * 2);
+    B2_CUDA_OK(cudaMemcpy(dst, stage.data(), stage.size() * 2, cudaMemcpyHostToDevice));
+    return 0;
+  };
+  auto put_head_cols = [&](bf16* dst, const uint16_t* src, int heads, int step, int slots) -> int {
+    const size_t in_cols = (size_t)heads * hd_r, out_cols = (size_t)slots * 128;
+    std::vector<uint16_t> stage((size_t)H * out_cols, 0);
+    for (int r = 0; r < H; ++r)
+      for (int h = 0; h < heads; ++h)
+        memcpy(&stage[(size_t)r * out_cols + (size_t)h * step * 128], src + (size_t)r * in_cols + (size_t)h * hd_r, (size_t)hd_r * 2);
+    B2_CUDA_OK(cudaMemcpy(dst, stage.data(), stage.size() * 2, cudaMemcpyHostToDevice));
+    return 0;
+  };
+  auto expect = [&](size_t elems) -> int {
+    if (nbytes != elems * 2) {
+      b2_set_error("tensor %s: expected %zu bytes, got %zu", name.c_str(), elems * 2, nbytes);
+      return -22;
+    }
+    return 0;
+  };
+  const size_t q_r = (size_t)c.num_q_heads * hd_r, kv_r = (size_t)c.num_kv_heads * hd_r;  // checkpoint widths
+  const uint16_t* src16 = reinterpret_cast<const uint16_t*>(host);
   if (name == "model.embed_tokens.weight") return put(e->embed, (size_t)c.vocab * H);
   if (name == "model.norm.weight") return put(e->final_norm, H);
   if (name == "lm_head.weight") {
@@ -646,14 +687,39 @@ int layer_tensor(b2_engine* e, const std::string& name, const void* host, size_t
   std::string rest = name.substr(dot + 1);
   if (rest == "input_layernorm.weight") return put(L.ln1, H);
   if (rest == "post_attention_layernorm.weight") return put(L.ln2, H);
-  if (rest == "self_attn.q_norm.weight") return put(L.qnorm, c.head_dim);
-  if (rest == "self_attn.k_norm.weight") return put(L.knorm, c.head_dim);
-  if (rest == "self_attn.q_proj.weight") return put(L.wqkv, (size_t)e->q_size * H);
-  if (rest == "self_attn.k_proj.weight") return put(L.wqkv + (size_t)e->q_size * H, (size_t)e->kv_size * H);
-  if (rest == "self_attn.v_proj.weight") return put(L.wqkv + (size_t)(e->q_size + e->kv_size) * H, (size_t)e->kv_size * H);
-  if (rest == "self_attn.o_proj.weight") return put(L.wo, (size_t)H * e->q_size);
-  if (rest == "mlp.gate_proj.weight") return put(L.wgu, (size_t)I * H);
-  if (rest == "mlp.up_proj.weight") return put(L.wgu + (size_t)I * H, (size_t)I * H);
+  bf16* wq = L.wqkv;
+  bf16* wk = L.wqkv + (size_t)e->q_size * H;
+  bf16* wv = L.wqkv + (size_t)(e->q_size + e->kv_size) * H;
+  auto done = [&](int rc) {
+    if (rc == 0) e->loaded[name] = 1;
+    return rc;
+  };
+  if (c.arch == B2_ARCH_QWEN3) {
+    if (rest == "self_attn.q_norm.weight") return put(L.qnorm, c.head_dim);
+    if (rest == "self_attn.k_norm.weight") return put(L.knorm, c.head_dim);
+    if (rest == "mlp.gate_proj.weight") return put(L.wgu, (size_t)I * H);
+    if (rest == "mlp.up_proj.weight") return put(L.wgu + (size_t)I * H, (size_t)I * H);
+    if (e->native_geom) {
+      if (rest == "self_attn.q_proj.weight") return put(wq, (size_t)e->q_size * H);
+      if (rest == "self_attn.k_proj.weight") return put(wk, (size_t)e->kv_size * H);
+      if (rest == "self_attn.v_proj.weight") return put(wv, (size_t)e->kv_size * H);
+      if (rest == "self_attn.o_proj.weight") return put(L.wo, (size_t)H * e->q_size);
+    } else {
+      if (rest == "self_attn.q_proj.weight") { B2_TRY(expect(q_r * H)); return done(put_head_rows(wq, src16, c.num_q_heads, e->qhead_step, e->nq)); }
+      if (rest == "self_attn.k_proj.weight") { B2_TRY(expect(kv_r * H)); return done(put_head_rows(wk, src16, c.num_kv_heads, 1, e->nkv)); }
+      if (rest == "self_attn.v_proj.weight") { B2_TRY(expect(kv_r * H)); return done(put_head_rows(wv, src16, c.num_kv_heads, 1, e->nkv)); }
+      if (rest == "self_attn.o_proj.weight") { B2_TRY(expect((size_t)H * q_r)); return done(put_head_cols(L.wo, src16, c.num_q_heads, e->qhead_step, e->nq)); }
+    }
+  } else {  // Phi-3: fused projections in the checkpoint, HF:models/phi3/modeling_phi3.py:53-54,224,237-241
+    if (rest == "self_attn.qkv_proj.weight") {
+      B2_TRY(expect((q_r + 2 * kv_r) * H));
+      B2_TRY(put_head_rows(wq, src16, c.num_q_heads, e->qhead_step, e->nq));
+      B2_TRY(put_head_rows(wk, src16 + q_r * H, c.num_kv_heads, 1, e->nkv));
+      return done(put_head_rows(wv, src16 + (q_r + kv_r) * H, c.num_kv_heads, 1, e->nkv));
+    }
+    if (rest == "self_attn.o_proj.weight") { B2_TRY(expect((size_t)H * q_r)); return done(put_head_cols(L.wo, src16, c.num_q_heads, e->qhead_step, e->nq)); }
+    if (rest == "mlp.gate_up_proj.weight") return put(L.wgu, (size_t)2 * I * H);  // [gate; up], the order chunk(2) splits
+  }
   if (rest == "mlp.down_proj.weight") return put(L.wd, (size_t)H * I);
   b2_set_error("unknown tensor name %s", name.c_str());
   return -22;
@@ -724,8 +790,17 @@ int load_safetensors(b2_engine* e, const char* path) {
 extern "C" int b2_engine_create(const b2_config* cfg, const char* safetensors_path, int device, b2_engine** out) {
   B2_REQUIRE(cfg != nullptr && out != nullptr, "b2_engine_create: null argument");
   B2_REQUIRE(cfg->abi_version == B2_ABI_VERSION, "b2_engine_create: abi_version %d != %d", cfg->abi_version, B2_ABI_VERSION);
-  B2_REQUIRE(cfg->head_dim == 128, "head_dim %d not built this round (128 only)", cfg->head_dim);
-  B2_REQUIRE(cfg->num_q_heads == 2 * cfg->num_kv_heads, "GQA group must be 2 (nq=%d nkv=%d)", cfg->num_q_heads, cfg->num_kv_heads);
+  B2_REQUIRE(cfg->arch == B2_ARCH_QWEN3 || cfg->arch == B2_ARCH_PHI3, "arch %d not built (0 = Qwen3, 1 = Phi-3)", cfg->arch);
+  B2_REQUIRE(cfg->head_dim >= 8 && cfg->head_dim <= 128 && cfg->head_dim % 8 == 0, "head_dim %d not supported (multiple of 8, <= 128)",
+             cfg->head_dim);
+  B2_REQUIRE(cfg->num_kv_heads >= 1 && (cfg->num_q_heads == 2 * cfg->num_kv_heads || cfg->num_q_heads == cfg->num_kv_heads),
+             "query heads per kv head must be 1 or 2 (nq=%d nkv=%d)", cfg->num_q_heads, cfg->num_kv_heads);
+  {
+    const int rd = cfg->rotary_dim > 0 ? cfg->rotary_dim : cfg->head_dim;
+    B2_REQUIRE(rd % 8 == 0 && rd <= cfg->head_dim, "rotary_dim %d must be a multiple of 8 and <= head_dim", rd);
+    B2_REQUIRE(cfg->arch != B2_ARCH_QWEN3 || (rd == cfg->head_dim && cfg->head_dim == 128),
+               "Qwen3: QK-norm is built for 128-wide, fully rotated heads (head_dim %d, rotary_dim %d)", cfg->head_dim, rd);
+  }
   B2_REQUIRE(cfg->block_size == 16, "block_size %d not built (16 only)", cfg->block_size);
   B2_REQUIRE(cfg->hidden % 256 == 0 && cfg->intermediate % 256 == 0, "hidden/intermediate must be multiples of 256");
   B2_REQUIRE(cfg->max_seqs >= 1 && cfg->max_batch_tokens >= 1 && cfg->max_model_len >= 1, "bad sizing");
@@ -747,8 +822,15 @@ extern "C" int b2_engine_create(const b2_config* cfg, const char* safetensors_pa
   e->device = device;
   e->num_sms = prop.multiProcessorCount;
   const b2_config& c = e->cfg;
-  e->q_size = c.num_q_heads * c.head_dim;
-  e->kv_size = c.num_kv_heads * c.head_dim;
+  e->hd = 128;
+  e->nkv = c.num_kv_heads;
+  e->nq = 2 * c.num_kv_heads;
+  e->qhead_step = (c.num_q_heads == c.num_kv_heads) ? 2 : 1;
+  e->native_geom = (c.head_dim == 128 && e->qhead_step == 1);
+  e->attn_scale = (float)(1.0 / sqrt((double)c.head_dim));  // HF passes head_dim**-0.5 as a double
+  e->rotary_dim = c.rotary_dim > 0 ? c.rotary_dim : c.head_dim;
+  e->q_size = e->nq * e->hd;
+  e->kv_size = e->nkv * e->hd;
   e->qkv_size = e->q_size + 2 * e->kv_size;
   e->simt_max_tokens = env_int("B2_SIMT_MAX_TOKENS", 0);
   e->attn_split_override = env_int("B2_ATTN_SPLITS", 0);
@@ -785,37 +867,46 @@ extern "C" int b2_engine_create(const b2_config* cfg, const char* safetensors_pa
     for (auto& L : e->layers) {
       E_TRY(dalloc(&L.ln1, (size_t)H));
       E_TRY(dalloc(&L.ln2, (size_t)H));
-      E_TRY(dalloc(&L.qnorm, (size_t)c.head_dim));
-      E_TRY(dalloc(&L.knorm, (size_t)c.head_dim));
+      if (c.arch == B2_ARCH_QWEN3) {  // Phi-3 has no QK-norm: the null gains switch it off in the kernel
+        E_TRY(dalloc(&L.qnorm, (size_t)c.head_dim));
+        E_TRY(dalloc(&L.knorm, (size_t)c.head_dim));
+      }
       E_TRY(dalloc(&L.wqkv, (size_t)e->qkv_size * H));
       E_TRY(dalloc(&L.wo, (size_t)H * e->q_size));
       E_TRY(dalloc(&L.wgu, (size_t)2 * I * H));
       E_TRY(dalloc(&L.wd, (size_t)H * I));
     }
     e->weight_bytes = 2ll * ((int64_t)c.vocab * H * (c.tie_embeddings ? 1 : 2) + H +
-                             (int64_t)c.num_layers * (2 * H + 2 * c.head_dim + (int64_t)e->qkv_size * H +
+                             (int64_t)c.num_layers * (2 * H + (c.arch == B2_ARCH_QWEN3 ? 2 * c.head_dim : 0) + (int64_t)e->qkv_size * H +
                                                       (int64_t)H * e->q_size + 3ll * I * H));
     // ---- RoPE table: cos/sin in fp32 from fp32 inv_freq * position, rounded to bf16
     //      (HF:models/qwen3/modeling_qwen3.py:132-148) ----
     {
-      const int hd = c.head_dim, half = hd / 2;
+      // table row = [cos 64 | sin 64]; a rotary width below 128 (Phi-3: 96) fills the first rotary_dim/2
+      // entries of each half, HF:models/phi3/modeling_phi3.py:199-205
+      const int rd = e->rotary_dim, half = rd / 2, row = 128;
       std::vector<float> inv(half);
       for (int i = 0; i < half; ++i) {
         if (cfg->rope_inv_freq) inv[i] = cfg->rope_inv_freq[i];
-        else inv[i] = (float)(1.0 / pow((double)c.rope_theta, (double)(2 * i) / (double)hd));
+        else inv[i] = (float)(1.0 / pow((double)c.rope_theta, (double)(2 * i) / (double)rd));
       }
-      std::vector<uint16_t> tab((size_t)c.max_model_len * hd);
+      std::vector<uint16_t> tab((size_t)c.max_model_len * row);
       auto to_bf16 = [](float f) -> uint16_t {
         uint32_t u;
         memcpy(&u, &f, 4);
         return (uint16_t)((u + 0x7fffu + ((u >> 16) & 1u)) >> 16);
       };
-      for (int p = 0; p < c.max_model_len; ++p)
+      for (int p = 0; p < c.max_model_len; ++p) {
+        for (int i = 0; i < 64; ++i) {
+          tab[(size_t)p * row + i] = to_bf16(1.0f);
+          tab[(size_t)p * row + 64 + i] = to_bf16(0.0f);
+        }
         for (int i = 0; i < half; ++i) {
           float fr = (float)p * inv[i];  // fp32 product, as the fp32 matmul in HF
-          tab[(size_t)p * hd + i] = to_bf16((float)cos((double)fr));
-          tab[(size_t)p * hd + half + i] = to_bf16((float)sin((double)fr));
+          tab[(size_t)p * row + i] = to_bf16((float)cos((double)fr));
+          tab[(size_t)p * row + 64 + i] = to_bf16((float)sin((double)fr));
         }
+      }
       E_TRY(dalloc(&e->cos_sin, tab.size()));
       E_CUDA(cudaMemcpy(e->cos_sin, tab.data(), tab.size() * 2, cudaMemcpyHostToDevice));
     }
@@ -838,7 +929,7 @@ extern "C" int b2_engine_create(const b2_config* cfg, const char* safetensors_pa
     E_CUDA(cudaMemset(e->xlast, 0, last_rows * H * 2));
     e->partial_floats = (size_t)16 << 20;  // 64 MB of fp32 split-K partials
     E_TRY(dalloc(&e->partial, e->partial_floats));
-    e->attn_scratch_floats = attn_decode_scratch_floats(bucket_batch(c.max_seqs), c.num_q_heads, c.num_kv_heads, c.head_dim);
+    e->attn_scratch_floats = attn_decode_scratch_floats(bucket_batch(c.max_seqs), e->nq, e->nkv, e->hd);
     E_TRY(dalloc(&e->attn_scratch, e->attn_scratch_floats));
     E_CUDA(cudaMemset(e->attn_scratch, 0, e->attn_scratch_floats * sizeof(float)));  // arrival counters start at zero
     for (int bi = 0; bi < 5; ++bi) {
@@ -886,7 +977,7 @@ extern "C" int b2_engine_create(const b2_config* cfg, const char* safetensors_pa
     e->seqs.resize(c.max_seqs);
     // ---- KV pool ----
     {
-      const size_t blk_elems = (size_t)c.num_kv_heads * c.block_size * c.head_dim;
+      const size_t blk_elems = (size_t)e->nkv * c.block_size * e->hd;
       int64_t nb = c.num_blocks;
       if (nb <= 0) {
         size_t free_b = 0, total_b = 0;
@@ -932,7 +1023,7 @@ extern "C" int b2_engine_load_tensor(b2_engine* e, const char* hf_name, const vo
 
 extern "C" int b2_engine_finalize(b2_engine* e) {
   B2_REQUIRE(e, "b2_engine_finalize: null engine");
-  const int per_layer = 11;
+  const int per_layer = e->cfg.arch == B2_ARCH_QWEN3 ? 11 : 6;
   const int want = 2 + e->cfg.num_layers * per_layer;
   int have = 0;
   for (auto& kv : e->loaded)
@@ -1266,14 +1357,14 @@ extern "C" int b2_attn_profile(b2_engine* e, int32_t nseq, const int32_t* seq_id
              "b2_attn_profile: run a decode step on exactly this batch first (the pass reuses its device-side page tables)");
   const b2_config& c = e->cfg;
   int64_t bytes = 0;
-  for (int i = 0; i < nseq; ++i) bytes += (int64_t)(e->seqs[seq_ids[i]].len + 1) * c.num_kv_heads * c.head_dim * 2 * 2;
+  for (int i = 0; i < nseq; ++i) bytes += (int64_t)(e->seqs[seq_ids[i]].len + 1) * e->nkv * e->hd * 2 * 2;
   const int B = e->cur_B;
   auto pass = [&]() -> int {
     for (int l = 0; l < c.num_layers; ++l) {
       bf16* kp = e->kv_pool + (size_t)(2 * l) * e->layer_kv_elems;
       bf16* vp = kp + e->layer_kv_elems;
       B2_TRY(launch_attn_decode(e->qrot, kp, vp, e->d_block_table, e->bt_stride, e->d_seq_lens, e->attn_scratch, e->attn, B,
-                                c.num_q_heads, c.num_kv_heads, c.head_dim, c.block_size, e->stream));
+                                e->nq, e->nkv, e->hd, c.block_size, e->stream, e->attn_scale));
     }
     return 0;
   };

@@ -20,7 +20,9 @@ int launch_embed(const int32_t* ids, const bf16* table, bf16* h, int T, int H, i
 int launch_add_rmsnorm(bf16* h, ActIn delta, const bf16* w, bf16* x, int T, int H, float eps, cudaStream_t s);
 int launch_qknorm_rope_kv(ActIn qkv, const bf16* qw, const bf16* kw, const bf16* cos_sin, const int32_t* positions,
                           const int32_t* slots, bf16* q_out, bf16* k_pages, bf16* v_pages, int T, int nq, int nkv,
-                          int hd, int block_size, float eps, cudaStream_t s);
+                          int hd, int block_size, float eps, cudaStream_t s, int rotary_dim = 128);
+// qw == kw == nullptr: no QK-norm (Phi-3).  rotary_dim: width of the rotated prefix of each head; heads narrower
+// than 128 are stored zero-padded to 128 (see engine.cu, "internal geometry").
 int launch_silu_mul(ActIn gu, bf16* act, int T, int I, cudaStream_t s);
 int launch_gather_rows(const bf16* src, const int32_t* rows, bf16* dst, int n, int H, cudaStream_t s);
 int launch_argmax_rows(const bf16* logits, int32_t* out, int T, int V, cudaStream_t s);
@@ -103,7 +105,8 @@ size_t attn_decode_scratch_floats(int B, int nq, int nkv, int hd);
 int attn_decode_zero_counters(float* scratch, cudaStream_t s);
 int launch_attn_decode(const bf16* q, const bf16* k_pages, const bf16* v_pages, const int32_t* block_table,
                        int bt_stride, const int32_t* seq_lens, float* scratch, bf16* out, int B, int nq, int nkv,
-                       int hd, int block_size, cudaStream_t s);
+                       int hd, int block_size, cudaStream_t s, float softmax_scale = 0.f);
+// softmax_scale 0 = hd^-0.5; a padded head passes the scale of its real width.
 
 // ---- attn_prefill.cu ----
 struct PrefillTile {  // one 64-query tile of one sequence
@@ -114,7 +117,7 @@ struct PrefillTile {  // one 64-query tile of one sequence
 };
 int launch_attn_prefill(const bf16* q, const bf16* k_pages, const bf16* v_pages, const int32_t* block_table,
                         int bt_stride, const PrefillTile* tiles_dev, int ntiles, bf16* out, int nq, int nkv, int hd,
-                        int block_size, cudaStream_t s);
+                        int block_size, cudaStream_t s, float softmax_scale = 0.f);
 
 // ---- sampling.cu ----
 int launch_sample(const bf16* logits, int32_t* out, int nseq, int V, float temperature, int top_k, float top_p, uint64_t seed,

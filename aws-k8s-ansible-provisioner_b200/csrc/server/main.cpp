@@ -146,6 +146,12 @@ static void fill_config(const Options& o, b2_config& c) {
     const Value* rp = j.find("rope_parameters");
     if (rp && rp->find("rope_theta")) theta = rp->find("rope_theta")->as_double(theta);
     c.rope_theta = (float)theta;
+    // model family: "model_type" of the HF config.json (qwen3 / phi3)
+    const Value* mt = j.find("model_type");
+    if (mt && mt->is_string() && mt->as_string() == "phi3") {
+      c.arch = B2_ARCH_PHI3;
+      c.rotary_dim = (int)(getf("partial_rotary_factor", 1.0) * c.head_dim + 0.5);
+    }
   }
   c.max_model_len = o.max_model_len;
   c.block_size = o.block_size;

@@ -37,6 +37,8 @@ class EngineConfig:
     max_seqs: int = 64
     max_batch_tokens: int = 8192
     use_cuda_graphs: bool = True
+    arch: str = "qwen3"          # "qwen3" | "phi3" (include/b2_engine.h, enum b2_arch)
+    rotary_dim: int = 0          # 0 = head_dim
 
     def kv_bytes_per_token(self) -> int:
         return 2 * self.num_layers * self.num_kv_heads * self.head_dim * 2
@@ -75,10 +77,12 @@ class Engine:
         c.rms_eps = cfg.rms_eps
         c.rope_theta = cfg.rope_theta
         c.gpu_mem_fraction = cfg.gpu_mem_fraction
+        c.arch = {"qwen3": capi.ARCH_QWEN3, "phi3": capi.ARCH_PHI3}[cfg.arch]
+        c.rotary_dim = int(cfg.rotary_dim)
         self._inv = None
         if rope_inv_freq is not None:
             self._inv = np.ascontiguousarray(np.asarray(rope_inv_freq, dtype=np.float32))
-            assert self._inv.shape == (cfg.head_dim // 2,)
+            assert self._inv.shape == ((cfg.rotary_dim or cfg.head_dim) // 2,)
             c.rope_inv_freq = self._inv.ctypes.data_as(C.POINTER(C.c_float))
         h = C.c_void_p()
         path = safetensors_path.encode() if safetensors_path else None

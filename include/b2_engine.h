@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define B2_ABI_VERSION 1
+#define B2_ABI_VERSION 2
 
 typedef struct b2_engine b2_engine;
 
@@ -38,7 +38,7 @@ typedef struct b2_config {
   int32_t hidden;            /* 1024 */
   int32_t num_q_heads;       /* 16 */
   int32_t num_kv_heads;      /* 8 */
-  int32_t head_dim;          /* 128 (only 128 is built this round) */
+  int32_t head_dim;          /* 128; narrower heads (Phi-3: 96) run zero-padded to 128 */
   int32_t intermediate;      /* 3072 */
   int32_t vocab;             /* 151936 */
   int32_t tie_embeddings;    /* 1: lm_head shares embed_tokens (HF:...modeling_qwen3.py:443) */
@@ -51,9 +51,18 @@ typedef struct b2_config {
   int32_t max_seqs;          /* max concurrently resident sequences (decode batch ceiling) */
   int32_t max_batch_tokens;  /* max tokens in one prefill forward */
   int32_t use_cuda_graphs;   /* 1: decode steps replay a captured graph per batch bucket */
-  const float* rope_inv_freq;/* optional host [head_dim/2] fp32 table (HF:...:129-131); NULL =
+  const float* rope_inv_freq;/* optional host [rotary_dim/2] fp32 table (HF:...:129-131); NULL =
                                 computed as theta^(-2i/d) in double, rounded to fp32 */
+  int32_t arch;              /* B2_ARCH_*: which HF model family the tensors and the layer follow */
+  int32_t rotary_dim;        /* width of the rotated prefix of each head; 0 = head_dim */
 } b2_config;
+
+/* Model families.  QWEN3: HF:models/qwen3/modeling_qwen3.py (QK-norm, separate q/k/v and gate/up
+ * tensors, GQA).  PHI3: HF:models/phi3/modeling_phi3.py:49-64,208-272 (fused qkv_proj and
+ * gate_up_proj tensors, no QK-norm, one query head per kv head or two, rotary over rotary_dim,
+ * usually an untied lm_head; sliding-window attention is NOT implemented -- contexts up to the
+ * window are exact). */
+enum b2_arch { B2_ARCH_QWEN3 = 0, B2_ARCH_PHI3 = 1 };
 
 const char* b2_last_error(void);
 int  b2_abi_version(void);

@@ -110,6 +110,30 @@ def tiny() -> None:
     print("wrote qwen3_tiny.npz", out.logits.shape)
 
 
+def phi3_tiny() -> None:
+    """HF Phi3ForCausalLM outputs for the two tiny Phi-3 variants (full and partial rotary)."""
+    from oracle.phi3_oracle import PHI3_TINY, PHI3_TINY_PARTIAL, hf_phi3_model
+
+    out_d = {}
+    for tag, arch in (("full", PHI3_TINY), ("partial", PHI3_TINY_PARTIAL)):
+        model = hf_phi3_model(arch, seed=0)
+        sd = hf_state_dict(model)
+        perturb_norm_weights(sd)
+        model.load_state_dict(sd)
+        ids = make_prompts(3, 40, arch.vocab, seed=1)
+        with torch.no_grad():
+            gen = model.generate(ids, attention_mask=torch.ones_like(ids), do_sample=False, max_new_tokens=24,
+                                 min_new_tokens=24, pad_token_id=0)[:, 40:]
+            full = torch.cat([ids, gen], dim=1)
+            out = model(full, output_hidden_states=True)
+        out_d[tag + "_prompt_ids"] = ids.numpy().astype(np.int32)
+        out_d[tag + "_greedy_ids"] = gen.numpy().astype(np.int32)
+        out_d[tag + "_logits_bf16"] = out.logits.view(torch.int16).numpy()
+        out_d[tag + "_hidden_bf16"] = torch.stack(out.hidden_states).view(torch.int16).numpy()
+    np.savez_compressed(os.path.join(GOLD, "phi3_tiny.npz"), **out_d)
+    print("wrote phi3_tiny.npz")
+
+
 def templates() -> None:
     import jinja2
     import yaml
@@ -142,12 +166,18 @@ def templates() -> None:
 def main() -> None:
     ap = argparse.ArgumentParser()
     ap.add_argument("--skip-full", action="store_true")
+    ap.add_argument("--only", default="", help="comma list of: templates,tiny,phi3,full")
     a = ap.parse_args()
     os.makedirs(GOLD, exist_ok=True)
     torch.set_num_threads(min(8, os.cpu_count() or 1))
-    templates()
-    tiny()
-    if not a.skip_full:
+    only = set(x for x in a.only.split(",") if x)
+    if not only or "templates" in only:
+        templates()
+    if not only or "tiny" in only:
+        tiny()
+    if not only or "phi3" in only:
+        phi3_tiny()
+    if (not only and not a.skip_full) or "full" in only:
         full_c1()
 
 
