@@ -146,6 +146,8 @@ int launch_add_rmsnorm(bf16* h, ActIn delta, const bf16* w, bf16* x, int T, int 
 // (qw == kw == nullptr) and a rotary width other than 128 -- rot_quads = rotary_dim / 8 lanes hold
 // the first half, the next rot_quads lanes the second half, later lanes pass through (q_pass);
 // heads narrower than 128 are stored zero-padded, and zeros stay zeros through every step here.
+// OPT (HF:models/opt/modeling_opt.py:151-157): neither norm nor rotary (rot_quads == 0), but biased
+// projections and a pre-scaled query: v = bf16(partials + bias), q = bf16(v * q_mul).
 // ---------------------------------------------------------------------------------------
 template <bool F32IN>
 __global__ void qknorm_rope_kv_kernel(const void* __restrict__ qkv, int nsplit, size_t split_stride,
@@ -153,7 +155,7 @@ __global__ void qknorm_rope_kv_kernel(const void* __restrict__ qkv, int nsplit, 
                                       const bf16* __restrict__ cos_sin, const int32_t* __restrict__ positions,
                                       const int32_t* __restrict__ slots, bf16* __restrict__ q_out,
                                       bf16* __restrict__ k_pages, bf16* __restrict__ v_pages, int T, int nq, int nkv,
-                                      int block_size, float eps, int early, int rot_quads) {
+                                      int block_size, float eps, int early, int rot_quads, const bf16* __restrict__ bias, float q_mul) {
   constexpr int HD = 128;
   if (!early) pdl_wait();
   const int nheads = nq + 2 * nkv;
@@ -192,6 +194,11 @@ __global__ void qknorm_rope_kv_kernel(const void* __restrict__ qkv, int nsplit, 
       sn[0] = bf16lo(sraw.x); sn[1] = bf16hi(sraw.x); sn[2] = bf16lo(sraw.y); sn[3] = bf16hi(sraw.y);
     }
   }
+  float bq[4] = {0.f, 0.f, 0.f, 0.f};
+  if (F32IN && bias != nullptr) {
+    uint2 braw = *reinterpret_cast<const uint2*>(bias + (size_t)head * HD + lane * 4);
+    bq[0] = bf16lo(braw.x); bq[1] = bf16hi(braw.x); bq[2] = bf16lo(braw.y); bq[3] = bf16hi(braw.y);
+  }
   pdl_wait();
   pdl_launch_dependents();
 
@@ -203,6 +210,7 @@ __global__ void qknorm_rope_kv_kernel(const void* __restrict__ qkv, int nsplit, 
       float4 a = *reinterpret_cast<const float4*>(p + s * split_stride);
       acc.x += a.x; acc.y += a.y; acc.z += a.z; acc.w += a.w;
     }
+    acc.x += bq[0]; acc.y += bq[1]; acc.z += bq[2]; acc.w += bq[3];  // zeros unless the projection has a bias
     v[0] = bf16_round(acc.x); v[1] = bf16_round(acc.y); v[2] = bf16_round(acc.z); v[3] = bf16_round(acc.w);
   } else {
     uint2 a = *reinterpret_cast<const uint2*>(reinterpret_cast<const bf16*>(qkv) + row);
@@ -224,6 +232,10 @@ __global__ void qknorm_rope_kv_kernel(const void* __restrict__ qkv, int nsplit, 
       if (rotates) v[e] = bf16_round(bf16_round(v[e] * c[e]) + bf16_round(rot * sn[e]));
     }
   }
+  if (is_q && q_mul != 1.0f) {
+#pragma unroll
+    for (int e = 0; e < 4; ++e) v[e] = bf16_round(v[e] * q_mul);
+  }
   uint2 o;
   o.x = pack_bf16x2(v[0], v[1]);
   o.y = pack_bf16x2(v[2], v[3]);
@@ -242,11 +254,12 @@ __global__ void qknorm_rope_kv_kernel(const void* __restrict__ qkv, int nsplit, 
 
 int launch_qknorm_rope_kv(ActIn qkv, const bf16* qw, const bf16* kw, const bf16* cos_sin, const int32_t* positions,
                           const int32_t* slots, bf16* q_out, bf16* k_pages, bf16* v_pages, int T, int nq, int nkv,
-                          int hd, int block_size, float eps, cudaStream_t s, int rotary_dim) {
+                          int hd, int block_size, float eps, cudaStream_t s, int rotary_dim, const bf16* bias, float q_mul) {
   if (T <= 0) return 0;
   B2_REQUIRE(hd == 128, "qknorm_rope_kv: head_dim %d not built (128 only; narrower heads are stored padded)", hd);
   B2_REQUIRE((qw == nullptr) == (kw == nullptr), "qknorm_rope_kv: q and k norm gains must both be given or both be null");
-  B2_REQUIRE(rotary_dim >= 8 && rotary_dim <= 128 && rotary_dim % 8 == 0, "qknorm_rope_kv: rotary width %d not supported", rotary_dim);
+  B2_REQUIRE(rotary_dim >= 0 && rotary_dim <= 128 && rotary_dim % 8 == 0, "qknorm_rope_kv: rotary width %d not supported", rotary_dim);
+  B2_REQUIRE(bias == nullptr || qkv.is_f32, "qknorm_rope_kv: a bias needs the projection's fp32 partials (it is added before rounding)");
   const int rot_quads = rotary_dim / 8;
   const int nheads = nq + 2 * nkv;
   const long long warps = (long long)T * nheads;
@@ -254,10 +267,10 @@ int launch_qknorm_rope_kv(ActIn qkv, const bf16* qw, const bf16* kw, const bf16*
   if (qkv.is_f32)
     B2_CUDA_OK(b2_launch(qknorm_rope_kv_kernel<true>, dim3(blocks), dim3(128), 0, s, qkv.ptr, qkv.nsplit,
                          (size_t)T * nheads * hd, qw, kw, cos_sin, positions, slots, q_out, k_pages, v_pages, T, nq, nkv,
-                         block_size, eps, b2_pdl_early_mask() & 4, rot_quads));
+                         block_size, eps, b2_pdl_early_mask() & 4, rot_quads, bias, q_mul));
   else
     B2_CUDA_OK(b2_launch(qknorm_rope_kv_kernel<false>, dim3(blocks), dim3(128), 0, s, qkv.ptr, 1, (size_t)0, qw, kw, cos_sin,
-                         positions, slots, q_out, k_pages, v_pages, T, nq, nkv, block_size, eps, b2_pdl_early_mask() & 4, rot_quads));
+                         positions, slots, q_out, k_pages, v_pages, T, nq, nkv, block_size, eps, b2_pdl_early_mask() & 4, rot_quads, bias, q_mul));
   return 0;
 }
 

@@ -53,6 +53,8 @@ namespace {
 struct LayerW {
   bf16 *ln1 = nullptr, *ln2 = nullptr, *qnorm = nullptr, *knorm = nullptr;
   bf16 *wqkv = nullptr, *wo = nullptr, *wgu = nullptr, *wd = nullptr;
+  // OPT only (biased projections, LayerNorm biases); wgu then holds fc1 [I][H] and wd holds fc2
+  bf16 *bqkv = nullptr, *bo = nullptr, *ln1_b = nullptr, *ln2_b = nullptr, *b1 = nullptr, *b2 = nullptr;
   CUtensorMap tm_qkv, tm_o, tm_gu, tm_d;
 };
 
@@ -100,6 +102,10 @@ struct b2_engine {
   bf16* embed = nullptr;
   bf16* lm_head = nullptr;  // == embed when tied
   bf16* final_norm = nullptr;
+  bf16* final_norm_b = nullptr;  // OPT
+  bf16* pos_embed = nullptr;     // OPT: learned positions [pos_rows][H], row = position + 2
+  int pos_rows = 0;
+  int gu_rows = 0;               // rows of wgu: 2*I (gate; up) or I (OPT fc1)
   std::vector<LayerW> layers;
   CUtensorMap tm_lm_head;
   std::map<std::string, int> loaded;
@@ -236,11 +242,21 @@ int pick_attn_split(b2_engine* e, int B, int max_len) {
 
 // ---- one Linear layer: picks SIMT GEMV or the tcgen05 kernel, bf16 or split-K partial output
 ActIn linear(b2_engine* e, int cls, XBuf xb, const bf16* xptr, const bf16* w, const CUtensorMap& tm_w, bf16* out_bf16, int T,
-             int N, int K, int* rc, const KvPrefetch& pf = KvPrefetch()) {
+             int N, int K, int* rc, const KvPrefetch& pf = KvPrefetch(), bool want_f32 = false) {
+  // want_f32: hand the consumer fp32 sums even when K is not split (a bias is added before the rounding)
   *rc = 0;
   int impl = e->force_gemm_impl >= 0 ? e->force_gemm_impl : (T <= e->simt_max_tokens ? 0 : 1);
+  if (want_f32 && (size_t)T * N > e->partial_floats) {
+    b2_set_error("linear: %d x %d fp32 outputs exceed the partial buffer", T, N);
+    *rc = -12;
+    return act_bf16(nullptr);
+  }
   if (impl == 0) {
     KL k(e, cls);
+    if (want_f32) {
+      if (!k.skip()) *rc = launch_linear_simt(xptr, w, e->partial, 1, T, N, K, e->stream);
+      return act_f32(e->partial, 1);
+    }
     if (!k.skip()) *rc = launch_linear_simt(xptr, w, out_bf16, 0, T, N, K, e->stream);
     return act_bf16(out_bf16);
   }
@@ -259,7 +275,7 @@ ActIn linear(b2_engine* e, int cls, XBuf xb, const bf16* xptr, const bf16* w, co
   }
   a.nsplit = ns;
   KL k(e, cls);
-  if (ns == 1) {
+  if (ns == 1 && !want_f32) {
     a.epilogue = TC_EPI_BF16;
     a.out = out_bf16;
     if (!k.skip()) *rc = launch_linear_tc(a, e->stream);
@@ -356,11 +372,86 @@ int forward_decode_chain(b2_engine* e, int T) {
   return lm_head_and_argmax(e, T, e->x, XB_X);
 }
 
+// OPT decoder (HF:models/opt/modeling_opt.py:363-391 OPTDecoder.forward, :203-254 OPTDecoderLayer.forward with
+// do_layer_norm_before): same GEMM and attention kernels, the elementwise steps of elementwise_opt.cu.
+int forward_opt(b2_engine* e, int T, int ntiles, int nlast) {
+  const b2_config& c = e->cfg;
+  const int H = c.hidden, I = c.intermediate;
+  int rc = 0;
+  {
+    KL k(e, B2K_EMBED);
+    if (!k.skip()) B2_TRY(launch_embed_pos(e->d_tokens, e->d_positions, e->embed, e->pos_embed, e->h, T, H, c.vocab, e->pos_rows,
+                                           e->d_argmax, nlast, e->stream));
+  }
+  dbg_capture(e, 0, e->h, T);
+  ActIn delta = act_bf16(nullptr);
+  const bf16* delta_bias = nullptr;
+  for (int l = 0; l < c.num_layers; ++l) {
+    LayerW& L = e->layers[l];
+    bf16* kp = e->kv_pool + (size_t)(2 * l) * e->layer_kv_elems;
+    bf16* vp = kp + e->layer_kv_elems;
+    {
+      KL k(e, B2K_NORM);
+      if (!k.skip()) B2_TRY(launch_add_layernorm(e->h, delta, delta_bias, L.ln1, L.ln1_b, e->x, T, H, c.rms_eps, e->stream));
+    }
+    if (l > 0) dbg_capture(e, l, e->h, T);
+    ActIn qkv = linear(e, B2K_GEMM_QKV, XB_X, e->x, L.wqkv, L.tm_qkv, e->qkv, T, e->qkv_size, H, &rc, KvPrefetch(), true);
+    B2_TRY(rc);
+    {
+      // HF:...:151 "query_states = self.q_proj(hidden_states) * self.scaling", then attention with scaling 1.0
+      KL k(e, B2K_ROPE_KV);
+      if (!k.skip()) B2_TRY(launch_qknorm_rope_kv(qkv, nullptr, nullptr, e->cos_sin, e->d_positions, e->d_slots, e->qrot, kp, vp, T,
+                                   e->nq, e->nkv, e->hd, c.block_size, c.rms_eps, e->stream, 0, L.bqkv, e->attn_scale));
+    }
+    if (ntiles > 0) {
+      KL k(e, B2K_MISC);
+      if (!k.skip()) B2_TRY(launch_attn_prefill(e->qrot, kp, vp, e->d_block_table, e->bt_stride, e->d_tiles, ntiles, e->attn,
+                                 e->nq, e->nkv, e->hd, c.block_size, e->stream, 1.0f));
+    } else {
+      KL k(e, B2K_ATTN_DECODE);
+      if (!k.skip())
+        B2_TRY(launch_attn_decode(e->qrot, kp, vp, e->d_block_table, e->bt_stride, e->d_seq_lens, e->attn_scratch, e->attn, T,
+                                  e->nq, e->nkv, e->hd, c.block_size, e->stream, 1.0f));
+    }
+    ActIn o = linear(e, B2K_GEMM_O, XB_ATTN, e->attn, L.wo, L.tm_o, e->proj, T, H, e->q_size, &rc, KvPrefetch(), true);
+    B2_TRY(rc);
+    {
+      KL k(e, B2K_NORM);
+      if (!k.skip()) B2_TRY(launch_add_layernorm(e->h, o, L.bo, L.ln2, L.ln2_b, e->x, T, H, c.rms_eps, e->stream));
+    }
+    ActIn f1 = linear(e, B2K_GEMM_GATEUP, XB_X, e->x, L.wgu, L.tm_gu, e->gu, T, I, H, &rc, KvPrefetch(), true);
+    B2_TRY(rc);
+    {
+      KL k(e, B2K_ACT);
+      if (!k.skip()) B2_TRY(launch_bias_relu(f1, L.b1, e->act, T, I, e->stream));
+    }
+    delta = linear(e, B2K_GEMM_DOWN, XB_ACT, e->act, L.wd, L.tm_d, e->proj, T, H, I, &rc, KvPrefetch(), true);
+    delta_bias = L.b2;
+    B2_TRY(rc);
+  }
+  {
+    KL k(e, B2K_NORM);
+    if (!k.skip()) B2_TRY(launch_add_layernorm(e->h, delta, delta_bias, e->final_norm, e->final_norm_b, e->x, T, H, c.rms_eps, e->stream));
+  }
+  dbg_capture(e, c.num_layers, e->h, T);
+  dbg_capture(e, c.num_layers + 1, e->x, T);
+  const bf16* xl = e->x;
+  XBuf xb = XB_X;
+  if (ntiles > 0) {
+    KL k(e, B2K_MISC);
+    if (!k.skip()) B2_TRY(launch_gather_rows(e->x, e->d_last_rows, e->xlast, nlast, H, e->stream));
+    xl = e->xlast;
+    xb = XB_LAST;
+  }
+  return lm_head_and_argmax(e, nlast, xl, xb);
+}
+
 int forward(b2_engine* e, int T, int ntiles, int nlast, int attn_split) {
   const b2_config& c = e->cfg;
   const int H = c.hidden, I = c.intermediate;
   int rc = 0;
-  if (ntiles == 0 && e->use_chain && !(e->debug_flags & 1) && e->force_gemm_impl != 0 && T > e->simt_max_tokens)
+  if (c.arch == B2_ARCH_OPT) return forward_opt(e, T, ntiles, nlast);
+  if (ntiles == 0 && e->use_chain && c.arch == B2_ARCH_QWEN3 && !(e->debug_flags & 1) && e->force_gemm_impl != 0 && T > e->simt_max_tokens)
     return forward_decode_chain(e, T);
   {
     KL k(e, B2K_EMBED);
@@ -659,6 +750,67 @@ int layer_tensor(b2_engine* e, const std::string& name, const void* host, size_t
   };
   const size_t q_r = (size_t)c.num_q_heads * hd_r, kv_r = (size_t)c.num_kv_heads * hd_r;  // checkpoint widths
   const uint16_t* src16 = reinterpret_cast<const uint16_t*>(host);
+  if (c.arch == B2_ARCH_OPT) {
+    // HF:models/opt/modeling_opt.py state dict: model.decoder.{embed_tokens,embed_positions,final_layer_norm,layers.N.*}
+    auto put_head_vec = [&](bf16* dst, int heads, int step) -> int {  // bias of a per-head projection, zero in the padding
+      std::vector<uint16_t> stage((size_t)heads * step * 128, 0);
+      for (int h = 0; h < heads; ++h) memcpy(&stage[(size_t)h * step * 128], src16 + (size_t)h * hd_r, (size_t)hd_r * 2);
+      B2_CUDA_OK(cudaMemcpy(dst, stage.data(), stage.size() * 2, cudaMemcpyHostToDevice));
+      return 0;
+    };
+    auto mark = [&](int rc) {
+      if (rc == 0) e->loaded[name] = 1;
+      return rc;
+    };
+    const std::string dec = "model.decoder.";
+    if (name == "lm_head.weight") {
+      e->loaded[name] = 1;  // tied to embed_tokens
+      return 0;
+    }
+    if (name.compare(0, dec.size(), dec) != 0) {
+      b2_set_error("unknown tensor name %s", name.c_str());
+      return -22;
+    }
+    const std::string r0 = name.substr(dec.size());
+    if (r0 == "embed_tokens.weight") return put(e->embed, (size_t)c.vocab * H);
+    if (r0 == "embed_positions.weight") return put(e->pos_embed, (size_t)e->pos_rows * H);
+    if (r0 == "final_layer_norm.weight") return put(e->final_norm, H);
+    if (r0 == "final_layer_norm.bias") return put(e->final_norm_b, H);
+    const std::string lp = "layers.";
+    size_t d2 = r0.find('.', lp.size());
+    if (r0.compare(0, lp.size(), lp) != 0 || d2 == std::string::npos) {
+      b2_set_error("unknown tensor name %s", name.c_str());
+      return -22;
+    }
+    const int li = atoi(r0.substr(lp.size(), d2 - lp.size()).c_str());
+    if (li < 0 || li >= c.num_layers) {
+      b2_set_error("tensor %s: layer out of range", name.c_str());
+      return -22;
+    }
+    LayerW& L = e->layers[li];
+    const std::string rest = r0.substr(d2 + 1);
+    bf16* wq = L.wqkv;
+    bf16* wk = L.wqkv + (size_t)e->q_size * H;
+    bf16* wv = L.wqkv + (size_t)(e->q_size + e->kv_size) * H;
+    if (rest == "self_attn_layer_norm.weight") return put(L.ln1, H);
+    if (rest == "self_attn_layer_norm.bias") return put(L.ln1_b, H);
+    if (rest == "final_layer_norm.weight") return put(L.ln2, H);
+    if (rest == "final_layer_norm.bias") return put(L.ln2_b, H);
+    if (rest == "self_attn.q_proj.weight") { B2_TRY(expect(q_r * H)); return mark(put_head_rows(wq, src16, c.num_q_heads, e->qhead_step, e->nq)); }
+    if (rest == "self_attn.k_proj.weight") { B2_TRY(expect(kv_r * H)); return mark(put_head_rows(wk, src16, c.num_kv_heads, 1, e->nkv)); }
+    if (rest == "self_attn.v_proj.weight") { B2_TRY(expect(kv_r * H)); return mark(put_head_rows(wv, src16, c.num_kv_heads, 1, e->nkv)); }
+    if (rest == "self_attn.out_proj.weight") { B2_TRY(expect((size_t)H * q_r)); return mark(put_head_cols(L.wo, src16, c.num_q_heads, e->qhead_step, e->nq)); }
+    if (rest == "self_attn.q_proj.bias") { B2_TRY(expect(q_r)); return mark(put_head_vec(L.bqkv, c.num_q_heads, e->qhead_step)); }
+    if (rest == "self_attn.k_proj.bias") { B2_TRY(expect(kv_r)); return mark(put_head_vec(L.bqkv + e->q_size, c.num_kv_heads, 1)); }
+    if (rest == "self_attn.v_proj.bias") { B2_TRY(expect(kv_r)); return mark(put_head_vec(L.bqkv + e->q_size + e->kv_size, c.num_kv_heads, 1)); }
+    if (rest == "self_attn.out_proj.bias") return put(L.bo, H);
+    if (rest == "fc1.weight") return put(L.wgu, (size_t)I * H);
+    if (rest == "fc1.bias") return put(L.b1, I);
+    if (rest == "fc2.weight") return put(L.wd, (size_t)H * I);
+    if (rest == "fc2.bias") return put(L.b2, H);
+    b2_set_error("unknown tensor name %s", name.c_str());
+    return -22;
+  }
   if (name == "model.embed_tokens.weight") return put(e->embed, (size_t)c.vocab * H);
   if (name == "model.norm.weight") return put(e->final_norm, H);
   if (name == "lm_head.weight") {
@@ -790,13 +942,15 @@ int load_safetensors(b2_engine* e, const char* path) {
 extern "C" int b2_engine_create(const b2_config* cfg, const char* safetensors_path, int device, b2_engine** out) {
   B2_REQUIRE(cfg != nullptr && out != nullptr, "b2_engine_create: null argument");
   B2_REQUIRE(cfg->abi_version == B2_ABI_VERSION, "b2_engine_create: abi_version %d != %d", cfg->abi_version, B2_ABI_VERSION);
-  B2_REQUIRE(cfg->arch == B2_ARCH_QWEN3 || cfg->arch == B2_ARCH_PHI3, "arch %d not built (0 = Qwen3, 1 = Phi-3)", cfg->arch);
+  B2_REQUIRE(cfg->arch == B2_ARCH_QWEN3 || cfg->arch == B2_ARCH_PHI3 || cfg->arch == B2_ARCH_OPT,
+             "arch %d not built (0 = Qwen3, 1 = Phi-3, 2 = OPT)", cfg->arch);
+  B2_REQUIRE(cfg->arch != B2_ARCH_OPT || cfg->tie_embeddings, "OPT: the lm_head is tied to embed_tokens");
   B2_REQUIRE(cfg->head_dim >= 8 && cfg->head_dim <= 128 && cfg->head_dim % 8 == 0, "head_dim %d not supported (multiple of 8, <= 128)",
              cfg->head_dim);
   B2_REQUIRE(cfg->num_kv_heads >= 1 && (cfg->num_q_heads == 2 * cfg->num_kv_heads || cfg->num_q_heads == cfg->num_kv_heads),
              "query heads per kv head must be 1 or 2 (nq=%d nkv=%d)", cfg->num_q_heads, cfg->num_kv_heads);
   {
-    const int rd = cfg->rotary_dim > 0 ? cfg->rotary_dim : cfg->head_dim;
+    const int rd = cfg->arch == B2_ARCH_OPT ? 0 : (cfg->rotary_dim > 0 ? cfg->rotary_dim : cfg->head_dim);
     B2_REQUIRE(rd % 8 == 0 && rd <= cfg->head_dim, "rotary_dim %d must be a multiple of 8 and <= head_dim", rd);
     B2_REQUIRE(cfg->arch != B2_ARCH_QWEN3 || (rd == cfg->head_dim && cfg->head_dim == 128),
                "Qwen3: QK-norm is built for 128-wide, fully rotated heads (head_dim %d, rotary_dim %d)", cfg->head_dim, rd);
@@ -828,7 +982,9 @@ extern "C" int b2_engine_create(const b2_config* cfg, const char* safetensors_pa
   e->qhead_step = (c.num_q_heads == c.num_kv_heads) ? 2 : 1;
   e->native_geom = (c.head_dim == 128 && e->qhead_step == 1);
   e->attn_scale = (float)(1.0 / sqrt((double)c.head_dim));  // HF passes head_dim**-0.5 as a double
-  e->rotary_dim = c.rotary_dim > 0 ? c.rotary_dim : c.head_dim;
+  e->rotary_dim = c.arch == B2_ARCH_OPT ? 0 : (c.rotary_dim > 0 ? c.rotary_dim : c.head_dim);
+  e->gu_rows = c.arch == B2_ARCH_OPT ? c.intermediate : 2 * c.intermediate;
+  e->pos_rows = c.arch == B2_ARCH_OPT ? (c.max_positions > 0 ? c.max_positions : c.max_model_len) + 2 : 0;
   e->q_size = e->nq * e->hd;
   e->kv_size = e->nkv * e->hd;
   e->qkv_size = e->q_size + 2 * e->kv_size;
@@ -873,12 +1029,27 @@ extern "C" int b2_engine_create(const b2_config* cfg, const char* safetensors_pa
       }
       E_TRY(dalloc(&L.wqkv, (size_t)e->qkv_size * H));
       E_TRY(dalloc(&L.wo, (size_t)H * e->q_size));
-      E_TRY(dalloc(&L.wgu, (size_t)2 * I * H));
+      E_TRY(dalloc(&L.wgu, (size_t)e->gu_rows * H));
       E_TRY(dalloc(&L.wd, (size_t)H * I));
+      if (c.arch == B2_ARCH_OPT) {
+        E_TRY(dalloc(&L.bqkv, (size_t)e->qkv_size));
+        E_CUDA(cudaMemset(L.bqkv, 0, (size_t)e->qkv_size * 2));  // padded slots keep a zero bias
+        E_TRY(dalloc(&L.bo, (size_t)H));
+        E_TRY(dalloc(&L.ln1_b, (size_t)H));
+        E_TRY(dalloc(&L.ln2_b, (size_t)H));
+        E_TRY(dalloc(&L.b1, (size_t)I));
+        E_TRY(dalloc(&L.b2, (size_t)H));
+      }
+    }
+    if (c.arch == B2_ARCH_OPT) {
+      E_TRY(dalloc(&e->final_norm_b, (size_t)H));
+      E_TRY(dalloc(&e->pos_embed, (size_t)e->pos_rows * H));
     }
     e->weight_bytes = 2ll * ((int64_t)c.vocab * H * (c.tie_embeddings ? 1 : 2) + H +
                              (int64_t)c.num_layers * (2 * H + (c.arch == B2_ARCH_QWEN3 ? 2 * c.head_dim : 0) + (int64_t)e->qkv_size * H +
-                                                      (int64_t)H * e->q_size + 3ll * I * H));
+                                                      (int64_t)H * e->q_size + ((int64_t)e->gu_rows + I) * H) +
+                             (c.arch == B2_ARCH_OPT ? (int64_t)e->pos_rows * H + H +
+                                                          (int64_t)c.num_layers * (e->qkv_size + 4ll * H + I) : 0));
     // ---- RoPE table: cos/sin in fp32 from fp32 inv_freq * position, rounded to bf16
     //      (HF:models/qwen3/modeling_qwen3.py:132-148) ----
     {
@@ -928,6 +1099,8 @@ extern "C" int b2_engine_create(const b2_config* cfg, const char* safetensors_pa
     E_CUDA(cudaMemset(e->act, 0, Tc * I * 2));
     E_CUDA(cudaMemset(e->xlast, 0, last_rows * H * 2));
     e->partial_floats = (size_t)16 << 20;  // 64 MB of fp32 split-K partials
+    if (c.arch == B2_ARCH_OPT)  // every projection hands over fp32 sums (the bias goes in before the rounding), even unsplit
+      e->partial_floats = std::max(e->partial_floats, Tc * (size_t)std::max(std::max(e->qkv_size, I), H));
     E_TRY(dalloc(&e->partial, e->partial_floats));
     e->attn_scratch_floats = attn_decode_scratch_floats(bucket_batch(c.max_seqs), e->nq, e->nkv, e->hd);
     E_TRY(dalloc(&e->attn_scratch, e->attn_scratch_floats));
@@ -941,7 +1114,7 @@ extern "C" int b2_engine_create(const b2_config* cfg, const char* safetensors_pa
     for (auto& L : e->layers) {
       E_TRY(b2_make_tmap_bf16(&L.tm_qkv, L.wqkv, e->qkv_size, H, H, 128));
       E_TRY(b2_make_tmap_bf16(&L.tm_o, L.wo, H, e->q_size, e->q_size, 128));
-      E_TRY(b2_make_tmap_bf16(&L.tm_gu, L.wgu, 2 * I, H, H, 128));
+      E_TRY(b2_make_tmap_bf16(&L.tm_gu, L.wgu, e->gu_rows, H, H, 128));
       E_TRY(b2_make_tmap_bf16(&L.tm_d, L.wd, H, I, I, 128));
     }
     E_TRY(b2_make_tmap_bf16(&e->tm_lm_head, e->lm_head, c.vocab, H, H, 128));
@@ -1023,8 +1196,9 @@ extern "C" int b2_engine_load_tensor(b2_engine* e, const char* hf_name, const vo
 
 extern "C" int b2_engine_finalize(b2_engine* e) {
   B2_REQUIRE(e, "b2_engine_finalize: null engine");
-  const int per_layer = e->cfg.arch == B2_ARCH_QWEN3 ? 11 : 6;
-  const int want = 2 + e->cfg.num_layers * per_layer;
+  const int arch = e->cfg.arch;
+  const int per_layer = arch == B2_ARCH_QWEN3 ? 11 : arch == B2_ARCH_PHI3 ? 6 : 16;
+  const int want = (arch == B2_ARCH_OPT ? 4 : 2) + e->cfg.num_layers * per_layer;
   int have = 0;
   for (auto& kv : e->loaded)
     if (kv.first != "lm_head.weight") ++have;
@@ -1047,9 +1221,10 @@ extern "C" void b2_engine_free(b2_engine* e) {
     if (p) cudaFree(p);
   };
   if (e->lm_head != e->embed) F(e->lm_head);
-  F(e->embed); F(e->final_norm); F(e->cos_sin);
+  F(e->embed); F(e->final_norm); F(e->cos_sin); F(e->final_norm_b); F(e->pos_embed);
   for (auto& L : e->layers) {
     F(L.ln1); F(L.ln2); F(L.qnorm); F(L.knorm); F(L.wqkv); F(L.wo); F(L.wgu); F(L.wd);
+    F(L.bqkv); F(L.bo); F(L.ln1_b); F(L.ln2_b); F(L.b1); F(L.b2);
   }
   F(e->kv_pool); F(e->h); F(e->x); F(e->qkv); F(e->qrot); F(e->attn); F(e->gu); F(e->act); F(e->proj); F(e->xlast);
   F(e->partial); F(e->attn_scratch); F(e->d_tokens); F(e->d_positions); F(e->d_seq_lens); F(e->d_slots);

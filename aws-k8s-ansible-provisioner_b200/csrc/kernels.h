@@ -20,9 +20,18 @@ int launch_embed(const int32_t* ids, const bf16* table, bf16* h, int T, int H, i
 int launch_add_rmsnorm(bf16* h, ActIn delta, const bf16* w, bf16* x, int T, int H, float eps, cudaStream_t s);
 int launch_qknorm_rope_kv(ActIn qkv, const bf16* qw, const bf16* kw, const bf16* cos_sin, const int32_t* positions,
                           const int32_t* slots, bf16* q_out, bf16* k_pages, bf16* v_pages, int T, int nq, int nkv,
-                          int hd, int block_size, float eps, cudaStream_t s, int rotary_dim = 128);
+                          int hd, int block_size, float eps, cudaStream_t s, int rotary_dim = 128, const bf16* bias = nullptr,
+                          float q_mul = 1.0f);
 // qw == kw == nullptr: no QK-norm (Phi-3).  rotary_dim: width of the rotated prefix of each head; heads narrower
-// than 128 are stored zero-padded to 128 (see engine.cu, "internal geometry").
+// than 128 are stored zero-padded to 128 (see engine.cu, "internal geometry").  bias [(nq + 2 nkv) * 128]: added to the
+// fp32 partials before the rounding; q_mul: the query is multiplied by it afterwards (OPT pre-scales q).
+
+// ---- elementwise_opt.cu (OPT variant) ----
+int launch_embed_pos(const int32_t* ids, const int32_t* positions, const bf16* table, const bf16* pos_table, bf16* h, int T, int H,
+                     int vocab, int pos_rows, unsigned long long* zero_buf, int nzero, cudaStream_t s);
+int launch_add_layernorm(bf16* h, ActIn delta, const bf16* delta_bias, const bf16* w, const bf16* b, bf16* x, int T, int H, float eps,
+                         cudaStream_t s);
+int launch_bias_relu(ActIn fc1, const bf16* bias, bf16* act, int T, int I, cudaStream_t s);
 int launch_silu_mul(ActIn gu, bf16* act, int T, int I, cudaStream_t s);
 int launch_gather_rows(const bf16* src, const int32_t* rows, bf16* dst, int n, int H, cudaStream_t s);
 int launch_argmax_rows(const bf16* logits, int32_t* out, int T, int V, cudaStream_t s);

@@ -151,6 +151,15 @@ static void fill_config(const Options& o, b2_config& c) {
     if (mt && mt->is_string() && mt->as_string() == "phi3") {
       c.arch = B2_ARCH_PHI3;
       c.rotary_dim = (int)(getf("partial_rotary_factor", 1.0) * c.head_dim + 0.5);
+    } else if (mt && mt->is_string() && mt->as_string() == "opt") {
+      // HF OPTConfig names: ffn_dim, no kv-head count (MHA), LayerNorm eps is torch's default
+      c.arch = B2_ARCH_OPT;
+      c.num_kv_heads = c.num_q_heads;
+      c.head_dim = c.hidden / std::max(1, c.num_q_heads);
+      c.intermediate = geti("ffn_dim", c.intermediate);
+      c.max_positions = geti("max_position_embeddings", 2048);
+      c.rms_eps = 1e-5f;
+      c.tie_embeddings = 1;
     }
   }
   c.max_model_len = o.max_model_len;

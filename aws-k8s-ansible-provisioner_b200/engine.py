@@ -37,8 +37,9 @@ class EngineConfig:
     max_seqs: int = 64
     max_batch_tokens: int = 8192
     use_cuda_graphs: bool = True
-    arch: str = "qwen3"          # "qwen3" | "phi3" (include/b2_engine.h, enum b2_arch)
+    arch: str = "qwen3"          # "qwen3" | "phi3" | "opt" (include/b2_engine.h, enum b2_arch)
     rotary_dim: int = 0          # 0 = head_dim
+    max_positions: int = 0       # OPT: learned position table rows - 2 (0 = max_model_len)
 
     def kv_bytes_per_token(self) -> int:
         return 2 * self.num_layers * self.num_kv_heads * self.head_dim * 2
@@ -77,8 +78,9 @@ class Engine:
         c.rms_eps = cfg.rms_eps
         c.rope_theta = cfg.rope_theta
         c.gpu_mem_fraction = cfg.gpu_mem_fraction
-        c.arch = {"qwen3": capi.ARCH_QWEN3, "phi3": capi.ARCH_PHI3}[cfg.arch]
+        c.arch = {"qwen3": capi.ARCH_QWEN3, "phi3": capi.ARCH_PHI3, "opt": capi.ARCH_OPT}[cfg.arch]
         c.rotary_dim = int(cfg.rotary_dim)
+        c.max_positions = int(cfg.max_positions)
         self._inv = None
         if rope_inv_freq is not None:
             self._inv = np.ascontiguousarray(np.asarray(rope_inv_freq, dtype=np.float32))

@@ -134,6 +134,31 @@ def phi3_tiny() -> None:
     print("wrote phi3_tiny.npz")
 
 
+def opt_tiny() -> None:
+    """HF OPTForCausalLM outputs for the tiny OPT configuration (LayerNorm gains and all biases perturbed)."""
+    from oracle.opt_oracle import OPT_TINY, hf_opt_model, perturb_opt_weights
+
+    arch = OPT_TINY
+    model = hf_opt_model(arch, seed=0)
+    sd = hf_state_dict(model)
+    perturb_opt_weights(sd)
+    model.load_state_dict(sd)
+    ids = make_prompts(3, 40, arch.vocab, seed=1)
+    with torch.no_grad():
+        gen = model.generate(ids, attention_mask=torch.ones_like(ids), do_sample=False, max_new_tokens=24,
+                             min_new_tokens=24, pad_token_id=1)[:, 40:]
+        full = torch.cat([ids, gen], dim=1)
+        out = model(full, output_hidden_states=True)
+    np.savez_compressed(
+        os.path.join(GOLD, "opt_tiny.npz"),
+        prompt_ids=ids.numpy().astype(np.int32),
+        greedy_ids=gen.numpy().astype(np.int32),
+        logits_bf16=out.logits.view(torch.int16).numpy(),
+        hidden_bf16=torch.stack(out.hidden_states).view(torch.int16).numpy(),
+    )
+    print("wrote opt_tiny.npz", out.logits.shape)
+
+
 def templates() -> None:
     import jinja2
     import yaml
@@ -166,7 +191,7 @@ def templates() -> None:
 def main() -> None:
     ap = argparse.ArgumentParser()
     ap.add_argument("--skip-full", action="store_true")
-    ap.add_argument("--only", default="", help="comma list of: templates,tiny,phi3,full")
+    ap.add_argument("--only", default="", help="comma list of: templates,tiny,phi3,opt,full")
     a = ap.parse_args()
     os.makedirs(GOLD, exist_ok=True)
     torch.set_num_threads(min(8, os.cpu_count() or 1))
@@ -177,6 +202,8 @@ def main() -> None:
         tiny()
     if not only or "phi3" in only:
         phi3_tiny()
+    if not only or "opt" in only:
+        opt_tiny()
     if (not only and not a.skip_full) or "full" in only:
         full_c1()
 
