@@ -64,6 +64,7 @@ SIGNATURES = {
     "b2k_linear": (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _I, _P]),
     "b2k_debug_gemm_trace": (_I, [_P]),
     "b2k_debug_chain_trace": (_I, [_P]),
+    "b2k_debug_fused_trace": (_I, [_P]),
     "b2k_lmhead_argmax": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _I, _P]),
     "b2k_attn_decode": (_I, [_P, _P, _P, _P, _I, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
     "b2k_attn_decode_scratch_floats": (C.c_size_t, [_I, _I, _I, _I]),

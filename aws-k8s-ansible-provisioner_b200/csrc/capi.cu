@@ -64,6 +64,7 @@ extern "C" int b2k_linear(const void* x, const void* w, void* out, int out_is_f3
 
 extern "C" int b2k_debug_gemm_trace(void* dev_u64_buf) { return tc_set_trace((unsigned long long*)dev_u64_buf); }
 extern "C" int b2k_debug_chain_trace(void* dev_u64_buf) { return chain_set_trace((unsigned long long*)dev_u64_buf); }
+extern "C" int b2k_debug_fused_trace(void* dev_u64_buf) { return fused_chain_set_trace((unsigned long long*)dev_u64_buf); }
 
 extern "C" int b2k_lmhead_argmax(const void* x, const void* w, void* logits, int32_t* out_tokens, void* scratch_u64, int T, int V,
                                  int K, int impl, void* stream) {

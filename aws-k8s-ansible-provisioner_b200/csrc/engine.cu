@@ -56,6 +56,7 @@ struct LayerW {
   // OPT only (biased projections, LayerNorm biases); wgu then holds fc1 [I][H] and wd holds fc2
   bf16 *bqkv = nullptr, *bo = nullptr, *ln1_b = nullptr, *ln2_b = nullptr, *b1 = nullptr, *b2 = nullptr;
   CUtensorMap tm_qkv, tm_o, tm_gu, tm_d;
+  CUtensorMap tm_o32, tm_gu96, tm_d32;  // narrow-box maps of the fused chain (chain_cluster.cu)
 };
 
 struct Seq {
@@ -176,6 +177,9 @@ struct b2_engine {
   int32_t* d_pf_frac = nullptr;
   int32_t* d_sample_out = nullptr;
   unsigned long long* d_gbar = nullptr;  // grid-barrier arrival counter of the decode chain kernel
+  float* d_ss = nullptr;                  // fused chain: 2 x [32][64] sums of squares
+  unsigned long long* d_gbar2 = nullptr;  // fused chain: its grid-barrier counter
+  bool fused_ok = false;                  // shapes + cluster occupancy allow the fused chain
   int use_chain = 0;              // B2_CHAIN=1: decode through the persistent chain kernel (chain.cu; measured slower, kept for A/B runs)  // B2_SKIP_MASK: kernel classes left out (timing ablations only; results are garbage)
 };
 
@@ -372,6 +376,68 @@ int forward_decode_chain(b2_engine* e, int T) {
   return lm_head_and_argmax(e, T, e->x, XB_X);
 }
 
+// Decode through the fused four-step chain (chain_cluster.cu).  The head of the forward (embedding, layer 0's input
+// norm, QKV and QK-norm/RoPE) and the tail (final norm, lm_head) use the separate kernels.
+int forward_decode_fused(b2_engine* e, int T) {
+  const b2_config& c = e->cfg;
+  const int H = c.hidden, I = c.intermediate, L = c.num_layers;
+  int rc = 0;
+  {
+    KL k(e, B2K_EMBED);
+    if (!k.skip()) B2_TRY(launch_embed(e->d_tokens, e->embed, e->h, T, H, c.vocab, e->d_argmax, T, e->stream));
+  }
+  {
+    KL k(e, B2K_NORM);
+    if (!k.skip()) B2_TRY(launch_add_rmsnorm(e->h, act_bf16(nullptr), e->layers[0].ln1, e->x, T, H, c.rms_eps, e->stream));
+  }
+  {
+    LayerW& L0 = e->layers[0];
+    bf16* kp = e->kv_pool;
+    bf16* vp = kp + e->layer_kv_elems;
+    ActIn qkv = linear(e, B2K_GEMM_QKV, XB_X, e->x, L0.wqkv, L0.tm_qkv, e->qkv, T, e->qkv_size, H, &rc);
+    B2_TRY(rc);
+    KL k(e, B2K_ROPE_KV);
+    if (!k.skip()) B2_TRY(launch_qknorm_rope_kv(qkv, L0.qnorm, L0.knorm, e->cos_sin, e->d_positions, e->d_slots, e->qrot, kp, vp, T,
+                                 e->nq, e->nkv, e->hd, c.block_size, c.rms_eps, e->stream, e->rotary_dim));
+  }
+  FusedChainParams p;
+  memset(&p, 0, sizeof p);
+  p.T = T;
+  p.h = e->h; p.act = e->act; p.qrot = e->qrot;
+  p.cos_sin = e->cos_sin; p.positions = e->d_positions; p.slots = e->d_slots;
+  p.ss_a = e->d_ss; p.ss_b = e->d_ss + 32 * 64;
+  p.H = H; p.I = I; p.nq = e->nq; p.nkv = e->nkv; p.block_size = c.block_size; p.eps = c.rms_eps;
+  p.gbar = e->d_gbar2;
+  const int bi = bn_index(64);
+  CUtensorMap am[2] = {e->tm_x[XB_ATTN][bi], e->tm_x[XB_ACT][bi]};
+  for (int l = 0; l < L; ++l) {
+    LayerW& Lw = e->layers[l];
+    bf16* kp = e->kv_pool + (size_t)(2 * l) * e->layer_kv_elems;
+    bf16* vp = kp + e->layer_kv_elems;
+    {
+      KL k(e, B2K_ATTN_DECODE);
+      if (!k.skip())
+        B2_TRY(launch_attn_decode(e->qrot, kp, vp, e->d_block_table, e->bt_stride, e->d_seq_lens, e->attn_scratch, e->attn, T,
+                                  e->nq, e->nkv, e->hd, c.block_size, e->stream, e->attn_scale));
+    }
+    const bool last = (l + 1 == L);
+    LayerW& Ln = e->layers[last ? l : l + 1];
+    CUtensorMap wm[4] = {Lw.tm_o32, Lw.tm_gu96, Lw.tm_d32, Ln.tm_qkv};
+    p.phase_begin = 0; p.phase_end = last ? 3 : 4;
+    p.norm_w_a = Lw.ln2; p.norm_w_b = Ln.ln1;
+    p.qw = Ln.qnorm; p.kw = Ln.knorm;
+    p.k_pages = e->kv_pool + (size_t)(2 * (last ? l : l + 1)) * e->layer_kv_elems;
+    p.v_pages = p.k_pages + e->layer_kv_elems;
+    KL k(e, B2K_CHAIN);
+    if (!k.skip()) B2_TRY(launch_decode_fused_chain(wm, am, p, e->stream));
+  }
+  {
+    KL k(e, B2K_NORM);  // the last down step has already added the residual: normalise only
+    if (!k.skip()) B2_TRY(launch_add_rmsnorm(e->h, act_bf16(nullptr), e->final_norm, e->x, T, H, c.rms_eps, e->stream));
+  }
+  return lm_head_and_argmax(e, T, e->x, XB_X);
+}
+
 // OPT decoder (HF:models/opt/modeling_opt.py:363-391 OPTDecoder.forward, :203-254 OPTDecoderLayer.forward with
 // do_layer_norm_before): same GEMM and attention kernels, the elementwise steps of elementwise_opt.cu.
 int forward_opt(b2_engine* e, int T, int ntiles, int nlast) {
@@ -451,7 +517,10 @@ int forward(b2_engine* e, int T, int ntiles, int nlast, int attn_split) {
   const int H = c.hidden, I = c.intermediate;
   int rc = 0;
   if (c.arch == B2_ARCH_OPT) return forward_opt(e, T, ntiles, nlast);
-  if (ntiles == 0 && e->use_chain && c.arch == B2_ARCH_QWEN3 && !(e->debug_flags & 1) && e->force_gemm_impl != 0 && T > e->simt_max_tokens)
+  if (ntiles == 0 && e->use_chain == 2 && e->fused_ok && c.arch == B2_ARCH_QWEN3 && !(e->debug_flags & 1) &&
+      e->force_gemm_impl != 0 && T > e->simt_max_tokens && T <= 64 && e->skip_mask == 0)
+    return forward_decode_fused(e, T);
+  if (ntiles == 0 && e->use_chain == 1 && c.arch == B2_ARCH_QWEN3 && !(e->debug_flags & 1) && e->force_gemm_impl != 0 && T > e->simt_max_tokens)
     return forward_decode_chain(e, T);
   {
     KL k(e, B2K_EMBED);
@@ -992,6 +1061,8 @@ extern "C" int b2_engine_create(const b2_config* cfg, const char* safetensors_pa
   e->attn_split_override = env_int("B2_ATTN_SPLITS", 0);
   e->force_gemm_impl = env_int("B2_GEMM_IMPL", -1);
   e->skip_mask = (unsigned)env_int("B2_SKIP_MASK", 0);
+  // 0 separate kernels (default: fastest measured), 1 eight-step chain kernel (chain.cu), 2 fused four-step cluster
+  // chain (chain_cluster.cu); 1 and 2 are kept as measured experiments with parity tests
   e->use_chain = env_int("B2_CHAIN", 0);
   // Off by default: measured on B200 at C2 (ms/step) 0 MB 2.22, 40 MB 2.24, 72 MB 2.33, 100 MB 2.38 --
   // un-paced prefetch bursts queue ahead of the projections' own latency-critical weight loads.
@@ -1115,6 +1186,9 @@ extern "C" int b2_engine_create(const b2_config* cfg, const char* safetensors_pa
       E_TRY(b2_make_tmap_bf16(&L.tm_qkv, L.wqkv, e->qkv_size, H, H, 128));
       E_TRY(b2_make_tmap_bf16(&L.tm_o, L.wo, H, e->q_size, e->q_size, 128));
       E_TRY(b2_make_tmap_bf16(&L.tm_gu, L.wgu, e->gu_rows, H, H, 128));
+      E_TRY(b2_make_tmap_bf16(&L.tm_o32, L.wo, H, e->q_size, e->q_size, 32));
+      E_TRY(b2_make_tmap_bf16(&L.tm_gu96, L.wgu, e->gu_rows, H, H, 96));
+      E_TRY(b2_make_tmap_bf16(&L.tm_d32, L.wd, H, I, I, 32));
       E_TRY(b2_make_tmap_bf16(&L.tm_d, L.wd, H, I, I, 128));
     }
     E_TRY(b2_make_tmap_bf16(&e->tm_lm_head, e->lm_head, c.vocab, H, H, 128));
@@ -1134,6 +1208,13 @@ extern "C" int b2_engine_create(const b2_config* cfg, const char* safetensors_pa
     E_TRY(dalloc(&e->d_sample_out, Bcap));
     E_TRY(dalloc(&e->d_gbar, (size_t)1));
     E_CUDA(cudaMemset(e->d_gbar, 0, 8));
+    E_TRY(dalloc(&e->d_gbar2, (size_t)1));
+    E_CUDA(cudaMemset(e->d_gbar2, 0, 8));
+    // the fused chain spins on a grid-wide barrier: all of its 32 clusters must be resident at once
+    e->fused_ok = e->native_geom && c.arch == B2_ARCH_QWEN3 &&
+                  fused_chain_supported(H, I, e->nq, e->nkv, e->hd, 1, c.block_size) && fused_chain_max_clusters() >= 32;
+    E_TRY(dalloc(&e->d_ss, (size_t)2 * 32 * 64));
+    E_CUDA(cudaMemset(e->d_ss, 0, 2 * 32 * 64 * 4));
     E_CUDA(cudaMemset(e->d_pf_frac, 0, 4));
     e->log_cap_steps = 4096;
     E_TRY(dalloc(&e->d_token_log, (size_t)e->log_cap_steps * c.max_seqs));
@@ -1228,7 +1309,7 @@ extern "C" void b2_engine_free(b2_engine* e) {
   }
   F(e->kv_pool); F(e->h); F(e->x); F(e->qkv); F(e->qrot); F(e->attn); F(e->gu); F(e->act); F(e->proj); F(e->xlast);
   F(e->partial); F(e->attn_scratch); F(e->d_tokens); F(e->d_positions); F(e->d_seq_lens); F(e->d_slots);
-  F(e->d_block_table); F(e->d_last_rows); F(e->d_out_tokens); F(e->d_token_log); F(e->d_step); F(e->d_argmax); F(e->d_pf_frac); F(e->d_sample_out); F(e->d_gbar);
+  F(e->d_block_table); F(e->d_last_rows); F(e->d_out_tokens); F(e->d_token_log); F(e->d_step); F(e->d_argmax); F(e->d_pf_frac); F(e->d_sample_out); F(e->d_gbar); F(e->d_gbar2); F(e->d_ss);
   F(e->d_tiles); F(e->dbg_hidden); F(e->logits);
   if (e->h_stage) cudaFreeHost(e->h_stage);
   if (e->h_tiles) cudaFreeHost(e->h_tiles);

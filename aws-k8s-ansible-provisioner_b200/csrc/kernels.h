@@ -104,6 +104,27 @@ struct ChainParams {
 int chain_set_trace(unsigned long long* dev_buf);  // diagnostics (null = off)
 int launch_decode_chain(const CUtensorMap* w_maps4, const CUtensorMap* x_maps4, const ChainParams& p, cudaStream_t s);
 
+// ---- chain_cluster.cu: the chain in four fused steps (0 O + residual, 1 RMSNorm + gate-up + SwiGLU,
+//      2 down + residual, 3 RMSNorm + QKV of the next layer + QK-norm/RoPE/KV write) ----
+struct FusedChainParams {
+  int T, phase_begin, phase_end;      // runs steps [phase_begin, phase_end)
+  bf16 *h, *act, *qrot;
+  const bf16 *norm_w_a, *norm_w_b;    // gains folded into step 1 (post-attention norm) / step 3 (next layer's input norm)
+  const bf16 *qw, *kw, *cos_sin;
+  const int32_t *positions, *slots;
+  bf16 *k_pages, *v_pages;            // pools of the layer whose QKV step 3 computes
+  float *ss_a, *ss_b;                 // [32 slices][64 tokens] sums of squares left by step 0 / step 2
+  int H, I, nq, nkv, block_size;
+  float eps;
+  unsigned long long* gbar;           // grid barrier arrival counter (its own: 128 CTAs)
+};
+int fused_chain_supported(int H, int I, int nq, int nkv, int hd, int T, int block_size);
+int fused_chain_max_clusters();
+int fused_chain_set_trace(unsigned long long* dev_buf);
+// w_maps4: Wo (box 64x32), Wgu (64x96), Wd (64x32), Wqkv of the next layer (64x128); a_maps2: attention output, SwiGLU
+// output (box 64x64)
+int launch_decode_fused_chain(const CUtensorMap* w_maps4, const CUtensorMap* a_maps2, const FusedChainParams& p, cudaStream_t s);
+
 // ---- attn_decode.cu ----
 // KV page-slice layout ([16 tokens][128 dims] bf16 = 4 KB per (page, kv head)): the 16-byte chunk c
 // (8 dims) of token row r is stored at chunk position c ^ (r & 7).  Every kernel that touches the

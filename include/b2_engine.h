@@ -196,6 +196,7 @@ int b2k_debug_gemm_trace(void* dev_u64_buf);
  * CTA finished step i's work (before the grid barrier), 8 = CTA start, 9 = dependency satisfied,
  * 10 = CTA done. */
 int b2k_debug_chain_trace(void* dev_u64_buf);
+int b2k_debug_fused_trace(void* dev_u64_buf);  /* same, for the fused four-step chain: 128 CTAs x 32 slots */
 
 /* lm_head + greedy argmax fused (HF:...:504-505 + generate(do_sample=False)).
  * logits_bf16 may be NULL.  out_tokens [T] int32 (device). scratch: [T] uint64 (device). */

@@ -297,6 +297,46 @@ def test_full_c1_greedy_and_logits(P, full):
     e.close()
 
 
+@pytest.mark.parametrize("chain", ["1", "2"])
+def test_full_alternative_decode_schedules(P, full, monkeypatch, chain):
+    """The two experimental decode schedules -- chain.cu (B2_CHAIN=1: eight steps behind grid barriers) and
+    chain_cluster.cu (B2_CHAIN=2: four fused steps, split-K reduced through distributed shared memory, RMSNorm
+    folded into the next GEMM's operand) -- compute the same layer with other summation orders: they must
+    reproduce HF's greedy ids on config 1 like the default path, and a batch of 64 must be deterministic."""
+    monkeypatch.setenv("B2_CHAIN", chain)
+    model, sd = full
+    arch = QWEN3_0_6B
+    fx = json.load(open(os.path.join(GOLD, "qwen3_0p6b_c1.json")))
+    prompt, gold = fx["prompt_ids"], np.array(fx["greedy_ids"])
+    e = make_engine(P, arch, sd, max_model_len=512, num_blocks=64 * 12 + 8, max_seqs=64, max_batch_tokens=2048, use_cuda_graphs=True)
+    sid = e.seq_create(300)
+    first = int(e.prefill([sid], [prompt])[0])
+    toks, _ = e.decode_run([sid], 127)
+    got = np.concatenate([[first], toks[:, 0]])
+    mism = np.nonzero(got != gold)[0]
+    n_match = 128 if len(mism) == 0 else int(mism[0])
+    print("B2_CHAIN=%s, C1 greedy: %d/128 leading tokens identical to HF" % (chain, n_match))
+    if len(mism):
+        top4 = np.array(fx["tf_top4_logits"])
+        t = int(mism[0])
+        gap = top4[127 + t][0] - top4[127 + t][1]
+        assert gap <= 0.0625, "first mismatch at step %d where the oracle's top-2 gap is %.4f (not a near-tie)" % (t, gap)
+    assert n_match >= 16
+    e.seq_free(sid)
+    # batch 64 (the shape chain_cluster.cu is built for): same bits run after run
+    p64 = make_prompts(64, 100, arch.vocab, seed=3)
+    runs = []
+    for rep in range(2):
+        sids = [e.seq_create(150) for _ in range(64)]
+        f = np.concatenate([e.prefill(sids[i:i + 16], [q.tolist() for q in p64[i:i + 16]]) for i in range(0, 64, 16)])
+        t64, _ = e.decode_run(sids, 16)
+        runs.append((f.copy(), t64.copy()))
+        for s_ in sids:
+            e.seq_free(s_)
+    assert np.array_equal(runs[0][0], runs[1][0]) and np.array_equal(runs[0][1], runs[1][1])
+    e.close()
+
+
 def test_full_batch64_properties(P):
     """BASELINE.json config 2 shapes (batch 64, paged KV) through size-independent properties.
     64 copies of one prompt: the prefill (one CTA per sequence tile) must give 64 identical first tokens;
