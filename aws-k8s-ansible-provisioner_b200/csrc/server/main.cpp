@@ -47,6 +47,7 @@ struct Options {
   std::string host = "0.0.0.0";
   int port = 8000;
   std::string chat_template_path;
+  std::string tokenizer_path;        // tokenizer.json, or a directory holding one; default: the model directory
   std::string load_format = "auto";  // auto: safetensors if the model dir has one, else dummy
   int max_model_len = 4096;
   int block_size = 16;
@@ -65,7 +66,9 @@ static void usage() {
           "usage: b2serve [MODEL] [--model M] [--served-model-name N] [--host H] [--port P] [--chat-template FILE]\n"
           "               [--max-model-len L] [--block-size 16] [--gpu-memory-utilization F] [--max-num-seqs N]\n"
           "               [--max-num-batched-tokens T] [--num-gpu-blocks-override N] [--seed S] [--load-format auto|dummy|safetensors]\n"
-          "               [--eos-token-id ID] [--device D] [--enforce-eager]\n");
+          "               [--eos-token-id ID] [--device D] [--enforce-eager] [--tokenizer FILE_OR_DIR]\n"
+          "       b2serve --render-chat-template FILE < {\"messages\": ...}     (no GPU)\n"
+          "       b2serve --tokenize TOKENIZER_JSON < {\"text\": ...} per line  (no GPU)\n");
 }
 
 static bool parse_args(int argc, char** argv, Options& o) {
@@ -97,8 +100,9 @@ static bool parse_args(int argc, char** argv, Options& o) {
     else if (key == "--device") o.device = atoi(V("--device").c_str());
     else if (key == "--enforce-eager") o.use_graphs = 0;
     else if (key == "--help" || key == "-h") { usage(); exit(0); }
+    else if (key == "--tokenizer") o.tokenizer_path = V("--tokenizer");
     else if (key == "--dtype" || key == "--tensor-parallel-size" || key == "--trust-remote-code" || key == "--disable-log-requests" ||
-             key == "--kv-cache-dtype" || key == "--tokenizer" || key == "--download-dir" || key == "--enable-prefix-caching") {
+             key == "--kv-cache-dtype" || key == "--download-dir" || key == "--enable-prefix-caching") {
       // accepted for chart compatibility; this build is bf16, one GPU per replica
       if (!has_inl && key != "--trust-remote-code" && key != "--disable-log-requests" && key != "--enable-prefix-caching" && i + 1 < argc) ++i;
     } else if (a.rfind("--", 0) == 0) { fprintf(stderr, "b2serve: unknown flag %s\n", a.c_str()); return false; }
@@ -460,8 +464,10 @@ struct App {
 };
 
 static const char* kDefaultChatTemplate =
-    "{%- for message in messages -%}<|im_start|>{{ message['role'] }}\n{{ message['content'] }}<|im_end|>\n{%- endfor -%}"
-    "{%- if add_generation_prompt -%}<|im_start|>assistant\n{%- endif -%}";
+    // ChatML, as Qwen's own template renders plain messages; no whitespace control: a `{%-` would eat the
+    // newline that belongs to the prompt
+    "{% for message in messages %}<|im_start|>{{ message['role'] }}\n{{ message['content'] }}<|im_end|>\n{% endfor %}"
+    "{% if add_generation_prompt %}<|im_start|>assistant\n{% endif %}";
 
 static std::string err_json(const std::string& msg, const std::string& type, int code) {
   Value e = Value::object();
@@ -744,8 +750,42 @@ static int render_mode(const char* path) {
   return 0;
 }
 
+// `b2serve --tokenize TOKENIZER_JSON` : reads one JSON object {"text": "..."} per line from stdin and prints
+// {"ids": [...], "text": <ids decoded again>} per line.  Needs no GPU; the CPU tests compare it with the HF
+// `tokenizers` library on the same tokenizer.json.
+static int tokenize_mode(const char* path) {
+  try {
+    std::string raw = read_file(path);
+    if (raw.empty()) throw std::runtime_error(std::string("cannot read ") + path);
+    b2tok::global_bpe() = std::make_shared<b2tok::Bpe>(raw);
+    std::string line;
+    while (std::getline(std::cin, line)) {
+      if (line.empty()) continue;
+      Value in = b2json::parse(line);
+      const Value* t = in.find("text");
+      std::vector<int32_t> ids = b2tok::encode(t ? t->as_string() : std::string());
+      b2tok::Detok d;
+      std::string back;
+      Value arr = Value::array();
+      for (int32_t id : ids) { arr.push(Value((int64_t)id)); back += d.push(id); }
+      back += d.finish();
+      Value out = Value::object();
+      out.set("ids", arr);
+      out.set("text", back);
+      std::string o = b2json::dump(out);
+      fwrite(o.data(), 1, o.size(), stdout);
+      fputc('\n', stdout);
+    }
+  } catch (const std::exception& ex) {
+    fprintf(stderr, "b2serve: %s\n", ex.what());
+    return 1;
+  }
+  return 0;
+}
+
 int main(int argc, char** argv) {
   if (argc == 3 && std::string(argv[1]) == "--render-chat-template") return render_mode(argv[2]);
+  if (argc == 3 && std::string(argv[1]) == "--tokenize") return tokenize_mode(argv[2]);
   App app;
   if (!parse_args(argc, argv, app.opt)) { usage(); return 2; }
   fill_config(app.opt, app.cfg);
@@ -760,6 +800,24 @@ int main(int argc, char** argv) {
     fprintf(stderr, "b2serve: no checkpoint found for %s; using random-init bf16 weights (seed %llu)\n", app.opt.model.c_str(), (unsigned long long)app.opt.seed);
     rc = load_dummy_weights(app.engine, app.cfg, app.opt.seed);
     if (rc != 0) { fprintf(stderr, "b2serve: weight init failed: %s\n", b2_last_error()); return 1; }
+  }
+  {  // tokenizer.json next to the weights (or --tokenizer): byte-level BPE; otherwise the byte fallback
+    std::string tp = app.opt.tokenizer_path.empty() ? app.opt.model : app.opt.tokenizer_path;
+    if (is_dir(tp)) tp += "/tokenizer.json";
+    if (is_file(tp) && tp.size() > 5 && tp.compare(tp.size() - 5, 5, ".json") == 0) {
+      try {
+        b2tok::global_bpe() = std::make_shared<b2tok::Bpe>(read_file(tp));
+        fprintf(stderr, "b2serve: tokenizer %s (%d tokens)\n", tp.c_str(), b2tok::global_bpe()->vocab_size());
+      } catch (const std::exception& ex) {
+        fprintf(stderr, "b2serve: %s: %s\n", tp.c_str(), ex.what());
+        return 1;
+      }
+    } else if (!app.opt.tokenizer_path.empty()) {
+      fprintf(stderr, "b2serve: no tokenizer.json at %s\n", app.opt.tokenizer_path.c_str());
+      return 1;
+    } else {
+      fprintf(stderr, "b2serve: no tokenizer.json for %s; text prompts use the byte fallback (1 byte = 1 id)\n", app.opt.model.c_str());
+    }
   }
   std::string tpl = kDefaultChatTemplate;
   if (!app.opt.chat_template_path.empty()) {

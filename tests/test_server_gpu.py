@@ -210,3 +210,72 @@ def test_concurrent_requests_share_the_batch(server):
     # the same prompt alone must give the same greedy text as inside the concurrent batch (tie-aware: prefix)
     st, solo = call(port, "POST", "/v1/completions", {"model": MODEL_ID, "prompt": [1, 2, 3, 4][:1], "max_tokens": 20, "temperature": 0})
     assert solo["choices"][0]["text"][:8] == results[0][1]["choices"][0]["text"][:8]
+
+
+# ---- with a tokenizer.json next to the weights (what the reference's model download provides) ---------
+@pytest.fixture(scope="module")
+def server_bpe(tmp_path_factory):
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    tokenizers = pytest.importorskip("tokenizers")
+    from tokenizers import Regex, Tokenizer, decoders, models, pre_tokenizers, trainers
+    P = pkg()
+    weights = importlib.import_module("aws-k8s-ansible-provisioner_b200.weights")
+    exe = os.path.join(os.path.dirname(P.LIB_PATH), "b2serve")
+    d = tmp_path_factory.mktemp("model_bpe")
+    arch = QWEN3_TINY
+    sd = random_weights(arch, seed=0)
+    weights.write_safetensors(sd, str(d / "model.safetensors"))
+    (d / "config.json").write_text(json.dumps({
+        "num_hidden_layers": arch.num_layers, "hidden_size": arch.hidden, "num_attention_heads": arch.num_q_heads,
+        "num_key_value_heads": arch.num_kv_heads, "head_dim": arch.head_dim, "intermediate_size": arch.intermediate,
+        "vocab_size": arch.vocab, "tie_word_embeddings": True, "rms_norm_eps": arch.rms_eps, "rope_theta": arch.rope_theta}))
+    pattern = (r"(?i:'s|'t|'re|'ve|'m|'ll|'d)|[^\r\n\p{L}\p{N}]?\p{L}+|\p{N}| ?[^\s\p{L}\p{N}]+[\r\n]*|\s*[\r\n]+|\s+(?!\S)|\s+")
+    tok = Tokenizer(models.BPE())
+    tok.pre_tokenizer = pre_tokenizers.Sequence([pre_tokenizers.Split(Regex(pattern), behavior="isolated"),
+                                                 pre_tokenizers.ByteLevel(add_prefix_space=False, use_regex=False)])
+    tok.decoder = decoders.ByteLevel()
+    with open(os.path.join(ROOT, "SURVEY.md"), encoding="utf-8") as f:
+        text = f.read()
+    tok.train_from_iterator([text], trainers.BpeTrainer(vocab_size=arch.vocab - 24, special_tokens=["<|im_start|>", "<|im_end|>"],
+                                                        initial_alphabet=pre_tokenizers.ByteLevel.alphabet(), show_progress=False))
+    tok.save(str(d / "tokenizer.json"))
+    proc = subprocess.Popen([exe, str(d), "--served-model-name", MODEL_ID, "--port", "0", "--host", "127.0.0.1", "--max-model-len", "512",
+                             "--max-num-seqs", "8", "--num-gpu-blocks-override", "128", "--max-num-batched-tokens", "256",
+                             "--eos-token-id", "-1"], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
+    port = None
+    t0 = time.time()
+    while time.time() - t0 < 120:
+        line = proc.stdout.readline()
+        if line.startswith("READY"):
+            port = int(line.split()[1])
+            break
+        if proc.poll() is not None:
+            break
+    if port is None:
+        proc.kill()
+        pytest.fail("b2serve did not start: " + proc.stderr.read())
+    yield {"port": port, "tok": tok}
+    proc.terminate()
+    try:
+        proc.wait(timeout=10)
+    except Exception:
+        proc.kill()
+
+
+def test_text_prompts_go_through_the_bpe_tokenizer(server_bpe):
+    tok, port = server_bpe["tok"], server_bpe["port"]
+    prompt = "Who are you? The model server's forward pass, 2026."
+    st, j = call(port, "POST", "/v1/completions", {"model": MODEL_ID, "prompt": prompt, "max_tokens": 8, "temperature": 0})
+    assert st == 200, j
+    assert j["usage"]["prompt_tokens"] == len(tok.encode(prompt).ids) < len(prompt)
+    # the same prompt as ids gives the same greedy continuation, and the text is those ids decoded
+    st, j2 = call(port, "POST", "/v1/completions", {"model": MODEL_ID, "prompt": tok.encode(prompt).ids, "max_tokens": 8, "temperature": 0})
+    assert st == 200 and j2["choices"][0]["text"] == j["choices"][0]["text"]
+    # default chat template: the <|im_start|> / <|im_end|> markers are single special tokens, not spelled out
+    msgs = [{"role": "user", "content": "Who are you?"}]
+    st, j3 = call(port, "POST", "/v1/chat/completions", {"model": MODEL_ID, "messages": msgs, "max_tokens": 4, "temperature": 0})
+    assert st == 200, j3
+    rendered = "<|im_start|>user\nWho are you?<|im_end|>\n<|im_start|>assistant\n"
+    assert j3["usage"]["prompt_tokens"] == len(tok.encode(rendered).ids)
+    assert j3["usage"]["prompt_tokens"] < 20
