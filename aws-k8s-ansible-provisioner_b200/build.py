@@ -21,6 +21,7 @@ CSRC = os.path.join(PKG, "csrc")
 BUILD = os.path.join(ROOT, "build")
 LIB = os.path.join(PKG, "libb2engine.so")
 SERVER = os.path.join(PKG, "b2serve")
+ROUTER = os.path.join(PKG, "b2route")
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
@@ -93,6 +94,14 @@ def build(verbose: bool = False, force: bool = False, ptxas_info: bool = False) 
             r = subprocess.run(cmd, capture_output=True, text=True)
             if r.returncode != 0:
                 raise RuntimeError("server build failed:\n%s\n%s" % (r.stdout, r.stderr))
+    router_dir = os.path.join(CSRC, "router")
+    if os.path.isdir(router_dir):  # the replica front needs neither CUDA nor the engine library
+        srcs = sorted(os.path.join(router_dir, f) for f in os.listdir(router_dir) if f.endswith(".cpp"))
+        if srcs and (force or _newer(ROUTER, srcs + hdrs)):
+            cmd = ["g++", "-O2", "-std=c++17", "-Wall", "-pthread", "-I", CSRC, *srcs, "-o", ROUTER]
+            r = subprocess.run(cmd, capture_output=True, text=True)
+            if r.returncode != 0:
+                raise RuntimeError("router build failed:\n%s\n%s" % (r.stdout, r.stderr))
     return LIB
 
 

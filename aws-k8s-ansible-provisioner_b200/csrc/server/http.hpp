@@ -45,6 +45,8 @@ class Conn {
     write_all(std::string(len) + payload + "\r\n");
   }
   void end_sse() { write_all("0\r\n\r\n"); }
+  // bytes that already are an HTTP response (a proxy relaying a backend's answer)
+  void raw_write(const char* p, size_t n) { write_all(std::string(p, n)); }
 
  private:
   int fd_;
