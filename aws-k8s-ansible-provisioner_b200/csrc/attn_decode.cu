@@ -60,6 +60,9 @@ struct AdPos {  // a position on the page line
   int b, kvh, j, nb;
 };
 
+#ifndef B2_ATTN_TRACE_BY_SMID
+#define B2_ATTN_TRACE_BY_SMID 1  // timing breadcrumbs indexed by SM id (tools/attn_timeline.py)
+#endif
 template <int AD_WARPS, int AD_STAGES>
 __global__ void __launch_bounds__(AD_WARPS * 32, 1)
 attn_decode_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k_pages, const bf16* __restrict__ v_pages,
@@ -368,8 +371,13 @@ attn_decode_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k_pages,
     unsigned long long t_end;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_end));
     int* meta = reinterpret_cast<int*>(scratch);
-    meta[600 + 2 * blockIdx.x] = (int)(t_start & 0x7fffffff);
-    meta[601 + 2 * blockIdx.x] = (int)(t_end & 0x7fffffff);
+    unsigned smid;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    const int slot = B2_ATTN_TRACE_BY_SMID ? (int)smid : (int)blockIdx.x;
+    if (slot < 148) {
+      meta[600 + 2 * slot] = (int)(t_start & 0x7fffffff);
+      meta[601 + 2 * slot] = (int)(t_end & 0x7fffffff);
+    }
   }
 }
 

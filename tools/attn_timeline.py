@@ -43,12 +43,12 @@ live = st > 0
 st, en = st[live], en[live]
 t0 = st.min()
 dur = en - st
-print("cfg", os.environ.get("B2_ATTN_CFG", "8x3"), "mode", mode, "B", B, "S", S, "event us (last 5): %s" % ["%.1f" % t for t in times[-5:]], "MB %.1f" % (B * S * 4096 / 1e6))
+print("cfg", os.environ.get("B2_ATTN_CFG", "8x2"), "mode", mode, "B", B, "S", S, "event us (last 5): %s" % ["%.1f" % t for t in times[-5:]], "MB %.1f" % (B * S * 4096 / 1e6))
 print("start skew us: max %.2f" % ((st.max() - t0) / 1e3), " end: min %.2f median %.2f max %.2f us" % ((en.min() - t0) / 1e3, np.median(en - t0) / 1e3, (en.max() - t0) / 1e3))
 print("per-CTA duration us: min %.2f p10 %.2f median %.2f p90 %.2f max %.2f" % tuple(np.percentile(dur, [0, 10, 50, 90, 100]) / 1e3))
 print("ideal at 6539.5 GB/s: %.2f us" % (B * S * 4096 / 6539.5e9 * 1e6))
 if os.environ.get("DUMP"):
     allst = meta[600:600 + 2 * 148:2].astype(np.int64); allen = meta[601:601 + 2 * 148:2].astype(np.int64)
     d = (allen - allst) / 1e3
-    print("per-CTA us by blockIdx:", " ".join("%.1f" % x for x in d))
+    print("per-CTA us by SM id (pairs share a TPC):", " ".join("%.1f" % x for x in d))
     print("start offsets us:", " ".join("%.1f" % ((x - allst[allst > 0].min()) / 1e3) for x in allst))
