@@ -435,6 +435,10 @@ int launch_attn_decode(const bf16* q, const bf16* k_pages, const bf16* v_pages, 
     AD_CASE(4, 6);
     AD_CASE(8, 2);
     AD_CASE(16, 1);
+    AD_CASE(8, 1);
+    AD_CASE(6, 2);
+    AD_CASE(12, 1);
+    AD_CASE(10, 1);
   }
 #undef AD_CASE
   b2_set_error("attn_decode: B2_ATTN_CFG shape %d not built", cfg);
