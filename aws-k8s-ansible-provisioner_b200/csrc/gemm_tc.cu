@@ -427,6 +427,10 @@ int tc_pick_nsplit(int T, int N, int K, int num_sms) {
   if (ns < 1) ns = 1;
   if (ns > kb_total) ns = kb_total;
   if (ns > 32) ns = 32;
+  // At most 8 splits: past that the consumer kernel's partial-sum loads cost more than the extra streaming CTAs
+  // gain (C2 decode on B200, ms/step: cap 32 1.929, 12 1.881, 8 1.877, 6 1.910, 4 1.933, 2 2.077).  B2_SPLIT_MAX overrides.
+  static const int cap = [] { const char* e = getenv("B2_SPLIT_MAX"); return e ? atoi(e) : 8; }();
+  if (ns > cap && cap >= 1) ns = cap;
   const int kps = (kb_total + ns - 1) / ns;
   return (kb_total + kps - 1) / kps;  // every split non-empty
 }
