@@ -82,18 +82,18 @@ __global__ void add_rmsnorm_kernel(bf16* __restrict__ h, const void* __restrict_
 #pragma unroll
     for (int e = 0; e < 8; ++e) d[e] = 0.f;
     const float* p = reinterpret_cast<const float*>(delta) + (size_t)t * H + (size_t)i * 8;
-    // all loads of a group of 4 splits are issued before any add (the adds stay in split order)
-    for (int s0 = 0; s0 < nsplit; s0 += 4) {
-      float4 a[4], b[4];
+    // all loads of a group of 8 splits (the split-K cap) are issued before any add (the adds stay in split order)
+    for (int s0 = 0; s0 < nsplit; s0 += 8) {
+      float4 a[8], b[8];
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
+      for (int j = 0; j < 8; ++j) {
         if (s0 + j < nsplit) {
           a[j] = reinterpret_cast<const float4*>(p + (size_t)(s0 + j) * split_stride)[0];
           b[j] = reinterpret_cast<const float4*>(p + (size_t)(s0 + j) * split_stride)[1];
         }
       }
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
+      for (int j = 0; j < 8; ++j) {
         if (s0 + j < nsplit) {
           d[0] += a[j].x; d[1] += a[j].y; d[2] += a[j].z; d[3] += a[j].w;
           d[4] += b[j].x; d[5] += b[j].y; d[6] += b[j].z; d[7] += b[j].w;
@@ -206,9 +206,16 @@ __global__ void qknorm_rope_kv_kernel(const void* __restrict__ qkv, int nsplit, 
   if (F32IN) {
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
     const float* p = reinterpret_cast<const float*>(qkv) + row;
-    for (int s = 0; s < nsplit; ++s) {
-      float4 a = *reinterpret_cast<const float4*>(p + s * split_stride);
-      acc.x += a.x; acc.y += a.y; acc.z += a.z; acc.w += a.w;
+    // all loads of a group of 4 splits go out before any add (the adds stay in split order): one L2 round trip
+    // per group instead of one per split
+    for (int s0 = 0; s0 < nsplit; s0 += 4) {
+      float4 a[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (s0 + j < nsplit) a[j] = *reinterpret_cast<const float4*>(p + (size_t)(s0 + j) * split_stride);
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (s0 + j < nsplit) { acc.x += a[j].x; acc.y += a[j].y; acc.z += a[j].z; acc.w += a[j].w; }
     }
     acc.x += bq[0]; acc.y += bq[1]; acc.z += bq[2]; acc.w += bq[3];  // zeros unless the projection has a bias
     v[0] = bf16_round(acc.x); v[1] = bf16_round(acc.y); v[2] = bf16_round(acc.z); v[3] = bf16_round(acc.w);
@@ -294,13 +301,22 @@ __global__ void silu_mul_kernel(const void* __restrict__ gu, int nsplit, size_t 
     for (int e = 0; e < 8; ++e) g[e] = u[e] = 0.f;
     const float* pg = reinterpret_cast<const float*>(gu) + (size_t)t * 2 * I + i;
     const float* pu = pg + I;
-    for (int s = 0; s < nsplit; ++s) {
-      float4 a = reinterpret_cast<const float4*>(pg + s * split_stride)[0];
-      float4 b = reinterpret_cast<const float4*>(pg + s * split_stride)[1];
-      float4 c = reinterpret_cast<const float4*>(pu + s * split_stride)[0];
-      float4 d = reinterpret_cast<const float4*>(pu + s * split_stride)[1];
-      g[0] += a.x; g[1] += a.y; g[2] += a.z; g[3] += a.w; g[4] += b.x; g[5] += b.y; g[6] += b.z; g[7] += b.w;
-      u[0] += c.x; u[1] += c.y; u[2] += c.z; u[3] += c.w; u[4] += d.x; u[5] += d.y; u[6] += d.z; u[7] += d.w;
+    for (int s0 = 0; s0 < nsplit; s0 += 4) {  // loads of up to 4 splits in flight together, adds in split order
+      float4 a[4], b[4], c[4], d[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (s0 + j < nsplit) {
+          a[j] = reinterpret_cast<const float4*>(pg + (size_t)(s0 + j) * split_stride)[0];
+          b[j] = reinterpret_cast<const float4*>(pg + (size_t)(s0 + j) * split_stride)[1];
+          c[j] = reinterpret_cast<const float4*>(pu + (size_t)(s0 + j) * split_stride)[0];
+          d[j] = reinterpret_cast<const float4*>(pu + (size_t)(s0 + j) * split_stride)[1];
+        }
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (s0 + j < nsplit) {
+          g[0] += a[j].x; g[1] += a[j].y; g[2] += a[j].z; g[3] += a[j].w; g[4] += b[j].x; g[5] += b[j].y; g[6] += b[j].z; g[7] += b[j].w;
+          u[0] += c[j].x; u[1] += c[j].y; u[2] += c[j].z; u[3] += c[j].w; u[4] += d[j].x; u[5] += d[j].y; u[6] += d[j].z; u[7] += d[j].w;
+        }
     }
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
