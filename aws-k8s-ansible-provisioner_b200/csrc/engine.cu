@@ -180,6 +180,9 @@ struct b2_engine {
   float* d_ss = nullptr;                  // fused chain: 2 x [32][64] sums of squares
   unsigned long long* d_gbar2 = nullptr;  // fused chain: its grid-barrier counter
   bool fused_ok = false;                  // shapes + cluster occupancy allow the fused chain
+  int o_small_smem = 0;                   // B2_O_SMALL=1: O projection with a short stage ring so that it is resident beside
+                                          // attention's CTAs (measured slower: 1.869 vs 1.832 ms/step at C2 -- its weight
+                                          // prefetch competes with the tail of the K/V stream)
   int use_chain = 0;              // B2_CHAIN=1: decode through the persistent chain kernel (chain.cu; measured slower, kept for A/B runs)  // B2_SKIP_MASK: kernel classes left out (timing ablations only; results are garbage)
 };
 
@@ -246,7 +249,7 @@ int pick_attn_split(b2_engine* e, int B, int max_len) {
 
 // ---- one Linear layer: picks SIMT GEMV or the tcgen05 kernel, bf16 or split-K partial output
 ActIn linear(b2_engine* e, int cls, XBuf xb, const bf16* xptr, const bf16* w, const CUtensorMap& tm_w, bf16* out_bf16, int T,
-             int N, int K, int* rc, const KvPrefetch& pf = KvPrefetch(), bool want_f32 = false) {
+             int N, int K, int* rc, const KvPrefetch& pf = KvPrefetch(), bool want_f32 = false, bool after_attention = false) {
   // want_f32: hand the consumer fp32 sums even when K is not split (a bias is added before the rounding)
   *rc = 0;
   int impl = e->force_gemm_impl >= 0 ? e->force_gemm_impl : (T <= e->simt_max_tokens ? 0 : 1);
@@ -271,6 +274,7 @@ ActIn linear(b2_engine* e, int cls, XBuf xb, const bf16* xptr, const bf16* w, co
   a.T = T; a.N = N; a.K = K;
   a.argmax_packed = nullptr;
   a.prefetch = pf;
+  a.small_smem = (after_attention && e->o_small_smem) ? 1 : 0;
   int ns = tc_pick_nsplit(T, N, K, e->num_sms);
   while (ns > 1 && (size_t)ns * T * N > e->partial_floats) --ns;
   if (ns > 1) {  // re-validate (every split non-empty)
@@ -571,7 +575,8 @@ int forward(b2_engine* e, int T, int ntiles, int nlast, int attn_split) {
         B2_TRY(launch_attn_decode(e->qrot, kp, vp, e->d_block_table, e->bt_stride, e->d_seq_lens, e->attn_scratch, e->attn, T,
                                   e->nq, e->nkv, e->hd, c.block_size, e->stream, e->attn_scale));
     }
-    ActIn o = linear(e, B2K_GEMM_O, XB_ATTN, e->attn, L.wo, L.tm_o, e->proj, T, H, e->q_size, &rc, prefetch_for(l + 1, 0));
+    ActIn o = linear(e, B2K_GEMM_O, XB_ATTN, e->attn, L.wo, L.tm_o, e->proj, T, H, e->q_size, &rc, prefetch_for(l + 1, 0), false,
+                     /*after_attention=*/ntiles == 0);
     B2_TRY(rc);
     {
       KL k(e, B2K_NORM);
@@ -1064,6 +1069,7 @@ extern "C" int b2_engine_create(const b2_config* cfg, const char* safetensors_pa
   // 0 separate kernels (default: fastest measured), 1 eight-step chain kernel (chain.cu), 2 fused four-step cluster
   // chain (chain_cluster.cu); 1 and 2 are kept as measured experiments with parity tests
   e->use_chain = env_int("B2_CHAIN", 0);
+  e->o_small_smem = env_int("B2_O_SMALL", 0);
   // Off by default: measured on B200 at C2 (ms/step) 0 MB 2.22, 40 MB 2.24, 72 MB 2.33, 100 MB 2.38 --
   // un-paced prefetch bursts queue ahead of the projections' own latency-critical weight loads.
   e->kv_l2_budget = (long long)env_int("B2_KV_L2_MB", 0) << 20;

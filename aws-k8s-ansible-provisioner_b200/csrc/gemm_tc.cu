@@ -39,11 +39,14 @@ constexpr int TC_BM = 128;
 constexpr int TC_BK = 64;
 constexpr int TC_W_BYTES = TC_BM * TC_BK * 2;  // 16 KB per stage
 
-template <int BN>
+// SMALL: a ring short enough (<= 96 KB) for the CTA to be resident on an SM BESIDE a decode-attention CTA (128 KB +
+// the 1 KB the system reserves per CTA, of 228 KB), so the O projection -- the kernel that follows attention --
+// can start and prefetch its weight tiles while attention's tail is still streaming.
+template <int BN, int SMALL = 0>
 struct TcCfg {
   static constexpr int X_BYTES = BN * TC_BK * 2;
   static constexpr int STAGE_BYTES = TC_W_BYTES + X_BYTES;
-  static constexpr int STAGES = (BN <= 64) ? 8 : (BN == 128 ? 6 : 4);
+  static constexpr int STAGES = SMALL ? (BN <= 32 ? 4 : 3) : ((BN <= 64) ? 8 : (BN == 128 ? 6 : 4));
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024;
   static constexpr int TMEM_COLS = 2 * BN < 32 ? 32 : 2 * BN;  // two accumulator stages
 };
@@ -57,12 +60,12 @@ __device__ __forceinline__ unsigned long long tc_argmax_pack(float v, int idx) {
 // Persistent: gridDim.x CTAs walk the (m tile, token tile, k split) work list with stride
 // gridDim.x.  The smem stage ring runs on across tiles, and the accumulator is double buffered
 // in TMEM so the epilogue of tile i overlaps the TMA/MMA main loop of tile i+1.
-template <int BN, int EPI>
+template <int BN, int EPI, int SMALL = 0>
 __global__ void __launch_bounds__(192, 1)
 linear_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_x,
                  void* __restrict__ out, unsigned long long* __restrict__ argmax_packed, int T, int N, int K,
                  int kb_per_split, int m_tiles, int n_tiles, int nsplit, const KvPrefetch pf) {
-  using C = TcCfg<BN>;
+  using C = TcCfg<BN, SMALL>;
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t full_bar[C::STAGES];
   __shared__ __align__(8) uint64_t empty_bar[C::STAGES];
@@ -435,11 +438,12 @@ int tc_pick_nsplit(int T, int N, int K, int num_sms) {
   return (kb_total + kps - 1) / kps;  // every split non-empty
 }
 
-template <int BN, int EPI>
+template <int BN, int EPI, int SMALL = 0>
 static int launch_one(const TcGemmArgs& a, int kb_per_split, cudaStream_t s) {
-  using C = TcCfg<BN>;
+  using C = TcCfg<BN, SMALL>;
   static B2PerDeviceOnce attr_once;
-  if (attr_once.need()) B2_CUDA_OK(cudaFuncSetAttribute(linear_tc_kernel<BN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
+  if (attr_once.need())
+    B2_CUDA_OK(cudaFuncSetAttribute(linear_tc_kernel<BN, EPI, SMALL>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
   // TC_EPI_ARGMAX_ROWS: tokens are the 128-row M tiles and weight rows the BN-wide N tiles
   const bool rows_mode = (EPI == TC_EPI_ARGMAX_ROWS);
   const int m_tiles = rows_mode ? (a.T + TC_BM - 1) / TC_BM : (a.N + TC_BM - 1) / TC_BM;
@@ -447,7 +451,7 @@ static int launch_one(const TcGemmArgs& a, int kb_per_split, cudaStream_t s) {
   const int total = m_tiles * n_tiles * a.nsplit;
   static int sms = device_num_sms();
   const int grid = total < sms ? total : sms;
-  B2_CUDA_OK(b2_launch(linear_tc_kernel<BN, EPI>, dim3(grid), dim3(192), (size_t)C::SMEM_BYTES, s, a.tmap_w, a.tmap_x, a.out,
+  B2_CUDA_OK(b2_launch(linear_tc_kernel<BN, EPI, SMALL>, dim3(grid), dim3(192), (size_t)C::SMEM_BYTES, s, a.tmap_w, a.tmap_x, a.out,
                        a.argmax_packed, a.T, a.N, a.K, kb_per_split, m_tiles, n_tiles, a.nsplit, a.prefetch));
   return 0;
 }
@@ -456,7 +460,9 @@ template <int BN>
 static int launch_bn(const TcGemmArgs& a, int kps, cudaStream_t s) {
   switch (a.epilogue) {
     case TC_EPI_BF16: return launch_one<BN, TC_EPI_BF16>(a, kps, s);
-    case TC_EPI_F32_PARTIAL: return launch_one<BN, TC_EPI_F32_PARTIAL>(a, kps, s);
+    case TC_EPI_F32_PARTIAL:
+      if (BN <= 64 && a.small_smem) return launch_one<(BN <= 64 ? BN : 64), TC_EPI_F32_PARTIAL, 1>(a, kps, s);
+      return launch_one<BN, TC_EPI_F32_PARTIAL>(a, kps, s);
     case TC_EPI_ARGMAX: return launch_one<BN, TC_EPI_ARGMAX>(a, kps, s);
     case TC_EPI_ARGMAX_ROWS: return launch_one<BN, TC_EPI_ARGMAX_ROWS>(a, kps, s);
   }

@@ -73,6 +73,7 @@ struct TcGemmArgs {
   void* out;           // bf16 [T][N] | fp32 [nsplit][T][N] | bf16 logits (may be null) for ARGMAX
   unsigned long long* argmax_packed;  // [T] for TC_EPI_ARGMAX (must be zeroed before launch)
   KvPrefetch prefetch;                // optional ride-along K/V prefetch
+  int small_smem = 0;                 // F32_PARTIAL, bn <= 64: short stage ring so the CTA fits beside a decode-attention CTA
 };
 int launch_linear_tc(const TcGemmArgs& a, cudaStream_t s);
 int tc_pick_bn(int T);
