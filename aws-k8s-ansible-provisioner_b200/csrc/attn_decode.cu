@@ -191,50 +191,87 @@ attn_decode_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k_pages,
   float m_run[2], l_run[2];
   bool fresh = true;  // (re)load q and reset the running state at the next tile
 
-  // Arrival + merge of one unit, deferred to the end of the warp's run so that the fence and the
-  // atomic round trip never stall the TMA pipeline mid-stream.
-  auto arrive_and_maybe_merge = [&](int unit) {
-    float* recs = scratch + AD_META;
-    // which warps' runs touch this unit (inverse of the partition above)
-    const int ub = unit / nkv, ukvh = unit - ub * nkv;
+  // Arrival + merge of the units this warp's run touched, deferred to the end of the run so that the fence and
+  // the atomic round trips never stall the TMA pipeline mid-stream -- and done for ALL pending units together:
+  // one fence, the arrivals of up to 8 units issued by different lanes at once, and in a merge the loads of up
+  // to four records in flight before the first is used (a serial version cost ~1 us per unit at the very end
+  // of the slowest warps, i.e. of the kernel).
+  auto unit_span = [&](int unit, int& ub, int& ukvh, int& w0, int& w1) {  // which warps' runs touch this unit
+    ub = unit / nkv;
+    ukvh = unit - ub * nkv;
     const int unb = s_prefix[ub + 1] - s_prefix[ub];
     const int u0 = s_prefix[ub] * nkv + ukvh * unb;
     const int cut = rem * (base + 1);
-    const int w0 = u0 < cut ? u0 / (base + 1) : rem + (u0 - cut) / base;
+    w0 = u0 < cut ? u0 / (base + 1) : rem + (u0 - cut) / base;
     const int ulast = u0 + unb - 1;
-    const int w1 = ulast < cut ? ulast / (base + 1) : rem + (ulast - cut) / base;
-    int* cnt = reinterpret_cast<int*>(scratch) + 1024 + unit;
-    __threadfence();  // this warp's record is visible before its arrival is
+    w1 = ulast < cut ? ulast / (base + 1) : rem + (ulast - cut) / base;
+  };
+  auto merge_unit = [&](int unit) {  // last to arrive: merge in run order and write the output
+    float* recs = scratch + AD_META;
+    int ub, ukvh, w0, w1;
+    unit_span(unit, ub, ukvh, w0, w1);
+    const int hh = lane >> 4, d0 = (lane & 15) * 8;  // lane covers 8 of the 256 (head, dim) outputs
+    float M = -INFINITY;
+    for (int wb = w0; wb <= w1; wb += 4) {
+      float mv[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (wb + j <= w1) mv[j] = __ldcg(recs + (size_t)(unit + wb + j) * AD_REC + 2 * AD_HD + hh);
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (wb + j <= w1) M = fmaxf(M, mv[j]);
+    }
+    float O[8], L = 0.f;
+#pragma unroll
+    for (int e = 0; e < 8; ++e) O[e] = 0.f;
+    for (int wb = w0; wb <= w1; wb += 4) {
+      float mv[4], lv[4];
+      float4 a[4], b[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (wb + j <= w1) {
+          const float* r2 = recs + (size_t)(unit + wb + j) * AD_REC;
+          mv[j] = __ldcg(r2 + 2 * AD_HD + hh);
+          lv[j] = __ldcg(r2 + 2 * AD_HD + 2 + hh);
+          a[j] = __ldcg(reinterpret_cast<const float4*>(r2 + hh * AD_HD + d0));
+          b[j] = __ldcg(reinterpret_cast<const float4*>(r2 + hh * AD_HD + d0 + 4));
+        }
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (wb + j <= w1) {  // run order: the sums do not depend on which warp does the merge
+          const float f = expf(mv[j] - M);
+          O[0] = fmaf(f, a[j].x, O[0]); O[1] = fmaf(f, a[j].y, O[1]); O[2] = fmaf(f, a[j].z, O[2]); O[3] = fmaf(f, a[j].w, O[3]);
+          O[4] = fmaf(f, b[j].x, O[4]); O[5] = fmaf(f, b[j].y, O[5]); O[6] = fmaf(f, b[j].z, O[6]); O[7] = fmaf(f, b[j].w, O[7]);
+          L = fmaf(f, lv[j], L);
+        }
+    }
+    const float inv = L > 0.f ? __fdiv_rn(1.0f, L) : 0.f;
+#pragma unroll
+    for (int e = 0; e < 8; ++e) O[e] *= inv;
+    *reinterpret_cast<uint4*>(out + ((size_t)ub * nq + ukvh * 2 + hh) * AD_HD + d0) = pack8(O);
+  };
+  auto arrive_all = [&](const int* units, int n) {
+    if (n <= 0) return;
+    __threadfence();  // this warp's records are visible before its arrivals are
     __syncwarp();
-    int prev = 0;
-    if (lane == 0) prev = atomicAdd(cnt, 1);
-    prev = __shfl_sync(0xffffffffu, prev, 0);
-    if (prev == w1 - w0) {  // last to arrive: merge in run order and write the output
-      __threadfence();
-      if (lane == 0) *cnt = 0;  // ready for the next launch
-      float M[2] = {-INFINITY, -INFINITY};
-      for (int w = w0; w <= w1; ++w) {
-        const float* r2 = recs + (size_t)(unit + w) * AD_REC + 2 * AD_HD;
-        M[0] = fmaxf(M[0], __ldcg(r2 + 0));
-        M[1] = fmaxf(M[1], __ldcg(r2 + 1));
+    int my_unit = lane < n ? units[lane] : -1;
+    bool last = false;
+    if (my_unit >= 0) {
+      int ub, ukvh, w0, w1;
+      unit_span(my_unit, ub, ukvh, w0, w1);
+      int* cnt = reinterpret_cast<int*>(scratch) + 1024 + my_unit;
+      const int prev = atomicAdd(cnt, 1);
+      if (prev == w1 - w0) {
+        last = true;
+        *cnt = 0;  // ready for the next launch
       }
-      float O[8], L[2] = {0.f, 0.f};  // lane covers 8 of the 256 (head, dim) outputs: head = lane / 16
-#pragma unroll
-      for (int e = 0; e < 8; ++e) O[e] = 0.f;
-      const int hh = lane >> 4, d0 = (lane & 15) * 8;
-      for (int w = w0; w <= w1; ++w) {
-        const float* r2 = recs + (size_t)(unit + w) * AD_REC;
-        const float f = expf(__ldcg(r2 + 2 * AD_HD + hh) - M[hh]);
-        const float4 a = __ldcg(reinterpret_cast<const float4*>(r2 + hh * AD_HD + d0));
-        const float4 b = __ldcg(reinterpret_cast<const float4*>(r2 + hh * AD_HD + d0 + 4));
-        O[0] = fmaf(f, a.x, O[0]); O[1] = fmaf(f, a.y, O[1]); O[2] = fmaf(f, a.z, O[2]); O[3] = fmaf(f, a.w, O[3]);
-        O[4] = fmaf(f, b.x, O[4]); O[5] = fmaf(f, b.y, O[5]); O[6] = fmaf(f, b.z, O[6]); O[7] = fmaf(f, b.w, O[7]);
-        L[hh] = fmaf(f, __ldcg(r2 + 2 * AD_HD + 2 + hh), L[hh]);
-      }
-      const float inv = L[hh] > 0.f ? __fdiv_rn(1.0f, L[hh]) : 0.f;
-#pragma unroll
-      for (int e = 0; e < 8; ++e) O[e] *= inv;
-      *reinterpret_cast<uint4*>(out + ((size_t)ub * nq + ukvh * 2 + hh) * AD_HD + d0) = pack8(O);
+    }
+    unsigned todo = __ballot_sync(0xffffffffu, last);
+    if (todo) __threadfence();  // acquire side: the other warps' records
+    while (todo) {
+      const int src = __ffs(todo) - 1;
+      todo &= todo - 1;
+      merge_unit(__shfl_sync(0xffffffffu, my_unit, src));
     }
   };
   int pending[8];
@@ -361,12 +398,15 @@ attn_decode_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k_pages,
         rec[2 * AD_HD + 2] = l_run[0];
         rec[2 * AD_HD + 3] = l_run[1];
       }
-      if (npending < 8) pending[npending++] = unit;
-      else arrive_and_maybe_merge(unit);  // (never in practice: > 8 unit ends in one run)
+      if (npending == 8) {  // (never in practice: more than 8 unit ends in one run)
+        arrive_all(pending, npending);
+        npending = 0;
+      }
+      pending[npending++] = unit;
       fresh = true;
     }
   }
-  for (int i = 0; i < npending; ++i) arrive_and_maybe_merge(pending[i]);
+  arrive_all(pending, npending);
   if (dbg_time) {  // timing breadcrumbs for tools/attn_timeline.py (unused words of the geometry header)
     unsigned long long t_end;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_end));
