@@ -37,6 +37,10 @@ for it in range(8):
     torch.cuda.synchronize()
     assert rc == 0
     times.append(e0.elapsed_time(e1) * 1e3)
+    if os.environ.get("PER_SM"):
+        m = scratch.view(torch.int32)[:1024].cpu().numpy()
+        d = (m[601:601 + 2 * 148:2].astype(np.int64) - m[600:600 + 2 * 148:2].astype(np.int64)) / 1e3
+        per_sm = d[None, :] if it == 0 else np.concatenate([per_sm, d[None, :]], axis=0)
 meta = scratch.view(torch.int32)[:1024].cpu().numpy()
 st, en = meta[600:600 + 2 * 148:2].astype(np.int64), meta[601:601 + 2 * 148:2].astype(np.int64)
 live = st > 0
@@ -52,3 +56,12 @@ if os.environ.get("DUMP"):
     d = (allen - allst) / 1e3
     print("per-CTA us by SM id (pairs share a TPC):", " ".join("%.1f" % x for x in d))
     print("start offsets us:", " ".join("%.1f" % ((x - allst[allst > 0].min()) / 1e3) for x in allst))
+
+if os.environ.get("PER_SM"):
+    mean, sd = per_sm[2:].mean(axis=0), per_sm[2:].std(axis=0)
+    order = np.argsort(-mean)
+    print("per-SM mean busy time over %d launches: overall mean %.2f; between-SM std %.2f; mean within-SM std %.2f" % (
+        per_sm.shape[0] - 2, mean.mean(), mean.std(), sd.mean()))
+    print("slowest SMs (id: mean+-sd):", " ".join("%d:%.1f+-%.1f" % (i, mean[i], sd[i]) for i in order[:16]))
+    print("fastest SMs:", " ".join("%d:%.1f+-%.1f" % (i, mean[i], sd[i]) for i in order[-10:]))
+    print("by id:", " ".join("%.1f" % x for x in mean))
