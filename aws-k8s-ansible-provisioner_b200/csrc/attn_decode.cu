@@ -427,9 +427,10 @@ size_t attn_decode_scratch_floats(int B, int nq, int nkv, int hd) {
   return (size_t)AD_META + ((size_t)B * nkv + (size_t)AD_MAX_CTAS * AD_WARPS_MAX) * AD_REC;
 }
 
-// (warps per CTA, pipeline stages per warp).  Default 8 x 2 x 8 KB = 128 KB of K/V in flight per SM:
-// measured equal to 8 x 3 (192 KB) on B200, and it leaves room for the decode chain kernel's CTA (96 KB)
-// to be resident on the same SM, so each kernel's prologue overlaps the other's tail.
+// (warps per CTA, pipeline stages per warp).  Default 8 x 2 x 8 KB = 128 KB of K/V in flight per SM.  Measured on
+// B200 at the bench shape (median / slowest CTA busy time, us): 8x2 28.5/36, 8x3 28.6/36, 16x1 28.1/35, 12x1 28.1/35,
+// 10x1 28.5/35, 6x2 30.2/35, 8x1 30.1/37 -- nothing below 96 KB in flight keeps up, nothing above 128 KB helps, and
+// the spread between the SMs of one launch is the same for all of them.
 // B2_ATTN_CFG=<warps>x<stages> selects another built shape for experiments.
 static int ad_grid() {
   static int sms = device_num_sms();
