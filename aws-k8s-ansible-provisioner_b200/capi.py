@@ -21,7 +21,7 @@ class b2_config(C.Structure):
         ("tie_embeddings", C.c_int32), ("rms_eps", C.c_float), ("rope_theta", C.c_float), ("max_model_len", C.c_int32),
         ("block_size", C.c_int32), ("num_blocks", C.c_int32), ("gpu_mem_fraction", C.c_float), ("max_seqs", C.c_int32),
         ("max_batch_tokens", C.c_int32), ("use_cuda_graphs", C.c_int32), ("rope_inv_freq", C.POINTER(C.c_float)),
-        ("arch", C.c_int32), ("rotary_dim", C.c_int32), ("max_positions", C.c_int32),
+        ("arch", C.c_int32), ("rotary_dim", C.c_int32), ("max_positions", C.c_int32), ("sliding_window", C.c_int32),
     ]
 
 

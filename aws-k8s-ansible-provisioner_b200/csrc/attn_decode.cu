@@ -67,8 +67,15 @@ template <int AD_WARPS, int AD_STAGES>
 __global__ void __launch_bounds__(AD_WARPS * 32, 1)
 attn_decode_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k_pages, const bf16* __restrict__ v_pages,
                    const int32_t* __restrict__ block_table, int bt_stride, const int32_t* __restrict__ seq_lens,
-                   float* __restrict__ scratch, bf16* __restrict__ out, int B, int nq, int nkv, float scale, int early) {
+                   float* __restrict__ scratch, bf16* __restrict__ out, int B, int nq, int nkv, float scale, int early,
+                   int window) {
   extern __shared__ __align__(128) uint8_t smem[];
+  // Sliding-window attention (Phi-3, HF:models/phi3/modeling_phi3.py:265 sliding_window): a query at position
+  // S-1 sees the last `window` keys only, i.e. tokens lo(S) = max(0, S - window) .. S-1.  Whole pages below lo are
+  // never enumerated (first_page), the partly covered one is masked.  window == 0: everything is visible.
+  auto lo_of = [&](int S) { return (window > 0 && S > window) ? S - window : 0; };
+  auto first_page_of = [&](int S) { return lo_of(S) / AD_BS; };
+  auto pages_of = [&](int S) { return (S + AD_BS - 1) / AD_BS - first_page_of(S); };
   __shared__ __align__(8) uint64_t bars[AD_WARPS][AD_STAGES];
   __shared__ int s_prefix[AD_MAX_B + 1];  // pages of sequences before b (exclusive prefix)
 
@@ -88,7 +95,7 @@ attn_decode_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k_pages,
     int local = 0;
     for (int i = 0; i < per; ++i) {
       const int b = lane * per + i;
-      if (b < B) local += (seq_lens[b] + AD_BS - 1) / AD_BS;
+      if (b < B) local += pages_of(seq_lens[b]);
     }
     int incl = local;
 #pragma unroll
@@ -101,7 +108,7 @@ attn_decode_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k_pages,
       const int b = lane * per + i;
       if (b < B) {
         s_prefix[b] = run;
-        run += (seq_lens[b] + AD_BS - 1) / AD_BS;
+        run += pages_of(seq_lens[b]);
       }
     }
     if (lane == 31) s_prefix[B] = incl;
@@ -143,7 +150,7 @@ attn_decode_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k_pages,
       cached_slice = 0;
       if (nn < ntiles) {
         const AdPos r = locate(p0 + nn);
-        cached_slice = block_table[(size_t)r.b * bt_stride + r.j] * nkv + r.kvh;
+        cached_slice = block_table[(size_t)r.b * bt_stride + r.j + first_page_of(seq_lens[r.b])] * nkv + r.kvh;
         if (r.j == r.nb - 1) cached_slice |= AD_LAST_PAGE;  // holds the slot the previous kernel is writing
       }
       cached_group = g;
@@ -186,6 +193,7 @@ attn_decode_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k_pages,
   const int g = lane >> 2, t4 = lane & 3;
   AdPos cur = locate(p0);
   int S = seq_lens[cur.b];
+  int lo = lo_of(S), fp = first_page_of(S);  // first visible token / first enumerated page of the current sequence
   uint32_t qb0[8], qb1[8];
   float oacc[8][4];
   float m_run[2], l_run[2];
@@ -313,8 +321,8 @@ attn_decode_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k_pages,
     s[0][1] = __shfl_sync(0xffffffffu, sacc[1], lane & ~3);
     s[1][0] = __shfl_sync(0xffffffffu, sacc[2], lane & ~3);
     s[1][1] = __shfl_sync(0xffffffffu, sacc[3], lane & ~3);
-    const int tok = cur.j * AD_BS + g;
-    const bool ok_a = tok < S, ok_b = tok + 8 < S;
+    const int tok = (cur.j + fp) * AD_BS + g;
+    const bool ok_a = tok < S && tok >= lo, ok_b = tok + 8 < S && tok + 8 >= lo;
     float p[2][2], corr[2];
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
@@ -377,6 +385,8 @@ attn_decode_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k_pages,
         if (cur.b < B) {
           cur.nb = s_prefix[cur.b + 1] - s_prefix[cur.b];
           S = seq_lens[cur.b];
+          lo = lo_of(S);
+          fp = first_page_of(S);
         }
       }
     }
@@ -439,12 +449,13 @@ static int ad_grid() {
 
 template <int W, int S>
 static int launch_cfg(const bf16* q, const bf16* k_pages, const bf16* v_pages, const int32_t* block_table, int bt_stride,
-                      const int32_t* seq_lens, float* scratch, bf16* out, int B, int nq, int nkv, float scale, cudaStream_t s) {
+                      const int32_t* seq_lens, float* scratch, bf16* out, int B, int nq, int nkv, float scale, int window,
+                      cudaStream_t s) {
   constexpr int SMEM = W * S * AD_STAGE;
   static B2PerDeviceOnce attr_once;
   if (attr_once.need()) B2_CUDA_OK(cudaFuncSetAttribute(attn_decode_kernel<W, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
   B2_CUDA_OK(b2_launch(attn_decode_kernel<W, S>, dim3(ad_grid()), dim3(W * 32), (size_t)SMEM, s, q, k_pages, v_pages, block_table,
-                       bt_stride, seq_lens, scratch, out, B, nq, nkv, scale, b2_pdl_early_mask() & 1));
+                       bt_stride, seq_lens, scratch, out, B, nq, nkv, scale, b2_pdl_early_mask() & 1, window));
   return 0;
 }
 
@@ -452,8 +463,9 @@ static int launch_cfg(const bf16* q, const bf16* k_pages, const bf16* v_pages, c
 // must be zero when the kernel starts -- the kernel leaves them zero again when it is done.
 int launch_attn_decode(const bf16* q, const bf16* k_pages, const bf16* v_pages, const int32_t* block_table,
                        int bt_stride, const int32_t* seq_lens, float* scratch, bf16* out, int B, int nq, int nkv,
-                       int hd, int block_size, cudaStream_t s, float softmax_scale) {
+                       int hd, int block_size, cudaStream_t s, float softmax_scale, int window) {
   if (B <= 0) return 0;
+  B2_REQUIRE(window >= 0, "attn_decode: negative window");
   B2_REQUIRE(hd == AD_HD && block_size == AD_BS, "attn_decode: built for head_dim 128 / page 16 (got %d / %d)", hd, block_size);
   B2_REQUIRE(nq == 2 * nkv, "attn_decode: built for a GQA group of 2 (nq=%d nkv=%d)", nq, nkv);
   B2_REQUIRE(B <= AD_MAX_B && B * nkv <= AD_CNT, "attn_decode: batch %d x %d kv heads exceeds %d units", B, nkv, AD_CNT);
@@ -466,7 +478,7 @@ int launch_attn_decode(const bf16* q, const bf16* k_pages, const bf16* v_pages, 
     cfg = 82;
     if (e) { int w = 0, st = 0; if (sscanf(e, "%dx%d", &w, &st) == 2) cfg = w * 10 + st; }
   }
-#define AD_CASE(W, S) case (W) * 10 + (S): return launch_cfg<W, S>(q, k_pages, v_pages, block_table, bt_stride, seq_lens, scratch, out, B, nq, nkv, scale, s)
+#define AD_CASE(W, S) case (W) * 10 + (S): return launch_cfg<W, S>(q, k_pages, v_pages, block_table, bt_stride, seq_lens, scratch, out, B, nq, nkv, scale, window, s)
   switch (cfg) {
     AD_CASE(8, 3);
     AD_CASE(6, 4);

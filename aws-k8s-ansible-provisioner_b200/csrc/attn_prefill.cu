@@ -46,7 +46,7 @@ __device__ __forceinline__ void mma_bf16(float* d, const uint32_t* a, uint32_t b
 __global__ void __launch_bounds__(128)
 attn_prefill_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k_pages, const bf16* __restrict__ v_pages,
                     const int32_t* __restrict__ block_table, int bt_stride, const PrefillTile* __restrict__ tiles,
-                    bf16* __restrict__ out, int nq, int nkv, int block_size, float scale_log2) {
+                    bf16* __restrict__ out, int nq, int nkv, int block_size, float scale_log2, int window) {
   extern __shared__ __align__(128) uint8_t smem[];
   pdl_wait();
   pdl_launch_dependents();
@@ -56,6 +56,9 @@ attn_prefill_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k_pages
   const int g = lane >> 2, t4 = lane & 3;
   const int kv_len = tile.q_pos0 + tile.nrows;  // keys visible to the last row of the tile
   const int n_kv_tiles = (kv_len + AP_BN - 1) / AP_BN;
+  // sliding window (0 = off): a query at position p sees keys p - window + 1 .. p; key tiles wholly below the
+  // window of the tile's FIRST row are skipped, the rest is masked per element
+  const int j0 = (window > 0 && tile.q_pos0 - window + 1 > 0) ? (tile.q_pos0 - window + 1) / AP_BN : 0;
   const int32_t* bt = block_table + (size_t)tile.bt_row * bt_stride;
   const uint32_t smem0 = smem_u32(smem);
 
@@ -82,7 +85,7 @@ attn_prefill_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k_pages
     cp_async_commit();
   };
 
-  load_tile(0, 0);
+  load_tile(j0, 0);
 
   // Q fragments for this warp's 16 rows, straight from global (read once)
   const int row_a = warp * 16 + g, row_b = row_a + 8;
@@ -106,8 +109,8 @@ attn_prefill_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k_pages
   float m_run[2] = {-INFINITY, -INFINITY}, l_run[2] = {0.f, 0.f};
   const int qpos_a = tile.q_pos0 + row_a, qpos_b = tile.q_pos0 + row_b;
 
-  for (int j = 0; j < n_kv_tiles; ++j) {
-    const int buf = j & 1;
+  for (int j = j0; j < n_kv_tiles; ++j) {
+    const int buf = (j - j0) & 1;
     if (j + 1 < n_kv_tiles) {
       load_tile(j + 1, buf ^ 1);
       cp_async_wait<1>();
@@ -143,7 +146,7 @@ attn_prefill_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k_pages
         const int col = j * AP_BN + nt * 8 + 2 * t4 + (e & 1);
         const int qp = (e < 2) ? qpos_a : qpos_b;
         float s = sacc[nt][e] * scale_log2;
-        if (col > qp || col >= kv_len) s = -INFINITY;
+        if (col > qp || col >= kv_len || (window > 0 && qp - col >= window)) s = -INFINITY;
         sacc[nt][e] = s;
         mx[e >> 1] = fmaxf(mx[e >> 1], s);
       }
@@ -219,7 +222,7 @@ attn_prefill_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k_pages
 
 int launch_attn_prefill(const bf16* q, const bf16* k_pages, const bf16* v_pages, const int32_t* block_table,
                         int bt_stride, const PrefillTile* tiles_dev, int ntiles, bf16* out, int nq, int nkv, int hd,
-                        int block_size, cudaStream_t s, float softmax_scale) {
+                        int block_size, cudaStream_t s, float softmax_scale, int window) {
   if (ntiles <= 0) return 0;
   B2_REQUIRE(hd == AP_HD, "attn_prefill: head_dim %d not built (128 only)", hd);
   B2_REQUIRE(nq % nkv == 0, "attn_prefill: nq=%d not a multiple of nkv=%d", nq, nkv);
@@ -229,7 +232,7 @@ int launch_attn_prefill(const bf16* q, const bf16* k_pages, const bf16* v_pages,
   const float scale_log2 = (float)(scale * 1.4426950408889634);
   dim3 grid(ntiles, nq);
   B2_CUDA_OK(b2_launch(attn_prefill_kernel, grid, dim3(128), (size_t)AP_SMEM, s, q, k_pages, v_pages, block_table, bt_stride,
-                       tiles_dev, out, nq, nkv, block_size, scale_log2));
+                       tiles_dev, out, nq, nkv, block_size, scale_log2, window));
   return 0;
 }
 

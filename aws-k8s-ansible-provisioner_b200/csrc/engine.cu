@@ -568,12 +568,12 @@ int forward(b2_engine* e, int T, int ntiles, int nlast, int attn_split) {
     if (ntiles > 0) {
       KL k(e, B2K_MISC);
       if (!k.skip()) B2_TRY(launch_attn_prefill(e->qrot, kp, vp, e->d_block_table, e->bt_stride, e->d_tiles, ntiles, e->attn,
-                                 e->nq, e->nkv, e->hd, c.block_size, e->stream, e->attn_scale));
+                                 e->nq, e->nkv, e->hd, c.block_size, e->stream, e->attn_scale, c.sliding_window));
     } else {
       KL k(e, B2K_ATTN_DECODE);
       if (!k.skip())
         B2_TRY(launch_attn_decode(e->qrot, kp, vp, e->d_block_table, e->bt_stride, e->d_seq_lens, e->attn_scratch, e->attn, T,
-                                  e->nq, e->nkv, e->hd, c.block_size, e->stream, e->attn_scale));
+                                  e->nq, e->nkv, e->hd, c.block_size, e->stream, e->attn_scale, c.sliding_window));
     }
     ActIn o = linear(e, B2K_GEMM_O, XB_ATTN, e->attn, L.wo, L.tm_o, e->proj, T, H, e->q_size, &rc, prefetch_for(l + 1, 0), false,
                      /*after_attention=*/ntiles == 0);
@@ -1019,6 +1019,8 @@ extern "C" int b2_engine_create(const b2_config* cfg, const char* safetensors_pa
   B2_REQUIRE(cfg->arch == B2_ARCH_QWEN3 || cfg->arch == B2_ARCH_PHI3 || cfg->arch == B2_ARCH_OPT,
              "arch %d not built (0 = Qwen3, 1 = Phi-3, 2 = OPT)", cfg->arch);
   B2_REQUIRE(cfg->arch != B2_ARCH_OPT || cfg->tie_embeddings, "OPT: the lm_head is tied to embed_tokens");
+  B2_REQUIRE(cfg->sliding_window >= 0 && (cfg->sliding_window == 0 || cfg->arch == B2_ARCH_PHI3),
+             "sliding_window %d: only the Phi-3 family has one", cfg->sliding_window);
   B2_REQUIRE(cfg->head_dim >= 8 && cfg->head_dim <= 128 && cfg->head_dim % 8 == 0, "head_dim %d not supported (multiple of 8, <= 128)",
              cfg->head_dim);
   B2_REQUIRE(cfg->num_kv_heads >= 1 && (cfg->num_q_heads == 2 * cfg->num_kv_heads || cfg->num_q_heads == cfg->num_kv_heads),

@@ -136,8 +136,9 @@ size_t attn_decode_scratch_floats(int B, int nq, int nkv, int hd);
 int attn_decode_zero_counters(float* scratch, cudaStream_t s);
 int launch_attn_decode(const bf16* q, const bf16* k_pages, const bf16* v_pages, const int32_t* block_table,
                        int bt_stride, const int32_t* seq_lens, float* scratch, bf16* out, int B, int nq, int nkv,
-                       int hd, int block_size, cudaStream_t s, float softmax_scale = 0.f);
-// softmax_scale 0 = hd^-0.5; a padded head passes the scale of its real width.
+                       int hd, int block_size, cudaStream_t s, float softmax_scale = 0.f, int window = 0);
+// softmax_scale 0 = hd^-0.5; a padded head passes the scale of its real width.  window > 0: sliding-window attention,
+// each query sees its last `window` keys (itself included).
 
 // ---- attn_prefill.cu ----
 struct PrefillTile {  // one 64-query tile of one sequence
@@ -148,7 +149,7 @@ struct PrefillTile {  // one 64-query tile of one sequence
 };
 int launch_attn_prefill(const bf16* q, const bf16* k_pages, const bf16* v_pages, const int32_t* block_table,
                         int bt_stride, const PrefillTile* tiles_dev, int ntiles, bf16* out, int nq, int nkv, int hd,
-                        int block_size, cudaStream_t s, float softmax_scale = 0.f);
+                        int block_size, cudaStream_t s, float softmax_scale = 0.f, int window = 0);
 
 // ---- sampling.cu ----
 int launch_sample(const bf16* logits, int32_t* out, int nseq, int V, float temperature, int top_k, float top_p, uint64_t seed,

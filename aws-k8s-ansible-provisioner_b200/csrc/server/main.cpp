@@ -155,6 +155,7 @@ static void fill_config(const Options& o, b2_config& c) {
     if (mt && mt->is_string() && mt->as_string() == "phi3") {
       c.arch = B2_ARCH_PHI3;
       c.rotary_dim = (int)(getf("partial_rotary_factor", 1.0) * c.head_dim + 0.5);
+      c.sliding_window = geti("sliding_window", 0);  // null in the config parses as "not a number" -> 0
     } else if (mt && mt->is_string() && mt->as_string() == "opt") {
       // HF OPTConfig names: ffn_dim, no kv-head count (MHA), LayerNorm eps is torch's default
       c.arch = B2_ARCH_OPT;

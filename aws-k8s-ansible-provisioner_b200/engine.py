@@ -40,6 +40,7 @@ class EngineConfig:
     arch: str = "qwen3"          # "qwen3" | "phi3" | "opt" (include/b2_engine.h, enum b2_arch)
     rotary_dim: int = 0          # 0 = head_dim
     max_positions: int = 0       # OPT: learned position table rows - 2 (0 = max_model_len)
+    sliding_window: int = 0      # Phi-3: attend to the last N keys only (0 = all)
 
     def kv_bytes_per_token(self) -> int:
         return 2 * self.num_layers * self.num_kv_heads * self.head_dim * 2
@@ -81,6 +82,7 @@ class Engine:
         c.arch = {"qwen3": capi.ARCH_QWEN3, "phi3": capi.ARCH_PHI3, "opt": capi.ARCH_OPT}[cfg.arch]
         c.rotary_dim = int(cfg.rotary_dim)
         c.max_positions = int(cfg.max_positions)
+        c.sliding_window = int(cfg.sliding_window)
         self._inv = None
         if rope_inv_freq is not None:
             self._inv = np.ascontiguousarray(np.asarray(rope_inv_freq, dtype=np.float32))

@@ -56,13 +56,13 @@ typedef struct b2_config {
   int32_t arch;              /* B2_ARCH_*: which HF model family the tensors and the layer follow */
   int32_t rotary_dim;        /* width of the rotated prefix of each head; 0 = head_dim */
   int32_t max_positions;     /* OPT: rows of the learned position table minus 2; 0 = max_model_len */
+  int32_t sliding_window;    /* Phi-3: every query attends to its last `sliding_window` keys only; 0 = all */
 } b2_config;
 
 /* Model families.  QWEN3: HF:models/qwen3/modeling_qwen3.py (QK-norm, separate q/k/v and gate/up
  * tensors, GQA).  PHI3: HF:models/phi3/modeling_phi3.py:49-64,208-272 (fused qkv_proj and
  * gate_up_proj tensors, no QK-norm, one query head per kv head or two, rotary over rotary_dim,
- * usually an untied lm_head; sliding-window attention is NOT implemented -- contexts up to the
- * window are exact).
+ * usually an untied lm_head, sliding-window attention when config.sliding_window is set).
  * OPT: HF:models/opt/modeling_opt.py:45-70,97-181,184-254,273-397 (learned positions with the +2
  * offset, LayerNorm with bias before attention and before the feed-forward, biased q/k/v/out and
  * fc1/fc2 projections, query pre-scaled by head_dim^-0.5, ReLU, tied lm_head; rms_eps carries the

@@ -112,10 +112,11 @@ def tiny() -> None:
 
 def phi3_tiny() -> None:
     """HF Phi3ForCausalLM outputs for the two tiny Phi-3 variants (full and partial rotary)."""
-    from oracle.phi3_oracle import PHI3_TINY, PHI3_TINY_PARTIAL, hf_phi3_model
+    from oracle.phi3_oracle import PHI3_TINY, PHI3_TINY_PARTIAL, PHI3_TINY_WINDOW, hf_phi3_model
 
     out_d = {}
-    for tag, arch in (("full", PHI3_TINY), ("partial", PHI3_TINY_PARTIAL)):
+    # "window": sliding_window 24 with 40-token prompts + 24 generated tokens, so the window cuts from the start
+    for tag, arch in (("full", PHI3_TINY), ("partial", PHI3_TINY_PARTIAL), ("window", PHI3_TINY_WINDOW)):
         model = hf_phi3_model(arch, seed=0)
         sd = hf_state_dict(model)
         perturb_norm_weights(sd)

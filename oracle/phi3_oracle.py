@@ -16,8 +16,9 @@ that forward, reusing the Qwen3 restatement's pieces where the two models share 
 
 Parity pin: tests/test_oracle.py checks the restatement bit-for-bit against HF on the tiny
 configuration below, and tests/golden/phi3_tiny.npz holds HF's own outputs (oracle/make_golden.py).
-Sliding-window attention (Phi-3-mini-4k ships `sliding_window: 2047`) is outside both the
-restatement and the engine: the fixtures use contexts far below the window, where it is inactive.
+Sliding-window attention (Phi-3-mini-4k ships `sliding_window: 2047`; HF:...:265 and the sliding-window
+mask of masking_utils) is restated by `attention_window` below and pinned by the "window" fixture, whose
+window (24) is shorter than its contexts.
 """
 from __future__ import annotations
 
@@ -33,6 +34,7 @@ from .qwen3_oracle import ArchConfig, KVState, Restated, attention_sdpa, rms_nor
 class Phi3Arch(ArchConfig):
     family: str = "phi3"
     rotary_dim: int = 0  # 0 = head_dim (partial_rotary_factor 1.0, what Phi-3-mini uses)
+    sliding_window: int = 0  # 0 = none; Phi-3-mini-4k ships 2047: a query sees its last 2047 keys, itself included
 
     @property
     def rot(self) -> int:
@@ -50,6 +52,10 @@ PHI3_TINY = Phi3Arch(name="phi3-tiny-test", num_layers=2, hidden=768, num_q_head
 PHI3_MINI_2L = Phi3Arch(name="phi3-mini-2-layers", num_layers=2, hidden=3072, num_q_heads=32, num_kv_heads=32, head_dim=96,
                         intermediate=8192, vocab=32064, rms_eps=1e-5, rope_theta=10000.0, max_position=4096,
                         tie_embeddings=False)
+# a window shorter than the test contexts, so that it actually cuts
+PHI3_TINY_WINDOW = Phi3Arch(name="phi3-tiny-sliding-window", num_layers=2, hidden=768, num_q_heads=8, num_kv_heads=8, head_dim=96,
+                            intermediate=1024, vocab=1024, rms_eps=1e-5, rope_theta=10000.0, max_position=4096,
+                            tie_embeddings=False, sliding_window=24)
 # partial rotary (the "partial-rotary support" of SURVEY.md a14): 64 of 96 dims rotate
 PHI3_TINY_PARTIAL = Phi3Arch(name="phi3-tiny-partial-rotary", num_layers=2, hidden=768, num_q_heads=8, num_kv_heads=8, head_dim=96,
                              intermediate=1024, vocab=1024, rms_eps=1e-5, rope_theta=10000.0, max_position=4096,
@@ -72,7 +78,7 @@ def hf_phi3_config(arch: Phi3Arch):
         rms_norm_eps=arch.rms_eps, rope_parameters={"rope_type": "default", "rope_theta": arch.rope_theta,
                                                     "partial_rotary_factor": arch.rot / arch.head_dim},
         tie_word_embeddings=arch.tie_embeddings, attention_dropout=0.0, resid_pdrop=0.0, embd_pdrop=0.0,
-        sliding_window=None, pad_token_id=0, bos_token_id=1, eos_token_id=2,
+        sliding_window=arch.sliding_window or None, pad_token_id=0, bos_token_id=1, eos_token_id=2,
     )
 
 
@@ -111,6 +117,19 @@ def apply_partial_rope(q, k, cos, sin):
     return q2, k2
 
 
+def attention_window(window: int):
+    """softmax(q k^T * scaling + mask) v with the sliding-window causal mask HF builds for Phi-3: key j is visible
+    to the query at position i iff j <= i and i - j < window.  Evaluated by torch's sdpa with an explicit boolean
+    mask (what HF's sdpa path receives); q: [B, H, T, d], k/v: [B, Hk, S, d], the T queries are the LAST T positions."""
+    def attn(q, k, v, scaling: float, causal: bool):
+        T, S = q.shape[2], k.shape[2]
+        qi = torch.arange(S - T, S)[:, None]
+        kj = torch.arange(S)[None, :]
+        mask = (kj <= qi) & (qi - kj < window)
+        return F.scaled_dot_product_attention(q, k, v, attn_mask=mask[None, None], scale=scaling, enable_gqa=q.shape[1] != k.shape[1])
+    return attn
+
+
 def linear_fp32_order(x: torch.Tensor, w: torch.Tensor) -> torch.Tensor:
     """y = x W^T with fp32 accumulation and one rounding, like F.linear on bf16, but summed by the fp32
     GEMM (different blocking, hence a different order of the same additions)."""
@@ -120,10 +139,12 @@ def linear_fp32_order(x: torch.Tensor, w: torch.Tensor) -> torch.Tensor:
 class RestatedPhi3(Restated):
     """Plain-torch Phi-3 forward over an HF-named state dict (forward()/greedy() come from Restated)."""
 
-    def __init__(self, arch: Phi3Arch, sd, attention=attention_sdpa, linear=F.linear):
-        """`linear`: the nn.Linear arithmetic.  F.linear is HF's (bf16 in, fp32 accumulate, one rounding);
+    def __init__(self, arch: Phi3Arch, sd, attention=None, linear=F.linear):
+        """`attention`: default sdpa, or the sliding-window form when the architecture has a window.  `linear`: the nn.Linear arithmetic.  F.linear is HF's (bf16 in, fp32 accumulate, one rounding);
         `linear_fp32_order` below is the same contract with another fp32 summation order -- tests use the
         distance between the two as the bf16 noise floor that no implementation can get under."""
+        if attention is None:
+            attention = attention_window(arch.sliding_window) if arch.sliding_window else attention_sdpa
         super().__init__(arch, sd, attention)
         self.lin = linear
 

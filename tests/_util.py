@@ -72,7 +72,8 @@ def engine_config_from_arch(p, arch, **kw):
                          vocab=arch.vocab, tie_embeddings=arch.tie_embeddings, rms_eps=arch.rms_eps,
                          rope_theta=arch.rope_theta, arch=getattr(arch, "family", "qwen3"),
                          rotary_dim=getattr(arch, "rotary_dim", 0) or 0,
-                         max_positions=getattr(arch, "max_position", 0) if getattr(arch, "family", "") == "opt" else 0)
+                         max_positions=getattr(arch, "max_position", 0) if getattr(arch, "family", "") == "opt" else 0,
+                         sliding_window=getattr(arch, "sliding_window", 0) or 0)
     for k, v in kw.items():
         setattr(cfg, k, v)
     return cfg

@@ -39,8 +39,8 @@ def test_library_exports_every_declared_symbol(pkg, lib):
 def test_config_struct_layout(pkg):
     from importlib import import_module
     capi = import_module("aws-k8s-ansible-provisioner_b200.capi")
-    # 18 four-byte fields + one pointer + 3 four-byte fields (ABI v2: arch, rotary_dim, max_positions),
-    # padded to the pointer's alignment
+    # 18 four-byte fields + one pointer + 4 four-byte fields (ABI v2: arch, rotary_dim, max_positions,
+    # sliding_window)
     assert C.sizeof(capi.b2_config) == 18 * 4 + 8 + 4 * 4
     assert capi.b2_config.arch.offset == 18 * 4 + 8 and capi.b2_config.rotary_dim.offset == 18 * 4 + 12
     assert C.sizeof(capi.b2_sampling) == 24

@@ -12,8 +12,8 @@ import pytest
 import torch
 
 from _util import ROOT, engine_config_from_arch, pkg, rel_err, rel_fro
-from oracle.phi3_oracle import (PHI3_MINI_2L, PHI3_TINY, PHI3_TINY_PARTIAL, RestatedPhi3, hf_phi3_model, linear_fp32_order,
-                                phi3_inv_freq)
+from oracle.phi3_oracle import (PHI3_MINI_2L, PHI3_TINY, PHI3_TINY_PARTIAL, PHI3_TINY_WINDOW, RestatedPhi3, hf_phi3_model,
+                                linear_fp32_order, phi3_inv_freq)
 from oracle.qwen3_oracle import KVState, attention_explicit, hf_state_dict, make_prompts, perturb_norm_weights, top2_gap
 
 pytestmark = pytest.mark.gpu
@@ -39,10 +39,10 @@ def make_engine(P, arch, sd, **kw):
     return e
 
 
-@pytest.mark.parametrize("tag", ["full", "partial"])
+@pytest.mark.parametrize("tag", ["full", "partial", "window"])
 @pytest.mark.parametrize("graphs", [False, True])
 def test_phi3_tiny_matches_hf_golden(P, tag, graphs):
-    arch = PHI3_TINY if tag == "full" else PHI3_TINY_PARTIAL
+    arch = {"full": PHI3_TINY, "partial": PHI3_TINY_PARTIAL, "window": PHI3_TINY_WINDOW}[tag]
     model = hf_phi3_model(arch, seed=0)
     sd = hf_state_dict(model)
     perturb_norm_weights(sd)
@@ -148,3 +148,50 @@ def test_phi3_rejects_unsupported_shapes(P):
     with pytest.raises(Exception) as ei:
         P.Engine(cfg)
     assert "query heads per kv head" in str(ei.value)
+
+
+@pytest.mark.parametrize("window", [24, 100])
+def test_phi3_sliding_window_long_ragged(P, window):
+    """Sliding-window attention at contexts many pages longer than the window: prompts of 5 .. 700 tokens, the
+    window starting inside a page, at a page boundary and before the first token; prefill (window mask + skipped key
+    tiles) and 12 decode steps (skipped pages + masked first page) against the restatement, tie-aware."""
+    from dataclasses import replace
+    arch = replace(PHI3_TINY_WINDOW, sliding_window=window, name="phi3-tiny-window-%d" % window)
+    sd = hf_state_dict(hf_phi3_model(arch, seed=0))
+    perturb_norm_weights(sd)
+    g = torch.Generator().manual_seed(31)
+    lens = [5, window - 1, window, window + 1, 40, 100, 333, 700, 16 * 9, 16 * 9 + window]
+    steps = 12
+    prompts = [torch.randint(0, arch.vocab, (n,), generator=g).tolist() for n in lens]
+    e = make_engine(P, arch, sd, max_model_len=1024, num_blocks=sum((n + steps) // 16 + 2 for n in lens) + 8, max_seqs=16,
+                    max_batch_tokens=2048, use_cuda_graphs=True)
+    e.set_debug(logits=True)
+    sids = [e.seq_create(n + steps + 2) for n in lens]
+    first = e.prefill(sids, prompts)
+    pre_logits = torch.from_numpy(e.get_logits(len(lens)).copy())
+    toks = [first] + [e.decode_step(sids) for _ in range(steps - 1)]
+    got = np.stack(toks, axis=1)
+    last_logits = torch.from_numpy(e.get_logits(len(lens)).copy())
+    r = RestatedPhi3(arch, sd)
+    r2 = RestatedPhi3(arch, sd, linear=linear_fp32_order)  # the oracle's own bf16 noise floor (see the full-width test)
+    full = RestatedPhi3(replace(arch, sliding_window=0), sd)  # no window: must differ once the context exceeds it
+    for k, pr in enumerate(prompts):
+        ref_ids, ref_logits = r.greedy(torch.tensor([pr]), steps)
+        alt_ids, alt = r2.greedy(torch.tensor([pr]), steps)
+        floor = rel_err(alt[0, 0].float(), ref_logits[0, 0].float())
+        # the floor of the LAST step only means something if the reordered oracle decoded the same tokens
+        floor_last = rel_err(alt[0, steps - 1].float(), ref_logits[0, steps - 1].float()) if torch.equal(alt_ids, ref_ids) else 1.0
+        assert rel_err(pre_logits[k], ref_logits[0, 0].float()) <= max(REL_TOL, 2.0 * floor), "prefill logits, prompt of %d tokens" % lens[k]
+        if lens[k] > 2 * window:
+            _, nowin = full.greedy(torch.tensor([pr]), 1)
+            assert rel_err(pre_logits[k], nowin[0, 0].float()) > REL_TOL, "the window had no effect at %d tokens" % lens[k]
+        gaps = top2_gap(ref_logits)
+        same = True
+        for t in range(steps):
+            if got[k, t] != int(ref_ids[0, t]):
+                assert gaps[0, t] <= 0.0625, "prompt %d step %d: %d != %d, oracle gap %.4f" % (lens[k], t, got[k, t], int(ref_ids[0, t]), gaps[0, t])
+                same = False
+                break
+        if same:
+            assert rel_err(last_logits[k], ref_logits[0, steps - 1].float()) <= max(REL_TOL, 2.0 * floor_last), "decode logits, prompt of %d tokens" % lens[k]
+    e.close()
