@@ -44,7 +44,7 @@ class Phi3Arch(ArchConfig):
 # microsoft/Phi-3-mini-4k-instruct shapes (BASELINE.json config 4)
 PHI3_MINI = Phi3Arch(name="microsoft/Phi-3-mini-4k-instruct", num_layers=32, hidden=3072, num_q_heads=32, num_kv_heads=32,
                      head_dim=96, intermediate=8192, vocab=32064, rms_eps=1e-5, rope_theta=10000.0, max_position=4096,
-                     tie_embeddings=False)
+                     tie_embeddings=False, sliding_window=2047)
 # same structure (MHA, 96-wide heads, untied head), CPU-cheap
 PHI3_TINY = Phi3Arch(name="phi3-tiny-test", num_layers=2, hidden=768, num_q_heads=8, num_kv_heads=8, head_dim=96,
                      intermediate=1024, vocab=1024, rms_eps=1e-5, rope_theta=10000.0, max_position=4096, tie_embeddings=False)

@@ -112,12 +112,13 @@ def test_c3_opt125m_batch256(P):
         100 * together, STEPS, agree, STEPS))
     first_split = next((t for t in range(STEPS) if (toks[t] != toks[t, 0]).any()), STEPS)
     print("C3: first step at which any copy differs: %d" % first_split)
-    assert first_split >= 2 and together >= 0.1 and agree >= 4
+    assert first_split >= 2 and agree >= 4  # `together` is reported, not asserted: it is a count of near-ties
     e.close()
 
 
 def test_c4_phi3mini_batch32_prefill2048(P):
-    """Config 4: Phi-3-mini (32 layers, 3072 wide, 32 heads of 96), batch 32, 2048-token prefill, then decode."""
+    """Config 4: Phi-3-mini-4k (32 layers, 3072 wide, 32 heads of 96, sliding window 2047), batch 32, 2048-token
+    prefill, then decode -- the contexts of this configuration are longer than the window from the first step."""
     arch = PHI3_MINI
     B, PL, STEPS = 32, 2048, 16
     cfg = engine_config_from_arch(P, arch, max_model_len=PL + 64, max_seqs=B, max_batch_tokens=8192, use_cuda_graphs=True)
@@ -133,5 +134,5 @@ def test_c4_phi3mini_batch32_prefill2048(P):
         100 * together, STEPS, agree, STEPS))
     first_split = next((t for t in range(STEPS) if (toks[t] != toks[t, 0]).any()), STEPS)
     print("C4: first step at which any copy differs: %d" % first_split)
-    assert first_split >= 2 and together >= 0.1 and agree >= 4
+    assert first_split >= 2 and agree >= 4  # `together` is reported, not asserted: it is a count of near-ties
     e.close()
