@@ -39,6 +39,7 @@ SIGNATURES = {
     "b2_abi_version": (_I, []),
     "b2_engine_create": (_I, [C.POINTER(b2_config), C.c_char_p, _I, C.POINTER(_P)]),
     "b2_engine_load_tensor": (_I, [_P, C.c_char_p, _P, C.c_size_t]),
+    "b2_engine_load_safetensors": (_I, [_P, C.c_char_p]),
     "b2_engine_finalize": (_I, [_P]),
     "b2_engine_free": (None, [_P]),
     "b2_engine_info": (_I, [_P, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),

@@ -993,8 +993,29 @@ int load_safetensors(b2_engine* e, const char* path) {
         }
         src = conv.data();
         nbytes = n * 2;
+      } else if (dt->as_string() == "F16") {  // fp16 -> fp32 (exact) -> bf16 (round to nearest even)
+        size_t n = nbytes / 2;
+        conv.resize(n);
+        const uint16_t* hsrc = reinterpret_cast<const uint16_t*>(src);
+        for (size_t i = 0; i < n; ++i) {
+          const uint32_t hbits = hsrc[i], sign = (hbits & 0x8000u) << 16, ex = (hbits >> 10) & 0x1fu, man = hbits & 0x3ffu;
+          uint32_t u;
+          if (ex == 0) {
+            if (man == 0) u = sign;
+            else {  // subnormal half: normalise
+              int sh = 0;
+              uint32_t m = man;
+              while (!(m & 0x400u)) { m <<= 1; ++sh; }
+              u = sign | ((uint32_t)(127 - 15 - sh + 1) << 23) | ((m & 0x3ffu) << 13);
+            }
+          } else if (ex == 31) u = sign | 0x7f800000u | (man << 13);
+          else u = sign | ((ex + 112u) << 23) | (man << 13);
+          conv[i] = (uint16_t)((u + 0x7fffu + ((u >> 16) & 1u)) >> 16);
+        }
+        src = conv.data();
+        nbytes = n * 2;
       } else if (dt->as_string() != "BF16") {
-        throw std::runtime_error("tensor " + kv.first + ": dtype " + dt->as_string() + " not supported (BF16/F32)");
+        throw std::runtime_error("tensor " + kv.first + ": dtype " + dt->as_string() + " not supported (BF16/F16/F32)");
       }
       if (kv.first.find("rotary_emb.inv_freq") != std::string::npos) continue;
       rc = layer_tensor(e, kv.first, src, nbytes);
@@ -1281,6 +1302,12 @@ extern "C" int b2_engine_load_tensor(b2_engine* e, const char* hf_name, const vo
   B2_REQUIRE(e && hf_name && host_bf16, "b2_engine_load_tensor: null argument");
   B2_CUDA_OK(cudaSetDevice(e->device));
   return layer_tensor(e, hf_name, host_bf16, nbytes);
+}
+
+extern "C" int b2_engine_load_safetensors(b2_engine* e, const char* path) {
+  B2_REQUIRE(e && path, "b2_engine_load_safetensors: null argument");
+  B2_CUDA_OK(cudaSetDevice(e->device));
+  return load_safetensors(e, path);
 }
 
 extern "C" int b2_engine_finalize(b2_engine* e) {

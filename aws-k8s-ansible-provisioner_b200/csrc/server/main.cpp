@@ -790,14 +790,36 @@ int main(int argc, char** argv) {
   App app;
   if (!parse_args(argc, argv, app.opt)) { usage(); return 2; }
   fill_config(app.opt, app.cfg);
+  // checkpoint files: model.safetensors, or the shards listed in model.safetensors.index.json (Phi-3-mini ships two)
   std::string st_path;
+  std::vector<std::string> shards;
   if (app.opt.load_format != "dummy" && is_dir(app.opt.model) && is_file(app.opt.model + "/model.safetensors")) st_path = app.opt.model + "/model.safetensors";
-  else if (app.opt.load_format != "dummy" && is_file(app.opt.model)) st_path = app.opt.model;
-  if (app.opt.load_format == "safetensors" && st_path.empty()) { fprintf(stderr, "b2serve: no model.safetensors under %s\n", app.opt.model.c_str()); return 1; }
+  else if (app.opt.load_format != "dummy" && is_dir(app.opt.model) && is_file(app.opt.model + "/model.safetensors.index.json")) {
+    try {
+      Value idx = b2json::parse(read_file(app.opt.model + "/model.safetensors.index.json"));
+      const Value* wm = idx.find("weight_map");
+      if (wm && wm->is_object())
+        for (auto& kv : *wm->obj) {
+          const std::string f = app.opt.model + "/" + kv.second.as_string();
+          if (std::find(shards.begin(), shards.end(), f) == shards.end()) shards.push_back(f);
+        }
+    } catch (const std::exception& ex) {
+      fprintf(stderr, "b2serve: model.safetensors.index.json: %s\n", ex.what());
+      return 1;
+    }
+  } else if (app.opt.load_format != "dummy" && is_file(app.opt.model)) st_path = app.opt.model;
+  if (app.opt.load_format == "safetensors" && st_path.empty() && shards.empty()) { fprintf(stderr, "b2serve: no model.safetensors under %s\n", app.opt.model.c_str()); return 1; }
   const double t0 = now_s();
   int rc = b2_engine_create(&app.cfg, st_path.empty() ? nullptr : st_path.c_str(), app.opt.device, &app.engine);
   if (rc != 0) { fprintf(stderr, "b2serve: engine creation failed (%d): %s\n", rc, b2_last_error()); return 1; }
-  if (st_path.empty()) {
+  if (!shards.empty()) {
+    for (auto& f : shards) {
+      rc = b2_engine_load_safetensors(app.engine, f.c_str());
+      if (rc != 0) { fprintf(stderr, "b2serve: %s: %s\n", f.c_str(), b2_last_error()); return 1; }
+    }
+    rc = b2_engine_finalize(app.engine);
+    if (rc != 0) { fprintf(stderr, "b2serve: %s\n", b2_last_error()); return 1; }
+  } else if (st_path.empty()) {
     fprintf(stderr, "b2serve: no checkpoint found for %s; using random-init bf16 weights (seed %llu)\n", app.opt.model.c_str(), (unsigned long long)app.opt.seed);
     rc = load_dummy_weights(app.engine, app.cfg, app.opt.seed);
     if (rc != 0) { fprintf(stderr, "b2serve: weight init failed: %s\n", b2_last_error()); return 1; }

@@ -95,6 +95,12 @@ class Engine:
         self.device = device
 
     # ---- weights -----------------------------------------------------------------------
+    def load_safetensors(self, paths) -> None:
+        """Loads one or more safetensors files (the shards of a checkpoint) and finalises the weights."""
+        for p in ([paths] if isinstance(paths, str) else list(paths)):
+            check(self.lib.b2_engine_load_safetensors(self.h, p.encode()), self.lib)
+        check(self.lib.b2_engine_finalize(self.h), self.lib)
+
     def load_state_dict(self, sd) -> None:
         """Uploads an HF-named state dict of torch bf16 CPU tensors (no file round trip)."""
         import torch

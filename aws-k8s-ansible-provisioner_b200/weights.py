@@ -46,12 +46,14 @@ def random_state_dict(cfg: EngineConfig, seed: int = 0, std: float = 0.02) -> di
 
 
 def write_safetensors(sd: dict[str, torch.Tensor], path: str) -> None:
-    """Minimal safetensors writer (BF16 only) so the C++ server can mmap a synthetic checkpoint."""
+    """Minimal safetensors writer so the C++ server can mmap a synthetic checkpoint: every tensor is stored in its
+    own dtype (bf16, fp16 or fp32 -- the three the engine's loader reads)."""
+    names = {torch.bfloat16: "BF16", torch.float16: "F16", torch.float32: "F32"}
     header = {}
     off = 0
     for name, t in sd.items():
-        n = t.numel() * 2
-        header[name] = {"dtype": "BF16", "shape": list(t.shape), "data_offsets": [off, off + n]}
+        n = t.numel() * t.element_size()
+        header[name] = {"dtype": names[t.dtype], "shape": list(t.shape), "data_offsets": [off, off + n]}
         off += n
     hb = json.dumps(header, separators=(",", ":")).encode()
     hb += b" " * ((8 - len(hb) % 8) % 8)
@@ -59,4 +61,5 @@ def write_safetensors(sd: dict[str, torch.Tensor], path: str) -> None:
         f.write(struct.pack("<Q", len(hb)))
         f.write(hb)
         for t in sd.values():
-            f.write(t.contiguous().view(torch.int16).numpy().tobytes())
+            t = t.contiguous()
+            f.write(t.view(torch.int16 if t.element_size() == 2 else torch.int32).numpy().tobytes())

@@ -80,6 +80,9 @@ int  b2_abi_version(void);
  * Replaces: the model-server container start at llm-d-deploy.yaml:176-193. */
 int  b2_engine_create(const b2_config* cfg, const char* safetensors_path, int device, b2_engine** out);
 int  b2_engine_load_tensor(b2_engine* e, const char* hf_name, const void* host_bf16, size_t nbytes);
+/* Reads every tensor of one safetensors file (BF16, F16 or F32; converted to bf16) into an engine created without
+ * a path: call it once per shard of a sharded checkpoint (model-0000i-of-0000N.safetensors), then finalize. */
+int  b2_engine_load_safetensors(b2_engine* e, const char* path);
 int  b2_engine_finalize(b2_engine* e);
 void b2_engine_free(b2_engine* e);
 /* Info: KV pages total / free, bytes of weights resident. */

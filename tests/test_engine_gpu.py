@@ -421,3 +421,36 @@ def test_tiny_long_ragged_contexts(P, tiny):
         e.seq_free(s)
     assert e.info()["free_blocks"] == e.info()["num_blocks"] - 1  # everything returned (page 0 is the null page)
     e.close()
+
+
+def test_sharded_checkpoint_and_dtypes(P, tiny, tmp_path):
+    """A checkpoint split over two safetensors files, one stored in fp16 and one in fp32, loaded through
+    b2_engine_load_safetensors: the engine must end up with exactly the weights (rounded to bf16, to nearest even)
+    that a state dict of the same values gives -- identical greedy tokens."""
+    weights = __import__("importlib").import_module("aws-k8s-ansible-provisioner_b200.weights")
+    model, sd = tiny
+    arch = QWEN3_TINY
+    g = torch.Generator().manual_seed(5)
+    wide = {k: (v.float() + 1e-3 * torch.randn(v.shape, generator=g)) for k, v in sd.items()}  # not bf16-representable
+    names = list(wide)
+    a = {k: wide[k].to(torch.float16) for k in names[: len(names) // 2]}
+    b = {k: wide[k] for k in names[len(names) // 2:]}
+    weights.write_safetensors(a, str(tmp_path / "model-00001-of-00002.safetensors"))
+    weights.write_safetensors(b, str(tmp_path / "model-00002-of-00002.safetensors"))
+    expect = {k: a[k].float().to(torch.bfloat16) for k in a}
+    expect.update({k: b[k].to(torch.bfloat16) for k in b})
+    prompts = make_prompts(2, 30, arch.vocab, seed=2)
+    outs = []
+    for mode in ("files", "dict"):
+        cfg = engine_config_from_arch(P, arch, max_model_len=128, num_blocks=32, max_seqs=4, max_batch_tokens=128, use_cuda_graphs=False)
+        e = P.Engine(cfg, rope_inv_freq=rope_inv_freq(arch).numpy())
+        if mode == "files":
+            e.load_safetensors([str(tmp_path / "model-00001-of-00002.safetensors"), str(tmp_path / "model-00002-of-00002.safetensors")])
+        else:
+            e.load_state_dict(expect)
+        sids = [e.seq_create(64) for _ in range(2)]
+        first = e.prefill(sids, [p.tolist() for p in prompts])
+        toks, _ = e.decode_run(sids, 12)
+        outs.append(np.concatenate([first[None, :], toks], axis=0))
+        e.close()
+    assert np.array_equal(outs[0], outs[1])
