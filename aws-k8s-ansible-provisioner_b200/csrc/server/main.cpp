@@ -237,6 +237,7 @@ struct Req {
   int max_tokens = 16;
   b2_sampling samp{1.0f, 0, 1.0f, 0};
   bool ignore_eos = false;
+  bool streaming = false;  // a handler is waiting for every token (SSE); otherwise only for the end
   std::vector<std::string> stops;
   // produced
   std::mutex mu;
@@ -326,7 +327,9 @@ class Scheduler {
           if (pos != std::string::npos) { r->text.erase(pos); stop_hit = true; break; }
         }
       }
-      r->cv.notify_all();
+      // a non-streaming handler only cares about `done`: waking 64 of them per decode step costs the scheduler
+      // thread more host time than the step's own bookkeeping
+      if (r->streaming) r->cv.notify_all();
     }
     r->next_token = tok;
     if (eos || stop_hit) { finish(r, "stop"); return true; }
@@ -559,6 +562,7 @@ static Value usage_json(const std::vector<ReqP>& rs, size_t prompts_each) {
 }
 
 static void run_requests(App& app, std::vector<ReqP>& rs, bool stream, bool chat, const std::string& id, b2http::Conn& c, int n_per_prompt) {
+  for (auto& r : rs) r->streaming = stream;
   for (auto& r : rs) app.sched->submit(r);
   const char* object = chat ? (stream ? "chat.completion.chunk" : "chat.completion") : "text_completion";
   auto base = [&]() {
