@@ -212,6 +212,73 @@ def test_concurrent_requests_share_the_batch(server):
     assert solo["choices"][0]["text"][:8] == results[0][1]["choices"][0]["text"][:8]
 
 
+def test_overload_cancellation_and_cleanup(server):
+    """More requests than sequence slots (16) and than KV pages allow at once, ragged prompts longer than one
+    prefill chunk (256 tokens), a mix of plain and streamed requests, and clients that hang up mid-stream: every
+    surviving request completes with its full length, and afterwards nothing is running, waiting or holding pages."""
+    import random
+    import socket
+    import threading
+    port = server["port"]
+    rnd = random.Random(7)
+    N = 60
+    specs = [(rnd.randint(1, 300), rnd.randint(1, 40), rnd.random() < 0.4) for _ in range(N)]  # (prompt len, new tokens, stream)
+    results = [None] * N
+
+    def plain(i, plen, ntok):
+        results[i] = call(port, "POST", "/v1/completions", {"model": MODEL_ID, "prompt": [rnd.randrange(1, 1000) for _ in range(plen)],
+                                                             "max_tokens": ntok, "temperature": 0, "ignore_eos": True})
+
+    def streamed(i, plen, ntok, hang_up):
+        body = json.dumps({"model": MODEL_ID, "prompt": [3 + (i % 50)] * plen, "max_tokens": ntok, "temperature": 0, "ignore_eos": True,
+                           "stream": True}).encode()
+        s = socket.create_connection(("127.0.0.1", port), timeout=60)
+        s.sendall(b"POST /v1/completions HTTP/1.1\r\nHost: x\r\nContent-Type: application/json\r\nContent-Length: %d\r\n\r\n" % len(body) + body)
+        buf = b""
+        while b"data: [DONE]" not in buf:
+            chunk = s.recv(65536)
+            if not chunk:
+                break
+            buf += chunk
+            if hang_up and buf.count(b"data: ") >= 2:
+                break  # client disappears after the second event
+        s.close()
+        # (events can be fewer than tokens: a token that ends inside a UTF-8 sequence produces no text yet)
+        results[i] = ("hung up" if hang_up else (b"data: [DONE]" in buf, buf.count(b"data: {")), ntok)
+
+    th = []
+    for i, (plen, ntok, stream) in enumerate(specs):
+        if stream:
+            th.append(threading.Thread(target=streamed, args=(i, plen, ntok, i % 3 == 0)))
+        else:
+            th.append(threading.Thread(target=plain, args=(i, plen, ntok)))
+    [t.start() for t in th]
+    [t.join(timeout=120) for t in th]
+    assert not any(t.is_alive() for t in th), "a request never finished"
+    for i, (plen, ntok, stream) in enumerate(specs):
+        r = results[i]
+        assert r is not None
+        if not stream:
+            assert r[0] == 200 and r[1]["usage"]["completion_tokens"] == ntok and r[1]["usage"]["prompt_tokens"] == plen, r
+        elif r[0] != "hung up":
+            done, events = r[0]
+            assert done and 1 <= events <= ntok + 1, "streamed request %d: done=%s, %d events for %d tokens" % (i, done, events, ntok)
+    # drained: the hang-ups were noticed and their sequences released
+    deadline = time.time() + 20
+    while time.time() < deadline:
+        st, text = call(port, "GET", "/metrics", raw=True)
+        vals = {ln.split("{")[0]: float(ln.split()[-1]) for ln in text.splitlines()
+                if ln.startswith(("vllm:num_requests_running", "vllm:num_requests_waiting", "vllm:kv_cache_usage_perc"))}
+        if vals.get("vllm:num_requests_running") == 0 and vals.get("vllm:num_requests_waiting") == 0 and vals.get("vllm:kv_cache_usage_perc") == 0:
+            break
+        time.sleep(0.2)
+    assert vals.get("vllm:num_requests_running") == 0 and vals.get("vllm:num_requests_waiting") == 0, vals
+    assert vals.get("vllm:kv_cache_usage_perc") == 0, vals
+    # and the server still answers
+    st, j = call(port, "POST", "/v1/completions", {"model": MODEL_ID, "prompt": "Who are you?", "max_tokens": 3})
+    assert st == 200 and j["usage"]["completion_tokens"] == 3
+
+
 # ---- with a tokenizer.json next to the weights (what the reference's model download provides) ---------
 @pytest.fixture(scope="module")
 def server_bpe(tmp_path_factory):
