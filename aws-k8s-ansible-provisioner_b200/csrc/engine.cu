@@ -276,6 +276,19 @@ ActIn linear(b2_engine* e, int cls, XBuf xb, const bf16* xptr, const bf16* w, co
   a.prefetch = pf;
   a.small_smem = (after_attention && e->o_small_smem) ? 1 : 0;
   int ns = tc_pick_nsplit(T, N, K, e->num_sms);
+  {  // experiments: B2_NS_<class index>=n forces the split factor of one projection class
+    static int forced[B2_NUM_KERNEL_CLASSES];
+    static bool init = false;
+    if (!init) {
+      for (int i = 0; i < B2_NUM_KERNEL_CLASSES; ++i) {
+        char name[32];
+        snprintf(name, sizeof name, "B2_NS_%d", i);
+        forced[i] = env_int(name, 0);
+      }
+      init = true;
+    }
+    if (cls >= 0 && cls < B2_NUM_KERNEL_CLASSES && forced[cls] > 0) ns = std::min(forced[cls], K / 64);
+  }
   while (ns > 1 && (size_t)ns * T * N > e->partial_floats) --ns;
   if (ns > 1) {  // re-validate (every split non-empty)
     const int kb = K / 64, kps = (kb + ns - 1) / ns;
