@@ -311,7 +311,7 @@ def run_b200(args, rank, world, local, dist):
     # scaled by its own traffic/algorithmic ratio, which is what the figure is for)
     traffic = None
     try:
-        with open(os.path.join(ROOT, "profiles", "r01_b_attn_traffic.json")) as f:
+        with open(os.path.join(ROOT, "profiles", "r01_c_attn_traffic.json")) as f:
             tj = json.load(f)
         traffic = attn_bytes * (tj["dram_bytes_read"] + tj["dram_bytes_write"]) / tj["algorithmic_bytes"]
     except (OSError, KeyError, ValueError):
