@@ -183,7 +183,7 @@ struct b2_engine {
   int o_small_smem = 0;                   // B2_O_SMALL=1: O projection with a short stage ring so that it is resident beside
                                           // attention's CTAs (measured slower: 1.869 vs 1.832 ms/step at C2 -- its weight
                                           // prefetch competes with the tail of the K/V stream)
-  int use_chain = 0;              // B2_CHAIN=1: decode through the persistent chain kernel (chain.cu; measured slower, kept for A/B runs)  // B2_SKIP_MASK: kernel classes left out (timing ablations only; results are garbage)
+  int use_chain = 0;  // B2_CHAIN: 0 separate kernels (default, fastest measured), 1 chain.cu, 2 chain_cluster.cu
 };
 
 namespace {
