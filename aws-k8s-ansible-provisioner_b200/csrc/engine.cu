@@ -671,7 +671,7 @@ __global__ void publish_tokens_kernel(const int32_t* __restrict__ out_tokens, in
     if (st < log_cap_steps) log[(size_t)st * stride + b] = out_tokens[b];
   }
   __syncthreads();
-  if (threadIdx.x == 0) *step = st + 1;
+  if (threadIdx.x == 0) *step = st < 0x7fffffff ? st + 1 : st;  // saturates: a server steps for weeks without b2_decode_run resetting it
 }
 
 // decode step body recorded into a graph (or run eagerly): bookkeeping, forward, token feedback
