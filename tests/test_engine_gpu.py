@@ -454,3 +454,40 @@ def test_sharded_checkpoint_and_dtypes(P, tiny, tmp_path):
         outs.append(np.concatenate([first[None, :], toks], axis=0))
         e.close()
     assert np.array_equal(outs[0], outs[1])
+
+
+def test_full_c2_shape_against_hf(P, full):
+    """The bench workload's shape (BASELINE.json config 2: batch 64, 512-token random prompts, paged KV, CUDA-graph
+    decode with device-side token feedback) against HF itself: four of the 64 sequences are also generated by HF
+    transformers on the CPU; their greedy ids must match up to the first step where HF's own top-2 logit gap is within
+    bf16 noise, and most must match over the whole window."""
+    model, sd = full
+    arch = QWEN3_0_6B
+    B, PL, NEW = 64, 512, 24
+    prompts = make_prompts(B, PL, arch.vocab, seed=1)
+    e = make_engine(P, arch, sd, max_model_len=PL + NEW + 16, num_blocks=B * ((PL + NEW + 31) // 16) + 8, max_seqs=B,
+                    max_batch_tokens=8192, use_cuda_graphs=True)
+    sids = [e.seq_create(PL + NEW + 8) for _ in range(B)]
+    first = np.concatenate([e.prefill(sids[i:i + 16], [p.tolist() for p in prompts[i:i + 16]]) for i in range(0, B, 16)])
+    toks, _ = e.decode_run(sids, NEW - 1)
+    got = np.concatenate([first[None, :], toks], axis=0).T  # [B][NEW]
+    pick = [0, 21, 42, 63]
+    ids = prompts[pick]
+    with torch.no_grad():
+        out = model.generate(ids, attention_mask=torch.ones_like(ids), do_sample=False, max_new_tokens=NEW, min_new_tokens=NEW,
+                             pad_token_id=0, output_logits=True, return_dict_in_generate=True)
+    ref = out.sequences[:, PL:].numpy()
+    logits = torch.stack(out.logits, dim=1).float()  # [4][NEW][V]
+    gaps = top2_gap(logits)
+    full_match = 0
+    for k, b in enumerate(pick):
+        mism = np.nonzero(got[b] != ref[k])[0]
+        n = NEW if len(mism) == 0 else int(mism[0])
+        print("C2 sequence %d: %d/%d leading greedy tokens identical to HF" % (b, n, NEW))
+        if len(mism):
+            assert gaps[k, n] <= 0.0625, "sequence %d diverges at step %d where HF's top-2 gap is %.4f" % (b, n, gaps[k, n])
+        else:
+            full_match += 1
+        assert n >= 4
+    assert full_match >= 2
+    e.close()
