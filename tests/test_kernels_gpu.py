@@ -129,6 +129,39 @@ def test_qknorm_rope_kv(lib, f32in):
             assert not kp_c[sl // bs, :, sl % bs, :].any(), "stray K write at slot %d" % sl
 
 
+def test_qknorm_rope_kv_prefill_sized(lib):
+    """Prefill-sized token counts take a different kernel (four heads per warp): it must agree BIT FOR BIT with the
+    one-head-per-warp kernel on the same inputs (same arithmetic, same rounding points), pages included."""
+    a = QWEN3_0_6B
+    nq, nkv, hd, bs = a.num_q_heads, a.num_kv_heads, a.head_dim, 16
+    T = 1100  # 1100 x 32 heads >= 32768: the prefill variant
+    nblocks = (T + bs - 1) // bs + 2
+    g = torch.Generator().manual_seed(16)
+    qkv = bf(T, (nq + 2 * nkv) * hd, seed=15)
+    qw = (1 + 0.25 * torch.randn(hd, generator=g)).to(torch.bfloat16)
+    kw = (1 + 0.25 * torch.randn(hd, generator=g)).to(torch.bfloat16)
+    positions = torch.randint(0, 4000, (T,), generator=g, dtype=torch.int32)
+    slots = torch.randperm(nblocks * bs, generator=g)[:T].to(torch.int32)
+    slots[7] = -1
+    cos, sin = rope_cos_sin(a, torch.arange(4096)[None, :])
+    table = torch.cat([cos[0, :, :64], sin[0, :, :64]], dim=-1).contiguous()
+    src, dqw, dkw, dtab, dpos, dsl = qkv.cuda(), dv(qw), dv(kw), dv(table), dv(positions), dv(slots)
+    outs = []
+    for whole in (True, False):  # whole batch through the prefill kernel, then in slices small enough for the other one
+        kp = torch.zeros(nblocks, nkv, bs, hd, dtype=torch.bfloat16, device="cuda")
+        vp = torch.zeros_like(kp)
+        q_out = torch.zeros(T, nq * hd, dtype=torch.bfloat16, device="cuda")
+        spans = [(0, T)] if whole else [(i, min(T, i + 500)) for i in range(0, T, 500)]
+        for (i0, i1) in spans:
+            rc = lib.b2k_qknorm_rope_kv(ptr(src[i0:i1]), 0, 1, ptr(dqw), ptr(dkw), ptr(dtab), ptr(dpos[i0:i1]), ptr(dsl[i0:i1]),
+                                        ptr(q_out[i0:i1]), ptr(kp), ptr(vp), i1 - i0, nq, nkv, hd, bs, 1e-6, cuda_stream_ptr())
+            chk(lib, rc)
+        torch.cuda.synchronize()
+        outs.append((q_out.cpu(), kp.cpu(), vp.cpu()))
+    for x, y, what in zip(outs[0], outs[1], ("q", "k pages", "v pages")):
+        assert torch.equal(x, y), "prefill-sized kernel differs from the per-head kernel in " + what
+
+
 @pytest.mark.parametrize("f32in", [False, True])
 def test_silu_mul(lib, f32in):
     T, I = 23, 3072
