@@ -176,6 +176,8 @@ struct b2_engine {
   long long kv_l2_budget = 0;      // B2_KV_L2_MB: bytes of next-layer K/V the projections prefetch into L2 (0 = off)
   int32_t* d_pf_frac = nullptr;
   int32_t* d_sample_out = nullptr;
+  SampleRow* d_sample_rows = nullptr;     // per-row sampling parameters of one b2_sample(_rows) call
+  std::vector<SampleRow> h_sample_rows;
   unsigned long long* d_gbar = nullptr;  // grid-barrier arrival counter of the decode chain kernel
   float* d_ss = nullptr;                  // fused chain: 2 x [32][64] sums of squares
   unsigned long long* d_gbar2 = nullptr;  // fused chain: its grid-barrier counter
@@ -1248,6 +1250,7 @@ extern "C" int b2_engine_create(const b2_config* cfg, const char* safetensors_pa
     E_TRY(dalloc(&e->d_step, (size_t)1));
     E_TRY(dalloc(&e->d_pf_frac, (size_t)1));
     E_TRY(dalloc(&e->d_sample_out, Bcap));
+    E_TRY(dalloc(&e->d_sample_rows, Bcap));
     E_TRY(dalloc(&e->d_gbar, (size_t)1));
     E_CUDA(cudaMemset(e->d_gbar, 0, 8));
     E_TRY(dalloc(&e->d_gbar2, (size_t)1));
@@ -1357,7 +1360,7 @@ extern "C" void b2_engine_free(b2_engine* e) {
   }
   F(e->kv_pool); F(e->h); F(e->x); F(e->qkv); F(e->qrot); F(e->attn); F(e->gu); F(e->act); F(e->proj); F(e->xlast);
   F(e->partial); F(e->attn_scratch); F(e->d_tokens); F(e->d_positions); F(e->d_seq_lens); F(e->d_slots);
-  F(e->d_block_table); F(e->d_last_rows); F(e->d_out_tokens); F(e->d_token_log); F(e->d_step); F(e->d_argmax); F(e->d_pf_frac); F(e->d_sample_out); F(e->d_gbar); F(e->d_gbar2); F(e->d_ss);
+  F(e->d_block_table); F(e->d_last_rows); F(e->d_out_tokens); F(e->d_token_log); F(e->d_step); F(e->d_argmax); F(e->d_pf_frac); F(e->d_sample_out); F(e->d_sample_rows); F(e->d_gbar); F(e->d_gbar2); F(e->d_ss);
   F(e->d_tiles); F(e->dbg_hidden); F(e->logits);
   if (e->h_stage) cudaFreeHost(e->h_stage);
   if (e->h_tiles) cudaFreeHost(e->h_tiles);
@@ -1757,12 +1760,10 @@ extern "C" int b2_sample(b2_engine* e, int32_t nseq, const b2_sampling* params, 
   B2_REQUIRE((e->debug_flags & 2) && e->logits, "b2_sample: logits capture not enabled (b2_set_debug(e, 2))");
   B2_REQUIRE(nseq >= 1 && nseq <= e->last_n, "b2_sample: nseq %d > sequences of the last forward (%d)", nseq, e->last_n);
   B2_CUDA_OK(cudaSetDevice(e->device));
-  if (params->temperature <= 0.f) {
-    B2_TRY(launch_argmax_rows(e->logits, e->d_out_tokens, nseq, e->cfg.vocab, e->stream));
-  } else {
-    B2_TRY(launch_sample(e->logits, e->d_out_tokens, nseq, e->cfg.vocab, params->temperature, params->top_k, params->top_p,
-                         params->seed, (uint64_t)e->launches, e->stream));
-  }
+  e->h_sample_rows.resize(nseq);
+  for (int i = 0; i < nseq; ++i) e->h_sample_rows[i] = SampleRow{i, params->temperature, params->top_k, params->top_p, params->seed};
+  B2_TRY(launch_sample_rows(e->logits, e->h_sample_rows.data(), e->d_sample_rows, e->d_out_tokens, nseq, e->cfg.vocab, (uint64_t)e->launches,
+                            e->stream));
   e->launches++;
   B2_CUDA_OK(cudaMemcpyAsync(e->h_out, e->d_out_tokens, nseq * 4, cudaMemcpyDeviceToHost, e->stream));
   B2_CUDA_OK(cudaStreamSynchronize(e->stream));
@@ -1775,16 +1776,15 @@ extern "C" int b2_sample_rows(b2_engine* e, int32_t nrows, const int32_t* rows, 
   B2_REQUIRE((e->debug_flags & 2) && e->logits, "b2_sample_rows: logits capture not enabled (b2_set_debug(e, 2))");
   B2_REQUIRE(nrows <= e->cfg.max_seqs, "b2_sample_rows: too many rows");
   B2_CUDA_OK(cudaSetDevice(e->device));
+  e->h_sample_rows.resize(nrows);
   for (int i = 0; i < nrows; ++i) {
     B2_REQUIRE(rows[i] >= 0 && rows[i] < e->last_n, "b2_sample_rows: row %d outside the last forward (%d rows)", rows[i], e->last_n);
-    const bf16* lg = e->logits + (size_t)rows[i] * e->cfg.vocab;
-    if (params[i].temperature <= 0.f)
-      B2_TRY(launch_argmax_rows(lg, e->d_sample_out + i, 1, e->cfg.vocab, e->stream));
-    else
-      B2_TRY(launch_sample(lg, e->d_sample_out + i, 1, e->cfg.vocab, params[i].temperature, params[i].top_k, params[i].top_p,
-                           params[i].seed, (uint64_t)e->launches, e->stream));
-    e->launches++;
+    e->h_sample_rows[i] = SampleRow{rows[i], params[i].temperature, params[i].top_k, params[i].top_p, params[i].seed};
   }
+  // one launch for all rows (the host vector outlives the copy: the call synchronises below)
+  B2_TRY(launch_sample_rows(e->logits, e->h_sample_rows.data(), e->d_sample_rows, e->d_sample_out, nrows, e->cfg.vocab, (uint64_t)e->launches,
+                            e->stream));
+  e->launches++;
   B2_CUDA_OK(cudaMemcpyAsync(e->h_out, e->d_sample_out, nrows * 4, cudaMemcpyDeviceToHost, e->stream));
   B2_CUDA_OK(cudaStreamSynchronize(e->stream));
   memcpy(out_tokens, e->h_out, nrows * 4);

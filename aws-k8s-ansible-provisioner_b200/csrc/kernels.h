@@ -152,8 +152,15 @@ int launch_attn_prefill(const bf16* q, const bf16* k_pages, const bf16* v_pages,
                         int block_size, cudaStream_t s, float softmax_scale = 0.f, int window = 0);
 
 // ---- sampling.cu ----
-int launch_sample(const bf16* logits, int32_t* out, int nseq, int V, float temperature, int top_k, float top_p, uint64_t seed,
-                  uint64_t step, cudaStream_t s);
+struct SampleRow {  // one row to draw from (temperature <= 0: greedy arg-max, lowest index on ties)
+  int row;
+  float temperature;
+  int top_k;
+  float top_p;
+  unsigned long long seed;
+};
+int launch_sample_rows(const bf16* logits, const SampleRow* rows_host, SampleRow* stage_dev, int32_t* out, int nrows, int V, uint64_t step,
+                       cudaStream_t s);
 
 int device_num_sms();
 

@@ -4,6 +4,7 @@ import http.client, json, os, random, subprocess, sys, threading, time
 R = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 EXE = os.path.join(R, "aws-k8s-ansible-provisioner_b200", "b2serve")
 SECONDS = float(sys.argv[1]) if len(sys.argv) > 1 else 120.0
+SAMPLED = float(sys.argv[2]) if len(sys.argv) > 2 else 0.3  # share of requests with temperature > 0
 proc = subprocess.Popen([EXE, "--load-format", "dummy", "--served-model-name", "Qwen/Qwen3-0.6B", "--port", "0", "--host", "127.0.0.1",
                          "--max-model-len", "2048", "--max-num-seqs", "64", "--eos-token-id", "-1"],
                         stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
@@ -24,7 +25,7 @@ try:
         while time.time() < t_end:
             plen, ntok = r.randint(1, 1500), r.randint(1, 200)
             body = {"model": "Qwen/Qwen3-0.6B", "prompt": [r.randrange(0, 151936) for _ in range(plen)], "max_tokens": ntok,
-                    "temperature": 0 if r.random() < 0.7 else 0.8, "top_p": 0.9, "ignore_eos": True}
+                    "temperature": 0.8 if r.random() < SAMPLED else 0, "top_p": 0.9, "ignore_eos": True}
             c = http.client.HTTPConnection("127.0.0.1", port, timeout=300)
             c.request("POST", "/v1/completions", json.dumps(body), {"Content-Type": "application/json"})
             resp = c.getresponse(); j = json.loads(resp.read()); c.close()
