@@ -88,7 +88,8 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) {
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
-bool b2_pdl_enabled();
+bool b2_pdl_enabled();     // consumes a pending b2_pdl_skip_next()
+void b2_pdl_skip_next();   // the calling thread's next launch is an ordinary (fully serialised) one
 int b2_pdl_early_mask();  // B2_PDL_EARLY bitmask (diagnostics): 1 attention streams before its wait, 2 norm, 4 rope
 // Function attributes (opt-in shared memory size) are per device: remember which devices were set.
 struct B2PerDeviceOnce {

@@ -36,7 +36,15 @@ int b2_pdl_early_mask() {
   }
   return v;
 }
+// The next launch of this thread goes out WITHOUT the programmatic attribute (the first kernel after a cross-stream
+// fork or join: its predecessors are ordinary full dependencies).
+static thread_local int g_pdl_skip_next = 0;
+void b2_pdl_skip_next() { g_pdl_skip_next = 1; }
 bool b2_pdl_enabled() {
+  if (g_pdl_skip_next) {
+    g_pdl_skip_next = 0;
+    return false;
+  }
   static int v = -1;
   if (v < 0) {
     const char* e = getenv("B2_PDL");
@@ -71,6 +79,19 @@ struct Seq {
 enum XBuf { XB_X = 0, XB_ATTN = 1, XB_ACT = 2, XB_LAST = 3, XB_COUNT = 4 };
 static const int kBnList[5] = {16, 32, 64, 128, 256};
 static int bn_index(int bn) { return bn == 16 ? 0 : bn == 32 ? 1 : bn == 64 ? 2 : bn == 128 ? 3 : 4; }
+
+// One stream of dependent launches over a contiguous block of batch rows.  A forward normally has a single lane
+// (all rows, the engine's stream); a decode step over a large enough batch runs as TWO lanes -- two half-batches on
+// two streams inside one step / one captured graph (see forward()).
+struct Lane {
+  cudaStream_t stream = nullptr;
+  int row0 = 0;                 // first batch row of the lane
+  float* partial = nullptr;     // split-K partials of this lane's projections
+  size_t partial_floats = 0;
+  float* attn_scratch = nullptr;
+  bool beside_attention = false;  // projections use the short stage ring so their CTAs fit on an SM next to a
+                                  // decode-attention CTA of the OTHER lane
+};
 
 struct GraphKey {
   int B, attn_split;
@@ -186,6 +207,14 @@ struct b2_engine {
                                           // attention's CTAs (measured slower: 1.869 vs 1.832 ms/step at C2 -- its weight
                                           // prefetch competes with the tail of the K/V stream)
   int use_chain = 0;  // B2_CHAIN: 0 separate kernels (default, fastest measured), 1 chain.cu, 2 chain_cluster.cu
+
+  // two-lane decode (B2_MB, see forward()): second stream, its own partials and attention scratch, fork/join events
+  int mb_min_batch = 0;  // padded decode batches of at least this many rows (and at most 128) run as two lanes; 0 = never
+  cudaStream_t stream2 = nullptr;
+  float* partial2 = nullptr;
+  size_t partial2_floats = 0;
+  float* attn_scratch2 = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
 };
 
 namespace {
@@ -221,7 +250,7 @@ struct KL {
   KL(b2_engine* e_, int cls_) : e(e_), cls(cls_) {
     if (skip()) return;
     e->launches++;
-    if (e->profiling && e->ev_next + 2 <= (int)e->ev_pool.size()) {
+    if (e->profiling && e->ev_next + 2 <= (int)e->ev_pool.size()) {  // profiled steps are single-lane: the engine's stream
       ev = e->ev_next;
       e->ev_next += 2;
       cudaEventRecord(e->ev_pool[ev], e->stream);
@@ -250,12 +279,15 @@ int pick_attn_split(b2_engine* e, int B, int max_len) {
 }
 
 // ---- one Linear layer: picks SIMT GEMV or the tcgen05 kernel, bf16 or split-K partial output
-ActIn linear(b2_engine* e, int cls, XBuf xb, const bf16* xptr, const bf16* w, const CUtensorMap& tm_w, bf16* out_bf16, int T,
-             int N, int K, int* rc, const KvPrefetch& pf = KvPrefetch(), bool want_f32 = false, bool after_attention = false) {
+// xptr / out_bf16 are already offset to the lane's first row; the X tensor map covers the whole buffer, so the
+// tcgen05 kernel gets the lane's row offset as a coordinate.
+ActIn linear(b2_engine* e, const Lane& ln, int cls, XBuf xb, const bf16* xptr, const bf16* w, const CUtensorMap& tm_w, bf16* out_bf16,
+             int T, int N, int K, int* rc, const KvPrefetch& pf = KvPrefetch(), bool want_f32 = false, bool after_attention = false) {
   // want_f32: hand the consumer fp32 sums even when K is not split (a bias is added before the rounding)
   *rc = 0;
   int impl = e->force_gemm_impl >= 0 ? e->force_gemm_impl : (T <= e->simt_max_tokens ? 0 : 1);
-  if (want_f32 && (size_t)T * N > e->partial_floats) {
+  if (ln.beside_attention && impl == 1 && tc_pick_bn(T) <= 64) want_f32 = true;  // the short ring is built for the partial epilogue
+  if (want_f32 && (size_t)T * N > ln.partial_floats) {
     b2_set_error("linear: %d x %d fp32 outputs exceed the partial buffer", T, N);
     *rc = -12;
     return act_bf16(nullptr);
@@ -263,10 +295,10 @@ ActIn linear(b2_engine* e, int cls, XBuf xb, const bf16* xptr, const bf16* w, co
   if (impl == 0) {
     KL k(e, cls);
     if (want_f32) {
-      if (!k.skip()) *rc = launch_linear_simt(xptr, w, e->partial, 1, T, N, K, e->stream);
-      return act_f32(e->partial, 1);
+      if (!k.skip()) *rc = launch_linear_simt(xptr, w, ln.partial, 1, T, N, K, ln.stream);
+      return act_f32(ln.partial, 1);
     }
-    if (!k.skip()) *rc = launch_linear_simt(xptr, w, out_bf16, 0, T, N, K, e->stream);
+    if (!k.skip()) *rc = launch_linear_simt(xptr, w, out_bf16, 0, T, N, K, ln.stream);
     return act_bf16(out_bf16);
   }
   TcGemmArgs a;
@@ -276,7 +308,8 @@ ActIn linear(b2_engine* e, int cls, XBuf xb, const bf16* xptr, const bf16* w, co
   a.T = T; a.N = N; a.K = K;
   a.argmax_packed = nullptr;
   a.prefetch = pf;
-  a.small_smem = (after_attention && e->o_small_smem) ? 1 : 0;
+  a.x_row0 = ln.row0;
+  a.small_smem = ((after_attention && e->o_small_smem) || ln.beside_attention) ? 1 : 0;
   int ns = tc_pick_nsplit(T, N, K, e->num_sms);
   {  // experiments: B2_NS_<class index>=n forces the split factor of one projection class
     static int forced[B2_NUM_KERNEL_CLASSES];
@@ -291,7 +324,7 @@ ActIn linear(b2_engine* e, int cls, XBuf xb, const bf16* xptr, const bf16* w, co
     }
     if (cls >= 0 && cls < B2_NUM_KERNEL_CLASSES && forced[cls] > 0) ns = std::min(forced[cls], K / 64);
   }
-  while (ns > 1 && (size_t)ns * T * N > e->partial_floats) --ns;
+  while (ns > 1 && (size_t)ns * T * N > ln.partial_floats) --ns;
   if (ns > 1) {  // re-validate (every split non-empty)
     const int kb = K / 64, kps = (kb + ns - 1) / ns;
     ns = (kb + kps - 1) / kps;
@@ -301,13 +334,23 @@ ActIn linear(b2_engine* e, int cls, XBuf xb, const bf16* xptr, const bf16* w, co
   if (ns == 1 && !want_f32) {
     a.epilogue = TC_EPI_BF16;
     a.out = out_bf16;
-    if (!k.skip()) *rc = launch_linear_tc(a, e->stream);
+    if (!k.skip()) *rc = launch_linear_tc(a, ln.stream);
     return act_bf16(out_bf16);
   }
   a.epilogue = TC_EPI_F32_PARTIAL;
-  a.out = e->partial;
-  if (!k.skip()) *rc = launch_linear_tc(a, e->stream);
-  return act_f32(e->partial, ns);
+  a.out = ln.partial;
+  if (!k.skip()) *rc = launch_linear_tc(a, ln.stream);
+  return act_f32(ln.partial, ns);
+}
+
+Lane whole_batch_lane(b2_engine* e) {
+  Lane ln;
+  ln.stream = e->stream;
+  ln.row0 = 0;
+  ln.partial = e->partial;
+  ln.partial_floats = e->partial_floats;
+  ln.attn_scratch = e->attn_scratch;
+  return ln;
 }
 
 void dbg_capture(b2_engine* e, int slot, const bf16* src, int T) {
@@ -413,7 +456,7 @@ int forward_decode_fused(b2_engine* e, int T) {
     LayerW& L0 = e->layers[0];
     bf16* kp = e->kv_pool;
     bf16* vp = kp + e->layer_kv_elems;
-    ActIn qkv = linear(e, B2K_GEMM_QKV, XB_X, e->x, L0.wqkv, L0.tm_qkv, e->qkv, T, e->qkv_size, H, &rc);
+    ActIn qkv = linear(e, whole_batch_lane(e), B2K_GEMM_QKV, XB_X, e->x, L0.wqkv, L0.tm_qkv, e->qkv, T, e->qkv_size, H, &rc);
     B2_TRY(rc);
     KL k(e, B2K_ROPE_KV);
     if (!k.skip()) B2_TRY(launch_qknorm_rope_kv(qkv, L0.qnorm, L0.knorm, e->cos_sin, e->d_positions, e->d_slots, e->qrot, kp, vp, T,
@@ -463,6 +506,7 @@ int forward_opt(b2_engine* e, int T, int ntiles, int nlast) {
   const b2_config& c = e->cfg;
   const int H = c.hidden, I = c.intermediate;
   int rc = 0;
+  const Lane ln = whole_batch_lane(e);
   {
     KL k(e, B2K_EMBED);
     if (!k.skip()) B2_TRY(launch_embed_pos(e->d_tokens, e->d_positions, e->embed, e->pos_embed, e->h, T, H, c.vocab, e->pos_rows,
@@ -480,7 +524,7 @@ int forward_opt(b2_engine* e, int T, int ntiles, int nlast) {
       if (!k.skip()) B2_TRY(launch_add_layernorm(e->h, delta, delta_bias, L.ln1, L.ln1_b, e->x, T, H, c.rms_eps, e->stream));
     }
     if (l > 0) dbg_capture(e, l, e->h, T);
-    ActIn qkv = linear(e, B2K_GEMM_QKV, XB_X, e->x, L.wqkv, L.tm_qkv, e->qkv, T, e->qkv_size, H, &rc, KvPrefetch(), true);
+    ActIn qkv = linear(e, ln, B2K_GEMM_QKV, XB_X, e->x, L.wqkv, L.tm_qkv, e->qkv, T, e->qkv_size, H, &rc, KvPrefetch(), true);
     B2_TRY(rc);
     {
       // HF:...:151 "query_states = self.q_proj(hidden_states) * self.scaling", then attention with scaling 1.0
@@ -498,19 +542,19 @@ int forward_opt(b2_engine* e, int T, int ntiles, int nlast) {
         B2_TRY(launch_attn_decode(e->qrot, kp, vp, e->d_block_table, e->bt_stride, e->d_seq_lens, e->attn_scratch, e->attn, T,
                                   e->nq, e->nkv, e->hd, c.block_size, e->stream, 1.0f));
     }
-    ActIn o = linear(e, B2K_GEMM_O, XB_ATTN, e->attn, L.wo, L.tm_o, e->proj, T, H, e->q_size, &rc, KvPrefetch(), true);
+    ActIn o = linear(e, ln, B2K_GEMM_O, XB_ATTN, e->attn, L.wo, L.tm_o, e->proj, T, H, e->q_size, &rc, KvPrefetch(), true);
     B2_TRY(rc);
     {
       KL k(e, B2K_NORM);
       if (!k.skip()) B2_TRY(launch_add_layernorm(e->h, o, L.bo, L.ln2, L.ln2_b, e->x, T, H, c.rms_eps, e->stream));
     }
-    ActIn f1 = linear(e, B2K_GEMM_GATEUP, XB_X, e->x, L.wgu, L.tm_gu, e->gu, T, I, H, &rc, KvPrefetch(), true);
+    ActIn f1 = linear(e, ln, B2K_GEMM_GATEUP, XB_X, e->x, L.wgu, L.tm_gu, e->gu, T, I, H, &rc, KvPrefetch(), true);
     B2_TRY(rc);
     {
       KL k(e, B2K_ACT);
       if (!k.skip()) B2_TRY(launch_bias_relu(f1, L.b1, e->act, T, I, e->stream));
     }
-    delta = linear(e, B2K_GEMM_DOWN, XB_ACT, e->act, L.wd, L.tm_d, e->proj, T, H, I, &rc, KvPrefetch(), true);
+    delta = linear(e, ln, B2K_GEMM_DOWN, XB_ACT, e->act, L.wd, L.tm_d, e->proj, T, H, I, &rc, KvPrefetch(), true);
     delta_bias = L.b2;
     B2_TRY(rc);
   }
@@ -531,21 +575,26 @@ int forward_opt(b2_engine* e, int T, int ntiles, int nlast) {
   return lm_head_and_argmax(e, nlast, xl, xb);
 }
 
-int forward(b2_engine* e, int T, int ntiles, int nlast, int attn_split) {
+// The decoder layers and the final norm over the lane's rows [row0, row0 + T): everything between the embedding and
+// the lm_head.  Qwen3 / Phi-3 (HF:models/qwen3/modeling_qwen3.py:423-434).
+int forward_layers(b2_engine* e, const Lane& ln, int T, int ntiles) {
   const b2_config& c = e->cfg;
   const int H = c.hidden, I = c.intermediate;
+  const size_t r0 = (size_t)ln.row0;
+  cudaStream_t st = ln.stream;
+  bf16* h = e->h + r0 * H;
+  bf16* x = e->x + r0 * H;
+  bf16* qkvb = e->qkv + r0 * e->qkv_size;
+  bf16* qrot = e->qrot + r0 * e->q_size;
+  bf16* attn = e->attn + r0 * e->q_size;
+  bf16* gub = e->gu + r0 * 2 * I;
+  bf16* act = e->act + r0 * I;
+  bf16* proj = e->proj + r0 * H;
+  const int32_t* positions = e->d_positions + r0;
+  const int32_t* slots = e->d_slots + r0;
+  const int32_t* block_table = e->d_block_table + r0 * e->bt_stride;
+  const int32_t* seq_lens = e->d_seq_lens + r0;
   int rc = 0;
-  if (c.arch == B2_ARCH_OPT) return forward_opt(e, T, ntiles, nlast);
-  if (ntiles == 0 && e->use_chain == 2 && e->fused_ok && c.arch == B2_ARCH_QWEN3 && !(e->debug_flags & 1) &&
-      e->force_gemm_impl != 0 && T > e->simt_max_tokens && T <= 64 && e->skip_mask == 0)
-    return forward_decode_fused(e, T);
-  if (ntiles == 0 && e->use_chain == 1 && c.arch == B2_ARCH_QWEN3 && !(e->debug_flags & 1) && e->force_gemm_impl != 0 && T > e->simt_max_tokens)
-    return forward_decode_chain(e, T);
-  {
-    KL k(e, B2K_EMBED);
-    if (!k.skip()) B2_TRY(launch_embed(e->d_tokens, e->embed, e->h, T, H, c.vocab, e->d_argmax, nlast, e->stream));
-  }
-  dbg_capture(e, 0, e->h, T);
   ActIn delta = act_bf16(nullptr);
   // decode only: the projections of layer l prefetch shares of the K/V pages the next attention pass
   // will read (QKV: this layer's own; O, gate-up, down: layer l+1's)
@@ -554,8 +603,8 @@ int forward(b2_engine* e, int T, int ntiles, int nlast, int attn_split) {
     if (ntiles > 0 || e->kv_l2_budget <= 0 || layer >= c.num_layers) return pf;
     pf.k_pages = e->kv_pool + (size_t)(2 * layer) * e->layer_kv_elems;
     pf.v_pages = pf.k_pages + e->layer_kv_elems;
-    pf.block_table = e->d_block_table;
-    pf.seq_lens = e->d_seq_lens;
+    pf.block_table = block_table;
+    pf.seq_lens = seq_lens;
     pf.frac_q16 = e->d_pf_frac;
     pf.bt_stride = e->bt_stride;
     pf.B = T;
@@ -570,45 +619,103 @@ int forward(b2_engine* e, int T, int ntiles, int nlast, int attn_split) {
     bf16* vp = kp + e->layer_kv_elems;
     {
       KL k(e, B2K_NORM);
-      if (!k.skip()) B2_TRY(launch_add_rmsnorm(e->h, delta, L.ln1, e->x, T, H, c.rms_eps, e->stream));
+      if (!k.skip()) B2_TRY(launch_add_rmsnorm(h, delta, L.ln1, x, T, H, c.rms_eps, st));
     }
     if (l > 0) dbg_capture(e, l, e->h, T);
-    ActIn qkv = linear(e, B2K_GEMM_QKV, XB_X, e->x, L.wqkv, L.tm_qkv, e->qkv, T, e->qkv_size, H, &rc, prefetch_for(l, 3));
+    ActIn qkv = linear(e, ln, B2K_GEMM_QKV, XB_X, x, L.wqkv, L.tm_qkv, qkvb, T, e->qkv_size, H, &rc, prefetch_for(l, 3));
     B2_TRY(rc);
     {
       KL k(e, B2K_ROPE_KV);
-      if (!k.skip()) B2_TRY(launch_qknorm_rope_kv(qkv, L.qnorm, L.knorm, e->cos_sin, e->d_positions, e->d_slots, e->qrot, kp, vp, T,
-                                   e->nq, e->nkv, e->hd, c.block_size, c.rms_eps, e->stream, e->rotary_dim));
+      if (!k.skip()) B2_TRY(launch_qknorm_rope_kv(qkv, L.qnorm, L.knorm, e->cos_sin, positions, slots, qrot, kp, vp, T,
+                                   e->nq, e->nkv, e->hd, c.block_size, c.rms_eps, st, e->rotary_dim));
     }
     if (ntiles > 0) {
       KL k(e, B2K_MISC);
-      if (!k.skip()) B2_TRY(launch_attn_prefill(e->qrot, kp, vp, e->d_block_table, e->bt_stride, e->d_tiles, ntiles, e->attn,
-                                 e->nq, e->nkv, e->hd, c.block_size, e->stream, e->attn_scale, c.sliding_window));
+      if (!k.skip()) B2_TRY(launch_attn_prefill(qrot, kp, vp, block_table, e->bt_stride, e->d_tiles, ntiles, attn,
+                                 e->nq, e->nkv, e->hd, c.block_size, st, e->attn_scale, c.sliding_window));
     } else {
       KL k(e, B2K_ATTN_DECODE);
       if (!k.skip())
-        B2_TRY(launch_attn_decode(e->qrot, kp, vp, e->d_block_table, e->bt_stride, e->d_seq_lens, e->attn_scratch, e->attn, T,
-                                  e->nq, e->nkv, e->hd, c.block_size, e->stream, e->attn_scale, c.sliding_window));
+        B2_TRY(launch_attn_decode(qrot, kp, vp, block_table, e->bt_stride, seq_lens, ln.attn_scratch, attn, T,
+                                  e->nq, e->nkv, e->hd, c.block_size, st, e->attn_scale, c.sliding_window));
     }
-    ActIn o = linear(e, B2K_GEMM_O, XB_ATTN, e->attn, L.wo, L.tm_o, e->proj, T, H, e->q_size, &rc, prefetch_for(l + 1, 0), false,
+    ActIn o = linear(e, ln, B2K_GEMM_O, XB_ATTN, attn, L.wo, L.tm_o, proj, T, H, e->q_size, &rc, prefetch_for(l + 1, 0), false,
                      /*after_attention=*/ntiles == 0);
     B2_TRY(rc);
     {
       KL k(e, B2K_NORM);
-      if (!k.skip()) B2_TRY(launch_add_rmsnorm(e->h, o, L.ln2, e->x, T, H, c.rms_eps, e->stream));
+      if (!k.skip()) B2_TRY(launch_add_rmsnorm(h, o, L.ln2, x, T, H, c.rms_eps, st));
     }
-    ActIn gu = linear(e, B2K_GEMM_GATEUP, XB_X, e->x, L.wgu, L.tm_gu, e->gu, T, 2 * I, H, &rc, prefetch_for(l + 1, 1));
+    ActIn gu = linear(e, ln, B2K_GEMM_GATEUP, XB_X, x, L.wgu, L.tm_gu, gub, T, 2 * I, H, &rc, prefetch_for(l + 1, 1));
     B2_TRY(rc);
     {
       KL k(e, B2K_ACT);
-      if (!k.skip()) B2_TRY(launch_silu_mul(gu, e->act, T, I, e->stream));
+      if (!k.skip()) B2_TRY(launch_silu_mul(gu, act, T, I, st));
     }
-    delta = linear(e, B2K_GEMM_DOWN, XB_ACT, e->act, L.wd, L.tm_d, e->proj, T, H, I, &rc, prefetch_for(l + 1, 2));
+    delta = linear(e, ln, B2K_GEMM_DOWN, XB_ACT, act, L.wd, L.tm_d, proj, T, H, I, &rc, prefetch_for(l + 1, 2));
     B2_TRY(rc);
   }
   {
     KL k(e, B2K_NORM);
-    if (!k.skip()) B2_TRY(launch_add_rmsnorm(e->h, delta, e->final_norm, e->x, T, H, c.rms_eps, e->stream));
+    if (!k.skip()) B2_TRY(launch_add_rmsnorm(h, delta, e->final_norm, x, T, H, c.rms_eps, st));
+  }
+  return 0;
+}
+
+// Two-lane decode.  At batch 64 a decode step is two things that do not overlap when they depend on each other: the
+// attention pass of a layer (HBM-bound, about half the step) and the eight small kernels between two attention
+// passes (a chain of dependent launches that moves 31 MB of weights in ~30 us: latency-bound, HBM nearly idle).
+// Sequences are independent, so the batch is cut into two halves that run as two dependent chains on two streams of
+// the same step (and the same captured graph): while one half is in its latency-bound chain the other half streams
+// its K/V pages.  Both attention kernels want every SM (129 KB of shared memory per CTA), so they take turns by
+// themselves and the halves fall into opposite phases; the projections of a lane use the short stage ring (<= 82 KB)
+// so that their CTAs are resident NEXT to the other lane's attention CTAs instead of queueing behind them.  The price
+// is that the weights are streamed once per lane (L2 keeps part of the second pass).
+bool two_lane_decode(const b2_engine* e, int T, int ntiles) {
+  return ntiles == 0 && e->mb_min_batch > 0 && T >= e->mb_min_batch && T <= 128 && T % 2 == 0 && e->stream2 != nullptr &&
+         !e->profiling && !(e->debug_flags & 1) && e->force_gemm_impl != 0 && (T / 2) > e->simt_max_tokens;
+}
+
+int forward(b2_engine* e, int T, int ntiles, int nlast, int attn_split) {
+  const b2_config& c = e->cfg;
+  const int H = c.hidden;
+  (void)attn_split;
+  if (c.arch == B2_ARCH_OPT) return forward_opt(e, T, ntiles, nlast);
+  if (ntiles == 0 && e->use_chain == 2 && e->fused_ok && c.arch == B2_ARCH_QWEN3 && !(e->debug_flags & 1) &&
+      e->force_gemm_impl != 0 && T > e->simt_max_tokens && T <= 64 && e->skip_mask == 0)
+    return forward_decode_fused(e, T);
+  if (ntiles == 0 && e->use_chain == 1 && c.arch == B2_ARCH_QWEN3 && !(e->debug_flags & 1) && e->force_gemm_impl != 0 && T > e->simt_max_tokens)
+    return forward_decode_chain(e, T);
+  {
+    KL k(e, B2K_EMBED);
+    if (!k.skip()) B2_TRY(launch_embed(e->d_tokens, e->embed, e->h, T, H, c.vocab, e->d_argmax, nlast, e->stream));
+  }
+  dbg_capture(e, 0, e->h, T);
+  if (two_lane_decode(e, T, ntiles)) {
+    Lane a = whole_batch_lane(e), b;
+    a.beside_attention = true;
+    b.stream = e->stream2;
+    b.row0 = T / 2;
+    b.partial = e->partial2;
+    b.partial_floats = e->partial2_floats;
+    b.attn_scratch = e->attn_scratch2;
+    b.beside_attention = true;
+    // fork: lane b starts once the embedding is done (a full dependency: no programmatic edge across streams)
+    B2_CUDA_OK(cudaEventRecord(e->ev_fork, e->stream));
+    B2_CUDA_OK(cudaStreamWaitEvent(e->stream2, e->ev_fork, 0));
+    b2_pdl_skip_next();
+    int rc_b = forward_layers(e, b, T - T / 2, 0);
+    int rc_a = forward_layers(e, a, T / 2, 0);
+    // join (always, so that a capture in progress is left with both streams merged)
+    cudaError_t j1 = cudaEventRecord(e->ev_join, e->stream2);
+    cudaError_t j2 = cudaStreamWaitEvent(e->stream, e->ev_join, 0);
+    B2_TRY(rc_a);
+    B2_TRY(rc_b);
+    B2_CUDA_OK(j1);
+    B2_CUDA_OK(j2);
+    b2_pdl_skip_next();  // the lm_head waits for both lanes in full
+  } else {
+    B2_TRY(forward_layers(e, whole_batch_lane(e), T, ntiles));
   }
   dbg_capture(e, c.num_layers, e->h, T);
   dbg_capture(e, c.num_layers + 1, e->x, T);
@@ -670,7 +777,8 @@ __global__ void publish_tokens_kernel(const int32_t* __restrict__ out_tokens, in
   const int st = *step;  // single CTA
   for (int b = threadIdx.x; b < B; b += blockDim.x) {
     next_in[b] = out_tokens[b];
-    if (st < log_cap_steps) log[(size_t)st * stride + b] = out_tokens[b];
+    // the log has `stride` (= max_seqs) columns; B is the padded bucket and may be wider
+    if (st < log_cap_steps && b < stride) log[(size_t)st * stride + b] = out_tokens[b];
   }
   __syncthreads();
   if (threadIdx.x == 0) *step = st < 0x7fffffff ? st + 1 : st;  // saturates: a server steps for weeks without b2_decode_run resetting it
@@ -795,7 +903,9 @@ int check_seq(b2_engine* e, int id) {
 
 int ensure_logits(b2_engine* e) {
   if (e->logits) return 0;
-  return dalloc(&e->logits, (size_t)std::max(e->cfg.max_seqs, 1) * e->cfg.vocab);
+  // rows for the padded graph bucket: a captured step runs the lm_head over bucket_batch(n) rows, and max_seqs need
+  // not be a bucket value (--max-num-seqs is free-form)
+  return dalloc(&e->logits, (size_t)bucket_batch(std::max(e->cfg.max_seqs, 1)) * e->cfg.vocab);
 }
 
 int layer_tensor(b2_engine* e, const std::string& name, const void* host, size_t nbytes) {
@@ -1220,6 +1330,18 @@ extern "C" int b2_engine_create(const b2_config* cfg, const char* safetensors_pa
     e->attn_scratch_floats = attn_decode_scratch_floats(bucket_batch(c.max_seqs), e->nq, e->nkv, e->hd);
     E_TRY(dalloc(&e->attn_scratch, e->attn_scratch_floats));
     E_CUDA(cudaMemset(e->attn_scratch, 0, e->attn_scratch_floats * sizeof(float)));  // arrival counters start at zero
+    // two-lane decode: B2_MB = smallest padded decode batch that is cut into two half-batch lanes (0 = off)
+    e->mb_min_batch = c.arch == B2_ARCH_OPT ? 0 : env_int("B2_MB", 32);
+    if (c.arch != B2_ARCH_OPT && c.max_seqs >= 2) {
+      E_CUDA(cudaStreamCreateWithFlags(&e->stream2, cudaStreamNonBlocking));
+      E_CUDA(cudaEventCreateWithFlags(&e->ev_fork, cudaEventDisableTiming));
+      E_CUDA(cudaEventCreateWithFlags(&e->ev_join, cudaEventDisableTiming));
+      // a lane has at most 64 rows: 8 splits x 64 x the widest projection
+      e->partial2_floats = (size_t)8 * 64 * (size_t)std::max(std::max(e->qkv_size, 2 * I), H);
+      E_TRY(dalloc(&e->partial2, e->partial2_floats));
+      E_TRY(dalloc(&e->attn_scratch2, e->attn_scratch_floats));
+      E_CUDA(cudaMemset(e->attn_scratch2, 0, e->attn_scratch_floats * sizeof(float)));
+    }
     for (int bi = 0; bi < 5; ++bi) {
       E_TRY(b2_make_tmap_bf16(&e->tm_x[XB_X][bi], e->x, Tc, H, H, kBnList[bi]));
       E_TRY(b2_make_tmap_bf16(&e->tm_x[XB_ATTN][bi], e->attn, Tc, e->q_size, e->q_size, kBnList[bi]));
@@ -1367,6 +1489,10 @@ extern "C" void b2_engine_free(b2_engine* e) {
   if (e->h_out) cudaFreeHost(e->h_out);
   if (e->h_tok) cudaFreeHost(e->h_tok);
   if (e->ev_tok) cudaEventDestroy(e->ev_tok);
+  F(e->partial2); F(e->attn_scratch2);
+  if (e->ev_fork) cudaEventDestroy(e->ev_fork);
+  if (e->ev_join) cudaEventDestroy(e->ev_join);
+  if (e->stream2) cudaStreamDestroy(e->stream2);
   if (e->stream) cudaStreamDestroy(e->stream);
   delete e;
 }
@@ -1698,6 +1824,24 @@ extern "C" int b2_attn_profile(b2_engine* e, int32_t nseq, const int32_t* seq_id
 
 extern "C" int64_t b2_launch_count(b2_engine* e) { return e ? e->launches : 0; }
 
+extern "C" int b2_set_tuning(b2_engine* e, int32_t key, int64_t value) {
+  B2_REQUIRE(e, "b2_set_tuning: null engine");
+  B2_CUDA_OK(cudaSetDevice(e->device));
+  B2_CUDA_OK(cudaStreamSynchronize(e->stream));
+  switch (key) {
+    case B2_TUNE_SKIP_MASK: e->skip_mask = (unsigned)value; break;
+    case B2_TUNE_TWO_LANE:
+      B2_REQUIRE(value == 0 || e->stream2 != nullptr, "b2_set_tuning: this engine was created without a second lane (B2_MB=0 or OPT)");
+      e->mb_min_batch = (int)value;
+      break;
+    default: b2_set_error("b2_set_tuning: unknown key %d", key); return -22;
+  }
+  for (auto& kv : e->graphs) cudaGraphExecDestroy(kv.second);  // captured with the old setting
+  e->graphs.clear();
+  e->graph_nodes.clear();
+  return 0;
+}
+
 extern "C" int b2_set_debug(b2_engine* e, int32_t flags) {
   B2_REQUIRE(e, "b2_set_debug: null engine");
   B2_CUDA_OK(cudaSetDevice(e->device));
@@ -1761,7 +1905,12 @@ extern "C" int b2_sample(b2_engine* e, int32_t nseq, const b2_sampling* params, 
   B2_REQUIRE(nseq >= 1 && nseq <= e->last_n, "b2_sample: nseq %d > sequences of the last forward (%d)", nseq, e->last_n);
   B2_CUDA_OK(cudaSetDevice(e->device));
   e->h_sample_rows.resize(nseq);
-  for (int i = 0; i < nseq; ++i) e->h_sample_rows[i] = SampleRow{i, params->temperature, params->top_k, params->top_p, params->seed};
+  for (int i = 0; i < nseq; ++i) {
+    // one seed for the whole batch: row i draws from its own stream derived from (seed, i)
+    unsigned long long sd = params->seed == 0 ? 0ull : (params->seed * 0x9E3779B97F4A7C15ull + (unsigned long long)i);
+    if (params->seed != 0 && sd == 0) sd = 1;
+    e->h_sample_rows[i] = SampleRow{i, params->temperature, params->top_k, params->top_p, sd};
+  }
   B2_TRY(launch_sample_rows(e->logits, e->h_sample_rows.data(), e->d_sample_rows, e->d_out_tokens, nseq, e->cfg.vocab, (uint64_t)e->launches,
                             e->stream));
   e->launches++;

@@ -57,6 +57,7 @@ __device__ __forceinline__ unsigned long long tc_argmax_pack(float v, int idx) {
   return ((unsigned long long)key << 32) | (unsigned long long)(0xffffffffu - (uint32_t)idx);
 }
 
+// x_row0: first row of X this launch reads (a micro-batch of a larger activation buffer; `out` is already offset).
 // Persistent: gridDim.x CTAs walk the (m tile, token tile, k split) work list with stride
 // gridDim.x.  The smem stage ring runs on across tiles, and the accumulator is double buffered
 // in TMEM so the epilogue of tile i overlaps the TMA/MMA main loop of tile i+1.
@@ -64,7 +65,7 @@ template <int BN, int EPI, int SMALL = 0>
 __global__ void __launch_bounds__(192, 1)
 linear_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_x,
                  void* __restrict__ out, unsigned long long* __restrict__ argmax_packed, int T, int N, int K,
-                 int kb_per_split, int m_tiles, int n_tiles, int nsplit, const KvPrefetch pf) {
+                 int kb_per_split, int m_tiles, int n_tiles, int nsplit, const KvPrefetch pf, int x_row0) {
   using C = TcCfg<BN, SMALL>;
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t full_bar[C::STAGES];
@@ -124,7 +125,7 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
             const uint32_t fb = smem_u32(&full_bar[i]);
             mbar_arrive_expect_tx(fb, C::STAGE_BYTES);
             if (kWeightsFirst) tma_load_2d(smem_base + i * C::STAGE_BYTES, &tmap_w, (kb0 + i) * TC_BK, m_tile * TC_BM, fb);
-            else tma_load_2d(smem_base + i * C::STAGE_BYTES + TC_W_BYTES, &tmap_x, (kb0 + i) * TC_BK, n_tile * BN, fb);
+            else tma_load_2d(smem_base + i * C::STAGE_BYTES + TC_W_BYTES, &tmap_x, (kb0 + i) * TC_BK, n_tile * BN + x_row0, fb);
           }
           pdl_wait();
           pdl_launch_dependents();
@@ -132,7 +133,7 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
           waited = true;
           for (int i = 0; i < npre; ++i) {
             const uint32_t fb = smem_u32(&full_bar[i]);
-            if (kWeightsFirst) tma_load_2d(smem_base + i * C::STAGE_BYTES + TC_W_BYTES, &tmap_x, (kb0 + i) * TC_BK, n_tile * BN, fb);
+            if (kWeightsFirst) tma_load_2d(smem_base + i * C::STAGE_BYTES + TC_W_BYTES, &tmap_x, (kb0 + i) * TC_BK, n_tile * BN + x_row0, fb);
             else tma_load_2d(smem_base + i * C::STAGE_BYTES, &tmap_w, (kb0 + i) * TC_BK, m_tile * TC_BM, fb);
           }
           it = npre;
@@ -143,7 +144,7 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
             mbar_arrive_expect_tx(fb, C::STAGE_BYTES);
             const uint32_t ws = smem_base + s * C::STAGE_BYTES;
             tma_load_2d(ws, &tmap_w, kb * TC_BK, m_tile * TC_BM, fb);
-            tma_load_2d(ws + TC_W_BYTES, &tmap_x, kb * TC_BK, n_tile * BN, fb);
+            tma_load_2d(ws + TC_W_BYTES, &tmap_x, kb * TC_BK, n_tile * BN + x_row0, fb);
           }
           continue;
         }
@@ -154,7 +155,7 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
           mbar_arrive_expect_tx(fb, C::STAGE_BYTES);
           const uint32_t ws = smem_base + s * C::STAGE_BYTES;
           tma_load_2d(ws, &tmap_w, kb * TC_BK, m_tile * TC_BM, fb);
-          tma_load_2d(ws + TC_W_BYTES, &tmap_x, kb * TC_BK, n_tile * BN, fb);
+          tma_load_2d(ws + TC_W_BYTES, &tmap_x, kb * TC_BK, n_tile * BN + x_row0, fb);
         }
       }
       if (!waited) {
@@ -452,7 +453,7 @@ static int launch_one(const TcGemmArgs& a, int kb_per_split, cudaStream_t s) {
   static int sms = device_num_sms();
   const int grid = total < sms ? total : sms;
   B2_CUDA_OK(b2_launch(linear_tc_kernel<BN, EPI, SMALL>, dim3(grid), dim3(192), (size_t)C::SMEM_BYTES, s, a.tmap_w, a.tmap_x, a.out,
-                       a.argmax_packed, a.T, a.N, a.K, kb_per_split, m_tiles, n_tiles, a.nsplit, a.prefetch));
+                       a.argmax_packed, a.T, a.N, a.K, kb_per_split, m_tiles, n_tiles, a.nsplit, a.prefetch, a.x_row0));
   return 0;
 }
 
@@ -479,6 +480,8 @@ int launch_linear_tc(const TcGemmArgs& a, cudaStream_t s) {
   B2_REQUIRE((kb_total + kps - 1) / kps == a.nsplit, "linear_tc: nsplit=%d leaves an empty split for %d k-blocks", a.nsplit,
              kb_total);
   B2_REQUIRE(a.nsplit == 1 || a.epilogue == TC_EPI_F32_PARTIAL, "linear_tc: split-K needs the fp32 partial epilogue");
+  B2_REQUIRE(a.x_row0 == 0 || a.epilogue == TC_EPI_BF16 || a.epilogue == TC_EPI_F32_PARTIAL,
+             "linear_tc: a row offset into X is only built for the plain epilogues");
   switch (a.bn) {
     case 16: return launch_bn<16>(a, kps, s);
     case 32: return launch_bn<32>(a, kps, s);

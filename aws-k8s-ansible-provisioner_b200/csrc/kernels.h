@@ -74,6 +74,7 @@ struct TcGemmArgs {
   unsigned long long* argmax_packed;  // [T] for TC_EPI_ARGMAX (must be zeroed before launch)
   KvPrefetch prefetch;                // optional ride-along K/V prefetch
   int small_smem = 0;                 // F32_PARTIAL, bn <= 64: short stage ring so the CTA fits beside a decode-attention CTA
+  int x_row0 = 0;                     // first row of X (tmap_x) this launch reads: a micro-batch of a larger buffer
 };
 int launch_linear_tc(const TcGemmArgs& a, cudaStream_t s);
 int tc_pick_bn(int T);

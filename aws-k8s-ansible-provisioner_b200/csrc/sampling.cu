@@ -67,16 +67,6 @@ sample_rows_kernel(const bf16* __restrict__ logits, const SampleRowDev* __restri
     mx = redf[0];
     for (int k = 1; k < (int)(blockDim.x >> 5); ++k) mx = fmaxf(mx, redf[k]);
     const bool want_p = rp.top_p > 0.f && rp.top_p < 1.f;
-    if (want_p) {
-      z = 0.f;
-      for (int i = threadIdx.x; i < nvec; i += blockDim.x) {
-        float v[8];
-        unpack8(row[i], v);
-#pragma unroll
-        for (int e = 0; e < 8; ++e) z += __expf(v[e] * invT - mx);
-      }
-      z = block_sum<float>(z, redf);
-    }
     if (rp.top_k > 0 && rp.top_k < V) {
       uint32_t cand = 0;
       for (int bit = 31; bit >= 16; --bit) {
@@ -94,16 +84,28 @@ sample_rows_kernel(const bf16* __restrict__ logits, const SampleRowDev* __restri
       thr = cand;
     }
     if (want_p) {
+      // top-p is taken over the distribution that is left after top-k (vLLM applies top-k first and renormalises):
+      // z is the mass of the top-k survivors, not of the whole vocabulary
+      z = 0.f;
+      for (int i = threadIdx.x; i < nvec; i += blockDim.x) {
+        float v[8];
+        unpack8(row[i], v);
+#pragma unroll
+        for (int e = 0; e < 8; ++e)
+          if (okey(v[e]) >= thr) z += __expf(v[e] * invT - mx);
+      }
+      z = block_sum<float>(z, redf);
       uint32_t cand = 0;
       for (int bit = 31; bit >= 16; --bit) {
         const uint32_t c = cand | (1u << bit);
+        const uint32_t lo = c > thr ? c : thr;  // only top-k survivors carry mass
         float mass = 0.f;
         for (int i = threadIdx.x; i < nvec; i += blockDim.x) {
           float v[8];
           unpack8(row[i], v);
 #pragma unroll
           for (int e = 0; e < 8; ++e)
-            if (okey(v[e]) >= c) mass += __expf(v[e] * invT - mx);
+            if (okey(v[e]) >= lo) mass += __expf(v[e] * invT - mx);
         }
         mass = block_sum<float>(mass, redf);
         if (mass >= rp.top_p * z) cand = c;
@@ -123,8 +125,14 @@ sample_rows_kernel(const bf16* __restrict__ logits, const SampleRowDev* __restri
       if (!(l == l) || okey(l) < thr) continue;
       float score = l;
       if (!greedy) {
-        const uint64_t r = mix64(rp.seed ^ mix64(step * 0x100000001b3ull + (uint64_t)rp.row) ^ ((uint64_t)idx << 20));
-        const float u = ((float)(r >> 40) + 0.5f) * (1.0f / 16777216.0f);
+        // A request that gives a seed gets draws that depend on (seed, token index) only -- the caller advances the
+        // seed per generated token -- so its output does not depend on what else is in the batch or on how long the
+        // process has run; seed 0 means "no seed given" and mixes in the launch counter and the row.
+        const uint64_t salt = rp.seed != 0ull ? 0ull : mix64(step * 0x100000001b3ull + (uint64_t)rp.row);
+        const uint64_t r = mix64(rp.seed ^ salt ^ ((uint64_t)idx << 20));
+        // u strictly inside (0, 1): 23 random bits + 0.5 is exact in fp32 (24 bits + 0.5 rounds up to 2^24, i.e. u == 1,
+        // whose Gumbel score is +inf: that token would win whatever its probability)
+        const float u = ((float)(r >> 41) + 0.5f) * (1.0f / 8388608.0f);
         score = l * invT - __logf(-__logf(u));
       }
       const unsigned long long pk = ((unsigned long long)okey(score) << 32) | (unsigned long long)(0xffffffffu - (uint32_t)idx);

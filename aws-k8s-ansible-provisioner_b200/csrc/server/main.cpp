@@ -366,7 +366,17 @@ class Scheduler {
           ReqP r = waiting_.front();
           const int need = std::min(cfg_.max_model_len, (int)r->prompt.size() + r->max_tokens);
           int32_t sid = -1;
-          if (b2_seq_create(e_, need, &sid) != 0) break;  // pool full: retry after sequences finish
+          if (b2_seq_create(e_, need, &sid) != 0) {
+            // Pool full: retry after sequences finish -- unless nothing is running, in which case no page will ever
+            // come back and this request (it needs more pages than the pool holds) would block the queue for good.
+            if (running_.empty() && prefilling_.empty()) {
+              waiting_.pop_front();
+              fail(r, std::string("request needs ") + std::to_string(need) + " tokens of KV cache, more than the pool holds: " +
+                          b2_last_error());
+              continue;
+            }
+            break;
+          }
           waiting_.pop_front();
           r->seq = sid;
           prefilling_.push_back(r);
@@ -376,8 +386,9 @@ class Scheduler {
       const bool want_logits = needs_logits();
       if (want_logits != logits_on_) { b2_set_debug(e_, want_logits ? 2 : 0); logits_on_ = want_logits; }
 
-      // ---- chunked prefill: pack admitted prompts into forwards of <= max_batch_tokens tokens ----
-      while (!prefilling_.empty()) {
+      // ---- chunked prefill: pack admitted prompts into ONE forward of <= max_batch_tokens tokens per loop turn, so the
+      //      running streams get a decode step between the chunks of a long prompt ----
+      if (!prefilling_.empty()) {
         std::vector<int32_t> ids, offs{0}, sids;
         std::vector<ReqP> batch;
         std::vector<int> take;

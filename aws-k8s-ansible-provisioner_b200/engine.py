@@ -177,6 +177,13 @@ class Engine:
         check(self.lib.b2_attn_profile(self.h, len(sids), _p32(sids), int(reps), C.byref(ms), C.byref(nbytes)), self.lib)
         return ms.value, int(nbytes.value)
 
+    def set_tuning(self, skip_mask: int | None = None, two_lane_min_batch: int | None = None) -> None:
+        """Run-time measurement knobs (include/b2_engine.h, b2_set_tuning); drops the captured decode graphs."""
+        if skip_mask is not None:
+            check(self.lib.b2_set_tuning(self.h, 0, int(skip_mask)), self.lib)
+        if two_lane_min_batch is not None:
+            check(self.lib.b2_set_tuning(self.h, 1, int(two_lane_min_batch)), self.lib)
+
     def launch_count(self) -> int:
         return int(self.lib.b2_launch_count(self.h))
 

@@ -6,20 +6,26 @@
 
 Workload (config.workload = "C2"): BASELINE.json configs[1] -- batch 64, 512-token prompts,
 256 generated tokens, paged KV.  One "step" = one decode forward over the whole batch
-(64 tokens).  With the defaults (W=8, K=248) the timed region generates tokens 9..256 of every
-sequence, i.e. the context grows from 520 to 768 tokens inside it.
+(64 tokens).  The workload does NOT shrink with --steps: whatever K and W are, the K timed steps
+are centred on the middle of C2's decode window (mean context 640.5; `config.timed_context` gives the
+first and last context length).  With the defaults (W=8, K=248) the timed region is tokens 9..256 of
+every sequence (context 520 -> 768); a short run (K=20) first advances the sequences, untimed, to
+context ~630.  The timed region is repeated REPEATS times from the same context and the median is
+reported (a 20-step region lasts ~30 ms).  Both arms print the same `config`.
 
 Numbers on the JSON line:
   value      device-resident decode: K steps replayed as CUDA graphs with token feedback on the GPU,
-             timed with CUDA events on the engine's stream, max over ranks
+             timed with CUDA events on the engine's stream, max over ranks, median of the repeats
   e2e        the same K steps through the public C-ABI call b2_decode_step with HOST token buffers
              in and out every step (H2D + D2H inside the timed region, host clock)
-  roofline   the dominant kernel (paged decode attention): algorithmic K/V bytes per launch over
-             its average launch duration at mid context, measured live after the timed region:
-             every layer's pass launched back to back over the real pages, 8 rounds (224 launches),
-             between one CUDA-event pair on the engine's stream (b2_attn_profile).  The per-class
-             table (kernel_ms_per_step_eager) and ms_per_launch_isolated come from an eager step
-             with an event pair around every launch, which adds launch latency to each figure
+  roofline   the dominant kernel (paged decode attention), per layer pass, at the mid context:
+               frac / achieved   IN THE STEP: (step time - step time with the attention class left out
+                                 of the graph) / layers, i.e. what the pass adds to the critical path
+                                 with programmatic dependent launch and the two-lane overlap in place
+               frac_burst        every layer's pass launched back to back over the real pages, 8 rounds
+                                 (224 launches) between one CUDA-event pair (b2_attn_profile)
+             The per-class table (kernel_ms_per_step_eager) and ms_per_launch_isolated come from an
+             eager single-lane step with an event pair around every launch (adds launch latency).
   cpu_baseline  HF Qwen3 on the host CPU, same batch/context, a bounded number of steps
 N > 1: one replica per GPU (request-level data parallelism, no collective on the data path);
 ranks only meet at a gloo barrier around the timed region ("scaling": "weak").
@@ -44,6 +50,30 @@ PKG = "aws-k8s-ansible-provisioner_b200"
 BATCH = 64
 PROMPT = 512
 OUT_TOKENS = 256
+REPEATS = 3
+NUM_LAYERS = 28
+KV_BYTES_PER_TOKEN = 2 * NUM_LAYERS * 8 * 128 * 2          # K+V, 28 layers, 8 kv heads x 128 dims, bf16
+WEIGHT_BYTES = 1_192_099_840                                 # SURVEY.md section 8d (tied head counted once)
+
+
+def timed_window(K: int, W: int):
+    """Context lengths (first, last) of the K timed steps and the untimed advance that puts them there:
+    centred on C2's mean context (512 + 257/2) unless the run already covers the window."""
+    lo = PROMPT + W if K + W >= OUT_TOKENS else PROMPT + (OUT_TOKENS + 1) // 2 - K // 2
+    lo = max(lo, PROMPT + W)
+    advance = lo - PROMPT - W
+    return lo, lo + K, advance
+
+
+def c2_config(world: int, K: int, W: int) -> dict:
+    """The workload description both arms print (identical for the same --gpus/--steps/--warmup)."""
+    lo, hi, _ = timed_window(K, W)
+    s_mean = lo + (K + 1) / 2.0
+    step_bytes = WEIGHT_BYTES + BATCH * s_mean * KV_BYTES_PER_TOKEN + BATCH * KV_BYTES_PER_TOKEN
+    return {"workload": "C2", "model": "Qwen3-0.6B arch random-init", "batch": BATCH, "prompt_len": PROMPT,
+            "new_tokens": OUT_TOKENS, "timed_context": [lo, hi], "kv_block": 16,
+            "parallelism": "dp%d replicas, no collective" % world,
+            "l2": "inputs_exceed_l2 (%.2f GB read per step)" % (step_bytes / 1e9)}
 
 
 def measured_peaks():
@@ -203,20 +233,22 @@ def hf_cpu_decode(batch: int, ctx: int, steps: int, warmup: int, budget_s: float
 def run_reference(args, rank, world, dist):
     if rank != 0:
         return
-    steps = args.steps
-    warm = max(1, min(args.warmup, 2))
-    r = hf_cpu_decode(BATCH, PROMPT + args.warmup, steps=min(steps, 16), warmup=warm, budget_s=150.0)
-    sample = "HF transformers Qwen3 bf16 sdpa on host CPU: %d decode steps, batch %d of %d, context %d (random KV, no prefill)" % (
-        r["steps"], r["batch"], BATCH, r["ctx"])
+    K, W = args.steps, args.warmup
+    lo, hi, _ = timed_window(K, W)
+    steps = min(K, 32)  # bounded sample: ~0.3 s per full-batch step on 16 cores
+    warm = max(1, min(W, 2))
+    ctx = lo + (K - steps) // 2  # the sample sits in the middle of the GPU arm's timed window
+    r = hf_cpu_decode(BATCH, ctx - warm, steps=steps, warmup=warm, budget_s=150.0)
+    sample = "HF transformers Qwen3 bf16 sdpa on host CPU: %d decode steps, batch %d of %d, context %d..%d (random KV, no prefill)" % (
+        r["steps"], r["batch"], BATCH, ctx, ctx + r["steps"])
     line = {
         "impl": "reference", "metric": "decode_tok_s", "value": r["tok_s"], "unit": "tok/s", "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
+        "steps": r["steps"], "warmup": warm, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-        "config": {"workload": "C2", "model": "Qwen3-0.6B arch random-init", "batch": BATCH, "prompt_len": PROMPT,
-                   "new_tokens": OUT_TOKENS, "l2": "inputs_exceed_l2"},
+        "config": c2_config(world, K, W),
         "cpu_baseline": {"value": r["tok_s"], "unit": "tok/s", "cores": r["threads"], "kind": "reference", "sample": sample},
         "e2e": {"value": r["tok_s"], "unit": "tok/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "host_cpus": os.cpu_count(),
+        "host_cpus": os.cpu_count(), "steps_requested": K, "warmup_requested": W,
     }
     print(json.dumps(line), flush=True)
 
@@ -235,7 +267,9 @@ def run_b200(args, rank, world, local, dist):
     K, W = args.steps, args.warmup
     assert W >= 3, "at least 3 warm-up steps"
     assert W + K <= OUT_TOKENS + 1024
-    cfg = pkg.EngineConfig(max_model_len=PROMPT + W + K + 16, max_seqs=BATCH, max_batch_tokens=8192, use_cuda_graphs=True)
+    lo, hi, advance = timed_window(K, W)
+    cfg = pkg.EngineConfig(max_model_len=max(PROMPT + OUT_TOKENS, hi) + 16, max_seqs=BATCH, max_batch_tokens=8192, use_cuda_graphs=True)
+    assert cfg.weight_bytes() == WEIGHT_BYTES and cfg.kv_bytes_per_token() == KV_BYTES_PER_TOKEN and cfg.num_layers == NUM_LAYERS
     cfg.num_blocks = BATCH * ((cfg.max_model_len + 15) // 16) + 8
     t0 = time.time()
     sd = weights.random_state_dict(cfg, seed=0)
@@ -253,102 +287,142 @@ def run_b200(args, rank, world, local, dist):
     prefill_s = time.perf_counter() - tp0
     setup_s = time.time() - t0
 
-    # ---- device-resident decode: warm-up, then K timed steps -----------------------------------
-    eng.decode_run(sids, W, want_tokens=False)
+    def rewind(ctx):
+        """Back to context `ctx` (the K/V of the dropped positions are simply rewritten): one untimed step re-seeds
+        the device batch after the truncate."""
+        for s_ in sids:
+            eng.seq_truncate(s_, ctx - 1)
+        eng.decode_step(sids)
+
+    # ---- device-resident decode: untimed advance to the window, then REPEATS x (W warm-up + K timed) steps ----
+    if advance > 0:
+        eng.decode_run(sids, advance, want_tokens=False)
     sampler = ClockSampler(local)
-    torch.cuda.synchronize(local)
-    barrier(dist)
-    sampler.start()
-    l0 = eng.launch_count()
-    _, ms = eng.decode_run(sids, K, want_tokens=False)
-    torch.cuda.synchronize(local)
-    barrier(dist)
+    launches = 0
+    ms_runs = []
+    for rep in range(REPEATS):
+        if rep > 0:
+            rewind(lo - W)
+        eng.decode_run(sids, W, want_tokens=False)
+        torch.cuda.synchronize(local)
+        barrier(dist)
+        if rep == 0:
+            sampler.start()
+        l0 = eng.launch_count()
+        _, ms = eng.decode_run(sids, K, want_tokens=False)
+        torch.cuda.synchronize(local)
+        barrier(dist)
+        launches = eng.launch_count() - l0
+        ms_runs.append(reduce_max(dist, ms))
     clocks = sampler.stop()
-    launches = eng.launch_count() - l0
-    ms_max = reduce_max(dist, ms)
+    ms_max = statistics.median(ms_runs)
     tok_s = world * BATCH * K / (ms_max / 1e3)
     if args.value_only:
         if rank == 0:
-            print(json.dumps({"ms_per_step": ms_max / K, "value": tok_s, "skip_mask": os.environ.get("B2_SKIP_MASK", "0"),
+            print(json.dumps({"ms_per_step": ms_max / K, "value": tok_s, "ms_runs": [m / K for m in ms_runs],
+                              "skip_mask": os.environ.get("B2_SKIP_MASK", "0"),
                               "env": {k: v for k, v in os.environ.items() if k.startswith("B2_")}}), flush=True)
         eng.close()
         return
 
     # ---- end to end through the public call, host buffers in and out every step ----------------
-    for s in sids:
-        eng.seq_truncate(s, PROMPT + W)
-    tok = eng.decode_step(sids)  # re-seeds the device batch after the truncate (not timed)
-    for s in sids:
-        eng.seq_truncate(s, PROMPT + W)
-    torch.cuda.synchronize(local)
-    barrier(dist)
-    step_times = []
-    te0 = time.perf_counter()
-    for _ in range(K):
-        ts = time.perf_counter()
-        tok = eng.decode_step(sids, in_tokens=tok)  # H2D ids, graph launch, D2H ids, sync
-        step_times.append(time.perf_counter() - ts)
-    e2e_s = time.perf_counter() - te0
-    barrier(dist)
-    e2e_max = reduce_max(dist, e2e_s)
+    e2e_runs, step_times = [], []
+    for rep in range(REPEATS):
+        rewind(lo - W)
+        tok = None
+        for _ in range(W):
+            tok = eng.decode_step(sids, in_tokens=tok)
+        torch.cuda.synchronize(local)
+        barrier(dist)
+        st = []
+        te0 = time.perf_counter()
+        for _ in range(K):
+            ts = time.perf_counter()
+            tok = eng.decode_step(sids, in_tokens=tok)  # H2D ids, graph launch, D2H ids, sync
+            st.append(time.perf_counter() - ts)
+        e2e_s = time.perf_counter() - te0
+        barrier(dist)
+        e2e_runs.append(reduce_max(dist, e2e_s))
+        step_times += st
+    e2e_max = statistics.median(e2e_runs)
     e2e_tok_s = world * BATCH * K / e2e_max
 
-    # ---- live roofline of the dominant kernel (eager profiled pass at mid context) --------------
-    mid = PROMPT + W + K // 2
-    for s in sids:
-        eng.seq_truncate(s, mid)
+    # ---- the dominant kernel in the step: the same K steps with the attention class left out of the graph ----
+    ATTN_CLASS = 4  # aws-k8s-ansible-provisioner_b200.engine.KERNEL_CLASSES.index("attn_decode")
+    eng.set_tuning(skip_mask=1 << ATTN_CLASS)
+    noattn_runs = []
+    for rep in range(REPEATS):
+        rewind(lo - W)
+        eng.decode_run(sids, W, want_tokens=False)
+        _, ms = eng.decode_run(sids, K, want_tokens=False)
+        noattn_runs.append(ms)
+    eng.set_tuning(skip_mask=0)
+    ms_noattn = statistics.median(noattn_runs)
+    attn_ms_in_step = max(1e-6, (ms_max - reduce_max(dist, ms_noattn)) / K / cfg.num_layers)
+
+    # ---- the same kernel alone: eager profiled pass and a back-to-back burst at mid context ------
+    mid = lo + K // 2
+    rewind(mid)
     prof = eng.decode_profile(sids, 3)
     attn = prof["attn_decode"]
     attn_ms_isolated = attn["ms"] / max(1, attn["launches"])  # event pair around every single launch: + launch latency
-    # the figure used: all layers' passes back to back over the real pages between ONE event pair, 8 rounds
+    # all layers' passes back to back over the real pages between ONE event pair, 8 rounds
     # (28 x 8 launches; every layer's K/V is its own 170 MB region, so no launch finds its input in L2)
-    attn_ms, kv_bytes = eng.attn_profile(sids, reps=8)
-    ctx_mid = kv_bytes // (BATCH * 2 * cfg.num_kv_heads * cfg.head_dim * 2)
-    attn_bytes = kv_bytes + 2 * BATCH * cfg.num_q_heads * cfg.head_dim * 2  # + q in, o out
+    attn_ms_burst, kv_bytes = eng.attn_profile(sids, reps=8)
+    ctx_burst = kv_bytes // (BATCH * 2 * cfg.num_kv_heads * cfg.head_dim * 2)
+    io_bytes = 2 * BATCH * cfg.num_q_heads * cfg.head_dim * 2  # q in, o out
+    burst_bytes = kv_bytes + io_bytes
+    # in the step the pass of one layer reads the K/V of the mean context of the timed region
+    s_mean = lo + (K + 1) / 2.0
+    step_pass_bytes = BATCH * s_mean * (KV_BYTES_PER_TOKEN // cfg.num_layers) + io_bytes
     peak, peak_kind = measured_peaks()
-    achieved = attn_bytes / (attn_ms / 1e3) / 1e9
-    # DRAM traffic of one launch, from the committed ncu --set full capture (taken at another context:
+    achieved = step_pass_bytes / (attn_ms_in_step / 1e3) / 1e9
+    achieved_burst = burst_bytes / (attn_ms_burst / 1e3) / 1e9
+    # DRAM traffic of one pass, from the committed ncu --set full capture (taken at another context:
     # scaled by its own traffic/algorithmic ratio, which is what the figure is for)
     traffic = None
     try:
         with open(os.path.join(ROOT, "profiles", "r01_c_attn_traffic.json")) as f:
             tj = json.load(f)
-        traffic = attn_bytes * (tj["dram_bytes_read"] + tj["dram_bytes_write"]) / tj["algorithmic_bytes"]
+        traffic = step_pass_bytes * (tj["dram_bytes_read"] + tj["dram_bytes_write"]) / tj["algorithmic_bytes"]
     except (OSError, KeyError, ValueError):
         pass
     prof_total = sum(v["ms"] for v in prof.values()) / 3.0
     kernel_ms = {k: round(v["ms"] / 3.0, 4) for k, v in prof.items() if v["launches"]}
     # whole-step algorithmic bytes (SURVEY.md 8d): W + B*S*kv + B*kv at the mean context of the timed region
-    s_mean = PROMPT + W + (K + 1) / 2.0
-    step_bytes = cfg.weight_bytes() + BATCH * s_mean * cfg.kv_bytes_per_token() + BATCH * cfg.kv_bytes_per_token()
+    step_bytes = WEIGHT_BYTES + BATCH * s_mean * KV_BYTES_PER_TOKEN + BATCH * KV_BYTES_PER_TOKEN
     step_frac = (step_bytes / (ms_max / K / 1e3) / 1e9) / peak
 
     line = {
         "metric": "decode_tok_s", "value": tok_s, "unit": "tok/s", "n_gpus": world, "steps": K, "warmup": W,
         "ms_per_step": ms_max / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
         "data": "synthetic",
-        "config": {"workload": "C2", "model": "Qwen3-0.6B arch random-init", "batch": BATCH, "prompt_len": PROMPT,
-                   "new_tokens": W + K, "kv_block": 16, "parallelism": "dp%d replicas, no collective" % world,
-                   "l2": "inputs_exceed_l2 (%.2f GB read per step)" % (step_bytes / 1e9)},
+        "config": c2_config(world, K, W),
         "e2e": {"value": e2e_tok_s, "unit": "tok/s", "h2d_bytes_per_step": BATCH * 4, "d2h_bytes_per_step": BATCH * 4},
         "tpot_ms_p50": 1e3 * statistics.median(step_times),
         "gpu_launches": int(launches),
         "clocks": clocks,
-        "roofline": {"bound": "hbm", "kernel": "attn_decode_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak, "traffic": traffic, "traffic_source": "ncu capture at context 520, ratio 1.05 applied",
-                     "peak_kind": peak_kind, "bytes_per_launch": attn_bytes,
-                     "ms_per_launch": attn_ms, "context": ctx_mid,
-                     "launches_timed": 8 * cfg.num_layers, "ms_per_launch_isolated": attn_ms_isolated},
+        "repeats": REPEATS, "ms_per_step_runs": [round(m / K, 5) for m in ms_runs],
+        "roofline": {"bound": "hbm", "kernel": "attn_decode_kernel (one layer's pass)", "achieved": achieved, "peak": peak,
+                     "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+                     "traffic_source": "ncu capture at context 520, ratio 1.05 applied", "peak_kind": peak_kind,
+                     "how": "in-step: (step - step without the attention class) / layers",
+                     "bytes_per_launch": step_pass_bytes, "ms_per_launch": attn_ms_in_step, "context": s_mean,
+                     "ms_per_step_without_attention": ms_noattn / K,
+                     "frac_burst": achieved_burst / peak, "achieved_burst": achieved_burst, "bytes_per_launch_burst": burst_bytes,
+                     "ms_per_launch_burst": attn_ms_burst, "context_burst": ctx_burst, "launches_timed_burst": 8 * cfg.num_layers,
+                     "ms_per_launch_isolated": attn_ms_isolated},
         "step_hbm_frac": step_frac,
         "step_bytes": step_bytes,
         "kernel_ms_per_step_eager": kernel_ms,
         "eager_step_ms": prof_total,
         "prefill_s": prefill_s,
         "setup_s": setup_s,
+        "two_lane": os.environ.get("B2_MB", "default"),
     }
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         try:
-            r = hf_cpu_decode(BATCH, PROMPT + W, steps=6, warmup=1, budget_s=40.0)
+            r = hf_cpu_decode(BATCH, lo + K // 2, steps=6, warmup=1, budget_s=40.0)
             line["cpu_baseline"] = {
                 "value": r["tok_s"], "unit": "tok/s", "cores": r["threads"], "kind": "reference",
                 "sample": "HF transformers Qwen3 bf16 sdpa on host CPU: %d decode steps, batch %d of %d, context %d (random KV, "

@@ -125,12 +125,23 @@ int  b2_get_logits(b2_engine* e, int32_t nseq, float* out_logits);
 int  b2_set_debug(b2_engine* e, int32_t capture_hidden);
 int  b2_get_hidden(b2_engine* e, int32_t layer, int32_t ntokens, uint16_t* out_bf16);
 
+/* Measurement knobs that can change while the engine lives (bench.py's ablation leg, the two-lane tests); every
+ * call drops the captured decode graphs, so the next step re-captures with the new setting.
+ *   B2_TUNE_SKIP_MASK   bit k set = kernel class k (b2_kernel_class order) is left out of the step: timing only,
+ *                       the outputs are then meaningless
+ *   B2_TUNE_TWO_LANE    smallest padded decode batch that runs as two half-batch lanes (0 = never; default 32,
+ *                       environment B2_MB) */
+enum b2_tuning_key { B2_TUNE_SKIP_MASK = 0, B2_TUNE_TWO_LANE = 1 };
+int  b2_set_tuning(b2_engine* e, int32_t key, int64_t value);
+
 /* Sampling for the API surface (temperature / top-k / top-p over the last logits). */
 typedef struct b2_sampling {
   float    temperature;  /* 0 = greedy */
   int32_t  top_k;        /* <=0 = off */
-  float    top_p;        /* >=1 = off */
-  uint64_t seed;
+  float    top_p;        /* >=1 = off; taken over what top_k leaves (top-k first, then top-p, as vLLM) */
+  uint64_t seed;         /* != 0: the draw depends on (seed, row parameters, logits) only -- a caller that wants a
+                          * different draw per generated token advances the seed itself (b2serve adds the number of
+                          * tokens generated so far); 0: no seed given, draws also mix in a launch counter */
 } b2_sampling;
 int  b2_sample(b2_engine* e, int32_t nseq, const b2_sampling* params, int32_t* out_tokens);
 /* Per-row variant for a batch whose requests carry different sampling parameters: rows[i] indexes
@@ -246,7 +257,9 @@ int b2k_attn_decode_noalloc(const void* q, const void* k_pages, const void* v_pa
 
 /* Same contract at T > 1 (causal): ragged prefill over the paged cache.  q [T][nq*hd];
  * q_seq[T] / q_pos[T] int32 give the sequence row in block_table and the position of each
- * query token (tokens of one sequence contiguous and ascending).  Host arrays. */
+ * query token (tokens of one sequence contiguous and ascending).  Host arrays.
+ * A test hook, not a serving call: it cudaMallocs a tile list, synchronises `stream` before it returns and frees
+ * the list again (the engine's own prefill keeps its tile list in engine-owned buffers and does none of that). */
 int b2k_attn_prefill(const void* q, const void* k_pages, const void* v_pages,
                      const int32_t* block_table_dev, int bt_stride, const int32_t* host_seq_first_tok,
                      const int32_t* host_seq_pos0, const int32_t* host_seq_ntok,

@@ -84,3 +84,30 @@ def test_single_rank_needs_no_process_group(monkeypatch):
     assert (rank, world, local, dist) == (0, 1, 0, None)
     assert bench.reduce_max(None, 3.5) == 3.5 and bench.reduce_sum(None, 2.0) == 2.0
     bench.barrier(None)
+
+
+def test_timed_window_is_pinned_to_c2_whatever_the_step_count():
+    """--steps must not shrink the workload.  Every (K, W) is timed around C2's mean context
+    (512-token prompts, 256 new tokens -> 640.5) and both arms print the same config."""
+    sys.path.insert(0, ROOT)
+    import bench
+    for K, W in [(248, 8), (20, 5), (8, 3), (120, 4), (64, 3)]:
+        lo, hi, advance = bench.timed_window(K, W)
+        assert hi - lo == K and advance >= 0 and lo == bench.PROMPT + W + advance
+        assert abs((lo + hi) / 2.0 - 640.5) <= 4.5, (K, W, lo, hi)
+        cfg = bench.c2_config(1, K, W)
+        assert cfg["new_tokens"] == 256 and cfg["timed_context"] == [lo, hi] and cfg["workload"] == "C2"
+        assert "5.9" in cfg["l2"]  # 5.90 GB +- the window's centre: SURVEY.md section 8d
+    # the reference arm prints exactly the GPU arm's config for the same flags
+    import types
+    got = []
+    bench.hf_cpu_decode = lambda b, ctx, steps, warmup, budget_s: got.append((ctx, steps)) or {
+        "tok_s": 1.0, "ms_per_step": 1.0, "steps": steps, "batch": b, "ctx": ctx, "threads": 1}
+    import io, contextlib
+    buf = io.StringIO()
+    with contextlib.redirect_stdout(buf):
+        bench.run_reference(types.SimpleNamespace(steps=20, warmup=5, gpus=1), 0, 1, None)
+    line = json.loads(buf.getvalue())
+    assert line["config"] == bench.c2_config(1, 20, 5) and line["steps"] == 20
+    ctx, steps = got[0]
+    assert 625 <= ctx <= 640 and steps == 20
