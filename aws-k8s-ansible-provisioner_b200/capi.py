@@ -4,7 +4,8 @@ from __future__ import annotations
 import ctypes as C
 import os
 
-LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libb2engine.so")
+# B2_LIB_PATH: an alternative build of the same library (A/B measurements of one source change); never a fallback
+LIB_PATH = os.environ.get("B2_LIB_PATH") or os.path.join(os.path.dirname(os.path.abspath(__file__)), "libb2engine.so")
 ABI_VERSION = 2
 ARCH_QWEN3, ARCH_PHI3, ARCH_OPT = 0, 1, 2
 NUM_KERNEL_CLASSES = 12
@@ -64,6 +65,7 @@ SIGNATURES = {
     "b2k_qknorm_rope_kv": (_I, [_P, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, C.c_float, _P]),
     "b2k_silu_mul": (_I, [_P, _I, _I, _P, _I, _I, _P]),
     "b2k_linear": (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _I, _P]),
+    "b2k_debug_step_trace": (_I, [_P]),
     "b2k_debug_gemm_trace": (_I, [_P]),
     "b2k_debug_chain_trace": (_I, [_P]),
     "b2k_debug_fused_trace": (_I, [_P]),

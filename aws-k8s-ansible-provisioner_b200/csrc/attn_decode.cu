@@ -27,6 +27,8 @@
 
 namespace b2 {
 
+B2_STEP_TRACE_DEFINE(step_trace_set_attn)
+
 constexpr int AD_WARPS_MAX = 16;
 constexpr int AD_BS = 16;    // tokens per KV page
 constexpr int AD_HD = 128;   // head dim
@@ -68,7 +70,7 @@ __global__ void __launch_bounds__(AD_WARPS * 32, 1)
 attn_decode_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k_pages, const bf16* __restrict__ v_pages,
                    const int32_t* __restrict__ block_table, int bt_stride, const int32_t* __restrict__ seq_lens,
                    float* __restrict__ scratch, bf16* __restrict__ out, int B, int nq, int nkv, float scale, int early,
-                   int window) {
+                   int window, int tag) {
   extern __shared__ __align__(128) uint8_t smem[];
   // Sliding-window attention (Phi-3, HF:models/phi3/modeling_phi3.py:265 sliding_window): a query at position
   // S-1 sees the last `window` keys only, i.e. tokens lo(S) = max(0, S - window) .. S-1.  Whole pages below lo are
@@ -83,6 +85,7 @@ attn_decode_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k_pages,
   // the NEW token's K/V slot) is still executing: sequence lengths and block tables were written at the
   // top of the step, and every page except the last one of each sequence is at least a step old.
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  B2_STAMP_BEGIN();
   if (!early) pdl_wait();
   if (threadIdx.x == 0) {
     for (int w = 0; w < AD_WARPS; ++w)
@@ -177,6 +180,7 @@ attn_decode_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k_pages,
   }
   pdl_wait();
   pdl_launch_dependents();
+  B2_STAMP_WAIT();
   if (blockIdx.x == 0) {
     // empty sequences (padding rows of a graph bucket) own no pages: their output rows are zeros
     for (int b = 0; b < B; ++b)
@@ -417,6 +421,7 @@ attn_decode_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k_pages,
     }
   }
   arrive_all(pending, npending);
+  B2_STAMP_END_AUX(B2K_ATTN_DECODE, (unsigned)tag);  // warp 0's end: all warps of a CTA run the same number of pages
   if (dbg_time) {  // timing breadcrumbs for tools/attn_timeline.py (unused words of the geometry header)
     unsigned long long t_end;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_end));
@@ -444,18 +449,21 @@ size_t attn_decode_scratch_floats(int B, int nq, int nkv, int hd) {
 // B2_ATTN_CFG=<warps>x<stages> selects another built shape for experiments.
 static int ad_grid() {
   static int sms = device_num_sms();
+  static int forced = [] { const char* e = getenv("B2_ATTN_GRID"); return e ? atoi(e) : 0; }();  // experiments
+  if (forced > 0 && forced <= AD_MAX_CTAS) return forced;
   return sms < AD_MAX_CTAS ? sms : AD_MAX_CTAS;
 }
 
 template <int W, int S>
 static int launch_cfg(const bf16* q, const bf16* k_pages, const bf16* v_pages, const int32_t* block_table, int bt_stride,
                       const int32_t* seq_lens, float* scratch, bf16* out, int B, int nq, int nkv, float scale, int window,
-                      cudaStream_t s) {
+                      cudaStream_t s, int tag) {
   constexpr int SMEM = W * S * AD_STAGE;
-  static B2PerDeviceOnce attr_once;
+  static B2PerDeviceOnce attr_once, carve_once;
   if (attr_once.need()) B2_CUDA_OK(cudaFuncSetAttribute(attn_decode_kernel<W, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
+  b2_prefer_max_smem(attn_decode_kernel<W, S>, carve_once);
   B2_CUDA_OK(b2_launch(attn_decode_kernel<W, S>, dim3(ad_grid()), dim3(W * 32), (size_t)SMEM, s, q, k_pages, v_pages, block_table,
-                       bt_stride, seq_lens, scratch, out, B, nq, nkv, scale, b2_pdl_early_mask() & 1, window));
+                       bt_stride, seq_lens, scratch, out, B, nq, nkv, scale, b2_pdl_early_mask() & 1, window, tag));
   return 0;
 }
 
@@ -463,7 +471,7 @@ static int launch_cfg(const bf16* q, const bf16* k_pages, const bf16* v_pages, c
 // must be zero when the kernel starts -- the kernel leaves them zero again when it is done.
 int launch_attn_decode(const bf16* q, const bf16* k_pages, const bf16* v_pages, const int32_t* block_table,
                        int bt_stride, const int32_t* seq_lens, float* scratch, bf16* out, int B, int nq, int nkv,
-                       int hd, int block_size, cudaStream_t s, float softmax_scale, int window) {
+                       int hd, int block_size, cudaStream_t s, float softmax_scale, int window, int tag) {
   if (B <= 0) return 0;
   B2_REQUIRE(window >= 0, "attn_decode: negative window");
   B2_REQUIRE(hd == AD_HD && block_size == AD_BS, "attn_decode: built for head_dim 128 / page 16 (got %d / %d)", hd, block_size);
@@ -478,7 +486,7 @@ int launch_attn_decode(const bf16* q, const bf16* k_pages, const bf16* v_pages, 
     cfg = 82;
     if (e) { int w = 0, st = 0; if (sscanf(e, "%dx%d", &w, &st) == 2) cfg = w * 10 + st; }
   }
-#define AD_CASE(W, S) case (W) * 10 + (S): return launch_cfg<W, S>(q, k_pages, v_pages, block_table, bt_stride, seq_lens, scratch, out, B, nq, nkv, scale, window, s)
+#define AD_CASE(W, S) case (W) * 10 + (S): return launch_cfg<W, S>(q, k_pages, v_pages, block_table, bt_stride, seq_lens, scratch, out, B, nq, nkv, scale, window, s, tag)
   switch (cfg) {
     AD_CASE(8, 3);
     AD_CASE(6, 4);

@@ -62,6 +62,12 @@ extern "C" int b2k_linear(const void* x, const void* w, void* out, int out_is_f3
   return launch_linear_tc(a, (cudaStream_t)stream);
 }
 
+extern "C" int b2k_debug_step_trace(void* dev_u64_buf) {
+  unsigned long long* b = (unsigned long long*)dev_u64_buf;
+  CAPI_TRY(step_trace_set_elementwise(b));
+  CAPI_TRY(step_trace_set_gemm(b));
+  return step_trace_set_attn(b);
+}
 extern "C" int b2k_debug_gemm_trace(void* dev_u64_buf) { return tc_set_trace((unsigned long long*)dev_u64_buf); }
 extern "C" int b2k_debug_chain_trace(void* dev_u64_buf) { return chain_set_trace((unsigned long long*)dev_u64_buf); }
 extern "C" int b2k_debug_fused_trace(void* dev_u64_buf) { return fused_chain_set_trace((unsigned long long*)dev_u64_buf); }

@@ -6,6 +6,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 
 #include <string>
 
@@ -102,6 +103,24 @@ struct B2PerDeviceOnce {
     return true;
   }
 };
+// Every kernel of the decode path asks for the largest shared-memory carve-out, whatever it uses itself: an SM's
+// L1/shared split can only change while the SM is idle, so a CTA that needs 82 KB cannot join a running CTA on an SM
+// that was configured for that CTA's 132 KB alone -- it would wait for the SM to drain (two-lane decode, engine.cu).
+template <typename... KArgs>
+inline void b2_prefer_max_smem(void (*kernel)(KArgs...), B2PerDeviceOnce& once) {
+  if (once.need()) {
+    // On only with the two-lane schedule (B2_MB > 0) or B2_CARVEOUT=1: the smaller L1 costs a one-lane step 1.5 %.
+    static const bool on = [] {
+      const char* e = getenv("B2_CARVEOUT");
+      if (e) return *e != '0';
+      const char* mb = getenv("B2_MB");
+      return mb != nullptr && atoi(mb) > 0;
+    }();
+    if (!on) return;
+    if (cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared) != cudaSuccess)
+      cudaGetLastError();  // a preference only
+  }
+}
 template <typename... KArgs, typename... Args>
 inline cudaError_t b2_launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args&&... args) {
   cudaLaunchConfig_t cfg = {};
@@ -116,6 +135,74 @@ inline cudaError_t b2_launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, si
   cfg.numAttrs = b2_pdl_enabled() ? 1 : 0;
   return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
+
+// ---------------------------------------------------------------------------------------
+// Step timeline (tools/step_timeline.py): when a trace buffer is registered (b2k_debug_step_trace), thread 0 of
+// every CTA of every kernel on the decode path appends one record {class | blockIdx << 8 | smid << 32 | aux << 40, CTA start,
+// dependency wait returned, CTA end} (%globaltimer, ns).  buf[0] = record counter (atomic), buf[1] = capacity in
+// records, records start at buf[4].  Each .cu file holds its own copy of the pointer (no relocatable device code);
+// B2_STEP_TRACE_DEFINE(setter) defines it and its host-side setter.  Compiled in only with -DB2_STEP_TRACE
+// (tools/build_variant.sh trace -DB2_STEP_TRACE -> libb2engine_trace.so, which tools/step_timeline.py loads).
+// ---------------------------------------------------------------------------------------
+#ifdef B2_STEP_TRACE
+#define B2_STEP_TRACE_DEFINE(setter)                                              \
+  static __constant__ unsigned long long* g_step_trace = nullptr;                 \
+  int setter(unsigned long long* dev_buf) {                                       \
+    B2_CUDA_OK(cudaMemcpyToSymbol(g_step_trace, &dev_buf, sizeof(dev_buf)));       \
+    return 0;                                                                     \
+  }
+#else
+#define B2_STEP_TRACE_DEFINE(setter)                                                                              \
+  int setter(unsigned long long* dev_buf) {                                                                       \
+    if (dev_buf == nullptr) return 0;                                                                             \
+    b2_set_error("step trace: this library was built without -DB2_STEP_TRACE (tools/build_variant.sh trace ...)"); \
+    return -38;                                                                                                   \
+  }
+#endif
+// The stamps of a CTA live in shared memory (24 bytes), not in registers: the projection kernel must stay at 72
+// registers to fit on an SM next to a decode-attention CTA (engine.cu, two-lane decode).
+__device__ __forceinline__ unsigned long long b2_globaltimer() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+__device__ __forceinline__ void b2_stamp_begin(unsigned long long* st, unsigned long long* buf) {
+  st[0] = (unsigned long long)buf;
+  st[1] = st[2] = 0;
+  if (buf != nullptr) st[1] = b2_globaltimer();
+}
+__device__ __forceinline__ void b2_stamp_wait(unsigned long long* st) {
+  if (st[0] != 0ull) st[2] = b2_globaltimer();
+}
+__device__ __forceinline__ void b2_stamp_end(const unsigned long long* st, int cls, unsigned aux = 0) {
+  unsigned long long* buf = (unsigned long long*)st[0];
+  if (buf == nullptr) return;
+  const unsigned long long t1 = b2_globaltimer();
+  const unsigned long long slot = atomicAdd(buf, 1ull);
+  if (slot < buf[1]) {
+    unsigned smid;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    unsigned long long* r = buf + 4 + slot * 4;
+    r[0] = (unsigned long long)((unsigned)cls & 0xffu) | ((unsigned long long)(blockIdx.x & 0xffffffu) << 8) |
+           ((unsigned long long)(smid & 0xffu) << 32) | ((unsigned long long)(aux & 0xffffffu) << 40);
+    r[1] = st[1];
+    r[2] = st[2];
+    r[3] = t1;
+  }
+}
+// Use inside a kernel (thread 0 only does anything): B2_STAMP_BEGIN at entry, B2_STAMP_WAIT right after
+// griddepcontrol.wait, B2_STAMP_END(cls) last.
+#ifndef B2_STEP_TRACE  // the stamps cost 1.5 % of a decode step (measured, 258 tiny kernels): only the trace build has them
+#define B2_STAMP_BEGIN() do { } while (0)
+#define B2_STAMP_WAIT() do { } while (0)
+#define B2_STAMP_END(cls) do { } while (0)
+#define B2_STAMP_END_AUX(cls, aux) do { } while (0)
+#else
+#define B2_STAMP_BEGIN() __shared__ unsigned long long _stamp[3]; if (threadIdx.x == 0) b2_stamp_begin(_stamp, g_step_trace)
+#define B2_STAMP_WAIT() do { if (threadIdx.x == 0) b2_stamp_wait(_stamp); } while (0)
+#define B2_STAMP_END(cls) do { if (threadIdx.x == 0) b2_stamp_end(_stamp, (cls)); } while (0)
+#define B2_STAMP_END_AUX(cls, aux) do { if (threadIdx.x == 0) b2_stamp_end(_stamp, (cls), (aux)); } while (0)
+#endif
 
 // ---------------------------------------------------------------------------------------
 // mbarrier + bulk async copy (TMA engine, SASS: UBLKCP / UTMALDG)

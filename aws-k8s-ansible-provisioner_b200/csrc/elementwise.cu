@@ -6,13 +6,17 @@
 
 namespace b2 {
 
+B2_STEP_TRACE_DEFINE(step_trace_set_elementwise)
+
 // ---------------------------------------------------------------------------------------
 // a1: nn.Embedding lookup, HF:models/qwen3/modeling_qwen3.py:363,392
 // ---------------------------------------------------------------------------------------
 __global__ void embed_kernel(const int32_t* __restrict__ ids, const bf16* __restrict__ table, bf16* __restrict__ h,
                              int H, int vocab, unsigned long long* __restrict__ zero_buf, int nzero) {
+  B2_STAMP_BEGIN();
   pdl_wait();
   pdl_launch_dependents();
+  B2_STAMP_WAIT();
   int t = blockIdx.x;
   // first kernel of every forward: also clears the fused arg-max slots the lm_head will atomicMax into
   if (t == 0 && zero_buf != nullptr)
@@ -22,11 +26,14 @@ __global__ void embed_kernel(const int32_t* __restrict__ ids, const bf16* __rest
   const uint4* src = reinterpret_cast<const uint4*>(table + (size_t)id * H);
   uint4* dst = reinterpret_cast<uint4*>(h + (size_t)t * H);
   for (int i = threadIdx.x; i < H / 8; i += blockDim.x) dst[i] = src[i];
+  B2_STAMP_END(B2K_EMBED);
 }
 
 int launch_embed(const int32_t* ids, const bf16* table, bf16* h, int T, int H, int vocab, unsigned long long* zero_buf, int nzero,
                  cudaStream_t s) {
   if (T <= 0) return 0;
+  static B2PerDeviceOnce c0;
+  b2_prefer_max_smem(embed_kernel, c0);
   B2_CUDA_OK(b2_launch(embed_kernel, dim3(T), dim3(128), 0, s, ids, table, h, H, vocab, zero_buf, nzero));
   return 0;
 }
@@ -55,8 +62,9 @@ int launch_gather_rows(const bf16* src, const int32_t* rows, bf16* dst, int n, i
 // ---------------------------------------------------------------------------------------
 template <int MODE>  // 0: no delta, 1: bf16 delta, 2: fp32 partials
 __global__ void add_rmsnorm_kernel(bf16* __restrict__ h, const void* __restrict__ delta, int nsplit, size_t split_stride,
-                                   const bf16* __restrict__ w, bf16* __restrict__ x, int H, float eps, int early) {
+                                   const bf16* __restrict__ w, bf16* __restrict__ x, int H, float eps, int early, int tag) {
   __shared__ float red[32];
+  B2_STAMP_BEGIN();
   if (!early) pdl_wait();
   const int t = blockIdx.x;
   const int i = threadIdx.x;  // vector index, 8 elements
@@ -69,6 +77,7 @@ __global__ void add_rmsnorm_kernel(bf16* __restrict__ h, const void* __restrict_
   if (MODE != 0) hv = reinterpret_cast<const uint4*>(h + (size_t)t * H)[i];
   pdl_wait();
   pdl_launch_dependents();
+  B2_STAMP_WAIT();
   if (MODE == 0) hv = reinterpret_cast<const uint4*>(h + (size_t)t * H)[i];
   float v[8];
   unpack8(hv, v);
@@ -119,19 +128,24 @@ __global__ void add_rmsnorm_kernel(bf16* __restrict__ h, const void* __restrict_
 #pragma unroll
   for (int e = 0; e < 8; ++e) v[e] = bf16_round(wv[e] * bf16_round(v[e] * rstd));
   reinterpret_cast<uint4*>(x + (size_t)t * H)[i] = pack8(v);
+  B2_STAMP_END_AUX(B2K_NORM, (unsigned)tag);
 }
 
-int launch_add_rmsnorm(bf16* h, ActIn delta, const bf16* w, bf16* x, int T, int H, float eps, cudaStream_t s) {
+int launch_add_rmsnorm(bf16* h, ActIn delta, const bf16* w, bf16* x, int T, int H, float eps, cudaStream_t s, int tag) {
   if (T <= 0) return 0;
   B2_REQUIRE(H % 256 == 0 && H <= 8192, "add_rmsnorm: hidden %d must be a multiple of 256 and <= 8192", H);
   const int threads = H / 8;
+  static B2PerDeviceOnce c0, c1, c2;
+  b2_prefer_max_smem(add_rmsnorm_kernel<0>, c0);
+  b2_prefer_max_smem(add_rmsnorm_kernel<1>, c1);
+  b2_prefer_max_smem(add_rmsnorm_kernel<2>, c2);
   if (delta.ptr == nullptr)
-    B2_CUDA_OK(b2_launch(add_rmsnorm_kernel<0>, dim3(T), dim3(threads), 0, s, h, (const void*)nullptr, 0, (size_t)0, w, x, H, eps, b2_pdl_early_mask() & 2));
+    B2_CUDA_OK(b2_launch(add_rmsnorm_kernel<0>, dim3(T), dim3(threads), 0, s, h, (const void*)nullptr, 0, (size_t)0, w, x, H, eps, b2_pdl_early_mask() & 2, tag));
   else if (!delta.is_f32)
-    B2_CUDA_OK(b2_launch(add_rmsnorm_kernel<1>, dim3(T), dim3(threads), 0, s, h, delta.ptr, 1, (size_t)0, w, x, H, eps, b2_pdl_early_mask() & 2));
+    B2_CUDA_OK(b2_launch(add_rmsnorm_kernel<1>, dim3(T), dim3(threads), 0, s, h, delta.ptr, 1, (size_t)0, w, x, H, eps, b2_pdl_early_mask() & 2, tag));
   else
     B2_CUDA_OK(b2_launch(add_rmsnorm_kernel<2>, dim3(T), dim3(threads), 0, s, h, delta.ptr, delta.nsplit, (size_t)T * H, w, x, H,
-                         eps, b2_pdl_early_mask() & 2));
+                         eps, b2_pdl_early_mask() & 2, tag));
   return 0;
 }
 
@@ -155,8 +169,9 @@ __global__ void qknorm_rope_kv_kernel(const void* __restrict__ qkv, int nsplit, 
                                       const bf16* __restrict__ cos_sin, const int32_t* __restrict__ positions,
                                       const int32_t* __restrict__ slots, bf16* __restrict__ q_out,
                                       bf16* __restrict__ k_pages, bf16* __restrict__ v_pages, int T, int nq, int nkv,
-                                      int block_size, float eps, int early, int rot_quads, const bf16* __restrict__ bias, float q_mul) {
+                                      int block_size, float eps, int early, int rot_quads, const bf16* __restrict__ bias, float q_mul, int tag) {
   constexpr int HD = 128;
+  B2_STAMP_BEGIN();
   if (!early) pdl_wait();
   const int nheads = nq + 2 * nkv;
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -201,6 +216,7 @@ __global__ void qknorm_rope_kv_kernel(const void* __restrict__ qkv, int nsplit, 
   }
   pdl_wait();
   pdl_launch_dependents();
+  B2_STAMP_WAIT();
 
   float v[4];
   if (F32IN) {
@@ -248,8 +264,7 @@ __global__ void qknorm_rope_kv_kernel(const void* __restrict__ qkv, int nsplit, 
   o.y = pack_bf16x2(v[2], v[3]);
   if (is_q) {
     *reinterpret_cast<uint2*>(q_out + ((size_t)t * nq + head) * HD + lane * 4) = o;
-  } else {
-    if (slot < 0) return;
+  } else if (slot >= 0) {
     const int kvh = is_k ? head - nq : head - nq - nkv;
     const int blk = slot / block_size, off = slot % block_size;
     bf16* base = is_k ? k_pages : v_pages;
@@ -257,6 +272,7 @@ __global__ void qknorm_rope_kv_kernel(const void* __restrict__ qkv, int nsplit, 
     const int chunk = kv_swizzled_chunk(off, lane >> 1);
     *reinterpret_cast<uint2*>(base + (((size_t)blk * nkv + kvh) * block_size + off) * HD + chunk * 8 + (lane & 1) * 4) = o;
   }
+  B2_STAMP_END_AUX(B2K_ROPE_KV, (unsigned)tag);
 }
 
 // Prefill-sized variant of the kernel above (same arithmetic, same rounding points): with thousands of tokens the
@@ -338,7 +354,7 @@ __global__ void qknorm_rope_kv_prefill_kernel(const bf16* __restrict__ qkv, cons
 
 int launch_qknorm_rope_kv(ActIn qkv, const bf16* qw, const bf16* kw, const bf16* cos_sin, const int32_t* positions,
                           const int32_t* slots, bf16* q_out, bf16* k_pages, bf16* v_pages, int T, int nq, int nkv,
-                          int hd, int block_size, float eps, cudaStream_t s, int rotary_dim, const bf16* bias, float q_mul) {
+                          int hd, int block_size, float eps, cudaStream_t s, int rotary_dim, const bf16* bias, float q_mul, int tag) {
   if (T <= 0) return 0;
   B2_REQUIRE(hd == 128, "qknorm_rope_kv: head_dim %d not built (128 only; narrower heads are stored padded)", hd);
   B2_REQUIRE((qw == nullptr) == (kw == nullptr), "qknorm_rope_kv: q and k norm gains must both be given or both be null");
@@ -354,13 +370,16 @@ int launch_qknorm_rope_kv(ActIn qkv, const bf16* qw, const bf16* kw, const bf16*
   }
   const long long warps = (long long)T * nheads;
   const int blocks = (int)((warps + 3) / 4);
+  static B2PerDeviceOnce c0, c1;
+  b2_prefer_max_smem(qknorm_rope_kv_kernel<true>, c0);
+  b2_prefer_max_smem(qknorm_rope_kv_kernel<false>, c1);
   if (qkv.is_f32)
     B2_CUDA_OK(b2_launch(qknorm_rope_kv_kernel<true>, dim3(blocks), dim3(128), 0, s, qkv.ptr, qkv.nsplit,
                          (size_t)T * nheads * hd, qw, kw, cos_sin, positions, slots, q_out, k_pages, v_pages, T, nq, nkv,
-                         block_size, eps, b2_pdl_early_mask() & 4, rot_quads, bias, q_mul));
+                         block_size, eps, b2_pdl_early_mask() & 4, rot_quads, bias, q_mul, tag));
   else
     B2_CUDA_OK(b2_launch(qknorm_rope_kv_kernel<false>, dim3(blocks), dim3(128), 0, s, qkv.ptr, 1, (size_t)0, qw, kw, cos_sin,
-                         positions, slots, q_out, k_pages, v_pages, T, nq, nkv, block_size, eps, b2_pdl_early_mask() & 4, rot_quads, bias, q_mul));
+                         positions, slots, q_out, k_pages, v_pages, T, nq, nkv, block_size, eps, b2_pdl_early_mask() & 4, rot_quads, bias, q_mul, tag));
   return 0;
 }
 
@@ -370,9 +389,11 @@ int launch_qknorm_rope_kv(ActIn qkv, const bf16* qw, const bf16* kw, const bf16*
 // ---------------------------------------------------------------------------------------
 template <bool F32IN>
 __global__ void silu_mul_kernel(const void* __restrict__ gu, int nsplit, size_t split_stride, bf16* __restrict__ act,
-                                int T, int I) {
+                                int T, int I, int tag) {
+  B2_STAMP_BEGIN();
   pdl_wait();
   pdl_launch_dependents();
+  B2_STAMP_WAIT();
   const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;  // vector of 8 over [T][I]
   const size_t nvec = (size_t)T * I / 8;
   if (idx >= nvec) return;
@@ -418,17 +439,27 @@ __global__ void silu_mul_kernel(const void* __restrict__ gu, int nsplit, size_t 
     o[e] = bf16_round(sl * u[e]);
   }
   *reinterpret_cast<uint4*>(act + (size_t)t * I + i) = pack8(o);
+  B2_STAMP_END_AUX(B2K_ACT, (unsigned)tag);
 }
 
-int launch_silu_mul(ActIn gu, bf16* act, int T, int I, cudaStream_t s) {
+int launch_silu_mul(ActIn gu, bf16* act, int T, int I, cudaStream_t s, int tag) {
   if (T <= 0) return 0;
   B2_REQUIRE(I % 8 == 0, "silu_mul: intermediate %d must be a multiple of 8", I);
   const size_t nvec = (size_t)T * I / 8;
   const int blocks = (int)((nvec + 255) / 256);
-  if (gu.is_f32)
-    B2_CUDA_OK(b2_launch(silu_mul_kernel<true>, dim3(blocks), dim3(256), 0, s, gu.ptr, gu.nsplit, (size_t)T * 2 * I, act, T, I));
+  static B2PerDeviceOnce c0, c1;
+  b2_prefer_max_smem(silu_mul_kernel<true>, c0);
+  b2_prefer_max_smem(silu_mul_kernel<false>, c1);
+  // two-lane schedule: four warps per CTA (one per warp scheduler, 96 registers) so that a CTA fits into the register
+  // banks a decode-attention CTA leaves free (see linear_tc_kernel, SMALL)
+  static const bool narrow = [] { const char* mb = getenv("B2_MB"); return mb != nullptr && atoi(mb) > 0; }();
+  if (gu.is_f32 && narrow)
+    B2_CUDA_OK(b2_launch(silu_mul_kernel<true>, dim3((unsigned)((nvec + 127) / 128)), dim3(128), 0, s, gu.ptr, gu.nsplit,
+                         (size_t)T * 2 * I, act, T, I, tag));
+  else if (gu.is_f32)
+    B2_CUDA_OK(b2_launch(silu_mul_kernel<true>, dim3(blocks), dim3(256), 0, s, gu.ptr, gu.nsplit, (size_t)T * 2 * I, act, T, I, tag));
   else
-    B2_CUDA_OK(b2_launch(silu_mul_kernel<false>, dim3(blocks), dim3(256), 0, s, gu.ptr, 1, (size_t)0, act, T, I));
+    B2_CUDA_OK(b2_launch(silu_mul_kernel<false>, dim3(blocks), dim3(256), 0, s, gu.ptr, 1, (size_t)0, act, T, I, tag));
   return 0;
 }
 

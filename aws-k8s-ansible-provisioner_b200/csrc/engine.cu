@@ -582,6 +582,7 @@ int forward_layers(b2_engine* e, const Lane& ln, int T, int ntiles) {
   const int H = c.hidden, I = c.intermediate;
   const size_t r0 = (size_t)ln.row0;
   cudaStream_t st = ln.stream;
+  const int tag = ln.row0 != 0 ? 1 : 0;  // lane marker in the step timeline
   bf16* h = e->h + r0 * H;
   bf16* x = e->x + r0 * H;
   bf16* qkvb = e->qkv + r0 * e->qkv_size;
@@ -619,7 +620,7 @@ int forward_layers(b2_engine* e, const Lane& ln, int T, int ntiles) {
     bf16* vp = kp + e->layer_kv_elems;
     {
       KL k(e, B2K_NORM);
-      if (!k.skip()) B2_TRY(launch_add_rmsnorm(h, delta, L.ln1, x, T, H, c.rms_eps, st));
+      if (!k.skip()) B2_TRY(launch_add_rmsnorm(h, delta, L.ln1, x, T, H, c.rms_eps, st, tag));
     }
     if (l > 0) dbg_capture(e, l, e->h, T);
     ActIn qkv = linear(e, ln, B2K_GEMM_QKV, XB_X, x, L.wqkv, L.tm_qkv, qkvb, T, e->qkv_size, H, &rc, prefetch_for(l, 3));
@@ -627,7 +628,7 @@ int forward_layers(b2_engine* e, const Lane& ln, int T, int ntiles) {
     {
       KL k(e, B2K_ROPE_KV);
       if (!k.skip()) B2_TRY(launch_qknorm_rope_kv(qkv, L.qnorm, L.knorm, e->cos_sin, positions, slots, qrot, kp, vp, T,
-                                   e->nq, e->nkv, e->hd, c.block_size, c.rms_eps, st, e->rotary_dim));
+                                   e->nq, e->nkv, e->hd, c.block_size, c.rms_eps, st, e->rotary_dim, nullptr, 1.0f, tag));
     }
     if (ntiles > 0) {
       KL k(e, B2K_MISC);
@@ -637,27 +638,27 @@ int forward_layers(b2_engine* e, const Lane& ln, int T, int ntiles) {
       KL k(e, B2K_ATTN_DECODE);
       if (!k.skip())
         B2_TRY(launch_attn_decode(qrot, kp, vp, block_table, e->bt_stride, seq_lens, ln.attn_scratch, attn, T,
-                                  e->nq, e->nkv, e->hd, c.block_size, st, e->attn_scale, c.sliding_window));
+                                  e->nq, e->nkv, e->hd, c.block_size, st, e->attn_scale, c.sliding_window, tag));
     }
     ActIn o = linear(e, ln, B2K_GEMM_O, XB_ATTN, attn, L.wo, L.tm_o, proj, T, H, e->q_size, &rc, prefetch_for(l + 1, 0), false,
                      /*after_attention=*/ntiles == 0);
     B2_TRY(rc);
     {
       KL k(e, B2K_NORM);
-      if (!k.skip()) B2_TRY(launch_add_rmsnorm(h, o, L.ln2, x, T, H, c.rms_eps, st));
+      if (!k.skip()) B2_TRY(launch_add_rmsnorm(h, o, L.ln2, x, T, H, c.rms_eps, st, tag));
     }
     ActIn gu = linear(e, ln, B2K_GEMM_GATEUP, XB_X, x, L.wgu, L.tm_gu, gub, T, 2 * I, H, &rc, prefetch_for(l + 1, 1));
     B2_TRY(rc);
     {
       KL k(e, B2K_ACT);
-      if (!k.skip()) B2_TRY(launch_silu_mul(gu, act, T, I, st));
+      if (!k.skip()) B2_TRY(launch_silu_mul(gu, act, T, I, st, tag));
     }
     delta = linear(e, ln, B2K_GEMM_DOWN, XB_ACT, act, L.wd, L.tm_d, proj, T, H, I, &rc, prefetch_for(l + 1, 2));
     B2_TRY(rc);
   }
   {
     KL k(e, B2K_NORM);
-    if (!k.skip()) B2_TRY(launch_add_rmsnorm(h, delta, e->final_norm, x, T, H, c.rms_eps, st));
+    if (!k.skip()) B2_TRY(launch_add_rmsnorm(h, delta, e->final_norm, x, T, H, c.rms_eps, st, tag));
   }
   return 0;
 }
@@ -1331,7 +1332,8 @@ extern "C" int b2_engine_create(const b2_config* cfg, const char* safetensors_pa
     E_TRY(dalloc(&e->attn_scratch, e->attn_scratch_floats));
     E_CUDA(cudaMemset(e->attn_scratch, 0, e->attn_scratch_floats * sizeof(float)));  // arrival counters start at zero
     // two-lane decode: B2_MB = smallest padded decode batch that is cut into two half-batch lanes (0 = off)
-    e->mb_min_batch = c.arch == B2_ARCH_OPT ? 0 : env_int("B2_MB", 32);
+    // Off by default: measured slower (C2: 2.03 against 1.90 ms/step) -- DESIGN.md section 4 has the timeline.
+    e->mb_min_batch = c.arch == B2_ARCH_OPT ? 0 : env_int("B2_MB", 0);
     if (c.arch != B2_ARCH_OPT && c.max_seqs >= 2) {
       E_CUDA(cudaStreamCreateWithFlags(&e->stream2, cudaStreamNonBlocking));
       E_CUDA(cudaEventCreateWithFlags(&e->ev_fork, cudaEventDisableTiming));

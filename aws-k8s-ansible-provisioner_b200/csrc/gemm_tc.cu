@@ -24,6 +24,8 @@
 
 namespace b2 {
 
+B2_STEP_TRACE_DEFINE(step_trace_set_gemm)
+
 // Optional phase trace (tools/gemm_timeline.py): when a buffer is registered, every CTA stamps
 // %globaltimer at its phase boundaries into trace[blockIdx.x * 8 + slot].
 __device__ unsigned long long* g_tc_trace = nullptr;
@@ -61,8 +63,11 @@ __device__ __forceinline__ unsigned long long tc_argmax_pack(float v, int idx) {
 // Persistent: gridDim.x CTAs walk the (m tile, token tile, k split) work list with stride
 // gridDim.x.  The smem stage ring runs on across tiles, and the accumulator is double buffered
 // in TMEM so the epilogue of tile i overlaps the TMA/MMA main loop of tile i+1.
+// SMALL also caps the kernel at 56 registers (launch bound of 6 CTAs per SM): an SM's register file is four banks of
+// 16 K, one per warp scheduler, and a decode-attention CTA holds 2 warps x 200 registers in each; this kernel's six
+// warps put up to two on a scheduler, so it fits beside that CTA only if 2 x 32 x (200 + R) <= 16384, R <= 56.
 template <int BN, int EPI, int SMALL = 0>
-__global__ void __launch_bounds__(192, 1)
+__global__ void __launch_bounds__(192, SMALL ? 6 : 1)
 linear_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_x,
                  void* __restrict__ out, unsigned long long* __restrict__ argmax_packed, int T, int N, int K,
                  int kb_per_split, int m_tiles, int n_tiles, int nsplit, const KvPrefetch pf, int x_row0) {
@@ -77,6 +82,7 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
   (void)amax_red;
 
   if (threadIdx.x == 0) tc_stamp(0);  // CTA started
+  B2_STAMP_BEGIN();
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int kb_total = K / TC_BK;
@@ -130,6 +136,7 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
           pdl_wait();
           pdl_launch_dependents();
           tc_stamp(2);  // dependency satisfied, the activation tiles go out
+          B2_STAMP_WAIT();
           waited = true;
           for (int i = 0; i < npre; ++i) {
             const uint32_t fb = smem_u32(&full_bar[i]);
@@ -269,13 +276,17 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
         }
       } else if (EPI == TC_EPI_F32_PARTIAL) {
         float* dst = reinterpret_cast<float*>(out) + ((size_t)split * T + tok0) * N + row;  // + j * N per token
-        if (BN == 16) {
-          uint32_t r[16];
-          tmem_ld16(tbase, r);
-          tmem_ld_wait();
+        if (BN == 16 || SMALL) {  // 16 columns at a time: half the live registers of the 32-column loop below
+#pragma unroll 1
+          for (int c0 = 0; c0 < BN; c0 += 16) {
+            uint32_t r[16];
+            tmem_ld16(tbase + (uint32_t)c0, r);
+            tmem_ld_wait();
+            float* d = dst + (size_t)c0 * N;
 #pragma unroll
-          for (int j = 0; j < 16; ++j)
-            if (full || (row_ok && tok0 + j < T)) dst[(size_t)j * N] = __uint_as_float(r[j]);
+            for (int j = 0; j < 16; ++j)
+              if (full || (row_ok && tok0 + c0 + j < T)) d[(size_t)j * N] = __uint_as_float(r[j]);
+          }
         } else {
 #pragma unroll 1
           for (int c0 = 0; c0 < BN; c0 += 32) {
@@ -364,6 +375,7 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
   tc_fence_before();
   __syncthreads();
   if (threadIdx.x == 0) tc_stamp(6);  // epilogue done
+  B2_STAMP_END_AUX(100 /* any projection: the aux word tells them apart by (N, K) */, ((unsigned)(N >> 6) & 0xfffu) | (((unsigned)(K >> 6) & 0x7ffu) << 12) | (x_row0 != 0 ? (1u << 23) : 0u));
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc(tmem_base, C::TMEM_COLS);
@@ -442,9 +454,10 @@ int tc_pick_nsplit(int T, int N, int K, int num_sms) {
 template <int BN, int EPI, int SMALL = 0>
 static int launch_one(const TcGemmArgs& a, int kb_per_split, cudaStream_t s) {
   using C = TcCfg<BN, SMALL>;
-  static B2PerDeviceOnce attr_once;
+  static B2PerDeviceOnce attr_once, carve_once;
   if (attr_once.need())
     B2_CUDA_OK(cudaFuncSetAttribute(linear_tc_kernel<BN, EPI, SMALL>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
+  b2_prefer_max_smem(linear_tc_kernel<BN, EPI, SMALL>, carve_once);
   // TC_EPI_ARGMAX_ROWS: tokens are the 128-row M tiles and weight rows the BN-wide N tiles
   const bool rows_mode = (EPI == TC_EPI_ARGMAX_ROWS);
   const int m_tiles = rows_mode ? (a.T + TC_BM - 1) / TC_BM : (a.N + TC_BM - 1) / TC_BM;

@@ -1,8 +1,14 @@
 // kernels.h -- internal C++ launch API of the sm_100a kernels (engine.cu and capi.cu call these).
 #pragma once
+#include "../../include/b2_engine.h"
 #include "common.cuh"
 
 namespace b2 {
+
+// step timeline (common.cuh): one setter per .cu file that holds kernels of the decode path
+int step_trace_set_elementwise(unsigned long long* dev_buf);
+int step_trace_set_gemm(unsigned long long* dev_buf);
+int step_trace_set_attn(unsigned long long* dev_buf);
 
 // An activation operand that is either bf16 [T][N] or fp32 split-K partials [nsplit][T][N]
 // (summed in split order, then rounded to bf16 -- the rounding point of HF's nn.Linear).
@@ -17,11 +23,12 @@ inline ActIn act_f32(const void* p, int nsplit) { return ActIn{p, 1, nsplit}; }
 // ---- elementwise.cu ----
 int launch_embed(const int32_t* ids, const bf16* table, bf16* h, int T, int H, int vocab, unsigned long long* zero_buf, int nzero,
                  cudaStream_t s);
-int launch_add_rmsnorm(bf16* h, ActIn delta, const bf16* w, bf16* x, int T, int H, float eps, cudaStream_t s);
+int launch_add_rmsnorm(bf16* h, ActIn delta, const bf16* w, bf16* x, int T, int H, float eps, cudaStream_t s, int tag = 0);
+// tag: lane marker for the step timeline (common.cuh), no effect on the result
 int launch_qknorm_rope_kv(ActIn qkv, const bf16* qw, const bf16* kw, const bf16* cos_sin, const int32_t* positions,
                           const int32_t* slots, bf16* q_out, bf16* k_pages, bf16* v_pages, int T, int nq, int nkv,
                           int hd, int block_size, float eps, cudaStream_t s, int rotary_dim = 128, const bf16* bias = nullptr,
-                          float q_mul = 1.0f);
+                          float q_mul = 1.0f, int tag = 0);
 // qw == kw == nullptr: no QK-norm (Phi-3).  rotary_dim: width of the rotated prefix of each head; heads narrower
 // than 128 are stored zero-padded to 128 (see engine.cu, "internal geometry").  bias [(nq + 2 nkv) * 128]: added to the
 // fp32 partials before the rounding; q_mul: the query is multiplied by it afterwards (OPT pre-scales q).
@@ -32,7 +39,7 @@ int launch_embed_pos(const int32_t* ids, const int32_t* positions, const bf16* t
 int launch_add_layernorm(bf16* h, ActIn delta, const bf16* delta_bias, const bf16* w, const bf16* b, bf16* x, int T, int H, float eps,
                          cudaStream_t s);
 int launch_bias_relu(ActIn fc1, const bf16* bias, bf16* act, int T, int I, cudaStream_t s);
-int launch_silu_mul(ActIn gu, bf16* act, int T, int I, cudaStream_t s);
+int launch_silu_mul(ActIn gu, bf16* act, int T, int I, cudaStream_t s, int tag = 0);
 int launch_gather_rows(const bf16* src, const int32_t* rows, bf16* dst, int n, int H, cudaStream_t s);
 int launch_argmax_rows(const bf16* logits, int32_t* out, int T, int V, cudaStream_t s);
 int launch_argmax_finalize(const unsigned long long* packed, int32_t* out, int T, cudaStream_t s);
@@ -137,7 +144,7 @@ size_t attn_decode_scratch_floats(int B, int nq, int nkv, int hd);
 int attn_decode_zero_counters(float* scratch, cudaStream_t s);
 int launch_attn_decode(const bf16* q, const bf16* k_pages, const bf16* v_pages, const int32_t* block_table,
                        int bt_stride, const int32_t* seq_lens, float* scratch, bf16* out, int B, int nq, int nkv,
-                       int hd, int block_size, cudaStream_t s, float softmax_scale = 0.f, int window = 0);
+                       int hd, int block_size, cudaStream_t s, float softmax_scale = 0.f, int window = 0, int tag = 0);
 // softmax_scale 0 = hd^-0.5; a padded head passes the scale of its real width.  window > 0: sliding-window attention,
 // each query sees its last `window` keys (itself included).
 

@@ -129,7 +129,7 @@ int  b2_get_hidden(b2_engine* e, int32_t layer, int32_t ntokens, uint16_t* out_b
  * call drops the captured decode graphs, so the next step re-captures with the new setting.
  *   B2_TUNE_SKIP_MASK   bit k set = kernel class k (b2_kernel_class order) is left out of the step: timing only,
  *                       the outputs are then meaningless
- *   B2_TUNE_TWO_LANE    smallest padded decode batch that runs as two half-batch lanes (0 = never; default 32,
+ *   B2_TUNE_TWO_LANE    smallest padded decode batch that runs as two half-batch lanes (0 = never, the default;
  *                       environment B2_MB) */
 enum b2_tuning_key { B2_TUNE_SKIP_MASK = 0, B2_TUNE_TWO_LANE = 1 };
 int  b2_set_tuning(b2_engine* e, int32_t key, int64_t value);
@@ -203,6 +203,12 @@ int b2k_silu_mul(const void* gu, int gu_is_f32, int nsplit, void* act_bf16, int 
 int b2k_linear(const void* x_bf16, const void* w_bf16, void* out, int out_is_f32, int nsplit,
                int T, int N, int K, int impl, void* stream);
 
+/* Diagnostics (tools/step_timeline.py): register a device buffer of uint64 in which thread 0 of every CTA of every
+ * kernel on the decode path appends one 4-word record {class | blockIdx << 8 | smid << 32 | aux << 40, CTA start,
+ * dependency wait returned, CTA end} in %globaltimer ns.  The caller sets buf[0] = 0 (record counter) and
+ * buf[1] = capacity in records; records start at buf[4].  NULL switches the trace off.  class 100 = a projection
+ * (aux = N/64 | (K/64) << 12 | second lane << 23); for the other kernels aux = 1 on the second lane of a two-lane step. */
+int b2k_debug_step_trace(void* dev_u64_buf);
 /* Diagnostics: register a device buffer of (148 * 8) uint64 in which every CTA of the tcgen05
  * projection kernel stamps %globaltimer at its phase boundaries (NULL switches the trace off). */
 int b2k_debug_gemm_trace(void* dev_u64_buf);
