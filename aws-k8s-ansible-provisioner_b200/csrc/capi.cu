@@ -52,6 +52,7 @@ extern "C" int b2k_linear(const void* x, const void* w, void* out, int out_is_f3
   a.T = T; a.N = N; a.K = K;
   a.nsplit = nsplit;
   a.out = out;
+  a.x_raw = x;
   a.argmax_packed = nullptr;
   if (nsplit > 1) {
     B2_REQUIRE(out_is_f32, "b2k_linear: split-K output must be fp32 partials");

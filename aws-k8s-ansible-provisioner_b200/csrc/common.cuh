@@ -91,6 +91,7 @@ __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepc
 
 bool b2_pdl_enabled();     // consumes a pending b2_pdl_skip_next()
 void b2_pdl_skip_next();   // the calling thread's next launch is an ordinary (fully serialised) one
+bool b2_pdl_trigger_early();  // B2_PDL_TRIGGER (default 1): norm / SwiGLU kernels release the projection behind them at their start
 int b2_pdl_early_mask();  // B2_PDL_EARLY bitmask (diagnostics): 1 attention streams before its wait, 2 norm, 4 rope
 // Function attributes (opt-in shared memory size) are per device: remember which devices were set.
 struct B2PerDeviceOnce {

@@ -65,7 +65,14 @@ __global__ void add_rmsnorm_kernel(bf16* __restrict__ h, const void* __restrict_
                                    const bf16* __restrict__ w, bf16* __restrict__ x, int H, float eps, int early, int tag) {
   __shared__ float red[32];
   B2_STAMP_BEGIN();
-  if (!early) pdl_wait();
+  // The kernel that follows a norm is always a projection, and all a projection does before ITS dependency wait is
+  // start the TMA stream of its weight tiles (constants).  Releasing it at the very start of this kernel -- before
+  // this kernel's own wait -- gives that stream the whole hand-off + norm time instead of the ~1.5 us it had, which
+  // was less than a 64-96 KB weight slice takes to arrive (the projection then issued its last MMA ~2 us after its
+  // wait; tools/step_timeline.py).  The projection triggers ITS dependents only after its own wait, so the
+  // discipline stated in common.cuh still holds for every other kernel.
+  if (early & 2) pdl_launch_dependents();
+  if (!(early & 1)) pdl_wait();
   const int t = blockIdx.x;
   const int i = threadIdx.x;  // vector index, 8 elements
   // Before the dependency wait: the norm gains (constant) and, when a delta is added, the residual
@@ -76,7 +83,7 @@ __global__ void add_rmsnorm_kernel(bf16* __restrict__ h, const void* __restrict_
   uint4 hv = make_uint4(0, 0, 0, 0);
   if (MODE != 0) hv = reinterpret_cast<const uint4*>(h + (size_t)t * H)[i];
   pdl_wait();
-  pdl_launch_dependents();
+  if (!(early & 2)) pdl_launch_dependents();
   B2_STAMP_WAIT();
   if (MODE == 0) hv = reinterpret_cast<const uint4*>(h + (size_t)t * H)[i];
   float v[8];
@@ -140,12 +147,12 @@ int launch_add_rmsnorm(bf16* h, ActIn delta, const bf16* w, bf16* x, int T, int 
   b2_prefer_max_smem(add_rmsnorm_kernel<1>, c1);
   b2_prefer_max_smem(add_rmsnorm_kernel<2>, c2);
   if (delta.ptr == nullptr)
-    B2_CUDA_OK(b2_launch(add_rmsnorm_kernel<0>, dim3(T), dim3(threads), 0, s, h, (const void*)nullptr, 0, (size_t)0, w, x, H, eps, b2_pdl_early_mask() & 2, tag));
+    B2_CUDA_OK(b2_launch(add_rmsnorm_kernel<0>, dim3(T), dim3(threads), 0, s, h, (const void*)nullptr, 0, (size_t)0, w, x, H, eps, ((b2_pdl_early_mask() & 2) ? 1 : 0) | (b2_pdl_trigger_early() ? 2 : 0), tag));
   else if (!delta.is_f32)
-    B2_CUDA_OK(b2_launch(add_rmsnorm_kernel<1>, dim3(T), dim3(threads), 0, s, h, delta.ptr, 1, (size_t)0, w, x, H, eps, b2_pdl_early_mask() & 2, tag));
+    B2_CUDA_OK(b2_launch(add_rmsnorm_kernel<1>, dim3(T), dim3(threads), 0, s, h, delta.ptr, 1, (size_t)0, w, x, H, eps, ((b2_pdl_early_mask() & 2) ? 1 : 0) | (b2_pdl_trigger_early() ? 2 : 0), tag));
   else
     B2_CUDA_OK(b2_launch(add_rmsnorm_kernel<2>, dim3(T), dim3(threads), 0, s, h, delta.ptr, delta.nsplit, (size_t)T * H, w, x, H,
-                         eps, b2_pdl_early_mask() & 2, tag));
+                         eps, ((b2_pdl_early_mask() & 2) ? 1 : 0) | (b2_pdl_trigger_early() ? 2 : 0), tag));
   return 0;
 }
 
@@ -389,10 +396,11 @@ int launch_qknorm_rope_kv(ActIn qkv, const bf16* qw, const bf16* kw, const bf16*
 // ---------------------------------------------------------------------------------------
 template <bool F32IN>
 __global__ void silu_mul_kernel(const void* __restrict__ gu, int nsplit, size_t split_stride, bf16* __restrict__ act,
-                                int T, int I, int tag) {
+                                int T, int I, int tag, int trigger_early) {
   B2_STAMP_BEGIN();
+  if (trigger_early) pdl_launch_dependents();  // the down projection starts streaming its weights (see add_rmsnorm_kernel)
   pdl_wait();
-  pdl_launch_dependents();
+  if (!trigger_early) pdl_launch_dependents();
   B2_STAMP_WAIT();
   const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;  // vector of 8 over [T][I]
   const size_t nvec = (size_t)T * I / 8;
@@ -455,11 +463,11 @@ int launch_silu_mul(ActIn gu, bf16* act, int T, int I, cudaStream_t s, int tag) 
   static const bool narrow = [] { const char* mb = getenv("B2_MB"); return mb != nullptr && atoi(mb) > 0; }();
   if (gu.is_f32 && narrow)
     B2_CUDA_OK(b2_launch(silu_mul_kernel<true>, dim3((unsigned)((nvec + 127) / 128)), dim3(128), 0, s, gu.ptr, gu.nsplit,
-                         (size_t)T * 2 * I, act, T, I, tag));
+                         (size_t)T * 2 * I, act, T, I, tag, b2_pdl_trigger_early() ? 1 : 0));
   else if (gu.is_f32)
-    B2_CUDA_OK(b2_launch(silu_mul_kernel<true>, dim3(blocks), dim3(256), 0, s, gu.ptr, gu.nsplit, (size_t)T * 2 * I, act, T, I, tag));
+    B2_CUDA_OK(b2_launch(silu_mul_kernel<true>, dim3(blocks), dim3(256), 0, s, gu.ptr, gu.nsplit, (size_t)T * 2 * I, act, T, I, tag, b2_pdl_trigger_early() ? 1 : 0));
   else
-    B2_CUDA_OK(b2_launch(silu_mul_kernel<false>, dim3(blocks), dim3(256), 0, s, gu.ptr, 1, (size_t)0, act, T, I, tag));
+    B2_CUDA_OK(b2_launch(silu_mul_kernel<false>, dim3(blocks), dim3(256), 0, s, gu.ptr, 1, (size_t)0, act, T, I, tag, b2_pdl_trigger_early() ? 1 : 0));
   return 0;
 }
 

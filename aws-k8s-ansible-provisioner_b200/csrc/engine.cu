@@ -36,6 +36,14 @@ int b2_pdl_early_mask() {
   }
   return v;
 }
+bool b2_pdl_trigger_early() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("B2_PDL_TRIGGER");
+    v = (e && *e == '0') ? 0 : 1;
+  }
+  return v != 0;
+}
 // The next launch of this thread goes out WITHOUT the programmatic attribute (the first kernel after a cross-stream
 // fork or join: its predecessors are ordinary full dependencies).
 static thread_local int g_pdl_skip_next = 0;
@@ -309,6 +317,7 @@ ActIn linear(b2_engine* e, const Lane& ln, int cls, XBuf xb, const bf16* xptr, c
   a.argmax_packed = nullptr;
   a.prefetch = pf;
   a.x_row0 = ln.row0;
+  a.x_raw = xptr;
   a.small_smem = ((after_attention && e->o_small_smem) || ln.beside_attention) ? 1 : 0;
   int ns = tc_pick_nsplit(T, N, K, e->num_sms);
   {  // experiments: B2_NS_<class index>=n forces the split factor of one projection class

@@ -66,11 +66,18 @@ __device__ __forceinline__ unsigned long long tc_argmax_pack(float v, int idx) {
 // SMALL also caps the kernel at 56 registers (launch bound of 6 CTAs per SM): an SM's register file is four banks of
 // 16 K, one per warp scheduler, and a decode-attention CTA holds 2 warps x 200 registers in each; this kernel's six
 // warps put up to two on a scheduler, so it fits beside that CTA only if 2 x 32 x (200 + R) <= 16384, R <= 56.
-template <int BN, int EPI, int SMALL = 0>
+// XCP (decode shapes: one tile per CTA, its k-blocks all fit the stage ring): the X tiles do not come through the
+// tensor map but through cp.async issued by the four epilogue warps, which are idle until the accumulator is ready.
+// Measured in the captured step (tools/step_timeline.py): with TMA the first X tile lands 0.6-0.8 us after the
+// dependency wait and every further one 0.35 us later (the tiled copy of a 64-row box is 64 requests of 128 bytes,
+// and dozens of CTAs ask for the same rows), so a CTA with 4-6 k-blocks issued its last MMA 1.8-2.4 us after the
+// wait; 128 threads x 16-byte LDGSTS have the whole slice in flight at once.
+template <int BN, int EPI, int SMALL = 0, int XCP = 0>
 __global__ void __launch_bounds__(192, SMALL ? 6 : 1)
 linear_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_x,
                  void* __restrict__ out, unsigned long long* __restrict__ argmax_packed, int T, int N, int K,
-                 int kb_per_split, int m_tiles, int n_tiles, int nsplit, const KvPrefetch pf, int x_row0) {
+                 int kb_per_split, int m_tiles, int n_tiles, int nsplit, const KvPrefetch pf, int x_row0,
+                 const bf16* __restrict__ x_raw) {
   using C = TcCfg<BN, SMALL>;
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t full_bar[C::STAGES];
@@ -83,6 +90,12 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
 
   if (threadIdx.x == 0) tc_stamp(0);  // CTA started
   B2_STAMP_BEGIN();
+#ifdef B2_STEP_TRACE
+  __shared__ unsigned long long phase_t[3];  // first operands landed, all MMAs of the first tile issued, accumulator visible
+#define TC_PHASE(i) do { if (_stamp[0] != 0ull) phase_t[i] = b2_globaltimer(); } while (0)
+#else
+#define TC_PHASE(i) do { } while (0)
+#endif
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int kb_total = K / TC_BK;
@@ -90,7 +103,7 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < C::STAGES; ++s) {
-      mbar_init(smem_u32(&full_bar[s]), 1);
+      mbar_init(smem_u32(&full_bar[s]), XCP ? 1 + 128 : 1);  // XCP: + one arrival per epilogue thread (its share of X)
       mbar_init(smem_u32(&empty_bar[s]), 1);
     }
     for (int a = 0; a < 2; ++a) {
@@ -127,6 +140,20 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
           // (TC_EPI_ARGMAX_ROWS trades the operands: there the SECOND map holds the weights.)
           constexpr bool kWeightsFirst = (EPI != TC_EPI_ARGMAX_ROWS);
           const int npre = min(kb1 - kb0, C::STAGES);
+          if (XCP) {  // one tile, all of its k-blocks resident: the weight tiles are all this thread loads
+            // ONE barrier for the whole tile (all weight bytes + the 128 X-loader arrivals): a wait on an mbarrier that
+            // has already completed still costs ~0.1 us, and the MMA thread paid it once per k-block
+            const uint32_t fb = smem_u32(&full_bar[0]);
+            mbar_arrive_expect_tx(fb, (uint32_t)npre * TC_W_BYTES);
+            for (int i = 0; i < npre; ++i)
+              tma_load_2d(smem_base + i * C::STAGE_BYTES, &tmap_w, (kb0 + i) * TC_BK, m_tile * TC_BM, fb);
+            pdl_wait();
+            pdl_launch_dependents();
+            tc_stamp(2);
+            B2_STAMP_WAIT();
+            waited = true;
+            continue;
+          }
           for (int i = 0; i < npre; ++i) {
             const uint32_t fb = smem_u32(&full_bar[i]);
             mbar_arrive_expect_tx(fb, C::STAGE_BYTES);
@@ -182,10 +209,29 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
         mbar_wait(smem_u32(&tmem_empty_bar[as]), ((lt >> 1) & 1) ^ 1);  // epilogue drained this accumulator
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + (uint32_t)(as * BN);
+        if (XCP) {
+          // one tile, every k-block has its own stage: wait for all of them, then issue the whole MMA chain back to back
+          mbar_wait(smem_u32(&full_bar[0]), 0);
+          tc_stamp(3);
+          TC_PHASE(0);
+          tc_fence_after();
+          for (int kb = kb0; kb < kb1; ++kb) {
+            const uint32_t ws = smem_base + (kb - kb0) * C::STAGE_BYTES;
+            const uint64_t da = umma_desc_sw128(ws);
+            const uint64_t db = umma_desc_sw128(ws + TC_W_BYTES);
+#pragma unroll
+            for (int k = 0; k < TC_BK / 16; ++k)
+              tc_mma_bf16(tmem_d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+          }
+          tc_commit(smem_u32(&tmem_full_bar[as]));
+          tc_stamp(4);
+          TC_PHASE(1);
+          continue;
+        }
         for (int kb = kb0; kb < kb1; ++kb, ++it) {
           const int s = it % C::STAGES;
           mbar_wait(smem_u32(&full_bar[s]), (it / C::STAGES) & 1);
-          if (it == 0) tc_stamp(3);  // first operands landed
+          if (it == 0) { tc_stamp(3); TC_PHASE(0); }  // first operands landed
           tc_fence_after();
           const uint32_t ws = smem_base + s * C::STAGE_BYTES;
           const uint64_t da = umma_desc_sw128(ws);
@@ -196,10 +242,10 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
             // (address >> 4) field of both descriptors
             tc_mma_bf16(tmem_d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb > kb0 || k > 0) ? 1u : 0u);
           }
-          tc_commit(smem_u32(&empty_bar[s]));  // frees the smem stage once these MMAs retire
+          if (!XCP) tc_commit(smem_u32(&empty_bar[s]));  // frees the smem stage once these MMAs retire (XCP: no stage is reused)
         }
         tc_commit(smem_u32(&tmem_full_bar[as]));  // accumulator complete
-        if (lt == 0) tc_stamp(4);  // all MMAs of the first tile issued
+        if (lt == 0) { tc_stamp(4); TC_PHASE(1); }  // all MMAs of the first tile issued
       }
     }
   } else {
@@ -207,6 +253,42 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
     unsigned long long row_best = 0ull;  // TC_EPI_ARGMAX_ROWS: running arg-max of this thread's token
     int row_best_tok = -1;
     pdl_wait();
+    if (XCP) {
+      // this CTA's only tile: X rows [tok0, tok0 + BN) x its k-blocks, 16 bytes per cp.async, into the 128-byte-swizzled
+      // layout the MMA descriptors expect (chunk c of row r at chunk position c ^ (r & 7); the X tile of a stage is
+      // 1024-byte aligned).
+      const int tile = blockIdx.x;
+      const int n_tile = (tile / m_tiles) % n_tiles;
+      const int split = tile / (m_tiles * n_tiles);
+      const int kb0 = split * kb_per_split;
+      const int nkb = min(kb_total, kb0 + kb_per_split) - kb0;
+      const int et = threadIdx.x - 64;
+      const bf16* xg = x_raw + (size_t)(n_tile * BN) * K + (size_t)kb0 * TC_BK;
+      constexpr int CHUNKS = BN * 8;  // 16-byte chunks per k-block tile
+#pragma unroll 1
+      for (int i = 0; i < nkb; ++i) {
+        const uint32_t xs = smem_base + i * C::STAGE_BYTES + TC_W_BYTES;
+#pragma unroll
+        for (int c0 = 0; c0 < CHUNKS; c0 += 128) {
+          const int idx = c0 + et;
+          if (CHUNKS >= 128 || idx < CHUNKS) {
+            const int r = idx >> 3, c = idx & 7;
+            // rows past T are zero-filled (source size 0), as the tensor map's out-of-bounds fill would
+            const bool in = n_tile * BN + r < T;
+            const bf16* src = xg + (size_t)(in ? r : 0) * K + i * TC_BK + c * 8;
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(xs + r * 128 + ((c ^ (r & 7)) << 4)), "l"(src),
+                         "r"(in ? 16 : 0)
+                         : "memory");
+          }
+        }
+      }
+      asm volatile("cp.async.commit_group;" ::: "memory");
+      // All copies were issued together and land within one L2 round trip of each other: one wait, one proxy fence
+      // (a fence per k-block cost more than the pipelining it allowed), then the arrival on the tile's barrier.
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+      fence_proxy_async();
+      mbar_arrive(smem_u32(&full_bar[0]));
+    }
     if (pf.k_pages != nullptr) {
       // These four warps idle until the first accumulator is ready: spend the time asking the TMA
       // engine to pull this launch's share of the next attention pass's K/V pages into L2.
@@ -232,7 +314,7 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
       const int split = tile / (m_tiles * n_tiles);
       const int as = lt & 1;
       mbar_wait(smem_u32(&tmem_full_bar[as]), (lt >> 1) & 1);
-      if (lt == 0 && threadIdx.x == 64) tc_stamp(5);  // accumulator visible to the epilogue
+      if (lt == 0 && threadIdx.x == 64) { tc_stamp(5); TC_PHASE(2); }  // accumulator visible to the epilogue
       tc_fence_after();
       const int row = m_tile * TC_BM + q * 32 + lane;  // output feature
       const bool row_ok = row < N;
@@ -375,6 +457,18 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
   tc_fence_before();
   __syncthreads();
   if (threadIdx.x == 0) tc_stamp(6);  // epilogue done
+#ifdef B2_STEP_TRACE
+  if (threadIdx.x == 0 && _stamp[0] != 0ull) {  // second record: the phases of the first tile
+    unsigned long long* buf = (unsigned long long*)_stamp[0];
+    const unsigned long long slot = atomicAdd(buf, 1ull);
+    if (slot < buf[1]) {
+      unsigned long long* r = buf + 4 + slot * 4;
+      r[0] = 101ull | ((unsigned long long)(blockIdx.x & 0xffffffu) << 8) |
+             ((unsigned long long)((((unsigned)(N >> 6) & 0xfffu) | (((unsigned)(K >> 6) & 0x7ffu) << 12) | (x_row0 != 0 ? (1u << 23) : 0u))) << 40);
+      r[1] = phase_t[0]; r[2] = phase_t[1]; r[3] = phase_t[2];
+    }
+  }
+#endif
   B2_STAMP_END_AUX(100 /* any projection: the aux word tells them apart by (N, K) */, ((unsigned)(N >> 6) & 0xfffu) | (((unsigned)(K >> 6) & 0x7ffu) << 12) | (x_row0 != 0 ? (1u << 23) : 0u));
   if (warp == 1) {
     tc_fence_after();
@@ -451,13 +545,13 @@ int tc_pick_nsplit(int T, int N, int K, int num_sms) {
   return (kb_total + kps - 1) / kps;  // every split non-empty
 }
 
-template <int BN, int EPI, int SMALL = 0>
+template <int BN, int EPI, int SMALL = 0, int XCP = 0>
 static int launch_one(const TcGemmArgs& a, int kb_per_split, cudaStream_t s) {
   using C = TcCfg<BN, SMALL>;
   static B2PerDeviceOnce attr_once, carve_once;
   if (attr_once.need())
-    B2_CUDA_OK(cudaFuncSetAttribute(linear_tc_kernel<BN, EPI, SMALL>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
-  b2_prefer_max_smem(linear_tc_kernel<BN, EPI, SMALL>, carve_once);
+    B2_CUDA_OK(cudaFuncSetAttribute(linear_tc_kernel<BN, EPI, SMALL, XCP>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
+  b2_prefer_max_smem(linear_tc_kernel<BN, EPI, SMALL, XCP>, carve_once);
   // TC_EPI_ARGMAX_ROWS: tokens are the 128-row M tiles and weight rows the BN-wide N tiles
   const bool rows_mode = (EPI == TC_EPI_ARGMAX_ROWS);
   const int m_tiles = rows_mode ? (a.T + TC_BM - 1) / TC_BM : (a.N + TC_BM - 1) / TC_BM;
@@ -465,17 +559,36 @@ static int launch_one(const TcGemmArgs& a, int kb_per_split, cudaStream_t s) {
   const int total = m_tiles * n_tiles * a.nsplit;
   static int sms = device_num_sms();
   const int grid = total < sms ? total : sms;
-  B2_CUDA_OK(b2_launch(linear_tc_kernel<BN, EPI, SMALL>, dim3(grid), dim3(192), (size_t)C::SMEM_BYTES, s, a.tmap_w, a.tmap_x, a.out,
-                       a.argmax_packed, a.T, a.N, a.K, kb_per_split, m_tiles, n_tiles, a.nsplit, a.prefetch, a.x_row0));
+  if (XCP) {
+    B2_REQUIRE(total <= sms && kb_per_split <= C::STAGES && a.x_raw != nullptr, "linear_tc: cp.async X path needs one tile per CTA");
+  }
+  B2_CUDA_OK(b2_launch(linear_tc_kernel<BN, EPI, SMALL, XCP>, dim3(grid), dim3(192), (size_t)C::SMEM_BYTES, s, a.tmap_w, a.tmap_x, a.out,
+                       a.argmax_packed, a.T, a.N, a.K, kb_per_split, m_tiles, n_tiles, a.nsplit, a.prefetch, a.x_row0,
+                       reinterpret_cast<const bf16*>(a.x_raw)));
   return 0;
+}
+
+// one tile per CTA and every k-block of a split resident in the ring: the shapes of a decode step
+template <int BN, int SMALL>
+static bool xcp_ok(const TcGemmArgs& a, int kps) {
+  static const bool on = [] { const char* e = getenv("B2_XCP"); return !(e && *e == '0'); }();
+  static int sms = device_num_sms();
+  const int total = ((a.N + TC_BM - 1) / TC_BM) * ((a.T + BN - 1) / BN) * a.nsplit;
+  return on && a.x_raw != nullptr && BN <= 64 && total <= sms && kps <= TcCfg<BN, SMALL>::STAGES;
 }
 
 template <int BN>
 static int launch_bn(const TcGemmArgs& a, int kps, cudaStream_t s) {
   switch (a.epilogue) {
-    case TC_EPI_BF16: return launch_one<BN, TC_EPI_BF16>(a, kps, s);
+    case TC_EPI_BF16:
+      if (BN <= 64 && xcp_ok<(BN <= 64 ? BN : 64), 0>(a, kps)) return launch_one<(BN <= 64 ? BN : 64), TC_EPI_BF16, 0, 1>(a, kps, s);
+      return launch_one<BN, TC_EPI_BF16>(a, kps, s);
     case TC_EPI_F32_PARTIAL:
-      if (BN <= 64 && a.small_smem) return launch_one<(BN <= 64 ? BN : 64), TC_EPI_F32_PARTIAL, 1>(a, kps, s);
+      if (BN <= 64 && a.small_smem) {
+        if (xcp_ok<(BN <= 64 ? BN : 64), 1>(a, kps)) return launch_one<(BN <= 64 ? BN : 64), TC_EPI_F32_PARTIAL, 1, 1>(a, kps, s);
+        return launch_one<(BN <= 64 ? BN : 64), TC_EPI_F32_PARTIAL, 1>(a, kps, s);
+      }
+      if (BN <= 64 && xcp_ok<(BN <= 64 ? BN : 64), 0>(a, kps)) return launch_one<(BN <= 64 ? BN : 64), TC_EPI_F32_PARTIAL, 0, 1>(a, kps, s);
       return launch_one<BN, TC_EPI_F32_PARTIAL>(a, kps, s);
     case TC_EPI_ARGMAX: return launch_one<BN, TC_EPI_ARGMAX>(a, kps, s);
     case TC_EPI_ARGMAX_ROWS: return launch_one<BN, TC_EPI_ARGMAX_ROWS>(a, kps, s);

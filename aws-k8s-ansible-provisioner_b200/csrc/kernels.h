@@ -82,6 +82,8 @@ struct TcGemmArgs {
   KvPrefetch prefetch;                // optional ride-along K/V prefetch
   int small_smem = 0;                 // F32_PARTIAL, bn <= 64: short stage ring so the CTA fits beside a decode-attention CTA
   int x_row0 = 0;                     // first row of X (tmap_x) this launch reads: a micro-batch of a larger buffer
+  const void* x_raw = nullptr;        // X rows [0, T) as a plain pointer (row stride K), ALREADY offset to the launch's first row:
+                                      // lets decode-sized launches fetch X with cp.async instead of the tensor map (gemm_tc.cu, XCP)
 };
 int launch_linear_tc(const TcGemmArgs& a, cudaStream_t s);
 int tc_pick_bn(int T);

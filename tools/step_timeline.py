@@ -78,6 +78,27 @@ def main():
     step0 = starts[-1]
     keep = t0 >= step0
     cls, smid, aux, t0, tw, t1 = cls[keep], smid[keep], aux[keep], t0[keep], tw[keep], t1[keep]
+    bid = ((rec[:, 0] >> 8) & 0xffffff).astype(np.int64)[keep]
+    # projection phase records (class 101): first operands landed / MMAs issued / accumulator visible, joined to the
+    # CTA's main record (class 100) by (shape word, block index, nearest earlier wait)
+    ph = cls == 101
+    ph_aux, ph_bid, ph_a, ph_b, ph_c = aux[ph], bid[ph], t0[ph], tw[ph], t1[ph]
+    main = ~ph
+    cls, smid, aux, t0, tw, t1, bid = cls[main], smid[main], aux[main], t0[main], tw[main], t1[main], bid[main]
+    phases = {}
+    for a in sorted(set(ph_aux)):
+        name = GEMM.get((a & 0xfff, (a >> 12) & 0x7ff))
+        if name is None:
+            continue
+        m100 = (cls == 100) & (aux == a)
+        rows = []
+        for i in np.nonzero(ph_aux == a)[0]:
+            cand = np.nonzero(m100 & (bid == ph_bid[i]) & (tw <= ph_a[i]) & (t1 >= ph_c[i]))[0]
+            if len(cand):
+                j = cand[np.argmax(tw[cand])]
+                rows.append((ph_a[i] - tw[j], ph_b[i] - tw[j], ph_c[i] - tw[j], t1[j] - tw[j]))
+        if rows:
+            phases.setdefault(name, []).extend(rows)
     # ---- group records into launches ----
     names, lanes = [], []
     for c, a in zip(cls, aux):
@@ -133,6 +154,13 @@ def main():
     per_layer = sum(np.median(d["handoff"]) + np.median(d["work"]) for k, d in summary.items()) + \
         (np.median(summary["norm"]["handoff"]) + np.median(summary["norm"]["work"]) if "norm" in summary else 0)
     print("sum over one layer's 9 launches (norm counted twice) of hand-off + work: %.1f us" % per_layer)
+    if phases:
+        print("\nprojection CTAs, time after their dependency wait returned (median / p90 over CTAs x layers, us):")
+        print("| kind | first operands landed | MMAs issued | accumulator visible | CTA end |")
+        print("|---|---|---|---|---|")
+        for name, rows in phases.items():
+            a = np.array(rows) / 1e3
+            print("| %s | %s |" % (name, " | ".join("%.2f / %.2f" % (np.median(a[:, k]), np.percentile(a[:, k], 90)) for k in range(4))))
     # ---- one layer, launch by launch ----
     for lane in sorted(set(r["lane"] for r in L)):
         att = [r for r in L if r["lane"] == lane and r["kind"] == "attn"]
