@@ -89,3 +89,33 @@ def kv_swizzle(pages: torch.Tensor) -> torch.Tensor:
     src = c ^ (r & 7)                  # stored[r][c] = logical[r][c ^ (r & 7)]
     out = torch.gather(x, 2, src[None, :, :, None].expand(x.shape[0], 16, 16, 8))
     return out.reshape(shp)
+
+
+def record_parity(key: str, value) -> None:
+    """Keeps the numbers a parity test printed (leading-match counts, gaps at the first mismatch, errors) in a JSON
+    file that outlives `pytest -q`: gpurun_out/parity.json on the GPU box (merged back by gpurun; copied to
+    profiles/ when committed as evidence)."""
+    import json
+    d = os.path.join(ROOT, "gpurun_out")
+    try:
+        os.makedirs(d, exist_ok=True)
+        path = os.path.join(d, "parity.json")
+        cur = {}
+        if os.path.exists(path):
+            try:
+                cur = json.load(open(path))
+            except ValueError:
+                cur = {}
+        cur[key] = value
+        json.dump(cur, open(path, "w"), indent=1, sort_keys=True)
+    except OSError:
+        pass
+
+
+def bf16_ulp_of(x: float) -> float:
+    """Size of one bf16 ulp at magnitude |x| (8 significand bits)."""
+    import math
+    x = abs(float(x))
+    if x == 0.0:
+        return 2.0 ** -133
+    return 2.0 ** (math.floor(math.log2(x)) - 7)

@@ -10,7 +10,7 @@ import numpy as np
 import pytest
 import torch
 
-from _util import ROOT, engine_config_from_arch, pkg, rel_err, rel_fro
+from _util import ROOT, bf16_ulp_of, engine_config_from_arch, pkg, record_parity, rel_err, rel_fro
 from oracle.qwen3_oracle import (QWEN3_0_6B, QWEN3_TINY, KVState, Restated, attention_explicit, hf_model, hf_state_dict,
                                  make_prompts, perturb_norm_weights, random_weights, rope_inv_freq, top2_gap)
 
@@ -289,11 +289,19 @@ def test_full_c1_greedy_and_logits(P, full):
     mism = np.nonzero(toks != gold)[0]
     n_match = 128 if len(mism) == 0 else int(mism[0])
     print("C1 greedy: %d/128 leading tokens identical to HF; worst hidden rel err %.3g" % (n_match, worst))
+    rec = {"leading_match": n_match, "of": 128, "worst_hidden_rel_err": float(worst), "last_logits_rel_err": float(lerr),
+           "last_logits_floor": float(lfloor)}
     if len(mism):
+        # north_star: identical over the first 128 tokens; the only divergence tolerated is at a step where HF's own
+        # top-2 gap is within 2 bf16 ulp of its top logit (HF's two attention paths flip such a step themselves)
         t = int(mism[0])
-        gap = top4[127 + t][0] - top4[127 + t][1]
-        assert gap <= 0.0625, "first mismatch at step %d where the oracle's top-2 gap is %.4f (not a near-tie)" % (t, gap)
-    assert n_match >= 16
+        gap = float(top4[127 + t][0] - top4[127 + t][1])
+        ulp = bf16_ulp_of(float(top4[127 + t][0]))
+        rec.update({"first_mismatch_step": t, "hf_top2_gap": gap, "gap_in_bf16_ulp_of_top1": gap / ulp})
+        record_parity("c1_batch1_prompt128", rec)
+        assert gap <= 2 * ulp, "first mismatch at step %d where the oracle's top-2 gap is %.4f = %.1f bf16 ulp (not a tie)" % (
+            t, gap, gap / ulp)
+    record_parity("c1_batch1_prompt128", rec)
     e.close()
 
 
@@ -456,38 +464,4 @@ def test_sharded_checkpoint_and_dtypes(P, tiny, tmp_path):
     assert np.array_equal(outs[0], outs[1])
 
 
-def test_full_c2_shape_against_hf(P, full):
-    """The bench workload's shape (BASELINE.json config 2: batch 64, 512-token random prompts, paged KV, CUDA-graph
-    decode with device-side token feedback) against HF itself: four of the 64 sequences are also generated by HF
-    transformers on the CPU; their greedy ids must match up to the first step where HF's own top-2 logit gap is within
-    bf16 noise, and most must match over the whole window."""
-    model, sd = full
-    arch = QWEN3_0_6B
-    B, PL, NEW = 64, 512, 24
-    prompts = make_prompts(B, PL, arch.vocab, seed=1)
-    e = make_engine(P, arch, sd, max_model_len=PL + NEW + 16, num_blocks=B * ((PL + NEW + 31) // 16) + 8, max_seqs=B,
-                    max_batch_tokens=8192, use_cuda_graphs=True)
-    sids = [e.seq_create(PL + NEW + 8) for _ in range(B)]
-    first = np.concatenate([e.prefill(sids[i:i + 16], [p.tolist() for p in prompts[i:i + 16]]) for i in range(0, B, 16)])
-    toks, _ = e.decode_run(sids, NEW - 1)
-    got = np.concatenate([first[None, :], toks], axis=0).T  # [B][NEW]
-    pick = [0, 21, 42, 63]
-    ids = prompts[pick]
-    with torch.no_grad():
-        out = model.generate(ids, attention_mask=torch.ones_like(ids), do_sample=False, max_new_tokens=NEW, min_new_tokens=NEW,
-                             pad_token_id=0, output_logits=True, return_dict_in_generate=True)
-    ref = out.sequences[:, PL:].numpy()
-    logits = torch.stack(out.logits, dim=1).float()  # [4][NEW][V]
-    gaps = top2_gap(logits)
-    full_match = 0
-    for k, b in enumerate(pick):
-        mism = np.nonzero(got[b] != ref[k])[0]
-        n = NEW if len(mism) == 0 else int(mism[0])
-        print("C2 sequence %d: %d/%d leading greedy tokens identical to HF" % (b, n, NEW))
-        if len(mism):
-            assert gaps[k, n] <= 0.0625, "sequence %d diverges at step %d where HF's top-2 gap is %.4f" % (b, n, gaps[k, n])
-        else:
-            full_match += 1
-        assert n >= 4
-    assert full_match >= 2
-    e.close()
+# The bench workload's shape (batch 64, 512-token prompts, graph decode) against HF over 128 tokens: test_parity_full_gpu.py
