@@ -346,3 +346,45 @@ def test_text_prompts_go_through_the_bpe_tokenizer(server_bpe):
     rendered = "<|im_start|>user\nWho are you?<|im_end|>\n<|im_start|>assistant\n"
     assert j3["usage"]["prompt_tokens"] == len(tok.encode(rendered).ids)
     assert j3["usage"]["prompt_tokens"] < 20
+
+
+def test_starts_with_the_argv_the_image_and_the_values_file_give():
+    """The launch boundary (llm-d-deploy.yaml:147-151,176-184): the pod runs deploy/Dockerfile's ENTRYPOINT + CMD with
+    the chart's extraArgs (deploy/values-b2serve.yaml) appended.  Exactly that argv -- only the binary's path is the
+    in-tree build instead of /opt/b2/bin -- must come up on port 8000, with no checkpoint at /models (random-init
+    weights of the served architecture, as BASELINE.json prescribes), and answer the reference's two requests."""
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    import re
+    import yaml
+    P = pkg()
+    txt = open(os.path.join(ROOT, "deploy", "Dockerfile")).read()
+    ep = json.loads(re.search(r"^ENTRYPOINT\s+(\[.*\])\s*$", txt, re.M).group(1))
+    cmd = json.loads(re.search(r"^CMD\s+(\[.*\])\s*$", txt, re.M).group(1))
+    extra = yaml.safe_load(open(os.path.join(ROOT, "deploy", "values-b2serve.yaml")))["sampleApplication"]["decode"]["extraArgs"]
+    assert ep == ["/opt/b2/bin/b2serve"]
+    exe = os.path.join(os.path.dirname(P.LIB_PATH), "b2serve")
+    proc = subprocess.Popen([exe] + cmd + extra, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
+    try:
+        port = None
+        t0 = time.time()
+        while time.time() - t0 < 300:
+            line = proc.stdout.readline()
+            if line.startswith("READY"):
+                port = int(line.split()[1])
+                break
+            if proc.poll() is not None:
+                break
+        assert port == 8000, "b2serve did not come up on the image's port: " + (proc.stderr.read()[-1500:] if proc.poll() is not None else "")
+        st, raw = call(port, "GET", "/v1/models", raw=True)
+        assert st == 200 and MODEL_ID in raw and json.loads(raw)["data"][0]["max_model_len"] == 4096
+        st, j = call(port, "POST", "/v1/completions", {"model": MODEL_ID, "prompt": "Who are you?"})
+        assert st == 200 and j["usage"]["completion_tokens"] == 16 and j["model"] == MODEL_ID
+        st, m = call(port, "GET", "/metrics", raw=True)
+        assert st == 200 and "vllm:kv_cache_usage_perc" in m
+    finally:
+        proc.terminate()
+        try:
+            proc.wait(timeout=20)
+        except Exception:
+            proc.kill()
