@@ -61,6 +61,7 @@ SIGNATURES = {
     "b2_attn_profile": (_I, [_P, C.c_int32, _I32P, C.c_int32, C.POINTER(C.c_float), C.POINTER(C.c_int64)]),
     "b2_launch_count": (C.c_int64, [_P]),
     "b2_set_tuning": (_I, [_P, C.c_int32, C.c_int64]),
+    "b2_prefix_cache_stats": (_I, [_P, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     "b2k_add_rmsnorm": (_I, [_P, _P, _I, _I, _P, _P, _I, _I, C.c_float, _P]),
     "b2k_qknorm_rope_kv": (_I, [_P, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, C.c_float, _P]),
     "b2k_silu_mul": (_I, [_P, _I, _I, _P, _I, _I, _P]),

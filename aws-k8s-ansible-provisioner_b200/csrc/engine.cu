@@ -11,7 +11,9 @@
 #include <unistd.h>
 
 #include <algorithm>
+#include <list>
 #include <map>
+#include <unordered_map>
 #include <string>
 #include <vector>
 
@@ -82,6 +84,12 @@ struct Seq {
   int32_t next_token = 0;   // greedy token the last forward produced for this sequence (host copy)
   bool next_valid = false;  // false when only the device holds it (no D2H was requested)
   std::vector<int32_t> blocks;
+  // prefix cache: chain[j] = hash of the first 16 (j + 1) prompt tokens (one entry per full page whose token ids the
+  // host has seen), pending = ids since the last page boundary, chain_open = every token so far came from a prefill
+  // call (a decode step's token lives on the device only, so the chain ends there)
+  std::vector<uint64_t> chain;
+  std::vector<int32_t> pending;
+  bool chain_open = false;
 };
 
 enum XBuf { XB_X = 0, XB_ATTN = 1, XB_ACT = 2, XB_LAST = 3, XB_COUNT = 4 };
@@ -147,6 +155,20 @@ struct b2_engine {
   int64_t num_blocks = 0;
   size_t layer_kv_elems = 0;  // elements of one layer's K (or V) pool
   std::vector<int32_t> free_blocks;
+  // Prefix cache (B2_TUNE_PREFIX_CACHE; vLLM's --enable-prefix-caching): full pages of PROMPT tokens are registered under
+  // the hash of the whole token prefix they end; a new sequence whose prompt starts with the same tokens takes those
+  // pages instead of recomputing them (reference-counted; a page nobody holds any more stays registered on an LRU list
+  // until the allocator needs it).  A hit is verified against the stored token ids and the parent page, not the hash alone.
+  bool prefix_cache = false;
+  std::vector<int32_t> blk_ref;       // sequences holding the page
+  std::vector<uint64_t> blk_hash;     // 0 = not registered
+  std::vector<int32_t> blk_parent;    // registered: the page holding the 16 tokens before it (-1 = first page)
+  std::vector<int32_t> blk_tokens;    // registered: its 16 token ids
+  std::unordered_map<uint64_t, int32_t> pc_map;
+  std::list<int32_t> pc_lru;          // registered pages with no holder, oldest first
+  std::vector<std::list<int32_t>::iterator> pc_lru_pos;
+  std::vector<char> pc_in_lru;
+  int64_t pc_queries = 0, pc_hits = 0;  // prompt tokens looked up / served from the cache
   std::vector<Seq> seqs;
   int bt_stride = 0;
 
@@ -911,6 +933,108 @@ int check_seq(b2_engine* e, int id) {
   return 0;
 }
 
+// ---- page allocator with the prefix cache in it ----
+int64_t pages_available(const b2_engine* e) { return (int64_t)e->free_blocks.size() + (int64_t)e->pc_lru.size(); }
+
+void pc_unregister(b2_engine* e, int32_t b) {
+  if (e->blk_hash[b] == 0) return;
+  auto it = e->pc_map.find(e->blk_hash[b]);
+  if (it != e->pc_map.end() && it->second == b) e->pc_map.erase(it);
+  e->blk_hash[b] = 0;
+}
+
+// a page for exclusive use: a free one, else the registered page that has gone unused the longest
+int32_t take_page(b2_engine* e) {
+  if (!e->free_blocks.empty()) {
+    const int32_t b = e->free_blocks.back();
+    e->free_blocks.pop_back();
+    e->blk_ref[b] = 1;
+    return b;
+  }
+  const int32_t b = e->pc_lru.front();
+  e->pc_lru.pop_front();
+  e->pc_in_lru[b] = 0;
+  pc_unregister(e, b);
+  e->blk_ref[b] = 1;
+  return b;
+}
+
+void release_page(b2_engine* e, int32_t b) {
+  if (--e->blk_ref[b] > 0) return;
+  e->blk_ref[b] = 0;
+  if (e->prefix_cache && e->blk_hash[b] != 0) {  // still worth something to a later prompt
+    e->pc_lru.push_back(b);
+    e->pc_lru_pos[b] = std::prev(e->pc_lru.end());
+    e->pc_in_lru[b] = 1;
+  } else {
+    pc_unregister(e, b);
+    e->free_blocks.push_back(b);
+  }
+}
+
+uint64_t pc_hash(uint64_t parent, const int32_t* tok) {
+  uint64_t h = parent ^ 0x9e3779b97f4a7c15ull;
+  for (int i = 0; i < 16; ++i) {
+    h ^= (uint64_t)(uint32_t)tok[i] + 0x9e3779b97f4a7c15ull + (h << 6) + (h >> 2);
+    h *= 0xff51afd7ed558ccdull;
+    h ^= h >> 33;
+  }
+  return h ? h : 1;  // 0 means "not registered"
+}
+
+// Leading pages of a fresh sequence's prompt that are already in the cache: the sequence drops its own pages for them
+// and holds the cached ones.  At least one token is always left to compute (its logits are the call's result).
+int pc_match(b2_engine* e, Seq& s, const int32_t* ids, int n) {
+  const int bs = e->cfg.block_size;
+  int matched = 0;
+  uint64_t h = 0;
+  int32_t parent = -1;
+  const int max_pages = (n - 1) / bs;
+  for (int j = 0; j < max_pages; ++j) {
+    h = pc_hash(h, ids + (size_t)j * bs);
+    auto it = e->pc_map.find(h);
+    if (it == e->pc_map.end()) break;
+    const int32_t b = it->second;
+    if (e->blk_parent[b] != parent || memcmp(&e->blk_tokens[(size_t)b * bs], ids + (size_t)j * bs, bs * sizeof(int32_t)) != 0) break;
+    if (e->blk_ref[b] == 0 && e->pc_in_lru[b]) {
+      e->pc_lru.erase(e->pc_lru_pos[b]);
+      e->pc_in_lru[b] = 0;
+    }
+    e->blk_ref[b] += 1;
+    release_page(e, s.blocks[j]);  // the private page reserved for these positions is not needed
+    s.blocks[j] = b;
+    s.chain.push_back(h);
+    parent = b;
+    matched += bs;
+  }
+  return matched;
+}
+
+// After a prefill call: pages of this sequence that the call's tokens completed get registered.
+void pc_register(b2_engine* e, Seq& s, const int32_t* ids, int n) {
+  const int bs = e->cfg.block_size;
+  if (!s.chain_open) return;
+  for (int i = 0; i < n; ++i) {
+    s.pending.push_back(ids[i]);
+    if ((int)s.pending.size() < bs) continue;
+    const int j = (int)s.chain.size();
+    const uint64_t h = pc_hash(j > 0 ? s.chain[j - 1] : 0, s.pending.data());
+    const int32_t b = s.blocks[j];
+    if (e->blk_hash[b] == 0 && e->pc_map.find(h) == e->pc_map.end()) {
+      e->blk_hash[b] = h;
+      e->blk_parent[b] = j > 0 ? s.blocks[j - 1] : -1;
+      // the parent must itself be the registered holder of its hash, or a later match could not verify the chain
+      if (j > 0 && (e->blk_hash[s.blocks[j - 1]] != s.chain[j - 1])) e->blk_hash[b] = 0;
+      if (e->blk_hash[b] != 0) {
+        memcpy(&e->blk_tokens[(size_t)b * bs], s.pending.data(), bs * sizeof(int32_t));
+        e->pc_map[h] = b;
+      }
+    }
+    s.chain.push_back(h);
+    s.pending.clear();
+  }
+}
+
 int ensure_logits(b2_engine* e) {
   if (e->logits) return 0;
   // rows for the padded graph bucket: a captured step runs the lm_head over bucket_batch(n) rows, and max_seqs need
@@ -1429,6 +1553,13 @@ extern "C" int b2_engine_create(const b2_config* cfg, const char* safetensors_pa
       E_CUDA(cudaMemset(e->kv_pool, 0, (size_t)2 * c.num_layers * e->layer_kv_elems * 2));
       e->free_blocks.reserve(nb);
       for (int64_t b = nb - 1; b >= 1; --b) e->free_blocks.push_back((int32_t)b);  // page 0 = null page
+      e->blk_ref.assign(nb, 0);
+      e->blk_hash.assign(nb, 0);
+      e->blk_parent.assign(nb, -1);
+      e->blk_tokens.assign((size_t)nb * c.block_size, 0);
+      e->pc_lru_pos.assign(nb, e->pc_lru.end());
+      e->pc_in_lru.assign(nb, 0);
+      e->prefix_cache = env_int("B2_PREFIX_CACHE", 0) != 0;
     }
     if (e->force_gemm_impl == 0 || e->simt_max_tokens > 0) E_TRY(ensure_logits(e));  // SIMT lm_head writes logits
     e->ev_pool.resize(2 * 400);
@@ -1511,7 +1642,7 @@ extern "C" void b2_engine_free(b2_engine* e) {
 extern "C" int b2_engine_info(b2_engine* e, int64_t* num_blocks, int64_t* free_blocks, int64_t* weight_bytes) {
   B2_REQUIRE(e, "b2_engine_info: null engine");
   if (num_blocks) *num_blocks = e->num_blocks;
-  if (free_blocks) *free_blocks = (int64_t)e->free_blocks.size();
+  if (free_blocks) *free_blocks = pages_available(e);  // cached pages nobody holds are reusable at once
   if (weight_bytes) *weight_bytes = e->weight_bytes;
   return 0;
 }
@@ -1522,8 +1653,8 @@ extern "C" int b2_seq_create(b2_engine* e, int32_t reserve_tokens, int32_t* seq_
              reserve_tokens, e->cfg.max_model_len);
   const int bs = e->cfg.block_size;
   const int need = (reserve_tokens + bs - 1) / bs;
-  if ((int)e->free_blocks.size() < need) {
-    b2_set_error("KV pool exhausted: need %d pages, %zu free", need, e->free_blocks.size());
+  if (pages_available(e) < need) {
+    b2_set_error("KV pool exhausted: need %d pages, %lld free", need, (long long)pages_available(e));
     return -12;
   }
   int id = -1;
@@ -1541,10 +1672,10 @@ extern "C" int b2_seq_create(b2_engine* e, int32_t reserve_tokens, int32_t* seq_
   s.len = 0;
   s.reserved = need * bs;
   s.blocks.clear();
-  for (int i = 0; i < need; ++i) {
-    s.blocks.push_back(e->free_blocks.back());
-    e->free_blocks.pop_back();
-  }
+  for (int i = 0; i < need; ++i) s.blocks.push_back(take_page(e));
+  s.chain.clear();
+  s.pending.clear();
+  s.chain_open = e->prefix_cache;
   *seq_id = id;
   return 0;
 }
@@ -1553,8 +1684,12 @@ extern "C" int b2_seq_free(b2_engine* e, int32_t seq_id) {
   B2_REQUIRE(e, "b2_seq_free: null engine");
   B2_TRY(check_seq(e, seq_id));
   Seq& s = e->seqs[seq_id];
-  for (int32_t b : s.blocks) e->free_blocks.push_back(b);
+  // leading pages first, so that on the LRU list a prefix outlives its continuations
+  for (auto it = s.blocks.rbegin(); it != s.blocks.rend(); ++it) release_page(e, *it);
   s.blocks.clear();
+  s.chain.clear();
+  s.pending.clear();
+  s.chain_open = false;
   s.active = false;
   s.len = 0;
   e->cur_batch.clear();
@@ -1571,6 +1706,38 @@ extern "C" int b2_seq_truncate(b2_engine* e, int32_t seq_id, int32_t new_len) {
   B2_TRY(check_seq(e, seq_id));
   Seq& s = e->seqs[seq_id];
   B2_REQUIRE(new_len >= 0 && new_len <= s.len, "b2_seq_truncate: new_len %d outside [0, %d]", new_len, s.len);
+  // Positions >= new_len will be written again.  Pages from there on that are registered in the prefix cache or held by
+  // other sequences too must not be: the sequence swaps them for private pages (copying the kept part of the page
+  // new_len falls into), and its own chain ends at the cut.
+  const int bs = e->cfg.block_size;
+  const int first = new_len / bs;
+  int need = 0;
+  for (int j = first; j < (int)s.blocks.size(); ++j)
+    if (e->blk_hash[s.blocks[j]] != 0 || e->blk_ref[s.blocks[j]] > 1) ++need;
+  if (need > 0) {
+    B2_REQUIRE(pages_available(e) >= need, "b2_seq_truncate: no free pages to un-share %d cached pages", need);
+    B2_CUDA_OK(cudaSetDevice(e->device));
+    B2_CUDA_OK(cudaStreamSynchronize(e->stream));
+    const size_t blk_elems = (size_t)e->nkv * bs * e->hd;
+    for (int j = first; j < (int)s.blocks.size(); ++j) {
+      const int32_t old_b = s.blocks[j];
+      if (e->blk_hash[old_b] == 0 && e->blk_ref[old_b] <= 1) continue;
+      const int32_t nb = take_page(e);
+      if (j == first && new_len % bs != 0) {
+        for (int l = 0; l < 2 * e->cfg.num_layers; ++l) {
+          bf16* base = e->kv_pool + (size_t)l * e->layer_kv_elems;
+          B2_CUDA_OK(cudaMemcpyAsync(base + (size_t)nb * blk_elems, base + (size_t)old_b * blk_elems, blk_elems * 2, cudaMemcpyDeviceToDevice,
+                                     e->stream));
+        }
+      }
+      s.blocks[j] = nb;
+      release_page(e, old_b);
+    }
+    B2_CUDA_OK(cudaStreamSynchronize(e->stream));
+  }
+  if ((int)s.chain.size() > first) s.chain.resize(first);
+  s.pending.clear();
+  s.chain_open = false;
   s.len = new_len;
   e->cur_batch.clear();
   return 0;
@@ -1582,16 +1749,12 @@ extern "C" int b2_prefill(b2_engine* e, const int32_t* ids, const int32_t* seq_o
   B2_REQUIRE(e->finalized, "b2_prefill: weights not finalized");
   B2_REQUIRE(nseq <= e->cfg.max_seqs, "b2_prefill: %d sequences > max_seqs %d", nseq, e->cfg.max_seqs);
   B2_CUDA_OK(cudaSetDevice(e->device));
-  const int T = seq_offsets[nseq] - seq_offsets[0];
-  B2_REQUIRE(T >= 1 && T <= e->cap_tokens && T <= e->cfg.max_batch_tokens, "b2_prefill: %d tokens exceed max_batch_tokens %d", T,
+  const int T_in = seq_offsets[nseq] - seq_offsets[0];
+  B2_REQUIRE(T_in >= 1 && T_in <= e->cap_tokens && T_in <= e->cfg.max_batch_tokens, "b2_prefill: %d tokens exceed max_batch_tokens %d", T_in,
              e->cfg.max_batch_tokens);
   const int bs = e->cfg.block_size;
-  int32_t* tok = e->h_stage;
-  int32_t* pos = tok + T;
-  int32_t* slots = pos + T;
-  int32_t* last = slots + T;
-  int32_t* bt = last + nseq;
-  int ntiles = 0;
+  // ---- validate, then let fresh sequences take what the prefix cache already holds of their prompt ----
+  std::vector<int> skip(nseq, 0);
   for (int i = 0; i < nseq; ++i) {
     B2_TRY(check_seq(e, seq_ids[i]));
     Seq& s = e->seqs[seq_ids[i]];
@@ -1599,10 +1762,32 @@ extern "C" int b2_prefill(b2_engine* e, const int32_t* ids, const int32_t* seq_o
     B2_REQUIRE(n >= 1, "b2_prefill: sequence %d has no tokens", i);
     B2_REQUIRE(s.len + n <= s.reserved, "b2_prefill: sequence %d would exceed its reservation (%d + %d > %d)", seq_ids[i], s.len, n,
                s.reserved);
-    const int row0 = seq_offsets[i] - seq_offsets[0];
+  }
+  for (int i = 0; i < nseq; ++i) {
+    Seq& s = e->seqs[seq_ids[i]];
+    const int n = seq_offsets[i + 1] - seq_offsets[i];
+    if (e->prefix_cache && s.len == 0 && s.chain_open && s.chain.empty()) {
+      skip[i] = pc_match(e, s, ids + seq_offsets[i], n);
+      s.len = skip[i];  // K/V of those positions are in the pages just taken
+      e->pc_queries += n;
+      e->pc_hits += skip[i];
+    }
+  }
+  int T = 0;
+  for (int i = 0; i < nseq; ++i) T += seq_offsets[i + 1] - seq_offsets[i] - skip[i];
+  int32_t* tok = e->h_stage;
+  int32_t* pos = tok + T;
+  int32_t* slots = pos + T;
+  int32_t* last = slots + T;
+  int32_t* bt = last + nseq;
+  int ntiles = 0, row0 = 0;
+  for (int i = 0; i < nseq; ++i) {
+    Seq& s = e->seqs[seq_ids[i]];
+    const int n = seq_offsets[i + 1] - seq_offsets[i] - skip[i];
+    const int32_t* src = ids + seq_offsets[i] + skip[i];
     for (int j = 0; j < n; ++j) {
       const int p = s.len + j;
-      tok[row0 + j] = ids[seq_offsets[i] + j];
+      tok[row0 + j] = src[j];
       pos[row0 + j] = p;
       slots[row0 + j] = s.blocks[p / bs] * bs + p % bs;
     }
@@ -1613,6 +1798,7 @@ extern "C" int b2_prefill(b2_engine* e, const int32_t* ids, const int32_t* seq_o
       B2_REQUIRE(ntiles < e->tiles_cap, "b2_prefill: too many attention tiles");
       e->h_tiles[ntiles++] = PrefillTile{row0 + j, s.len + j, std::min(64, n - j), i};
     }
+    row0 += n;
   }
   B2_CUDA_OK(cudaMemcpyAsync(e->d_tokens, tok, T * 4, cudaMemcpyHostToDevice, e->stream));
   B2_CUDA_OK(cudaMemcpyAsync(e->d_positions, pos, T * 4, cudaMemcpyHostToDevice, e->stream));
@@ -1628,9 +1814,11 @@ extern "C" int b2_prefill(b2_engine* e, const int32_t* ids, const int32_t* seq_o
   B2_CUDA_OK(cudaStreamSynchronize(e->stream));
   for (int i = 0; i < nseq; ++i) {
     Seq& s = e->seqs[seq_ids[i]];
-    s.len += seq_offsets[i + 1] - seq_offsets[i];
+    const int n = seq_offsets[i + 1] - seq_offsets[i] - skip[i];
+    s.len += n;
     s.next_token = e->h_out[i];
     s.next_valid = true;
+    if (e->prefix_cache) pc_register(e, s, ids + seq_offsets[i] + skip[i], n);  // the forward that filled the pages is complete
   }
   if (out_tokens) memcpy(out_tokens, e->h_out, nseq * 4);
   // remember them host-side too so the first decode step can seed d_tokens
@@ -1650,6 +1838,7 @@ int prepare_decode(b2_engine* e, int n, const int32_t* seq_ids, const int32_t* i
     Seq& s = e->seqs[seq_ids[i]];
     B2_REQUIRE(s.len >= 1, "decode: sequence %d has no prefilled tokens", seq_ids[i]);
     B2_REQUIRE(s.len + 1 <= s.reserved, "decode: sequence %d would exceed its reservation (%d tokens)", seq_ids[i], s.reserved);
+    s.chain_open = false;  // generated tokens are not registered in the prefix cache
     max_len = std::max(max_len, s.len + 1);
   }
   const int B = e->cfg.use_cuda_graphs ? bucket_batch(n) : n;
@@ -1835,12 +2024,32 @@ extern "C" int b2_attn_profile(b2_engine* e, int32_t nseq, const int32_t* seq_id
 
 extern "C" int64_t b2_launch_count(b2_engine* e) { return e ? e->launches : 0; }
 
+extern "C" int b2_prefix_cache_stats(b2_engine* e, int64_t* queried_tokens, int64_t* hit_tokens, int64_t* cached_pages) {
+  B2_REQUIRE(e, "b2_prefix_cache_stats: null engine");
+  if (queried_tokens) *queried_tokens = e->pc_queries;
+  if (hit_tokens) *hit_tokens = e->pc_hits;
+  if (cached_pages) *cached_pages = (int64_t)e->pc_map.size();
+  return 0;
+}
+
 extern "C" int b2_set_tuning(b2_engine* e, int32_t key, int64_t value) {
   B2_REQUIRE(e, "b2_set_tuning: null engine");
   B2_CUDA_OK(cudaSetDevice(e->device));
   B2_CUDA_OK(cudaStreamSynchronize(e->stream));
   switch (key) {
     case B2_TUNE_SKIP_MASK: e->skip_mask = (unsigned)value; break;
+    case B2_TUNE_PREFIX_CACHE:
+      e->prefix_cache = value != 0;
+      if (!e->prefix_cache) {  // forget everything: registered pages nobody holds go back to the free list
+        for (int32_t b : e->pc_lru) {
+          e->pc_in_lru[b] = 0;
+          e->free_blocks.push_back(b);
+        }
+        e->pc_lru.clear();
+        e->pc_map.clear();
+        std::fill(e->blk_hash.begin(), e->blk_hash.end(), 0);
+      }
+      break;
     case B2_TUNE_TWO_LANE:
       B2_REQUIRE(value == 0 || e->stream2 != nullptr, "b2_set_tuning: this engine was created without a second lane (B2_MB=0 or OPT)");
       e->mb_min_batch = (int)value;

@@ -59,6 +59,7 @@ struct Options {
   int eos_token_id = 151645;
   int device = 0;
   int use_graphs = 1;
+  bool prefix_caching = false;  // --enable-prefix-caching
 };
 
 static void usage() {
@@ -66,7 +67,7 @@ static void usage() {
           "usage: b2serve [MODEL] [--model M] [--served-model-name N] [--host H] [--port P] [--chat-template FILE]\n"
           "               [--max-model-len L] [--block-size 16] [--gpu-memory-utilization F] [--max-num-seqs N]\n"
           "               [--max-num-batched-tokens T] [--num-gpu-blocks-override N] [--seed S] [--load-format auto|dummy|safetensors]\n"
-          "               [--eos-token-id ID] [--device D] [--enforce-eager] [--tokenizer FILE_OR_DIR]\n"
+          "               [--eos-token-id ID] [--device D] [--enforce-eager] [--tokenizer FILE_OR_DIR] [--enable-prefix-caching]\n"
           "       b2serve --render-chat-template FILE < {\"messages\": ...}     (no GPU)\n"
           "       b2serve --tokenize TOKENIZER_JSON < {\"text\": ...} per line  (no GPU)\n");
 }
@@ -101,10 +102,12 @@ static bool parse_args(int argc, char** argv, Options& o) {
     else if (key == "--enforce-eager") o.use_graphs = 0;
     else if (key == "--help" || key == "-h") { usage(); exit(0); }
     else if (key == "--tokenizer") o.tokenizer_path = V("--tokenizer");
+    else if (key == "--enable-prefix-caching") o.prefix_caching = true;
+    else if (key == "--no-enable-prefix-caching") o.prefix_caching = false;
     else if (key == "--dtype" || key == "--tensor-parallel-size" || key == "--trust-remote-code" || key == "--disable-log-requests" ||
-             key == "--kv-cache-dtype" || key == "--download-dir" || key == "--enable-prefix-caching") {
+             key == "--kv-cache-dtype" || key == "--download-dir") {
       // accepted for chart compatibility; this build is bf16, one GPU per replica
-      if (!has_inl && key != "--trust-remote-code" && key != "--disable-log-requests" && key != "--enable-prefix-caching" && i + 1 < argc) ++i;
+      if (!has_inl && key != "--trust-remote-code" && key != "--disable-log-requests" && i + 1 < argc) ++i;
     } else if (a.rfind("--", 0) == 0) { fprintf(stderr, "b2serve: unknown flag %s\n", a.c_str()); return false; }
     else if (a == "serve") continue;  // `vllm serve MODEL` style
     else o.model = a;
@@ -347,6 +350,8 @@ class Scheduler {
     b2_engine_info(e_, &nb, &fb, nullptr);
     m_->kv_total_blocks = std::max<int64_t>(1, nb - 1);
     m_->kv_used_blocks = std::max<int64_t>(0, nb - 1 - fb);
+    int64_t q = 0, h = 0;
+    if (b2_prefix_cache_stats(e_, &q, &h, nullptr) == 0) { m_->prefix_queries = q; m_->prefix_hits = h; }
     m_->running = (int64_t)(running_.size() + prefilling_.size());
   }
 
@@ -867,6 +872,10 @@ int main(int argc, char** argv) {
   app.metrics.model = app.opt.served_name;
   int64_t nb = 0, fb = 0, wb = 0;
   b2_engine_info(app.engine, &nb, &fb, &wb);
+  if (app.opt.prefix_caching && b2_set_tuning(app.engine, B2_TUNE_PREFIX_CACHE, 1) != 0) {
+    fprintf(stderr, "b2serve: --enable-prefix-caching: %s\n", b2_last_error());
+    return 1;
+  }
   app.sched.reset(new Scheduler(app.engine, app.cfg, app.opt, &app.metrics));
   app.sched->start();
   b2http::Server srv(app.opt.host, app.opt.port, [&app](const b2http::Request& r, b2http::Conn& c) { handle(app, r, c); });

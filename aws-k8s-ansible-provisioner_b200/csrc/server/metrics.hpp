@@ -50,6 +50,7 @@ struct Registry {
   std::atomic<int64_t> prompt_tokens{0}, generation_tokens{0};
   std::atomic<int64_t> success_stop{0}, success_length{0}, success_abort{0};
   std::atomic<int64_t> kv_used_blocks{0}, kv_total_blocks{1};
+  std::atomic<int64_t> prefix_queries{0}, prefix_hits{0};  // prompt tokens looked up in / served from the prefix cache
   Histogram ttft{{0.001, 0.005, 0.01, 0.02, 0.04, 0.06, 0.08, 0.1, 0.25, 0.5, 0.75, 1.0, 2.5, 5.0, 7.5, 10.0, 20.0, 40.0, 80.0, 160.0, 640.0, 2560.0}};
   Histogram itl{{0.01, 0.025, 0.05, 0.075, 0.1, 0.15, 0.2, 0.3, 0.4, 0.5, 0.75, 1.0, 2.5, 5.0, 7.5, 10.0, 20.0, 40.0, 80.0}};
   Histogram e2e{{0.3, 0.5, 0.8, 1.0, 1.5, 2.0, 2.5, 5.0, 10.0, 15.0, 20.0, 30.0, 40.0, 50.0, 60.0, 120.0, 240.0, 480.0, 960.0, 1920.0, 7680.0}};
@@ -72,6 +73,8 @@ struct Registry {
     gauge("vllm:gpu_cache_usage_perc", "GPU KV-cache usage (legacy name). 1 means 100 percent usage.", usage);
     counter("vllm:prompt_tokens_total", "Number of prefill tokens processed.", prompt_tokens.load());
     counter("vllm:generation_tokens_total", "Number of generation tokens processed.", generation_tokens.load());
+    counter("vllm:prefix_cache_queries_total", "Prefix cache queries, in number of queried tokens.", prefix_queries.load());
+    counter("vllm:prefix_cache_hits_total", "Prefix cache hits, in number of cached tokens.", prefix_hits.load());
     o += "# HELP vllm:request_success_total Count of successfully processed requests.\n# TYPE vllm:request_success_total counter\n";
     o += "vllm:request_success_total{" + L + ",finished_reason=\"stop\"} " + std::to_string(success_stop.load()) + "\n";
     o += "vllm:request_success_total{" + L + ",finished_reason=\"length\"} " + std::to_string(success_length.load()) + "\n";

@@ -177,12 +177,19 @@ class Engine:
         check(self.lib.b2_attn_profile(self.h, len(sids), _p32(sids), int(reps), C.byref(ms), C.byref(nbytes)), self.lib)
         return ms.value, int(nbytes.value)
 
-    def set_tuning(self, skip_mask: int | None = None, two_lane_min_batch: int | None = None) -> None:
+    def prefix_cache_stats(self) -> dict:
+        a, b, c = C.c_int64(), C.c_int64(), C.c_int64()
+        check(self.lib.b2_prefix_cache_stats(self.h, C.byref(a), C.byref(b), C.byref(c)), self.lib)
+        return {"queried_tokens": a.value, "hit_tokens": b.value, "cached_pages": c.value}
+
+    def set_tuning(self, skip_mask: int | None = None, two_lane_min_batch: int | None = None, prefix_cache: bool | None = None) -> None:
         """Run-time measurement knobs (include/b2_engine.h, b2_set_tuning); drops the captured decode graphs."""
         if skip_mask is not None:
             check(self.lib.b2_set_tuning(self.h, 0, int(skip_mask)), self.lib)
         if two_lane_min_batch is not None:
             check(self.lib.b2_set_tuning(self.h, 1, int(two_lane_min_batch)), self.lib)
+        if prefix_cache is not None:
+            check(self.lib.b2_set_tuning(self.h, 2, 1 if prefix_cache else 0), self.lib)
 
     def launch_count(self) -> int:
         return int(self.lib.b2_launch_count(self.h))

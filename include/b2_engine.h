@@ -129,10 +129,18 @@ int  b2_get_hidden(b2_engine* e, int32_t layer, int32_t ntokens, uint16_t* out_b
  * call drops the captured decode graphs, so the next step re-captures with the new setting.
  *   B2_TUNE_SKIP_MASK   bit k set = kernel class k (b2_kernel_class order) is left out of the step: timing only,
  *                       the outputs are then meaningless
+ *   B2_TUNE_PREFIX_CACHE  1 = full pages of prompt tokens are kept under the hash of the token prefix they end, and
+ *                       b2_prefill lets a fresh sequence whose prompt starts with the same tokens take those pages
+ *                       instead of recomputing them (vLLM's --enable-prefix-caching; environment B2_PREFIX_CACHE).
+ *                       Results are unchanged: the cached K/V are the bits the same prefill would write.  0 = off and
+ *                       forget what was cached (the default)
  *   B2_TUNE_TWO_LANE    smallest padded decode batch that runs as two half-batch lanes (0 = never, the default;
  *                       environment B2_MB) */
-enum b2_tuning_key { B2_TUNE_SKIP_MASK = 0, B2_TUNE_TWO_LANE = 1 };
+enum b2_tuning_key { B2_TUNE_SKIP_MASK = 0, B2_TUNE_TWO_LANE = 1, B2_TUNE_PREFIX_CACHE = 2 };
 int  b2_set_tuning(b2_engine* e, int32_t key, int64_t value);
+/* Prefix cache counters since the engine was created: prompt tokens looked up, prompt tokens served from cached pages,
+ * pages currently registered (any pointer may be NULL). */
+int  b2_prefix_cache_stats(b2_engine* e, int64_t* queried_tokens, int64_t* hit_tokens, int64_t* cached_pages);
 
 /* Sampling for the API surface (temperature / top-k / top-p over the last logits). */
 typedef struct b2_sampling {

@@ -465,3 +465,65 @@ def test_sharded_checkpoint_and_dtypes(P, tiny, tmp_path):
 
 
 # The bench workload's shape (batch 64, 512-token prompts, graph decode) against HF over 128 tokens: test_parity_full_gpu.py
+
+
+def test_prefix_cache_reuses_prompt_pages(P, tiny):
+    """vLLM's --enable-prefix-caching in the engine (the router's prefix affinity needs it): a second
+    prompt that shares a 448-token prefix with an earlier one prefills only its tail, gives the same greedy ids as the
+    cold run, and pages are neither leaked nor rewritten while shared."""
+    model, sd = tiny
+    arch = QWEN3_TINY
+    e = make_engine(P, arch, sd, max_model_len=640, num_blocks=200, max_seqs=8, max_batch_tokens=1024, use_cuda_graphs=True)
+    g = torch.Generator().manual_seed(31)
+    prefix = torch.randint(0, arch.vocab, (448,), generator=g).tolist()
+    tails = [torch.randint(0, arch.vocab, (40,), generator=g).tolist() for _ in range(3)]
+
+    def run(prompt, steps=12):
+        sid = e.seq_create(len(prompt) + steps + 4)
+        l0 = e.launch_count()
+        first = int(e.prefill([sid], [prompt])[0])
+        toks, _ = e.decode_run([sid], steps)
+        return sid, [first] + toks[:, 0].tolist(), l0
+
+    free0 = e.info()["free_blocks"]
+    cold = []
+    for t in tails:  # cache off: the reference streams
+        sid, out, _ = run(prefix + t)
+        cold.append(out)
+        e.seq_free(sid)
+    assert e.info()["free_blocks"] == free0
+    e.set_tuning(prefix_cache=True)
+    sid_a, out_a, _ = run(prefix + tails[0])
+    st = e.prefix_cache_stats()
+    assert out_a == cold[0] and st["hit_tokens"] == 0 and st["queried_tokens"] == 488 and st["cached_pages"] == 488 // 16
+    # while A is alive: B shares A's 28 prefix pages, C too; both only compute their 40-token tails (+ nothing of the prefix)
+    sid_b, out_b, _ = run(prefix + tails[1])
+    st = e.prefix_cache_stats()
+    assert st["hit_tokens"] == 448, st
+    assert out_b == cold[1], "a prompt served from cached pages must give the cold run's tokens"
+    e.seq_free(sid_a)  # B still holds the pages
+    sid_c, out_c, _ = run(prefix + tails[2])
+    assert out_c == cold[2] and e.prefix_cache_stats()["hit_tokens"] == 896
+    # the very same prompt again: everything but the last page's worth is a hit, the result is the same
+    sid_d, out_d, _ = run(prefix + tails[1])
+    assert out_d == cold[1] and e.prefix_cache_stats()["hit_tokens"] == 896 + 480
+    # truncating into the shared prefix un-shares those pages for this sequence only: B keeps decoding what it decoded
+    e.seq_truncate(sid_d, 100)
+    e.prefill([sid_d], [[7] * 20])  # rewrites positions 100..119 of D's private copies
+    sid_e, out_e, _ = run(prefix + tails[1])
+    assert out_e == cold[1], "pages shared with a truncated sequence were modified"
+    for s in (sid_b, sid_c, sid_d, sid_e):
+        e.seq_free(s)
+    assert e.info()["free_blocks"] == free0, "pages leaked (cached pages nobody holds count as free)"
+    # a pool too small to keep everything: old cached pages are evicted, nothing breaks
+    many = [e.seq_create(600) for _ in range(5)]
+    for s in many:
+        e.prefill([s], [torch.randint(0, arch.vocab, (590,), generator=g).tolist()])
+    for s in many:
+        e.seq_free(s)
+    sid_f, out_f, _ = run(prefix + tails[0])
+    assert out_f == cold[0]
+    e.seq_free(sid_f)
+    e.set_tuning(prefix_cache=False)
+    assert e.prefix_cache_stats()["cached_pages"] == 0 and e.info()["free_blocks"] == free0
+    e.close()

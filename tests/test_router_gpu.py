@@ -54,7 +54,8 @@ def cluster(tmp_path_factory):
     for i in range(2):
         reps.append(subprocess.Popen([os.path.join(bindir, "b2serve"), str(d), "--served-model-name", MODEL_ID, "--port", "0", "--host",
                                       "127.0.0.1", "--device", str(i % ngpu), "--max-model-len", "512", "--max-num-seqs", "16",
-                                      "--num-gpu-blocks-override", "256", "--max-num-batched-tokens", "256", "--eos-token-id", "-1"],
+                                      "--num-gpu-blocks-override", "256", "--max-num-batched-tokens", "256", "--eos-token-id", "-1",
+                                      "--enable-prefix-caching"],
                                      stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True))
     ports = [wait_ready(p, "b2serve") for p in reps]
     rt = subprocess.Popen([os.path.join(bindir, "b2route"), "--port", "0", "--host", "127.0.0.1", "--scrape-interval-ms", "100", "--backends",
@@ -130,6 +131,37 @@ def test_stream_relayed_in_order_and_complete(cluster):
         assert js[-1]["choices"][0]["finish_reason"] == "length" and all(j["choices"][0]["finish_reason"] is None for j in js[:-1])
         return "".join(j["choices"][0]["text"] for j in js)
     assert text_of(via) == text_of(direct) and len(text_of(via)) > 0
+
+
+def test_prefix_affinity_lands_on_cached_pages(cluster):
+    """What the router's prefix policy is for: requests that share a prompt prefix are sent to the replica that served it
+    last, and that replica (started with --enable-prefix-caching) prefills only the new tail -- its
+    vllm:prefix_cache_hits_total moves, the other replica's does not, and the text is what a cold replica gives."""
+    port = cluster["router"]
+    shared = list(range(300, 300 + 256))
+
+    def hits():
+        out = []
+        for p in cluster["ports"]:
+            m = call(p, "GET", "/metrics", raw=True)[1]
+            out.append(sum(float(l.split()[-1]) for l in m.splitlines() if l.startswith("vllm:prefix_cache_hits_total")))
+        return out
+    h0 = hits()
+    texts = []
+    for k in range(4):
+        body = {"model": MODEL_ID, "prompt": shared + [900 + k, 901 + k, 902 + k], "max_tokens": 6, "temperature": 0, "ignore_eos": True}
+        st, j = call(port, "POST", "/v1/completions", body)
+        assert st == 200
+        texts.append(j["choices"][0]["text"])
+    h1 = hits()
+    gained = [b - a for a, b in zip(h0, h1)]
+    # 240, not 256, tokens per request: the replica prefills in chunks of --max-num-batched-tokens 256 and a prefill call
+    # always computes at least its own last token
+    assert sorted(gained) == [0.0, 3 * 240.0], "three of the four requests should have found the prefix cached on ONE replica: %s" % gained
+    # the same request sent straight to the replica that never saw the prefix: same greedy text (cached pages hold the same bits)
+    cold = cluster["ports"][gained.index(0.0)]
+    body = {"model": MODEL_ID, "prompt": shared + [903, 904, 905], "max_tokens": 6, "temperature": 0, "ignore_eos": True}
+    assert call(cold, "POST", "/v1/completions", body)[1]["choices"][0]["text"] == texts[3]
 
 
 def test_failover_to_the_surviving_replica(cluster):
