@@ -66,6 +66,8 @@ SIGNATURES = {
     "b2k_qknorm_rope_kv": (_I, [_P, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, C.c_float, _P]),
     "b2k_silu_mul": (_I, [_P, _I, _I, _P, _I, _I, _P]),
     "b2k_linear": (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _I, _P]),
+    "b2k_gateup_swiglu": (_I, [_P, _P, _P, _I, _I, _I, _P]),
+    "b2k_qkv_rope": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, C.c_float, _P]),
     "b2k_debug_step_trace": (_I, [_P]),
     "b2k_debug_gemm_trace": (_I, [_P]),
     "b2k_debug_chain_trace": (_I, [_P]),

@@ -67,8 +67,26 @@ extern "C" int b2k_debug_step_trace(void* dev_u64_buf) {
   unsigned long long* b = (unsigned long long*)dev_u64_buf;
   CAPI_TRY(step_trace_set_elementwise(b));
   CAPI_TRY(step_trace_set_gemm(b));
+  CAPI_TRY(step_trace_set_pair(b));
   return step_trace_set_attn(b);
 }
+extern "C" int b2k_gateup_swiglu(const void* x, const void* w_gu, void* act, int T, int I, int K, void* stream) {
+  B2_REQUIRE(x && w_gu && act, "b2k_gateup_swiglu: null pointer");
+  CUtensorMap tm;
+  CAPI_TRY(b2_make_tmap_bf16(&tm, w_gu, (uint64_t)2 * I, (uint64_t)K, (uint64_t)K, 64));
+  return launch_gateup_swiglu(tm, (const bf16*)x, (bf16*)act, T, I, K, (cudaStream_t)stream);
+}
+
+extern "C" int b2k_qkv_rope(const void* x, const void* w_qkv, const void* qnorm_w, const void* knorm_w, const void* cos_sin,
+                            const int32_t* positions, const int32_t* slots, void* q_out, void* k_pages, void* v_pages, int T, int nq, int nkv,
+                            int K, int block_size, float eps, void* stream) {
+  B2_REQUIRE(x && w_qkv && q_out && k_pages && v_pages, "b2k_qkv_rope: null pointer");
+  CUtensorMap tm;
+  CAPI_TRY(b2_make_tmap_bf16(&tm, w_qkv, (uint64_t)(nq + 2 * nkv) * 128, (uint64_t)K, (uint64_t)K, 128));
+  return launch_qkv_rope(tm, (const bf16*)x, (const bf16*)qnorm_w, (const bf16*)knorm_w, (const bf16*)cos_sin, positions, slots, (bf16*)q_out,
+                         (bf16*)k_pages, (bf16*)v_pages, T, nq, nkv, K, block_size, eps, (cudaStream_t)stream);
+}
+
 extern "C" int b2k_debug_gemm_trace(void* dev_u64_buf) { return tc_set_trace((unsigned long long*)dev_u64_buf); }
 extern "C" int b2k_debug_chain_trace(void* dev_u64_buf) { return chain_set_trace((unsigned long long*)dev_u64_buf); }
 extern "C" int b2k_debug_fused_trace(void* dev_u64_buf) { return fused_chain_set_trace((unsigned long long*)dev_u64_buf); }

@@ -75,6 +75,7 @@ struct LayerW {
   bf16 *bqkv = nullptr, *bo = nullptr, *ln1_b = nullptr, *ln2_b = nullptr, *b1 = nullptr, *b2 = nullptr;
   CUtensorMap tm_qkv, tm_o, tm_gu, tm_d;
   CUtensorMap tm_o32, tm_gu96, tm_d32;  // narrow-box maps of the fused chain (chain_cluster.cu)
+  CUtensorMap tm_gu64;                  // 64-row box: gate rows and up rows of one SwiGLU tile (gemm_pair.cu)
 };
 
 struct Seq {
@@ -237,6 +238,7 @@ struct b2_engine {
                                           // attention's CTAs (measured slower: 1.869 vs 1.832 ms/step at C2 -- its weight
                                           // prefetch competes with the tail of the K/V stream)
   int use_chain = 0;  // B2_CHAIN: 0 separate kernels (default, fastest measured), 1 chain.cu, 2 chain_cluster.cu
+  int use_pair = 1;   // B2_PAIR: bit 0 gate/up + SwiGLU, bit 1 QKV + QK-norm/RoPE/KV write as fused cluster-pair launches (gemm_pair.cu)
 
   // two-lane decode (B2_MB, see forward()): second stream, its own partials and attention scratch, fork/join events
   int mb_min_batch = 0;  // padded decode batches of at least this many rows (and at most 128) run as two lanes; 0 = never
@@ -654,9 +656,19 @@ int forward_layers(b2_engine* e, const Lane& ln, int T, int ntiles) {
       if (!k.skip()) B2_TRY(launch_add_rmsnorm(h, delta, L.ln1, x, T, H, c.rms_eps, st, tag));
     }
     if (l > 0) dbg_capture(e, l, e->h, T);
-    ActIn qkv = linear(e, ln, B2K_GEMM_QKV, XB_X, x, L.wqkv, L.tm_qkv, qkvb, T, e->qkv_size, H, &rc, prefetch_for(l, 3));
-    B2_TRY(rc);
-    {
+    // decode-sized forwards: the fused cluster-pair launches of gemm_pair.cu take the place of (projection, element-wise
+    // kernel) pairs where the model's shapes allow it
+    const bool pair_ok = ntiles == 0 && !ln.beside_attention && e->force_gemm_impl != 0 && T > e->simt_max_tokens && pair_shapes_ok(T, H) &&
+                         !(e->debug_flags & 1) && e->kv_l2_budget <= 0;
+    if (pair_ok && (e->use_pair & 2) && c.arch == B2_ARCH_QWEN3 && e->native_geom && e->rotary_dim == 128 && L.qnorm != nullptr &&
+        !((e->skip_mask >> B2K_ROPE_KV) & 1u)) {
+      KL k(e, B2K_GEMM_QKV);
+      if (!k.skip())
+        B2_TRY(launch_qkv_rope(L.tm_qkv, x, L.qnorm, L.knorm, e->cos_sin, positions, slots, qrot, kp, vp, T, e->nq, e->nkv, H, c.block_size,
+                               c.rms_eps, st, tag));
+    } else {
+      ActIn qkv = linear(e, ln, B2K_GEMM_QKV, XB_X, x, L.wqkv, L.tm_qkv, qkvb, T, e->qkv_size, H, &rc, prefetch_for(l, 3));
+      B2_TRY(rc);
       KL k(e, B2K_ROPE_KV);
       if (!k.skip()) B2_TRY(launch_qknorm_rope_kv(qkv, L.qnorm, L.knorm, e->cos_sin, positions, slots, qrot, kp, vp, T,
                                    e->nq, e->nkv, e->hd, c.block_size, c.rms_eps, st, e->rotary_dim, nullptr, 1.0f, tag));
@@ -678,9 +690,12 @@ int forward_layers(b2_engine* e, const Lane& ln, int T, int ntiles) {
       KL k(e, B2K_NORM);
       if (!k.skip()) B2_TRY(launch_add_rmsnorm(h, o, L.ln2, x, T, H, c.rms_eps, st, tag));
     }
-    ActIn gu = linear(e, ln, B2K_GEMM_GATEUP, XB_X, x, L.wgu, L.tm_gu, gub, T, 2 * I, H, &rc, prefetch_for(l + 1, 1));
-    B2_TRY(rc);
-    {
+    if (pair_ok && (e->use_pair & 1) && I % 64 == 0 && !((e->skip_mask >> B2K_ACT) & 1u)) {
+      KL k(e, B2K_GEMM_GATEUP);
+      if (!k.skip()) B2_TRY(launch_gateup_swiglu(L.tm_gu64, x, act, T, I, H, st, tag));
+    } else {
+      ActIn gu = linear(e, ln, B2K_GEMM_GATEUP, XB_X, x, L.wgu, L.tm_gu, gub, T, 2 * I, H, &rc, prefetch_for(l + 1, 1));
+      B2_TRY(rc);
       KL k(e, B2K_ACT);
       if (!k.skip()) B2_TRY(launch_silu_mul(gu, act, T, I, st, tag));
     }
@@ -1351,6 +1366,7 @@ extern "C" int b2_engine_create(const b2_config* cfg, const char* safetensors_pa
   // 0 separate kernels (default: fastest measured), 1 eight-step chain kernel (chain.cu), 2 fused four-step cluster
   // chain (chain_cluster.cu); 1 and 2 are kept as measured experiments with parity tests
   e->use_chain = env_int("B2_CHAIN", 0);
+  e->use_pair = env_int("B2_PAIR", 3);
   e->o_small_smem = env_int("B2_O_SMALL", 0);
   // Off by default: measured on B200 at C2 (ms/step) 0 MB 2.22, 40 MB 2.24, 72 MB 2.33, 100 MB 2.38 --
   // un-paced prefetch bursts queue ahead of the projections' own latency-critical weight loads.
@@ -1489,6 +1505,7 @@ extern "C" int b2_engine_create(const b2_config* cfg, const char* safetensors_pa
       E_TRY(b2_make_tmap_bf16(&L.tm_gu, L.wgu, e->gu_rows, H, H, 128));
       E_TRY(b2_make_tmap_bf16(&L.tm_o32, L.wo, H, e->q_size, e->q_size, 32));
       E_TRY(b2_make_tmap_bf16(&L.tm_gu96, L.wgu, e->gu_rows, H, H, 96));
+      E_TRY(b2_make_tmap_bf16(&L.tm_gu64, L.wgu, e->gu_rows, H, H, 64));
       E_TRY(b2_make_tmap_bf16(&L.tm_d32, L.wd, H, I, I, 32));
       E_TRY(b2_make_tmap_bf16(&L.tm_d, L.wd, H, I, I, 128));
     }

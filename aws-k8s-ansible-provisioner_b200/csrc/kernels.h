@@ -91,6 +91,15 @@ int tc_set_trace(unsigned long long* dev_buf);  // diagnostics: per-CTA phase ti
 // choose a split-K factor so that tiles * splits fills the SMs (each split gets >= 1 k-block)
 int tc_pick_nsplit(int T, int N, int K, int num_sms);
 
+// ---- gemm_pair.cu: a projection and the element-wise kernel behind it in one launch (clusters of two CTAs split K and
+//      exchange accumulator halves through distributed shared memory); at most 64 tokens, K <= 1024 ----
+bool pair_shapes_ok(int T, int K);
+int launch_gateup_swiglu(const CUtensorMap& tm_gu64, const bf16* x, bf16* act, int T, int I, int K, cudaStream_t s, int tag = 0);
+int launch_qkv_rope(const CUtensorMap& tm_qkv, const bf16* x, const bf16* qw, const bf16* kw, const bf16* cos_sin, const int32_t* positions,
+                    const int32_t* slots, bf16* q_out, bf16* k_pages, bf16* v_pages, int T, int nq, int nkv, int K, int block_size,
+                    float eps, cudaStream_t s, int tag = 0);
+int step_trace_set_pair(unsigned long long* dev_buf);
+
 // ---- chain.cu ----
 // The eight dependent steps between two decode-attention passes as one persistent kernel
 // (step numbers: 0 O-proj, 1 add+norm, 2 gate-up, 3 SwiGLU, 4 down, 5 add+norm, 6 QKV, 7 QK-norm/RoPE/KV).

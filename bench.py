@@ -378,11 +378,11 @@ def run_b200(args, rank, world, local, dist):
     peak, peak_kind = measured_peaks()
     achieved = step_pass_bytes / (attn_ms_in_step / 1e3) / 1e9
     achieved_burst = burst_bytes / (attn_ms_burst / 1e3) / 1e9
-    # DRAM traffic of one pass, from the committed ncu --set full capture (taken at another context:
-    # scaled by its own traffic/algorithmic ratio, which is what the figure is for)
+    # DRAM traffic of one pass, from the committed ncu --set full capture (context 641; scaled to this context by its
+    # own traffic/algorithmic ratio, which is what the figure is for)
     traffic = None
     try:
-        with open(os.path.join(ROOT, "profiles", "r01_c_attn_traffic.json")) as f:
+        with open(os.path.join(ROOT, "profiles", "r02_attn_traffic.json")) as f:
             tj = json.load(f)
         traffic = step_pass_bytes * (tj["dram_bytes_read"] + tj["dram_bytes_write"]) / tj["algorithmic_bytes"]
     except (OSError, KeyError, ValueError):
@@ -405,7 +405,7 @@ def run_b200(args, rank, world, local, dist):
         "repeats": REPEATS, "ms_per_step_runs": [round(m / K, 5) for m in ms_runs],
         "roofline": {"bound": "hbm", "kernel": "attn_decode_kernel (one layer's pass)", "achieved": achieved, "peak": peak,
                      "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-                     "traffic_source": "ncu capture at context 520, ratio 1.05 applied", "peak_kind": peak_kind,
+                     "traffic_source": "ncu --set full capture at context 641 (profiles/r02_attn_traffic.json): DRAM read+write = 1.024 x algorithmic, applied to this context", "peak_kind": peak_kind,
                      "how": "in-step: (step - step without the attention class) / layers",
                      "bytes_per_launch": step_pass_bytes, "ms_per_launch": attn_ms_in_step, "context": s_mean,
                      "ms_per_step_without_attention": ms_noattn / K,

@@ -211,6 +211,16 @@ int b2k_silu_mul(const void* gu, int gu_is_f32, int nsplit, void* act_bf16, int 
 int b2k_linear(const void* x_bf16, const void* w_bf16, void* out, int out_is_f32, int nsplit,
                int T, int N, int K, int impl, void* stream);
 
+/* The two fused projections of a decode step (csrc/gemm_pair.cu), T <= 64 tokens, K <= 1024 in steps of 128:
+ *   b2k_gateup_swiglu: act[T][I] = bf16(bf16(silu(g)) * u) with g | u = bf16(x . Wgu^T), Wgu [2I][K] = gate rows then up
+ *                      rows (HF:...:81-83); the [T][2I] intermediate is never written
+ *   b2k_qkv_rope:      b2k_linear with Wqkv [(nq + 2 nkv) * 128][K] followed by b2k_qknorm_rope_kv, in one launch
+ * Same rounding points as the separate kernels; the fp32 sum of a dot product is formed from two K halves. */
+int b2k_gateup_swiglu(const void* x_bf16, const void* w_gu_bf16, void* act_bf16, int T, int I, int K, void* stream);
+int b2k_qkv_rope(const void* x_bf16, const void* w_qkv_bf16, const void* qnorm_w, const void* knorm_w, const void* cos_sin,
+                 const int32_t* positions, const int32_t* slots, void* q_out, void* k_pages, void* v_pages, int T, int nq,
+                 int nkv, int K, int block_size, float eps, void* stream);
+
 /* Diagnostics (tools/step_timeline.py): register a device buffer of uint64 in which thread 0 of every CTA of every
  * kernel on the decode path appends one 4-word record {class | blockIdx << 8 | smid << 32 | aux << 40, CTA start,
  * dependency wait returned, CTA end} in %globaltimer ns.  The caller sets buf[0] = 0 (record counter) and

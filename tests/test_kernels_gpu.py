@@ -220,6 +220,92 @@ def test_linear_splitk_partials(lib, T, N, K, ns):
         assert rel_err(out[s].cpu(), part) < 2e-5, "split %d" % s
 
 
+@pytest.mark.parametrize("T", [64, 33, 32, 5, 1])
+def test_gateup_swiglu_fused(lib, T):
+    """gemm_pair.cu: gate/up projection + SwiGLU in one launch (a pair of CTAs per tile splits K and exchanges halves of
+    the accumulator through distributed shared memory).  Against the two-kernel path's arithmetic: g | u = bf16(x . W^T),
+    act = bf16(bf16(silu(g)) * u).  The projection's fp32 sum is formed in another order than torch's, so g and u may be
+    off by one bf16 ulp now and then, which the product can turn into two."""
+    I, K = 3072, 1024
+    x = bf(T, K, seed=21)
+    w = bf(2 * I, K, scale=0.05, seed=22)
+    act = torch.full((T, I), float("nan"), dtype=torch.bfloat16, device="cuda")
+    chk(lib, lib.b2k_gateup_swiglu(ptr(dv(x)), ptr(dv(w)), ptr(act), T, I, K, cuda_stream_ptr()))
+    gu = (x.float() @ w.float().t()).to(torch.bfloat16)
+    ref = torch.nn.functional.silu(gu[:, :I]) * gu[:, I:]
+    assert_bf16_close(act, ref, 2, 0.05, "fused gate/up + SwiGLU, T=%d" % T, abs_floor=2e-3)
+    # bit-identical run to run
+    act2 = torch.empty_like(act)
+    chk(lib, lib.b2k_gateup_swiglu(ptr(dv(x)), ptr(dv(w)), ptr(act2), T, I, K, cuda_stream_ptr()))
+    assert torch.equal(act, act2)
+    # and against the library's own two-kernel path (same rounding points; only the order of the fp32 sum differs)
+    g2 = torch.empty(T, 2 * I, dtype=torch.bfloat16, device="cuda")
+    a2 = torch.empty(T, I, dtype=torch.bfloat16, device="cuda")
+    chk(lib, lib.b2k_linear(ptr(dv(x)), ptr(dv(w)), ptr(g2), 0, 1, T, 2 * I, K, 1, cuda_stream_ptr()))
+    chk(lib, lib.b2k_silu_mul(ptr(g2), 0, 1, ptr(a2), T, I, cuda_stream_ptr()))
+    assert_bf16_close(act, a2, 2, 0.02, "fused vs separate kernels", abs_floor=2e-3)
+
+
+@pytest.mark.parametrize("T", [64, 40, 17, 1])
+def test_qkv_rope_fused(lib, T):
+    """gemm_pair.cu: QKV projection + QK-norm + RoPE + KV page write in one launch, against b2k_linear followed by
+    b2k_qknorm_rope_kv (the path it replaces) and against the oracle's functions."""
+    a = QWEN3_0_6B
+    nq, nkv, hd, bs, K = a.num_q_heads, a.num_kv_heads, a.head_dim, 16, a.hidden
+    N = (nq + 2 * nkv) * hd
+    nblocks = (T + bs - 1) // bs + 3
+    g = torch.Generator().manual_seed(23)
+    x = bf(T, K, seed=24)
+    w = bf(N, K, scale=0.05, seed=25)
+    qw = (1 + 0.25 * torch.randn(hd, generator=g)).to(torch.bfloat16)
+    kw = (1 + 0.25 * torch.randn(hd, generator=g)).to(torch.bfloat16)
+    positions = torch.randint(0, 4000, (T,), generator=g, dtype=torch.int32)
+    slots = torch.randperm(nblocks * bs, generator=g)[:T].to(torch.int32)
+    if T > 3:
+        slots[3] = -1
+    cos, sin = rope_cos_sin(a, torch.arange(4096)[None, :])
+    table = torch.cat([cos[0, :, :64], sin[0, :, :64]], dim=-1).contiguous()
+    dx, dw, dqw, dkw, dtab, dpos, dsl = dv(x), dv(w), dv(qw), dv(kw), dv(table), dv(positions), dv(slots)
+    outs = []
+    for fused in (True, False):
+        kp = torch.zeros(nblocks, nkv, bs, hd, dtype=torch.bfloat16, device="cuda")
+        vp = torch.zeros_like(kp)
+        q_out = torch.zeros(T, nq * hd, dtype=torch.bfloat16, device="cuda")
+        if fused:
+            chk(lib, lib.b2k_qkv_rope(ptr(dx), ptr(dw), ptr(dqw), ptr(dkw), ptr(dtab), ptr(dpos), ptr(dsl), ptr(q_out), ptr(kp), ptr(vp), T,
+                                     nq, nkv, K, bs, 1e-6, cuda_stream_ptr()))
+        else:
+            qkv = torch.empty(T, N, dtype=torch.bfloat16, device="cuda")
+            chk(lib, lib.b2k_linear(ptr(dx), ptr(dw), ptr(qkv), 0, 1, T, N, K, 1, cuda_stream_ptr()))
+            chk(lib, lib.b2k_qknorm_rope_kv(ptr(qkv), 0, 1, ptr(dqw), ptr(dkw), ptr(dtab), ptr(dpos), ptr(dsl), ptr(q_out), ptr(kp), ptr(vp), T,
+                                           nq, nkv, hd, bs, 1e-6, cuda_stream_ptr()))
+        outs.append((q_out.cpu(), kv_swizzle(kp.cpu()), kv_swizzle(vp.cpu())))
+    (qf, kf, vf), (qs, ks, vs) = outs
+    # against the path it replaces: same rounding points, another order of the projection's fp32 sum -> an occasional ulp
+    # before the norm, up to two after norm and RoPE.  RoPE is a difference of products: where it cancels, one input ulp
+    # (2^-6 at the magnitudes here) is many ulps of the small result, hence the absolute floor of one input ulp.
+    assert_bf16_close(qf, qs, 2, 0.05, "q: fused vs separate", abs_floor=0.02)
+    assert_bf16_close(kf, ks, 2, 0.05, "k pages: fused vs separate", abs_floor=0.02)
+    assert_bf16_close(vf, vs, 1, 0.02, "v pages: fused vs separate", abs_floor=2e-3)
+    # against the oracle
+    qkv_ref = (x.float() @ w.float().t()).to(torch.bfloat16)
+    q = qkv_ref[:, : nq * hd].view(1, T, nq, hd)
+    k = qkv_ref[:, nq * hd: (nq + nkv) * hd].view(1, T, nkv, hd)
+    qn = rms_norm(q, qw, 1e-6).transpose(1, 2)
+    kn = rms_norm(k, kw, 1e-6).transpose(1, 2)
+    c, s_ = rope_cos_sin(a, positions[None, :].long())
+    qr, kr = apply_rope(qn, kn, c, s_)
+    assert_bf16_close(qf, qr.transpose(1, 2).reshape(T, nq * hd), 2, 0.05, "q vs oracle", abs_floor=0.02)
+    for t in range(T):
+        sl = int(slots[t])
+        if sl >= 0:
+            assert_bf16_close(kf[sl // bs, :, sl % bs, :], kr.transpose(1, 2)[0][t], 2, 0.08, "k page vs oracle t=%d" % t, abs_floor=0.02)
+    written = {int(v) for v in slots if v >= 0}
+    for sl in range(nblocks * bs):
+        if sl not in written:
+            assert not kf[sl // bs, :, sl % bs, :].any() and not vf[sl // bs, :, sl % bs, :].any(), "stray K/V write at slot %d" % sl
+
+
 def test_linear_is_deterministic(lib):
     T, N, K = 64, 1024, 2048
     x, w = bf(T, K, seed=12).cuda(), bf(N, K, scale=0.05, seed=13).cuda()

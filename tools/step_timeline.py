@@ -136,6 +136,20 @@ def main():
     step_us = max(r["end"] for r in L)
     print("step: %.1f us by stamps, %.1f us by events (2 steps / 2); %d records, %d launches; two-lane=%s" % (
         step_us, ms * 1e3 / 2, len(cls), len(L), os.environ.get("B2_MB", "default")))
+    # ---- attention: how the CTAs of one launch are spread in time ----
+    att_idx = [grp for (name, lane), grp in launches if name == "attn"]
+    if att_idx:
+        rows = []
+        for grp in att_idx:
+            grp = np.array(grp)
+            s0 = t0[grp].min()
+            st, wt, en = (t0[grp] - s0) / 1e3, (tw[grp] - s0) / 1e3, (t1[grp] - s0) / 1e3
+            busy = en - np.maximum(st, wt)
+            rows.append([np.percentile(st, 50), st.max(), np.median(wt), np.percentile(en, 10), np.percentile(en, 50), np.percentile(en, 90), en.max(),
+                         np.median(busy), np.corrcoef(st, en)[0, 1] if st.std() > 0 else 0.0])
+        a = np.median(np.array(rows), axis=0)
+        print("\nattention launches (median over %d launches; us from the launch's first CTA start): CTA start p50 %.2f max %.2f | wait returned %.2f | "
+              "CTA end p10 %.2f p50 %.2f p90 %.2f max %.2f | CTA busy after wait p50 %.2f | corr(start, end) %.2f" % ((len(rows),) + tuple(a)))
     # ---- per-lane chains: hand-off and work ----
     summary = {}
     for lane in sorted(set(r["lane"] for r in L)):
@@ -156,6 +170,7 @@ def main():
     print("sum over one layer's 9 launches (norm counted twice) of hand-off + work: %.1f us" % per_layer)
     if phases:
         print("\nprojection CTAs, time after their dependency wait returned (median / p90 over CTAs x layers, us):")
+        print("(fused pair kernels, gemm_pair.cu: the three columns are accumulator visible | pair barrier passed | tail done)")
         print("| kind | first operands landed | MMAs issued | accumulator visible | CTA end |")
         print("|---|---|---|---|---|")
         for name, rows in phases.items():
