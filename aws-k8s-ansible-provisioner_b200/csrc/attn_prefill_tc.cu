@@ -1,0 +1,313 @@
+// attn_prefill_tc.cu -- causal prefill attention over the paged KV cache on the 5th-generation tensor cores
+// (HF:integrations/sdpa_attention.py:40-104 at T > 1; eager form HF:models/qwen3/modeling_qwen3.py:196-218).
+// Same contract and the same tile list as attn_prefill.cu (the mma.sync kernel, kept as the cross-check and for
+// callers without a tensor map): fp32 scores, fp32 online-softmax statistics, probabilities rounded to bf16 for P.V,
+// the row sum from the unrounded fp32 probabilities, fp32 accumulation, one multiply by 1/l, one rounding.
+//
+// One CTA = one 64-query tile of one sequence x one kv head.  Both query heads of the GQA group sit on the MMA's M side
+// (row r = head (r >> 6), query token (r & 63)), so K and V are read once per pair:
+//   S[128 x 128 keys]  = Q[128 x 128 dims] . K^T      tcgen05.mma, A and B K-major from shared memory, S in TMEM
+//   softmax            : 128 threads, thread r owns row r: tcgen05.ld its S row, scale / mask / running max and sum,
+//                        P (bf16) into shared memory in the K-major 128-byte-swizzled layout the next MMA reads
+//   PV[128 x 128 dims] = P[128 x 128 keys] . V        V is the B operand in MN-major form: the page layout
+//                        [key][128 dims] with its 16-byte chunks XOR-swizzled by (key & 7) IS the canonical MN-major
+//                        128-byte-swizzle layout once the two 64-dim halves of every row are stored apart
+//   O (registers)      = O * corr + PV                 PV read back from TMEM by the thread that owns the row
+// K and V pages come in through TMA (a 2-D map over the page pool, box 64 dims x 16 keys, no TMA swizzle: the pool is
+// stored swizzled): half h of key row k lands at [h][k][128 bytes], which serves as K-major B for Q.K^T and as
+// MN-major B for P.V without any re-layout.  Inside a CTA the steps of a key tile run one after the other; the overlap
+// comes from two CTAs per SM (96 KB of shared memory, 256 TMEM columns each).
+#include "kernels.h"
+
+namespace b2 {
+
+namespace {
+
+constexpr int PT_TQ = 64;                    // query tokens per tile
+constexpr int PT_M = 128;                    // MMA rows: 2 heads x 64 tokens
+constexpr int PT_BN = 128;                   // keys per key tile
+constexpr int PT_HD = 128;
+constexpr int PT_HALF_BYTES = PT_BN * 128;   // one 64-dim half of a key tile: 128 keys x 128 bytes = 16 KB
+constexpr int PT_TILE_BYTES = 2 * PT_HALF_BYTES;
+// Q | K | V, 32 KB each.  P is written over K: once S = Q.K^T is complete the K tile is dead.  96 KB per CTA, so TWO CTAs
+// share an SM and one's softmax runs while the other's MMAs and page loads do -- the overlap a deeper in-CTA pipeline
+// would otherwise have to provide.
+constexpr int PT_SMEM = 3 * PT_TILE_BYTES + 1024;
+constexpr int PT_MAX_PAGES = 1024;           // block-table entries staged in shared memory (16 K tokens of context)
+constexpr int PT_TMEM_COLS = 256;            // S: columns 0..127, PV: 128..255
+
+// K-major, 128-byte swizzle (rows of 128 bytes, 8-row groups 1024 bytes apart): Q, K and P tiles
+__device__ __forceinline__ uint64_t pt_desc_k(uint32_t smem_addr) { return umma_desc_sw128(smem_addr); }
+// MN-major, 128-byte swizzle: the V tile.  64 contiguous dims (128 bytes) per key, 8-key groups 1024 bytes apart
+// (stride byte offset), the other 64 dims 16 KB further on (leading byte offset).
+__device__ __forceinline__ uint64_t pt_desc_mn(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr & 0x3FFFFu) >> 4);
+  d |= (uint64_t)(PT_HALF_BYTES >> 4) << 16;
+  d |= (uint64_t)(1024 >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+__device__ __forceinline__ float pt_ex2(float x) {  // 2^x, one MUFU (results below 2^-126 flush to zero: they are probabilities)
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+constexpr uint32_t PT_IDESC_QK = umma_idesc_bf16(PT_M, PT_BN);                // both operands K-major
+constexpr uint32_t PT_IDESC_PV = umma_idesc_bf16(PT_M, PT_HD) | (1u << 16);  // B (V) MN-major
+
+__global__ void __launch_bounds__(160, 2)
+attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_constant__ CUtensorMap tmap_v, const bf16* __restrict__ q,
+                       const int32_t* __restrict__ block_table, int bt_stride, const PrefillTile* __restrict__ tiles,
+                       bf16* __restrict__ out, int nq, int nkv, float scale_log2, int window, int dbg) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t k_full, v_full, s_full, p_full, o_full;
+  __shared__ uint32_t tmem_slot;
+  __shared__ int32_t s_bt[PT_MAX_PAGES];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* sm = smem_raw + (base - smem_u32(smem_raw));
+  const uint32_t q_s = base, k_s = base + PT_TILE_BYTES, v_s = base + 2 * PT_TILE_BYTES, p_s = k_s;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const PrefillTile tile = tiles[blockIdx.x];
+  const int kvh = blockIdx.y;
+  const int kv_len = tile.q_pos0 + tile.nrows;
+  const int n_kt = (kv_len + PT_BN - 1) / PT_BN;
+  const int kt0 = (window > 0 && tile.q_pos0 - window + 1 > 0) ? (tile.q_pos0 - window + 1) / PT_BN : 0;
+  const int32_t* bt = block_table + (size_t)tile.bt_row * bt_stride;
+
+  if (threadIdx.x == 0) {
+    mbar_init(smem_u32(&k_full), 1);
+    mbar_init(smem_u32(&v_full), 1);
+    mbar_init(smem_u32(&s_full), 1);
+    mbar_init(smem_u32(&p_full), 128);
+    mbar_init(smem_u32(&o_full), 1);
+    mbar_fence_init();
+  }
+  if (warp == 4) {
+    tmem_alloc(smem_u32(&tmem_slot), PT_TMEM_COLS);
+    tmem_relinquish();
+  }
+  // this sequence's block-table row (written by the host before the forward started) into shared memory: the control
+  // thread would otherwise chain a global load in front of every TMA issue
+  for (int i = threadIdx.x; i < n_kt * (PT_BN / 16) && i < PT_MAX_PAGES; i += blockDim.x) s_bt[i] = i < bt_stride ? bt[i] : 0;
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = tmem_slot;
+  pdl_wait();  // q and the newest K/V rows come from the kernel before this one
+  if (threadIdx.x == 0) pdl_launch_dependents();
+
+  auto load_tile = [&](int kt, uint32_t dst, const CUtensorMap* tm, uint32_t fb) {  // the 8 pages of key tile kt, both halves
+    mbar_arrive_expect_tx(fb, PT_TILE_BYTES);
+    for (int pg = 0; pg < PT_BN / 16; ++pg) {
+      const int row0 = (s_bt[kt * (PT_BN / 16) + pg] * nkv + kvh) * 16;  // pages past the sequence are the null page 0
+      tma_load_2d(dst + pg * 16 * 128, tm, 0, row0, fb);
+      tma_load_2d(dst + PT_HALF_BYTES + pg * 16 * 128, tm, 64, row0, fb);
+    }
+  };
+
+  if (warp == 4) {
+    if (lane == 0) {
+      tma_prefetch_desc(&tmap_k);
+      tma_prefetch_desc(&tmap_v);
+      load_tile(kt0, k_s, &tmap_k, smem_u32(&k_full));
+      load_tile(kt0, v_s, &tmap_v, smem_u32(&v_full));
+      mbar_wait(smem_u32(&p_full), 0);  // phase 0 of p_full: the softmax threads have staged Q
+      int it = 0;
+      for (int kt = kt0; kt < n_kt; ++kt, ++it) {
+        mbar_wait(smem_u32(&k_full), it & 1);
+        tc_fence_after();
+        // S = Q . K^T : K = 128 dims = 2 k-blocks x 4 MMAs of 16
+#pragma unroll
+        for (int kb = 0; kb < 2; ++kb) {
+          const uint64_t da = pt_desc_k(q_s + kb * PT_HALF_BYTES), db = pt_desc_k(k_s + kb * PT_HALF_BYTES);
+#pragma unroll
+          for (int k = 0; k < 4; ++k) tc_mma_bf16(tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), PT_IDESC_QK, (kb | k) ? 1u : 0u);
+        }
+        tc_commit(smem_u32(&s_full));
+        // PV = P . V : K = 128 keys = 2 k-blocks (of P, which now lies where K was) x 4 MMAs of 16 keys
+        mbar_wait(smem_u32(&p_full), (it + 1) & 1);
+        mbar_wait(smem_u32(&v_full), it & 1);
+        tc_fence_after();
+#pragma unroll
+        for (int kb = 0; kb < 2; ++kb) {
+          const uint64_t da = pt_desc_k(p_s + kb * PT_HALF_BYTES);
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const uint64_t db = pt_desc_mn(v_s + (uint32_t)((kb * 64 + k * 16) * 128));
+            tc_mma_bf16(tmem + 128u, da + (uint64_t)(2 * k), db, PT_IDESC_PV, (kb | k) ? 1u : 0u);
+          }
+        }
+        tc_commit(smem_u32(&o_full));
+        // P (in K's place) and V are read by those MMAs: the next tile's pages may land only once they have completed
+        mbar_wait(smem_u32(&o_full), it & 1);
+        if (kt + 1 < n_kt) {
+          load_tile(kt + 1, k_s, &tmap_k, smem_u32(&k_full));
+          load_tile(kt + 1, v_s, &tmap_v, smem_u32(&v_full));
+        }
+      }
+    }
+  } else {
+    // ---- 128 softmax threads: thread r owns MMA row r = (head r >> 6, query token r & 63) ----
+    const int r = threadIdx.x;
+    const int h = r >> 6, t = r & 63;
+    const bool row_ok = t < tile.nrows;
+    const int qpos = tile.q_pos0 + t;
+    // stage Q: rows in the K-major swizzled layout, 16 bytes per thread and step (rows past the tile are zeros)
+#pragma unroll
+    for (int k = 0; k < (PT_M * 16) / 128; ++k) {  // 16 cp.async per thread, all in flight together
+      const int idx = r + k * 128;
+      const int row = idx >> 4, c = idx & 15;
+      const int rh = row >> 6, rt = row & 63;
+      const bool in = rt < tile.nrows;
+      const bf16* src = q + ((size_t)(tile.q_row0 + (in ? rt : 0)) * nq + kvh * 2 + rh) * PT_HD + c * 8;
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(q_s + (c >> 3) * PT_HALF_BYTES + row * 128 + (((c & 7) ^ (row & 7)) << 4)),
+                   "l"(src), "r"(in ? 16 : 0)
+                   : "memory");
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    fence_proxy_async();
+    mbar_arrive(smem_u32(&p_full));  // phase 0 of p_full = "Q is staged"
+
+    float o[PT_HD];
+#pragma unroll
+    for (int i = 0; i < PT_HD; ++i) o[i] = 0.f;
+    float m_run = -INFINITY, l_run = 0.f;
+    const uint32_t trow = tmem + ((uint32_t)(warp * 32) << 16);
+    uint8_t* prow = sm + PT_TILE_BYTES + r * 128;  // P goes where K was (the S product has consumed K)
+    int it = 0;
+    for (int kt = kt0; kt < n_kt; ++kt, ++it) {
+      mbar_wait(smem_u32(&s_full), it & 1);
+      tc_fence_after();
+      const int key0 = kt * PT_BN;
+      // Valid keys of this row in this tile are a contiguous range [lo_col, hi_col] (causal bound, sequence end, window).
+      // A tile that lies wholly inside the range of EVERY row of the CTA (all but the last one or two tiles of a row
+      // block) takes the branch without per-element masks; the test is uniform over the CTA.
+      const int hi_col = row_ok ? min(qpos, kv_len - 1) : -1;
+      const int lo_col = (window > 0 && qpos - window + 1 > 0) ? qpos - window + 1 : 0;
+      const bool full_tile = key0 + PT_BN - 1 <= tile.q_pos0 && tile.nrows == PT_TQ &&
+                             (window <= 0 || tile.q_pos0 + PT_TQ - 1 - key0 < window);
+      // pass 1: the row maximum (the scale is positive: max(s * c) = c * max(s)); four chains instead of one
+      float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+#pragma unroll 1
+      for (int c0 = 0; c0 < ((dbg & 1) ? 0 : PT_BN); c0 += 32) {
+        uint32_t sr[32];
+        tmem_ld32(trow + (uint32_t)c0, sr);
+        tmem_ld_wait();
+        if (full_tile) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) m4[j & 3] = fmaxf(m4[j & 3], __uint_as_float(sr[j]));
+        } else {
+          const int jlo = lo_col - (key0 + c0);
+          const unsigned span = (unsigned)(hi_col - lo_col);  // hi < lo (nothing valid) wraps to a huge span: guard below
+          const bool any = hi_col >= lo_col;
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const bool ok = any && (unsigned)(j - jlo) <= span;
+            m4[j & 3] = fmaxf(m4[j & 3], ok ? __uint_as_float(sr[j]) : -INFINITY);
+          }
+        }
+      }
+      const float mx = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3])) * scale_log2;
+      const float m_new = fmaxf(m_run, mx);
+      const float msub = (m_new == -INFINITY) ? 0.f : m_new;
+      const float corr = exp2f(m_run - msub);
+      m_run = m_new;
+      // pass 2: probabilities, their fp32 sum, and P as bf16 into the A-operand tile of the PV product
+      float l4[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll 1
+      for (int c0 = 0; c0 < ((dbg & 2) ? 0 : PT_BN); c0 += 32) {
+        uint32_t sr[32];
+        tmem_ld32(trow + (uint32_t)c0, sr);
+        tmem_ld_wait();
+        float p[32];
+        if (full_tile) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            p[j] = pt_ex2(__uint_as_float(sr[j]) * scale_log2 - msub);
+            l4[j & 3] += p[j];
+          }
+        } else {
+          const int jlo = lo_col - (key0 + c0);
+          const unsigned span = (unsigned)(hi_col - lo_col);
+          const bool any = hi_col >= lo_col;
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const bool ok = any && (unsigned)(j - jlo) <= span;
+            p[j] = ok ? pt_ex2(__uint_as_float(sr[j]) * scale_log2 - msub) : 0.f;
+            l4[j & 3] += p[j];
+          }
+        }
+#pragma unroll
+        for (int c8 = 0; c8 < 4; ++c8) {  // four 16-byte chunks of 8 keys
+          const int chunk = (c0 >> 3) + c8;  // 0..15 within the 128-key row
+          *reinterpret_cast<uint4*>(prow + (chunk >> 3) * PT_HALF_BYTES + (((chunk & 7) ^ (r & 7)) << 4)) = pack8(p + c8 * 8);
+        }
+      }
+      l_run = l_run * corr + ((l4[0] + l4[1]) + (l4[2] + l4[3]));
+      tc_fence_before();
+      fence_proxy_async();
+      mbar_arrive(smem_u32(&p_full));
+      // O = O * corr + P.V
+      mbar_wait(smem_u32(&o_full), it & 1);
+      tc_fence_after();
+      if (!(dbg & 4))
+#pragma unroll
+      for (int c0 = 0; c0 < PT_HD; c0 += 32) {
+        uint32_t pv[32];
+        tmem_ld32(trow + 128u + (uint32_t)c0, pv);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 32; ++j) o[c0 + j] = fmaf(o[c0 + j], corr, __uint_as_float(pv[j]));
+      }
+      tc_fence_before();
+    }
+    if (row_ok) {
+      const float inv = l_run > 0.f ? __fdiv_rn(1.0f, l_run) : 0.f;
+      bf16* dst = out + ((size_t)(tile.q_row0 + t) * nq + kvh * 2 + h) * PT_HD;
+#pragma unroll
+      for (int c = 0; c < PT_HD / 8; ++c) {
+        float v[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) v[e] = o[c * 8 + e] * inv;
+        reinterpret_cast<uint4*>(dst)[c] = pack8(v);
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 4) {
+    tc_fence_after();
+    tmem_dealloc(tmem, PT_TMEM_COLS);
+  }
+}
+
+}  // namespace
+
+// num_pages: pages in the pool k_pages / v_pages point to (the TMA maps cover exactly the pool).
+int launch_attn_prefill_tc(const bf16* q, const bf16* k_pages, const bf16* v_pages, int64_t num_pages, const int32_t* block_table,
+                           int bt_stride, const PrefillTile* tiles_dev, int ntiles, bf16* out, int nq, int nkv, int hd, int block_size,
+                           cudaStream_t s, float softmax_scale, int window) {
+  if (ntiles <= 0) return 0;
+  B2_REQUIRE(hd == PT_HD && block_size == 16 && nq == 2 * nkv, "attn_prefill_tc: built for 128-wide heads in GQA groups of two, 16-token pages");
+  B2_REQUIRE(num_pages >= 1, "attn_prefill_tc: the page pool's size is needed for the tensor maps");
+  B2_REQUIRE(bt_stride <= PT_MAX_PAGES, "attn_prefill_tc: contexts beyond %d tokens not built (block table row of %d pages)", PT_MAX_PAGES * 16, bt_stride);
+  CUtensorMap tk, tv;
+  const uint64_t rows = (uint64_t)num_pages * nkv * 16;
+  int rc = b2_make_tmap_bf16_ex(&tk, k_pages, rows, PT_HD, PT_HD, 64, 16, /*swizzle128=*/0);
+  if (rc != 0) return rc;
+  rc = b2_make_tmap_bf16_ex(&tv, v_pages, rows, PT_HD, PT_HD, 64, 16, 0);
+  if (rc != 0) return rc;
+  static B2PerDeviceOnce attr_once;
+  if (attr_once.need()) B2_CUDA_OK(cudaFuncSetAttribute(attn_prefill_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PT_SMEM));
+  const double scale = softmax_scale > 0.f ? (double)softmax_scale : 1.0 / sqrt((double)hd);
+  const float scale_log2 = (float)(scale * 1.4426950408889634);
+  static const int dbg = [] { const char* e = getenv("B2_PTC_DBG"); return e ? atoi(e) : 0; }();  // timing experiments only
+  B2_CUDA_OK(b2_launch(attn_prefill_tc_kernel, dim3(ntiles, nkv), dim3(160), (size_t)PT_SMEM, s, tk, tv, q, block_table, bt_stride, tiles_dev,
+                       out, nq, nkv, scale_log2, window, dbg));
+  return 0;
+}
+
+}  // namespace b2

@@ -150,8 +150,22 @@ extern "C" int b2k_attn_prefill(const void* q, const void* k_pages, const void* 
     b2_set_error("b2k_attn_prefill: tile upload failed: %s", cudaGetErrorString(ce));
     rc = -5;
   } else {
-    rc = launch_attn_prefill((const bf16*)q, (const bf16*)k_pages, (const bf16*)v_pages, block_table_dev, bt_stride, d,
-                             (int)tiles.size(), (bf16*)out, nq, nkv, hd, block_size, s);
+    const char* env = getenv("B2_PREFILL_TC");
+    if (env == nullptr || *env != '0') {
+      // this hook is not told the size of the page pool: the largest page its block table names bounds what can be read
+      int max_row = 0;
+      for (int i = 0; i < nseq; ++i) max_row = std::max(max_row, host_seq_row[i]);
+      std::vector<int32_t> bth((size_t)(max_row + 1) * bt_stride);
+      cudaStreamSynchronize(s);
+      cudaMemcpy(bth.data(), block_table_dev, bth.size() * sizeof(int32_t), cudaMemcpyDeviceToHost);
+      int64_t pages = 1;
+      for (int32_t v : bth) pages = std::max<int64_t>(pages, (int64_t)v + 1);
+      rc = launch_attn_prefill_tc((const bf16*)q, (const bf16*)k_pages, (const bf16*)v_pages, pages, block_table_dev, bt_stride, d,
+                                  (int)tiles.size(), (bf16*)out, nq, nkv, hd, block_size, s);
+    } else {
+      rc = launch_attn_prefill((const bf16*)q, (const bf16*)k_pages, (const bf16*)v_pages, block_table_dev, bt_stride, d,
+                               (int)tiles.size(), (bf16*)out, nq, nkv, hd, block_size, s);
+    }
   }
   cudaStreamSynchronize(s);
   cudaFree(d);

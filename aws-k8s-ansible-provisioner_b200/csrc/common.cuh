@@ -331,3 +331,6 @@ __host__ __device__ constexpr uint32_t umma_idesc_bf16(int m, int n) {
 // 2-D row-major bf16 matrix [rows][cols] with leading dimension ld (elements); box = 64 cols x
 // box_rows rows, 128-byte swizzle.
 int b2_make_tmap_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows);
+// General form: box = box_cols x box_rows elements; swizzle128 = 0 copies rows as they are (for data that is stored swizzled).
+int b2_make_tmap_bf16_ex(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_cols, uint32_t box_rows,
+                         int swizzle128);

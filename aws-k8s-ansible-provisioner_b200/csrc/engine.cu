@@ -238,6 +238,7 @@ struct b2_engine {
                                           // attention's CTAs (measured slower: 1.869 vs 1.832 ms/step at C2 -- its weight
                                           // prefetch competes with the tail of the K/V stream)
   int use_chain = 0;  // B2_CHAIN: 0 separate kernels (default, fastest measured), 1 chain.cu, 2 chain_cluster.cu
+  int prefill_tc = 1; // B2_PREFILL_TC: prefill attention on tcgen05 (attn_prefill_tc.cu); 0 = the mma.sync kernel (attn_prefill.cu)
   int use_pair = 1;   // B2_PAIR: bit 0 gate/up + SwiGLU, bit 1 QKV + QK-norm/RoPE/KV write as fused cluster-pair launches (gemm_pair.cu)
 
   // two-lane decode (B2_MB, see forward()): second stream, its own partials and attention scratch, fork/join events
@@ -675,8 +676,14 @@ int forward_layers(b2_engine* e, const Lane& ln, int T, int ntiles) {
     }
     if (ntiles > 0) {
       KL k(e, B2K_MISC);
-      if (!k.skip()) B2_TRY(launch_attn_prefill(qrot, kp, vp, block_table, e->bt_stride, e->d_tiles, ntiles, attn,
-                                 e->nq, e->nkv, e->hd, c.block_size, st, e->attn_scale, c.sliding_window));
+      if (!k.skip()) {
+        if (e->prefill_tc)
+          B2_TRY(launch_attn_prefill_tc(qrot, kp, vp, e->num_blocks, block_table, e->bt_stride, e->d_tiles, ntiles, attn, e->nq, e->nkv, e->hd,
+                                        c.block_size, st, e->attn_scale, c.sliding_window));
+        else
+          B2_TRY(launch_attn_prefill(qrot, kp, vp, block_table, e->bt_stride, e->d_tiles, ntiles, attn,
+                                     e->nq, e->nkv, e->hd, c.block_size, st, e->attn_scale, c.sliding_window));
+      }
     } else {
       KL k(e, B2K_ATTN_DECODE);
       if (!k.skip())
@@ -1367,6 +1374,7 @@ extern "C" int b2_engine_create(const b2_config* cfg, const char* safetensors_pa
   // chain (chain_cluster.cu); 1 and 2 are kept as measured experiments with parity tests
   e->use_chain = env_int("B2_CHAIN", 0);
   e->use_pair = env_int("B2_PAIR", 3);
+  e->prefill_tc = env_int("B2_PREFILL_TC", 1);
   e->o_small_smem = env_int("B2_O_SMALL", 0);
   // Off by default: measured on B200 at C2 (ms/step) 0 MB 2.22, 40 MB 2.24, 72 MB 2.33, 100 MB 2.38 --
   // un-paced prefetch bursts queue ahead of the projections' own latency-critical weight loads.

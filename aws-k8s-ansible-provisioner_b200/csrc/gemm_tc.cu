@@ -499,16 +499,21 @@ static PFN_encodeTiled get_encode_fn() {
 }  // namespace b2
 
 int b2_make_tmap_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows) {
+  return b2_make_tmap_bf16_ex(out, base, rows, cols, ld, 64, box_rows, 1);
+}
+
+int b2_make_tmap_bf16_ex(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_cols, uint32_t box_rows,
+                         int swizzle128) {
   auto fn = b2::get_encode_fn();
   B2_REQUIRE(fn != nullptr, "cuTensorMapEncodeTiled driver entry point not available");
   B2_REQUIRE(((uintptr_t)base & 15) == 0 && (ld * 2) % 16 == 0, "tensor map: base/stride must be 16-byte aligned");
   cuuint64_t gdim[2] = {cols, rows};
   cuuint64_t gstride[1] = {ld * 2};
-  cuuint32_t box[2] = {64, box_rows};
+  cuuint32_t box[2] = {box_cols, box_rows};
   cuuint32_t estr[2] = {1, 1};
   CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstride, box, estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   B2_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with CUresult %d (rows=%llu cols=%llu ld=%llu box=%u)",
              (int)r, (unsigned long long)rows, (unsigned long long)cols, (unsigned long long)ld, box_rows);
   return 0;

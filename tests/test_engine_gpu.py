@@ -289,8 +289,19 @@ def test_full_c1_greedy_and_logits(P, full):
     mism = np.nonzero(toks != gold)[0]
     n_match = 128 if len(mism) == 0 else int(mism[0])
     print("C1 greedy: %d/128 leading tokens identical to HF; worst hidden rel err %.3g" % (n_match, worst))
-    rec = {"leading_match": n_match, "of": 128, "worst_hidden_rel_err": float(worst), "last_logits_rel_err": float(lerr),
-           "last_logits_floor": float(lfloor)}
+    # the same 128 steps teacher-forced with HF's tokens: how many of the engine's tokens equal HF's when every step sees
+    # HF's context (a free-running stream stops being comparable at its first tie flip)
+    sid2 = e.seq_create(300)
+    tf = [int(e.prefill([sid2], [prompt])[0])]
+    for t in range(1, 128):
+        tf.append(int(e.decode_step([sid2], in_tokens=[int(gold[t - 1])])[0]))
+    tf = np.array(tf)
+    tf_mism = np.nonzero(tf != gold)[0]
+    for t in tf_mism:
+        gap_t = float(top4[127 + t][0] - top4[127 + t][1])
+        assert gap_t <= 2 * bf16_ulp_of(float(top4[127 + t][0])), "teacher-forced step %d differs from HF where its top-2 gap is %.4f" % (t, gap_t)
+    rec = {"leading_match": n_match, "of": 128, "teacher_forced_equal": int(128 - len(tf_mism)), "teacher_forced_differing_steps": tf_mism.tolist(),
+           "worst_hidden_rel_err": float(worst), "last_logits_rel_err": float(lerr), "last_logits_floor": float(lfloor)}
     if len(mism):
         # north_star: identical over the first 128 tokens; the only divergence tolerated is at a step where HF's own
         # top-2 gap is within 2 bf16 ulp of its top logit (HF's two attention paths flip such a step themselves)
@@ -318,18 +329,20 @@ def test_full_alternative_decode_schedules(P, full, monkeypatch, chain):
     prompt, gold = fx["prompt_ids"], np.array(fx["greedy_ids"])
     e = make_engine(P, arch, sd, max_model_len=512, num_blocks=64 * 12 + 8, max_seqs=64, max_batch_tokens=2048, use_cuda_graphs=True)
     sid = e.seq_create(300)
-    first = int(e.prefill([sid], [prompt])[0])
-    toks, _ = e.decode_run([sid], 127)
-    got = np.concatenate([[first], toks[:, 0]])
+    # teacher-forced with HF's tokens, so that every one of the 128 steps is compared (a free-running stream is only
+    # comparable up to its first tie flip): the engine's token may differ from HF's only where HF's own top-2 logit gap
+    # is within 2 bf16 ulp of the top logit
+    got = [int(e.prefill([sid], [prompt])[0])]
+    for t in range(1, 128):
+        got.append(int(e.decode_step([sid], in_tokens=[int(gold[t - 1])])[0]))
+    got = np.array(got)
+    top4 = np.array(fx["tf_top4_logits"])
     mism = np.nonzero(got != gold)[0]
-    n_match = 128 if len(mism) == 0 else int(mism[0])
-    print("B2_CHAIN=%s, C1 greedy: %d/128 leading tokens identical to HF" % (chain, n_match))
-    if len(mism):
-        top4 = np.array(fx["tf_top4_logits"])
-        t = int(mism[0])
-        gap = top4[127 + t][0] - top4[127 + t][1]
-        assert gap <= 0.0625, "first mismatch at step %d where the oracle's top-2 gap is %.4f (not a near-tie)" % (t, gap)
-    assert n_match >= 16
+    print("B2_CHAIN=%s, C1 teacher-forced: %d/128 tokens identical to HF (differing steps: %s)" % (chain, 128 - len(mism), mism.tolist()))
+    for t in mism:
+        gap = float(top4[127 + t][0] - top4[127 + t][1])
+        assert gap <= 2 * bf16_ulp_of(float(top4[127 + t][0])), "step %d differs from HF where its top-2 gap is %.4f (not a tie)" % (t, gap)
+    assert len(mism) <= 6
     e.seq_free(sid)
     # batch 64 (the shape chain_cluster.cu is built for): same bits run after run
     p64 = make_prompts(64, 100, arch.vocab, seed=3)

@@ -435,6 +435,43 @@ def test_attn_decode(lib, seq_lens):
     assert torch.equal(out, out2)
 
 
+def test_attn_prefill_copies_are_bit_identical(lib):
+    """Identical sequences in different rows of the batch (other pages, other CTAs) and repeated launches must give the
+    same bits: nothing in the prefill kernel depends on where a sequence sits or on timing."""
+    a = QWEN3_0_6B
+    nq, nkv, hd, bs = a.num_q_heads, a.num_kv_heads, a.head_dim, 16
+    n, copies = 2100, 3
+    bt1, kp1, vp1, ks, vs = build_pages([n], nkv, hd, bs, seed=40)
+    pages = bt1.shape[1]
+    # the same K/V written to three different sets of pages
+    kp = torch.zeros(1 + copies * pages, nkv, bs, hd, dtype=torch.bfloat16)
+    vp = torch.zeros_like(kp)
+    bt = torch.zeros(copies, pages, dtype=torch.int32)
+    g = torch.Generator().manual_seed(41)
+    perm = (torch.randperm(copies * pages, generator=g) + 1).to(torch.int32)
+    for c in range(copies):
+        for j in range(pages):
+            dst = int(perm[c * pages + j])
+            src = int(bt1[0, j])
+            kp[dst], vp[dst] = kp1[src], vp1[src]
+            bt[c, j] = dst
+    q1 = bf(n, nq * hd, seed=42)
+    q = q1.repeat(copies, 1)
+    T = copies * n
+    I32 = lambda v: (C.c_int32 * len(v))(*v)
+    outs = []
+    for rep in range(2):
+        out = torch.full((T, nq * hd), float("nan"), dtype=torch.bfloat16, device="cuda")
+        chk(lib, lib.b2k_attn_prefill(ptr(dv(q)), ptr(dv(kp)), ptr(dv(vp)), ptr(dv(bt)), pages, I32([c * n for c in range(copies)]),
+                                     I32([0] * copies), I32([n] * copies), I32(list(range(copies))), copies, ptr(out), nq, nkv, hd, bs,
+                                     cuda_stream_ptr()))
+        outs.append(out.cpu())
+    assert torch.equal(outs[0], outs[1]), "two launches on the same inputs differ"
+    o = outs[0].view(copies, n, nq * hd)
+    for c in range(1, copies):
+        assert torch.equal(o[0], o[c]), "copy %d of the sequence differs from copy 0" % c
+
+
 def test_attn_decode_empty_and_padding_rows(lib):
     """A graph bucket pads the batch with rows of length 0: their output must be zeros, not NaN."""
     a = QWEN3_0_6B
@@ -452,13 +489,16 @@ def test_attn_decode_empty_and_padding_rows(lib):
     check_attention(o[1].view(1, nq, 1, hd), q[1].view(1, nq, 1, hd), ks[1][None], vs[1][None], False, "attn_decode mid row")
 
 
-@pytest.mark.parametrize("case", ["fresh", "chunked"])
+@pytest.mark.parametrize("case", ["fresh", "chunked", "long"])
 def test_attn_prefill(lib, case):
     a = QWEN3_0_6B
     nq, nkv, hd, bs = a.num_q_heads, a.num_kv_heads, a.head_dim, 16
     if case == "fresh":
         pos0 = [0, 0, 0, 0]
         ntok = [5, 64, 130, 1]
+    elif case == "long":  # many key tiles: the K/V double buffer and every barrier phase of the tcgen05 kernel turn over
+        pos0 = [300, 0, 1000]
+        ntok = [200, 700, 90]
     else:  # queries appended after an existing prefix (chunked prefill)
         pos0 = [70, 3, 129]
         ntok = [61, 200, 64]
@@ -476,3 +516,13 @@ def test_attn_prefill(lib, case):
         qs = q[first[i]: first[i] + n].view(n, nq, hd).transpose(0, 1)[None]  # [1][nq][n][hd]
         got = o[first[i]: first[i] + n].view(n, nq, hd).transpose(0, 1)[None]  # causal with prefix: tril(diagonal=S-T)
         check_attention(got, qs, ks[i][None], vs[i][None], True, "attn_prefill seq %d (%s)" % (i, case))
+    # the tcgen05 kernel (default) against the mma.sync kernel it replaced: same contract, other tile sizes and sum orders
+    import os
+    out2 = torch.full((T, nq * hd), float("nan"), dtype=torch.bfloat16, device="cuda")
+    os.environ["B2_PREFILL_TC"] = "0"
+    try:
+        chk(lib, lib.b2k_attn_prefill(ptr(dv(q)), ptr(dv(kp)), ptr(dv(vp)), ptr(dv(bt)), bt.shape[1], I32(first), I32(pos0),
+                                     I32(ntok), I32(list(range(len(ntok)))), len(ntok), ptr(out2), nq, nkv, hd, bs, cuda_stream_ptr()))
+    finally:
+        del os.environ["B2_PREFILL_TC"]
+    assert_bf16_close(out, out2, 2, 0.2, "tcgen05 vs mma.sync prefill attention (%s)" % case, abs_floor=2e-3)

@@ -12,7 +12,7 @@ import numpy as np
 import pytest
 import torch
 
-from _util import engine_config_from_arch, pkg
+from _util import bf16_ulp_of, engine_config_from_arch, pkg
 from oracle.opt_oracle import OPT_125M
 from oracle.phi3_oracle import PHI3_MINI, phi3_inv_freq
 from oracle.qwen3_oracle import make_prompts
@@ -80,7 +80,17 @@ def properties(e, B, prompt, reserve, steps, chunk):
             firsts.append(e.prefill(sids[i:i + chunk], [prompt] * len(sids[i:i + chunk])))
         first = np.concatenate(firsts)
         assert (first == first[0]).all(), "identical prompts produced different first tokens"
-        toks, _ = e.decode_run(sids, steps)
+        if rep == 0:
+            # the first decode step through the call that also returns logits: how close to a tie is its arg-max?
+            e.set_debug(logits=True)
+            t0 = e.decode_step(sids)
+            lg = torch.from_numpy(e.get_logits(B)).topk(2, dim=-1).values
+            e.set_debug(logits=False)
+            properties.step0_gap_ulp = float(((lg[:, 0] - lg[:, 1]) / torch.tensor([bf16_ulp_of(float(v)) for v in lg[:, 0]])).min())
+            rest, _ = e.decode_run(sids, steps - 1)
+            toks = np.concatenate([t0[None, :], rest], axis=0)
+        else:
+            toks, _ = e.decode_run(sids, steps)
         runs.append((first.copy(), toks.copy()))
         for s in sids:
             e.seq_free(s)
@@ -105,14 +115,17 @@ def test_c3_opt125m_batch256(P):
     e.load_state_dict(opt_weights(arch, 3))
     prompt = make_prompts(1, PL, arch.vocab, seed=1)[0].tolist()
     toks, solo = properties(e, B, prompt, PL + 48, STEPS, chunk=64)
-    assert (toks[0] == toks[0, 0]).all(), "first decode step differs across identical sequences"
+    if not (toks[0] == toks[0, 0]).all():
+        assert properties.step0_gap_ulp <= 2.0, "first decode step differs across identical sequences away from a tie (gap %.1f ulp)" % properties.step0_gap_ulp
     together = (toks == toks[:, :1]).all(axis=0).mean()
     agree = int((solo == toks[:, 0]).sum())
     print("C3: %d%% of 256 copies stayed together for %d steps; batch vs solo agree on %d/%d tokens" % (
         100 * together, STEPS, agree, STEPS))
     first_split = next((t for t in range(STEPS) if (toks[t] != toks[t, 0]).any()), STEPS)
     print("C3: first step at which any copy differs: %d" % first_split)
-    assert first_split >= 2 and agree >= 4  # `together` is reported, not asserted: it is a count of near-ties
+    # `together` is reported, not asserted: it counts near-ties.  A tie at the very first step (gap <= 2 ulp) lets the copies and
+    # the solo run part at once; otherwise they must stay together for a few steps
+    assert properties.step0_gap_ulp <= 2.0 or (first_split >= 2 and agree >= 4)
     e.close()
 
 
@@ -127,12 +140,17 @@ def test_c4_phi3mini_batch32_prefill2048(P):
     e.load_state_dict(phi3_weights(arch, 4))
     prompt = make_prompts(1, PL, arch.vocab, seed=1)[0].tolist()
     toks, solo = properties(e, B, prompt, PL + 32, STEPS, chunk=4)
-    assert (toks[0] == toks[0, 0]).all(), "first decode step differs across identical sequences"
+    # copies of one sequence sit in different rows, and decode attention cuts a row's pages by its place in the batch
+    # (DESIGN.md section 2): they may part at a step whose top two logits are within bf16 noise of each other, not elsewhere
+    if not (toks[0] == toks[0, 0]).all():
+        assert properties.step0_gap_ulp <= 2.0, "first decode step differs across identical sequences away from a tie (gap %.1f ulp)" % properties.step0_gap_ulp
     together = (toks == toks[:, :1]).all(axis=0).mean()
     agree = int((solo == toks[:, 0]).sum())
     print("C4: %d%% of 32 copies stayed together for %d steps; batch vs solo agree on %d/%d tokens" % (
         100 * together, STEPS, agree, STEPS))
     first_split = next((t for t in range(STEPS) if (toks[t] != toks[t, 0]).any()), STEPS)
     print("C4: first step at which any copy differs: %d" % first_split)
-    assert first_split >= 2 and agree >= 4  # `together` is reported, not asserted: it is a count of near-ties
+    # `together` is reported, not asserted: it counts near-ties.  A tie at the very first step (gap <= 2 ulp) lets the copies and
+    # the solo run part at once; otherwise they must stay together for a few steps
+    assert properties.step0_gap_ulp <= 2.0 or (first_split >= 2 and agree >= 4)
     e.close()
