@@ -7,12 +7,14 @@
 // One CTA = one 64-query tile of one sequence x one kv head.  Both query heads of the GQA group sit on the MMA's M side
 // (row r = head (r >> 6), query token (r & 63)), so K and V are read once per pair:
 //   S[128 x 128 keys]  = Q[128 x 128 dims] . K^T      tcgen05.mma, A and B K-major from shared memory, S in TMEM
-//   softmax            : 128 threads, thread r owns row r: tcgen05.ld its S row, scale / mask / running max and sum,
-//                        P (bf16) into shared memory in the K-major 128-byte-swizzled layout the next MMA reads
+//   softmax            : 256 threads, TWO per row (warps w and w + 4 may both read TMEM lanes 32 (w & 3)..+31): each takes
+//                        64 of the tile's 128 keys -- tcgen05.ld, scale / mask, row maximum exchanged through shared
+//                        memory between the two, running sum kept per thread and added at the end -- and writes its
+//                        half of P (bf16) into shared memory in the K-major 128-byte-swizzled layout the next MMA reads
 //   PV[128 x 128 dims] = P[128 x 128 keys] . V        V is the B operand in MN-major form: the page layout
 //                        [key][128 dims] with its 16-byte chunks XOR-swizzled by (key & 7) IS the canonical MN-major
 //                        128-byte-swizzle layout once the two 64-dim halves of every row are stored apart
-//   O (registers)      = O * corr + PV                 PV read back from TMEM by the thread that owns the row
+//   O (registers)      = O * corr + PV                 each of the row's two threads keeps 64 of the 128 output dims
 // K and V pages come in through TMA (a 2-D map over the page pool, box 64 dims x 16 keys, no TMA swizzle: the pool is
 // stored swizzled): half h of key row k lands at [h][k][128 bytes], which serves as K-major B for Q.K^T and as
 // MN-major B for P.V without any re-layout.  Inside a CTA the steps of a key tile run one after the other; the overlap
@@ -57,14 +59,15 @@ __device__ __forceinline__ float pt_ex2(float x) {  // 2^x, one MUFU (results be
 constexpr uint32_t PT_IDESC_QK = umma_idesc_bf16(PT_M, PT_BN);                // both operands K-major
 constexpr uint32_t PT_IDESC_PV = umma_idesc_bf16(PT_M, PT_HD) | (1u << 16);  // B (V) MN-major
 
-__global__ void __launch_bounds__(160, 2)
+__global__ void __launch_bounds__(288, 2)
 attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_constant__ CUtensorMap tmap_v, const bf16* __restrict__ q,
                        const int32_t* __restrict__ block_table, int bt_stride, const PrefillTile* __restrict__ tiles,
-                       bf16* __restrict__ out, int nq, int nkv, float scale_log2, int window, int dbg) {
+                       bf16* __restrict__ out, int nq, int nkv, float scale_log2, int window) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t k_full, v_full, s_full, p_full, o_full;
   __shared__ uint32_t tmem_slot;
   __shared__ int32_t s_bt[PT_MAX_PAGES];
+  __shared__ float s_mx[2][PT_M];  // row maxima of the two key halves of the current tile; at the end: the two row sums
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* sm = smem_raw + (base - smem_u32(smem_raw));
   const uint32_t q_s = base, k_s = base + PT_TILE_BYTES, v_s = base + 2 * PT_TILE_BYTES, p_s = k_s;
@@ -80,11 +83,11 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_
     mbar_init(smem_u32(&k_full), 1);
     mbar_init(smem_u32(&v_full), 1);
     mbar_init(smem_u32(&s_full), 1);
-    mbar_init(smem_u32(&p_full), 128);
+    mbar_init(smem_u32(&p_full), 256);
     mbar_init(smem_u32(&o_full), 1);
     mbar_fence_init();
   }
-  if (warp == 4) {
+  if (warp == 8) {
     tmem_alloc(smem_u32(&tmem_slot), PT_TMEM_COLS);
     tmem_relinquish();
   }
@@ -107,7 +110,7 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_
     }
   };
 
-  if (warp == 4) {
+  if (warp == 8) {
     if (lane == 0) {
       tma_prefetch_desc(&tmap_k);
       tma_prefetch_desc(&tmap_v);
@@ -149,15 +152,16 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_
       }
     }
   } else {
-    // ---- 128 softmax threads: thread r owns MMA row r = (head r >> 6, query token r & 63) ----
-    const int r = threadIdx.x;
+    // ---- 256 softmax threads: threads r and r + 128 own MMA row r = (head r >> 6, query token r & 63); `kh` says which
+    // 64 keys of a tile (and which 64 output dims) are this thread's ----
+    const int r = threadIdx.x & 127, kh = threadIdx.x >> 7;
     const int h = r >> 6, t = r & 63;
     const bool row_ok = t < tile.nrows;
     const int qpos = tile.q_pos0 + t;
     // stage Q: rows in the K-major swizzled layout, 16 bytes per thread and step (rows past the tile are zeros)
 #pragma unroll
-    for (int k = 0; k < (PT_M * 16) / 128; ++k) {  // 16 cp.async per thread, all in flight together
-      const int idx = r + k * 128;
+    for (int k = 0; k < (PT_M * 16) / 256; ++k) {  // 8 cp.async per thread, all in flight together
+      const int idx = (int)threadIdx.x + k * 256;
       const int row = idx >> 4, c = idx & 15;
       const int rh = row >> 6, rt = row & 63;
       const bool in = rt < tile.nrows;
@@ -171,12 +175,14 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_
     fence_proxy_async();
     mbar_arrive(smem_u32(&p_full));  // phase 0 of p_full = "Q is staged"
 
-    float o[PT_HD];
+    constexpr int HALF = PT_BN / 2;  // keys per thread and tile == output dims per thread
+    float o[HALF];
 #pragma unroll
-    for (int i = 0; i < PT_HD; ++i) o[i] = 0.f;
-    float m_run = -INFINITY, l_run = 0.f;
-    const uint32_t trow = tmem + ((uint32_t)(warp * 32) << 16);
-    uint8_t* prow = sm + PT_TILE_BYTES + r * 128;  // P goes where K was (the S product has consumed K)
+    for (int i = 0; i < HALF; ++i) o[i] = 0.f;
+    float m_run = -INFINITY, l_run = 0.f;  // l_run: the sum over THIS thread's keys only
+    const uint32_t trow = tmem + ((uint32_t)((warp & 3) * 32) << 16);
+    uint8_t* prow = sm + PT_TILE_BYTES + kh * PT_HALF_BYTES + r * 128;  // P goes where K was (the S product has consumed K)
+    const int pair_bar = 1 + (warp & 3);  // named barrier of the two warps that share a lane quarter
     int it = 0;
     for (int kt = kt0; kt < n_kt; ++kt, ++it) {
       mbar_wait(smem_u32(&s_full), it & 1);
@@ -192,7 +198,7 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_
       // pass 1: the row maximum (the scale is positive: max(s * c) = c * max(s)); four chains instead of one
       float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll 1
-      for (int c0 = 0; c0 < ((dbg & 1) ? 0 : PT_BN); c0 += 32) {
+      for (int c0 = kh * HALF; c0 < kh * HALF + HALF; c0 += 32) {
         uint32_t sr[32];
         tmem_ld32(trow + (uint32_t)c0, sr);
         tmem_ld_wait();
@@ -210,7 +216,10 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_
           }
         }
       }
-      const float mx = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3])) * scale_log2;
+      const float mx_own = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
+      s_mx[kh][r] = mx_own;
+      asm volatile("bar.sync %0, 64;" ::"r"(pair_bar) : "memory");
+      const float mx = fmaxf(mx_own, s_mx[kh ^ 1][r]) * scale_log2;
       const float m_new = fmaxf(m_run, mx);
       const float msub = (m_new == -INFINITY) ? 0.f : m_new;
       const float corr = exp2f(m_run - msub);
@@ -218,7 +227,7 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_
       // pass 2: probabilities, their fp32 sum, and P as bf16 into the A-operand tile of the PV product
       float l4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll 1
-      for (int c0 = 0; c0 < ((dbg & 2) ? 0 : PT_BN); c0 += 32) {
+      for (int c0 = kh * HALF; c0 < kh * HALF + HALF; c0 += 32) {
         uint32_t sr[32];
         tmem_ld32(trow + (uint32_t)c0, sr);
         tmem_ld_wait();
@@ -242,8 +251,8 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_
         }
 #pragma unroll
         for (int c8 = 0; c8 < 4; ++c8) {  // four 16-byte chunks of 8 keys
-          const int chunk = (c0 >> 3) + c8;  // 0..15 within the 128-key row
-          *reinterpret_cast<uint4*>(prow + (chunk >> 3) * PT_HALF_BYTES + (((chunk & 7) ^ (r & 7)) << 4)) = pack8(p + c8 * 8);
+          const int chunk = ((c0 >> 3) & 7) + c8;  // 0..7 within this thread's 64-key half of the row
+          *reinterpret_cast<uint4*>(prow + ((chunk ^ (r & 7)) << 4)) = pack8(p + c8 * 8);
         }
       }
       l_run = l_run * corr + ((l4[0] + l4[1]) + (l4[2] + l4[3]));
@@ -253,22 +262,24 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_
       // O = O * corr + P.V
       mbar_wait(smem_u32(&o_full), it & 1);
       tc_fence_after();
-      if (!(dbg & 4))
 #pragma unroll
-      for (int c0 = 0; c0 < PT_HD; c0 += 32) {
+      for (int c0 = 0; c0 < HALF; c0 += 32) {
         uint32_t pv[32];
-        tmem_ld32(trow + 128u + (uint32_t)c0, pv);
+        tmem_ld32(trow + 128u + (uint32_t)(kh * HALF + c0), pv);
         tmem_ld_wait();
 #pragma unroll
         for (int j = 0; j < 32; ++j) o[c0 + j] = fmaf(o[c0 + j], corr, __uint_as_float(pv[j]));
       }
       tc_fence_before();
     }
+    s_mx[kh][r] = l_run;  // the pair's last barrier of the loop is behind both threads' reads of s_mx
+    asm volatile("bar.sync %0, 64;" ::"r"(pair_bar) : "memory");
+    const float l_row = s_mx[0][r] + s_mx[1][r];
     if (row_ok) {
-      const float inv = l_run > 0.f ? __fdiv_rn(1.0f, l_run) : 0.f;
-      bf16* dst = out + ((size_t)(tile.q_row0 + t) * nq + kvh * 2 + h) * PT_HD;
+      const float inv = l_row > 0.f ? __fdiv_rn(1.0f, l_row) : 0.f;
+      bf16* dst = out + ((size_t)(tile.q_row0 + t) * nq + kvh * 2 + h) * PT_HD + kh * HALF;
 #pragma unroll
-      for (int c = 0; c < PT_HD / 8; ++c) {
+      for (int c = 0; c < HALF / 8; ++c) {
         float v[8];
 #pragma unroll
         for (int e = 0; e < 8; ++e) v[e] = o[c * 8 + e] * inv;
@@ -278,7 +289,7 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 4) {
+  if (warp == 8) {
     tc_fence_after();
     tmem_dealloc(tmem, PT_TMEM_COLS);
   }
@@ -304,9 +315,8 @@ int launch_attn_prefill_tc(const bf16* q, const bf16* k_pages, const bf16* v_pag
   if (attr_once.need()) B2_CUDA_OK(cudaFuncSetAttribute(attn_prefill_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PT_SMEM));
   const double scale = softmax_scale > 0.f ? (double)softmax_scale : 1.0 / sqrt((double)hd);
   const float scale_log2 = (float)(scale * 1.4426950408889634);
-  static const int dbg = [] { const char* e = getenv("B2_PTC_DBG"); return e ? atoi(e) : 0; }();  // timing experiments only
-  B2_CUDA_OK(b2_launch(attn_prefill_tc_kernel, dim3(ntiles, nkv), dim3(160), (size_t)PT_SMEM, s, tk, tv, q, block_table, bt_stride, tiles_dev,
-                       out, nq, nkv, scale_log2, window, dbg));
+  B2_CUDA_OK(b2_launch(attn_prefill_tc_kernel, dim3(ntiles, nkv), dim3(288), (size_t)PT_SMEM, s, tk, tv, q, block_table, bt_stride, tiles_dev,
+                       out, nq, nkv, scale_log2, window));
   return 0;
 }
 

@@ -73,6 +73,12 @@ extern "C" int b2k_debug_step_trace(void* dev_u64_buf) {
 extern "C" int b2k_gateup_swiglu(const void* x, const void* w_gu, void* act, int T, int I, int K, void* stream) {
   B2_REQUIRE(x && w_gu && act, "b2k_gateup_swiglu: null pointer");
   CUtensorMap tm;
+  if (T > 64) {  // prefill-sized: gemm_gateup.cu
+    CUtensorMap tx;
+    CAPI_TRY(b2_make_tmap_bf16(&tm, w_gu, (uint64_t)2 * I, (uint64_t)K, (uint64_t)K, 128));
+    CAPI_TRY(b2_make_tmap_bf16(&tx, x, (uint64_t)T, (uint64_t)K, (uint64_t)K, 128));
+    return launch_gateup_swiglu_prefill(tm, tx, (bf16*)act, T, I, K, 0, (cudaStream_t)stream);
+  }
   CAPI_TRY(b2_make_tmap_bf16(&tm, w_gu, (uint64_t)2 * I, (uint64_t)K, (uint64_t)K, 64));
   return launch_gateup_swiglu(tm, (const bf16*)x, (bf16*)act, T, I, K, (cudaStream_t)stream);
 }

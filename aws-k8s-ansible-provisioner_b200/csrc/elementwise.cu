@@ -359,6 +359,95 @@ __global__ void qknorm_rope_kv_prefill_kernel(const bf16* __restrict__ qkv, cons
   }
 }
 
+// Same contract, 16 lanes per head (16 bytes each), the bf16 x bf16 products as packed HMUL2 (one rounding, identical to
+// rounding the exact fp32 product).  The four-byte-lane kernel above issued ~120 instructions per head per lane and ran
+// at a third of the HBM rate (61 us for 8192 tokens x 32 heads); this one is bound by the 134 MB it moves.
+// A half-warp walks four heads of one token; rot16 = rotary_dim / 16 lanes hold each half of the rotated span.
+__global__ void __launch_bounds__(128)
+qknorm_rope_kv_prefill16_kernel(const bf16* __restrict__ qkv, const bf16* __restrict__ qw, const bf16* __restrict__ kw,
+                                const bf16* __restrict__ cos_sin, const int32_t* __restrict__ positions,
+                                const int32_t* __restrict__ slots, bf16* __restrict__ q_out, bf16* __restrict__ k_pages,
+                                bf16* __restrict__ v_pages, int T, int nq, int nkv, int block_size, float eps, int rot16) {
+  constexpr int HD = 128;
+  pdl_wait();
+  pdl_launch_dependents();
+  const int nheads = nq + 2 * nkv, groups = nheads / 4;
+  const long long hw = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 4;
+  const int lane = threadIdx.x & 31, l16 = lane & 15;
+  const bool valid = hw < (long long)T * groups;
+  const int t = valid ? (int)(hw / groups) : 0, head0 = valid ? (int)(hw % groups) * 4 : 0;
+  const bool use_norm = qw != nullptr;
+  const bool first_half = l16 < rot16, rotates = l16 < 2 * rot16;
+  const int partner = (lane & 16) | ((first_half ? l16 + rot16 : l16 - rot16) & 15);
+  const unsigned hmask = 0xffffu << (lane & 16);  // the two halves of a warp may hold heads of different kinds
+  const uint32_t sign = first_half ? 0x80008000u : 0u;  // first half of the rotated span: rot = -partner
+  uint4 raw[4];
+#pragma unroll
+  for (int h = 0; h < 4; ++h)
+    raw[h] = *reinterpret_cast<const uint4*>(qkv + ((size_t)t * nheads + head0 + h) * HD + l16 * 8);
+  const int pos = max(positions[t], 0);
+  const int slot = slots[t];
+  uint4 co4 = make_uint4(0, 0, 0, 0), sn4 = co4, wq4 = co4, wk4 = co4;
+  if (rotates) {
+    const bf16* cs = cos_sin + (size_t)pos * HD + (first_half ? l16 : l16 - rot16) * 8;
+    co4 = *reinterpret_cast<const uint4*>(cs);
+    sn4 = *reinterpret_cast<const uint4*>(cs + 64);
+  }
+  if (use_norm) {
+    wq4 = *reinterpret_cast<const uint4*>(qw + l16 * 8);
+    wk4 = *reinterpret_cast<const uint4*>(kw + l16 * 8);
+  }
+  const uint32_t* co2 = &co4.x; const uint32_t* sn2 = &sn4.x;
+#pragma unroll
+  for (int h = 0; h < 4; ++h) {
+    const int head = head0 + h;
+    const bool is_q = head < nq, is_k = !is_q && head < nq + nkv;
+    uint32_t x2[4] = {raw[h].x, raw[h].y, raw[h].z, raw[h].w};
+    if (is_q || is_k) {  // uniform over the half-warp; the shuffles name only its own lanes
+      if (use_norm) {
+        float v[8];
+        unpack8(raw[h], v);
+        // the per-head kernel's summation tree, so that both give the same bits: there lane 2l and 2l+1 hold this
+        // lane's two quads and meet in the LAST butterfly step (xor 1), after the steps xor 16, 8, 4, 2
+        float sa = v[0] * v[0] + v[1] * v[1] + v[2] * v[2] + v[3] * v[3];
+        float sb = v[4] * v[4] + v[5] * v[5] + v[6] * v[6] + v[7] * v[7];
+#pragma unroll
+        for (int o = 8; o > 0; o >>= 1) {
+          sa += __shfl_xor_sync(hmask, sa, o);
+          sb += __shfl_xor_sync(hmask, sb, o);
+        }
+        const float ss = sa + sb;
+        const float rstd = __fdiv_rn(1.0f, __fsqrt_rn(ss / (float)HD + eps));
+        const uint32_t* w2 = is_q ? &wq4.x : &wk4.x;
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const uint32_t nx = pack_bf16x2(v[2 * e] * rstd, v[2 * e + 1] * rstd);  // bf16(x * rstd)
+          const __nv_bfloat162 n = __hmul2(*reinterpret_cast<const __nv_bfloat162*>(&w2[e]), *reinterpret_cast<const __nv_bfloat162*>(&nx));
+          x2[e] = *reinterpret_cast<const uint32_t*>(&n);
+        }
+      }
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        uint32_t rot = __shfl_sync(hmask, x2[e], partner) ^ sign;
+        const __nv_bfloat162 a = __hmul2(*reinterpret_cast<const __nv_bfloat162*>(&x2[e]), *reinterpret_cast<const __nv_bfloat162*>(&co2[e]));
+        const __nv_bfloat162 b = __hmul2(*reinterpret_cast<const __nv_bfloat162*>(&rot), *reinterpret_cast<const __nv_bfloat162*>(&sn2[e]));
+        const uint32_t au = *reinterpret_cast<const uint32_t*>(&a), bu = *reinterpret_cast<const uint32_t*>(&b);
+        if (rotates) x2[e] = pack_bf16x2(bf16lo(au) + bf16lo(bu), bf16hi(au) + bf16hi(bu));
+      }
+    }
+    const uint4 o = make_uint4(x2[0], x2[1], x2[2], x2[3]);
+    if (!valid) continue;
+    if (is_q) {
+      *reinterpret_cast<uint4*>(q_out + ((size_t)t * nq + head) * HD + l16 * 8) = o;
+    } else if (slot >= 0) {
+      const int kvh = is_k ? head - nq : head - nq - nkv;
+      const int blk = slot / block_size, off = slot % block_size;
+      bf16* base = (is_k ? k_pages : v_pages) + (((size_t)blk * nkv + kvh) * block_size + off) * HD;
+      *reinterpret_cast<uint4*>(base + kv_swizzled_chunk(off, l16) * 8) = o;
+    }
+  }
+}
+
 int launch_qknorm_rope_kv(ActIn qkv, const bf16* qw, const bf16* kw, const bf16* cos_sin, const int32_t* positions,
                           const int32_t* slots, bf16* q_out, bf16* k_pages, bf16* v_pages, int T, int nq, int nkv,
                           int hd, int block_size, float eps, cudaStream_t s, int rotary_dim, const bf16* bias, float q_mul, int tag) {
@@ -371,6 +460,12 @@ int launch_qknorm_rope_kv(ActIn qkv, const bf16* qw, const bf16* kw, const bf16*
   const int nheads = nq + 2 * nkv;
   if (!qkv.is_f32 && bias == nullptr && q_mul == 1.0f && nheads % 4 == 0 && (long long)T * nheads >= 32768) {
     const long long w4 = (long long)T * (nheads / 4);
+    static const bool lanes16 = getenv("B2_ROPE16") == nullptr || atoi(getenv("B2_ROPE16")) != 0;
+    if (lanes16 && rotary_dim % 16 == 0) {  // two four-head groups per warp
+      B2_CUDA_OK(b2_launch(qknorm_rope_kv_prefill16_kernel, dim3((unsigned)((w4 + 7) / 8)), dim3(128), 0, s, (const bf16*)qkv.ptr, qw, kw,
+                           cos_sin, positions, slots, q_out, k_pages, v_pages, T, nq, nkv, block_size, eps, rotary_dim / 16));
+      return 0;
+    }
     B2_CUDA_OK(b2_launch(qknorm_rope_kv_prefill_kernel, dim3((unsigned)((w4 + 3) / 4)), dim3(128), 0, s, (const bf16*)qkv.ptr, qw, kw,
                          cos_sin, positions, slots, q_out, k_pages, v_pages, T, nq, nkv, block_size, eps, rot_quads));
     return 0;

@@ -239,6 +239,7 @@ struct b2_engine {
                                           // prefetch competes with the tail of the K/V stream)
   int use_chain = 0;  // B2_CHAIN: 0 separate kernels (default, fastest measured), 1 chain.cu, 2 chain_cluster.cu
   int prefill_tc = 1; // B2_PREFILL_TC: prefill attention on tcgen05 (attn_prefill_tc.cu); 0 = the mma.sync kernel (attn_prefill.cu)
+  int gu_prefill_fused = 1;  // B2_GU_FUSED: prefill-sized gate/up projection with SwiGLU in its epilogue (gemm_gateup.cu)
   int use_pair = 1;   // B2_PAIR: bit 0 gate/up + SwiGLU, bit 1 QKV + QK-norm/RoPE/KV write as fused cluster-pair launches (gemm_pair.cu)
 
   // two-lane decode (B2_MB, see forward()): second stream, its own partials and attention scratch, fork/join events
@@ -700,6 +701,9 @@ int forward_layers(b2_engine* e, const Lane& ln, int T, int ntiles) {
     if (pair_ok && (e->use_pair & 1) && I % 64 == 0 && !((e->skip_mask >> B2K_ACT) & 1u)) {
       KL k(e, B2K_GEMM_GATEUP);
       if (!k.skip()) B2_TRY(launch_gateup_swiglu(L.tm_gu64, x, act, T, I, H, st, tag));
+    } else if (e->gu_prefill_fused && e->force_gemm_impl != 0 && gateup_prefill_shapes_ok(T, I, H) && !((e->skip_mask >> B2K_ACT) & 1u)) {
+      KL k(e, B2K_GEMM_GATEUP);  // prefill-sized: SwiGLU in the projection's epilogue, no gu round trip through HBM
+      if (!k.skip()) B2_TRY(launch_gateup_swiglu_prefill(L.tm_gu, e->tm_x[XB_X][bn_index(128)], act, T, I, H, ln.row0, st));
     } else {
       ActIn gu = linear(e, ln, B2K_GEMM_GATEUP, XB_X, x, L.wgu, L.tm_gu, gub, T, 2 * I, H, &rc, prefetch_for(l + 1, 1));
       B2_TRY(rc);
@@ -1375,6 +1379,7 @@ extern "C" int b2_engine_create(const b2_config* cfg, const char* safetensors_pa
   e->use_chain = env_int("B2_CHAIN", 0);
   e->use_pair = env_int("B2_PAIR", 3);
   e->prefill_tc = env_int("B2_PREFILL_TC", 1);
+  e->gu_prefill_fused = env_int("B2_GU_FUSED", 1);
   e->o_small_smem = env_int("B2_O_SMALL", 0);
   // Off by default: measured on B200 at C2 (ms/step) 0 MB 2.22, 40 MB 2.24, 72 MB 2.33, 100 MB 2.38 --
   // un-paced prefetch bursts queue ahead of the projections' own latency-critical weight loads.

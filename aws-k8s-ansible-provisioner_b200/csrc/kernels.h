@@ -94,6 +94,9 @@ int tc_pick_nsplit(int T, int N, int K, int num_sms);
 // ---- gemm_pair.cu: a projection and the element-wise kernel behind it in one launch (clusters of two CTAs split K and
 //      exchange accumulator halves through distributed shared memory); at most 64 tokens, K <= 1024 ----
 bool pair_shapes_ok(int T, int K);
+// gemm_gateup.cu: the prefill-sized counterpart (two accumulators per tile, SwiGLU in the epilogue)
+bool gateup_prefill_shapes_ok(int T, int I, int K);
+int launch_gateup_swiglu_prefill(const CUtensorMap& tm_w, const CUtensorMap& tm_x128, bf16* act, int T, int I, int K, int x_row0, cudaStream_t s);
 int launch_gateup_swiglu(const CUtensorMap& tm_gu64, const bf16* x, bf16* act, int T, int I, int K, cudaStream_t s, int tag = 0);
 int launch_qkv_rope(const CUtensorMap& tm_qkv, const bf16* x, const bf16* qw, const bf16* kw, const bf16* cos_sin, const int32_t* positions,
                     const int32_t* slots, bf16* q_out, bf16* k_pages, bf16* v_pages, int T, int nq, int nkv, int K, int block_size,

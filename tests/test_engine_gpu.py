@@ -132,7 +132,10 @@ def test_tiny_batch_invariance_and_ragged(P, tiny):
         sid = e.seq_create(200)
         f = e.prefill([sid], [p])
         solo_logits = e.get_logits(1)[0]
-        assert rel_err(torch.from_numpy(batch_logits[i]), torch.from_numpy(solo_logits)) < 2e-3
+        # the batched prefill and the solo one take different projection tiles / K splits (fp32 sums in another order),
+        # so activations round to the neighbouring bf16 here and there and two layers carry that into the logits: the bar is
+        # the one the oracle comparison below uses, not bit equality (one bf16 ulp of the largest logit alone is 3.9e-3)
+        assert rel_err(torch.from_numpy(batch_logits[i]), torch.from_numpy(solo_logits)) < REL_TOL
         ref_logits, _ = r.forward(torch.tensor([p]), torch.arange(len(p))[None], KVState(), last_only=True)
         assert rel_err(torch.from_numpy(solo_logits), ref_logits[0, 0].float()) < REL_TOL, "prompt len %d" % len(p)
         solo = [f] + [e.decode_step([sid]) for _ in range(6)]

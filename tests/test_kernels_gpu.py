@@ -246,6 +246,30 @@ def test_gateup_swiglu_fused(lib, T):
     assert_bf16_close(act, a2, 2, 0.02, "fused vs separate kernels", abs_floor=2e-3)
 
 
+@pytest.mark.parametrize("T,I,K", [(256, 3072, 1024), (1000, 3072, 1024), (4099, 3072, 1024), (300, 8192, 3072), (277, 512, 256)])
+def test_gateup_swiglu_prefill_fused(lib, T, I, K):
+    """gemm_gateup.cu: the prefill-sized gate/up projection with SwiGLU in its epilogue (two TMEM accumulators per tile).
+    Same k order, one accumulator per output, same rounding points as b2k_linear followed by b2k_silu_mul: BIT-identical to
+    that path, ragged last token tile included, and no write past row T."""
+    x = bf(T, K, seed=31)
+    w = bf(2 * I, K, scale=0.05, seed=32)
+    act = torch.full((T + 3, I), float("nan"), dtype=torch.bfloat16, device="cuda")
+    dx, dw = dv(x), dv(w)
+    chk(lib, lib.b2k_gateup_swiglu(ptr(dx), ptr(dw), ptr(act), T, I, K, cuda_stream_ptr()))
+    g2 = torch.empty(T, 2 * I, dtype=torch.bfloat16, device="cuda")
+    a2 = torch.empty(T, I, dtype=torch.bfloat16, device="cuda")
+    chk(lib, lib.b2k_linear(ptr(dx), ptr(dw), ptr(g2), 0, 1, T, 2 * I, K, 1, cuda_stream_ptr()))
+    chk(lib, lib.b2k_silu_mul(ptr(g2), 0, 1, ptr(a2), T, I, cuda_stream_ptr()))
+    torch.cuda.synchronize()
+    assert torch.equal(act[:T], a2), "fused prefill gate/up + SwiGLU differs from the two-kernel path"
+    assert torch.isnan(act[T:].float()).all(), "wrote past the last token row"
+    rows = slice(0, min(T, 512))
+    gu = (x[rows].float() @ w.float().t()).to(torch.bfloat16)
+    ref = torch.nn.functional.silu(gu[:, :I]) * gu[:, I:]
+    # torch sums the K products in another order: g and u may round to the neighbouring bf16, and the product carries it
+    assert rel_fro(act[rows], ref) < 5e-3 and rel_err(act[rows], ref) < 1e-2, (rel_fro(act[rows], ref), rel_err(act[rows], ref))
+
+
 @pytest.mark.parametrize("T", [64, 40, 17, 1])
 def test_qkv_rope_fused(lib, T):
     """gemm_pair.cu: QKV projection + QK-norm + RoPE + KV page write in one launch, against b2k_linear followed by
