@@ -68,6 +68,7 @@ extern "C" int b2k_debug_step_trace(void* dev_u64_buf) {
   CAPI_TRY(step_trace_set_elementwise(b));
   CAPI_TRY(step_trace_set_gemm(b));
   CAPI_TRY(step_trace_set_pair(b));
+  CAPI_TRY(step_trace_set_resid(b));
   return step_trace_set_attn(b);
 }
 extern "C" int b2k_gateup_swiglu(const void* x, const void* w_gu, void* act, int T, int I, int K, void* stream) {
@@ -91,6 +92,36 @@ extern "C" int b2k_qkv_rope(const void* x, const void* w_qkv, const void* qnorm_
   CAPI_TRY(b2_make_tmap_bf16(&tm, w_qkv, (uint64_t)(nq + 2 * nkv) * 128, (uint64_t)K, (uint64_t)K, 128));
   return launch_qkv_rope(tm, (const bf16*)x, (const bf16*)qnorm_w, (const bf16*)knorm_w, (const bf16*)cos_sin, positions, slots, (bf16*)q_out,
                          (bf16*)k_pages, (bf16*)v_pages, T, nq, nkv, K, block_size, eps, (cudaStream_t)stream);
+}
+
+extern "C" int b2k_linear_resid(const void* x, const void* w, void* h, float* ssq, int T, int N, int K, int ssq_ld, void* stream) {
+  B2_REQUIRE(x && w && h && ssq, "b2k_linear_resid: null pointer");
+  CUtensorMap tm;
+  CAPI_TRY(b2_make_tmap_bf16(&tm, w, (uint64_t)N, (uint64_t)K, (uint64_t)K, 128));
+  return launch_linear_resid(tm, (const bf16*)x, (bf16*)h, ssq, T, N, K, ssq_ld, (cudaStream_t)stream);
+}
+
+extern "C" int b2k_gateup_swiglu_norm(const void* h, const void* w_gu, const void* norm_w, const float* ssq, int pieces, int ssq_ld, float eps,
+                                      void* act, int T, int I, int K, void* stream) {
+  B2_REQUIRE(h && w_gu && norm_w && ssq && act, "b2k_gateup_swiglu_norm: null pointer");
+  CUtensorMap tm;
+  CAPI_TRY(b2_make_tmap_bf16(&tm, w_gu, (uint64_t)2 * I, (uint64_t)K, (uint64_t)K, 64));
+  PairNorm pn;
+  pn.ssq = ssq; pn.gain = (const bf16*)norm_w; pn.pieces = pieces; pn.ld = ssq_ld; pn.eps = eps;
+  return launch_gateup_swiglu(tm, (const bf16*)h, (bf16*)act, T, I, K, (cudaStream_t)stream, 0, pn);
+}
+
+extern "C" int b2k_qkv_rope_norm(const void* h, const void* w_qkv, const void* norm_w, const float* ssq, int pieces, int ssq_ld, float norm_eps,
+                                 const void* qnorm_w, const void* knorm_w, const void* cos_sin, const int32_t* positions, const int32_t* slots,
+                                 void* q_out, void* k_pages, void* v_pages, int T, int nq, int nkv, int K, int block_size, float eps,
+                                 void* stream) {
+  B2_REQUIRE(h && w_qkv && norm_w && ssq && q_out && k_pages && v_pages, "b2k_qkv_rope_norm: null pointer");
+  CUtensorMap tm;
+  CAPI_TRY(b2_make_tmap_bf16(&tm, w_qkv, (uint64_t)(nq + 2 * nkv) * 128, (uint64_t)K, (uint64_t)K, 128));
+  PairNorm pn;
+  pn.ssq = ssq; pn.gain = (const bf16*)norm_w; pn.pieces = pieces; pn.ld = ssq_ld; pn.eps = norm_eps;
+  return launch_qkv_rope(tm, (const bf16*)h, (const bf16*)qnorm_w, (const bf16*)knorm_w, (const bf16*)cos_sin, positions, slots, (bf16*)q_out,
+                         (bf16*)k_pages, (bf16*)v_pages, T, nq, nkv, K, block_size, eps, (cudaStream_t)stream, 0, pn);
 }
 
 extern "C" int b2k_debug_gemm_trace(void* dev_u64_buf) { return tc_set_trace((unsigned long long*)dev_u64_buf); }

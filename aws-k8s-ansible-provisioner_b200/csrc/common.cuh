@@ -86,6 +86,23 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) {
 // AND anything produced two or more kernels earlier (block tables, sequence lengths, the residual
 // stream, all K/V pages except the slots the previous kernel is writing).
 // ---------------------------------------------------------------------------------------
+// A kernel's idle lanes ask for the NEXT kernel's weights to be brought into L2 (cp.async.bulk.prefetch.L2, 4 KB per
+// request): the next kernel's TMA stream then starts from L2 instead of HBM even when its CTAs could not become
+// resident early (see gemm_resid.cu).  part / nparts: this CTA's share.
+struct L2Prefetch {
+  const void* ptr = nullptr;
+  unsigned long long bytes = 0;
+};
+__device__ __forceinline__ void b2_l2_prefetch(const L2Prefetch& pf, int part, int nparts, int lane) {
+  if (pf.ptr == nullptr) return;
+  const unsigned long long nchunks = (pf.bytes + 4095ull) >> 12;
+  for (unsigned long long c = (unsigned long long)part * 32 + lane; c < nchunks; c += (unsigned long long)nparts * 32) {
+    const unsigned long long off = c << 12;
+    const unsigned long long left = pf.bytes - off;
+    const unsigned sz = (unsigned)(left < 4096ull ? (left & ~15ull) : 4096ull);
+    if (sz) asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(reinterpret_cast<const char*>(pf.ptr) + off), "r"(sz) : "memory");
+  }
+}
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 

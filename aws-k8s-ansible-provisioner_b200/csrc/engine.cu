@@ -239,6 +239,7 @@ struct b2_engine {
                                           // prefetch competes with the tail of the K/V stream)
   int use_chain = 0;  // B2_CHAIN: 0 separate kernels (default, fastest measured), 1 chain.cu, 2 chain_cluster.cu
   int prefill_tc = 1; // B2_PREFILL_TC: prefill attention on tcgen05 (attn_prefill_tc.cu); 0 = the mma.sync kernel (attn_prefill.cu)
+  int l2_weight_prefetch = 0;  // B2_WPF: resid path, see forward_layers (measured slower: off)
   int gu_prefill_fused = 1;  // B2_GU_FUSED: prefill-sized gate/up projection with SwiGLU in its epilogue (gemm_gateup.cu)
   int use_pair = 1;   // B2_PAIR: bit 0 gate/up + SwiGLU, bit 1 QKV + QK-norm/RoPE/KV write as fused cluster-pair launches (gemm_pair.cu)
 
@@ -248,6 +249,7 @@ struct b2_engine {
   float* partial2 = nullptr;
   size_t partial2_floats = 0;
   float* attn_scratch2 = nullptr;
+  float* ssq = nullptr;  // [hidden / 16][64]: pieces of the next RMSNorm's sum of squares (gemm_resid.cu -> gemm_pair.cu)
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
 };
 
@@ -653,21 +655,45 @@ int forward_layers(b2_engine* e, const Lane& ln, int T, int ntiles) {
     LayerW& L = e->layers[l];
     bf16* kp = e->kv_pool + (size_t)(2 * l) * e->layer_kv_elems;
     bf16* vp = kp + e->layer_kv_elems;
-    {
-      KL k(e, B2K_NORM);
-      if (!k.skip()) B2_TRY(launch_add_rmsnorm(h, delta, L.ln1, x, T, H, c.rms_eps, st, tag));
-    }
-    if (l > 0) dbg_capture(e, l, e->h, T);
     // decode-sized forwards: the fused cluster-pair launches of gemm_pair.cu take the place of (projection, element-wise
     // kernel) pairs where the model's shapes allow it
     const bool pair_ok = ntiles == 0 && !ln.beside_attention && e->force_gemm_impl != 0 && T > e->simt_max_tokens && pair_shapes_ok(T, H) &&
                          !(e->debug_flags & 1) && e->kv_l2_budget <= 0;
-    if (pair_ok && (e->use_pair & 2) && c.arch == B2_ARCH_QWEN3 && e->native_geom && e->rotary_dim == 128 && L.qnorm != nullptr &&
-        !((e->skip_mask >> B2K_ROPE_KV) & 1u)) {
+    const bool qkv_pair = pair_ok && (e->use_pair & 2) && c.arch == B2_ARCH_QWEN3 && e->native_geom && e->rotary_dim == 128 && L.qnorm != nullptr &&
+                          !((e->skip_mask >> B2K_ROPE_KV) & 1u);
+    const bool gu_pair = pair_ok && (e->use_pair & 1) && I % 64 == 0 && !((e->skip_mask >> B2K_ACT) & 1u);
+    // ... and with both in place the O / down projections add into the residual stream themselves (gemm_resid.cu) and the
+    // pair kernels normalise h as they load it: no norm kernel inside the layer loop (skip-mask ablations take the old path)
+    const bool resid = qkv_pair && gu_pair && (e->use_pair & 4) && e->ssq != nullptr && H / 16 <= 64 && resid_shapes_ok(T, H, e->q_size) &&
+                       resid_shapes_ok(T, H, I) && !((e->skip_mask >> B2K_NORM) & 1u) && !((e->skip_mask >> B2K_GEMM_O) & 1u) &&
+                       !((e->skip_mask >> B2K_GEMM_DOWN) & 1u) && !((e->skip_mask >> B2K_GEMM_QKV) & 1u) && !((e->skip_mask >> B2K_GEMM_GATEUP) & 1u);
+    PairNorm pn1, pn2;
+    if (resid) {
+      pn1.ssq = pn2.ssq = e->ssq;
+      pn1.gain = L.ln1; pn2.gain = L.ln2;
+      pn1.pieces = pn2.pieces = H / 16;
+      pn1.ld = pn2.ld = 64;
+      pn1.eps = pn2.eps = c.rms_eps;
+    }
+    // resid path: each launch's idle lanes pull the NEXT launch's weights into L2 (the fat CTAs of these kernels cannot be
+    // resident beside each other, so a launch can no longer start its own weight stream while its predecessor runs)
+    L2Prefetch pf_gu, pf_d, pf_qkv_next;
+    if (resid && e->l2_weight_prefetch) {
+      pf_gu.ptr = L.wgu; pf_gu.bytes = (unsigned long long)2 * I * H * 2;
+      pf_d.ptr = L.wd; pf_d.bytes = (unsigned long long)H * I * 2;
+      if (l + 1 < c.num_layers) { pf_qkv_next.ptr = e->layers[l + 1].wqkv; pf_qkv_next.bytes = (unsigned long long)e->qkv_size * H * 2; }
+      pn2.next_w = pf_d;
+    }
+    if (!(resid && l > 0)) {  // layer 0 (h comes from the embedding kernel) and every layer of the stand-alone path
+      KL k(e, B2K_NORM);
+      if (!k.skip()) B2_TRY(launch_add_rmsnorm(h, delta, L.ln1, x, T, H, c.rms_eps, st, tag));
+    }
+    if (l > 0) dbg_capture(e, l, e->h, T);
+    if (qkv_pair) {
       KL k(e, B2K_GEMM_QKV);
       if (!k.skip())
-        B2_TRY(launch_qkv_rope(L.tm_qkv, x, L.qnorm, L.knorm, e->cos_sin, positions, slots, qrot, kp, vp, T, e->nq, e->nkv, H, c.block_size,
-                               c.rms_eps, st, tag));
+        B2_TRY(launch_qkv_rope(L.tm_qkv, (resid && l > 0) ? h : x, L.qnorm, L.knorm, e->cos_sin, positions, slots, qrot, kp, vp, T, e->nq, e->nkv, H,
+                               c.block_size, c.rms_eps, st, tag, (resid && l > 0) ? pn1 : PairNorm()));
     } else {
       ActIn qkv = linear(e, ln, B2K_GEMM_QKV, XB_X, x, L.wqkv, L.tm_qkv, qkvb, T, e->qkv_size, H, &rc, prefetch_for(l, 3));
       B2_TRY(rc);
@@ -691,6 +717,20 @@ int forward_layers(b2_engine* e, const Lane& ln, int T, int ntiles) {
         B2_TRY(launch_attn_decode(qrot, kp, vp, block_table, e->bt_stride, seq_lens, ln.attn_scratch, attn, T,
                                   e->nq, e->nkv, e->hd, c.block_size, st, e->attn_scale, c.sliding_window, tag));
     }
+    if (resid) {
+      {
+        KL k(e, B2K_GEMM_O);
+        B2_TRY(launch_linear_resid(L.tm_o, attn, h, e->ssq, T, H, e->q_size, 64, st, tag, pf_gu));
+      }
+      {
+        KL k(e, B2K_GEMM_GATEUP);
+        B2_TRY(launch_gateup_swiglu(L.tm_gu64, h, act, T, I, H, st, tag, pn2));
+      }
+      KL k(e, B2K_GEMM_DOWN);
+      B2_TRY(launch_linear_resid(L.tm_d, act, h, e->ssq, T, H, I, 64, st, tag, pf_qkv_next));
+      delta = act_bf16(nullptr);  // h is up to date: the next norm (layer 0's successor never runs one; the final norm) adds nothing
+      continue;
+    }
     ActIn o = linear(e, ln, B2K_GEMM_O, XB_ATTN, attn, L.wo, L.tm_o, proj, T, H, e->q_size, &rc, prefetch_for(l + 1, 0), false,
                      /*after_attention=*/ntiles == 0);
     B2_TRY(rc);
@@ -698,7 +738,7 @@ int forward_layers(b2_engine* e, const Lane& ln, int T, int ntiles) {
       KL k(e, B2K_NORM);
       if (!k.skip()) B2_TRY(launch_add_rmsnorm(h, o, L.ln2, x, T, H, c.rms_eps, st, tag));
     }
-    if (pair_ok && (e->use_pair & 1) && I % 64 == 0 && !((e->skip_mask >> B2K_ACT) & 1u)) {
+    if (gu_pair) {
       KL k(e, B2K_GEMM_GATEUP);
       if (!k.skip()) B2_TRY(launch_gateup_swiglu(L.tm_gu64, x, act, T, I, H, st, tag));
     } else if (e->gu_prefill_fused && e->force_gemm_impl != 0 && gateup_prefill_shapes_ok(T, I, H) && !((e->skip_mask >> B2K_ACT) & 1u)) {
@@ -1377,9 +1417,10 @@ extern "C" int b2_engine_create(const b2_config* cfg, const char* safetensors_pa
   // 0 separate kernels (default: fastest measured), 1 eight-step chain kernel (chain.cu), 2 fused four-step cluster
   // chain (chain_cluster.cu); 1 and 2 are kept as measured experiments with parity tests
   e->use_chain = env_int("B2_CHAIN", 0);
-  e->use_pair = env_int("B2_PAIR", 3);
+  e->use_pair = env_int("B2_PAIR", 7);  // bit 2: O / down projections update the residual stream themselves (gemm_resid.cu)
   e->prefill_tc = env_int("B2_PREFILL_TC", 1);
   e->gu_prefill_fused = env_int("B2_GU_FUSED", 1);
+  e->l2_weight_prefetch = env_int("B2_WPF", 0);
   e->o_small_smem = env_int("B2_O_SMALL", 0);
   // Off by default: measured on B200 at C2 (ms/step) 0 MB 2.22, 40 MB 2.24, 72 MB 2.33, 100 MB 2.38 --
   // un-paced prefetch bursts queue ahead of the projections' own latency-critical weight loads.
@@ -1506,6 +1547,7 @@ extern "C" int b2_engine_create(const b2_config* cfg, const char* safetensors_pa
       E_TRY(dalloc(&e->attn_scratch2, e->attn_scratch_floats));
       E_CUDA(cudaMemset(e->attn_scratch2, 0, e->attn_scratch_floats * sizeof(float)));
     }
+    E_TRY(dalloc(&e->ssq, (size_t)(H / 16) * 64));
     for (int bi = 0; bi < 5; ++bi) {
       E_TRY(b2_make_tmap_bf16(&e->tm_x[XB_X][bi], e->x, Tc, H, H, kBnList[bi]));
       E_TRY(b2_make_tmap_bf16(&e->tm_x[XB_ATTN][bi], e->attn, Tc, e->q_size, e->q_size, kBnList[bi]));
@@ -1661,7 +1703,7 @@ extern "C" void b2_engine_free(b2_engine* e) {
   if (e->h_out) cudaFreeHost(e->h_out);
   if (e->h_tok) cudaFreeHost(e->h_tok);
   if (e->ev_tok) cudaEventDestroy(e->ev_tok);
-  F(e->partial2); F(e->attn_scratch2);
+  F(e->partial2); F(e->attn_scratch2); F(e->ssq);
   if (e->ev_fork) cudaEventDestroy(e->ev_fork);
   if (e->ev_join) cudaEventDestroy(e->ev_join);
   if (e->stream2) cudaStreamDestroy(e->stream2);

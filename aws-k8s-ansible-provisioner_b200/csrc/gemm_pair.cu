@@ -29,6 +29,8 @@ namespace {
 constexpr int GP_BM = 128, GP_BK = 64;
 constexpr int GP_W_BYTES = GP_BM * GP_BK * 2;  // 16 KB of weights per k-block
 constexpr int GP_MAX_KB = 8;                   // k-blocks per CTA (K/2 <= 512)
+constexpr int GP_LOADERS = 256;                // X loader threads when the rows are normalised on load (warps 2..9), else 128 (warps 2..5)
+constexpr int GP_THREADS = 64 + GP_LOADERS;    // largest block; warps 2..5 are also the epilogue
 
 template <int BN>
 struct GpCfg {
@@ -42,6 +44,18 @@ struct GpCfg {
 };
 
 enum { GP_SWIGLU = 0, GP_QKV_ROPE = 1 };
+
+// Normalise-on-load: x is the RESIDUAL stream h (not a normalised copy) and ssq holds, per 16-feature piece, the sum of
+// squares of each token's row (written by gemm_resid.cu); the X loader threads scale the rows as they stage them:
+//   x = bf16(gain * bf16(h * rsqrt(mean(h^2) + eps)))          (HF:models/qwen3/modeling_qwen3.py:50-62)
+// so that no norm kernel runs between the projection that updated h and this one.  ssq == nullptr: x is used as it is.
+struct GpNorm {
+  const float* ssq;   // [pieces][ld]
+  const bf16* gain;   // [K]
+  int pieces, ld;
+  float eps;
+  L2Prefetch next_w;  // weights of the projection after this one, to be pulled into L2 (independent of ssq)
+};
 
 struct GpRope {  // QKV mode
   const bf16 *qw, *kw, *cos_sin;
@@ -65,12 +79,13 @@ __device__ __forceinline__ void gp_st_cluster_f32(uint32_t addr, float v) {
   asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
 }
 
-// grid = 2 * m_tiles CTAs in clusters of 2; block = 192 threads: warp 0 TMA producer (weights), warp 1 MMA issuer,
-// warps 2-5 fetch X with cp.async, then exchange / finish the accumulator.
+// grid = 2 * m_tiles CTAs in clusters of 2; block = 320 threads: warp 0 TMA producer (weights), warp 1 MMA issuer,
+// warps 2-9 bring in X (cp.async, or through registers when the rows are normalised on the way), warps 2-5 then
+// exchange / finish the accumulator.
 template <int BN, int MODE>
-__global__ void __launch_bounds__(192, 1)
+__global__ void __launch_bounds__(GP_THREADS, 1)
 linear_pair_kernel(const __grid_constant__ CUtensorMap tmap_w, const bf16* __restrict__ x, bf16* __restrict__ out, int T, int N, int K,
-                   int up_row0, int m_tiles, const GpRope rp, int tag) {
+                   int up_row0, int m_tiles, const GpRope rp, const GpNorm nm, int tag) {
   using C = GpCfg<BN>;
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t full_bar, tmem_full_bar;
@@ -89,6 +104,8 @@ linear_pair_kernel(const __grid_constant__ CUtensorMap tmap_w, const bf16* __res
   bf16* cs_rows = reinterpret_cast<bf16*>(smem_al + GP_MAX_KB * C::STAGE_BYTES + C::RED_BYTES);  // [token][cos 64 | sin 64]
   __shared__ int s_slot[C::HALF];
   __shared__ __align__(16) bf16 s_gain[2 * 128];  // QKV mode: QK-norm gains, q then k
+  __shared__ __align__(16) bf16 s_ngain[GP_MAX_KB * GP_BK];  // normalise-on-load: the RMSNorm gains of this CTA's K half
+  __shared__ float s_rstd[BN];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t rank = gp_cluster_rank();
   const int m_tile = (blockIdx.x >> 1) % m_tiles;
@@ -101,7 +118,7 @@ linear_pair_kernel(const __grid_constant__ CUtensorMap tmap_w, const bf16* __res
     // ONE barrier for all operands (all weight bytes + one arrival per X-loader thread).  Two barriers -- MMAs of the
     // first k-blocks issued while the second half of X lands -- measured slower (accumulator ready 2.6 instead of 2.05 us
     // after the wait): X lands within one L2 round trip anyway, and every extra wait / proxy fence costs ~0.1-0.3 us.
-    mbar_init(smem_u32(&full_bar), 1 + 128);
+    mbar_init(smem_u32(&full_bar), 1 + (blockDim.x - 64));  // all weight bytes + one arrival per X-loader thread
     mbar_init(smem_u32(&tmem_full_bar), 1);
     mbar_fence_init();
   }
@@ -128,6 +145,7 @@ linear_pair_kernel(const __grid_constant__ CUtensorMap tmap_w, const bf16* __res
       }
     }
   }
+  if (warp == 0) b2_l2_prefetch(nm.next_w, blockIdx.x, gridDim.x, lane);
   // both CTAs of the pair are running (their shared memory is live) before anyone stores into the peer's
   __syncwarp();
   asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
@@ -139,13 +157,17 @@ linear_pair_kernel(const __grid_constant__ CUtensorMap tmap_w, const bf16* __res
     const int et = threadIdx.x - 64;
     const int tb = tok0 + (int)rank * C::HALF;
     if (et < 32) reinterpret_cast<uint4*>(s_gain)[et] = reinterpret_cast<const uint4*>(et < 16 ? rp.qw : rp.kw)[et & 15];  // q gains | k gains
-    for (int idx = et; idx < C::HALF * 16; idx += 128) {  // 16 chunks of 16 bytes per 256-byte row
+    for (int idx = et; idx < C::HALF * 16; idx += (int)blockDim.x - 64) {  // 16 chunks of 16 bytes per 256-byte row
       const int j = idx >> 4, c = idx & 15;
       const int tok = tb + j;
       const int pos = tok < T ? max(rp.positions[tok], 0) : 0;
       reinterpret_cast<uint4*>(cs_rows + j * 128)[c] = reinterpret_cast<const uint4*>(rp.cos_sin + (size_t)pos * 128)[c];
     }
     if (et < C::HALF) s_slot[et] = (tb + et < T) ? rp.slots[tb + et] : -1;
+  }
+  if (nm.ssq != nullptr && warp >= 2) {  // the gains are constants: staged before the dependency wait
+    const int et = threadIdx.x - 64;
+    if (et < nkb * (GP_BK / 8)) reinterpret_cast<uint4*>(s_ngain)[et] = reinterpret_cast<const uint4*>(nm.gain + (size_t)kb0 * GP_BK)[et];
   }
   pdl_wait();
   if (threadIdx.x == 0) pdl_launch_dependents();
@@ -167,17 +189,18 @@ linear_pair_kernel(const __grid_constant__ CUtensorMap tmap_w, const bf16* __res
       tc_commit(smem_u32(&tmem_full_bar));
     }
   } else if (warp >= 2) {
-    // ---- X rows [0, BN) x this CTA's K half, 16 bytes per cp.async, into the 128-byte-swizzled tile layout ----
+    // ---- X rows [0, BN) x this CTA's K half into the 128-byte-swizzled tile layout, 16 bytes per thread and step ----
     const int et = threadIdx.x - 64;
     const bf16* xg = x + (size_t)tok0 * K + (size_t)kb0 * GP_BK;
-    constexpr int CHUNKS = BN * 8;
+    constexpr int CHUNKS = BN * 8;                        // 16-byte chunks per k-block tile
+    constexpr int CPT = GP_MAX_KB * CHUNKS / GP_LOADERS;  // chunks per thread at most: 16 (BN 64) or 8 (BN 32)
+    if (nm.ssq == nullptr) {  // 128 loader threads (a 192-thread block)
 #pragma unroll 1
-    for (int i = 0; i < nkb; ++i) {
-      const uint32_t xs = smem_base + i * C::STAGE_BYTES + GP_W_BYTES;
+      for (int i = 0; i < nkb; ++i) {
+        const uint32_t xs = smem_base + i * C::STAGE_BYTES + GP_W_BYTES;
 #pragma unroll
-      for (int c0 = 0; c0 < CHUNKS; c0 += 128) {
-        const int idx = c0 + et;
-        if (CHUNKS >= 128 || idx < CHUNKS) {
+        for (int c0 = 0; c0 < CHUNKS; c0 += 128) {
+          const int idx = c0 + et;
           const int r = idx >> 3, c = idx & 7;
           const bool in = tok0 + r < T;
           const bf16* src = xg + (size_t)(in ? r : 0) * K + i * GP_BK + c * 8;
@@ -185,9 +208,59 @@ linear_pair_kernel(const __grid_constant__ CUtensorMap tmap_w, const bf16* __res
                        : "memory");
         }
       }
+      asm volatile("cp.async.commit_group;" ::: "memory");
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+    } else {
+      // Normalise on load.  Everything this thread needs is requested at once -- its share of the statistic's pieces and
+      // its 16-byte chunks of h, through registers -- so the whole stage costs one L2 round trip plus ~25 instructions
+      // per chunk.  (A first version copied with cp.async and rescaled the tile in shared memory with 128 threads: 1.4-2.2 us
+      // more before the first MMA than the plain copy, which ate what dropping the norm kernel had saved.)
+      constexpr int TPN = GP_LOADERS / BN;  // threads per token for the statistic: 4 or 8
+      const int j = et / TPN, part = et % TPN;
+      const int per = nm.pieces / TPN;      // <= 16
+      const bool jin = tok0 + j < T;
+      const float* sp = nm.ssq + (size_t)(part * per) * nm.ld + tok0 + (jin ? j : 0);
+      float pv[16];
+#pragma unroll
+      for (int c = 0; c < 16; ++c) pv[c] = c < per ? sp[(size_t)c * nm.ld] : 0.f;
+      uint4 xr[CPT];
+#pragma unroll
+      for (int q = 0; q < CPT; ++q) {
+        const int idx = q * GP_LOADERS + et;
+        const int i = idx / CHUNKS, r = (idx % CHUNKS) >> 3, c = idx & 7;
+        xr[q] = make_uint4(0, 0, 0, 0);  // rows past T are zeros, as the tensor map's out-of-bounds fill would give
+        if (i < nkb && tok0 + r < T) xr[q] = *reinterpret_cast<const uint4*>(xg + (size_t)r * K + i * GP_BK + c * 8);
+      }
+      // rstd: `per` pieces in index order per thread, the TPN partial sums meet in lane order -- a fixed tree, the same in every CTA
+      float ssum = 0.f;
+#pragma unroll
+      for (int c = 0; c < 16; ++c) ssum += pv[c];  // the zeros behind `per` do not change the sum
+      ssum += __shfl_xor_sync(0xffffffffu, ssum, 1);
+      ssum += __shfl_xor_sync(0xffffffffu, ssum, 2);
+      if (TPN == 8) ssum += __shfl_xor_sync(0xffffffffu, ssum, 4);
+      if (part == 0) s_rstd[j] = jin ? __fdiv_rn(1.0f, __fsqrt_rn(ssum / (float)K + nm.eps)) : 0.f;
+      asm volatile("bar.sync 2, %0;" ::"n"(GP_LOADERS) : "memory");
+#pragma unroll
+      for (int q = 0; q < CPT; ++q) {
+        const int idx = q * GP_LOADERS + et;
+        const int i = idx / CHUNKS, r = (idx % CHUNKS) >> 3, c = idx & 7;
+        if (i < nkb) {
+          const uint4 g4 = *reinterpret_cast<const uint4*>(s_ngain + i * GP_BK + c * 8);
+          const float rs = s_rstd[r];
+          float v[8];
+          unpack8(xr[q], v);
+          const uint32_t* g2 = &g4.x;
+          uint32_t o2[4];
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const uint32_t nx = pack_bf16x2(v[2 * e] * rs, v[2 * e + 1] * rs);  // bf16(h * rstd)
+            const __nv_bfloat162 y = __hmul2(*reinterpret_cast<const __nv_bfloat162*>(&g2[e]), *reinterpret_cast<const __nv_bfloat162*>(&nx));
+            o2[e] = *reinterpret_cast<const uint32_t*>(&y);
+          }
+          *reinterpret_cast<uint4*>(smem_al + i * C::STAGE_BYTES + GP_W_BYTES + r * 128 + ((c ^ (r & 7)) << 4)) = make_uint4(o2[0], o2[1], o2[2], o2[3]);
+        }
+      }
     }
-    asm volatile("cp.async.commit_group;" ::: "memory");
-    asm volatile("cp.async.wait_group 0;" ::: "memory");
     fence_proxy_async();
     mbar_arrive(smem_u32(&full_bar));
   }
@@ -196,7 +269,8 @@ linear_pair_kernel(const __grid_constant__ CUtensorMap tmap_w, const bf16* __res
   float own[C::HALF];
   const int q4 = warp & 3;               // TMEM lane quarter this warp may read (epilogue warps 2..5 -> 2,3,0,1)
   const int row = q4 * 32 + lane;        // accumulator row = weight row of the tile
-  if (warp >= 2) {
+  const bool epi = warp >= 2 && warp < 6;
+  if (epi) {
     mbar_wait(smem_u32(&tmem_full_bar), 0);
     GP_PHASE(0);
     tc_fence_after();
@@ -226,7 +300,7 @@ linear_pair_kernel(const __grid_constant__ CUtensorMap tmap_w, const bf16* __res
 
   GP_PHASE(1);
   const int tok_base = tok0 + (int)rank * C::HALF;  // first token this CTA finishes
-  if (warp >= 2) {
+  if (epi) {
 #pragma unroll
     for (int j = 0; j < C::HALF; ++j) own[j] = bf16_round(own[j] + red[j * GP_BM + row]);  // nn.Linear's single rounding
     // the stage ring is free (every MMA has completed): reuse its first bytes as this CTA's staging area
@@ -274,7 +348,7 @@ linear_pair_kernel(const __grid_constant__ CUtensorMap tmap_w, const bf16* __res
       const bf16* tq = reinterpret_cast<const bf16*>(smem_al);
       const int head = m_tile;
       const bool is_q = head < rp.nq, is_k = !is_q && head < rp.nq + rp.nkv;
-      for (int item = threadIdx.x; item < C::HALF * 16; item += 192) {  // whole warps: HALF * 16 and 192 are multiples of 32
+      for (int item = threadIdx.x; item < C::HALF * 16; item += (int)blockDim.x) {  // whole warps: HALF * 16 and the block size are multiples of 32
         const int j = item >> 4, part = item & 15;
         const int tok = tok_base + j;
         const int d0 = part * 8, p0 = d0 ^ 64;
@@ -352,8 +426,8 @@ linear_pair_kernel(const __grid_constant__ CUtensorMap tmap_w, const bf16* __res
 }
 
 template <int BN, int MODE>
-int launch_pair(const CUtensorMap& tm_w, const bf16* x, bf16* out, int T, int N, int K, int up_row0, const GpRope& rp, int tag,
-                cudaStream_t s) {
+int launch_pair(const CUtensorMap& tm_w, const bf16* x, bf16* out, int T, int N, int K, int up_row0, const GpRope& rp, const GpNorm& nm,
+                int tag, cudaStream_t s) {
   using C = GpCfg<BN>;
   static B2PerDeviceOnce attr_once, carve_once;
   if (attr_once.need())
@@ -363,7 +437,7 @@ int launch_pair(const CUtensorMap& tm_w, const bf16* x, bf16* out, int T, int N,
   const int n_tiles = (T + BN - 1) / BN;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(2 * m_tiles * n_tiles);
-  cfg.blockDim = dim3(192);
+  cfg.blockDim = dim3(nm.ssq != nullptr ? GP_THREADS : 192);
   cfg.dynamicSmemBytes = C::SMEM_BYTES;
   cfg.stream = s;
   cudaLaunchAttribute attr[2];
@@ -375,18 +449,20 @@ int launch_pair(const CUtensorMap& tm_w, const bf16* x, bf16* out, int T, int N,
   attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = b2_pdl_enabled() ? 2 : 1;
-  B2_CUDA_OK(cudaLaunchKernelEx(&cfg, linear_pair_kernel<BN, MODE>, tm_w, x, out, T, N, K, up_row0, m_tiles, rp, tag));
+  B2_CUDA_OK(cudaLaunchKernelEx(&cfg, linear_pair_kernel<BN, MODE>, tm_w, x, out, T, N, K, up_row0, m_tiles, rp, nm, tag));
   return 0;
 }
 
 template <int MODE>
-int launch_pair_bn(const CUtensorMap& tm_w, const bf16* x, bf16* out, int T, int N, int K, int up_row0, const GpRope& rp, int tag,
-                   cudaStream_t s) {
+int launch_pair_bn(const CUtensorMap& tm_w, const bf16* x, bf16* out, int T, int N, int K, int up_row0, const GpRope& rp, const GpNorm& nm,
+                   int tag, cudaStream_t s) {
   // QKV: 32 heads x 2 K-halves are only 64 CTAs, and its tail (norm + RoPE of 128 dims per token) is instruction-bound:
   // two token tiles of 32 give 128 CTAs with 16 tokens each to finish (each weight tile is then read by two pairs; the
-  // second read hits L2).  SwiGLU has 48 tiles x 2 = 96 CTAs already.
-  if (T <= 32 || MODE == GP_QKV_ROPE) return launch_pair<32, MODE>(tm_w, x, out, T, N, K, up_row0, rp, tag, s);
-  return launch_pair<64, MODE>(tm_w, x, out, T, N, K, up_row0, rp, tag, s);
+  // second read hits L2; one 64-token tile measured 1.4 % slower per step even with the 320-thread tail).  SwiGLU has 48 tiles
+  // x 2 = 96 CTAs already.
+  B2_REQUIRE(nm.ssq == nullptr || (nm.gain != nullptr && nm.pieces % 8 == 0 && nm.pieces <= 64 && nm.ld >= T), "pair kernels: bad normalise-on-load arguments");
+  if (T <= 32 || MODE == GP_QKV_ROPE) return launch_pair<32, MODE>(tm_w, x, out, T, N, K, up_row0, rp, nm, tag, s);
+  return launch_pair<64, MODE>(tm_w, x, out, T, N, K, up_row0, rp, nm, tag, s);
 }
 
 }  // namespace
@@ -394,19 +470,22 @@ int launch_pair_bn(const CUtensorMap& tm_w, const bf16* x, bf16* out, int T, int
 bool pair_shapes_ok(int T, int K) { return T >= 1 && T <= 64 && K % (2 * GP_BK) == 0 && K / (2 * GP_BK) <= GP_MAX_KB; }
 
 // gu [T][2I] is never materialised: act [T][I] = SwiGLU(x . Wgu^T).  tm_gu64: Wgu [2I][K] with a 64-row box.
-int launch_gateup_swiglu(const CUtensorMap& tm_gu64, const bf16* x, bf16* act, int T, int I, int K, cudaStream_t s, int tag) {
+int launch_gateup_swiglu(const CUtensorMap& tm_gu64, const bf16* x, bf16* act, int T, int I, int K, cudaStream_t s, int tag,
+                         const PairNorm& norm) {
   B2_REQUIRE(pair_shapes_ok(T, K) && I % 64 == 0, "gateup_swiglu: T=%d K=%d I=%d not built (T <= 64, K <= 1024 in steps of 128)", T, K, I);
   GpRope none = {};
-  return launch_pair_bn<GP_SWIGLU>(tm_gu64, x, act, T, 2 * I, K, I, none, tag, s);
+  const GpNorm nm = {norm.ssq, norm.gain, norm.pieces, norm.ld, norm.eps, norm.next_w};
+  return launch_pair_bn<GP_SWIGLU>(tm_gu64, x, act, T, 2 * I, K, I, none, nm, tag, s);
 }
 
 // tm_qkv: Wqkv [(nq + 2 nkv) * 128][K] with a 128-row box (one head per tile).
 int launch_qkv_rope(const CUtensorMap& tm_qkv, const bf16* x, const bf16* qw, const bf16* kw, const bf16* cos_sin, const int32_t* positions,
                     const int32_t* slots, bf16* q_out, bf16* k_pages, bf16* v_pages, int T, int nq, int nkv, int K, int block_size,
-                    float eps, cudaStream_t s, int tag) {
+                    float eps, cudaStream_t s, int tag, const PairNorm& norm) {
   B2_REQUIRE(pair_shapes_ok(T, K) && qw != nullptr && kw != nullptr, "qkv_rope: T=%d K=%d not built, or no QK-norm gains", T, K);
   GpRope rp = {qw, kw, cos_sin, positions, slots, q_out, k_pages, v_pages, nq, nkv, block_size, eps};
-  return launch_pair_bn<GP_QKV_ROPE>(tm_qkv, x, nullptr, T, (nq + 2 * nkv) * 128, K, 0, rp, tag, s);
+  const GpNorm nm = {norm.ssq, norm.gain, norm.pieces, norm.ld, norm.eps, norm.next_w};
+  return launch_pair_bn<GP_QKV_ROPE>(tm_qkv, x, nullptr, T, (nq + 2 * nkv) * 128, K, 0, rp, nm, tag, s);
 }
 
 }  // namespace b2

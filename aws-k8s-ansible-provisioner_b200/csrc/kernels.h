@@ -97,10 +97,26 @@ bool pair_shapes_ok(int T, int K);
 // gemm_gateup.cu: the prefill-sized counterpart (two accumulators per tile, SwiGLU in the epilogue)
 bool gateup_prefill_shapes_ok(int T, int I, int K);
 int launch_gateup_swiglu_prefill(const CUtensorMap& tm_w, const CUtensorMap& tm_x128, bf16* act, int T, int I, int K, int x_row0, cudaStream_t s);
-int launch_gateup_swiglu(const CUtensorMap& tm_gu64, const bf16* x, bf16* act, int T, int I, int K, cudaStream_t s, int tag = 0);
+// Normalise-on-load (see gemm_pair.cu): x is the residual stream, ssq [pieces][ld] the per-16-feature sums of squares of
+// its rows (gemm_resid.cu writes them), gain the RMSNorm weight.  Default: x is used as given.
+struct PairNorm {
+  const float* ssq = nullptr;
+  const bf16* gain = nullptr;
+  int pieces = 0, ld = 0;
+  float eps = 0.f;
+  L2Prefetch next_w;  // optional: the next projection's weights, prefetched into L2 by this launch's idle lanes
+};
+int launch_gateup_swiglu(const CUtensorMap& tm_gu64, const bf16* x, bf16* act, int T, int I, int K, cudaStream_t s, int tag = 0,
+                         const PairNorm& norm = PairNorm());
+// gemm_resid.cu: h += x . W^T for the residual stream (O / down projection), split-K summed inside a cluster of 8;
+// also writes the pieces of the next RMSNorm's statistic
+bool resid_shapes_ok(int T, int N, int K);
+int launch_linear_resid(const CUtensorMap& tm_w, const bf16* x, bf16* h, float* ssq, int T, int N, int K, int ssq_ld, cudaStream_t s, int tag = 0,
+                        const L2Prefetch& next_w = L2Prefetch());
+int step_trace_set_resid(unsigned long long* buf);
 int launch_qkv_rope(const CUtensorMap& tm_qkv, const bf16* x, const bf16* qw, const bf16* kw, const bf16* cos_sin, const int32_t* positions,
                     const int32_t* slots, bf16* q_out, bf16* k_pages, bf16* v_pages, int T, int nq, int nkv, int K, int block_size,
-                    float eps, cudaStream_t s, int tag = 0);
+                    float eps, cudaStream_t s, int tag = 0, const PairNorm& norm = PairNorm());
 int step_trace_set_pair(unsigned long long* dev_buf);
 
 // ---- chain.cu ----

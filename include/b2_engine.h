@@ -221,6 +221,21 @@ int b2k_qkv_rope(const void* x_bf16, const void* w_qkv_bf16, const void* qnorm_w
                  const int32_t* positions, const int32_t* slots, void* q_out, void* k_pages, void* v_pages, int T, int nq,
                  int nkv, int K, int block_size, float eps, void* stream);
 
+/* The decode step's norm-free layer chain (round 2): the two projections that feed the residual stream update it
+ * themselves, and the two projections that read it normalise it as they load it, so that no RMSNorm kernel runs between
+ * them (HF:models/qwen3/modeling_qwen3.py:339-351 for the adds, :50-62 for the norm).
+ * b2k_linear_resid: h[T][N] (bf16, in place) = bf16(h + bf16(x[T][K] . W[N][K]^T)), T <= 64, N % 128 == 0, K % 512 == 0,
+ *   K <= 3072; ssq[N/16][ssq_ld] (fp32) receives per token column the sum of squares of each 16-feature piece of the new h.
+ * b2k_gateup_swiglu_norm / b2k_qkv_rope_norm: b2k_gateup_swiglu / b2k_qkv_rope with x = bf16(norm_w * bf16(h * rstd)) formed
+ *   on the fly, rstd = rsqrt(sum of the `pieces` pieces of ssq / K + eps). */
+int b2k_linear_resid(const void* x_bf16, const void* w_bf16, void* h_bf16, float* ssq, int T, int N, int K, int ssq_ld, void* stream);
+int b2k_gateup_swiglu_norm(const void* h_bf16, const void* w_gu_bf16, const void* norm_w, const float* ssq, int pieces, int ssq_ld,
+                           float eps, void* act_bf16, int T, int I, int K, void* stream);
+int b2k_qkv_rope_norm(const void* h_bf16, const void* w_qkv_bf16, const void* norm_w, const float* ssq, int pieces, int ssq_ld,
+                      float norm_eps, const void* qnorm_w, const void* knorm_w, const void* cos_sin, const int32_t* positions,
+                      const int32_t* slots, void* q_out, void* k_pages, void* v_pages, int T, int nq, int nkv, int K, int block_size,
+                      float eps, void* stream);
+
 /* Diagnostics (tools/step_timeline.py): register a device buffer of uint64 in which thread 0 of every CTA of every
  * kernel on the decode path appends one 4-word record {class | blockIdx << 8 | smid << 32 | aux << 40, CTA start,
  * dependency wait returned, CTA end} in %globaltimer ns.  The caller sets buf[0] = 0 (record counter) and

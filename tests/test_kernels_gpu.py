@@ -246,6 +246,114 @@ def test_gateup_swiglu_fused(lib, T):
     assert_bf16_close(act, a2, 2, 0.02, "fused vs separate kernels", abs_floor=2e-3)
 
 
+def _ssq_pieces(h, ld=64):
+    """[H/16][ld] fp32: per token column the sum of squares of each 16-feature piece of h's rows (what gemm_resid.cu writes)."""
+    T, H = h.shape
+    out = torch.zeros(H // 16, ld)
+    out[:, :T] = (h.float() ** 2).view(T, H // 16, 16).sum(-1).t()
+    return out
+
+
+@pytest.mark.parametrize("T", [64, 40, 32, 5])
+@pytest.mark.parametrize("K", [2048, 3072])
+def test_linear_resid(lib, T, K):
+    """gemm_resid.cu: O / down projection that adds into the residual stream itself (split-K summed across a cluster of
+    8 through distributed shared memory).  The residual stream must be BIT-identical to the path it replaces (b2k_linear
+    with 8 fp32 partials, then b2k_add_rmsnorm's sum in split order + add); the sum-of-squares pieces must be those of
+    the new rows."""
+    N = 1024
+    x = bf(T, K, seed=41)
+    w = bf(N, K, scale=0.03, seed=42)
+    h0 = bf(T + 2, N, seed=43)
+    gain = torch.ones(N, dtype=torch.bfloat16)
+    dx, dw = dv(x), dv(w)
+    h_new = h0.cuda()
+    ssq = torch.full((N // 16, 64), float("nan"), device="cuda")
+    chk(lib, lib.b2k_linear_resid(ptr(dx), ptr(dw), ptr(h_new), ptr(ssq), T, N, K, 64, cuda_stream_ptr()))
+    parts = torch.empty(8, T, N, device="cuda")
+    chk(lib, lib.b2k_linear(ptr(dx), ptr(dw), ptr(parts), 1, 8, T, N, K, 1, cuda_stream_ptr()))
+    h_ref = h0.cuda()
+    xn = torch.empty(T, N, dtype=torch.bfloat16, device="cuda")
+    chk(lib, lib.b2k_add_rmsnorm(ptr(h_ref), ptr(parts), 1, 8, ptr(dv(gain)), ptr(xn), T, N, 1e-6, cuda_stream_ptr()))
+    assert torch.equal(h_new[:T].cpu(), h_ref[:T].cpu()), "residual stream differs from the partials + add_rmsnorm path"
+    assert torch.equal(h_new[T:].cpu(), h0[T:]), "rows past T were touched"
+    want = _ssq_pieces(h_new[:T].cpu())
+    got = ssq.cpu()
+    assert torch.allclose(got[:, :T], want[:, :T], rtol=1e-5, atol=1e-6)
+    assert torch.isnan(got[:, T:]).all(), "wrote statistics for tokens past T"
+    # bit-identical run to run
+    h2 = h0.cuda()
+    ssq2 = torch.empty_like(ssq)
+    chk(lib, lib.b2k_linear_resid(ptr(dx), ptr(dw), ptr(h2), ptr(ssq2), T, N, K, 64, cuda_stream_ptr()))
+    assert torch.equal(h2.cpu(), h_new.cpu()) and torch.equal(ssq2[:, :T].cpu(), got[:, :T])
+
+
+@pytest.mark.parametrize("T", [64, 33, 32, 5])
+def test_gateup_swiglu_normalise_on_load(lib, T):
+    """gemm_pair.cu with PairNorm: the projection reads the residual stream and applies the RMSNorm while staging its
+    token rows.  Against b2k_add_rmsnorm followed by b2k_gateup_swiglu: the statistic is summed in another order, so rstd
+    may differ in its last bit and an element of x by one bf16 ulp now and then."""
+    I, K = 3072, 1024
+    h = bf(T, K, seed=51)
+    w = bf(2 * I, K, scale=0.05, seed=52)
+    gain = (1 + 0.25 * torch.randn(K, generator=torch.Generator().manual_seed(53))).to(torch.bfloat16)
+    dh, dw, dg = dv(h), dv(w), dv(gain)
+    ssq = dv(_ssq_pieces(h))
+    act = torch.full((T, I), float("nan"), dtype=torch.bfloat16, device="cuda")
+    chk(lib, lib.b2k_gateup_swiglu_norm(ptr(dh), ptr(dw), ptr(dg), ptr(ssq), K // 16, 64, 1e-6, ptr(act), T, I, K, cuda_stream_ptr()))
+    assert torch.equal(dh.cpu(), h), "the residual stream is an input only"
+    hh = h.cuda()
+    xn = torch.empty(T, K, dtype=torch.bfloat16, device="cuda")
+    chk(lib, lib.b2k_add_rmsnorm(ptr(hh), None, 0, 0, ptr(dg), ptr(xn), T, K, 1e-6, cuda_stream_ptr()))
+    a2 = torch.empty(T, I, dtype=torch.bfloat16, device="cuda")
+    chk(lib, lib.b2k_gateup_swiglu(ptr(xn), ptr(dw), ptr(a2), T, I, K, cuda_stream_ptr()))
+    assert_bf16_close(act, a2, 2, 0.02, "normalise-on-load vs norm kernel + projection, T=%d" % T, abs_floor=2e-3)
+    gu = (rms_norm(h, gain, 1e-6).float() @ w.float().t()).to(torch.bfloat16)
+    ref = torch.nn.functional.silu(gu[:, :I]) * gu[:, I:]
+    assert_bf16_close(act, ref, 2, 0.05, "normalise-on-load vs torch, T=%d" % T, abs_floor=2e-3)
+
+
+@pytest.mark.parametrize("T", [64, 40, 17, 1])
+def test_qkv_rope_normalise_on_load(lib, T):
+    """The QKV + QK-norm + RoPE + page-write launch with the input RMSNorm applied on load, against b2k_add_rmsnorm
+    followed by b2k_qkv_rope."""
+    a = QWEN3_0_6B
+    nq, nkv, hd, bs, K = a.num_q_heads, a.num_kv_heads, a.head_dim, 16, a.hidden
+    N = (nq + 2 * nkv) * hd
+    nblocks = (T + bs - 1) // bs + 3
+    g = torch.Generator().manual_seed(61)
+    h = bf(T, K, seed=62)
+    w = bf(N, K, scale=0.05, seed=63)
+    gain = (1 + 0.25 * torch.randn(K, generator=g)).to(torch.bfloat16)
+    qw = (1 + 0.25 * torch.randn(hd, generator=g)).to(torch.bfloat16)
+    kw = (1 + 0.25 * torch.randn(hd, generator=g)).to(torch.bfloat16)
+    positions = torch.randint(0, 4000, (T,), generator=g, dtype=torch.int32)
+    slots = torch.randperm(nblocks * bs, generator=g)[:T].to(torch.int32)
+    cos, sin = rope_cos_sin(a, torch.arange(4096)[None, :])
+    table = torch.cat([cos[0, :, :64], sin[0, :, :64]], dim=-1).contiguous()
+    dh, dw, dg, dqw, dkw, dtab, dpos, dsl = dv(h), dv(w), dv(gain), dv(qw), dv(kw), dv(table), dv(positions), dv(slots)
+    ssq = dv(_ssq_pieces(h))
+    outs = []
+    for fused in (True, False):
+        kp = torch.zeros(nblocks, nkv, bs, hd, dtype=torch.bfloat16, device="cuda")
+        vp = torch.zeros_like(kp)
+        q_out = torch.zeros(T, nq * hd, dtype=torch.bfloat16, device="cuda")
+        if fused:
+            chk(lib, lib.b2k_qkv_rope_norm(ptr(dh), ptr(dw), ptr(dg), ptr(ssq), K // 16, 64, 1e-6, ptr(dqw), ptr(dkw), ptr(dtab), ptr(dpos),
+                                          ptr(dsl), ptr(q_out), ptr(kp), ptr(vp), T, nq, nkv, K, bs, 1e-6, cuda_stream_ptr()))
+        else:
+            hh = h.cuda()
+            xn = torch.empty(T, K, dtype=torch.bfloat16, device="cuda")
+            chk(lib, lib.b2k_add_rmsnorm(ptr(hh), None, 0, 0, ptr(dg), ptr(xn), T, K, 1e-6, cuda_stream_ptr()))
+            chk(lib, lib.b2k_qkv_rope(ptr(xn), ptr(dw), ptr(dqw), ptr(dkw), ptr(dtab), ptr(dpos), ptr(dsl), ptr(q_out), ptr(kp), ptr(vp), T,
+                                     nq, nkv, K, bs, 1e-6, cuda_stream_ptr()))
+        outs.append((q_out.cpu(), kv_swizzle(kp.cpu()), kv_swizzle(vp.cpu())))
+    (qf, kf, vf), (qs, ks, vs) = outs
+    assert_bf16_close(qf, qs, 2, 0.02, "q: normalise-on-load vs norm kernel", abs_floor=0.02)
+    assert_bf16_close(kf, ks, 2, 0.02, "k pages: normalise-on-load vs norm kernel", abs_floor=0.02)
+    assert_bf16_close(vf, vs, 1, 0.02, "v pages: normalise-on-load vs norm kernel", abs_floor=2e-3)
+
+
 @pytest.mark.parametrize("T,I,K", [(256, 3072, 1024), (1000, 3072, 1024), (4099, 3072, 1024), (300, 8192, 3072), (277, 512, 256)])
 def test_gateup_swiglu_prefill_fused(lib, T, I, K):
     """gemm_gateup.cu: the prefill-sized gate/up projection with SwiGLU in its epilogue (two TMEM accumulators per tile).
