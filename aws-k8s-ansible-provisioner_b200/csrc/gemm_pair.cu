@@ -297,6 +297,12 @@ linear_pair_kernel(const __grid_constant__ CUtensorMap tmap_w, const bf16* __res
   __syncwarp();
   asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
   asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+  // every epilogue warp finished its tcgen05.ld before it arrived: TMEM goes back now, not at the end of the tail (the CTA
+  // then exits as soon as its last store is out; the next kernel's dependency wait returns on the LAST CTA's exit)
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_d, C::TMEM_COLS);
+  }
 
   GP_PHASE(1);
   const int tok_base = tok0 + (int)rank * C::HALF;  // first token this CTA finishes
@@ -404,9 +410,8 @@ linear_pair_kernel(const __grid_constant__ CUtensorMap tmap_w, const bf16* __res
     }
   }
   GP_PHASE(2);
-  tc_fence_before();
-  __syncthreads();
 #ifdef B2_STEP_TRACE
+  __syncthreads();  // the end stamp is the CTA's last thread's
   if (threadIdx.x == 0 && _stamp[0] != 0ull) {
     unsigned long long* buf = (unsigned long long*)_stamp[0];
     const unsigned long long slot = atomicAdd(buf, 1ull);
@@ -419,10 +424,6 @@ linear_pair_kernel(const __grid_constant__ CUtensorMap tmap_w, const bf16* __res
   }
 #endif
   B2_STAMP_END_AUX(100, ((unsigned)(N >> 6) & 0xfffu) | (((unsigned)(K >> 6) & 0x7ffu) << 12) | (tag ? (1u << 23) : 0u));
-  if (warp == 1) {
-    tc_fence_after();
-    tmem_dealloc(tmem_d, C::TMEM_COLS);
-  }
 }
 
 template <int BN, int MODE>

@@ -178,6 +178,10 @@ linear_resid_kernel(const __grid_constant__ CUtensorMap tmap_w, const bf16* __re
   __syncwarp();
   asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
   asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+  if (warp == 1) {  // every tcgen05.ld of this CTA is behind the barrier: TMEM goes back before the finishing pass
+    tc_fence_after();
+    tmem_dealloc(tmem_d, C::TMEM_COLS);
+  }
 
   if (warp >= 2) {
     float acc[RPT];
@@ -206,13 +210,10 @@ linear_resid_kernel(const __grid_constant__ CUtensorMap tmap_w, const bf16* __re
       if ((et % TPT) == 0) ssq[(size_t)(n0 / GR_ROWS) * ssq_ld + ft] = ss;
     }
   }
-  tc_fence_before();
-  __syncthreads();
+#ifdef B2_STEP_TRACE
+  __syncthreads();  // the end stamp is the CTA's last thread's
+#endif
   B2_STAMP_END_AUX(100, ((unsigned)(N >> 6) & 0xfffu) | (((unsigned)(K >> 6) & 0x7ffu) << 12) | (tag ? (1u << 23) : 0u));
-  if (warp == 1) {
-    tc_fence_after();
-    tmem_dealloc(tmem_d, C::TMEM_COLS);
-  }
 }
 
 template <int BN>

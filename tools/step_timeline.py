@@ -150,6 +150,24 @@ def main():
         a = np.median(np.array(rows), axis=0)
         print("\nattention launches (median over %d launches; us from the launch's first CTA start): CTA start p50 %.2f max %.2f | wait returned %.2f | "
               "CTA end p10 %.2f p50 %.2f p90 %.2f max %.2f | CTA busy after wait p50 %.2f | corr(start, end) %.2f" % ((len(rows),) + tuple(a)))
+        # is the tail made of the SAME CTAs every launch (block index -> SM placement is stable for a one-CTA-per-SM grid)?
+        ncta = max(len(g) for g in att_idx)
+        M = []
+        for grp in att_idx:
+            grp = np.array(grp)
+            if len(grp) != ncta:
+                continue
+            v = np.full(ncta, np.nan)
+            e = (t1[grp] - np.maximum(t0[grp], tw[grp])) / 1e3
+            v[bid[grp] % ncta] = e - np.median(e)
+            M.append(v)
+        M = np.array(M)
+        if len(M) >= 4 and not np.isnan(M).any():
+            mu = M.mean(axis=0)
+            print("attention CTA run time minus the launch's median, by block index over %d launches: std of the per-block means %.2f us, "
+                  "mean within-block std %.2f us (total std %.2f); the 8 slowest blocks %s are late by %s us on average" % (
+                      len(M), mu.std(), M.std(axis=0).mean(), M.std(), np.argsort(mu)[-8:][::-1].tolist(),
+                      np.round(np.sort(mu)[-8:][::-1], 2).tolist()))
     # ---- per-lane chains: hand-off and work ----
     summary = {}
     for lane in sorted(set(r["lane"] for r in L)):
