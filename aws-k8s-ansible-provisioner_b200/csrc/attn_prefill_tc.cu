@@ -59,7 +59,17 @@ __device__ __forceinline__ float pt_ex2(float x) {  // 2^x, one MUFU (results be
 constexpr uint32_t PT_IDESC_QK = umma_idesc_bf16(PT_M, PT_BN);                // both operands K-major
 constexpr uint32_t PT_IDESC_PV = umma_idesc_bf16(PT_M, PT_HD) | (1u << 16);  // B (V) MN-major
 
-__global__ void __launch_bounds__(288, 2)
+// Threads: warps 0-7 softmax (two threads per row), warp 8 the MMA issuer (and TMEM allocator), warps 9-12 one lane each
+// issuing the TMA loads of a key tile (K pages 0-3 | K pages 4-7 | V pages 0-3 | V pages 4-7).
+// Measured with clock64 on the first version of this kernel (one control thread did the MMAs AND all 32 TMA loads of a
+// tile, O lived in registers): per key tile the control thread spent ~3 000 cycles just issuing the loads (~100 per
+// cp.async.bulk.tensor, serial, in front of the next S = Q.K^T), the softmax threads ~3 000 in the probability pass and
+// ~2 200 in the O read-back (both slowed by register spills at the 96-register cap), against ~550 per MMA group.  Hence:
+// four loader warps, and O stays in TMEM.
+constexpr int PT_THREADS = 13 * 32;
+constexpr float PT_RESCALE = 8.0f;  // log2 units: the reference maximum is raised only when the row maximum grew by 2^8
+
+__global__ void __launch_bounds__(PT_THREADS, 2)
 attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_constant__ CUtensorMap tmap_v, const bf16* __restrict__ q,
                        const int32_t* __restrict__ block_table, int bt_stride, const PrefillTile* __restrict__ tiles,
                        bf16* __restrict__ out, int nq, int nkv, float scale_log2, int window) {
@@ -72,7 +82,9 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_
   uint8_t* sm = smem_raw + (base - smem_u32(smem_raw));
   const uint32_t q_s = base, k_s = base + PT_TILE_BYTES, v_s = base + 2 * PT_TILE_BYTES, p_s = k_s;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const PrefillTile tile = tiles[blockIdx.x];
+  // Blocks are dispatched in index order and a tile late in its sequence has the most key tiles: walking the tile list
+  // backwards starts the long CTAs first and leaves the short ones for the kernel's last wave.
+  const PrefillTile tile = tiles[gridDim.x - 1 - blockIdx.x];
   const int kvh = blockIdx.y;
   const int kv_len = tile.q_pos0 + tile.nrows;
   const int n_kt = (kv_len + PT_BN - 1) / PT_BN;
@@ -91,8 +103,8 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_
     tmem_alloc(smem_u32(&tmem_slot), PT_TMEM_COLS);
     tmem_relinquish();
   }
-  // this sequence's block-table row (written by the host before the forward started) into shared memory: the control
-  // thread would otherwise chain a global load in front of every TMA issue
+  // this sequence's block-table row (written by the host before the forward started) into shared memory: the loader
+  // threads would otherwise chain a global load in front of every TMA issue
   for (int i = threadIdx.x; i < n_kt * (PT_BN / 16) && i < PT_MAX_PAGES; i += blockDim.x) s_bt[i] = i < bt_stride ? bt[i] : 0;
   tc_fence_before();
   __syncthreads();
@@ -101,21 +113,30 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_
   pdl_wait();  // q and the newest K/V rows come from the kernel before this one
   if (threadIdx.x == 0) pdl_launch_dependents();
 
-  auto load_tile = [&](int kt, uint32_t dst, const CUtensorMap* tm, uint32_t fb) {  // the 8 pages of key tile kt, both halves
-    mbar_arrive_expect_tx(fb, PT_TILE_BYTES);
-    for (int pg = 0; pg < PT_BN / 16; ++pg) {
-      const int row0 = (s_bt[kt * (PT_BN / 16) + pg] * nkv + kvh) * 16;  // pages past the sequence are the null page 0
-      tma_load_2d(dst + pg * 16 * 128, tm, 0, row0, fb);
-      tma_load_2d(dst + PT_HALF_BYTES + pg * 16 * 128, tm, 64, row0, fb);
-    }
-  };
-
-  if (warp == 8) {
+  if (warp >= 9) {
+    // ---- loaders: warp 9 | 10 the K pages 0-3 | 4-7 of a key tile, warp 11 | 12 the V pages; both 64-dim halves each ----
     if (lane == 0) {
-      tma_prefetch_desc(&tmap_k);
-      tma_prefetch_desc(&tmap_v);
-      load_tile(kt0, k_s, &tmap_k, smem_u32(&k_full));
-      load_tile(kt0, v_s, &tmap_v, smem_u32(&v_full));
+      const int j = warp - 9;
+      const bool is_v = j >= 2;
+      const CUtensorMap* tm = is_v ? &tmap_v : &tmap_k;
+      const uint32_t fb = smem_u32(is_v ? &v_full : &k_full);
+      const uint32_t dst = (is_v ? v_s : k_s) + (uint32_t)((j & 1) * 4 * 16 * 128);
+      tma_prefetch_desc(tm);
+      int it = 0;
+      for (int kt = kt0; kt < n_kt; ++kt, ++it) {
+        // P (in K's place) and V of the previous tile are read by its P.V MMAs: pages may land once those have completed
+        if (it > 0) mbar_wait(smem_u32(&o_full), (it - 1) & 1);
+        if ((j & 1) == 0) mbar_arrive_expect_tx(fb, PT_TILE_BYTES);  // the other warp of the pair only adds bytes
+#pragma unroll
+        for (int pg = 0; pg < 4; ++pg) {
+          const int row0 = (s_bt[kt * (PT_BN / 16) + (j & 1) * 4 + pg] * nkv + kvh) * 16;  // pages past the sequence are the null page 0
+          tma_load_2d(dst + pg * 16 * 128, tm, 0, row0, fb);
+          tma_load_2d(dst + PT_HALF_BYTES + pg * 16 * 128, tm, 64, row0, fb);
+        }
+      }
+    }
+  } else if (warp == 8) {
+    if (lane == 0) {
       mbar_wait(smem_u32(&p_full), 0);  // phase 0 of p_full: the softmax threads have staged Q
       int it = 0;
       for (int kt = kt0; kt < n_kt; ++kt, ++it) {
@@ -129,7 +150,8 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_
           for (int k = 0; k < 4; ++k) tc_mma_bf16(tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), PT_IDESC_QK, (kb | k) ? 1u : 0u);
         }
         tc_commit(smem_u32(&s_full));
-        // PV = P . V : K = 128 keys = 2 k-blocks (of P, which now lies where K was) x 4 MMAs of 16 keys
+        // O (+)= P . V : K = 128 keys = 2 k-blocks (of P, which now lies where K was) x 4 MMAs of 16 keys.  O stays in TMEM
+        // across key tiles; the softmax threads rescale it in place when a row's reference maximum moves.
         mbar_wait(smem_u32(&p_full), (it + 1) & 1);
         mbar_wait(smem_u32(&v_full), it & 1);
         tc_fence_after();
@@ -139,16 +161,10 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_
 #pragma unroll
           for (int k = 0; k < 4; ++k) {
             const uint64_t db = pt_desc_mn(v_s + (uint32_t)((kb * 64 + k * 16) * 128));
-            tc_mma_bf16(tmem + 128u, da + (uint64_t)(2 * k), db, PT_IDESC_PV, (kb | k) ? 1u : 0u);
+            tc_mma_bf16(tmem + 128u, da + (uint64_t)(2 * k), db, PT_IDESC_PV, (it > 0 || (kb | k)) ? 1u : 0u);
           }
         }
         tc_commit(smem_u32(&o_full));
-        // P (in K's place) and V are read by those MMAs: the next tile's pages may land only once they have completed
-        mbar_wait(smem_u32(&o_full), it & 1);
-        if (kt + 1 < n_kt) {
-          load_tile(kt + 1, k_s, &tmap_k, smem_u32(&k_full));
-          load_tile(kt + 1, v_s, &tmap_v, smem_u32(&v_full));
-        }
       }
     }
   } else {
@@ -176,11 +192,12 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_
     mbar_arrive(smem_u32(&p_full));  // phase 0 of p_full = "Q is staged"
 
     constexpr int HALF = PT_BN / 2;  // keys per thread and tile == output dims per thread
-    float o[HALF];
-#pragma unroll
-    for (int i = 0; i < HALF; ++i) o[i] = 0.f;
-    float m_run = -INFINITY, l_run = 0.f;  // l_run: the sum over THIS thread's keys only
+    // m_ref: the value the probabilities of this row are scaled by, 2^(s - m_ref).  It follows the running row maximum
+    // lazily -- only when the maximum has grown by more than PT_RESCALE -- so that most key tiles leave O (in TMEM)
+    // untouched; probabilities then reach 2^8 at most, and l and O carry the same factor, which cancels in O / l.
+    float m_ref = -INFINITY, l_run = 0.f;  // l_run: the sum over THIS thread's keys only
     const uint32_t trow = tmem + ((uint32_t)((warp & 3) * 32) << 16);
+    const uint32_t orow = trow + 128u + (uint32_t)(kh * HALF);  // this thread's 64 output dims
     uint8_t* prow = sm + PT_TILE_BYTES + kh * PT_HALF_BYTES + r * 128;  // P goes where K was (the S product has consumed K)
     const int pair_bar = 1 + (warp & 3);  // named barrier of the two warps that share a lane quarter
     int it = 0;
@@ -198,19 +215,19 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_
       // pass 1: the row maximum (the scale is positive: max(s * c) = c * max(s)); four chains instead of one
       float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll 1
-      for (int c0 = kh * HALF; c0 < kh * HALF + HALF; c0 += 32) {
-        uint32_t sr[32];
-        tmem_ld32(trow + (uint32_t)c0, sr);
+      for (int c0 = kh * HALF; c0 < kh * HALF + HALF; c0 += 16) {
+        uint32_t sr[16];
+        tmem_ld16(trow + (uint32_t)c0, sr);
         tmem_ld_wait();
         if (full_tile) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j) m4[j & 3] = fmaxf(m4[j & 3], __uint_as_float(sr[j]));
+          for (int j = 0; j < 16; ++j) m4[j & 3] = fmaxf(m4[j & 3], __uint_as_float(sr[j]));
         } else {
           const int jlo = lo_col - (key0 + c0);
           const unsigned span = (unsigned)(hi_col - lo_col);  // hi < lo (nothing valid) wraps to a huge span: guard below
           const bool any = hi_col >= lo_col;
 #pragma unroll
-          for (int j = 0; j < 32; ++j) {
+          for (int j = 0; j < 16; ++j) {
             const bool ok = any && (unsigned)(j - jlo) <= span;
             m4[j & 3] = fmaxf(m4[j & 3], ok ? __uint_as_float(sr[j]) : -INFINITY);
           }
@@ -219,22 +236,38 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_
       const float mx_own = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
       s_mx[kh][r] = mx_own;
       asm volatile("bar.sync %0, 64;" ::"r"(pair_bar) : "memory");
-      const float mx = fmaxf(mx_own, s_mx[kh ^ 1][r]) * scale_log2;
-      const float m_new = fmaxf(m_run, mx);
-      const float msub = (m_new == -INFINITY) ? 0.f : m_new;
-      const float corr = exp2f(m_run - msub);
-      m_run = m_new;
+      const float mx = fmaxf(mx_own, s_mx[kh ^ 1][r]) * scale_log2;  // the same value in both threads of the row
+      // raise the reference?  (first tile: O does not exist yet, the first P.V overwrites it)
+      const bool raise = mx > m_ref + PT_RESCALE || (m_ref == -INFINITY && mx > -INFINITY);
+      if (it > 0 && __any_sync(0xffffffffu, raise)) {
+        const float corr = raise ? exp2f(m_ref - mx) : 1.0f;  // m_ref == -inf: 0 (O and l of such a row are zeros so far)
+        mbar_wait(smem_u32(&o_full), (it - 1) & 1);  // the previous tile's P.V has landed in O
+        tc_fence_after();
+#pragma unroll 1
+        for (int c0 = 0; c0 < HALF; c0 += 16) {
+          uint32_t ov[16];
+          tmem_ld16(orow + (uint32_t)c0, ov);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 16; ++j) ov[j] = __float_as_uint(__uint_as_float(ov[j]) * corr);
+          tmem_st16(orow + (uint32_t)c0, ov);
+        }
+        tmem_st_wait();
+        l_run *= corr;
+      }
+      if (raise) m_ref = mx;
+      const float msub = (m_ref == -INFINITY) ? 0.f : m_ref;
       // pass 2: probabilities, their fp32 sum, and P as bf16 into the A-operand tile of the PV product
       float l4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll 1
-      for (int c0 = kh * HALF; c0 < kh * HALF + HALF; c0 += 32) {
-        uint32_t sr[32];
-        tmem_ld32(trow + (uint32_t)c0, sr);
+      for (int c0 = kh * HALF; c0 < kh * HALF + HALF; c0 += 16) {  // 16 columns at a time: the kernel lives in 72 registers
+        uint32_t sr[16];
+        tmem_ld16(trow + (uint32_t)c0, sr);
         tmem_ld_wait();
-        float p[32];
+        float p[16];
         if (full_tile) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j) {
+          for (int j = 0; j < 16; ++j) {
             p[j] = pt_ex2(__uint_as_float(sr[j]) * scale_log2 - msub);
             l4[j & 3] += p[j];
           }
@@ -243,47 +276,44 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_
           const unsigned span = (unsigned)(hi_col - lo_col);
           const bool any = hi_col >= lo_col;
 #pragma unroll
-          for (int j = 0; j < 32; ++j) {
+          for (int j = 0; j < 16; ++j) {
             const bool ok = any && (unsigned)(j - jlo) <= span;
             p[j] = ok ? pt_ex2(__uint_as_float(sr[j]) * scale_log2 - msub) : 0.f;
             l4[j & 3] += p[j];
           }
         }
 #pragma unroll
-        for (int c8 = 0; c8 < 4; ++c8) {  // four 16-byte chunks of 8 keys
+        for (int c8 = 0; c8 < 2; ++c8) {  // two 16-byte chunks of 8 keys
           const int chunk = ((c0 >> 3) & 7) + c8;  // 0..7 within this thread's 64-key half of the row
           *reinterpret_cast<uint4*>(prow + ((chunk ^ (r & 7)) << 4)) = pack8(p + c8 * 8);
         }
       }
-      l_run = l_run * corr + ((l4[0] + l4[1]) + (l4[2] + l4[3]));
+      l_run += (l4[0] + l4[1]) + (l4[2] + l4[3]);
       tc_fence_before();
       fence_proxy_async();
       mbar_arrive(smem_u32(&p_full));
-      // O = O * corr + P.V
-      mbar_wait(smem_u32(&o_full), it & 1);
-      tc_fence_after();
-#pragma unroll
-      for (int c0 = 0; c0 < HALF; c0 += 32) {
-        uint32_t pv[32];
-        tmem_ld32(trow + 128u + (uint32_t)(kh * HALF + c0), pv);
-        tmem_ld_wait();
-#pragma unroll
-        for (int j = 0; j < 32; ++j) o[c0 + j] = fmaf(o[c0 + j], corr, __uint_as_float(pv[j]));
-      }
-      tc_fence_before();
     }
+    // ---- O / l, once ----
     s_mx[kh][r] = l_run;  // the pair's last barrier of the loop is behind both threads' reads of s_mx
     asm volatile("bar.sync %0, 64;" ::"r"(pair_bar) : "memory");
     const float l_row = s_mx[0][r] + s_mx[1][r];
-    if (row_ok) {
-      const float inv = l_row > 0.f ? __fdiv_rn(1.0f, l_row) : 0.f;
-      bf16* dst = out + ((size_t)(tile.q_row0 + t) * nq + kvh * 2 + h) * PT_HD + kh * HALF;
+    const float inv = l_row > 0.f ? __fdiv_rn(1.0f, l_row) : 0.f;
+    mbar_wait(smem_u32(&o_full), (it - 1) & 1);
+    tc_fence_after();
+    bf16* dst = out + ((size_t)(tile.q_row0 + t) * nq + kvh * 2 + h) * PT_HD + kh * HALF;
+#pragma unroll 1
+    for (int c0 = 0; c0 < HALF; c0 += 16) {
+      uint32_t ov[16];
+      tmem_ld16(orow + (uint32_t)c0, ov);
+      tmem_ld_wait();
+      if (row_ok) {
 #pragma unroll
-      for (int c = 0; c < HALF / 8; ++c) {
-        float v[8];
+        for (int c = 0; c < 2; ++c) {
+          float v[8];
 #pragma unroll
-        for (int e = 0; e < 8; ++e) v[e] = o[c * 8 + e] * inv;
-        reinterpret_cast<uint4*>(dst)[c] = pack8(v);
+          for (int e = 0; e < 8; ++e) v[e] = __uint_as_float(ov[c * 8 + e]) * inv;
+          reinterpret_cast<uint4*>(dst + c0)[c] = pack8(v);
+        }
       }
     }
   }
@@ -315,7 +345,7 @@ int launch_attn_prefill_tc(const bf16* q, const bf16* k_pages, const bf16* v_pag
   if (attr_once.need()) B2_CUDA_OK(cudaFuncSetAttribute(attn_prefill_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PT_SMEM));
   const double scale = softmax_scale > 0.f ? (double)softmax_scale : 1.0 / sqrt((double)hd);
   const float scale_log2 = (float)(scale * 1.4426950408889634);
-  B2_CUDA_OK(b2_launch(attn_prefill_tc_kernel, dim3(ntiles, nkv), dim3(288), (size_t)PT_SMEM, s, tk, tv, q, block_table, bt_stride, tiles_dev,
+  B2_CUDA_OK(b2_launch(attn_prefill_tc_kernel, dim3(ntiles, nkv), dim3(PT_THREADS), (size_t)PT_SMEM, s, tk, tv, q, block_table, bt_stride, tiles_dev,
                        out, nq, nkv, scale_log2, window));
   return 0;
 }

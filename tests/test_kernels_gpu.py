@@ -657,4 +657,7 @@ def test_attn_prefill(lib, case):
                                      I32(ntok), I32(list(range(len(ntok)))), len(ntok), ptr(out2), nq, nkv, hd, bs, cuda_stream_ptr()))
     finally:
         del os.environ["B2_PREFILL_TC"]
-    assert_bf16_close(out, out2, 2, 0.2, "tcgen05 vs mma.sync prefill attention (%s)" % case, abs_floor=2e-3)
+    # both round P to bf16 before P.V, but scale it differently (the tcgen05 kernel by a reference maximum that trails the
+    # running maximum by up to 2^8, the mma.sync one by the running maximum itself), so P's roundings differ: every element
+    # within 2 ulp, up to 40 % of them not bit-equal; each is checked against the oracle above
+    assert_bf16_close(out, out2, 2, 0.4, "tcgen05 vs mma.sync prefill attention (%s)" % case, abs_floor=2e-3)
