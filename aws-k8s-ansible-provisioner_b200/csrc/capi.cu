@@ -63,6 +63,22 @@ extern "C" int b2k_linear(const void* x, const void* w, void* out, int out_is_f3
   return launch_linear_tc(a, (cudaStream_t)stream);
 }
 
+extern "C" int b2k_linear_add(const void* x, const void* w, void* h, int T, int N, int K, void* stream) {
+  B2_REQUIRE(x && w && h, "b2k_linear_add: null pointer");
+  TcGemmArgs a;
+  a.bn = tc_pick_bn(T);
+  B2_REQUIRE(a.bn >= 32, "b2k_linear_add: built for prefill-sized token counts (T > 16)");
+  CAPI_TRY(b2_make_tmap_bf16(&a.tmap_w, w, (uint64_t)N, (uint64_t)K, (uint64_t)K, 128));
+  CAPI_TRY(b2_make_tmap_bf16(&a.tmap_x, x, (uint64_t)T, (uint64_t)K, (uint64_t)K, (uint32_t)a.bn));
+  a.T = T; a.N = N; a.K = K;
+  a.nsplit = 1;
+  a.out = h;
+  a.resid = h;
+  a.argmax_packed = nullptr;
+  a.epilogue = TC_EPI_BF16;
+  return launch_linear_tc(a, (cudaStream_t)stream);
+}
+
 extern "C" int b2k_debug_step_trace(void* dev_u64_buf) {
   unsigned long long* b = (unsigned long long*)dev_u64_buf;
   CAPI_TRY(step_trace_set_elementwise(b));

@@ -240,6 +240,7 @@ struct b2_engine {
   int use_chain = 0;  // B2_CHAIN: 0 separate kernels (default, fastest measured), 1 chain.cu, 2 chain_cluster.cu
   int prefill_tc = 1; // B2_PREFILL_TC: prefill attention on tcgen05 (attn_prefill_tc.cu); 0 = the mma.sync kernel (attn_prefill.cu)
   int l2_weight_prefetch = 0;  // B2_WPF: resid path, see forward_layers (measured slower: off)
+  int prefill_resid_fused = 0;  // B2_RESID_FUSED: prefill O / down projections add into the residual stream in their epilogue (measured slower: off)
   int gu_prefill_fused = 1;  // B2_GU_FUSED: prefill-sized gate/up projection with SwiGLU in its epilogue (gemm_gateup.cu)
   int use_pair = 1;   // B2_PAIR: bit 0 gate/up + SwiGLU, bit 1 QKV + QK-norm/RoPE/KV write as fused cluster-pair launches (gemm_pair.cu)
 
@@ -318,9 +319,14 @@ int pick_attn_split(b2_engine* e, int B, int max_len) {
 // xptr / out_bf16 are already offset to the lane's first row; the X tensor map covers the whole buffer, so the
 // tcgen05 kernel gets the lane's row offset as a coordinate.
 ActIn linear(b2_engine* e, const Lane& ln, int cls, XBuf xb, const bf16* xptr, const bf16* w, const CUtensorMap& tm_w, bf16* out_bf16,
-             int T, int N, int K, int* rc, const KvPrefetch& pf = KvPrefetch(), bool want_f32 = false, bool after_attention = false) {
+             int T, int N, int K, int* rc, const KvPrefetch& pf = KvPrefetch(), bool want_f32 = false, bool after_attention = false,
+             bf16* resid = nullptr, bool* resid_done = nullptr) {
   // want_f32: hand the consumer fp32 sums even when K is not split (a bias is added before the rounding)
+  // resid: the residual stream rows this projection's output is added to.  When the launch is a single-split tcgen05 GEMM
+  // with bf16 output (prefill shapes) the add happens in its epilogue, in place, and *resid_done tells the caller that the
+  // norm kernel behind it has no delta to add; otherwise nothing changes.
   *rc = 0;
+  if (resid_done) *resid_done = false;
   int impl = e->force_gemm_impl >= 0 ? e->force_gemm_impl : (T <= e->simt_max_tokens ? 0 : 1);
   if (ln.beside_attention && impl == 1 && tc_pick_bn(T) <= 64) want_f32 = true;  // the short ring is built for the partial epilogue
   if (want_f32 && (size_t)T * N > ln.partial_floats) {
@@ -371,6 +377,13 @@ ActIn linear(b2_engine* e, const Lane& ln, int cls, XBuf xb, const bf16* xptr, c
   if (ns == 1 && !want_f32) {
     a.epilogue = TC_EPI_BF16;
     a.out = out_bf16;
+    if (resid != nullptr && resid_done != nullptr && a.bn >= 32 && !k.skip()) {
+      a.out = resid;
+      a.resid = resid;
+      *rc = launch_linear_tc(a, ln.stream);
+      *resid_done = true;
+      return act_bf16(nullptr);
+    }
     if (!k.skip()) *rc = launch_linear_tc(a, ln.stream);
     return act_bf16(out_bf16);
   }
@@ -731,12 +744,18 @@ int forward_layers(b2_engine* e, const Lane& ln, int T, int ntiles) {
       delta = act_bf16(nullptr);  // h is up to date: the next norm (layer 0's successor never runs one; the final norm) adds nothing
       continue;
     }
+    // prefill-sized forwards, opt-in (B2_RESID_FUSED=1): the O and down projections add their output to the residual stream in
+    // their epilogue (gemm_tc.cu, `resid`), and the norm kernel behind them only normalises: half its traffic.  Measured at C2:
+    // the projection grows by 3.8 us (32 two-byte loads per thread and chunk, behind the accumulator read), the norm kernel
+    // shrinks by 1.7 us: 44.9 against 42.4 ms for the prefill on the same box.  Off.
+    bf16* fuse_resid = (ntiles > 0 && e->prefill_resid_fused && !((e->skip_mask >> B2K_NORM) & 1u)) ? h : nullptr;
+    bool o_added = false;
     ActIn o = linear(e, ln, B2K_GEMM_O, XB_ATTN, attn, L.wo, L.tm_o, proj, T, H, e->q_size, &rc, prefetch_for(l + 1, 0), false,
-                     /*after_attention=*/ntiles == 0);
+                     /*after_attention=*/ntiles == 0, fuse_resid, &o_added);
     B2_TRY(rc);
     {
       KL k(e, B2K_NORM);
-      if (!k.skip()) B2_TRY(launch_add_rmsnorm(h, o, L.ln2, x, T, H, c.rms_eps, st, tag));
+      if (!k.skip()) B2_TRY(launch_add_rmsnorm(h, o_added ? act_bf16(nullptr) : o, L.ln2, x, T, H, c.rms_eps, st, tag));
     }
     if (gu_pair) {
       KL k(e, B2K_GEMM_GATEUP);
@@ -750,8 +769,10 @@ int forward_layers(b2_engine* e, const Lane& ln, int T, int ntiles) {
       KL k(e, B2K_ACT);
       if (!k.skip()) B2_TRY(launch_silu_mul(gu, act, T, I, st, tag));
     }
-    delta = linear(e, ln, B2K_GEMM_DOWN, XB_ACT, act, L.wd, L.tm_d, proj, T, H, I, &rc, prefetch_for(l + 1, 2));
+    bool d_added = false;
+    delta = linear(e, ln, B2K_GEMM_DOWN, XB_ACT, act, L.wd, L.tm_d, proj, T, H, I, &rc, prefetch_for(l + 1, 2), false, false, fuse_resid, &d_added);
     B2_TRY(rc);
+    if (d_added) delta = act_bf16(nullptr);
   }
   {
     KL k(e, B2K_NORM);
@@ -1420,6 +1441,7 @@ extern "C" int b2_engine_create(const b2_config* cfg, const char* safetensors_pa
   e->use_pair = env_int("B2_PAIR", 7);  // bit 2: O / down projections update the residual stream themselves (gemm_resid.cu)
   e->prefill_tc = env_int("B2_PREFILL_TC", 1);
   e->gu_prefill_fused = env_int("B2_GU_FUSED", 1);
+  e->prefill_resid_fused = env_int("B2_RESID_FUSED", 0);
   e->l2_weight_prefetch = env_int("B2_WPF", 0);
   e->o_small_smem = env_int("B2_O_SMALL", 0);
   // Off by default: measured on B200 at C2 (ms/step) 0 MB 2.22, 40 MB 2.24, 72 MB 2.33, 100 MB 2.38 --

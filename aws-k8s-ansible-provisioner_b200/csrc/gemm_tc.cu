@@ -75,9 +75,9 @@ __device__ __forceinline__ unsigned long long tc_argmax_pack(float v, int idx) {
 template <int BN, int EPI, int SMALL = 0, int XCP = 0>
 __global__ void __launch_bounds__(192, SMALL ? 6 : 1)
 linear_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_x,
-                 void* __restrict__ out, unsigned long long* __restrict__ argmax_packed, int T, int N, int K,
+                 void* out, unsigned long long* __restrict__ argmax_packed, int T, int N, int K,
                  int kb_per_split, int m_tiles, int n_tiles, int nsplit, const KvPrefetch pf, int x_row0,
-                 const bf16* __restrict__ x_raw) {
+                 const bf16* __restrict__ x_raw, const bf16* resid) {
   using C = TcCfg<BN, SMALL>;
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t full_bar[C::STAGES];
@@ -402,7 +402,26 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
             tmem_ld32(tbase + (uint32_t)c0, r);
             tmem_ld_wait();
             bf16* d = dst + (size_t)c0 * N;
-            if (full) {
+            if (resid != nullptr) {
+              // out = bf16(resid + bf16(acc)): nn.Linear's rounding, then the residual add's (HF:...:339-351); resid may be out itself
+              // (all 32 loads first: resid and out may be the same buffer, so the compiler will not move a load above a store)
+              // and without a predicate per element -- with one the compiler wraps every load in a branch of its own and the
+              // 32 L2 round trips run one after the other: 186 instead of 29 us for an 8192 x 1024 x 2048 projection)
+              const unsigned short* rs = reinterpret_cast<const unsigned short*>(resid) + (size_t)(tok0 + c0) * N + row;
+              if (full) {
+                unsigned short rv[32];
+#pragma unroll
+                for (int j = 0; j < 32; ++j) rv[j] = rs[(size_t)j * N];
+#pragma unroll
+                for (int j = 0; j < 32; ++j)
+                  d[(size_t)j * N] = __float2bfloat16_rn(__uint_as_float((uint32_t)rv[j] << 16) + bf16_round(__uint_as_float(r[j])));
+              } else {  // the ragged last token tile / rows past N
+#pragma unroll 1
+                for (int j = 0; j < 32; ++j)
+                  if (row_ok && tok0 + c0 + j < T)
+                    d[(size_t)j * N] = __float2bfloat16_rn(__uint_as_float((uint32_t)rs[(size_t)j * N] << 16) + bf16_round(__uint_as_float(r[j])));
+              }
+            } else if (full) {
 #pragma unroll
               for (int j = 0; j < 32; ++j) d[(size_t)j * N] = __float2bfloat16_rn(__uint_as_float(r[j]));
             } else {
@@ -569,7 +588,7 @@ static int launch_one(const TcGemmArgs& a, int kb_per_split, cudaStream_t s) {
   }
   B2_CUDA_OK(b2_launch(linear_tc_kernel<BN, EPI, SMALL, XCP>, dim3(grid), dim3(192), (size_t)C::SMEM_BYTES, s, a.tmap_w, a.tmap_x, a.out,
                        a.argmax_packed, a.T, a.N, a.K, kb_per_split, m_tiles, n_tiles, a.nsplit, a.prefetch, a.x_row0,
-                       reinterpret_cast<const bf16*>(a.x_raw)));
+                       reinterpret_cast<const bf16*>(a.x_raw), reinterpret_cast<const bf16*>(a.resid)));
   return 0;
 }
 
@@ -611,6 +630,7 @@ int launch_linear_tc(const TcGemmArgs& a, cudaStream_t s) {
   B2_REQUIRE((kb_total + kps - 1) / kps == a.nsplit, "linear_tc: nsplit=%d leaves an empty split for %d k-blocks", a.nsplit,
              kb_total);
   B2_REQUIRE(a.nsplit == 1 || a.epilogue == TC_EPI_F32_PARTIAL, "linear_tc: split-K needs the fp32 partial epilogue");
+  B2_REQUIRE(a.resid == nullptr || (a.epilogue == TC_EPI_BF16 && a.bn >= 32), "linear_tc: a residual operand needs the bf16 epilogue and a token tile of at least 32");
   B2_REQUIRE(a.x_row0 == 0 || a.epilogue == TC_EPI_BF16 || a.epilogue == TC_EPI_F32_PARTIAL,
              "linear_tc: a row offset into X is only built for the plain epilogues");
   switch (a.bn) {

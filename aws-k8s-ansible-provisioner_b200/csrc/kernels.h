@@ -82,6 +82,7 @@ struct TcGemmArgs {
   KvPrefetch prefetch;                // optional ride-along K/V prefetch
   int small_smem = 0;                 // F32_PARTIAL, bn <= 64: short stage ring so the CTA fits beside a decode-attention CTA
   int x_row0 = 0;                     // first row of X (tmap_x) this launch reads: a micro-batch of a larger buffer
+  const void* resid = nullptr;        // TC_EPI_BF16, bn >= 32: out = bf16(resid[T][N] + bf16(x . W^T)); may be `out` itself (in-place residual add)
   const void* x_raw = nullptr;        // X rows [0, T) as a plain pointer (row stride K), ALREADY offset to the launch's first row:
                                       // lets decode-sized launches fetch X with cp.async instead of the tensor map (gemm_tc.cu, XCP)
 };

@@ -228,6 +228,8 @@ int b2k_qkv_rope(const void* x_bf16, const void* w_qkv_bf16, const void* qnorm_w
  *   K <= 3072; ssq[N/16][ssq_ld] (fp32) receives per token column the sum of squares of each 16-feature piece of the new h.
  * b2k_gateup_swiglu_norm / b2k_qkv_rope_norm: b2k_gateup_swiglu / b2k_qkv_rope with x = bf16(norm_w * bf16(h * rstd)) formed
  *   on the fly, rstd = rsqrt(sum of the `pieces` pieces of ssq / K + eps). */
+/* Prefill-sized residual add in the projection's epilogue: h[T][N] (bf16, in place) = bf16(h + bf16(x[T][K] . W[N][K]^T)), T > 16. */
+int b2k_linear_add(const void* x_bf16, const void* w_bf16, void* h_bf16, int T, int N, int K, void* stream);
 int b2k_linear_resid(const void* x_bf16, const void* w_bf16, void* h_bf16, float* ssq, int T, int N, int K, int ssq_ld, void* stream);
 int b2k_gateup_swiglu_norm(const void* h_bf16, const void* w_gu_bf16, const void* norm_w, const float* ssq, int pieces, int ssq_ld,
                            float eps, void* act_bf16, int T, int I, int K, void* stream);

@@ -288,6 +288,26 @@ def test_linear_resid(lib, T, K):
     assert torch.equal(h2.cpu(), h_new.cpu()) and torch.equal(ssq2[:, :T].cpu(), got[:, :T])
 
 
+@pytest.mark.parametrize("T,N,K", [(300, 1024, 2048), (8192, 1024, 3072), (33, 256, 512), (1000, 3072, 8192)])
+def test_linear_add_prefill(lib, T, N, K):
+    """gemm_tc.cu with a residual operand: the prefill-sized O / down projection adds into the residual stream in its
+    epilogue.  Bit-identical to b2k_linear (bf16 out) followed by b2k_add_rmsnorm's add."""
+    x = bf(T, K, seed=71)
+    w = bf(N, K, scale=0.03, seed=72)
+    h0 = bf(T + 1, N, seed=73)
+    dx, dw = dv(x), dv(w)
+    h_new = h0.cuda()
+    chk(lib, lib.b2k_linear_add(ptr(dx), ptr(dw), ptr(h_new), T, N, K, cuda_stream_ptr()))
+    y = torch.empty(T, N, dtype=torch.bfloat16, device="cuda")
+    chk(lib, lib.b2k_linear(ptr(dx), ptr(dw), ptr(y), 0, 1, T, N, K, 1, cuda_stream_ptr()))
+    h_ref = h0.cuda()
+    xn = torch.empty(T, N, dtype=torch.bfloat16, device="cuda")
+    gain = torch.ones(N, dtype=torch.bfloat16)
+    chk(lib, lib.b2k_add_rmsnorm(ptr(h_ref), ptr(y), 0, 1, ptr(dv(gain)), ptr(xn), T, N, 1e-6, cuda_stream_ptr()))
+    assert torch.equal(h_new[:T].cpu(), h_ref[:T].cpu()), "residual add in the epilogue differs from projection + add kernel"
+    assert torch.equal(h_new[T:].cpu(), h0[T:]), "rows past T were touched"
+
+
 @pytest.mark.parametrize("T", [64, 33, 32, 5])
 def test_gateup_swiglu_normalise_on_load(lib, T):
     """gemm_pair.cu with PairNorm: the projection reads the residual stream and applies the RMSNorm while staging its
