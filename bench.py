@@ -268,7 +268,7 @@ def run_b200(args, rank, world, local, dist):
     assert W >= 3, "at least 3 warm-up steps"
     assert W + K <= OUT_TOKENS + 1024
     lo, hi, advance = timed_window(K, W)
-    cfg = pkg.EngineConfig(max_model_len=max(PROMPT + OUT_TOKENS, hi) + 16, max_seqs=BATCH, max_batch_tokens=8192, use_cuda_graphs=True)
+    cfg = pkg.EngineConfig(max_model_len=max(PROMPT + OUT_TOKENS, hi) + 16, max_seqs=BATCH, max_batch_tokens=int(os.environ.get("B2_BENCH_CHUNK", "32768")), use_cuda_graphs=True)
     assert cfg.weight_bytes() == WEIGHT_BYTES and cfg.kv_bytes_per_token() == KV_BYTES_PER_TOKEN and cfg.num_layers == NUM_LAYERS
     cfg.num_blocks = BATCH * ((cfg.max_model_len + 15) // 16) + 8
     t0 = time.time()

@@ -21,15 +21,17 @@ def main():
     pkg = importlib.import_module("aws-k8s-ansible-provisioner_b200")
     weights = importlib.import_module("aws-k8s-ansible-provisioner_b200.weights")
     B, P = 64, 512
-    cfg = pkg.EngineConfig(max_model_len=args.ctx + 64, max_seqs=B, max_batch_tokens=8192)
+    chunk = int(os.environ.get("B2_BENCH_CHUNK", "32768"))  # bench.py's prefill: the whole batch in one call
+    cfg = pkg.EngineConfig(max_model_len=args.ctx + 64, max_seqs=B, max_batch_tokens=chunk)
     cfg.num_blocks = B * ((cfg.max_model_len + 15) // 16) + 8
     eng = pkg.Engine(cfg, device=0)
     eng.load_state_dict(weights.random_state_dict(cfg, seed=0))
     g = torch.Generator().manual_seed(1)
     prompts = torch.randint(0, cfg.vocab, (B, P), generator=g, dtype=torch.int32).numpy()
     sids = [eng.seq_create(cfg.max_model_len) for _ in range(B)]
-    for i in range(0, B, 16):
-        eng.prefill(sids[i:i + 16], [p.tolist() for p in prompts[i:i + 16]])
+    per = max(1, chunk // P)
+    for i in range(0, B, per):
+        eng.prefill(sids[i:i + per], [p.tolist() for p in prompts[i:i + per]])
     print("launches after prefill: %d" % eng.launch_count(), flush=True)
     if args.prefill_only:
         eng.close()
