@@ -28,7 +28,7 @@ NVCC_FLAGS = [
     "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr",
     "-Xcompiler", "-Wall", "-Xcudafe", "--diag_suppress=177",
 ]
-ENGINE_SOURCES = ["elementwise.cu", "elementwise_opt.cu", "gemm_simt.cu", "gemm_tc.cu", "gemm_pair.cu", "gemm_gateup.cu", "gemm_resid.cu", "attn_decode.cu", "attn_prefill.cu", "attn_prefill_tc.cu", "sampling.cu", "chain.cu", "chain_cluster.cu",
+ENGINE_SOURCES = ["elementwise.cu", "elementwise_opt.cu", "gemm_simt.cu", "gemm_tc.cu", "gemm_pair.cu", "gemm_gateup.cu", "gemm_resid.cu", "gemm_mc.cu", "attn_decode.cu", "attn_prefill.cu", "attn_prefill_tc.cu", "sampling.cu", "chain.cu", "chain_cluster.cu",
                   "engine.cu", "capi.cu"]
 
 

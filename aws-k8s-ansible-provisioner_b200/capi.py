@@ -70,6 +70,7 @@ SIGNATURES = {
     "b2k_qkv_rope": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, C.c_float, _P]),
     "b2k_linear_resid": (_I, [_P, _P, _P, _P, _I, _I, _I, _I, _P]),
     "b2k_linear_add": (_I, [_P, _P, _P, _I, _I, _I, _P]),
+    "b2k_linear_multicast": (_I, [_P, _P, _P, _I, _I, _I, _P]),
     "b2k_gateup_swiglu_norm": (_I, [_P, _P, _P, _P, _I, _I, C.c_float, _P, _I, _I, _I, _P]),
     "b2k_qkv_rope_norm": (_I, [_P, _P, _P, _P, _I, _I, C.c_float, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, C.c_float, _P]),
     "b2k_debug_step_trace": (_I, [_P]),

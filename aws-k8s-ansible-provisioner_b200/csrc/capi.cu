@@ -63,6 +63,14 @@ extern "C" int b2k_linear(const void* x, const void* w, void* out, int out_is_f3
   return launch_linear_tc(a, (cudaStream_t)stream);
 }
 
+extern "C" int b2k_linear_multicast(const void* x, const void* w, void* out, int T, int N, int K, void* stream) {
+  B2_REQUIRE(x && w && out, "b2k_linear_multicast: null pointer");
+  CUtensorMap tw, tx;
+  CAPI_TRY(b2_make_tmap_bf16(&tw, w, (uint64_t)N, (uint64_t)K, (uint64_t)K, 128));
+  CAPI_TRY(b2_make_tmap_bf16(&tx, x, (uint64_t)T, (uint64_t)K, (uint64_t)K, 128));
+  return launch_linear_mc(tw, tx, (bf16*)out, T, N, K, 0, (cudaStream_t)stream);
+}
+
 extern "C" int b2k_linear_add(const void* x, const void* w, void* h, int T, int N, int K, void* stream) {
   B2_REQUIRE(x && w && h, "b2k_linear_add: null pointer");
   TcGemmArgs a;

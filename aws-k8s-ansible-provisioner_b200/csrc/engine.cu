@@ -241,6 +241,7 @@ struct b2_engine {
   int prefill_tc = 1; // B2_PREFILL_TC: prefill attention on tcgen05 (attn_prefill_tc.cu); 0 = the mma.sync kernel (attn_prefill.cu)
   int l2_weight_prefetch = 0;  // B2_WPF: resid path, see forward_layers (measured slower: off)
   int prefill_resid_fused = 0;  // B2_RESID_FUSED: prefill O / down projections add into the residual stream in their epilogue (measured slower: off)
+  int prefill_mc = 1;  // B2_MC: prefill projections as multicast CTA pairs (gemm_mc.cu)
   int gu_prefill_fused = 1;  // B2_GU_FUSED: prefill-sized gate/up projection with SwiGLU in its epilogue (gemm_gateup.cu)
   int use_pair = 1;   // B2_PAIR: bit 0 gate/up + SwiGLU, bit 1 QKV + QK-norm/RoPE/KV write as fused cluster-pair launches (gemm_pair.cu)
 
@@ -383,6 +384,11 @@ ActIn linear(b2_engine* e, const Lane& ln, int cls, XBuf xb, const bf16* xptr, c
       *rc = launch_linear_tc(a, ln.stream);
       *resid_done = true;
       return act_bf16(nullptr);
+    }
+    if (e->prefill_mc && a.bn == 256 && linear_mc_shapes_ok(T, N, K) && !pf.k_pages) {
+      // prefill shapes: pairs of CTAs share the token tile (gemm_mc.cu); same arithmetic, a third less L2 -> shared-memory traffic
+      if (!k.skip()) *rc = launch_linear_mc(tm_w, e->tm_x[xb][bn_index(128)], out_bf16, T, N, K, ln.row0, ln.stream);
+      return act_bf16(out_bf16);
     }
     if (!k.skip()) *rc = launch_linear_tc(a, ln.stream);
     return act_bf16(out_bf16);
@@ -1441,6 +1447,7 @@ extern "C" int b2_engine_create(const b2_config* cfg, const char* safetensors_pa
   e->use_pair = env_int("B2_PAIR", 7);  // bit 2: O / down projections update the residual stream themselves (gemm_resid.cu)
   e->prefill_tc = env_int("B2_PREFILL_TC", 1);
   e->gu_prefill_fused = env_int("B2_GU_FUSED", 1);
+  e->prefill_mc = env_int("B2_MC", 1);
   e->prefill_resid_fused = env_int("B2_RESID_FUSED", 0);
   e->l2_weight_prefetch = env_int("B2_WPF", 0);
   e->o_small_smem = env_int("B2_O_SMALL", 0);

@@ -1,0 +1,213 @@
+// gemm_mc.cu -- prefill-sized projection y[T][N] = x[T][K] . W[N][K]^T (bf16 out) with the token operand SHARED between
+// the two CTAs of a cluster (HF nn.Linear, models/qwen3/modeling_qwen3.py:236-247).
+//
+// Why: the persistent 128 x 256 tile kernel of gemm_tc.cu moves 48 KB from L2 into shared memory per 64-wide k-block
+// (16 KB of weights + 32 KB of tokens) for 532 cycles of tcgen05.mma: 90 bytes per cycle and SM, more than an SM gets
+// from L2 when all 148 ask at once -- ncu shows the tensor pipe 52-68 % active and the share rising with K, i.e. with the
+// weight of the main loop (profiles/r02_prefill_full_raw.csv).  Here two CTAs take two ADJACENT weight-row tiles of the same
+// 256-token tile: each loads its own 16 KB of weights and only HALF of the token rows (16 KB), and the TMA engine writes that
+// half into BOTH CTAs' shared memory (cp.async.bulk.tensor ... .multicast::cluster; the tensor maps cover this GPU's memory
+// only).  32 KB per k-block and SM instead of 48.
+//   * full barrier of a stage (per CTA): one arrive.expect_tx of 48 KB by the CTA's own producer; bytes arrive from its own
+//     weight load, its own token half and the peer's token half
+//   * empty barrier of a stage (per CTA): TWO arrivals -- the stage is rewritten by the peer's multicast too, so both CTAs'
+//     MMAs must have read it: each MMA thread commits with .multicast::cluster to the barrier of both CTAs
+// Everything else is gemm_tc.cu's plain bf16 path: swap-AB (weight rows on MMA-M, tokens on MMA-N), double-buffered TMEM
+// accumulator, four epilogue warps, same k order -> the same bits (tests/test_kernels_gpu.py::test_linear_multicast).
+#include "kernels.h"
+
+namespace b2 {
+
+namespace {
+
+constexpr int MC_BM = 128, MC_BN = 256, MC_BK = 64;
+constexpr int MC_W_BYTES = MC_BM * MC_BK * 2;       // 16 KB
+constexpr int MC_XH_BYTES = (MC_BN / 2) * MC_BK * 2;  // 16 KB: one CTA's half of the token tile
+constexpr int MC_STAGE_BYTES = MC_W_BYTES + 2 * MC_XH_BYTES;
+constexpr int MC_STAGES = 4;
+constexpr int MC_SMEM_BYTES = MC_STAGES * MC_STAGE_BYTES + 1024;
+
+__device__ __forceinline__ uint32_t mc_cluster_rank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void mc_tma_load_2d_multicast(uint32_t dst_smem, const CUtensorMap* tmap, int c0, int c1, uint32_t bar, uint16_t mask) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1, {%3, %4}], [%2], %5;" ::"r"(
+          dst_smem),
+      "l"(tmap), "r"(bar), "r"(c0), "r"(c1), "h"(mask)
+      : "memory");
+}
+__device__ __forceinline__ void mc_commit_multicast(uint32_t bar, uint16_t mask) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar), "h"(mask)
+               : "memory");
+}
+__device__ __forceinline__ void mc_cluster_sync() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
+// grid = 2 * clusters; cluster c walks the (weight-tile pair, token tile) list with stride `clusters`, the pair index fastest.
+__global__ void __launch_bounds__(192, 1)
+linear_mc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_x, bf16* __restrict__ out, int T, int N,
+                 int K, int m_pairs, int n_tiles, int x_row0) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t full_bar[MC_STAGES];
+  __shared__ __align__(8) uint64_t empty_bar[MC_STAGES];
+  __shared__ __align__(8) uint64_t tmem_full_bar[2];
+  __shared__ __align__(8) uint64_t tmem_empty_bar[2];
+  __shared__ uint32_t tmem_slot;
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = mc_cluster_rank();
+  const int cluster = blockIdx.x >> 1, clusters = gridDim.x >> 1;
+  const int kb_total = K / MC_BK;
+  const int total = m_pairs * n_tiles;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < MC_STAGES; ++s) {
+      mbar_init(smem_u32(&full_bar[s]), 1);
+      mbar_init(smem_u32(&empty_bar[s]), 2);  // this CTA's MMAs and the peer's
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(smem_u32(&tmem_full_bar[a]), 1);
+      mbar_init(smem_u32(&tmem_empty_bar[a]), 128);
+    }
+    mbar_fence_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(smem_u32(&tmem_slot), 512);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_slot;
+  mc_cluster_sync();  // the peer's barriers exist before anything of mine can arrive on them
+  pdl_wait();
+  if (threadIdx.x == 0) pdl_launch_dependents();
+
+  if (warp == 0) {
+    if (lane == 0) {
+      tma_prefetch_desc(&tmap_w);
+      tma_prefetch_desc(&tmap_x);
+      int it = 0;
+      for (int p = cluster; p < total; p += clusters) {
+        const int m_tile = 2 * (p % m_pairs) + (int)rank, n_tile = p / m_pairs;
+        for (int kb = 0; kb < kb_total; ++kb, ++it) {
+          const int s = it % MC_STAGES;
+          mbar_wait(smem_u32(&empty_bar[s]), ((it / MC_STAGES) & 1) ^ 1);  // both CTAs are done with this stage
+          const uint32_t fb = smem_u32(&full_bar[s]);
+          mbar_arrive_expect_tx(fb, MC_STAGE_BYTES);
+          const uint32_t ws = smem_base + s * MC_STAGE_BYTES;
+          tma_load_2d(ws, &tmap_w, kb * MC_BK, m_tile * MC_BM, fb);
+          // my half of the token rows, into the same place of both CTAs' stage; the bytes are counted on both full barriers
+          mc_tma_load_2d_multicast(ws + MC_W_BYTES + rank * MC_XH_BYTES, &tmap_x, kb * MC_BK, n_tile * MC_BN + (int)rank * (MC_BN / 2) + x_row0, fb,
+                                   (uint16_t)3);
+        }
+      }
+      // tail: the releases of the last stages (this CTA's MMAs and the PEER's, which arrive through the cluster network) have
+      // landed on my barriers before this CTA goes to the final cluster barrier and exits
+      for (int j = it > MC_STAGES ? it - MC_STAGES : 0; j < it; ++j) mbar_wait(smem_u32(&empty_bar[j % MC_STAGES]), (j / MC_STAGES) & 1);
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(MC_BM, MC_BN);
+      int it = 0, lt = 0;
+      for (int p = cluster; p < total; p += clusters, ++lt) {
+        const int as = lt & 1;
+        mbar_wait(smem_u32(&tmem_empty_bar[as]), ((lt >> 1) & 1) ^ 1);
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + (uint32_t)(as * MC_BN);
+        for (int kb = 0; kb < kb_total; ++kb, ++it) {
+          const int s = it % MC_STAGES;
+          mbar_wait(smem_u32(&full_bar[s]), (it / MC_STAGES) & 1);
+          tc_fence_after();
+          const uint32_t ws = smem_base + s * MC_STAGE_BYTES;
+          const uint64_t da = umma_desc_sw128(ws);
+          const uint64_t db = umma_desc_sw128(ws + MC_W_BYTES);  // 256 token rows: the two halves are contiguous
+#pragma unroll
+          for (int k = 0; k < MC_BK / 16; ++k)
+            tc_mma_bf16(tmem_d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb > 0 || k > 0) ? 1u : 0u);
+          mc_commit_multicast(smem_u32(&empty_bar[s]), (uint16_t)3);
+        }
+        tc_commit(smem_u32(&tmem_full_bar[as]));
+      }
+    }
+  } else {
+    const int q = warp & 3;
+    int lt = 0;
+    for (int p = cluster; p < total; p += clusters, ++lt) {
+      const int m_tile = 2 * (p % m_pairs) + (int)rank, n_tile = p / m_pairs;
+      const int as = lt & 1;
+      mbar_wait(smem_u32(&tmem_full_bar[as]), (lt >> 1) & 1);
+      tc_fence_after();
+      const int row = m_tile * MC_BM + q * 32 + lane;
+      const bool row_ok = row < N;
+      const int tok0 = n_tile * MC_BN;
+      const bool full = row_ok && tok0 + MC_BN <= T;
+      const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * MC_BN);
+      bf16* dst = out + (size_t)tok0 * N + row;
+#pragma unroll 1
+      for (int c0 = 0; c0 < MC_BN; c0 += 32) {
+        uint32_t r[32];
+        tmem_ld32(tbase + (uint32_t)c0, r);
+        tmem_ld_wait();
+        bf16* d = dst + (size_t)c0 * N;
+        if (full) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) d[(size_t)j * N] = __float2bfloat16_rn(__uint_as_float(r[j]));
+        } else {
+#pragma unroll 1
+          for (int j = 0; j < 32; ++j)
+            if (row_ok && tok0 + c0 + j < T) d[(size_t)j * N] = __float2bfloat16_rn(__uint_as_float(r[j]));
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(smem_u32(&tmem_empty_bar[as]));
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  // no CTA leaves while its peer may still write into its shared memory or arrive on its barriers
+  mc_cluster_sync();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
+}  // namespace
+
+bool linear_mc_shapes_ok(int T, int N, int K) { return T >= 512 && N % (2 * MC_BM) == 0 && K % MC_BK == 0; }
+
+// tm_w: W [N][K], 128-row x 64-column box; tm_x128: X with a 128-row box (NOT the 256-row one of the single-CTA kernel).
+int launch_linear_mc(const CUtensorMap& tm_w, const CUtensorMap& tm_x128, bf16* out, int T, int N, int K, int x_row0, cudaStream_t s) {
+  if (T <= 0) return 0;
+  B2_REQUIRE(linear_mc_shapes_ok(T, N, K), "linear_mc: shape T=%d N=%d K=%d not built", T, N, K);
+  static B2PerDeviceOnce attr_once;
+  if (attr_once.need()) B2_CUDA_OK(cudaFuncSetAttribute(linear_mc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, MC_SMEM_BYTES));
+  const int m_pairs = N / (2 * MC_BM), n_tiles = (T + MC_BN - 1) / MC_BN;
+  const int total = m_pairs * n_tiles;
+  static int sms = device_num_sms();
+  const int clusters = total < sms / 2 ? total : sms / 2;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(2 * clusters);
+  cfg.blockDim = dim3(192);
+  cfg.dynamicSmemBytes = MC_SMEM_BYTES;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[2];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = b2_pdl_enabled() ? 2 : 1;
+  B2_CUDA_OK(cudaLaunchKernelEx(&cfg, linear_mc_kernel, tm_w, tm_x128, out, T, N, K, m_pairs, n_tiles, x_row0));
+  return 0;
+}
+
+}  // namespace b2

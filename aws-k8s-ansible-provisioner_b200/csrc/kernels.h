@@ -95,6 +95,9 @@ int tc_pick_nsplit(int T, int N, int K, int num_sms);
 // ---- gemm_pair.cu: a projection and the element-wise kernel behind it in one launch (clusters of two CTAs split K and
 //      exchange accumulator halves through distributed shared memory); at most 64 tokens, K <= 1024 ----
 bool pair_shapes_ok(int T, int K);
+// gemm_mc.cu: prefill-sized bf16 projection, two CTAs per cluster share the token tile through TMA multicast
+bool linear_mc_shapes_ok(int T, int N, int K);
+int launch_linear_mc(const CUtensorMap& tm_w, const CUtensorMap& tm_x128, bf16* out, int T, int N, int K, int x_row0, cudaStream_t s);
 // gemm_gateup.cu: the prefill-sized counterpart (two accumulators per tile, SwiGLU in the epilogue)
 bool gateup_prefill_shapes_ok(int T, int I, int K);
 int launch_gateup_swiglu_prefill(const CUtensorMap& tm_w, const CUtensorMap& tm_x128, bf16* act, int T, int I, int K, int x_row0, cudaStream_t s);

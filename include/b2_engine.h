@@ -228,6 +228,9 @@ int b2k_qkv_rope(const void* x_bf16, const void* w_qkv_bf16, const void* qnorm_w
  *   K <= 3072; ssq[N/16][ssq_ld] (fp32) receives per token column the sum of squares of each 16-feature piece of the new h.
  * b2k_gateup_swiglu_norm / b2k_qkv_rope_norm: b2k_gateup_swiglu / b2k_qkv_rope with x = bf16(norm_w * bf16(h * rstd)) formed
  *   on the fly, rstd = rsqrt(sum of the `pieces` pieces of ssq / K + eps). */
+/* Prefill-sized y[T][N] (bf16) = x[T][K] . W[N][K]^T by pairs of CTAs that share the token tile through TMA multicast (both
+ * operands in this GPU's memory); T >= 512, N % 256 == 0, K % 64 == 0.  Bit-identical to b2k_linear's bf16 output. */
+int b2k_linear_multicast(const void* x_bf16, const void* w_bf16, void* out_bf16, int T, int N, int K, void* stream);
 /* Prefill-sized residual add in the projection's epilogue: h[T][N] (bf16, in place) = bf16(h + bf16(x[T][K] . W[N][K]^T)), T > 16. */
 int b2k_linear_add(const void* x_bf16, const void* w_bf16, void* h_bf16, int T, int N, int K, void* stream);
 int b2k_linear_resid(const void* x_bf16, const void* w_bf16, void* h_bf16, float* ssq, int T, int N, int K, int ssq_ld, void* stream);

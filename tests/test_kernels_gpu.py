@@ -288,6 +288,27 @@ def test_linear_resid(lib, T, K):
     assert torch.equal(h2.cpu(), h_new.cpu()) and torch.equal(ssq2[:, :T].cpu(), got[:, :T])
 
 
+@pytest.mark.parametrize("T,N,K", [(512, 256, 256), (8192, 4096, 1024), (8192, 1024, 3072), (1000, 1024, 2048), (32768, 1024, 2048)])
+def test_linear_multicast(lib, T, N, K):
+    """gemm_mc.cu: prefill projection by CTA pairs that share the token tile through TMA multicast.  Same k order, one
+    accumulator per output: BIT-identical to b2k_linear's bf16 output; ragged last token tile; nothing written past row T."""
+    x = bf(T, K, seed=81)
+    w = bf(N, K, scale=0.03, seed=82)
+    dx, dw = dv(x), dv(w)
+    y = torch.full((T + 2, N), float("nan"), dtype=torch.bfloat16, device="cuda")
+    chk(lib, lib.b2k_linear_multicast(ptr(dx), ptr(dw), ptr(y), T, N, K, cuda_stream_ptr()))
+    y2 = torch.empty(T, N, dtype=torch.bfloat16, device="cuda")
+    chk(lib, lib.b2k_linear(ptr(dx), ptr(dw), ptr(y2), 0, 1, T, N, K, 1, cuda_stream_ptr()))
+    assert torch.equal(y[:T].cpu(), y2.cpu()), "multicast pair kernel differs from the single-CTA kernel"
+    assert torch.isnan(y[T:].float()).all(), "wrote past the last token row"
+    rows = slice(0, min(T, 256))
+    ref = (x[rows].float() @ w.float().t())
+    assert rel_fro(y[rows].float().cpu(), ref) < 5e-3
+    y3 = torch.empty(T, N, dtype=torch.bfloat16, device="cuda")
+    chk(lib, lib.b2k_linear_multicast(ptr(dx), ptr(dw), ptr(y3), T, N, K, cuda_stream_ptr()))
+    assert torch.equal(y3.cpu(), y[:T].cpu()), "two launches differ"
+
+
 @pytest.mark.parametrize("T,N,K", [(300, 1024, 2048), (8192, 1024, 3072), (33, 256, 512), (1000, 3072, 8192)])
 def test_linear_add_prefill(lib, T, N, K):
     """gemm_tc.cu with a residual operand: the prefill-sized O / down projection adds into the residual stream in its
