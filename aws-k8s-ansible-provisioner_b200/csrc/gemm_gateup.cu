@@ -23,13 +23,14 @@ constexpr int GU_BM = 128, GU_BN = 128, GU_BK = 64;
 constexpr int GU_W_BYTES = GU_BM * GU_BK * 2;          // 16 KB: one operand tile of a k-block
 constexpr int GU_STAGE_BYTES = 3 * GU_W_BYTES;         // gate | up | tokens
 constexpr int GU_STAGES = 4;
-constexpr int GU_SMEM_BYTES = GU_STAGES * GU_STAGE_BYTES + 1024;
+constexpr int GU_OUT_BYTES = 32 * GU_BM * 2;  // staging buffer of one 32-token column block: [32 tokens][128 features] bf16
+constexpr int GU_SMEM_BYTES = GU_STAGES * GU_STAGE_BYTES + 4 * GU_OUT_BYTES + 1024;
 constexpr int GU_EPI_WARPS = 16;
 constexpr int GU_THREADS = 64 + 32 * GU_EPI_WARPS;
 
 __global__ void __launch_bounds__(GU_THREADS, 1)
-gateup_swiglu_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_x, bf16* __restrict__ act,
-                        int T, int I, int K, int m_tiles, int n_tiles, int x_row0) {
+gateup_swiglu_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_x,
+                        const __grid_constant__ CUtensorMap tmap_out, int T, int I, int K, int m_tiles, int n_tiles, int x_row0) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t full_bar[GU_STAGES];
   __shared__ __align__(8) uint64_t empty_bar[GU_STAGES];
@@ -125,6 +126,8 @@ gateup_swiglu_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid
     const int q = warp & 3;             // TMEM lane quarter this warp may read
     const int part = (warp - 2) >> 2;   // which of the quarter's four warps: its 32-token column block
     pdl_wait();
+    const uint32_t obuf = smem_base + GU_STAGES * GU_STAGE_BYTES;
+    uint8_t* obuf_p = smem_raw + (smem_base - smem_u32(smem_raw)) + GU_STAGES * GU_STAGE_BYTES;
     int lt = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
       const int m_tile = tile % m_tiles, n_tile = tile / m_tiles;
@@ -143,17 +146,30 @@ gateup_swiglu_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid
         // both blocks are in registers: the accumulator pair goes back to the MMA warp before the activation math
         tc_fence_before();
         mbar_arrive(smem_u32(&tmem_empty_bar[as]));
-        bf16* d = act + (size_t)(tok0 + c0) * I + row;
-        const bool full = tok0 + c0 + 32 <= T;
+        // The block leaves through shared memory and ONE bulk tensor store ([32 tokens][128 features], full 256-byte rows;
+        // rows past T are clipped by the tensor map) instead of 32 two-byte stores per thread: see gemm_mc.cu.  The four
+        // warps of a column block share staging buffer `part` and named barrier 1 + part.
+        unsigned short* ob = reinterpret_cast<unsigned short*>(obuf_p + part * GU_OUT_BYTES) + q * 32 + lane;
+        const bool issuer = q == 0 && lane == 0;  // one of the block's 128 threads
+        if (issuer) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // the previous tile's store has read the buffer
+        asm volatile("bar.sync %0, 128;" ::"r"(1 + part) : "memory");
 #pragma unroll
         for (int j = 0; j < 32; ++j) {
           const float gv = bf16_round(__uint_as_float(g[j])), uv = bf16_round(__uint_as_float(u[j]));
           const float sl = bf16_round(__fdiv_rn(gv, 1.0f + expf(-gv)));
-          const bf16 o = __float2bfloat16_rn(sl * uv);
-          if (full || tok0 + c0 + j < T) d[(size_t)j * I] = o;
+          ob[j * GU_BM] = __bfloat16_as_ushort(__float2bfloat16_rn(sl * uv));
+        }
+        fence_proxy_async();
+        asm volatile("bar.sync %0, 128;" ::"r"(1 + part) : "memory");
+        if (issuer) {
+          asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%1, %2}], [%3];" ::"l"(&tmap_out), "r"(m_tile * GU_BM),
+                       "r"(tok0 + c0), "r"(obuf + (uint32_t)(part * GU_OUT_BYTES))
+                       : "memory");
+          asm volatile("cp.async.bulk.commit_group;" ::: "memory");
         }
       }
     }
+    if (q == 0 && lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
   }
   tc_fence_before();
   __syncthreads();
@@ -172,6 +188,11 @@ int launch_gateup_swiglu_prefill(const CUtensorMap& tm_w, const CUtensorMap& tm_
                                  cudaStream_t s) {
   if (T <= 0) return 0;
   B2_REQUIRE(gateup_prefill_shapes_ok(T, I, K), "gateup_swiglu_prefill: shape T=%d I=%d K=%d not built", T, I, K);
+  CUtensorMap tm_out;  // act [T][I], box 128 features x 32 tokens, no swizzle: the staging buffers' layout
+  {
+    const int rc = b2_make_tmap_bf16_ex(&tm_out, act, (uint64_t)T, (uint64_t)I, (uint64_t)I, GU_BM, 32, /*swizzle128=*/0);
+    if (rc != 0) return rc;
+  }
   static B2PerDeviceOnce attr_once;
   if (attr_once.need())
     B2_CUDA_OK(cudaFuncSetAttribute(gateup_swiglu_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GU_SMEM_BYTES));
@@ -179,7 +200,7 @@ int launch_gateup_swiglu_prefill(const CUtensorMap& tm_w, const CUtensorMap& tm_
   const int total = m_tiles * n_tiles;
   static int sms = device_num_sms();
   const int grid = total < sms ? total : sms;
-  B2_CUDA_OK(b2_launch(gateup_swiglu_tc_kernel, dim3(grid), dim3(GU_THREADS), (size_t)GU_SMEM_BYTES, s, tm_w, tm_x128, act, T, I, K, m_tiles,
+  B2_CUDA_OK(b2_launch(gateup_swiglu_tc_kernel, dim3(grid), dim3(GU_THREADS), (size_t)GU_SMEM_BYTES, s, tm_w, tm_x128, tm_out, T, I, K, m_tiles,
                        n_tiles, x_row0));
   return 0;
 }
