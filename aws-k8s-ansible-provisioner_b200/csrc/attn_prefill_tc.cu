@@ -72,7 +72,7 @@ constexpr float PT_RESCALE = 8.0f;  // log2 units: the reference maximum is rais
 __global__ void __launch_bounds__(PT_THREADS, 2)
 attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_constant__ CUtensorMap tmap_v, const bf16* __restrict__ q,
                        const int32_t* __restrict__ block_table, int bt_stride, const PrefillTile* __restrict__ tiles,
-                       bf16* __restrict__ out, int nq, int nkv, float scale_log2, int window) {
+                       bf16* __restrict__ out, int nq, int nkv, float scale_log2, int window, int pair_mode) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t k_full, v_full, s_full, p_full, o_full;
   __shared__ uint32_t tmem_slot;
@@ -84,9 +84,16 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   // Blocks are dispatched in index order and a tile late in its sequence has the most key tiles: walking the tile list
   // backwards starts the long CTAs first and leaves the short ones for the kernel's last wave.
-  const PrefillTile tile = tiles[gridDim.x - 1 - blockIdx.x];
+  // pair_mode (models with one query head per kv head, run through the GQA-2 layout with an all-zero partner head): the 128
+  // MMA rows are TWO consecutive 64-token tiles of one sequence x the real head, instead of one tile x (real, zero) heads --
+  // half the CTAs, no MMA rows spent on zeros; the partner head's output rows are not written (the output projection's
+  // columns for them are zeros, and the buffer holds finite values from its allocation).  The host pads every sequence to an
+  // even number of tiles (a tile with nrows == 0), so tiles 2i and 2i + 1 always belong together.
+  const int ti = gridDim.x - 1 - blockIdx.x;
+  const PrefillTile tile = tiles[pair_mode ? 2 * ti : ti];                // rows 0..63 (and, without pair_mode, 64..127)
+  const PrefillTile tile_b = pair_mode ? tiles[2 * ti + 1] : tile;        // rows 64..127 in pair_mode
   const int kvh = blockIdx.y;
-  const int kv_len = tile.q_pos0 + tile.nrows;
+  const int kv_len = (pair_mode && tile_b.nrows > 0) ? tile_b.q_pos0 + tile_b.nrows : tile.q_pos0 + tile.nrows;
   const int n_kt = (kv_len + PT_BN - 1) / PT_BN;
   const int kt0 = (window > 0 && tile.q_pos0 - window + 1 > 0) ? (tile.q_pos0 - window + 1) / PT_BN : 0;
   const int32_t* bt = block_table + (size_t)tile.bt_row * bt_stride;
@@ -171,17 +178,20 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_
     // ---- 256 softmax threads: threads r and r + 128 own MMA row r = (head r >> 6, query token r & 63); `kh` says which
     // 64 keys of a tile (and which 64 output dims) are this thread's ----
     const int r = threadIdx.x & 127, kh = threadIdx.x >> 7;
-    const int h = r >> 6, t = r & 63;
-    const bool row_ok = t < tile.nrows;
-    const int qpos = tile.q_pos0 + t;
+    const int h = pair_mode ? 0 : r >> 6, t = r & 63;
+    const PrefillTile& mt = (r >> 6) ? tile_b : tile;  // the tile this row belongs to
+    const bool row_ok = t < mt.nrows;
+    const int qpos = mt.q_pos0 + t;
+    const int row_kv_len = mt.q_pos0 + mt.nrows;
     // stage Q: rows in the K-major swizzled layout, 16 bytes per thread and step (rows past the tile are zeros)
 #pragma unroll
     for (int k = 0; k < (PT_M * 16) / 256; ++k) {  // 8 cp.async per thread, all in flight together
       const int idx = (int)threadIdx.x + k * 256;
       const int row = idx >> 4, c = idx & 15;
       const int rh = row >> 6, rt = row & 63;
-      const bool in = rt < tile.nrows;
-      const bf16* src = q + ((size_t)(tile.q_row0 + (in ? rt : 0)) * nq + kvh * 2 + rh) * PT_HD + c * 8;
+      const PrefillTile& st = rh ? tile_b : tile;
+      const bool in = rt < st.nrows;
+      const bf16* src = q + ((size_t)(st.q_row0 + (in ? rt : 0)) * nq + kvh * 2 + (pair_mode ? 0 : rh)) * PT_HD + c * 8;
       asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(q_s + (c >> 3) * PT_HALF_BYTES + row * 128 + (((c & 7) ^ (row & 7)) << 4)),
                    "l"(src), "r"(in ? 16 : 0)
                    : "memory");
@@ -208,10 +218,10 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_
       // Valid keys of this row in this tile are a contiguous range [lo_col, hi_col] (causal bound, sequence end, window).
       // A tile that lies wholly inside the range of EVERY row of the CTA (all but the last one or two tiles of a row
       // block) takes the branch without per-element masks; the test is uniform over the CTA.
-      const int hi_col = row_ok ? min(qpos, kv_len - 1) : -1;
+      const int hi_col = row_ok ? min(qpos, row_kv_len - 1) : -1;
       const int lo_col = (window > 0 && qpos - window + 1 > 0) ? qpos - window + 1 : 0;
-      const bool full_tile = key0 + PT_BN - 1 <= tile.q_pos0 && tile.nrows == PT_TQ &&
-                             (window <= 0 || tile.q_pos0 + PT_TQ - 1 - key0 < window);
+      const bool full_tile = key0 + PT_BN - 1 <= tile.q_pos0 && tile.nrows == PT_TQ && tile_b.nrows == PT_TQ &&
+                             (window <= 0 || tile_b.q_pos0 + PT_TQ - 1 - key0 < window);
       // pass 1: the row maximum (the scale is positive: max(s * c) = c * max(s)); four chains instead of one
       float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll 1
@@ -300,7 +310,7 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_
     const float inv = l_row > 0.f ? __fdiv_rn(1.0f, l_row) : 0.f;
     mbar_wait(smem_u32(&o_full), (it - 1) & 1);
     tc_fence_after();
-    bf16* dst = out + ((size_t)(tile.q_row0 + t) * nq + kvh * 2 + h) * PT_HD + kh * HALF;
+    bf16* dst = out + ((size_t)(mt.q_row0 + t) * nq + kvh * 2 + h) * PT_HD + kh * HALF;
 #pragma unroll 1
     for (int c0 = 0; c0 < HALF; c0 += 16) {
       uint32_t ov[16];
@@ -330,7 +340,7 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_
 // num_pages: pages in the pool k_pages / v_pages point to (the TMA maps cover exactly the pool).
 int launch_attn_prefill_tc(const bf16* q, const bf16* k_pages, const bf16* v_pages, int64_t num_pages, const int32_t* block_table,
                            int bt_stride, const PrefillTile* tiles_dev, int ntiles, bf16* out, int nq, int nkv, int hd, int block_size,
-                           cudaStream_t s, float softmax_scale, int window) {
+                           cudaStream_t s, float softmax_scale, int window, int pair_mode) {
   if (ntiles <= 0) return 0;
   B2_REQUIRE(hd == PT_HD && block_size == 16 && nq == 2 * nkv, "attn_prefill_tc: built for 128-wide heads in GQA groups of two, 16-token pages");
   B2_REQUIRE(num_pages >= 1, "attn_prefill_tc: the page pool's size is needed for the tensor maps");
@@ -345,8 +355,9 @@ int launch_attn_prefill_tc(const bf16* q, const bf16* k_pages, const bf16* v_pag
   if (attr_once.need()) B2_CUDA_OK(cudaFuncSetAttribute(attn_prefill_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PT_SMEM));
   const double scale = softmax_scale > 0.f ? (double)softmax_scale : 1.0 / sqrt((double)hd);
   const float scale_log2 = (float)(scale * 1.4426950408889634);
-  B2_CUDA_OK(b2_launch(attn_prefill_tc_kernel, dim3(ntiles, nkv), dim3(PT_THREADS), (size_t)PT_SMEM, s, tk, tv, q, block_table, bt_stride, tiles_dev,
-                       out, nq, nkv, scale_log2, window));
+  B2_REQUIRE(!pair_mode || ntiles % 2 == 0, "attn_prefill_tc: pair mode needs an even tile list (each sequence padded to an even number of tiles)");
+  B2_CUDA_OK(b2_launch(attn_prefill_tc_kernel, dim3(pair_mode ? ntiles / 2 : ntiles, nkv), dim3(PT_THREADS), (size_t)PT_SMEM, s, tk, tv, q, block_table,
+                       bt_stride, tiles_dev, out, nq, nkv, scale_log2, window, pair_mode));
   return 0;
 }
 

@@ -241,6 +241,7 @@ struct b2_engine {
   int prefill_tc = 1; // B2_PREFILL_TC: prefill attention on tcgen05 (attn_prefill_tc.cu); 0 = the mma.sync kernel (attn_prefill.cu)
   int l2_weight_prefetch = 0;  // B2_WPF: resid path, see forward_layers (measured slower: off)
   int prefill_resid_fused = 0;  // B2_RESID_FUSED: prefill O / down projections add into the residual stream in their epilogue (measured slower: off)
+  int prefill_pairs = 1;  // B2_PREFILL_PAIRS: see prefill_tile_pairs()
   int prefill_mc = 1;  // B2_MC: prefill projections as multicast CTA pairs (gemm_mc.cu)
   int gu_prefill_fused = 1;  // B2_GU_FUSED: prefill-sized gate/up projection with SwiGLU in its epilogue (gemm_gateup.cu)
   int use_pair = 1;   // B2_PAIR: bit 0 gate/up + SwiGLU, bit 1 QKV + QK-norm/RoPE/KV write as fused cluster-pair launches (gemm_pair.cu)
@@ -301,6 +302,10 @@ struct KL {
     }
   }
 };
+
+// Models with one query head per kv head run through the GQA-2 kernels with an all-zero partner head after every real one;
+// the tcgen05 prefill attention then pairs two 64-token tiles per CTA instead of (real, zero) heads.
+static bool prefill_tile_pairs(const b2_engine* e) { return e->prefill_tc && e->qhead_step == 2 && e->cfg.arch != B2_ARCH_OPT && e->prefill_pairs; }
 
 int bucket_batch(int B) {
   static const int bk[] = {1, 2, 4, 8, 16, 24, 32, 48, 64, 96, 128, 192, 256, 384, 512};
@@ -725,7 +730,7 @@ int forward_layers(b2_engine* e, const Lane& ln, int T, int ntiles) {
       if (!k.skip()) {
         if (e->prefill_tc)
           B2_TRY(launch_attn_prefill_tc(qrot, kp, vp, e->num_blocks, block_table, e->bt_stride, e->d_tiles, ntiles, attn, e->nq, e->nkv, e->hd,
-                                        c.block_size, st, e->attn_scale, c.sliding_window));
+                                        c.block_size, st, e->attn_scale, c.sliding_window, prefill_tile_pairs(e) ? 1 : 0));
         else
           B2_TRY(launch_attn_prefill(qrot, kp, vp, block_table, e->bt_stride, e->d_tiles, ntiles, attn,
                                      e->nq, e->nkv, e->hd, c.block_size, st, e->attn_scale, c.sliding_window));
@@ -1448,6 +1453,7 @@ extern "C" int b2_engine_create(const b2_config* cfg, const char* safetensors_pa
   e->prefill_tc = env_int("B2_PREFILL_TC", 1);
   e->gu_prefill_fused = env_int("B2_GU_FUSED", 1);
   e->prefill_mc = env_int("B2_MC", 1);
+  e->prefill_pairs = env_int("B2_PREFILL_PAIRS", 1);
   e->prefill_resid_fused = env_int("B2_RESID_FUSED", 0);
   e->l2_weight_prefetch = env_int("B2_WPF", 0);
   e->o_small_smem = env_int("B2_O_SMALL", 0);
@@ -1623,7 +1629,7 @@ extern "C" int b2_engine_create(const b2_config* cfg, const char* safetensors_pa
     E_TRY(dalloc(&e->d_token_log, (size_t)e->log_cap_steps * c.max_seqs));
     E_CUDA(cudaMemset(e->d_step, 0, 4));
     E_CUDA(cudaMemset(e->d_block_table, 0, Bcap * e->bt_stride * 4));
-    e->tiles_cap = (int)(Tc / 64 + Bcap + 16);
+    e->tiles_cap = (int)(Tc / 64 + 2 * Bcap + 16);
     E_TRY(dalloc(&e->d_tiles, (size_t)e->tiles_cap));
     e->h_stage_ints = std::max((size_t)3 * Tc + Bcap * (size_t)e->bt_stride + 4 * Bcap, (size_t)1 << 16);
     E_CUDA(cudaMallocHost(&e->h_stage, e->h_stage_ints * sizeof(int32_t)));
@@ -1895,9 +1901,14 @@ extern "C" int b2_prefill(b2_engine* e, const int32_t* ids, const int32_t* seq_o
     last[i] = row0 + n - 1;
     memset(bt + (size_t)i * e->bt_stride, 0, (size_t)e->bt_stride * 4);
     memcpy(bt + (size_t)i * e->bt_stride, s.blocks.data(), s.blocks.size() * 4);
+    const int first_tile = ntiles;
     for (int j = 0; j < n; j += 64) {
       B2_REQUIRE(ntiles < e->tiles_cap, "b2_prefill: too many attention tiles");
       e->h_tiles[ntiles++] = PrefillTile{row0 + j, s.len + j, std::min(64, n - j), i};
+    }
+    if (prefill_tile_pairs(e) && ((ntiles - first_tile) & 1)) {  // attn_prefill_tc.cu, pair mode: tiles 2i and 2i + 1 belong together
+      B2_REQUIRE(ntiles < e->tiles_cap, "b2_prefill: too many attention tiles");
+      e->h_tiles[ntiles++] = PrefillTile{row0, s.len + n, 0, i};
     }
     row0 += n;
   }

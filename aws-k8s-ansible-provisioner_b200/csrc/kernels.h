@@ -196,7 +196,7 @@ int launch_attn_prefill(const bf16* q, const bf16* k_pages, const bf16* v_pages,
 // ---- attn_prefill_tc.cu: the same pass on tcgen05 (S and P.V in TMEM, K/V pages through TMA); num_pages = size of the pool ----
 int launch_attn_prefill_tc(const bf16* q, const bf16* k_pages, const bf16* v_pages, int64_t num_pages, const int32_t* block_table,
                            int bt_stride, const PrefillTile* tiles_dev, int ntiles, bf16* out, int nq, int nkv, int hd, int block_size,
-                           cudaStream_t s, float softmax_scale = 0.f, int window = 0);
+                           cudaStream_t s, float softmax_scale = 0.f, int window = 0, int pair_mode = 0);
 
 // ---- sampling.cu ----
 struct SampleRow {  // one row to draw from (temperature <= 0: greedy arg-max, lowest index on ties)

@@ -7,7 +7,7 @@ import subprocess
 
 R = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(R, "aws-k8s-ansible-provisioner_b200", "libb2engine.so")
-PATS = ["UTCHMMA", "UTCBAR", "LDTM", "STTM", "UTMALDG", "UBLKCP", "HMMA", "LDGSTS", "SYNCS", "UCGABAR", "ACQBULK", "PREEXIT"]
+PATS = ["UTCHMMA", "UTCBAR", "LDTM", "STTM", "UTMALDG", "UTMASTG", "UBLKCP", "HMMA", "LDGSTS", "SYNCS", "UCGABAR", "ACQBULK", "PREEXIT"]
 
 sass = subprocess.run(["cuobjdump", "-sass", LIB], capture_output=True, text=True).stdout
 cur, cnt = None, collections.OrderedDict()
@@ -23,7 +23,7 @@ for line in sass.splitlines():
 names = list(cnt)
 dem = subprocess.run(["cu++filt"] + names, capture_output=True, text=True).stdout.splitlines()
 print("# SASS mnemonic counts per kernel of libb2engine.so (sm_100a), from: cuobjdump -sass libb2engine.so  (static instruction counts, loops not unrolled)")
-print("# UTCHMMA = tcgen05.mma (bf16), UTCBAR = tcgen05.commit, LDTM / STTM = tcgen05.ld / st, UTMALDG = TMA tensor load (cp.async.bulk.tensor),")
+print("# UTCHMMA = tcgen05.mma (bf16), UTCBAR = tcgen05.commit, LDTM / STTM = tcgen05.ld / st, UTMALDG / UTMASTG = TMA tensor load / store (cp.async.bulk.tensor),")
 print("# UBLKCP = cp.async.bulk, HMMA = mma.sync, LDGSTS = cp.async, SYNCS = mbarrier ops, UCGABAR = barrier.cluster,")
 print("# ACQBULK = griddepcontrol.wait, PREEXIT = griddepcontrol.launch_dependents")
 print("# template arguments: linear_tc_kernel<BN tokens, EPI, SMALL, XCP>; linear_pair_kernel<BN, MODE 0 SwiGLU / 1 QKV+RoPE>; linear_resid_kernel<BN>;")

@@ -19,9 +19,11 @@ def _peak():
 
 
 PEAK = _peak()
+CHUNK_TOKENS = int(os.environ.get("B2_BENCH_CHUNK", "32768"))  # tokens per prefill call (bench.py's default)
+ONLY = os.environ.get("B2_VARIANTS", "c3,c4").split(",")
 
 def run(tag, arch, sd, B, PL, new, chunk, inv=None):
-    cfg = engine_config_from_arch(P, arch, max_model_len=PL + new + 16, max_seqs=B, max_batch_tokens=8192, use_cuda_graphs=True)
+    cfg = engine_config_from_arch(P, arch, max_model_len=PL + new + 16, max_seqs=B, max_batch_tokens=CHUNK_TOKENS, use_cuda_graphs=True)
     cfg.num_blocks = B * ((cfg.max_model_len + 15) // 16) + 8
     e = P.Engine(cfg, rope_inv_freq=inv)
     e.load_state_dict(sd)
@@ -44,5 +46,7 @@ def run(tag, arch, sd, B, PL, new, chunk, inv=None):
                       "prefill_tok_s": B * PL / tp}), flush=True)
     e.close()
 
-run("C3 OPT-125m", OPT_125M, opt_weights(OPT_125M, 3), 256, 128, 136, 64)
-run("C4 Phi-3-mini-4k", PHI3_MINI, phi3_weights(PHI3_MINI, 4), 32, 2048, 72, 4, phi3_inv_freq(PHI3_MINI).numpy())
+if "c3" in ONLY:
+    run("C3 OPT-125m", OPT_125M, opt_weights(OPT_125M, 3), 256, 128, 136, max(1, CHUNK_TOKENS // 128))
+if "c4" in ONLY:
+    run("C4 Phi-3-mini-4k", PHI3_MINI, phi3_weights(PHI3_MINI, 4), 32, 2048, 72, max(1, CHUNK_TOKENS // 2048), phi3_inv_freq(PHI3_MINI).numpy())
