@@ -114,6 +114,12 @@ extern "C" int b2k_qkv_rope(const void* x, const void* w_qkv, const void* qnorm_
   B2_REQUIRE(x && w_qkv && q_out && k_pages && v_pages, "b2k_qkv_rope: null pointer");
   CUtensorMap tm;
   CAPI_TRY(b2_make_tmap_bf16(&tm, w_qkv, (uint64_t)(nq + 2 * nkv) * 128, (uint64_t)K, (uint64_t)K, 128));
+  if (T > 64) {  // prefill-sized: gemm_mc.cu, ROPE variant
+    CUtensorMap tx;
+    CAPI_TRY(b2_make_tmap_bf16(&tx, x, (uint64_t)T, (uint64_t)K, (uint64_t)K, 128));
+    return launch_qkv_rope_prefill(tm, tx, (const bf16*)qnorm_w, (const bf16*)knorm_w, (const bf16*)cos_sin, positions, slots, (bf16*)q_out,
+                                   (bf16*)k_pages, (bf16*)v_pages, T, nq, nkv, K, block_size, eps, 0, (cudaStream_t)stream);
+  }
   return launch_qkv_rope(tm, (const bf16*)x, (const bf16*)qnorm_w, (const bf16*)knorm_w, (const bf16*)cos_sin, positions, slots, (bf16*)q_out,
                          (bf16*)k_pages, (bf16*)v_pages, T, nq, nkv, K, block_size, eps, (cudaStream_t)stream);
 }

@@ -241,6 +241,7 @@ struct b2_engine {
   int prefill_tc = 1; // B2_PREFILL_TC: prefill attention on tcgen05 (attn_prefill_tc.cu); 0 = the mma.sync kernel (attn_prefill.cu)
   int l2_weight_prefetch = 0;  // B2_WPF: resid path, see forward_layers (measured slower: off)
   int prefill_resid_fused = 0;  // B2_RESID_FUSED: prefill O / down projections add into the residual stream in their epilogue (measured slower: off)
+  int qkv_rope_prefill_fused = 0;  // B2_QKV_ROPE_FUSED: prefill QKV projection finishes norm / RoPE / page write itself
   int prefill_pairs = 1;  // B2_PREFILL_PAIRS: see prefill_tile_pairs()
   int prefill_mc = 1;  // B2_MC: prefill projections as multicast CTA pairs (gemm_mc.cu)
   int gu_prefill_fused = 1;  // B2_GU_FUSED: prefill-sized gate/up projection with SwiGLU in its epilogue (gemm_gateup.cu)
@@ -713,7 +714,14 @@ int forward_layers(b2_engine* e, const Lane& ln, int T, int ntiles) {
       if (!k.skip()) B2_TRY(launch_add_rmsnorm(h, delta, L.ln1, x, T, H, c.rms_eps, st, tag));
     }
     if (l > 0) dbg_capture(e, l, e->h, T);
-    if (qkv_pair) {
+    const bool qkv_prefill_fused = ntiles > 0 && e->qkv_rope_prefill_fused && e->prefill_mc && e->force_gemm_impl != 0 && c.arch == B2_ARCH_QWEN3 &&
+                                   e->native_geom && e->rotary_dim == 128 && L.qnorm != nullptr && linear_mc_shapes_ok(T, e->qkv_size, H) &&
+                                   !((e->skip_mask >> B2K_ROPE_KV) & 1u) && !((e->skip_mask >> B2K_GEMM_QKV) & 1u);
+    if (qkv_prefill_fused) {
+      KL k(e, B2K_GEMM_QKV);  // prefill: QK-norm + RoPE + page write in the QKV projection's epilogue (gemm_mc.cu)
+      B2_TRY(launch_qkv_rope_prefill(L.tm_qkv, e->tm_x[XB_X][bn_index(128)], L.qnorm, L.knorm, e->cos_sin, positions, slots, qrot, kp, vp, T, e->nq,
+                                     e->nkv, H, c.block_size, c.rms_eps, ln.row0, st));
+    } else if (qkv_pair) {
       KL k(e, B2K_GEMM_QKV);
       if (!k.skip())
         B2_TRY(launch_qkv_rope(L.tm_qkv, (resid && l > 0) ? h : x, L.qnorm, L.knorm, e->cos_sin, positions, slots, qrot, kp, vp, T, e->nq, e->nkv, H,
@@ -1454,6 +1462,7 @@ extern "C" int b2_engine_create(const b2_config* cfg, const char* safetensors_pa
   e->gu_prefill_fused = env_int("B2_GU_FUSED", 1);
   e->prefill_mc = env_int("B2_MC", 1);
   e->prefill_pairs = env_int("B2_PREFILL_PAIRS", 1);
+  e->qkv_rope_prefill_fused = env_int("B2_QKV_ROPE_FUSED", 0);
   e->prefill_resid_fused = env_int("B2_RESID_FUSED", 0);
   e->l2_weight_prefetch = env_int("B2_WPF", 0);
   e->o_small_smem = env_int("B2_O_SMALL", 0);

@@ -98,6 +98,9 @@ bool pair_shapes_ok(int T, int K);
 // gemm_mc.cu: prefill-sized bf16 projection, two CTAs per cluster share the token tile through TMA multicast
 bool linear_mc_shapes_ok(int T, int N, int K);
 int launch_linear_mc(const CUtensorMap& tm_w, const CUtensorMap& tm_x128, bf16* out, int T, int N, int K, int x_row0, cudaStream_t s);
+int launch_qkv_rope_prefill(const CUtensorMap& tm_qkv, const CUtensorMap& tm_x128, const bf16* qw, const bf16* kw, const bf16* cos_sin,
+                            const int32_t* positions, const int32_t* slots, bf16* q_out, bf16* k_pages, bf16* v_pages, int T, int nq, int nkv,
+                            int K, int block_size, float eps, int x_row0, cudaStream_t s);
 // gemm_gateup.cu: the prefill-sized counterpart (two accumulators per tile, SwiGLU in the epilogue)
 bool gateup_prefill_shapes_ok(int T, int I, int K);
 int launch_gateup_swiglu_prefill(const CUtensorMap& tm_w, const CUtensorMap& tm_x128, bf16* act, int T, int I, int K, int x_row0, cudaStream_t s);

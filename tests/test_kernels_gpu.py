@@ -419,7 +419,7 @@ def test_gateup_swiglu_prefill_fused(lib, T, I, K):
     assert rel_fro(act[rows], ref) < 5e-3 and rel_err(act[rows], ref) < 1e-2, (rel_fro(act[rows], ref), rel_err(act[rows], ref))
 
 
-@pytest.mark.parametrize("T", [64, 40, 17, 1])
+@pytest.mark.parametrize("T", [64, 40, 17, 1, 512, 777])  # > 64 tokens: the prefill-sized kernel (gemm_mc.cu, ROPE epilogue)
 def test_qkv_rope_fused(lib, T):
     """gemm_pair.cu: QKV projection + QK-norm + RoPE + KV page write in one launch, against b2k_linear followed by
     b2k_qknorm_rope_kv (the path it replaces) and against the oracle's functions."""
@@ -468,11 +468,13 @@ def test_qkv_rope_fused(lib, T):
     kn = rms_norm(k, kw, 1e-6).transpose(1, 2)
     c, s_ = rope_cos_sin(a, positions[None, :].long())
     qr, kr = apply_rope(qn, kn, c, s_)
-    assert_bf16_close(qf, qr.transpose(1, 2).reshape(T, nq * hd), 2, 0.05, "q vs oracle", abs_floor=0.02)
+    # (a million elements at T >= 512: the rare q whose projection sum lands a full input ulp away at magnitude 4..8 -- 2^-5 --
+    # and whose RoPE terms cancel needs a floor of two input ulps at the common magnitude)
+    assert_bf16_close(qf, qr.transpose(1, 2).reshape(T, nq * hd), 2, 0.05, "q vs oracle", abs_floor=0.02 if T <= 64 else 0.04)
     for t in range(T):
         sl = int(slots[t])
         if sl >= 0:
-            assert_bf16_close(kf[sl // bs, :, sl % bs, :], kr.transpose(1, 2)[0][t], 2, 0.08, "k page vs oracle t=%d" % t, abs_floor=0.02)
+            assert_bf16_close(kf[sl // bs, :, sl % bs, :], kr.transpose(1, 2)[0][t], 2, 0.08, "k page vs oracle t=%d" % t, abs_floor=0.02 if T <= 64 else 0.04)
     written = {int(v) for v in slots if v >= 0}
     for sl in range(nblocks * bs):
         if sl not in written:
