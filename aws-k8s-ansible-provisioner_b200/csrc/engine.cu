@@ -241,7 +241,7 @@ struct b2_engine {
   int prefill_tc = 1; // B2_PREFILL_TC: prefill attention on tcgen05 (attn_prefill_tc.cu); 0 = the mma.sync kernel (attn_prefill.cu)
   int l2_weight_prefetch = 0;  // B2_WPF: resid path, see forward_layers (measured slower: off)
   int prefill_resid_fused = 0;  // B2_RESID_FUSED: prefill O / down projections add into the residual stream in their epilogue (measured slower: off)
-  int qkv_rope_prefill_fused = 0;  // B2_QKV_ROPE_FUSED: prefill QKV projection finishes norm / RoPE / page write itself
+  int qkv_rope_prefill_fused = 1;  // B2_QKV_ROPE_FUSED: prefill QKV projection finishes norm / RoPE / page write itself
   int prefill_pairs = 1;  // B2_PREFILL_PAIRS: see prefill_tile_pairs()
   int prefill_mc = 1;  // B2_MC: prefill projections as multicast CTA pairs (gemm_mc.cu)
   int gu_prefill_fused = 1;  // B2_GU_FUSED: prefill-sized gate/up projection with SwiGLU in its epilogue (gemm_gateup.cu)
@@ -1462,7 +1462,7 @@ extern "C" int b2_engine_create(const b2_config* cfg, const char* safetensors_pa
   e->gu_prefill_fused = env_int("B2_GU_FUSED", 1);
   e->prefill_mc = env_int("B2_MC", 1);
   e->prefill_pairs = env_int("B2_PREFILL_PAIRS", 1);
-  e->qkv_rope_prefill_fused = env_int("B2_QKV_ROPE_FUSED", 0);
+  e->qkv_rope_prefill_fused = env_int("B2_QKV_ROPE_FUSED", 1);
   e->prefill_resid_fused = env_int("B2_RESID_FUSED", 0);
   e->l2_weight_prefetch = env_int("B2_WPF", 0);
   e->o_small_smem = env_int("B2_O_SMALL", 0);

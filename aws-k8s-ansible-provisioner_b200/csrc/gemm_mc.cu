@@ -28,6 +28,9 @@ constexpr int MC_STAGES = 4;
 constexpr int MC_OUT_ROWS = 32;                               // tokens per output staging buffer
 constexpr int MC_OUT_BYTES = MC_OUT_ROWS * MC_BM * 2;         // 8 KB: [32 tokens][128 features] bf16
 constexpr int MC_SMEM_BYTES = MC_STAGES * MC_STAGE_BYTES + 2 * MC_OUT_BYTES + 1024;
+constexpr int MC_ROPE_GROUPS = 4;                             // ROPE variant: epilogue warp groups (four warps each)
+constexpr int MC_ROPE_ROWS = 16;                              // ... and tokens per staged block (4 KB; the groups' blocks fill the two 8 KB buffers)
+constexpr int MC_ROPE_THREADS = 64 + 128 * MC_ROPE_GROUPS;
 
 __device__ __forceinline__ uint32_t mc_cluster_rank() {
   uint32_t r;
@@ -52,8 +55,8 @@ __device__ __forceinline__ void mc_cluster_sync() {
 
 // ROPE variant (QKV projection of a Qwen3-geometry prefill: one 128-wide head per weight-row tile): the staged 32-token block
 // is not stored as it is but finished as qknorm_rope_kv does -- per-head RMS norm of q and k, RoPE, then q through a TMA store
-// into q_out and k / v as 16-byte chunks into their cache pages -- by EIGHT epilogue warps in two groups that take alternate
-// blocks (the tail is ~100 instructions per 8 dims: four warps would make the epilogue longer than the main loop).  Arithmetic
+// into q_out and k / v as 16-byte chunks into their cache pages -- by SIXTEEN epilogue warps in four groups that take every
+// fourth 16-token block (the tail is ~150 instructions per 8 dims: with eight warps the epilogue was longer than the main loop).  Arithmetic
 // and rounding points are those of the decode step's fused QKV kernel (gemm_pair.cu): sixteen threads per token, eight dims each,
 // RoPE partner dims +-64 read from the staged block, sum of squares over four shuffles.
 struct McRope {
@@ -66,7 +69,7 @@ struct McRope {
 
 // grid = 2 * clusters; cluster c walks the (weight-tile pair, token tile) list with stride `clusters`, the pair index fastest.
 template <bool ROPE>
-__global__ void __launch_bounds__(ROPE ? 320 : 192, 1)
+__global__ void __launch_bounds__(ROPE ? MC_ROPE_THREADS : 192, 1)
 linear_mc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_out,
                  int T, int N, int K, int m_pairs, int n_tiles, int x_row0, const McRope rp) {
   extern __shared__ uint8_t smem_raw[];
@@ -91,7 +94,7 @@ linear_mc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(smem_u32(&tmem_full_bar[a]), 1);
-      mbar_init(smem_u32(&tmem_empty_bar[a]), ROPE ? 256 : 128);
+      mbar_init(smem_u32(&tmem_empty_bar[a]), ROPE ? MC_ROPE_THREADS - 64 : 128);
     }
     mbar_fence_init();
   }
@@ -204,14 +207,15 @@ linear_mc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
     if (et == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // the last stores have left shared memory AND are complete
     } else {
     // ---- ROPE epilogue ----
-    constexpr int HD = 128;
-    const int q = warp & 3, g = (warp - 2) >> 2;  // TMEM lane quarter; which of the two groups (even / odd 32-token blocks)
-    const int et = threadIdx.x - 64;              // 0..255 over both groups
+    constexpr int HD = 128, RB = MC_ROPE_ROWS, NG = MC_ROPE_GROUPS, NE = 128 * NG;
+    constexpr int IPT = RB * 16 / 128;            // (token, 8-dim part) items per thread and block: 2
+    const int q = warp & 3, g = (warp - 2) >> 2;  // TMEM lane quarter; group 0..3 (blocks g, g + 4, g + 8, ...)
+    const int et = threadIdx.x - 64;              // 0..511 over the groups
     const int eg = et & 127;                      // 0..127 within the group
     const int part = eg & 15;                     // this thread's eight dims of a token: 8 part .. 8 part + 7
     const int d0 = part * 8;
-    const uint32_t obuf = smem_base + MC_STAGES * MC_STAGE_BYTES + (uint32_t)(g * MC_OUT_BYTES);
-    uint8_t* ob_p = smem_raw + (smem_base - smem_u32(smem_raw)) + MC_STAGES * MC_STAGE_BYTES + g * MC_OUT_BYTES;
+    const uint32_t obuf = smem_base + MC_STAGES * MC_STAGE_BYTES + (uint32_t)(g * RB * HD * 2);
+    uint8_t* ob_p = smem_raw + (smem_base - smem_u32(smem_raw)) + MC_STAGES * MC_STAGE_BYTES + g * RB * HD * 2;
     if (et < 32) reinterpret_cast<uint4*>(s_gain)[et] = reinterpret_cast<const uint4*>(et < 16 ? rp.qw : rp.kw)[et & 15];
     const uint32_t sign = d0 < 64 ? 0x80008000u : 0u;  // dims 0..63: rot = -partner
     int lt = 0;
@@ -219,34 +223,34 @@ linear_mc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
       const int head = 2 * (p % m_pairs) + (int)rank, n_tile = p / m_pairs;
       const bool is_q = head < rp.nq, is_k = !is_q && head < rp.nq + rp.nkv;
       const int tok0 = n_tile * MC_BN;
-      // both groups are done with the previous tile's positions / slots; then this tile's
-      asm volatile("bar.sync 3, 256;" ::: "memory");
-      {
+      // every group is done with the previous tile's positions / slots; then this tile's
+      asm volatile("bar.sync 5, %0;" ::"n"(NE) : "memory");
+      if (et < MC_BN) {
         const int tok = tok0 + et;
         s_pos[et] = tok < T ? max(rp.positions[tok], 0) : 0;
         s_slot[et] = tok < T ? rp.slots[tok] : -1;
       }
-      asm volatile("bar.sync 3, 256;" ::: "memory");
+      asm volatile("bar.sync 5, %0;" ::"n"(NE) : "memory");
       const int as = lt & 1;
       mbar_wait(smem_u32(&tmem_full_bar[as]), (lt >> 1) & 1);
       tc_fence_after();
       const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * MC_BN);
 #pragma unroll 1
-      for (int c0 = g * MC_OUT_ROWS; c0 < MC_BN; c0 += 2 * MC_OUT_ROWS) {
-        // the RoPE table rows of this thread's four tokens: requested now, used after the block is staged
-        uint4 co[4], sn[4];
+      for (int c0 = g * RB; c0 < MC_BN; c0 += NG * RB) {
+        // the RoPE table rows of this thread's tokens: requested now, used after the block is staged
+        uint4 co[IPT], sn[IPT];
         if (is_q || is_k) {
 #pragma unroll
-          for (int k = 0; k < 4; ++k) {
+          for (int k = 0; k < IPT; ++k) {
             const bf16* cs = rp.cos_sin + (size_t)s_pos[c0 + (eg >> 4) + 8 * k] * HD + (d0 & 63);
             co[k] = *reinterpret_cast<const uint4*>(cs);
             sn[k] = *reinterpret_cast<const uint4*>(cs + 64);
           }
         }
-        uint32_t r[32];
-        tmem_ld32(tbase + (uint32_t)c0, r);
+        uint32_t r[RB];
+        tmem_ld16(tbase + (uint32_t)c0, r);
         tmem_ld_wait();
-        if (c0 + 2 * MC_OUT_ROWS >= MC_BN) {  // this group's last block of the tile: its share of the accumulator is out
+        if (c0 + NG * RB >= MC_BN) {  // this group's last block of the tile: its share of the accumulator is out
           tc_fence_before();
           mbar_arrive(smem_u32(&tmem_empty_bar[as]));
         }
@@ -255,12 +259,12 @@ linear_mc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
         {
           unsigned short* ob = reinterpret_cast<unsigned short*>(ob_p) + q * 32 + lane;
 #pragma unroll
-          for (int j = 0; j < 32; ++j) ob[j * MC_BM] = __bfloat16_as_ushort(__float2bfloat16_rn(__uint_as_float(r[j])));
+          for (int j = 0; j < RB; ++j) ob[j * MC_BM] = __bfloat16_as_ushort(__float2bfloat16_rn(__uint_as_float(r[j])));
         }
         asm volatile("bar.sync %0, 128;" ::"r"(1 + g) : "memory");
-        uint4 res[4];
+        uint4 res[IPT];
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
+        for (int k = 0; k < IPT; ++k) {
           const int j = (eg >> 4) + 8 * k;  // token of the block; the 16 threads of a token are 16 consecutive lanes
           uint4 raw = *reinterpret_cast<const uint4*>(ob_p + j * 256 + part * 16);
           if (is_q || is_k) {
@@ -300,7 +304,7 @@ linear_mc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
           // back into the staged block (every thread has read its partner's dims: barrier first), then one bulk store
           asm volatile("bar.sync %0, 128;" ::"r"(1 + g) : "memory");
 #pragma unroll
-          for (int k = 0; k < 4; ++k) *reinterpret_cast<uint4*>(ob_p + ((eg >> 4) + 8 * k) * 256 + part * 16) = res[k];
+          for (int k = 0; k < IPT; ++k) *reinterpret_cast<uint4*>(ob_p + ((eg >> 4) + 8 * k) * 256 + part * 16) = res[k];
           fence_proxy_async();
           asm volatile("bar.sync %0, 128;" ::"r"(1 + g) : "memory");
           if (eg == 0) {
@@ -313,7 +317,7 @@ linear_mc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
           const int kvh = is_k ? head - rp.nq : head - rp.nq - rp.nkv;
           bf16* pages = is_k ? rp.k_pages : rp.v_pages;
 #pragma unroll
-          for (int k = 0; k < 4; ++k) {
+          for (int k = 0; k < IPT; ++k) {
             const int j = (eg >> 4) + 8 * k;
             const int slot = s_slot[c0 + j];
             if (slot >= 0) {
@@ -353,7 +357,7 @@ static int launch_mc(const CUtensorMap& tm_w, const CUtensorMap& tm_x128, const 
   const int clusters = total < sms / 2 ? total : sms / 2;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(2 * clusters);
-  cfg.blockDim = dim3(ROPE ? 320 : 192);
+  cfg.blockDim = dim3(ROPE ? MC_ROPE_THREADS : 192);
   cfg.dynamicSmemBytes = MC_SMEM_BYTES;
   cfg.stream = s;
   cudaLaunchAttribute attr[2];
@@ -390,9 +394,9 @@ int launch_qkv_rope_prefill(const CUtensorMap& tm_qkv, const CUtensorMap& tm_x12
   if (T <= 0) return 0;
   const int N = (nq + 2 * nkv) * 128;
   B2_REQUIRE(linear_mc_shapes_ok(T, N, K) && qw != nullptr && kw != nullptr, "qkv_rope_prefill: T=%d N=%d K=%d not built, or no QK-norm gains", T, N, K);
-  CUtensorMap tm_q;  // q_out [T][nq * 128], box one head x 32 tokens
+  CUtensorMap tm_q;  // q_out [T][nq * 128], box one head x 16 tokens
   {
-    const int rc = b2_make_tmap_bf16_ex(&tm_q, q_out, (uint64_t)T, (uint64_t)nq * 128, (uint64_t)nq * 128, MC_BM, MC_OUT_ROWS, /*swizzle128=*/0);
+    const int rc = b2_make_tmap_bf16_ex(&tm_q, q_out, (uint64_t)T, (uint64_t)nq * 128, (uint64_t)nq * 128, MC_BM, MC_ROPE_ROWS, /*swizzle128=*/0);
     if (rc != 0) return rc;
   }
   McRope rp = {qw, kw, cos_sin, positions, slots, k_pages, v_pages, nq, nkv, block_size, eps};
