@@ -10,7 +10,7 @@ B, P, N = 64, 512, 256
 
 def start():
     proc = subprocess.Popen([EXE, "--load-format", "dummy", "--served-model-name", "Qwen/Qwen3-0.6B", "--port", "0", "--host", "127.0.0.1",
-                             "--max-model-len", "1024", "--max-num-seqs", "64", "--max-num-batched-tokens", "8192", "--eos-token-id", "-1"],
+                             "--max-model-len", "1024", "--max-num-seqs", "64", "--max-num-batched-tokens", "32768", "--eos-token-id", "-1"],
                             stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
     t0 = time.time()
     while time.time() - t0 < 180:
